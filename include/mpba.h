@@ -1,0 +1,223 @@
+/* mpba.h -- C ABI of the B200-native bundle-adjustment engine (libmpba.so).
+ *
+ * The reference reaches its solver through pybind11 objects, not a C ABI:
+ *   mpsfm/sfm/mapper/bundle_adjustment.py:104      pycolmap.create_default_bundle_adjuster
+ *   mpsfm/sfm/mapper/bundle_adjustment.py:163-176  pycolmap.create_depth_bundle_adjuster (fork only)
+ *   mpsfm/sfm/mapper/bundle_adjustment.py:114-122  pyceres constant blocks / manifolds
+ *   mpsfm/sfm/mapper/bundle_adjustment.py:285-293  pyceres.solve (SPARSE_SCHUR, Ceres defaults)
+ * This header is the boundary a maintainer binds instead (ctypes stub in INTEGRATION.md).
+ * One `mpba_problem` is the array form of the Ceres problem those calls assemble.
+ *
+ * Conventions
+ *   - every pointer inside mpba_problem / workspace is a DEVICE pointer owned by the caller
+ *     (PyTorch tensors in this repo); the library never allocates device memory,
+ *   - all floating point data is IEEE double, all indices int32,
+ *   - every call returns 0 on success or a negative MPBA_E_* code; the message is available from
+ *     mpba_last_error(); nothing throws across the boundary,
+ *   - a handle is bound to one device and one stream and is not thread-safe,
+ *   - there is no CPU fallback: without a CUDA device mpba_create fails with MPBA_E_CUDA.
+ */
+#ifndef MPBA_H_
+#define MPBA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPBA_VERSION 100
+
+enum {
+  MPBA_OK = 0,
+  MPBA_E_INVALID = -1,   /* bad argument / inconsistent problem */
+  MPBA_E_CUDA = -2,      /* CUDA runtime error (message has the cudaError string) */
+  MPBA_E_WORKSPACE = -3, /* workspace too small */
+  MPBA_E_NUMERIC = -4,   /* non-finite value met where the algorithm cannot continue */
+  MPBA_E_NCCL = -5
+};
+
+/* COLMAP camera model ids (pycolmap.CameraModelId; upstream colmap/sensor/models.h) */
+enum {
+  MPBA_SIMPLE_PINHOLE = 0, MPBA_PINHOLE = 1, MPBA_SIMPLE_RADIAL = 2, MPBA_RADIAL = 3, MPBA_OPENCV = 4,
+  MPBA_OPENCV_FISHEYE = 5, MPBA_FULL_OPENCV = 6, MPBA_FOV = 7, MPBA_SIMPLE_RADIAL_FISHEYE = 8,
+  MPBA_RADIAL_FISHEYE = 9, MPBA_THIN_PRISM_FISHEYE = 10
+};
+
+/* Ceres loss functions reachable from bundle_adjustment.py:44-48,:100 (+ Huber, north star) */
+enum { MPBA_LOSS_TRIVIAL = 0, MPBA_LOSS_SOFT_L1 = 1, MPBA_LOSS_CAUCHY = 2, MPBA_LOSS_HUBER = 3 };
+
+/* Ceres TerminationType */
+enum { MPBA_CONVERGENCE = 0, MPBA_NO_CONVERGENCE = 1, MPBA_FAILURE = 2 };
+
+#define MPBA_MAX_CAMERA_PARAMS 12
+
+/* One bundle-adjustment problem.  C images (poses), K cameras (intrinsics, constant:
+ * bundle_adjustment.py:92-94), P points3D, N observations.
+ *
+ * Observations are given twice, in the two orders the two reduction keys need:
+ *   track order  ("pm"): grouped by point3D, pt_ptr[p]..pt_ptr[p+1]; inside a track sorted by image,
+ *   image order  ("cm"): grouped by image,   img_ptr[i]..img_ptr[i+1].
+ * Both orders hold the same N observations; *_src map each slot back to the caller's
+ * (natural) observation index, and is what makes the per-residual outputs comparable bit for bit.
+ * A depth prior is attached to an observation by depth weight w > 0 (w == 0: no prior row).
+ */
+typedef struct mpba_problem {
+  int32_t num_images, num_cameras, num_points, num_obs;
+
+  /* images: pose[i] = {qx,qy,qz,qw,tx,ty,tz,unused}  (Eigen quaternion order, cam_from_world) */
+  double* img_pose;             /* [C][8]  in/out */
+  const int32_t* img_camera;    /* [C]     row of cam_model / cam_params */
+  const uint8_t* img_free_mask; /* [C]     bit j: tangent coordinate j free (0-2 rot, 3-5 trans) */
+  const double* img_shift_scale;/* [C][2]  depth prior (shift b, log-scale s), constant blocks */
+  const int32_t* cam_model;     /* [K] */
+  const double* cam_params;     /* [K][12] */
+
+  /* points3D: {x,y,z,unused} */
+  double* pt_xyz;               /* [P][4]  in/out */
+  const uint8_t* pt_const;      /* [P]     1 = constant parameter block */
+
+  /* track order */
+  const int32_t* pt_ptr;        /* [P+1] */
+  const int32_t* pm_img;        /* [N] */
+  const double* pm_xy;          /* [N][2] */
+  const double* pm_depth;       /* [3][N]  rows d, w, a  (prior depth, ScaledLoss weight, loss scale) */
+  const int32_t* pm_src;        /* [N]     natural observation index */
+
+  /* image order */
+  const int32_t* img_ptr;       /* [C+1] */
+  const int32_t* cm_pt;         /* [N] */
+  const double* cm_xy;          /* [N][2] */
+  const double* cm_depth;       /* [3][N] */
+  /* image-order work chunks (at most MPBA_CHUNK observations of one image each) */
+  int32_t num_chunks;
+  const int32_t* chunk_img;     /* [num_chunks] */
+  const int32_t* chunk_begin;   /* [num_chunks] first slot (image order) */
+  const int32_t* chunk_end;     /* [num_chunks] */
+  const int32_t* img_chunk_ptr; /* [C+1] chunks of image i = img_chunk_ptr[i]..img_chunk_ptr[i+1] */
+
+  /* reduced camera system: block-CSR over co-visible image pairs, full (both triangles),
+   * columns sorted inside a row; 6x6 row-major blocks */
+  int32_t num_blocks;
+  const int32_t* s_row_ptr;     /* [C+1] */
+  const int32_t* s_col;         /* [B] */
+  const int32_t* s_diag;        /* [C]   block index of (i,i) */
+  const int32_t* s_transpose;   /* [B]   block index of (j,i) for block (i,j) */
+  /* for every track, every slot pair a<=b (row-major over a, then b): index of block
+   * (pm_img[a], pm_img[b]); pair_ptr[p] = first pair of track p */
+  const int32_t* pair_ptr;      /* [P+1] */
+  const int32_t* pair_block;    /* [pair_ptr[P]] */
+
+  /* losses: ScaledLoss(loss(scale), weight) shared by all reprojection blocks
+   * (bundle_adjustment.py:98-102); per-observation scale/weight for depth (:160-161) */
+  int32_t reproj_loss, depth_loss;
+  double reproj_loss_scale, reproj_loss_weight;
+
+  /* MPBA_FLAG_*; STRUCTURE_ONLY: every image pose is constant (refine_3d_points,
+   * bundle_adjustment.py:276-283) -- the normal equations are block diagonal in the points and
+   * the reduced camera system is skipped */
+  int32_t flags;
+  int32_t reserved;
+} mpba_problem;
+
+#define MPBA_FLAG_STRUCTURE_ONLY 1
+
+#define MPBA_CHUNK 1024
+
+/* Ceres Solver::Options subset; defaults (mpba_default_options) are Ceres 2.1's, which is what the
+ * reference runs with (bundle_adjustment.py:285-293 sets only solver type / threads / verbosity). */
+typedef struct mpba_options {
+  int32_t max_num_iterations;              /* 50 */
+  int32_t max_num_consecutive_invalid_steps; /* 5 */
+  int32_t jacobi_scaling;                  /* 1 */
+  int32_t pcg_max_iterations;              /* 2000 */
+  double initial_trust_region_radius;      /* 1e4 */
+  double max_trust_region_radius;          /* 1e16 */
+  double min_trust_region_radius;          /* 1e-32 */
+  double min_relative_decrease;            /* 1e-3 */
+  double min_lm_diagonal;                  /* 1e-6 */
+  double max_lm_diagonal;                  /* 1e32 */
+  double function_tolerance;               /* 1e-6 */
+  double gradient_tolerance;               /* 1e-10 */
+  double parameter_tolerance;              /* 1e-8 */
+  double pcg_tolerance;                    /* 1e-12: stop when sqrt(r'M^-1 r / b'M^-1 b) <= tol */
+  int32_t profile;                         /* 1: CUDA-event time every kernel launch (see mpba_kernel_times) */
+  int32_t verbose;
+} mpba_options;
+
+/* ceres::IterationSummary subset, one row per LM iteration (row 0 = initial evaluation) */
+typedef struct mpba_iteration {
+  double cost;               /* includes fixed_cost */
+  double cost_change;
+  double gradient_max_norm;
+  double step_norm;
+  double relative_decrease;
+  double trust_region_radius;
+  int32_t step_is_valid, step_is_successful;
+  int32_t pcg_iterations;
+  int32_t reserved;
+} mpba_iteration;
+
+typedef struct mpba_summary {
+  double initial_cost, final_cost, fixed_cost;
+  int32_t termination;       /* MPBA_CONVERGENCE / NO_CONVERGENCE / FAILURE */
+  int32_t num_iterations;    /* rows filled in `iterations` minus 1 = LM iterations run */
+  int32_t num_successful_steps, num_unsuccessful_steps;
+  int64_t total_pcg_iterations;
+  int64_t kernel_launches;   /* kernels this call launched */
+  double solve_ms;           /* device time of the whole call (CUDA events) */
+  mpba_iteration* iterations;/* HOST buffer with capacity rows, caller-owned; may be NULL */
+  int32_t capacity;
+  int32_t reserved;
+  char message[128];
+} mpba_summary;
+
+/* names of the kernels for mpba_kernel_times, in slot order */
+#define MPBA_NUM_KERNELS 12
+
+typedef struct mpba_handle mpba_handle;
+
+int mpba_version(void);
+
+/* lifetime */
+int mpba_create(mpba_handle** out, int device, void* cuda_stream /* cudaStream_t or NULL */);
+void mpba_destroy(mpba_handle* h);
+const char* mpba_last_error(const mpba_handle* h);
+void mpba_default_options(mpba_options* opt);
+
+/* bytes of device workspace mpba_* calls need for this problem */
+int mpba_workspace_bytes(const mpba_problem* prob, size_t* bytes);
+
+/* Residuals at the current state, in TRACK order: reproj [N][2], depth [N] (0 where no prior);
+ * cost[0] = 1/2 sum rho over blocks with a free parameter block, cost[1] = fixed cost.
+ * Output pointers are device pointers; NULL skips that output.  cost is a HOST pointer. */
+int mpba_evaluate(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
+                  double* r_reproj, double* r_depth, double* cost);
+
+/* Normal-equation blocks at the current state (unscaled, undamped), device outputs:
+ * Hcc [C][36], gc [C][6], Hpp [P][6] (xx,xy,xz,yy,yz,zz), gp [P][3]; cost as above. */
+int mpba_linearize(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
+                   double* Hcc, double* gc, double* Hpp, double* gp, double* cost);
+
+/* Reduced camera system for LM damping lambda_j = clamp(c_j^2 H_jj)/ (radius c_j^2) with Jacobi
+ * scaling c taken at the current state: S [B][36], rhs [C][6], and its PCG solution y [C][6]
+ * (any may be NULL).  pcg_iterations is a HOST pointer. */
+int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
+                        const mpba_options* opt, double radius, double* S, double* rhs, double* y,
+                        int32_t* pcg_iterations);
+
+/* Trust-region Levenberg-Marquardt (Ceres 2.1 TrustRegionMinimizer semantics); updates img_pose
+ * and pt_xyz in place to the best state visited. */
+int mpba_solve(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
+               const mpba_options* opt, mpba_summary* summary);
+
+/* After a call with opt->profile: per-kernel summed device ms and launch counts (HOST arrays of
+ * MPBA_NUM_KERNELS); names from mpba_kernel_name(slot). */
+int mpba_kernel_times(const mpba_handle* h, double* ms, int64_t* launches);
+const char* mpba_kernel_name(int slot);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPBA_H_ */

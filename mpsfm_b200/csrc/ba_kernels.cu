@@ -1,0 +1,926 @@
+// ba_kernels.cu -- hand-written sm_100a kernels of the bundle-adjustment hot path.
+//
+// The workload is gather / segmented-reduce / small-block algebra in fp64 at 1-2 flop per byte:
+// HBM- (or, for the reduced camera system, L2-) bound, so the kernels are plain SIMT with
+// vectorised 16-byte loads, SoA observation streams read once per pass, register-resident block
+// algebra, warp-shuffle reductions and fixed-order two-stage sums.  No tensor-core path: there is
+// no GEMM here ("Why no tcgen05").
+//
+// Two observation orders feed the two reduction keys (north star item 2):
+//   image order  -> Hcc, gc, cost      (k_img_chunks: one CTA per <=1024-observation chunk of one
+//                                       image, shuffle + shared-memory reduction, no atomics)
+//   track order  -> Hpp, gp, Hpp^-1, Schur complement, back-substitution (one thread per track)
+// Jacobians are never stored: every pass recomputes N, h, p_rot (ba_math.cuh) from the 52-byte
+// observation record and the cache-resident pose, which is cheaper than streaming 144-byte W blocks.
+#include <cooperative_groups.h>
+
+#include "ba_kernels.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace mpba {
+
+namespace {
+
+constexpr unsigned FULL = 0xffffffffu;
+
+__device__ __forceinline__ int upper_idx(int i, int j) { return i * (13 - i) / 2 + (j - i); }
+
+struct ImgConst {
+  double pose[8];
+  double R[9];
+  const double* prm;
+  int model;
+  double b, s;
+};
+
+__device__ __forceinline__ void load_img(const ProblemView& pv, const double* __restrict__ pose, int img, ImgConst& ic) {
+  const double2* pp = reinterpret_cast<const double2*>(pose + 8 * (size_t)img);
+  const double2 a = __ldg(pp), b = __ldg(pp + 1), c = __ldg(pp + 2), d = __ldg(pp + 3);
+  ic.pose[0] = a.x; ic.pose[1] = a.y; ic.pose[2] = b.x; ic.pose[3] = b.y;
+  ic.pose[4] = c.x; ic.pose[5] = c.y; ic.pose[6] = d.x; ic.pose[7] = d.y;
+  quat_to_rotmat(ic.pose, ic.R);
+  const int cam = __ldg(pv.img_camera + img);
+  ic.model = __ldg(pv.cam_model + cam);
+  ic.prm = pv.cam_params + (size_t)MPBA_MAX_PRM * cam;
+  const double2 ss = __ldg(reinterpret_cast<const double2*>(pv.img_shift_scale) + img);
+  ic.b = ss.x;
+  ic.s = ss.y;
+}
+
+__device__ __forceinline__ void load_point(const double* __restrict__ X, int p, double out[3]) {
+  const double2* xp = reinterpret_cast<const double2*>(X + 4 * (size_t)p);
+  const double2 a = __ldg(xp), b = __ldg(xp + 1);
+  out[0] = a.x; out[1] = a.y; out[2] = b.x;
+}
+
+// deterministic block sum (fixed shuffle tree, then warps in order); result valid in every thread
+template <int NWARP>
+__device__ __forceinline__ double block_sum(double v, double* sm /* [NWARP+1] */) {
+  for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(FULL, v, off);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane == 0) sm[warp] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int w = 0; w < NWARP; ++w) s += sm[w];
+    sm[NWARP] = s;
+  }
+  __syncthreads();
+  return sm[NWARP];
+}
+template <int NWARP>
+__device__ __forceinline__ double block_max(double v, double* sm) {
+  for (int off = 16; off > 0; off >>= 1) v = fmax(v, __shfl_down_sync(FULL, v, off));
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane == 0) sm[warp] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int w = 0; w < NWARP; ++w) s = fmax(s, sm[w]);
+    sm[NWARP] = s;
+  }
+  __syncthreads();
+  return sm[NWARP];
+}
+
+// ================================================================================================
+// image order
+// ================================================================================================
+__global__ void __launch_bounds__(256) k_img_chunks(ProblemView pv, const double* __restrict__ pose,
+                                                    const double* __restrict__ X, double* __restrict__ chunk_part) {
+  const int c = blockIdx.x;
+  const int img = pv.chunk_img[c];
+  const int beg = pv.chunk_begin[c], end = pv.chunk_end[c];
+  ImgConst ic;
+  load_img(pv, pose, img, ic);
+  double prm[MPBA_MAX_PRM];
+#pragma unroll
+  for (int j = 0; j < MPBA_MAX_PRM; ++j) prm[j] = __ldg(ic.prm + j);
+  const bool img_const = pv.img_free_mask[img] == 0;
+  const double2* xy = reinterpret_cast<const double2*>(pv.cm_xy);
+  const double* dd = pv.cm_depth;
+  const size_t N = (size_t)pv.N;
+
+  double acc[29];
+#pragma unroll
+  for (int j = 0; j < 29; ++j) acc[j] = 0.0;
+
+  for (int k = beg + (int)threadIdx.x; k < end; k += 256) {
+    const int pt = __ldg(pv.cm_pt + k);
+    double Xp[3];
+    load_point(X, pt, Xp);
+    const double2 o2 = __ldg(xy + k);
+    const double d = __ldg(dd + k), w = __ldg(dd + N + k), a = __ldg(dd + 2 * N + k);
+    ObsLin o;
+    linearize_obs<true, true>(ic.pose, ic.R, Xp, ic.model, prm, o2.x, o2.y, d, w, a, ic.b, ic.s, pv.loss, o);
+    double H[21], g[6];
+    gt_n_g_upper(o.prot, o.N, H);
+    gt_vec(o.prot, o.h, g);
+#pragma unroll
+    for (int j = 0; j < 21; ++j) acc[j] += H[j];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) acc[21 + j] += g[j];
+    const bool fixed = img_const && (pv.pt_const[pt] != 0);
+    if (fixed) acc[28] += o.rho; else acc[27] += o.rho;
+  }
+
+  __shared__ double sm[8][IMG_PART];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int j = 0; j < 29; ++j) {
+    double v = acc[j];
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(FULL, v, off);
+    if (lane == 0) sm[warp][j] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 29) {
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += sm[w][threadIdx.x];
+    chunk_part[(size_t)c * IMG_PART + threadIdx.x] = s;
+  }
+}
+
+// one thread per (image, value): sums the image's chunk partials in chunk order
+__global__ void __launch_bounds__(256) k_img_finalize(ProblemView pv, const double* __restrict__ chunk_part,
+                                                      double* __restrict__ Hc, double* __restrict__ gc,
+                                                      double* __restrict__ img_part, double* __restrict__ c_img,
+                                                      int compute_scaling, int jacobi_scaling) {
+  const int gid = blockIdx.x * 256 + threadIdx.x;
+  const int i = gid >> 5, v = gid & 31;
+  if (i >= pv.C || v >= 29) return;
+  double s = 0.0;
+  for (int ch = pv.img_chunk_ptr[i]; ch < pv.img_chunk_ptr[i + 1]; ++ch) s += chunk_part[(size_t)ch * IMG_PART + v];
+  const unsigned mask = pv.img_free_mask[i];
+  if (v < 21) {
+    // (r, c) of upper index v
+    int r = 0, base = 0;
+    while (v >= base + (6 - r)) { base += 6 - r; ++r; }
+    const int c = r + (v - base);
+    const bool fr = (mask >> r) & 1u, fc = (mask >> c) & 1u;
+    const double val = (fr && fc) ? s : 0.0;
+    Hc[(size_t)i * 21 + v] = val;
+    if (r == c && compute_scaling) c_img[(size_t)i * 6 + r] = fr ? (jacobi_scaling ? 1.0 / (1.0 + sqrt(val)) : 1.0) : 0.0;
+  } else if (v < 27) {
+    const int r = v - 21;
+    gc[(size_t)i * 6 + r] = ((mask >> r) & 1u) ? s : 0.0;
+  } else {
+    img_part[(size_t)i * 2 + (v - 27)] = s;
+  }
+}
+
+__global__ void __launch_bounds__(1024) k_img_scalars(int C, const double* __restrict__ img_part,
+                                                      const double* __restrict__ gc, double* __restrict__ scal) {
+  __shared__ double sm[33];
+  double cf = 0.0, cx = 0.0, gm = 0.0;
+  for (int i = threadIdx.x; i < C; i += 1024) {
+    cf += img_part[2 * (size_t)i];
+    cx += img_part[2 * (size_t)i + 1];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) gm = fmax(gm, fabs(gc[(size_t)i * 6 + j]));
+  }
+  cf = block_sum<32>(cf, sm);
+  cx = block_sum<32>(cx, sm);
+  gm = block_max<32>(gm, sm);
+  if (threadIdx.x == 0) {
+    scal[S_COST_FREE] = cf;
+    scal[S_COST_FIXED] = cx;
+    scal[S_GMAX_C] = gm;
+  }
+}
+
+// ================================================================================================
+// track order
+// ================================================================================================
+// sum of v[j] over the 32 lanes for j = 0..31, delivered to lane j, in 31 exchanges
+__device__ __forceinline__ double warp_transpose_reduce32(double (&v)[36], int lane) {
+#pragma unroll
+  for (int w = 16; w >= 1; w >>= 1) {
+    const bool up = (lane & w) != 0;
+#pragma unroll
+    for (int i = 0; i < w; ++i) {
+      const double send = up ? v[i] : v[i + w];
+      const double keep = up ? v[i + w] : v[i];
+      v[i] = keep + __shfl_xor_sync(FULL, send, w);
+    }
+  }
+  return v[0];
+}
+
+// add a 6x6 block per lane into T[key*36..]; lanes of a warp that all hold the same key are summed
+// in registers first (31 + 20 shuffle exchanges) and leave as ONE coalesced 36-value reduction.
+__device__ __forceinline__ void scatter_block36(double* __restrict__ T, int key, bool has, double (&M)[36], int lane) {
+  const int key0 = __shfl_sync(FULL, key, 0);
+  const bool uniform = __all_sync(FULL, has && key == key0);
+  if (uniform) {
+    double tail[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      double t = M[32 + j];
+      for (int off = 16; off > 0; off >>= 1) t += __shfl_xor_sync(FULL, t, off);
+      tail[j] = t;
+    }
+    const double mine = warp_transpose_reduce32(M, lane);
+    double* dst = T + (size_t)key0 * 36;
+    atomicAdd(dst + lane, mine);
+    if (lane < 4) atomicAdd(dst + 32 + lane, lane == 0 ? tail[0] : lane == 1 ? tail[1] : lane == 2 ? tail[2] : tail[3]);
+  } else if (has) {
+    double* dst = T + (size_t)key * 36;
+#pragma unroll
+    for (int j = 0; j < 36; ++j) atomicAdd(dst + j, M[j]);
+  }
+}
+
+__device__ __forceinline__ void scatter_vec6(double* __restrict__ out, int key, bool has, const double (&g)[6], int lane) {
+  const int key0 = __shfl_sync(FULL, key, 0);
+  const bool uniform = __all_sync(FULL, has && key == key0);
+  if (uniform) {
+    double mine = 0.0;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      double t = g[j];
+      for (int off = 16; off > 0; off >>= 1) t += __shfl_xor_sync(FULL, t, off);
+      if (lane == j) mine = t;
+    }
+    if (lane < 6) atomicAdd(out + (size_t)key0 * 6 + lane, mine);
+  } else if (has) {
+#pragma unroll
+    for (int j = 0; j < 6; ++j) atomicAdd(out + (size_t)key * 6 + j, g[j]);
+  }
+}
+
+struct TrackObs {
+  double Q[9];   // N R
+  double prot[3];
+  int img;
+};
+
+__device__ __forceinline__ void track_obs(const ProblemView& pv, const double* __restrict__ pose, const double Xp[3],
+                                          int k, ObsLin& o, ImgConst& ic) {
+  const int img = __ldg(pv.pm_img + k);
+  load_img(pv, pose, img, ic);
+  const double2 o2 = __ldg(reinterpret_cast<const double2*>(pv.pm_xy) + k);
+  const size_t N = (size_t)pv.N;
+  const double d = __ldg(pv.pm_depth + k), w = __ldg(pv.pm_depth + N + k), a = __ldg(pv.pm_depth + 2 * N + k);
+  linearize_obs<true, false>(ic.pose, ic.R, Xp, ic.model, ic.prm, o2.x, o2.y, d, w, a, ic.b, ic.s, pv.loss, o);
+}
+
+constexpr int PT_THREADS = 128;
+
+__global__ void __launch_bounds__(PT_THREADS) k_points_schur(ProblemView pv, const double* __restrict__ pose,
+                                                             const double* __restrict__ X, LmDiag lm,
+                                                             double* __restrict__ c_pt, int compute_scaling,
+                                                             int jacobi_scaling, double* __restrict__ Hpp,
+                                                             double* __restrict__ gp, double* __restrict__ Hinv,
+                                                             double* __restrict__ T, double* __restrict__ rhs_acc,
+                                                             double* __restrict__ pt_part, double* __restrict__ scal,
+                                                             int do_schur) {
+  const int p = blockIdx.x * PT_THREADS + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const bool valid = p < pv.P;
+  const bool active = valid && pv.pt_const[p] == 0;
+  int beg = 0, end = 0;
+  if (active) {
+    beg = pv.pt_ptr[p];
+    end = pv.pt_ptr[p + 1];
+  }
+  const int L = end - beg;
+  double Xp[3] = {0.0, 0.0, 0.0};
+  if (active) load_point(X, p, Xp);
+
+  // ---- pass 1: Hpp = sum R^T N R, gp = sum R^T h
+  double Hp[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, g[3] = {0.0, 0.0, 0.0};
+  for (int k = beg; k < end; ++k) {
+    ObsLin o;
+    ImgConst ic;
+    track_obs(pv, pose, Xp, k, o, ic);
+    double Q[9];
+    sym3_mul_mat(o.N, ic.R, Q);
+    const double* R = ic.R;
+    Hp[0] += R[0] * Q[0] + R[3] * Q[3] + R[6] * Q[6];
+    Hp[1] += R[0] * Q[1] + R[3] * Q[4] + R[6] * Q[7];
+    Hp[2] += R[0] * Q[2] + R[3] * Q[5] + R[6] * Q[8];
+    Hp[3] += R[1] * Q[1] + R[4] * Q[4] + R[7] * Q[7];
+    Hp[4] += R[1] * Q[2] + R[4] * Q[5] + R[7] * Q[8];
+    Hp[5] += R[2] * Q[2] + R[5] * Q[5] + R[8] * Q[8];
+    g[0] += R[0] * o.h[0] + R[3] * o.h[1] + R[6] * o.h[2];
+    g[1] += R[1] * o.h[0] + R[4] * o.h[1] + R[7] * o.h[2];
+    g[2] += R[2] * o.h[0] + R[5] * o.h[1] + R[8] * o.h[2];
+  }
+
+  double Hi[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  if (valid) {
+    double c[3] = {0.0, 0.0, 0.0};
+    if (compute_scaling) {
+      if (active && L > 0) {
+        c[0] = jacobi_scaling ? 1.0 / (1.0 + sqrt(Hp[0])) : 1.0;
+        c[1] = jacobi_scaling ? 1.0 / (1.0 + sqrt(Hp[3])) : 1.0;
+        c[2] = jacobi_scaling ? 1.0 / (1.0 + sqrt(Hp[5])) : 1.0;
+      }
+      c_pt[(size_t)p * 3] = c[0]; c_pt[(size_t)p * 3 + 1] = c[1]; c_pt[(size_t)p * 3 + 2] = c[2];
+    } else {
+      c[0] = c_pt[(size_t)p * 3]; c[1] = c_pt[(size_t)p * 3 + 1]; c[2] = c_pt[(size_t)p * 3 + 2];
+    }
+    if (active && L > 0) {
+      double Hd[6] = {Hp[0], Hp[1], Hp[2], Hp[3], Hp[4], Hp[5]};
+      Hd[0] += lm_damping(Hp[0], c[0], lm.radius, lm.lo, lm.hi);
+      Hd[3] += lm_damping(Hp[3], c[1], lm.radius, lm.lo, lm.hi);
+      Hd[5] += lm_damping(Hp[5], c[2], lm.radius, lm.lo, lm.hi);
+      if (!sym3_inverse(Hd, Hi)) {
+#pragma unroll
+        for (int j = 0; j < 6; ++j) Hi[j] = 0.0;
+        atomicAdd(scal + S_BAD_POINTS, 1.0);  // failure counter, not arithmetic
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      Hpp[(size_t)p * 6 + j] = Hp[j];
+      Hinv[(size_t)p * 6 + j] = Hi[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 3; ++j) gp[(size_t)p * 3 + j] = g[j];
+  }
+
+  // max |gp| of this CTA
+  {
+    __shared__ double smx[PT_THREADS / 32 + 1];
+    const double m = block_max<PT_THREADS / 32>(fmax(fabs(g[0]), fmax(fabs(g[1]), fabs(g[2]))), smx);
+    if (threadIdx.x == 0) pt_part[(size_t)blockIdx.x * PT_PART] = m;
+  }
+  if (!do_schur) return;
+
+  // ---- pass 2: T(i_a, i_b) += W_a Hpp^-1 W_b^T,  rhs_acc(i_a) += W_a Hpp^-1 gp,  W = G^T Q
+  double e[3];
+  sym3_mul_vec(Hi, g, e);
+  int Lmax = L;
+  for (int off = 16; off > 0; off >>= 1) Lmax = max(Lmax, __shfl_xor_sync(FULL, Lmax, off));
+  const int pair0 = active ? pv.pair_ptr[p] : 0;
+
+  for (int a = 0; a < Lmax; ++a) {
+    const bool has_a = a < L;
+    double Za[9], pa[3] = {0.0, 0.0, 0.0};
+    int img_a = -1;
+    double ga[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    if (has_a) {
+      ObsLin o;
+      ImgConst ic;
+      track_obs(pv, pose, Xp, beg + a, o, ic);
+      img_a = __ldg(pv.pm_img + beg + a);
+      double Q[9];
+      sym3_mul_mat(o.N, ic.R, Q);
+      pa[0] = o.prot[0]; pa[1] = o.prot[1]; pa[2] = o.prot[2];
+      // Za = Q Hi (Hi symmetric)
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        const double q0 = Q[3 * i], q1 = Q[3 * i + 1], q2 = Q[3 * i + 2];
+        Za[3 * i] = q0 * Hi[0] + q1 * Hi[1] + q2 * Hi[2];
+        Za[3 * i + 1] = q0 * Hi[1] + q1 * Hi[3] + q2 * Hi[4];
+        Za[3 * i + 2] = q0 * Hi[2] + q1 * Hi[4] + q2 * Hi[5];
+      }
+      double ua[3];
+      ua[0] = Q[0] * e[0] + Q[1] * e[1] + Q[2] * e[2];
+      ua[1] = Q[3] * e[0] + Q[4] * e[1] + Q[5] * e[2];
+      ua[2] = Q[6] * e[0] + Q[7] * e[1] + Q[8] * e[2];
+      gt_vec(pa, ua, ga);
+    }
+    scatter_vec6(rhs_acc, img_a, has_a, ga, lane);
+
+    for (int b = a; b < Lmax; ++b) {
+      const bool has_b = b < L;
+      double M[36];
+      int blk = -1;
+      if (has_b) {
+        ObsLin o;
+        ImgConst ic;
+        track_obs(pv, pose, Xp, beg + b, o, ic);
+        const int img_b = __ldg(pv.pm_img + beg + b);
+        double Q[9], K[9];
+        sym3_mul_mat(o.N, ic.R, Q);
+        // K = Za Qb^T
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+          for (int j = 0; j < 3; ++j) K[3 * i + j] = Za[3 * i] * Q[3 * j] + Za[3 * i + 1] * Q[3 * j + 1] + Za[3 * i + 2] * Q[3 * j + 2];
+        gt_k_g(pa, K, o.prot, M);
+        if (b > a && img_b == img_a) {  // two observations of one image in a track: M + M^T on the diagonal block
+#pragma unroll
+          for (int i = 0; i < 6; ++i)
+#pragma unroll
+            for (int j = i; j < 6; ++j) {
+              const double s = M[6 * i + j] + M[6 * j + i];
+              M[6 * i + j] = s;
+              M[6 * j + i] = s;
+            }
+        }
+        blk = __ldg(pv.pair_block + pair0 + a * L - (a * (a - 1)) / 2 + (b - a));
+      } else {
+#pragma unroll
+        for (int j = 0; j < 36; ++j) M[j] = 0.0;
+      }
+      scatter_block36(T, blk, has_b, M, lane);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(1024) k_pt_scalars_gmax(const double* __restrict__ pt_part, int nblk,
+                                                          double* __restrict__ scal) {
+  __shared__ double sm[33];
+  double gm = 0.0;
+  for (int i = threadIdx.x; i < nblk; i += 1024) gm = fmax(gm, pt_part[(size_t)i * PT_PART]);
+  gm = block_max<32>(gm, sm);
+  if (threadIdx.x == 0) scal[S_GMAX_P] = gm;
+}
+
+// ================================================================================================
+// reduced camera system
+// ================================================================================================
+// one CTA per block row: S = Hcc + D - T on the diagonal, -T off it, identity on fixed coordinates
+__global__ void __launch_bounds__(128) k_s_finalize(ProblemView pv, const double* __restrict__ Hc,
+                                                    const double* __restrict__ gc, const double* __restrict__ c_img,
+                                                    LmDiag lm, const double* __restrict__ T,
+                                                    const double* __restrict__ rhs_acc, double* __restrict__ S,
+                                                    double* __restrict__ rhs) {
+  const int i = blockIdx.x;
+  const int r0 = pv.s_row_ptr[i], r1 = pv.s_row_ptr[i + 1];
+  const unsigned mi = pv.img_free_mask[i];
+  const int total = (r1 - r0) * 36;
+  for (int idx = threadIdx.x; idx < total; idx += 128) {
+    const int blk = r0 + idx / 36, e = idx % 36, r = e / 6, c = e % 6;
+    const int j = pv.s_col[blk];
+    const bool fr = (mi >> r) & 1u;
+    double val;
+    if (j == i) {
+      const bool fc = (mi >> c) & 1u;
+      if (fr && fc) {
+        const int u = upper_idx(r < c ? r : c, r < c ? c : r);
+        val = Hc[(size_t)i * 21 + u] - 0.5 * (T[(size_t)blk * 36 + e] + T[(size_t)blk * 36 + c * 6 + r]);
+        if (r == c) val += lm_damping(Hc[(size_t)i * 21 + u], c_img[(size_t)i * 6 + r], lm.radius, lm.lo, lm.hi);
+      } else {
+        val = (r == c) ? 1.0 : 0.0;
+      }
+    } else {
+      const bool fc = (pv.img_free_mask[j] >> c) & 1u;
+      if (fr && fc) {
+        val = (i < j) ? -T[(size_t)blk * 36 + e] : -T[(size_t)pv.s_transpose[blk] * 36 + c * 6 + r];
+      } else {
+        val = 0.0;
+      }
+    }
+    S[(size_t)blk * 36 + e] = val;
+  }
+  if (threadIdx.x < 6) {
+    const int r = threadIdx.x;
+    rhs[(size_t)i * 6 + r] = ((mi >> r) & 1u) ? gc[(size_t)i * 6 + r] - rhs_acc[(size_t)i * 6 + r] : 0.0;
+  }
+}
+
+// block-Jacobi preconditioner: inverse of each 6x6 diagonal block through its Cholesky factor
+__global__ void __launch_bounds__(128) k_block_inverse(ProblemView pv, const double* __restrict__ S,
+                                                       double* __restrict__ Minv) {
+  const int i = blockIdx.x * 128 + threadIdx.x;
+  if (i >= pv.C) return;
+  double A[36], Li[36];
+  const double* src = S + (size_t)pv.s_diag[i] * 36;
+  for (int k = 0; k < 36; ++k) A[k] = src[k];
+  bool ok = true;
+  // in-place Cholesky, lower
+  for (int j = 0; j < 6; ++j) {
+    double d = A[7 * j];
+    for (int k = 0; k < j; ++k) d -= A[6 * j + k] * A[6 * j + k];
+    if (!(d > 0.0)) { ok = false; break; }
+    d = sqrt(d);
+    A[7 * j] = d;
+    for (int r = j + 1; r < 6; ++r) {
+      double s = A[6 * r + j];
+      for (int k = 0; k < j; ++k) s -= A[6 * r + k] * A[6 * j + k];
+      A[6 * r + j] = s / d;
+    }
+  }
+  double* dst = Minv + (size_t)i * 36;
+  if (!ok) {
+    for (int k = 0; k < 36; ++k) dst[k] = (k % 7 == 0) ? 1.0 : 0.0;
+    return;
+  }
+  // Li = L^-1 (lower)
+  for (int k = 0; k < 36; ++k) Li[k] = 0.0;
+  for (int c = 0; c < 6; ++c) {
+    Li[7 * c] = 1.0 / A[7 * c];
+    for (int r = c + 1; r < 6; ++r) {
+      double s = 0.0;
+      for (int k = c; k < r; ++k) s -= A[6 * r + k] * Li[6 * k + c];
+      Li[6 * r + c] = s / A[7 * r];
+    }
+  }
+  // A^-1 = Li^T Li
+  for (int r = 0; r < 6; ++r)
+    for (int c = 0; c < 6; ++c) {
+      double s = 0.0;
+      for (int k = (r > c ? r : c); k < 6; ++k) s += Li[6 * k + r] * Li[6 * k + c];
+      dst[6 * r + c] = s;
+    }
+}
+
+// ---- persistent cooperative PCG on the block-CSR reduced camera system --------------------------
+struct PcgArgs {
+  int C;
+  const int32_t* row_ptr;
+  const int32_t* col;
+  const double* S;
+  const double* Minv;
+  const double* rhs;
+  double* x;
+  double* r;
+  double* z;
+  double* p0;
+  double* p1;
+  double* q;
+  double* partial;  // [2][gridDim.x]
+  double* scal;
+  double tol;
+  int max_iter;
+};
+
+constexpr int PCG_THREADS = 256;
+
+__device__ __forceinline__ double grid_sum(cg::grid_group& grid, double part, double* partial_buf, double* sm) {
+  const double b = block_sum<PCG_THREADS / 32>(part, sm);
+  if (threadIdx.x == 0) partial_buf[blockIdx.x] = b;
+  grid.sync();
+  double v = 0.0;
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += PCG_THREADS) v += partial_buf[i];
+  return block_sum<PCG_THREADS / 32>(v, sm);
+}
+
+__global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
+  cg::grid_group grid = cg::this_grid();
+  __shared__ double sm[PCG_THREADS / 32 + 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int wpb = PCG_THREADS / 32;
+  const int gw = blockIdx.x * wpb + warp, nw = gridDim.x * wpb;
+  double* part0 = A.partial;
+  double* part1 = A.partial + gridDim.x;
+  const int r6 = lane % 6, kb0 = lane / 6;
+
+  // x = 0, r = b, z = M^-1 r, p = z
+  double part = 0.0;
+  for (int row = gw; row < A.C; row += nw) {
+    const double rr = lane < 6 ? A.rhs[(size_t)row * 6 + lane] : 0.0;
+    double zz = 0.0;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+      const double rc = __shfl_sync(FULL, rr, c);
+      if (lane < 6) zz += A.Minv[(size_t)row * 36 + lane * 6 + c] * rc;
+    }
+    if (lane < 6) {
+      A.x[(size_t)row * 6 + lane] = 0.0;
+      A.r[(size_t)row * 6 + lane] = rr;
+      A.z[(size_t)row * 6 + lane] = zz;
+      A.p0[(size_t)row * 6 + lane] = zz;
+      part += rr * zz;
+    }
+  }
+  const double rz0 = grid_sum(grid, part, part1, sm);
+  double rz = rz0;
+  int iters = 0, flag = 1;
+  double res = 1.0;
+  if (!(rz0 > 0.0) || !isfinite(rz0)) {
+    flag = (rz0 == 0.0) ? 0 : 2;
+    res = 0.0;
+  } else {
+    double* pc = A.p0;
+    double* pn = A.p1;
+    for (int it = 0; it < A.max_iter; ++it) {
+      // q = S p, p'q
+      part = 0.0;
+      for (int row = gw; row < A.C; row += nw) {
+        const int b0 = A.row_ptr[row], b1 = A.row_ptr[row + 1];
+        double acc = 0.0;
+        if (lane < 30) {
+          for (int blk = b0 + kb0; blk < b1; blk += 5) {
+            const int col = __ldg(A.col + blk);
+            const double2* Sb = reinterpret_cast<const double2*>(A.S + (size_t)blk * 36 + r6 * 6);
+            const double2* pcol = reinterpret_cast<const double2*>(pc + (size_t)col * 6);
+            const double2 s0 = Sb[0], s1 = Sb[1], s2 = Sb[2];
+            const double2 v0 = pcol[0], v1 = pcol[1], v2 = pcol[2];
+            acc += s0.x * v0.x + s0.y * v0.y + s1.x * v1.x + s1.y * v1.y + s2.x * v2.x + s2.y * v2.y;
+          }
+        }
+        const double a1 = __shfl_sync(FULL, acc, r6 + 6), a2 = __shfl_sync(FULL, acc, r6 + 12),
+                     a3 = __shfl_sync(FULL, acc, r6 + 18), a4 = __shfl_sync(FULL, acc, r6 + 24);
+        if (lane < 6) {
+          const double qv = acc + a1 + a2 + a3 + a4;
+          A.q[(size_t)row * 6 + lane] = qv;
+          part += pc[(size_t)row * 6 + lane] * qv;
+        }
+      }
+      const double pq = grid_sum(grid, part, part0, sm);
+      if (!(pq > 0.0) || !isfinite(pq)) {
+        flag = 2;
+        break;
+      }
+      const double alpha = rz / pq;
+      // x += alpha p, r -= alpha q, z = M^-1 r
+      part = 0.0;
+      for (int row = gw; row < A.C; row += nw) {
+        double rr = 0.0;
+        if (lane < 6) {
+          const size_t o = (size_t)row * 6 + lane;
+          A.x[o] += alpha * pc[o];
+          rr = A.r[o] - alpha * A.q[o];
+          A.r[o] = rr;
+        }
+        double zz = 0.0;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          const double rc = __shfl_sync(FULL, rr, c);
+          if (lane < 6) zz += A.Minv[(size_t)row * 36 + lane * 6 + c] * rc;
+        }
+        if (lane < 6) {
+          A.z[(size_t)row * 6 + lane] = zz;
+          part += rr * zz;
+        }
+      }
+      const double rz_new = grid_sum(grid, part, part1, sm);
+      iters = it + 1;
+      res = sqrt(fabs(rz_new) / rz0);
+      if (!isfinite(rz_new)) {
+        flag = 2;
+        break;
+      }
+      if (res <= A.tol) {
+        flag = 0;
+        break;
+      }
+      const double beta = rz_new / rz;
+      rz = rz_new;
+      // p <- z + beta p  (other buffer: readers of the old p may still be in flight elsewhere)
+      for (int row = gw; row < A.C; row += nw) {
+        if (lane < 6) {
+          const size_t o = (size_t)row * 6 + lane;
+          pn[o] = A.z[o] + beta * pc[o];
+        }
+      }
+      double* t = pc;
+      pc = pn;
+      pn = t;
+      grid.sync();
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    A.scal[S_PCG_ITERS] = (double)iters;
+    A.scal[S_PCG_FLAG] = (double)flag;
+    A.scal[S_PCG_RES] = res;
+  }
+}
+
+// ================================================================================================
+// step
+// ================================================================================================
+__global__ void __launch_bounds__(256) k_cam_update(ProblemView pv, const double* __restrict__ pose,
+                                                    const double* __restrict__ y, double* __restrict__ pose_cand,
+                                                    double* __restrict__ scal) {
+  __shared__ double sm[9];
+  double step2 = 0.0, xn2 = 0.0;
+  for (int i = threadIdx.x; i < pv.C; i += 256) {
+    const double* ps = pose + (size_t)i * 8;
+    const double* yi = y + (size_t)i * 6;
+    const unsigned mask = pv.img_free_mask[i];
+    const bool used = pv.img_ptr[i + 1] > pv.img_ptr[i];
+    const double q[4] = {ps[0], ps[1], ps[2], ps[3]};
+    const double d[3] = {-yi[0], -yi[1], -yi[2]};
+    double qn[4];
+    quat_plus(q, d, qn);
+    double* out = pose_cand + (size_t)i * 8;
+    out[0] = qn[0]; out[1] = qn[1]; out[2] = qn[2]; out[3] = qn[3];
+    const double t0 = ps[4] - yi[3], t1 = ps[5] - yi[4], t2 = ps[6] - yi[5];
+    out[4] = t0; out[5] = t1; out[6] = t2; out[7] = ps[7];
+    if (used && (mask & 7u)) {
+      step2 += (qn[0] - q[0]) * (qn[0] - q[0]) + (qn[1] - q[1]) * (qn[1] - q[1]) + (qn[2] - q[2]) * (qn[2] - q[2]) +
+               (qn[3] - q[3]) * (qn[3] - q[3]);
+      xn2 += q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
+    }
+    if (used && (mask & 0x38u)) {
+      step2 += (t0 - ps[4]) * (t0 - ps[4]) + (t1 - ps[5]) * (t1 - ps[5]) + (t2 - ps[6]) * (t2 - ps[6]);
+      xn2 += ps[4] * ps[4] + ps[5] * ps[5] + ps[6] * ps[6];
+    }
+  }
+  step2 = block_sum<8>(step2, sm);
+  xn2 = block_sum<8>(xn2, sm);
+  if (threadIdx.x == 0) {
+    scal[S_STEP2_C] = step2;
+    scal[S_XNORM2_C] = xn2;
+  }
+}
+
+// y_p = Hpp^-1 (gp - sum_a W_a^T y_c(a)); X_cand = X - y_p; model cost change of the whole step:
+//   sum_obs (v.h - v'Nv/2), v = G y_c + R y_p
+//     = sum_a (g_a.h_a - g_a'N_a g_a / 2) + y_p.gp - y_p.wty - y_p'Hpp y_p / 2,   g_a = G_a y_c(a).
+__global__ void __launch_bounds__(PT_THREADS) k_back_substitute(ProblemView pv, const double* __restrict__ pose,
+                                                                const double* __restrict__ X,
+                                                                const double* __restrict__ y,
+                                                                const double* __restrict__ Hpp,
+                                                                const double* __restrict__ gp,
+                                                                const double* __restrict__ Hinv,
+                                                                double* __restrict__ X_cand,
+                                                                double* __restrict__ pt_part) {
+  const int p = blockIdx.x * PT_THREADS + threadIdx.x;
+  const bool valid = p < pv.P;
+  double mcc = 0.0, step2 = 0.0, xn2 = 0.0;
+  if (valid) {
+    const bool is_const = pv.pt_const[p] != 0;
+    const int beg = pv.pt_ptr[p], end = pv.pt_ptr[p + 1];
+    double Xp[3];
+    load_point(X, p, Xp);
+    double wty[3] = {0.0, 0.0, 0.0};
+    for (int k = beg; k < end; ++k) {
+      ObsLin o;
+      ImgConst ic;
+      track_obs(pv, pose, Xp, k, o, ic);
+      const int img = __ldg(pv.pm_img + k);
+      const double* yi = y + (size_t)img * 6;
+      const double yc[6] = {__ldg(yi), __ldg(yi + 1), __ldg(yi + 2), __ldg(yi + 3), __ldg(yi + 4), __ldg(yi + 5)};
+      double ga[3], Ng[3];
+      g_vec(o.prot, yc, ga);
+      sym3_mul_vec(o.N, ga, Ng);
+      mcc += ga[0] * o.h[0] + ga[1] * o.h[1] + ga[2] * o.h[2] - 0.5 * (ga[0] * Ng[0] + ga[1] * Ng[1] + ga[2] * Ng[2]);
+      // wty += Q^T ga = R^T (N ga)
+      const double* R = ic.R;
+      wty[0] += R[0] * Ng[0] + R[3] * Ng[1] + R[6] * Ng[2];
+      wty[1] += R[1] * Ng[0] + R[4] * Ng[1] + R[7] * Ng[2];
+      wty[2] += R[2] * Ng[0] + R[5] * Ng[1] + R[8] * Ng[2];
+    }
+    double yp[3] = {0.0, 0.0, 0.0};
+    if (!is_const && end > beg) {
+      double Hi[6], Hp[6], g[3];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        Hi[j] = Hinv[(size_t)p * 6 + j];
+        Hp[j] = Hpp[(size_t)p * 6 + j];
+      }
+#pragma unroll
+      for (int j = 0; j < 3; ++j) g[j] = gp[(size_t)p * 3 + j];
+      const double rr[3] = {g[0] - wty[0], g[1] - wty[1], g[2] - wty[2]};
+      sym3_mul_vec(Hi, rr, yp);
+      double Hy[3];
+      sym3_mul_vec(Hp, yp, Hy);
+      mcc += yp[0] * (g[0] - wty[0]) + yp[1] * (g[1] - wty[1]) + yp[2] * (g[2] - wty[2]) -
+             0.5 * (yp[0] * Hy[0] + yp[1] * Hy[1] + yp[2] * Hy[2]);
+      step2 = yp[0] * yp[0] + yp[1] * yp[1] + yp[2] * yp[2];
+      xn2 = Xp[0] * Xp[0] + Xp[1] * Xp[1] + Xp[2] * Xp[2];
+    }
+    double2* out = reinterpret_cast<double2*>(X_cand + 4 * (size_t)p);
+    out[0] = make_double2(Xp[0] - yp[0], Xp[1] - yp[1]);
+    out[1] = make_double2(Xp[2] - yp[2], 0.0);
+  }
+  __shared__ double sm[PT_THREADS / 32 + 1];
+  mcc = block_sum<PT_THREADS / 32>(mcc, sm);
+  step2 = block_sum<PT_THREADS / 32>(step2, sm);
+  xn2 = block_sum<PT_THREADS / 32>(xn2, sm);
+  if (threadIdx.x == 0) {
+    pt_part[(size_t)blockIdx.x * PT_PART + 1] = mcc;
+    pt_part[(size_t)blockIdx.x * PT_PART + 2] = step2;
+    pt_part[(size_t)blockIdx.x * PT_PART + 3] = xn2;
+  }
+}
+
+__global__ void __launch_bounds__(1024) k_pt_scalars_step(const double* __restrict__ pt_part, int nblk,
+                                                          double* __restrict__ scal) {
+  __shared__ double sm[33];
+  double a = 0.0, b = 0.0, c = 0.0;
+  for (int i = threadIdx.x; i < nblk; i += 1024) {
+    a += pt_part[(size_t)i * PT_PART + 1];
+    b += pt_part[(size_t)i * PT_PART + 2];
+    c += pt_part[(size_t)i * PT_PART + 3];
+  }
+  a = block_sum<32>(a, sm);
+  b = block_sum<32>(b, sm);
+  c = block_sum<32>(c, sm);
+  if (threadIdx.x == 0) {
+    scal[S_MCC] = a;
+    scal[S_STEP2_P] = b;
+    scal[S_XNORM2_P] = c;
+  }
+}
+
+// ================================================================================================
+// misc
+// ================================================================================================
+__global__ void __launch_bounds__(PT_THREADS) k_evaluate(ProblemView pv, const double* __restrict__ pose,
+                                                         const double* __restrict__ X, double* __restrict__ r_reproj,
+                                                         double* __restrict__ r_depth) {
+  const int p = blockIdx.x * PT_THREADS + threadIdx.x;
+  if (p >= pv.P) return;
+  double Xp[3];
+  load_point(X, p, Xp);
+  const size_t N = (size_t)pv.N;
+  for (int k = pv.pt_ptr[p]; k < pv.pt_ptr[p + 1]; ++k) {
+    const int img = __ldg(pv.pm_img + k);
+    ImgConst ic;
+    load_img(pv, pose, img, ic);
+    const double2 o2 = __ldg(reinterpret_cast<const double2*>(pv.pm_xy) + k);
+    const double d = __ldg(pv.pm_depth + k), w = __ldg(pv.pm_depth + N + k), a = __ldg(pv.pm_depth + 2 * N + k);
+    ObsLin o;
+    linearize_obs<false, false>(ic.pose, ic.R, Xp, ic.model, ic.prm, o2.x, o2.y, d, w, a, ic.b, ic.s, pv.loss, o);
+    if (r_reproj) reinterpret_cast<double2*>(r_reproj)[k] = make_double2(o.r[0], o.r[1]);
+    if (r_depth) r_depth[k] = o.r[2];
+  }
+}
+
+// COLMAP normalises every quaternion before it enters the problem
+__global__ void k_normalize_poses(int C, const double* __restrict__ in, double* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= C) return;
+  const double* s = in + (size_t)i * 8;
+  const double n = sqrt(s[0] * s[0] + s[1] * s[1] + s[2] * s[2] + s[3] * s[3]);
+  double* o = out + (size_t)i * 8;
+  o[0] = s[0] / n; o[1] = s[1] / n; o[2] = s[2] / n; o[3] = s[3] / n;
+  o[4] = s[4]; o[5] = s[5]; o[6] = s[6]; o[7] = 0.0;
+}
+
+__global__ void k_expand_hcc(int C, const double* __restrict__ Hc, double* __restrict__ H36) {
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= C * 36) return;
+  const int i = gid / 36, e = gid % 36, r = e / 6, c = e % 6;
+  H36[gid] = Hc[(size_t)i * 21 + upper_idx(r < c ? r : c, r < c ? c : r)];
+}
+
+}  // namespace
+
+// ================================================================================================
+// launchers
+// ================================================================================================
+void launch_img_chunks(const ProblemView& pv, const double* pose, const double* X, double* chunk_part, cudaStream_t st) {
+  if (pv.num_chunks > 0) k_img_chunks<<<pv.num_chunks, 256, 0, st>>>(pv, pose, X, chunk_part);
+}
+void launch_img_finalize(const ProblemView& pv, const double* chunk_part, double* Hc, double* gc, double* img_part,
+                         double* c_img, int compute_scaling, int jacobi_scaling, cudaStream_t st) {
+  const int n = pv.C * 32;
+  k_img_finalize<<<(n + 255) / 256, 256, 0, st>>>(pv, chunk_part, Hc, gc, img_part, c_img, compute_scaling, jacobi_scaling);
+}
+void launch_img_scalars(const ProblemView& pv, const double* img_part, const double* gc, double* scal, cudaStream_t st) {
+  k_img_scalars<<<1, 1024, 0, st>>>(pv.C, img_part, gc, scal);
+}
+int points_grid(int P) { return (P + PT_THREADS - 1) / PT_THREADS; }
+void launch_points_schur(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,
+                         int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* T,
+                         double* rhs_acc, double* pt_part, double* scal, int do_schur, cudaStream_t st) {
+  if (pv.P > 0)
+    k_points_schur<<<points_grid(pv.P), PT_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp,
+                                                              gp, Hinv, T, rhs_acc, pt_part, scal, do_schur);
+}
+void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaStream_t st) {
+  k_pt_scalars_gmax<<<1, 1024, 0, st>>>(pt_part, nblk, scal);
+}
+void launch_s_finalize(const ProblemView& pv, const double* Hc, const double* gc, const double* c_img, LmDiag lm,
+                       const double* T, const double* rhs_acc, double* S, double* rhs, double* Minv, cudaStream_t st) {
+  k_s_finalize<<<pv.C, 128, 0, st>>>(pv, Hc, gc, c_img, lm, T, rhs_acc, S, rhs);
+  k_block_inverse<<<(pv.C + 127) / 128, 128, 0, st>>>(pv, S, Minv);
+}
+int pcg_grid(int device, int C) {
+  int sms = 0, per_sm = 0;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg, PCG_THREADS, 0);
+  if (per_sm < 1) per_sm = 1;
+  const int want = (C + (PCG_THREADS / 32) - 1) / (PCG_THREADS / 32);
+  int grid = want < sms ? want : sms;  // one CTA per SM at most: grid.sync cost grows with the CTA count
+  if (grid < 1) grid = 1;
+  return grid;
+}
+cudaError_t launch_pcg(const ProblemView& pv, const double* S, const double* Minv, const double* rhs, double* y,
+                       double* vec_r, double* vec_z, double* vec_p0, double* vec_p1, double* vec_q, double* partial,
+                       double* scal, double tol, int max_iter, int grid, cudaStream_t st) {
+  PcgArgs a;
+  a.C = pv.C; a.row_ptr = pv.s_row_ptr; a.col = pv.s_col; a.S = S; a.Minv = Minv; a.rhs = rhs; a.x = y;
+  a.r = vec_r; a.z = vec_z; a.p0 = vec_p0; a.p1 = vec_p1; a.q = vec_q; a.partial = partial; a.scal = scal;
+  a.tol = tol; a.max_iter = max_iter;
+  void* args[] = {&a};
+  return cudaLaunchCooperativeKernel((void*)k_pcg, dim3(grid), dim3(PCG_THREADS), args, 0, st);
+}
+void launch_cam_update(const ProblemView& pv, const double* pose, const double* y, double* pose_cand, double* scal,
+                       cudaStream_t st) {
+  k_cam_update<<<1, 256, 0, st>>>(pv, pose, y, pose_cand, scal);
+}
+void launch_back_substitute(const ProblemView& pv, const double* pose, const double* X, const double* y,
+                            const double* Hpp, const double* gp, const double* Hinv, double* X_cand, double* pt_part,
+                            cudaStream_t st) {
+  if (pv.P > 0)
+    k_back_substitute<<<points_grid(pv.P), PT_THREADS, 0, st>>>(pv, pose, X, y, Hpp, gp, Hinv, X_cand, pt_part);
+}
+void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, cudaStream_t st) {
+  k_pt_scalars_step<<<1, 1024, 0, st>>>(pt_part, nblk, scal);
+}
+void launch_evaluate(const ProblemView& pv, const double* pose, const double* X, double* r_reproj, double* r_depth,
+                     cudaStream_t st) {
+  if (pv.P > 0) k_evaluate<<<points_grid(pv.P), PT_THREADS, 0, st>>>(pv, pose, X, r_reproj, r_depth);
+}
+void launch_normalize_poses(int C, const double* in, double* out, cudaStream_t st) {
+  if (C > 0) k_normalize_poses<<<(C + 127) / 128, 128, 0, st>>>(C, in, out);
+}
+void launch_expand_hcc(int C, const double* Hc, double* Hcc36, cudaStream_t st) {
+  if (C > 0) k_expand_hcc<<<(C * 36 + 255) / 256, 256, 0, st>>>(C, Hc, Hcc36);
+}
+
+}  // namespace mpba

@@ -1,0 +1,105 @@
+// ba_kernels.cuh -- sm_100a kernels of the bundle-adjustment hot path (declarations + launch args).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "ba_math.cuh"
+
+namespace mpba {
+
+// scalar slots (device doubles) one LM iteration produces
+enum Scal {
+  S_COST_FREE = 0,   // sum rho over blocks with a free parameter block (not halved)
+  S_COST_FIXED = 1,  // sum rho over blocks Ceres removes from the program
+  S_GMAX_C = 2,      // max |gc|
+  S_GMAX_P = 3,      // max |gp|
+  S_MCC = 4,         // model cost change
+  S_STEP2_P = 5,     // |X - X_cand|^2 over active points
+  S_XNORM2_P = 6,    // |X|^2 over active points
+  S_STEP2_C = 7,     // ambient |q - q_cand|^2 + |t - t_cand|^2 over active image blocks
+  S_XNORM2_C = 8,
+  S_PCG_ITERS = 9,
+  S_PCG_FLAG = 10,   // 0 converged, 1 iteration cap, 2 breakdown (p'Sp <= 0 or non-finite)
+  S_PCG_RES = 11,    // final sqrt(r'M^-1 r / b'M^-1 b)
+  S_BAD_POINTS = 12, // number of point blocks whose damped Hpp was not positive definite
+  S_COUNT = 16
+};
+
+constexpr int MPBA_MAX_PRM = 12;
+constexpr int IMG_PART = 32;  // doubles per image-chunk partial: 21 Hcc + 6 gc + cost_free + cost_fixed (+pad)
+constexpr int PT_PART = 4;    // doubles per track-CTA partial
+
+struct ProblemView {
+  int C, K, P, N, B, num_chunks;
+  const int32_t* img_camera;
+  const uint8_t* img_free_mask;
+  const double* img_shift_scale;
+  const int32_t* cam_model;
+  const double* cam_params;
+  const uint8_t* pt_const;
+  const int32_t* pt_ptr;
+  const int32_t* pm_img;
+  const double* pm_xy;
+  const double* pm_depth;
+  const int32_t* img_ptr;
+  const int32_t* cm_pt;
+  const double* cm_xy;
+  const double* cm_depth;
+  const int32_t* chunk_img;
+  const int32_t* chunk_begin;
+  const int32_t* chunk_end;
+  const int32_t* img_chunk_ptr;
+  const int32_t* s_row_ptr;
+  const int32_t* s_col;
+  const int32_t* s_diag;
+  const int32_t* s_transpose;
+  const int32_t* pair_ptr;
+  const int32_t* pair_block;
+  LossSpec loss;
+};
+
+struct LmDiag {
+  double radius, lo, hi;
+};
+
+// ---- image order: Hcc, gc, cost ------------------------------------------------------------
+void launch_img_chunks(const ProblemView& pv, const double* pose, const double* X, double* chunk_part,
+                       cudaStream_t st);
+void launch_img_finalize(const ProblemView& pv, const double* chunk_part, double* Hc, double* gc, double* img_part,
+                         double* c_img, int compute_scaling, int jacobi_scaling, cudaStream_t st);
+void launch_img_scalars(const ProblemView& pv, const double* img_part, const double* gc, double* scal,
+                        cudaStream_t st);
+
+// ---- track order: Hpp, gp, point-block inverse, Schur complement scatter ----------------------
+void launch_points_schur(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,
+                         int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* T,
+                         double* rhs_acc, double* pt_part, double* scal, int do_schur, cudaStream_t st);
+int points_grid(int P);
+void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaStream_t st);
+
+// ---- reduced camera system ----------------------------------------------------------------------
+void launch_s_finalize(const ProblemView& pv, const double* Hc, const double* gc, const double* c_img, LmDiag lm,
+                       const double* T, const double* rhs_acc, double* S, double* rhs, double* Minv,
+                       cudaStream_t st);
+// returns cudaError from the cooperative launch
+cudaError_t launch_pcg(const ProblemView& pv, const double* S, const double* Minv, const double* rhs, double* y,
+                       double* vec_r, double* vec_z, double* vec_p0, double* vec_p1, double* vec_q, double* partial,
+                       double* scal, double tol, int max_iter, int grid, cudaStream_t st);
+int pcg_grid(int device, int C);
+
+// ---- step ---------------------------------------------------------------------------------------
+void launch_cam_update(const ProblemView& pv, const double* pose, const double* y, double* pose_cand, double* scal,
+                       cudaStream_t st);
+void launch_back_substitute(const ProblemView& pv, const double* pose, const double* X, const double* y,
+                            const double* Hpp, const double* gp, const double* Hinv, double* X_cand, double* pt_part,
+                            cudaStream_t st);
+void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, cudaStream_t st);
+
+// ---- misc ---------------------------------------------------------------------------------------
+void launch_evaluate(const ProblemView& pv, const double* pose, const double* X, double* r_reproj, double* r_depth,
+                     cudaStream_t st);
+void launch_normalize_poses(int C, const double* in, double* out, cudaStream_t st);
+void launch_expand_hcc(int C, const double* Hc, double* Hcc36, cudaStream_t st);
+
+}  // namespace mpba

@@ -1,0 +1,481 @@
+// ba_math.cuh -- per-observation arithmetic of the bundle-adjustment hot path.
+//
+// Everything here is __host__ __device__ so that tests can compile the very same arithmetic with
+// g++ and compare it with the numpy oracle on the CPU box (tests/hostcheck); the product only ever
+// runs it inside the sm_100a kernels of ba_kernels.cu.
+//
+// What is computed (reference call sites under /root/reference/mpsfm/sfm/mapper/bundle_adjustment.py):
+//   :104      reprojection residual  r = ImgFromCam(params, q*X + t) - x_obs   (COLMAP cost functor)
+//   :163-176  log-depth prior        r = log(exp(s) d + b) - log((q*X + t)_z)  (fork-only functor)
+//   :98-102, :160-161  ScaledLoss(loss(a), w) on each residual block, Ceres corrector
+//   :114-122  tangent of an image = (half-angle rotation vector, translation)
+//
+// With p_rot = R(q) X, p = p_rot + t and a_k = d r_k / d p (rows of the 3x3 matrix A), every
+// Jacobian block of an observation factors through three small objects:
+//     Jc = A' G,   G = [ -2 [p_rot]x | I3 ]     (image tangent, 3x6)
+//     Jp = A' R                                  (point, 3x3)
+// where A' = diag(sqrt(rho'_k)) A is the robustified A.  The kernels therefore only need
+//     N = A'^T A'  (3x3 symmetric),   h = A'^T r'  (3),   p_rot,   R
+// per observation: Hcc += G^T N G, gc += G^T h, Hpp += R^T N R, gp += R^T h, W = G^T N R.
+#pragma once
+
+#include <float.h>
+#include <math.h>
+#include <stdint.h>
+
+#ifdef __CUDACC__
+#define MPBA_HD __host__ __device__ __forceinline__
+#else
+#define MPBA_HD inline
+#endif
+
+namespace mpba {
+
+// ------------------------------------------------------------------------------------------------
+// forward-mode dual number over (u, v): the analytic derivative carrier for the camera models that
+// have no short closed form (fisheye family, FOV, FULL_OPENCV, THIN_PRISM).
+struct Dual2 {
+  double a, du, dv;
+};
+MPBA_HD Dual2 mk(double a) { return Dual2{a, 0.0, 0.0}; }
+MPBA_HD Dual2 operator+(Dual2 x, Dual2 y) { return Dual2{x.a + y.a, x.du + y.du, x.dv + y.dv}; }
+MPBA_HD Dual2 operator-(Dual2 x, Dual2 y) { return Dual2{x.a - y.a, x.du - y.du, x.dv - y.dv}; }
+MPBA_HD Dual2 operator*(Dual2 x, Dual2 y) {
+  return Dual2{x.a * y.a, x.a * y.du + y.a * x.du, x.a * y.dv + y.a * x.dv};
+}
+MPBA_HD Dual2 operator/(Dual2 x, Dual2 y) {
+  const double inv = 1.0 / y.a, q = x.a * inv;
+  return Dual2{q, (x.du - q * y.du) * inv, (x.dv - q * y.dv) * inv};
+}
+MPBA_HD Dual2 operator+(Dual2 x, double y) { return Dual2{x.a + y, x.du, x.dv}; }
+MPBA_HD Dual2 operator+(double y, Dual2 x) { return Dual2{x.a + y, x.du, x.dv}; }
+MPBA_HD Dual2 operator-(Dual2 x, double y) { return Dual2{x.a - y, x.du, x.dv}; }
+MPBA_HD Dual2 operator-(double y, Dual2 x) { return Dual2{y - x.a, -x.du, -x.dv}; }
+MPBA_HD Dual2 operator*(Dual2 x, double y) { return Dual2{x.a * y, x.du * y, x.dv * y}; }
+MPBA_HD Dual2 operator*(double y, Dual2 x) { return Dual2{x.a * y, x.du * y, x.dv * y}; }
+MPBA_HD Dual2 operator/(Dual2 x, double y) {
+  const double inv = 1.0 / y;
+  return Dual2{x.a * inv, x.du * inv, x.dv * inv};
+}
+MPBA_HD Dual2 dsqrt(Dual2 x) {
+  const double s = sqrt(x.a), k = 0.5 / s;
+  return Dual2{s, k * x.du, k * x.dv};
+}
+MPBA_HD Dual2 datan(Dual2 x) {
+  const double k = 1.0 / (1.0 + x.a * x.a);
+  return Dual2{atan(x.a), k * x.du, k * x.dv};
+}
+MPBA_HD double dsqrt(double x) { return sqrt(x); }
+MPBA_HD double datan(double x) { return atan(x); }
+MPBA_HD double val(double x) { return x; }
+MPBA_HD double val(Dual2 x) { return x.a; }
+MPBA_HD double one_like(double) { return 1.0; }
+MPBA_HD Dual2 one_like(Dual2) { return Dual2{1.0, 0.0, 0.0}; }
+
+// ------------------------------------------------------------------------------------------------
+// Ceres loss functions (upstream loss_function.cc): rho and rho' of `type` with scale a at squared
+// norm s, multiplied by `weight` as ceres::ScaledLoss does.  All four have rho'' <= 0, so the
+// corrector (upstream corrector.cc) always takes its "alpha = 0" branch: rows scale by sqrt(rho').
+template <bool WANT_RHO>
+MPBA_HD void loss_eval(int type, double a, double weight, double s, double& rho, double& rho1) {
+  if (type == 0) {  // TRIVIAL
+    rho = s;
+    rho1 = 1.0;
+  } else {
+    const double b = a * a, c = 1.0 / b;
+    if (type == 1) {  // SOFT_L1
+      const double sum = 1.0 + s * c, tmp = sqrt(sum);
+      rho = 2.0 * b * (tmp - 1.0);
+      rho1 = fmax(DBL_MIN, 1.0 / tmp);
+    } else if (type == 2) {  // CAUCHY
+      const double sum = 1.0 + s * c, inv = 1.0 / sum;
+      rho = WANT_RHO ? b * log(sum) : 0.0;
+      rho1 = fmax(DBL_MIN, inv);
+    } else {  // HUBER
+      if (s > b) {
+        const double r = sqrt(s);
+        rho = 2.0 * a * r - b;
+        rho1 = fmax(DBL_MIN, a / r);
+      } else {
+        rho = s;
+        rho1 = 1.0;
+      }
+    }
+  }
+  rho *= weight;
+  rho1 *= weight;
+}
+
+// ------------------------------------------------------------------------------------------------
+// COLMAP ImgFromCam for normalised coordinates (u, v) = (X/Z, Y/Z); T = double or Dual2.
+template <class T>
+MPBA_HD T fisheye_scale(T u, T v, double k1, double k2, double k3, double k4, bool plain_theta) {
+  // theta_d / r with theta = atan(r);  1 where r <= eps (COLMAP leaves the point undistorted)
+  const double r2v = val(u) * val(u) + val(v) * val(v);
+  if (sqrt(r2v) <= DBL_EPSILON) return one_like(u);
+  const T r = dsqrt(u * u + v * v);
+  const T theta = datan(r);
+  if (plain_theta) return theta / r;
+  const T t2 = theta * theta;
+  const T poly = 1.0 + t2 * (k1 + t2 * (k2 + t2 * (k3 + t2 * k4)));
+  return theta * poly / r;
+}
+
+template <class T>
+MPBA_HD void img_from_cam_generic(int model, const double* p, T u, T v, T& x, T& y) {
+  switch (model) {
+    case 0:  // SIMPLE_PINHOLE f, cx, cy
+      x = p[0] * u + p[1];
+      y = p[0] * v + p[2];
+      break;
+    case 1:  // PINHOLE fx, fy, cx, cy
+      x = p[0] * u + p[2];
+      y = p[1] * v + p[3];
+      break;
+    case 2: {  // SIMPLE_RADIAL f, cx, cy, k
+      const T r2 = u * u + v * v;
+      const T radial = p[3] * r2;
+      x = p[0] * (u + u * radial) + p[1];
+      y = p[0] * (v + v * radial) + p[2];
+    } break;
+    case 3: {  // RADIAL f, cx, cy, k1, k2
+      const T r2 = u * u + v * v;
+      const T radial = p[3] * r2 + p[4] * r2 * r2;
+      x = p[0] * (u + u * radial) + p[1];
+      y = p[0] * (v + v * radial) + p[2];
+    } break;
+    case 4: {  // OPENCV fx, fy, cx, cy, k1, k2, p1, p2
+      const T u2 = u * u, v2 = v * v, uv = u * v;
+      const T r2 = u2 + v2;
+      const T radial = p[4] * r2 + p[5] * r2 * r2;
+      const T du = u * radial + 2.0 * p[6] * uv + p[7] * (r2 + 2.0 * u2);
+      const T dv = v * radial + 2.0 * p[7] * uv + p[6] * (r2 + 2.0 * v2);
+      x = p[0] * (u + du) + p[2];
+      y = p[1] * (v + dv) + p[3];
+    } break;
+    case 5: {  // OPENCV_FISHEYE fx, fy, cx, cy, k1..k4
+      const T s = fisheye_scale(u, v, p[4], p[5], p[6], p[7], false);
+      x = p[0] * (u * s) + p[2];
+      y = p[1] * (v * s) + p[3];
+    } break;
+    case 6: {  // FULL_OPENCV fx, fy, cx, cy, k1, k2, p1, p2, k3, k4, k5, k6
+      const T u2 = u * u, v2 = v * v, uv = u * v;
+      const T r2 = u2 + v2, r4 = r2 * r2, r6 = r4 * r2;
+      const T radial = (1.0 + p[4] * r2 + p[5] * r4 + p[8] * r6) / (1.0 + p[9] * r2 + p[10] * r4 + p[11] * r6);
+      const T du = u * radial + 2.0 * p[6] * uv + p[7] * (r2 + 2.0 * u2) - u;
+      const T dv = v * radial + 2.0 * p[7] * uv + p[6] * (r2 + 2.0 * v2) - v;
+      x = p[0] * (u + du) + p[2];
+      y = p[1] * (v + dv) + p[3];
+    } break;
+    case 7: {  // FOV fx, fy, cx, cy, omega
+      const double omega = p[4], omega2 = omega * omega, kEps = 1e-4;
+      const T r2 = u * u + v * v;
+      T factor;
+      if (omega2 < kEps) {
+        factor = (omega2 * r2) / 3.0 - omega2 / 12.0 + 1.0;
+      } else {
+        const double th = tan(omega / 2.0);
+        if (val(r2) < kEps) {
+          factor = (-2.0 * th * (4.0 * r2 * th * th - 3.0)) / (3.0 * omega);
+        } else {
+          const T radius = dsqrt(r2);
+          factor = datan(radius * 2.0 * th) / (radius * omega);
+        }
+      }
+      x = p[0] * (u * factor) + p[2];
+      y = p[1] * (v * factor) + p[3];
+    } break;
+    case 8: {  // SIMPLE_RADIAL_FISHEYE f, cx, cy, k
+      const T s = fisheye_scale(u, v, p[3], 0.0, 0.0, 0.0, false);
+      x = p[0] * (u * s) + p[1];
+      y = p[0] * (v * s) + p[2];
+    } break;
+    case 9: {  // RADIAL_FISHEYE f, cx, cy, k1, k2
+      const T s = fisheye_scale(u, v, p[3], p[4], 0.0, 0.0, false);
+      x = p[0] * (u * s) + p[1];
+      y = p[0] * (v * s) + p[2];
+    } break;
+    default: {  // 10 THIN_PRISM_FISHEYE fx, fy, cx, cy, k1, k2, p1, p2, k3, k4, sx1, sy1
+      const T s = fisheye_scale(u, v, 0.0, 0.0, 0.0, 0.0, true);
+      const T uu = u * s, vv = v * s;
+      const T u2 = uu * uu, v2 = vv * vv, uv = uu * vv;
+      const T t2 = u2 + v2, t4 = t2 * t2;
+      const T radial = p[4] * t2 + p[5] * t4 + p[8] * t4 * t2 + p[9] * t4 * t4;
+      const T du = uu * radial + 2.0 * p[6] * uv + p[7] * (t2 + 2.0 * u2) + p[10] * t2;
+      const T dv = vv * radial + 2.0 * p[7] * uv + p[6] * (t2 + 2.0 * v2) + p[11] * t2;
+      x = p[0] * (uu + du) + p[2];
+      y = p[1] * (vv + dv) + p[3];
+    } break;
+  }
+}
+
+// value + 2x2 Jacobian D = d(x,y)/d(u,v) (row-major).  Closed forms for the five models the
+// reference pipeline can meet in practice, duals for the rest.
+MPBA_HD void img_from_cam_jac(int model, const double* p, double u, double v, double& x, double& y, double D[4]) {
+  switch (model) {
+    case 0:
+      x = p[0] * u + p[1];
+      y = p[0] * v + p[2];
+      D[0] = p[0]; D[1] = 0.0; D[2] = 0.0; D[3] = p[0];
+      return;
+    case 1:
+      x = p[0] * u + p[2];
+      y = p[1] * v + p[3];
+      D[0] = p[0]; D[1] = 0.0; D[2] = 0.0; D[3] = p[1];
+      return;
+    case 2: {
+      const double r2 = u * u + v * v, k = p[3], f = p[0];
+      const double radial = k * r2;
+      x = f * (u + u * radial) + p[1];
+      y = f * (v + v * radial) + p[2];
+      const double g = 1.0 + radial, kuv2 = 2.0 * k * u * v;
+      D[0] = f * (g + 2.0 * k * u * u); D[1] = f * kuv2; D[2] = f * kuv2; D[3] = f * (g + 2.0 * k * v * v);
+      return;
+    }
+    case 3: {
+      const double r2 = u * u + v * v, f = p[0];
+      const double radial = p[3] * r2 + p[4] * r2 * r2;
+      x = f * (u + u * radial) + p[1];
+      y = f * (v + v * radial) + p[2];
+      const double g = 1.0 + radial, gp = p[3] + 2.0 * p[4] * r2, c = 2.0 * u * v * gp;
+      D[0] = f * (g + 2.0 * u * u * gp); D[1] = f * c; D[2] = f * c; D[3] = f * (g + 2.0 * v * v * gp);
+      return;
+    }
+    case 4: {
+      const double k1 = p[4], k2 = p[5], p1 = p[6], p2 = p[7];
+      const double u2 = u * u, v2 = v * v, uv = u * v, r2 = u2 + v2;
+      const double radial = k1 * r2 + k2 * r2 * r2;
+      const double du = u * radial + 2.0 * p1 * uv + p2 * (r2 + 2.0 * u2);
+      const double dv = v * radial + 2.0 * p2 * uv + p1 * (r2 + 2.0 * v2);
+      x = p[0] * (u + du) + p[2];
+      y = p[1] * (v + dv) + p[3];
+      const double gp = k1 + 2.0 * k2 * r2;  // d radial / d r2
+      const double cross = 2.0 * (p1 * u + p2 * v + uv * gp);
+      D[0] = p[0] * (1.0 + radial + 2.0 * u2 * gp + 2.0 * p1 * v + 6.0 * p2 * u);
+      D[1] = p[0] * cross;
+      D[2] = p[1] * cross;
+      D[3] = p[1] * (1.0 + radial + 2.0 * v2 * gp + 6.0 * p1 * v + 2.0 * p2 * u);
+      return;
+    }
+    default: {
+      Dual2 xd, yd;
+      img_from_cam_generic<Dual2>(model, p, Dual2{u, 1.0, 0.0}, Dual2{v, 0.0, 1.0}, xd, yd);
+      x = xd.a;
+      y = yd.a;
+      D[0] = xd.du; D[1] = xd.dv; D[2] = yd.du; D[3] = yd.dv;
+      return;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// small dense helpers; symmetric 3x3 stored as (xx, xy, xz, yy, yz, zz)
+MPBA_HD void quat_to_rotmat(const double q[4], double R[9]) {
+  const double x = q[0], y = q[1], z = q[2], w = q[3];
+  R[0] = 1.0 - 2.0 * (y * y + z * z); R[1] = 2.0 * (x * y - z * w);       R[2] = 2.0 * (x * z + y * w);
+  R[3] = 2.0 * (x * y + z * w);       R[4] = 1.0 - 2.0 * (x * x + z * z); R[5] = 2.0 * (y * z - x * w);
+  R[6] = 2.0 * (x * z - y * w);       R[7] = 2.0 * (y * z + x * w);       R[8] = 1.0 - 2.0 * (x * x + y * y);
+}
+
+// Eigen's Quaternion::_transformVector: v + 2w (u x v) + 2 u x (u x v)
+MPBA_HD void quat_rotate(const double q[4], const double v[3], double out[3]) {
+  double uvx = q[1] * v[2] - q[2] * v[1], uvy = q[2] * v[0] - q[0] * v[2], uvz = q[0] * v[1] - q[1] * v[0];
+  uvx += uvx; uvy += uvy; uvz += uvz;
+  out[0] = v[0] + q[3] * uvx + (q[1] * uvz - q[2] * uvy);
+  out[1] = v[1] + q[3] * uvy + (q[2] * uvx - q[0] * uvz);
+  out[2] = v[2] + q[3] * uvz + (q[0] * uvy - q[1] * uvx);
+}
+
+// ceres::EigenQuaternionManifold::Plus: q (+) d = [sin|d| d/|d|, cos|d|] (x) q
+MPBA_HD void quat_plus(const double q[4], const double d[3], double out[4]) {
+  const double n2 = d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
+  if (n2 == 0.0) {
+    out[0] = q[0]; out[1] = q[1]; out[2] = q[2]; out[3] = q[3];
+    return;
+  }
+  const double n = sqrt(n2), sbd = sin(n) / n;
+  const double ax = d[0] * sbd, ay = d[1] * sbd, az = d[2] * sbd, aw = cos(n);
+  const double bx = q[0], by = q[1], bz = q[2], bw = q[3];
+  out[0] = aw * bx + ax * bw + ay * bz - az * by;
+  out[1] = aw * by - ax * bz + ay * bw + az * bx;
+  out[2] = aw * bz + ax * by - ay * bx + az * bw;
+  out[3] = aw * bw - ax * bx - ay * by - az * bz;
+}
+
+MPBA_HD void cross3(const double a[3], const double b[3], double c[3]) {
+  c[0] = a[1] * b[2] - a[2] * b[1];
+  c[1] = a[2] * b[0] - a[0] * b[2];
+  c[2] = a[0] * b[1] - a[1] * b[0];
+}
+
+MPBA_HD void sym3_mul_vec(const double S[6], const double v[3], double o[3]) {
+  o[0] = S[0] * v[0] + S[1] * v[1] + S[2] * v[2];
+  o[1] = S[1] * v[0] + S[3] * v[1] + S[4] * v[2];
+  o[2] = S[2] * v[0] + S[4] * v[1] + S[5] * v[2];
+}
+
+// Q = N R  (N symmetric 3x3, R row-major 3x3)
+MPBA_HD void sym3_mul_mat(const double N[6], const double R[9], double Q[9]) {
+  for (int j = 0; j < 3; ++j) {
+    const double r0 = R[j], r1 = R[3 + j], r2 = R[6 + j];
+    Q[j] = N[0] * r0 + N[1] * r1 + N[2] * r2;
+    Q[3 + j] = N[1] * r0 + N[3] * r1 + N[4] * r2;
+    Q[6 + j] = N[2] * r0 + N[4] * r1 + N[5] * r2;
+  }
+}
+
+// inverse of a symmetric positive definite 3x3 through its Cholesky factor (what Ceres' Schur
+// eliminator does with Eigen's LLT on the e-block); returns false if not positive definite.
+MPBA_HD bool sym3_inverse(const double H[6], double Hi[6]) {
+  const double a = H[0], b = H[1], c = H[2], d = H[3], e = H[4], f = H[5];
+  if (!(a > 0.0)) return false;
+  const double l00 = sqrt(a), l10 = b / l00, l20 = c / l00;
+  const double t11 = d - l10 * l10;
+  if (!(t11 > 0.0)) return false;
+  const double l11 = sqrt(t11), l21 = (e - l20 * l10) / l11;
+  const double t22 = f - l20 * l20 - l21 * l21;
+  if (!(t22 > 0.0)) return false;
+  const double l22 = sqrt(t22);
+  // inverse of L (lower)
+  const double i00 = 1.0 / l00, i11 = 1.0 / l11, i22 = 1.0 / l22;
+  const double i10 = -l10 * i00 * i11;
+  const double i21 = -l21 * i11 * i22;
+  const double i20 = -(l20 * i00 + l21 * i10) * i22;
+  // H^-1 = L^-T L^-1
+  Hi[0] = i00 * i00 + i10 * i10 + i20 * i20;
+  Hi[1] = i10 * i11 + i20 * i21;
+  Hi[2] = i20 * i22;
+  Hi[3] = i11 * i11 + i21 * i21;
+  Hi[4] = i21 * i22;
+  Hi[5] = i22 * i22;
+  return true;
+}
+
+// ------------------------------------------------------------------------------------------------
+struct LossSpec {
+  int reproj_loss, depth_loss;
+  double reproj_scale, reproj_weight;
+};
+
+struct ObsLin {
+  double N[6];     // A'^T A'
+  double h[3];     // A'^T r'
+  double prot[3];  // R(q) X
+  double rho;      // rho_reproj + rho_depth of the two blocks (not halved)
+  double r[3];     // raw residuals (x, y, log-depth); r[2] = 0 without a prior
+};
+
+// One observation.  pose = {qx,qy,qz,qw,tx,ty,tz}, R = rotmat(q), X the point, (d, w, a) the depth
+// prior (w == 0: none), (b, s) the image's shift / log-scale.
+template <bool WANT_JAC, bool WANT_RHO>
+MPBA_HD void linearize_obs(const double* pose, const double R[9], const double X[3], int model, const double* prm,
+                           double ox, double oy, double d, double w, double a, double b, double s,
+                           const LossSpec& ls, ObsLin& o) {
+  o.prot[0] = R[0] * X[0] + R[1] * X[1] + R[2] * X[2];
+  o.prot[1] = R[3] * X[0] + R[4] * X[1] + R[5] * X[2];
+  o.prot[2] = R[6] * X[0] + R[7] * X[1] + R[8] * X[2];
+  const double px = o.prot[0] + pose[4], py = o.prot[1] + pose[5], pz = o.prot[2] + pose[6];
+  const double iz = 1.0 / pz, u = px * iz, v = py * iz;
+  double x, y, D[4];
+  if (WANT_JAC) {
+    img_from_cam_jac(model, prm, u, v, x, y, D);
+  } else {
+    img_from_cam_generic<double>(model, prm, u, v, x, y);
+  }
+  const double r0 = x - ox, r1 = y - oy;
+  o.r[0] = r0;
+  o.r[1] = r1;
+  double rho, rho1;
+  loss_eval<WANT_RHO>(ls.reproj_loss, ls.reproj_scale, ls.reproj_weight, r0 * r0 + r1 * r1, rho, rho1);
+  o.rho = rho;
+  double a0[3], a1[3];
+  if (WANT_JAC) {
+    // rows of d(x,y)/dp = D * [[1/z, 0, -u/z], [0, 1/z, -v/z]]
+    a0[0] = D[0] * iz; a0[1] = D[1] * iz; a0[2] = -(D[0] * u + D[1] * v) * iz;
+    a1[0] = D[2] * iz; a1[1] = D[3] * iz; a1[2] = -(D[2] * u + D[3] * v) * iz;
+    o.N[0] = rho1 * (a0[0] * a0[0] + a1[0] * a1[0]);
+    o.N[1] = rho1 * (a0[0] * a0[1] + a1[0] * a1[1]);
+    o.N[2] = rho1 * (a0[0] * a0[2] + a1[0] * a1[2]);
+    o.N[3] = rho1 * (a0[1] * a0[1] + a1[1] * a1[1]);
+    o.N[4] = rho1 * (a0[1] * a0[2] + a1[1] * a1[2]);
+    o.N[5] = rho1 * (a0[2] * a0[2] + a1[2] * a1[2]);
+    o.h[0] = rho1 * (a0[0] * r0 + a1[0] * r1);
+    o.h[1] = rho1 * (a0[1] * r0 + a1[1] * r1);
+    o.h[2] = rho1 * (a0[2] * r0 + a1[2] * r1);
+  }
+  o.r[2] = 0.0;
+  if (w > 0.0) {
+    const double r2 = log((exp(s) * d + b) * iz);
+    o.r[2] = r2;
+    double rhod, rhod1;
+    loss_eval<WANT_RHO>(ls.depth_loss, a, w, r2 * r2, rhod, rhod1);
+    o.rho += rhod;
+    if (WANT_JAC) {
+      // a2 = (0, 0, -1/z)
+      o.N[5] += rhod1 * iz * iz;
+      o.h[2] -= rhod1 * iz * r2;
+    }
+  }
+}
+
+// G^T h = [2 p x h ; h]
+MPBA_HD void gt_vec(const double p[3], const double h[3], double o[6]) {
+  double c[3];
+  cross3(p, h, c);
+  o[0] = 2.0 * c[0]; o[1] = 2.0 * c[1]; o[2] = 2.0 * c[2];
+  o[3] = h[0]; o[4] = h[1]; o[5] = h[2];
+}
+
+// G y = y_t - 2 p x y_r
+MPBA_HD void g_vec(const double p[3], const double y[6], double o[3]) {
+  double c[3];
+  cross3(p, y, c);
+  o[0] = y[3] - 2.0 * c[0];
+  o[1] = y[4] - 2.0 * c[1];
+  o[2] = y[5] - 2.0 * c[2];
+}
+
+// explicit G (3x6 row-major) = [-2 [p]x | I]
+MPBA_HD void g_matrix(const double p[3], double G[18]) {
+  G[0] = 0.0;          G[1] = 2.0 * p[2];   G[2] = -2.0 * p[1];  G[3] = 1.0; G[4] = 0.0; G[5] = 0.0;
+  G[6] = -2.0 * p[2];  G[7] = 0.0;          G[8] = 2.0 * p[0];   G[9] = 0.0; G[10] = 1.0; G[11] = 0.0;
+  G[12] = 2.0 * p[1];  G[13] = -2.0 * p[0]; G[14] = 0.0;         G[15] = 0.0; G[16] = 0.0; G[17] = 1.0;
+}
+
+// upper triangle (21 values, row-major: (0,0..5),(1,1..5),...) of G^T N G
+MPBA_HD void gt_n_g_upper(const double p[3], const double N[6], double H[21]) {
+  double G[18], T[18];
+  g_matrix(p, G);
+  for (int j = 0; j < 6; ++j) {
+    const double g0 = G[j], g1 = G[6 + j], g2 = G[12 + j];
+    T[j] = N[0] * g0 + N[1] * g1 + N[2] * g2;
+    T[6 + j] = N[1] * g0 + N[3] * g1 + N[4] * g2;
+    T[12 + j] = N[2] * g0 + N[4] * g1 + N[5] * g2;
+  }
+  int k = 0;
+  for (int i = 0; i < 6; ++i)
+    for (int j = i; j < 6; ++j) H[k++] = G[i] * T[j] + G[6 + i] * T[6 + j] + G[12 + i] * T[12 + j];
+}
+
+// M (6x6 row-major) = Ga^T K Gb for a 3x3 K (row-major)
+MPBA_HD void gt_k_g(const double pa[3], const double K[9], const double pb[3], double M[36]) {
+  double Ga[18], Gb[18], T[18];
+  g_matrix(pa, Ga);
+  g_matrix(pb, Gb);
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 6; ++j) T[6 * i + j] = K[3 * i] * Gb[j] + K[3 * i + 1] * Gb[6 + j] + K[3 * i + 2] * Gb[12 + j];
+  for (int i = 0; i < 6; ++i)
+    for (int j = 0; j < 6; ++j) M[6 * i + j] = Ga[i] * T[j] + Ga[6 + i] * T[6 + j] + Ga[12 + i] * T[12 + j];
+}
+
+// Ceres LM damping of one tangent coordinate in unscaled variables:
+//   scaled system adds clamp(c^2 H_jj, lo, hi) / radius to the diagonal of diag(c) H diag(c),
+//   i.e. the unscaled one adds clamp(c^2 H_jj) / (radius c^2).
+MPBA_HD double lm_damping(double hjj, double c, double radius, double lo, double hi) {
+  const double cc = c * c;
+  double dj = cc * hjj;
+  dj = dj < lo ? lo : (dj > hi ? hi : dj);
+  return dj / (radius * cc);
+}
+
+}  // namespace mpba

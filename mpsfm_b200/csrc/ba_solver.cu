@@ -1,0 +1,640 @@
+// ba_solver.cu -- C ABI (include/mpba.h) and the host side of the Levenberg-Marquardt loop.
+//
+// The loop restates Ceres 2.1's TrustRegionMinimizer + LevenbergMarquardtStrategy, which is what
+// the reference runs through pyceres.solve (/root/reference/mpsfm/sfm/mapper/bundle_adjustment.py:285-293:
+// SPARSE_SCHUR, otherwise Ceres defaults).  Order of events per iteration:
+//   linear solve -> invalid step? -> candidate cost -> parameter tolerance -> function tolerance ->
+//   accept / reject -> radius update -> max-iterations / gradient / min-radius checks.
+// Everything numeric runs in the kernels of ba_kernels.cu on the handle's stream; the host only
+// reads back one block of 16 scalars per LM iteration to take the accept / reject decision.
+#include <cuda_runtime.h>
+#include <float.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/mpba.h"
+#include "ba_kernels.cuh"
+
+using namespace mpba;
+
+enum KernelSlot {
+  KS_IMG_CHUNKS = 0, KS_IMG_FINALIZE, KS_POINTS_SCHUR, KS_S_FINALIZE, KS_PCG, KS_CAM_UPDATE, KS_BACK_SUBSTITUTE,
+  KS_REDUCE, KS_EVALUATE, KS_MISC, KS_SPARE0, KS_SPARE1
+};
+static const char* kKernelNames[MPBA_NUM_KERNELS] = {
+    "img_chunks", "img_finalize", "points_schur", "s_finalize", "pcg", "cam_update", "back_substitute",
+    "reduce", "evaluate", "misc", "spare0", "spare1"};
+
+struct TimedEvent {
+  cudaEvent_t a, b;
+  int slot;
+};
+
+struct mpba_handle {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  double* h_scal = nullptr;  // pinned
+  std::vector<TimedEvent> pool;
+  size_t used = 0;
+  bool profile = false;
+  double ms[MPBA_NUM_KERNELS] = {0};
+  int64_t launches[MPBA_NUM_KERNELS] = {0};
+  int64_t launch_count = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int pcg_grid_sms = 0;
+};
+
+namespace {
+
+int fail(mpba_handle* h, int code, const std::string& msg) {
+  if (h) h->err = msg;
+  return code;
+}
+
+#define CU(call)                                                                                       \
+  do {                                                                                                 \
+    cudaError_t e_ = (call);                                                                           \
+    if (e_ != cudaSuccess)                                                                             \
+      return fail(h, MPBA_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));                 \
+  } while (0)
+
+struct Timer {
+  mpba_handle* h;
+  int slot;
+  size_t idx = (size_t)-1;
+  Timer(mpba_handle* h_, int slot_, int nkernels = 1) : h(h_), slot(slot_) {
+    h->launch_count += nkernels;
+    h->launches[slot] += nkernels;
+    if (!h->profile) return;
+    if (h->used == h->pool.size()) {
+      TimedEvent t;
+      cudaEventCreate(&t.a);
+      cudaEventCreate(&t.b);
+      t.slot = slot;
+      h->pool.push_back(t);
+    }
+    idx = h->used++;
+    h->pool[idx].slot = slot;
+    cudaEventRecord(h->pool[idx].a, h->stream);
+  }
+  ~Timer() {
+    if (idx != (size_t)-1) cudaEventRecord(h->pool[idx].b, h->stream);
+  }
+};
+
+// call after a stream synchronize
+void flush_timers(mpba_handle* h) {
+  for (size_t i = 0; i < h->used; ++i) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, h->pool[i].a, h->pool[i].b) == cudaSuccess) h->ms[h->pool[i].slot] += ms;
+  }
+  h->used = 0;
+}
+
+size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct Workspace {
+  double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *img_part, *c_img, *c_pt, *Hpp, *gp, *Hinv, *T, *S, *rhs_acc,
+      *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal;
+  size_t bytes = 0;
+};
+
+// bump allocation; base == nullptr just measures
+void carve(const mpba_problem* p, char* base, Workspace& w) {
+  size_t off = 0;
+  auto take = [&](size_t n_doubles) -> double* {
+    double* ptr = base ? reinterpret_cast<double*>(base + off) : nullptr;
+    off += align_up(n_doubles * sizeof(double));
+    return ptr;
+  };
+  const size_t C = p->num_images, P = p->num_points, B = p->num_blocks;
+  const size_t nblk = (size_t)points_grid((int)P);
+  for (int k = 0; k < 2; ++k) {
+    w.pose[k] = take(C * 8);
+    w.X[k] = take(P * 4);
+    w.Hc[k] = take(C * 21);
+    w.gc[k] = take(C * 6);
+  }
+  w.chunk_part = take((size_t)p->num_chunks * IMG_PART);
+  w.img_part = take(C * 2);
+  w.c_img = take(C * 6);
+  w.c_pt = take(P * 3);
+  w.Hpp = take(P * 6);
+  w.gp = take(P * 3);
+  w.Hinv = take(P * 6);
+  w.T = take(B * 36);
+  w.S = take(B * 36);
+  w.rhs_acc = take(C * 6);
+  w.rhs = take(C * 6);
+  w.Minv = take(C * 36);
+  w.y = take(C * 6);
+  w.vr = take(C * 6);
+  w.vz = take(C * 6);
+  w.vp0 = take(C * 6);
+  w.vp1 = take(C * 6);
+  w.vq = take(C * 6);
+  w.partial = take(2 * 2048);
+  w.pt_part = take(nblk * PT_PART + 8);
+  w.scal = take(S_COUNT);
+  w.bytes = off;
+}
+
+int check_problem(mpba_handle* h, const mpba_problem* p) {
+  if (!p) return fail(h, MPBA_E_INVALID, "problem is NULL");
+  if (p->num_images <= 0 || p->num_points < 0 || p->num_obs < 0 || p->num_cameras <= 0)
+    return fail(h, MPBA_E_INVALID, "problem sizes must be positive (num_images, num_cameras) / non-negative");
+  if (!p->img_pose || !p->img_camera || !p->img_free_mask || !p->img_shift_scale || !p->cam_model || !p->cam_params)
+    return fail(h, MPBA_E_INVALID, "image / camera arrays must not be NULL");
+  if (p->num_points > 0 && (!p->pt_xyz || !p->pt_const || !p->pt_ptr))
+    return fail(h, MPBA_E_INVALID, "point arrays must not be NULL");
+  if (p->num_obs > 0 && (!p->pm_img || !p->pm_xy || !p->pm_depth || !p->cm_pt || !p->cm_xy || !p->cm_depth))
+    return fail(h, MPBA_E_INVALID, "observation arrays must not be NULL");
+  if (!p->img_ptr || !p->img_chunk_ptr || (p->num_chunks > 0 && (!p->chunk_img || !p->chunk_begin || !p->chunk_end)))
+    return fail(h, MPBA_E_INVALID, "image-order chunk arrays must not be NULL");
+  if (p->num_blocks < p->num_images || !p->s_row_ptr || !p->s_col || !p->s_diag || !p->s_transpose)
+    return fail(h, MPBA_E_INVALID, "reduced camera system structure missing (needs at least the diagonal blocks)");
+  if (p->num_obs > 0 && (!p->pair_ptr || !p->pair_block))
+    return fail(h, MPBA_E_INVALID, "pair_ptr / pair_block must not be NULL");
+  if (p->reproj_loss < 0 || p->reproj_loss > 3 || p->depth_loss < 0 || p->depth_loss > 3)
+    return fail(h, MPBA_E_INVALID, "unknown loss type");
+  return MPBA_OK;
+}
+
+ProblemView view_of(const mpba_problem* p) {
+  ProblemView v;
+  v.C = p->num_images; v.K = p->num_cameras; v.P = p->num_points; v.N = p->num_obs; v.B = p->num_blocks;
+  v.num_chunks = p->num_chunks;
+  v.img_camera = p->img_camera; v.img_free_mask = p->img_free_mask; v.img_shift_scale = p->img_shift_scale;
+  v.cam_model = p->cam_model; v.cam_params = p->cam_params; v.pt_const = p->pt_const; v.pt_ptr = p->pt_ptr;
+  v.pm_img = p->pm_img; v.pm_xy = p->pm_xy; v.pm_depth = p->pm_depth; v.img_ptr = p->img_ptr; v.cm_pt = p->cm_pt;
+  v.cm_xy = p->cm_xy; v.cm_depth = p->cm_depth; v.chunk_img = p->chunk_img; v.chunk_begin = p->chunk_begin;
+  v.chunk_end = p->chunk_end; v.img_chunk_ptr = p->img_chunk_ptr; v.s_row_ptr = p->s_row_ptr; v.s_col = p->s_col;
+  v.s_diag = p->s_diag; v.s_transpose = p->s_transpose; v.pair_ptr = p->pair_ptr; v.pair_block = p->pair_block;
+  v.loss.reproj_loss = p->reproj_loss; v.loss.depth_loss = p->depth_loss;
+  v.loss.reproj_scale = p->reproj_loss_scale; v.loss.reproj_weight = p->reproj_loss_weight;
+  return v;
+}
+
+struct Ctx {
+  mpba_handle* h;
+  ProblemView pv;
+  Workspace w;
+  int nblk;
+  int structure_only;
+};
+
+int begin(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes, Ctx& c) {
+  if (!h) return MPBA_E_INVALID;
+  int rc = check_problem(h, prob);
+  if (rc) return rc;
+  Workspace probe;
+  carve(prob, nullptr, probe);
+  if (!workspace || workspace_bytes < probe.bytes)
+    return fail(h, MPBA_E_WORKSPACE, "workspace too small: need " + std::to_string(probe.bytes) + " bytes");
+  CU(cudaSetDevice(h->device));
+  c.h = h;
+  c.pv = view_of(prob);
+  carve(prob, static_cast<char*>(workspace), c.w);
+  c.nblk = points_grid(prob->num_points);
+  c.structure_only = prob->flags & MPBA_FLAG_STRUCTURE_ONLY;
+  h->launch_count = 0;
+  return MPBA_OK;
+}
+
+// cost / Hcc / gc of state (pose, X) into buffer set k
+void enqueue_image_pass(Ctx& c, const double* pose, const double* X, int k, int compute_scaling, int jacobi) {
+  mpba_handle* h = c.h;
+  {
+    Timer t(h, KS_IMG_CHUNKS);
+    launch_img_chunks(c.pv, pose, X, c.w.chunk_part, h->stream);
+  }
+  {
+    Timer t(h, KS_IMG_FINALIZE, 2);
+    launch_img_finalize(c.pv, c.w.chunk_part, c.w.Hc[k], c.w.gc[k], c.w.img_part, c.w.c_img, compute_scaling, jacobi,
+                        h->stream);
+    launch_img_scalars(c.pv, c.w.img_part, c.w.gc[k], c.w.scal, h->stream);
+  }
+}
+
+int fetch_scalars(Ctx& c) {
+  mpba_handle* h = c.h;
+  CU(cudaMemcpyAsync(h->h_scal, c.w.scal, S_COUNT * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  CU(cudaGetLastError());
+  if (h->profile) flush_timers(h);
+  return MPBA_OK;
+}
+
+int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int kset, LmDiag lm, int compute_scaling,
+                              const mpba_options* opt, bool want_system) {
+  mpba_handle* h = c.h;
+  const bool schur = want_system && !c.structure_only;
+  if (schur) {
+    Timer t(h, KS_MISC, 0);
+    CU(cudaMemsetAsync(c.w.T, 0, (size_t)c.pv.B * 36 * sizeof(double), h->stream));
+    CU(cudaMemsetAsync(c.w.rhs_acc, 0, (size_t)c.pv.C * 6 * sizeof(double), h->stream));
+  }
+  CU(cudaMemsetAsync(c.w.scal + S_BAD_POINTS, 0, sizeof(double), h->stream));
+  {
+    Timer t(h, KS_POINTS_SCHUR);
+    launch_points_schur(c.pv, pose, X, lm, c.w.c_pt, compute_scaling, opt->jacobi_scaling, c.w.Hpp, c.w.gp, c.w.Hinv,
+                        c.w.T, c.w.rhs_acc, c.w.pt_part, c.w.scal, schur ? 1 : 0, h->stream);
+  }
+  {
+    Timer t(h, KS_REDUCE);
+    launch_pt_scalars_gmax(c.w.pt_part, c.nblk, c.w.scal, h->stream);
+  }
+  if (!want_system) return MPBA_OK;
+  if (schur) {
+    {
+      Timer t(h, KS_S_FINALIZE, 2);
+      launch_s_finalize(c.pv, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.T, c.w.rhs_acc, c.w.S, c.w.rhs, c.w.Minv,
+                        h->stream);
+    }
+    {
+      Timer t(h, KS_PCG);
+      const int grid = pcg_grid(h->device, c.pv.C);
+      cudaError_t e = launch_pcg(c.pv, c.w.S, c.w.Minv, c.w.rhs, c.w.y, c.w.vr, c.w.vz, c.w.vp0, c.w.vp1, c.w.vq,
+                                 c.w.partial, c.w.scal, opt->pcg_tolerance, opt->pcg_max_iterations, grid, h->stream);
+      if (e != cudaSuccess) return fail(h, MPBA_E_CUDA, std::string("cooperative PCG launch: ") + cudaGetErrorString(e));
+    }
+  } else {
+    // all poses constant (refine_3d_points, bundle_adjustment.py:276-283): no reduced system, y_c = 0
+    CU(cudaMemsetAsync(c.w.y, 0, (size_t)c.pv.C * 6 * sizeof(double), h->stream));
+    CU(cudaMemsetAsync(c.w.scal + S_PCG_ITERS, 0, 3 * sizeof(double), h->stream));
+  }
+  return MPBA_OK;
+}
+
+}  // namespace
+
+// =================================================================================================
+extern "C" {
+
+int mpba_version(void) { return MPBA_VERSION; }
+
+const char* mpba_kernel_name(int slot) { return (slot >= 0 && slot < MPBA_NUM_KERNELS) ? kKernelNames[slot] : ""; }
+
+void mpba_default_options(mpba_options* o) {
+  if (!o) return;
+  memset(o, 0, sizeof(*o));
+  o->max_num_iterations = 50;
+  o->max_num_consecutive_invalid_steps = 5;
+  o->jacobi_scaling = 1;
+  o->pcg_max_iterations = 2000;
+  o->initial_trust_region_radius = 1e4;
+  o->max_trust_region_radius = 1e16;
+  o->min_trust_region_radius = 1e-32;
+  o->min_relative_decrease = 1e-3;
+  o->min_lm_diagonal = 1e-6;
+  o->max_lm_diagonal = 1e32;
+  o->function_tolerance = 1e-6;
+  o->gradient_tolerance = 1e-10;
+  o->parameter_tolerance = 1e-8;
+  o->pcg_tolerance = 1e-12;
+  o->profile = 0;
+  o->verbose = 0;
+}
+
+int mpba_create(mpba_handle** out, int device, void* cuda_stream) {
+  if (!out) return MPBA_E_INVALID;
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0 || device < 0 || device >= n) return MPBA_E_CUDA;  // no CPU fallback
+  mpba_handle* h = new mpba_handle();
+  h->device = device;
+  h->stream = static_cast<cudaStream_t>(cuda_stream);
+  if (cudaSetDevice(device) != cudaSuccess || cudaMallocHost(&h->h_scal, S_COUNT * sizeof(double)) != cudaSuccess ||
+      cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess) {
+    delete h;
+    return MPBA_E_CUDA;
+  }
+  *out = h;
+  return MPBA_OK;
+}
+
+void mpba_destroy(mpba_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  for (auto& t : h->pool) {
+    cudaEventDestroy(t.a);
+    cudaEventDestroy(t.b);
+  }
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->h_scal) cudaFreeHost(h->h_scal);
+  delete h;
+}
+
+const char* mpba_last_error(const mpba_handle* h) { return h ? h->err.c_str() : "invalid handle"; }
+
+int mpba_workspace_bytes(const mpba_problem* prob, size_t* bytes) {
+  if (!prob || !bytes) return MPBA_E_INVALID;
+  Workspace w;
+  carve(prob, nullptr, w);
+  *bytes = w.bytes;
+  return MPBA_OK;
+}
+
+int mpba_kernel_times(const mpba_handle* h, double* ms, int64_t* launches) {
+  if (!h) return MPBA_E_INVALID;
+  for (int i = 0; i < MPBA_NUM_KERNELS; ++i) {
+    if (ms) ms[i] = h->ms[i];
+    if (launches) launches[i] = h->launches[i];
+  }
+  return MPBA_OK;
+}
+
+static void reset_profile(mpba_handle* h, int profile) {
+  h->profile = profile != 0;
+  for (int i = 0; i < MPBA_NUM_KERNELS; ++i) {
+    h->ms[i] = 0.0;
+    h->launches[i] = 0;
+  }
+  h->used = 0;
+}
+
+int mpba_evaluate(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes, double* r_reproj,
+                  double* r_depth, double* cost) {
+  Ctx c;
+  int rc = begin(h, prob, workspace, workspace_bytes, c);
+  if (rc) return rc;
+  reset_profile(h, 0);
+  {
+    Timer t(h, KS_MISC);
+    launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[0], h->stream);
+  }
+  if (r_reproj || r_depth) {
+    Timer t(h, KS_EVALUATE);
+    launch_evaluate(c.pv, c.w.pose[0], prob->pt_xyz, r_reproj, r_depth, h->stream);
+  }
+  enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 0, 1);
+  rc = fetch_scalars(c);
+  if (rc) return rc;
+  if (cost) {
+    cost[0] = 0.5 * h->h_scal[S_COST_FREE];
+    cost[1] = 0.5 * h->h_scal[S_COST_FIXED];
+  }
+  return MPBA_OK;
+}
+
+int mpba_linearize(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes, double* Hcc,
+                   double* gc, double* Hpp, double* gp, double* cost) {
+  Ctx c;
+  int rc = begin(h, prob, workspace, workspace_bytes, c);
+  if (rc) return rc;
+  reset_profile(h, 0);
+  mpba_options opt;
+  mpba_default_options(&opt);
+  launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[0], h->stream);
+  enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 1, 1);
+  LmDiag lm{opt.initial_trust_region_radius, opt.min_lm_diagonal, opt.max_lm_diagonal};
+  rc = enqueue_points_and_system(c, c.w.pose[0], prob->pt_xyz, 0, lm, 1, &opt, false);
+  if (rc) return rc;
+  if (Hcc) launch_expand_hcc(c.pv.C, c.w.Hc[0], Hcc, h->stream);
+  if (gc) CU(cudaMemcpyAsync(gc, c.w.gc[0], (size_t)c.pv.C * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  if (Hpp) CU(cudaMemcpyAsync(Hpp, c.w.Hpp, (size_t)c.pv.P * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  if (gp) CU(cudaMemcpyAsync(gp, c.w.gp, (size_t)c.pv.P * 3 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  rc = fetch_scalars(c);
+  if (rc) return rc;
+  if (cost) {
+    cost[0] = 0.5 * h->h_scal[S_COST_FREE];
+    cost[1] = 0.5 * h->h_scal[S_COST_FIXED];
+  }
+  return MPBA_OK;
+}
+
+int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
+                        const mpba_options* opt_in, double radius, double* S, double* rhs, double* y,
+                        int32_t* pcg_iterations) {
+  Ctx c;
+  int rc = begin(h, prob, workspace, workspace_bytes, c);
+  if (rc) return rc;
+  reset_profile(h, 0);
+  mpba_options opt;
+  if (opt_in) opt = *opt_in; else mpba_default_options(&opt);
+  launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[0], h->stream);
+  enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 1, opt.jacobi_scaling);
+  LmDiag lm{radius, opt.min_lm_diagonal, opt.max_lm_diagonal};
+  rc = enqueue_points_and_system(c, c.w.pose[0], prob->pt_xyz, 0, lm, 1, &opt, true);
+  if (rc) return rc;
+  if (c.structure_only) return fail(h, MPBA_E_INVALID, "no reduced camera system: all poses are constant");
+  if (S) CU(cudaMemcpyAsync(S, c.w.S, (size_t)c.pv.B * 36 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  if (rhs) CU(cudaMemcpyAsync(rhs, c.w.rhs, (size_t)c.pv.C * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  if (y) CU(cudaMemcpyAsync(y, c.w.y, (size_t)c.pv.C * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  rc = fetch_scalars(c);
+  if (rc) return rc;
+  if (pcg_iterations) *pcg_iterations = (int32_t)h->h_scal[S_PCG_ITERS];
+  return MPBA_OK;
+}
+
+int mpba_solve(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
+               const mpba_options* opt_in, mpba_summary* sum) {
+  Ctx c;
+  int rc = begin(h, prob, workspace, workspace_bytes, c);
+  if (rc) return rc;
+  if (!sum) return fail(h, MPBA_E_INVALID, "summary is NULL");
+  mpba_options opt;
+  if (opt_in) opt = *opt_in; else mpba_default_options(&opt);
+  reset_profile(h, opt.profile);
+  mpba_iteration* its = sum->iterations;
+  const int cap = its ? sum->capacity : 0;
+  int nrows = 0;
+  mpba_iteration last;
+  memset(&last, 0, sizeof(last));
+  auto push = [&](const mpba_iteration& it) {
+    if (nrows < cap) its[nrows] = it;
+    ++nrows;
+    last = it;
+  };
+  auto set_last_gmax = [&](double g) {
+    last.gradient_max_norm = g;
+    if (nrows - 1 < cap && nrows > 0) its[nrows - 1].gradient_max_norm = g;
+  };
+
+  CU(cudaEventRecord(h->ev0, h->stream));
+  int cur = 0;
+  launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[cur], h->stream);
+  h->launch_count += 1;
+  if (c.pv.P > 0)
+    CU(cudaMemcpyAsync(c.w.X[cur], prob->pt_xyz, (size_t)c.pv.P * 4 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+
+  // ---- iteration zero
+  enqueue_image_pass(c, c.w.pose[cur], c.w.X[cur], cur, 1, opt.jacobi_scaling);
+  rc = fetch_scalars(c);
+  if (rc) return rc;
+  double x_cost = 0.5 * h->h_scal[S_COST_FREE];
+  const double initial_cost_free = x_cost;
+  const double fixed_cost = 0.5 * h->h_scal[S_COST_FIXED];
+  double gmax_c = h->h_scal[S_GMAX_C];
+  if (!isfinite(x_cost)) {
+    snprintf(sum->message, sizeof(sum->message), "Initial cost is not finite.");
+    sum->termination = MPBA_FAILURE;
+    sum->initial_cost = sum->final_cost = x_cost;
+    sum->fixed_cost = fixed_cost;
+    sum->num_iterations = 0;
+    return fail(h, MPBA_E_NUMERIC, "initial cost is not finite (point behind a camera or bad input)");
+  }
+  double radius = opt.initial_trust_region_radius, decrease_factor = 2.0;
+  double minimum_cost = x_cost;
+  int n_ok = 0, n_bad = 0, invalid_run = 0;
+  int64_t total_pcg = 0;
+  int termination = -1;
+  const char* msg = "";
+  bool need_gmax = true, first = true;
+  {
+    mpba_iteration it0;
+    memset(&it0, 0, sizeof(it0));
+    it0.cost = x_cost + fixed_cost;
+    it0.trust_region_radius = radius;
+    push(it0);
+  }
+  int iteration = 0;
+  if (iteration >= opt.max_num_iterations) {
+    termination = MPBA_NO_CONVERGENCE;
+    msg = "Maximum number of iterations reached.";
+  }
+
+  while (termination < 0) {
+    const int cand = cur ^ 1;
+    LmDiag lm{radius, opt.min_lm_diagonal, opt.max_lm_diagonal};
+    rc = enqueue_points_and_system(c, c.w.pose[cur], c.w.X[cur], cur, lm, first ? 1 : 0, &opt, true);
+    if (rc) return rc;
+    first = false;
+    {
+      Timer t(h, KS_CAM_UPDATE);
+      launch_cam_update(c.pv, c.w.pose[cur], c.w.y, c.w.pose[cand], c.w.scal, h->stream);
+    }
+    {
+      Timer t(h, KS_BACK_SUBSTITUTE);
+      launch_back_substitute(c.pv, c.w.pose[cur], c.w.X[cur], c.w.y, c.w.Hpp, c.w.gp, c.w.Hinv, c.w.X[cand],
+                             c.w.pt_part, h->stream);
+    }
+    {
+      Timer t(h, KS_REDUCE);
+      launch_pt_scalars_step(c.w.pt_part, c.nblk, c.w.scal, h->stream);
+    }
+    // cost (and, in case the step is accepted, Hcc / gc) at the candidate
+    enqueue_image_pass(c, c.w.pose[cand], c.w.X[cand], cand, 0, opt.jacobi_scaling);
+    rc = fetch_scalars(c);
+    if (rc) return rc;
+    const double* s = h->h_scal;
+
+    if (need_gmax) {
+      const double g = fmax(gmax_c, s[S_GMAX_P]);
+      set_last_gmax(g);
+      need_gmax = false;
+      if (g <= opt.gradient_tolerance) {
+        termination = MPBA_CONVERGENCE;
+        msg = "Gradient tolerance reached.";
+        break;
+      }
+    }
+
+    mpba_iteration it;
+    memset(&it, 0, sizeof(it));
+    it.cost = last.cost;
+    it.gradient_max_norm = last.gradient_max_norm;
+    it.pcg_iterations = (int32_t)s[S_PCG_ITERS];
+    total_pcg += it.pcg_iterations;
+    ++iteration;
+    const double mcc = s[S_MCC];
+    bool ok = s[S_PCG_FLAG] != 2.0 && s[S_BAD_POINTS] == 0.0 && isfinite(mcc) && isfinite(s[S_STEP2_P]) &&
+              isfinite(s[S_STEP2_C]) && mcc > 0.0;
+    it.step_is_valid = ok ? 1 : 0;
+    if (!ok) {
+      ++invalid_run;
+      radius /= decrease_factor;
+      decrease_factor *= 2.0;
+      it.trust_region_radius = radius;
+      ++n_bad;
+      push(it);
+      if (invalid_run >= opt.max_num_consecutive_invalid_steps) {
+        termination = MPBA_FAILURE;
+        msg = "Number of consecutive invalid steps more than max_num_consecutive_invalid_steps.";
+        break;
+      }
+    } else {
+      invalid_run = 0;
+      double cand_cost = 0.5 * s[S_COST_FREE];
+      if (!isfinite(cand_cost)) cand_cost = DBL_MAX;
+      it.step_norm = sqrt(s[S_STEP2_P] + s[S_STEP2_C]);
+      const double x_norm = sqrt(s[S_XNORM2_P] + s[S_XNORM2_C]);
+      if (it.step_norm <= opt.parameter_tolerance * (x_norm + opt.parameter_tolerance)) {
+        termination = MPBA_CONVERGENCE;
+        msg = "Parameter tolerance reached.";
+        push(it);
+        break;
+      }
+      it.cost_change = x_cost - cand_cost;
+      if (fabs(it.cost_change) <= opt.function_tolerance * x_cost) {
+        termination = MPBA_CONVERGENCE;
+        msg = "Function tolerance reached.";
+        push(it);
+        break;
+      }
+      it.relative_decrease = it.cost_change / mcc;
+      if (it.relative_decrease > opt.min_relative_decrease) {
+        cur = cand;
+        x_cost = cand_cost;
+        gmax_c = s[S_GMAX_C];
+        need_gmax = true;
+        it.cost = x_cost + fixed_cost;
+        it.step_is_successful = 1;
+        const double t = 2.0 * it.relative_decrease - 1.0;
+        radius = fmin(opt.max_trust_region_radius, radius / fmax(1.0 / 3.0, 1.0 - t * t * t));
+        decrease_factor = 2.0;
+        ++n_ok;
+        if (x_cost < minimum_cost) minimum_cost = x_cost;
+      } else {
+        radius /= decrease_factor;
+        decrease_factor *= 2.0;
+        ++n_bad;
+      }
+      it.trust_region_radius = radius;
+      push(it);
+    }
+    if (opt.verbose)
+      fprintf(stderr, "[mpba] %3d cost %.9e dcost %.3e |step| %.3e rho %.3e radius %.3e pcg %d (%s)\n", iteration,
+              last.cost, last.cost_change, last.step_norm, last.relative_decrease, last.trust_region_radius,
+              last.pcg_iterations, last.step_is_successful ? "ok" : (last.step_is_valid ? "rejected" : "invalid"));
+    if (iteration >= opt.max_num_iterations) {
+      termination = MPBA_NO_CONVERGENCE;
+      msg = "Maximum number of iterations reached.";
+    } else if (radius <= opt.min_trust_region_radius) {
+      termination = MPBA_CONVERGENCE;
+      msg = "Minimum trust region radius reached.";
+    }
+  }
+
+  // monotonic steps: the current state is the best state visited
+  CU(cudaMemcpyAsync(prob->img_pose, c.w.pose[cur], (size_t)c.pv.C * 8 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  if (c.pv.P > 0)
+    CU(cudaMemcpyAsync(prob->pt_xyz, c.w.X[cur], (size_t)c.pv.P * 4 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  CU(cudaEventRecord(h->ev1, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  if (h->profile) flush_timers(h);
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+
+  sum->initial_cost = initial_cost_free + fixed_cost;
+  sum->final_cost = minimum_cost + fixed_cost;
+  sum->fixed_cost = fixed_cost;
+  sum->termination = termination;
+  sum->num_iterations = iteration;
+  sum->num_successful_steps = n_ok;
+  sum->num_unsuccessful_steps = n_bad;
+  sum->total_pcg_iterations = total_pcg;
+  sum->kernel_launches = h->launch_count;
+  sum->solve_ms = ms;
+  snprintf(sum->message, sizeof(sum->message), "%s", msg);
+  return MPBA_OK;
+}
+
+}  // extern "C"

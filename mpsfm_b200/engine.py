@@ -1,0 +1,528 @@
+"""ctypes binding of ``libmpba.so`` (C ABI in ``include/mpba.h``) and the host-side problem layout.
+
+PyTorch is used for one thing only: owning the device buffers whose raw pointers go into
+``mpba_problem``.  All arithmetic of a solve runs inside the library's sm_100a kernels.  There is
+no CPU path: every compute entry point raises :class:`EngineUnavailable` when the shared library
+or a CUDA device is missing.
+
+Layout built here:
+
+* *track order* -- observations grouped by point3D (``pt_ptr``), sorted by image inside a track: feeds
+  the point-keyed reductions, the Schur complement and back-substitution,
+* *image order* -- observations grouped by image (``img_ptr``) in chunks of <= 1024: feeds the
+  image-keyed reductions,
+* the block-CSR structure of the reduced camera system over co-visible image pairs and, for every
+  track, the block index of each of its image pairs.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import dataclasses
+import os
+from typing import Optional
+
+import numpy as np
+
+from .problem import MAX_CAMERA_PARAMS, BundleProblem
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libmpba.so")
+MPBA_CHUNK = 1024
+MPBA_NUM_KERNELS = 12
+FLAG_STRUCTURE_ONLY = 1
+
+TERMINATION = {0: "CONVERGENCE", 1: "NO_CONVERGENCE", 2: "FAILURE"}
+
+
+class EngineUnavailable(RuntimeError):
+    """libmpba.so or a CUDA device is missing -- there is deliberately no fallback."""
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int32)
+_bp = C.POINTER(C.c_uint8)
+
+
+class MpbaProblem(C.Structure):
+    _fields_ = [
+        ("num_images", C.c_int32), ("num_cameras", C.c_int32), ("num_points", C.c_int32), ("num_obs", C.c_int32),
+        ("img_pose", C.c_void_p), ("img_camera", C.c_void_p), ("img_free_mask", C.c_void_p),
+        ("img_shift_scale", C.c_void_p), ("cam_model", C.c_void_p), ("cam_params", C.c_void_p),
+        ("pt_xyz", C.c_void_p), ("pt_const", C.c_void_p),
+        ("pt_ptr", C.c_void_p), ("pm_img", C.c_void_p), ("pm_xy", C.c_void_p), ("pm_depth", C.c_void_p),
+        ("pm_src", C.c_void_p),
+        ("img_ptr", C.c_void_p), ("cm_pt", C.c_void_p), ("cm_xy", C.c_void_p), ("cm_depth", C.c_void_p),
+        ("num_chunks", C.c_int32),
+        ("chunk_img", C.c_void_p), ("chunk_begin", C.c_void_p), ("chunk_end", C.c_void_p),
+        ("img_chunk_ptr", C.c_void_p),
+        ("num_blocks", C.c_int32),
+        ("s_row_ptr", C.c_void_p), ("s_col", C.c_void_p), ("s_diag", C.c_void_p), ("s_transpose", C.c_void_p),
+        ("pair_ptr", C.c_void_p), ("pair_block", C.c_void_p),
+        ("reproj_loss", C.c_int32), ("depth_loss", C.c_int32),
+        ("reproj_loss_scale", C.c_double), ("reproj_loss_weight", C.c_double),
+        ("flags", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class MpbaOptions(C.Structure):
+    _fields_ = [
+        ("max_num_iterations", C.c_int32), ("max_num_consecutive_invalid_steps", C.c_int32),
+        ("jacobi_scaling", C.c_int32), ("pcg_max_iterations", C.c_int32),
+        ("initial_trust_region_radius", C.c_double), ("max_trust_region_radius", C.c_double),
+        ("min_trust_region_radius", C.c_double), ("min_relative_decrease", C.c_double),
+        ("min_lm_diagonal", C.c_double), ("max_lm_diagonal", C.c_double),
+        ("function_tolerance", C.c_double), ("gradient_tolerance", C.c_double),
+        ("parameter_tolerance", C.c_double), ("pcg_tolerance", C.c_double),
+        ("profile", C.c_int32), ("verbose", C.c_int32),
+    ]
+
+
+class MpbaIteration(C.Structure):
+    _fields_ = [
+        ("cost", C.c_double), ("cost_change", C.c_double), ("gradient_max_norm", C.c_double),
+        ("step_norm", C.c_double), ("relative_decrease", C.c_double), ("trust_region_radius", C.c_double),
+        ("step_is_valid", C.c_int32), ("step_is_successful", C.c_int32),
+        ("pcg_iterations", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class MpbaSummary(C.Structure):
+    _fields_ = [
+        ("initial_cost", C.c_double), ("final_cost", C.c_double), ("fixed_cost", C.c_double),
+        ("termination", C.c_int32), ("num_iterations", C.c_int32),
+        ("num_successful_steps", C.c_int32), ("num_unsuccessful_steps", C.c_int32),
+        ("total_pcg_iterations", C.c_int64), ("kernel_launches", C.c_int64),
+        ("solve_ms", C.c_double),
+        ("iterations", C.POINTER(MpbaIteration)), ("capacity", C.c_int32), ("reserved", C.c_int32),
+        ("message", C.c_char * 128),
+    ]
+
+
+EXPORTS = (
+    "mpba_version", "mpba_create", "mpba_destroy", "mpba_last_error", "mpba_default_options",
+    "mpba_workspace_bytes", "mpba_evaluate", "mpba_linearize", "mpba_reduced_system", "mpba_solve",
+    "mpba_kernel_times", "mpba_kernel_name",
+)
+
+_lib = None
+
+
+def load_library(path: Optional[str] = None):
+    """dlopen libmpba.so and declare the prototypes of include/mpba.h.  Needs no GPU."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or _LIB_PATH
+    if not os.path.exists(p):
+        raise EngineUnavailable(f"{p} not found -- build it with `python -c 'import __graft_entry__ as g; g.build()'`")
+    lib = C.CDLL(p)
+    lib.mpba_version.restype = C.c_int
+    lib.mpba_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_void_p]
+    lib.mpba_destroy.argtypes = [C.c_void_p]
+    lib.mpba_destroy.restype = None
+    lib.mpba_last_error.argtypes = [C.c_void_p]
+    lib.mpba_last_error.restype = C.c_char_p
+    lib.mpba_default_options.argtypes = [C.POINTER(MpbaOptions)]
+    lib.mpba_default_options.restype = None
+    lib.mpba_workspace_bytes.argtypes = [C.POINTER(MpbaProblem), C.POINTER(C.c_size_t)]
+    lib.mpba_evaluate.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, _dp]
+    lib.mpba_linearize.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t,
+                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, _dp]
+    lib.mpba_reduced_system.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t,
+                                        C.POINTER(MpbaOptions), C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, _ip]
+    lib.mpba_solve.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t,
+                               C.POINTER(MpbaOptions), C.POINTER(MpbaSummary)]
+    lib.mpba_kernel_times.argtypes = [C.c_void_p, _dp, C.POINTER(C.c_int64)]
+    lib.mpba_kernel_name.argtypes = [C.c_int]
+    lib.mpba_kernel_name.restype = C.c_char_p
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def default_options(**overrides) -> MpbaOptions:
+    opt = MpbaOptions()
+    load_library().mpba_default_options(C.byref(opt))
+    for k, v in overrides.items():
+        if not hasattr(opt, k):
+            raise AttributeError(f"mpba_options has no field {k!r}")
+        setattr(opt, k, v)
+    return opt
+
+
+# ----------------------------------------------------------------------------------------------
+# host-side layout (numpy only; runs anywhere)
+# ----------------------------------------------------------------------------------------------
+@dataclasses.dataclass
+class HostLayout:
+    C: int
+    K: int
+    P: int
+    N: int
+    img_pose: np.ndarray  # [C,8]
+    img_camera: np.ndarray
+    img_free_mask: np.ndarray
+    img_shift_scale: np.ndarray  # [C,2]
+    cam_model: np.ndarray
+    cam_params: np.ndarray  # [K,12]
+    pt_xyz: np.ndarray  # [P,4]
+    pt_const: np.ndarray
+    pt_ptr: np.ndarray
+    pm_img: np.ndarray
+    pm_xy: np.ndarray
+    pm_depth: np.ndarray  # [3,N]
+    pm_src: np.ndarray
+    img_ptr: np.ndarray
+    cm_pt: np.ndarray
+    cm_xy: np.ndarray
+    cm_depth: np.ndarray
+    cm_src: np.ndarray
+    chunk_img: np.ndarray
+    chunk_begin: np.ndarray
+    chunk_end: np.ndarray
+    img_chunk_ptr: np.ndarray
+    s_row_ptr: np.ndarray
+    s_col: np.ndarray
+    s_diag: np.ndarray
+    s_transpose: np.ndarray
+    pair_ptr: np.ndarray
+    pair_block: np.ndarray
+    reproj_loss: int
+    depth_loss: int
+    reproj_loss_scale: float
+    reproj_loss_weight: float
+    flags: int
+
+    @property
+    def num_blocks(self) -> int:
+        return int(self.s_col.shape[0])
+
+    @property
+    def num_chunks(self) -> int:
+        return int(self.chunk_img.shape[0])
+
+
+def _ptr_from_counts(counts: np.ndarray) -> np.ndarray:
+    out = np.zeros(counts.shape[0] + 1, dtype=np.int64)
+    np.cumsum(counts, out=out[1:])
+    if out[-1] >= 2**31:
+        raise ValueError("more than 2^31-1 entries: shard the problem across GPUs")
+    return out.astype(np.int32)
+
+
+def build_layout(problem: BundleProblem) -> HostLayout:
+    """Sort the observations into the two orders and build the reduced-system structure.
+
+    The natural observation index of every slot is kept (``pm_src`` / ``cm_src``): per-residual
+    outputs are mapped back through it, which is the "correspondence / track indexing bit-exact"
+    gate of BASELINE.json."""
+    pr = problem.normalized()
+    pr.validate()
+    Cn, P, N = pr.num_images, pr.num_points, pr.num_obs
+    K = int(pr.cam_model.shape[0])
+    oi = pr.obs_img.astype(np.int64)
+    op = pr.obs_pt.astype(np.int64)
+
+    d = np.ones(N)
+    w = np.zeros(N)
+    a = np.ones(N)
+    d[pr.depth_obs] = pr.depth_d
+    w[pr.depth_obs] = pr.depth_w
+    a[pr.depth_obs] = pr.depth_a
+    if pr.num_depth and not np.all(pr.depth_w > 0):
+        raise ValueError("depth prior weights must be > 0 (w == 0 marks 'no prior' in the device layout)")
+
+    # ---- track order: by point, then image
+    pm_src = np.argsort(op * Cn + oi, kind="stable").astype(np.int32)
+    pt_cnt = np.bincount(op, minlength=P)
+    pt_ptr = _ptr_from_counts(pt_cnt)
+    pm_img = pr.obs_img[pm_src]
+    pm_xy = np.ascontiguousarray(pr.obs_xy[pm_src])
+    pm_depth = np.ascontiguousarray(np.stack([d[pm_src], w[pm_src], a[pm_src]], axis=0))
+
+    # ---- image order: by image, then point (ascending gather addresses)
+    cm_src = np.argsort(oi * max(P, 1) + op, kind="stable").astype(np.int32)
+    img_cnt = np.bincount(oi, minlength=Cn)
+    img_ptr = _ptr_from_counts(img_cnt)
+    cm_pt = pr.obs_pt[cm_src]
+    cm_xy = np.ascontiguousarray(pr.obs_xy[cm_src])
+    cm_depth = np.ascontiguousarray(np.stack([d[cm_src], w[cm_src], a[cm_src]], axis=0))
+
+    nch = (img_cnt + MPBA_CHUNK - 1) // MPBA_CHUNK
+    img_chunk_ptr = _ptr_from_counts(nch)
+    chunk_img = np.repeat(np.arange(Cn, dtype=np.int32), nch)
+    local = np.arange(chunk_img.shape[0], dtype=np.int64) - img_chunk_ptr[chunk_img]
+    chunk_begin = (img_ptr[chunk_img] + local * MPBA_CHUNK).astype(np.int32)
+    chunk_end = np.minimum(chunk_begin.astype(np.int64) + MPBA_CHUNK, img_ptr[chunk_img + 1]).astype(np.int32)
+
+    # ---- reduced camera system structure and per-track pair -> block map
+    structure_only = bool(np.all(pr.img_free_mask == 0))
+    active = (pr.pt_const == 0)
+    L = np.where(active, pt_cnt, 0).astype(np.int64)
+    npairs = L * (L + 1) // 2
+    pair_ptr = _ptr_from_counts(npairs)
+    pair_key = np.empty(int(pair_ptr[-1]), dtype=np.int64)
+    if not structure_only:
+        for ell in np.unique(L):
+            ell = int(ell)
+            if ell == 0:
+                continue
+            pts = np.flatnonzero(L == ell)
+            slots = pt_ptr[pts].astype(np.int64)[:, None] + np.arange(ell)[None, :]
+            imgs = pm_img[slots].astype(np.int64)  # [n, ell], ascending in every row
+            ia, ib = np.triu_indices(ell)  # row-major over a, then b >= a
+            keys = imgs[:, ia] * Cn + imgs[:, ib]
+            dst = pair_ptr[pts].astype(np.int64)[:, None] + np.arange(ia.shape[0])[None, :]
+            pair_key[dst.reshape(-1)] = keys.reshape(-1)
+    diag_keys = np.arange(Cn, dtype=np.int64) * (Cn + 1)
+    if structure_only:
+        all_keys = diag_keys
+        pair_block = np.zeros(pair_key.shape[0], dtype=np.int32)
+    else:
+        upper = np.unique(pair_key)
+        ui, uj = upper // Cn, upper % Cn
+        lower = (uj * Cn + ui)[ui != uj]
+        all_keys = np.unique(np.concatenate([upper, lower, diag_keys]))
+        pair_block = np.searchsorted(all_keys, pair_key).astype(np.int32)
+    rows, cols = all_keys // Cn, all_keys % Cn
+    s_row_ptr = _ptr_from_counts(np.bincount(rows, minlength=Cn))
+    s_col = cols.astype(np.int32)
+    s_diag = np.searchsorted(all_keys, diag_keys).astype(np.int32)
+    s_transpose = np.searchsorted(all_keys, cols * Cn + rows).astype(np.int32)
+
+    pose = np.zeros((Cn, 8))
+    pose[:, :4] = pr.img_q
+    pose[:, 4:7] = pr.img_t
+    xyz = np.zeros((P, 4))
+    xyz[:, :3] = pr.pt_xyz
+    params = np.zeros((K, MAX_CAMERA_PARAMS))
+    params[:, : pr.cam_params.shape[1]] = pr.cam_params
+
+    return HostLayout(
+        C=Cn, K=K, P=P, N=N,
+        img_pose=pose, img_camera=pr.img_camera, img_free_mask=pr.img_free_mask,
+        img_shift_scale=np.ascontiguousarray(pr.shift_scale), cam_model=pr.cam_model, cam_params=params,
+        pt_xyz=xyz, pt_const=pr.pt_const,
+        pt_ptr=pt_ptr, pm_img=np.ascontiguousarray(pm_img), pm_xy=pm_xy, pm_depth=pm_depth, pm_src=pm_src,
+        img_ptr=img_ptr, cm_pt=np.ascontiguousarray(cm_pt), cm_xy=cm_xy, cm_depth=cm_depth, cm_src=cm_src,
+        chunk_img=chunk_img, chunk_begin=chunk_begin, chunk_end=chunk_end, img_chunk_ptr=img_chunk_ptr,
+        s_row_ptr=s_row_ptr, s_col=s_col, s_diag=s_diag, s_transpose=s_transpose,
+        pair_ptr=pair_ptr, pair_block=pair_block,
+        reproj_loss=int(pr.reproj_loss), depth_loss=int(pr.depth_loss),
+        reproj_loss_scale=float(pr.reproj_loss_scale), reproj_loss_weight=float(pr.reproj_loss_weight),
+        flags=FLAG_STRUCTURE_ONLY if structure_only else 0,
+    )
+
+
+# ----------------------------------------------------------------------------------------------
+# device side
+# ----------------------------------------------------------------------------------------------
+_DEVICE_FIELDS = (
+    "img_pose", "img_camera", "img_free_mask", "img_shift_scale", "cam_model", "cam_params", "pt_xyz", "pt_const",
+    "pt_ptr", "pm_img", "pm_xy", "pm_depth", "pm_src", "img_ptr", "cm_pt", "cm_xy", "cm_depth",
+    "chunk_img", "chunk_begin", "chunk_end", "img_chunk_ptr", "s_row_ptr", "s_col", "s_diag", "s_transpose",
+    "pair_ptr", "pair_block",
+)
+
+
+@dataclasses.dataclass
+class SolveSummary:
+    initial_cost: float
+    final_cost: float
+    fixed_cost: float
+    termination: str
+    message: str
+    num_iterations: int
+    num_successful_steps: int
+    num_unsuccessful_steps: int
+    total_pcg_iterations: int
+    kernel_launches: int
+    solve_ms: float
+    iterations: list  # of dicts
+
+    def brief_report(self) -> str:
+        return (f"mpba: iterations {self.num_iterations}, initial cost {self.initial_cost:.6e}, final cost "
+                f"{self.final_cost:.6e}, termination {self.termination} ({self.message})")
+
+
+class BundleAdjuster:
+    """One problem resident on one GPU: buffers (torch), handle and workspace."""
+
+    def __init__(self, problem, device: int = 0, layout: Optional[HostLayout] = None, pinned: bool = False):
+        import torch
+
+        self.lib = load_library()
+        if not torch.cuda.is_available():
+            raise EngineUnavailable("no CUDA device: mpsfm_b200 has no CPU fallback")
+        self.torch = torch
+        self.device = torch.device("cuda", device)
+        self.layout = layout if layout is not None else build_layout(problem)
+        lay = self.layout
+        self.buf = {}
+        self.h2d_bytes = 0
+        with torch.cuda.device(self.device):
+            for name in _DEVICE_FIELDS:
+                arr = np.ascontiguousarray(getattr(lay, name))
+                t = torch.from_numpy(arr)
+                if pinned:
+                    t = t.pin_memory()
+                self.buf[name] = t.to(self.device, non_blocking=pinned)
+                self.h2d_bytes += arr.nbytes
+            if lay.pair_block.shape[0] == 0:
+                self.buf["pair_block"] = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self.handle = C.c_void_p()
+            rc = self.lib.mpba_create(C.byref(self.handle), device, None)
+            if rc != 0:
+                raise EngineUnavailable(f"mpba_create failed with code {rc} (no usable CUDA device {device})")
+            self.prob = MpbaProblem()
+            self.prob.num_images, self.prob.num_cameras = lay.C, lay.K
+            self.prob.num_points, self.prob.num_obs = lay.P, lay.N
+            for name in _DEVICE_FIELDS:
+                setattr(self.prob, name, self.buf[name].data_ptr())
+            self.prob.num_chunks = lay.num_chunks
+            self.prob.num_blocks = lay.num_blocks
+            self.prob.reproj_loss, self.prob.depth_loss = lay.reproj_loss, lay.depth_loss
+            self.prob.reproj_loss_scale, self.prob.reproj_loss_weight = lay.reproj_loss_scale, lay.reproj_loss_weight
+            self.prob.flags = lay.flags
+            nbytes = C.c_size_t()
+            self._check(self.lib.mpba_workspace_bytes(C.byref(self.prob), C.byref(nbytes)))
+            self.workspace = torch.empty(max(int(nbytes.value), 256), dtype=torch.uint8, device=self.device)
+            self.workspace_bytes = int(nbytes.value)
+        self._pose0 = self.buf["img_pose"].clone()
+        self._xyz0 = self.buf["pt_xyz"].clone()
+
+    # -- plumbing
+    def _check(self, rc: int):
+        if rc != 0:
+            msg = self.lib.mpba_last_error(self.handle)
+            raise EngineError(f"libmpba error {rc}: {msg.decode() if msg else ''}")
+
+    def close(self):
+        if getattr(self, "handle", None) is not None and self.handle.value:
+            self.lib.mpba_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset_state(self):
+        """Restore the poses / points the problem was created with (device-to-device)."""
+        self.buf["img_pose"].copy_(self._pose0)
+        self.buf["pt_xyz"].copy_(self._xyz0)
+
+    def set_state(self, img_q, img_t, pt_xyz):
+        torch = self.torch
+        pose = np.zeros((self.layout.C, 8))
+        pose[:, :4], pose[:, 4:7] = img_q, img_t
+        xyz = np.zeros((self.layout.P, 4))
+        xyz[:, :3] = pt_xyz
+        self.buf["img_pose"].copy_(torch.from_numpy(pose))
+        self.buf["pt_xyz"].copy_(torch.from_numpy(xyz))
+
+    def state(self):
+        """(img_q [C,4], img_t [C,3], pt_xyz [P,3]) as numpy (device -> host)."""
+        pose = self.buf["img_pose"].cpu().numpy()
+        xyz = self.buf["pt_xyz"].cpu().numpy()
+        return pose[:, :4].copy(), pose[:, 4:7].copy(), xyz[:, :3].copy()
+
+    def _ws(self):
+        return C.c_void_p(self.workspace.data_ptr()), C.c_size_t(self.workspace.numel())
+
+    # -- entry points of include/mpba.h
+    def evaluate(self):
+        """Raw residuals in NATURAL observation order: (reproj [N,2], depth [N] (nan where no prior),
+        cost, fixed_cost)."""
+        torch, lay = self.torch, self.layout
+        rr = torch.empty((lay.N, 2), dtype=torch.float64, device=self.device)
+        rd = torch.empty((lay.N,), dtype=torch.float64, device=self.device)
+        cost = (C.c_double * 2)()
+        ws, wsn = self._ws()
+        self._check(self.lib.mpba_evaluate(self.handle, C.byref(self.prob), ws, wsn, rr.data_ptr(), rd.data_ptr(), cost))
+        src = lay.pm_src.astype(np.int64)
+        r_reproj = np.empty((lay.N, 2))
+        r_depth = np.empty(lay.N)
+        r_reproj[src] = rr.cpu().numpy()
+        r_depth[src] = rd.cpu().numpy()
+        has = np.empty(lay.N, dtype=bool)
+        has[src] = lay.pm_depth[1] > 0
+        r_depth[~has] = np.nan
+        return r_reproj, r_depth, float(cost[0]), float(cost[1])
+
+    def linearize(self):
+        """(Hcc [C,6,6], gc [C,6], Hpp [P,3,3], gp [P,3], cost, fixed_cost) at the current state."""
+        torch, lay = self.torch, self.layout
+        Hcc = torch.empty((lay.C, 36), dtype=torch.float64, device=self.device)
+        gc = torch.empty((lay.C, 6), dtype=torch.float64, device=self.device)
+        Hpp = torch.empty((max(lay.P, 1), 6), dtype=torch.float64, device=self.device)
+        gp = torch.empty((max(lay.P, 1), 3), dtype=torch.float64, device=self.device)
+        cost = (C.c_double * 2)()
+        ws, wsn = self._ws()
+        self._check(self.lib.mpba_linearize(self.handle, C.byref(self.prob), ws, wsn, Hcc.data_ptr(), gc.data_ptr(),
+                                            Hpp.data_ptr(), gp.data_ptr(), cost))
+        h6 = Hpp.cpu().numpy()[: lay.P]
+        H3 = np.empty((lay.P, 3, 3))
+        H3[:, 0, 0], H3[:, 0, 1], H3[:, 0, 2] = h6[:, 0], h6[:, 1], h6[:, 2]
+        H3[:, 1, 0], H3[:, 1, 1], H3[:, 1, 2] = h6[:, 1], h6[:, 3], h6[:, 4]
+        H3[:, 2, 0], H3[:, 2, 1], H3[:, 2, 2] = h6[:, 2], h6[:, 4], h6[:, 5]
+        return (Hcc.cpu().numpy().reshape(lay.C, 6, 6), gc.cpu().numpy(), H3, gp.cpu().numpy()[: lay.P],
+                float(cost[0]), float(cost[1]))
+
+    def reduced_system(self, radius: float = 1e4, options: Optional[MpbaOptions] = None):
+        """(S blocks [B,6,6], rhs [C,6], y [C,6], pcg_iterations) of the damped normal equations."""
+        torch, lay = self.torch, self.layout
+        S = torch.empty((lay.num_blocks, 36), dtype=torch.float64, device=self.device)
+        rhs = torch.empty((lay.C, 6), dtype=torch.float64, device=self.device)
+        y = torch.empty((lay.C, 6), dtype=torch.float64, device=self.device)
+        it = C.c_int32()
+        opt = options or default_options()
+        ws, wsn = self._ws()
+        self._check(self.lib.mpba_reduced_system(self.handle, C.byref(self.prob), ws, wsn, C.byref(opt), radius,
+                                                 S.data_ptr(), rhs.data_ptr(), y.data_ptr(), C.byref(it)))
+        return S.cpu().numpy().reshape(-1, 6, 6), rhs.cpu().numpy(), y.cpu().numpy(), int(it.value)
+
+    def solve(self, options: Optional[MpbaOptions] = None) -> SolveSummary:
+        """Run the LM loop; poses / points on the device are updated in place."""
+        opt = options or default_options()
+        cap = int(opt.max_num_iterations) + 2
+        rows = (MpbaIteration * cap)()
+        sm = MpbaSummary()
+        sm.iterations = C.cast(rows, C.POINTER(MpbaIteration))
+        sm.capacity = cap
+        ws, wsn = self._ws()
+        self._check(self.lib.mpba_solve(self.handle, C.byref(self.prob), ws, wsn, C.byref(opt), C.byref(sm)))
+        n = min(sm.num_iterations + 1, cap)
+        its = []
+        for k in range(n):
+            r = rows[k]
+            its.append({f: getattr(r, f) for f, _ in MpbaIteration._fields_ if f != "reserved"})
+        return SolveSummary(
+            initial_cost=sm.initial_cost, final_cost=sm.final_cost, fixed_cost=sm.fixed_cost,
+            termination=TERMINATION.get(sm.termination, str(sm.termination)), message=sm.message.decode(),
+            num_iterations=sm.num_iterations, num_successful_steps=sm.num_successful_steps,
+            num_unsuccessful_steps=sm.num_unsuccessful_steps, total_pcg_iterations=int(sm.total_pcg_iterations),
+            kernel_launches=int(sm.kernel_launches), solve_ms=sm.solve_ms, iterations=its,
+        )
+
+    def kernel_times(self):
+        """{kernel: (summed ms, launches)} of the last call made with options.profile = 1."""
+        ms = (C.c_double * MPBA_NUM_KERNELS)()
+        n = (C.c_int64 * MPBA_NUM_KERNELS)()
+        self._check(self.lib.mpba_kernel_times(self.handle, ms, n))
+        return {self.lib.mpba_kernel_name(i).decode(): (ms[i], int(n[i])) for i in range(MPBA_NUM_KERNELS) if n[i]}
+
+
+def dense_reduced_system(layout: HostLayout, S_blocks: np.ndarray) -> np.ndarray:
+    """Assemble the block-CSR S into a dense [6C,6C] matrix (tests, tiny problems only)."""
+    Cn = layout.C
+    S = np.zeros((6 * Cn, 6 * Cn))
+    rows = np.repeat(np.arange(Cn), np.diff(layout.s_row_ptr))
+    for b, (i, j) in enumerate(zip(rows, layout.s_col)):
+        S[6 * i : 6 * i + 6, 6 * j : 6 * j + 6] = S_blocks[b]
+    return S
