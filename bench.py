@@ -1,0 +1,328 @@
+#!/usr/bin/env python
+"""bench.py -- LM iterations/s and ms per bundle-adjustment solve (BASELINE.json's metric).
+
+A *step* is one full BA solve (`mpba_solve`, Ceres termination rules) of the named synthetic scene from
+its perturbed start state.  `value` = LM iterations per second with the problem resident in HBM;
+`e2e` = the same through host buffers (pinned H2D of the whole problem + solve + D2H of poses/points).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg3] [--impl reference]
+
+Workloads (mpsfm_b200/synthetic.py CONFIGS): cfg2 (300k obs), cfg3 (5M obs, default: the largest
+single-GPU configuration BASELINE.json names), target10m (10M obs), cfg4, cfg5 (sharded).
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "LM iterations/sec"
+UNIT = "LM it/s"
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def __exit__(self, *a):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def algorithmic_bytes(lay):
+    """Algorithmic HBM bytes per launch of each pass (fixed before measuring)."""
+    N, P, C, B = lay.N, lay.P, lay.C, lay.num_blocks
+    npairs = int(lay.pair_block.shape[0])
+    return {
+        # 4 (point idx) + 16 (xy) + 24 (d,w,a) per observation, every point read at least once (32 B), chunk partials
+        "img_chunks": 44 * N + 32 * P + 256 * lay.num_chunks + 64 * C,
+        # 4 (image idx) + 16 + 24 per observation, pair->block map, point record in, Hpp/gp/Hinv/c_pt out, S once
+        "points_schur": 44 * N + 4 * npairs + (32 + 8 + 24 + 48 + 24 + 48) * P + 288 * B + 48 * C,
+        "back_substitute": 44 * N + (32 + 4 + 48 + 24 + 48 + 32) * P + 48 * C,
+    }
+
+
+def cpu_baseline_sample(workload: str, max_iters: int = 2, obs_target: int = 60_000):
+    """Oracle (numpy port of the reference's Ceres path) on a bounded sample of the workload's shape."""
+    from mpsfm_b200.problem import CameraModel, LossType
+    from mpsfm_b200.synthetic import CONFIGS
+    from oracle import lm
+
+    from mpsfm_b200 import synthetic
+
+    C, P, L = CONFIGS[workload]
+    scale = max(1.0, (P * L) / obs_target)
+    Cs, Ps = max(12, int(round(C / scale))), max(100, int(round(P / scale)))
+    kw = {}
+    if workload in ("cfg3", "cfg4", "cfg5", "target10m"):
+        kw["model"] = CameraModel.SIMPLE_RADIAL
+    if workload == "cfg3":
+        kw["reproj_loss"] = LossType.CAUCHY
+    prob = synthetic.make_scene(Cs, Ps, L, seed=0, **kw)
+    t0 = time.perf_counter()
+    summ = lm.solve(prob, lm.Options(max_num_iterations=max_iters))
+    dt = time.perf_counter() - t0
+    its = len(summ.iterations) - 1
+    n_full = P * L
+    it_s_sample = its / dt
+    return {
+        "value": it_s_sample * prob.num_obs / n_full,
+        "unit": UNIT,
+        "cores": int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1)),
+        "kind": "port",
+        "sample": (f"numpy oracle (oracle/lm.py, exact Schur + Cholesky), {its} LM iterations on a {Cs} img / {Ps} pt / "
+                   f"{prob.num_obs} obs scene of the same generator ({dt:.1f} s); it/s scaled by obs ratio "
+                   f"{prob.num_obs}/{n_full} (cost per LM iteration is linear in observations at fixed track length)"),
+        "sample_it_per_s": it_s_sample,
+        "sample_obs": int(prob.num_obs),
+    }
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    times, iters, info = [], 0, None
+    for k in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        info = cpu_baseline_sample(args.workload, max_iters=1, obs_target=args.ref_obs)
+        dt = time.perf_counter() - t0
+        if k >= args.warmup:
+            times.append(dt)
+    val = float(np.mean([info["value"]])) if info else 0.0
+    # value from the mean step time of the timed steps (one LM iteration per step on the sample)
+    mean_dt = float(np.mean(times)) if times else float("nan")
+    from mpsfm_b200.synthetic import CONFIGS
+
+    C, P, L = CONFIGS[args.workload]
+    val = (1.0 / mean_dt) * info["sample_obs"] / (P * L)
+    info["value"] = val
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": mean_dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "images": C, "points": P, "observations": P * L,
+                   "note": "pycolmap/pyceres/Ceres are not installable here; the reference arm is the numpy oracle "
+                           "(same algorithm, exact Schur solve) on a bounded sample, scaled by observation count"},
+        "cpu_baseline": info,
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def run_gpu(args):
+    import torch
+
+    from mpsfm_b200 import engine
+    from mpsfm_b200.synthetic import CONFIGS, make_config
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        dist = None
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: mpsfm_b200 has no CPU fallback")
+
+    t0 = time.perf_counter()
+    prob = make_config(args.workload, seed=rank)  # weak scaling: every rank owns one scene of the named shape
+    t_scene = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    lay = engine.build_layout(prob)
+    t_layout = time.perf_counter() - t0
+    ba = engine.BundleAdjuster(prob, device=local, layout=lay)
+    opt = engine.default_options(profile=1, pcg_tolerance=args.pcg_tol, pcg_max_iterations=args.pcg_max_iter)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- resident: inputs already in HBM
+    for _ in range(args.warmup):
+        ba.reset_state()
+        ba.solve(opt)
+    barrier()
+    ktimes, iters, launches, pcg_iters, solve_ms = {}, 0, 0, 0, 0.0
+    with ClockSampler(local) as clk:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        ev0.record()
+        for _ in range(args.steps):
+            ba.reset_state()
+            s = ba.solve(opt)
+            iters += s.num_iterations
+            launches += s.kernel_launches
+            pcg_iters += s.total_pcg_iterations
+            solve_ms += s.solve_ms
+            for k, (ms, n) in ba.kernel_times().items():
+                a = ktimes.setdefault(k, [0.0, 0])
+                a[0] += ms
+                a[1] += n
+        ev1.record()
+        barrier()
+        ms_total = ev0.elapsed_time(ev1)
+    clocks = clk.summary()
+    last = s
+
+    # ---- end to end: host buffers -> device -> solve -> host
+    h2d = d2h = 0
+    e2e_iters = 0
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ba2 = engine.BundleAdjuster(prob, device=local, layout=lay, pinned=True)
+        s2 = ba2.solve(opt)
+        q, t, X = ba2.state()
+        e2e_iters += s2.num_iterations
+        h2d = ba2.h2d_bytes
+        d2h = lay.C * 64 + lay.P * 32
+        ba2.close()
+        del ba2
+    barrier()
+    e2e_s = time.perf_counter() - t0
+
+    if dist is not None:
+        red = torch.tensor([ms_total, e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(red, op=dist.ReduceOp.MAX)
+        ms_total, e2e_s = float(red[0]), float(red[1])
+        cnt = torch.tensor([iters, e2e_iters, launches], dtype=torch.float64, device="cuda")
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        iters, e2e_iters, launches = int(cnt[0]), int(cnt[1]), int(cnt[2])
+    if rank != 0:
+        return
+
+    peak, peak_src = _peaks()
+    ab = algorithmic_bytes(lay)
+    top = max((k for k in ktimes if k in ab), key=lambda k: ktimes[k][0], default=None)
+    roof = None
+    per_kernel = {}
+    for k, (ms, n) in sorted(ktimes.items(), key=lambda kv: -kv[1][0]):
+        per_kernel[k] = {"ms_total": round(ms, 3), "launches": n, "avg_us": round(1e3 * ms / max(n, 1), 2)}
+        if k in ab:
+            per_kernel[k]["algorithmic_GBps"] = round(ab[k] / (ms / n * 1e-3) / 1e9, 1)
+    if top:
+        ms, n = ktimes[top]
+        achieved = ab[top] / (ms / n * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": ab[top],
+                "avg_launch_ms": ms / n, "frac_of_nominal_8TBps": achieved / 8000.0}
+
+    cpu = cpu_baseline_sample(args.workload) if (world == 1 and not args.no_cpu_baseline) else None
+    C_, P_, L_ = CONFIGS[args.workload]
+    line = {
+        "metric": METRIC, "value": iters / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {
+            "workload": args.workload, "images": C_, "points": P_, "observations": P_ * L_,
+            "sharding": "one scene per rank" if world > 1 else "single GPU",
+            "camera_model": prob.cam_model.tolist(), "reproj_loss": int(prob.reproj_loss), "depth_loss": int(prob.depth_loss),
+            "l2": "inputs larger than L2" if lay.N * 88 > 126e6 else "inputs fit in L2 (small workload; see DESIGN.md)",
+            "lm_iterations_per_solve": last.num_iterations, "termination": last.message,
+            "final_cost": last.final_cost, "pcg_iterations_per_solve": pcg_iters / args.steps,
+            "pcg_tolerance": args.pcg_tol, "rcs_blocks": lay.num_blocks,
+            "host_scene_s": round(t_scene, 2), "host_layout_s": round(t_layout, 2),
+        },
+        "ms_per_lm_iteration": ms_total / max(iters, 1),
+        "e2e": {"value": e2e_iters / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": 1e3 * e2e_s / args.steps},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": roof,
+        "kernels": per_kernel,
+        "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg3")
+    ap.add_argument("--pcg-tol", dest="pcg_tol", type=float, default=1e-12)
+    ap.add_argument("--pcg-max-iter", dest="pcg_max_iter", type=int, default=2000)
+    ap.add_argument("--ref-obs", dest="ref_obs", type=int, default=40_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()
