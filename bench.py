@@ -96,12 +96,16 @@ class ClockSampler:
 def algorithmic_bytes(lay):
     """Algorithmic HBM bytes per launch of each pass (fixed before measuring)."""
     N, P, C, B = lay.N, lay.P, lay.C, lay.num_blocks
-    npairs = int(lay.pair_block.shape[0])
+    n_items = int(lay.item_a.shape[0])
+    n_act = int(lay.u_item_ptr[-1] and np.count_nonzero(lay.pt_const == 0))
     return {
         # 4 (point idx) + 16 (xy) + 24 (d,w,a) per observation, every point read at least once (32 B), chunk partials
         "img_chunks": 44 * N + 32 * P + 256 * lay.num_chunks + 64 * C,
-        # 4 (image idx) + 16 + 24 per observation, pair->block map, point record in, Hpp/gp/Hinv/c_pt out, S once
-        "points_schur": 44 * N + 4 * npairs + (32 + 8 + 24 + 48 + 24 + 48) * P + 288 * B + 48 * C,
+        # 4 (image idx) + 16 + 24 in and one 128 B Schur factor out per observation; per point: xyz, pt_ptr, c_pt in,
+        # Hpp / gp / Hinv out
+        "points": (44 + 128) * N + (32 + 4 + 24 + 48 + 24 + 48) * P + 64 * C,
+        # every factor read at least once, 8 B per item, every block of S written once
+        "schur_blocks": 128 * N + 8 * n_items + 288 * B + (168 + 48 + 48) * C,
         "back_substitute": 44 * N + (32 + 4 + 48 + 24 + 48 + 32) * P + 48 * C,
     }
 

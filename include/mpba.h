@@ -104,10 +104,16 @@ typedef struct mpba_problem {
   const int32_t* s_col;         /* [B] */
   const int32_t* s_diag;        /* [C]   block index of (i,i) */
   const int32_t* s_transpose;   /* [B]   block index of (j,i) for block (i,j) */
-  /* for every track, every slot pair a<=b (row-major over a, then b): index of block
-   * (pm_img[a], pm_img[b]); pair_ptr[p] = first pair of track p */
-  const int32_t* pair_ptr;      /* [P+1] */
-  const int32_t* pair_block;    /* [pair_ptr[P]] */
+  const int32_t* s_row;         /* [B]   block row of every block */
+  /* Schur work lists: one unit per upper block (row <= col).  Unit u forms block u_block[u] from the
+   * items u_item_ptr[u]..u_item_ptr[u+1]; an item is a pair of TRACK-ORDER slots (a <= b) of one track
+   * whose images are (row, col) of the block; items of a unit are sorted by track.  Tracks of
+   * constant points contribute no items. */
+  int32_t num_upper;
+  const int32_t* u_block;       /* [U] */
+  const int32_t* u_item_ptr;    /* [U+1] */
+  const int32_t* item_a;        /* [u_item_ptr[U]] */
+  const int32_t* item_b;        /* [u_item_ptr[U]] */
 
   /* losses: ScaledLoss(loss(scale), weight) shared by all reprojection blocks
    * (bundle_adjustment.py:98-102); per-observation scale/weight for depth (:160-161) */

@@ -210,54 +210,6 @@ __device__ __forceinline__ double warp_transpose_reduce32(double (&v)[36], int l
   return v[0];
 }
 
-// add a 6x6 block per lane into T[key*36..]; lanes of a warp that all hold the same key are summed
-// in registers first (31 + 20 shuffle exchanges) and leave as ONE coalesced 36-value reduction.
-__device__ __forceinline__ void scatter_block36(double* __restrict__ T, int key, bool has, double (&M)[36], int lane) {
-  const int key0 = __shfl_sync(FULL, key, 0);
-  const bool uniform = __all_sync(FULL, has && key == key0);
-  if (uniform) {
-    double tail[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      double t = M[32 + j];
-      for (int off = 16; off > 0; off >>= 1) t += __shfl_xor_sync(FULL, t, off);
-      tail[j] = t;
-    }
-    const double mine = warp_transpose_reduce32(M, lane);
-    double* dst = T + (size_t)key0 * 36;
-    atomicAdd(dst + lane, mine);
-    if (lane < 4) atomicAdd(dst + 32 + lane, lane == 0 ? tail[0] : lane == 1 ? tail[1] : lane == 2 ? tail[2] : tail[3]);
-  } else if (has) {
-    double* dst = T + (size_t)key * 36;
-#pragma unroll
-    for (int j = 0; j < 36; ++j) atomicAdd(dst + j, M[j]);
-  }
-}
-
-__device__ __forceinline__ void scatter_vec6(double* __restrict__ out, int key, bool has, const double (&g)[6], int lane) {
-  const int key0 = __shfl_sync(FULL, key, 0);
-  const bool uniform = __all_sync(FULL, has && key == key0);
-  if (uniform) {
-    double mine = 0.0;
-#pragma unroll
-    for (int j = 0; j < 6; ++j) {
-      double t = g[j];
-      for (int off = 16; off > 0; off >>= 1) t += __shfl_xor_sync(FULL, t, off);
-      if (lane == j) mine = t;
-    }
-    if (lane < 6) atomicAdd(out + (size_t)key0 * 6 + lane, mine);
-  } else if (has) {
-#pragma unroll
-    for (int j = 0; j < 6; ++j) atomicAdd(out + (size_t)key * 6 + j, g[j]);
-  }
-}
-
-struct TrackObs {
-  double Q[9];   // N R
-  double prot[3];
-  int img;
-};
-
 __device__ __forceinline__ void track_obs(const ProblemView& pv, const double* __restrict__ pose, const double Xp[3],
                                           int k, ObsLin& o, ImgConst& ic) {
   const int img = __ldg(pv.pm_img + k);
@@ -270,16 +222,19 @@ __device__ __forceinline__ void track_obs(const ProblemView& pv, const double* _
 
 constexpr int PT_THREADS = 128;
 
-__global__ void __launch_bounds__(PT_THREADS) k_points_schur(ProblemView pv, const double* __restrict__ pose,
-                                                             const double* __restrict__ X, LmDiag lm,
-                                                             double* __restrict__ c_pt, int compute_scaling,
-                                                             int jacobi_scaling, double* __restrict__ Hpp,
-                                                             double* __restrict__ gp, double* __restrict__ Hinv,
-                                                             double* __restrict__ T, double* __restrict__ rhs_acc,
-                                                             double* __restrict__ pt_part, double* __restrict__ scal,
-                                                             int do_schur) {
+// One thread per track.  Pass 1: Hpp = sum R^T N R, gp = sum R^T h, damped Cholesky Hpp + D = L L^T.
+// Pass 2 (write_factors): one 128-byte Schur factor per observation,
+//     fac[k] = { Z = N R L^-T (9), p_rot (3), e = L^-1 gp (3), 0 },
+// from which k_schur_blocks forms  W_a Hpp^-1 W_b^T = G_a^T (Z_a Z_b^T) G_b  and
+// W_a Hpp^-1 gp = G_a^T Z_a e  without ever storing the 6x3 W blocks.
+__global__ void __launch_bounds__(PT_THREADS) k_points(ProblemView pv, const double* __restrict__ pose,
+                                                       const double* __restrict__ X, LmDiag lm,
+                                                       double* __restrict__ c_pt, int compute_scaling,
+                                                       int jacobi_scaling, double* __restrict__ Hpp,
+                                                       double* __restrict__ gp, double* __restrict__ Hinv,
+                                                       double* __restrict__ fac, double* __restrict__ pt_part,
+                                                       double* __restrict__ scal, int write_factors) {
   const int p = blockIdx.x * PT_THREADS + threadIdx.x;
-  const int lane = threadIdx.x & 31;
   const bool valid = p < pv.P;
   const bool active = valid && pv.pt_const[p] == 0;
   int beg = 0, end = 0;
@@ -291,7 +246,6 @@ __global__ void __launch_bounds__(PT_THREADS) k_points_schur(ProblemView pv, con
   double Xp[3] = {0.0, 0.0, 0.0};
   if (active) load_point(X, p, Xp);
 
-  // ---- pass 1: Hpp = sum R^T N R, gp = sum R^T h
   double Hp[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, g[3] = {0.0, 0.0, 0.0};
   for (int k = beg; k < end; ++k) {
     ObsLin o;
@@ -311,7 +265,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_points_schur(ProblemView pv, con
     g[2] += R[2] * o.h[0] + R[5] * o.h[1] + R[8] * o.h[2];
   }
 
-  double Hi[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  double Hi[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, Li[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  bool solvable = false;
   if (valid) {
     double c[3] = {0.0, 0.0, 0.0};
     if (compute_scaling) {
@@ -329,9 +284,12 @@ __global__ void __launch_bounds__(PT_THREADS) k_points_schur(ProblemView pv, con
       Hd[0] += lm_damping(Hp[0], c[0], lm.radius, lm.lo, lm.hi);
       Hd[3] += lm_damping(Hp[3], c[1], lm.radius, lm.lo, lm.hi);
       Hd[5] += lm_damping(Hp[5], c[2], lm.radius, lm.lo, lm.hi);
-      if (!sym3_inverse(Hd, Hi)) {
+      solvable = sym3_chol_inverse(Hd, Li);
+      if (solvable) {
+        sym3_from_chol_inverse(Li, Hi);
+      } else {
 #pragma unroll
-        for (int j = 0; j < 6; ++j) Hi[j] = 0.0;
+        for (int j = 0; j < 6; ++j) Li[j] = 0.0;
         atomicAdd(scal + S_BAD_POINTS, 1.0);  // failure counter, not arithmetic
       }
     }
@@ -344,84 +302,30 @@ __global__ void __launch_bounds__(PT_THREADS) k_points_schur(ProblemView pv, con
     for (int j = 0; j < 3; ++j) gp[(size_t)p * 3 + j] = g[j];
   }
 
-  // max |gp| of this CTA
   {
     __shared__ double smx[PT_THREADS / 32 + 1];
     const double m = block_max<PT_THREADS / 32>(fmax(fabs(g[0]), fmax(fabs(g[1]), fabs(g[2]))), smx);
     if (threadIdx.x == 0) pt_part[(size_t)blockIdx.x * PT_PART] = m;
   }
-  if (!do_schur) return;
+  if (!write_factors) return;
 
-  // ---- pass 2: T(i_a, i_b) += W_a Hpp^-1 W_b^T,  rhs_acc(i_a) += W_a Hpp^-1 gp,  W = G^T Q
-  double e[3];
-  sym3_mul_vec(Hi, g, e);
-  int Lmax = L;
-  for (int off = 16; off > 0; off >>= 1) Lmax = max(Lmax, __shfl_xor_sync(FULL, Lmax, off));
-  const int pair0 = active ? pv.pair_ptr[p] : 0;
-
-  for (int a = 0; a < Lmax; ++a) {
-    const bool has_a = a < L;
-    double Za[9], pa[3] = {0.0, 0.0, 0.0};
-    int img_a = -1;
-    double ga[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-    if (has_a) {
-      ObsLin o;
-      ImgConst ic;
-      track_obs(pv, pose, Xp, beg + a, o, ic);
-      img_a = __ldg(pv.pm_img + beg + a);
-      double Q[9];
-      sym3_mul_mat(o.N, ic.R, Q);
-      pa[0] = o.prot[0]; pa[1] = o.prot[1]; pa[2] = o.prot[2];
-      // Za = Q Hi (Hi symmetric)
-#pragma unroll
-      for (int i = 0; i < 3; ++i) {
-        const double q0 = Q[3 * i], q1 = Q[3 * i + 1], q2 = Q[3 * i + 2];
-        Za[3 * i] = q0 * Hi[0] + q1 * Hi[1] + q2 * Hi[2];
-        Za[3 * i + 1] = q0 * Hi[1] + q1 * Hi[3] + q2 * Hi[4];
-        Za[3 * i + 2] = q0 * Hi[2] + q1 * Hi[4] + q2 * Hi[5];
-      }
-      double ua[3];
-      ua[0] = Q[0] * e[0] + Q[1] * e[1] + Q[2] * e[2];
-      ua[1] = Q[3] * e[0] + Q[4] * e[1] + Q[5] * e[2];
-      ua[2] = Q[6] * e[0] + Q[7] * e[1] + Q[8] * e[2];
-      gt_vec(pa, ua, ga);
-    }
-    scatter_vec6(rhs_acc, img_a, has_a, ga, lane);
-
-    for (int b = a; b < Lmax; ++b) {
-      const bool has_b = b < L;
-      double M[36];
-      int blk = -1;
-      if (has_b) {
-        ObsLin o;
-        ImgConst ic;
-        track_obs(pv, pose, Xp, beg + b, o, ic);
-        const int img_b = __ldg(pv.pm_img + beg + b);
-        double Q[9], K[9];
-        sym3_mul_mat(o.N, ic.R, Q);
-        // K = Za Qb^T
-#pragma unroll
-        for (int i = 0; i < 3; ++i)
-#pragma unroll
-          for (int j = 0; j < 3; ++j) K[3 * i + j] = Za[3 * i] * Q[3 * j] + Za[3 * i + 1] * Q[3 * j + 1] + Za[3 * i + 2] * Q[3 * j + 2];
-        gt_k_g(pa, K, o.prot, M);
-        if (b > a && img_b == img_a) {  // two observations of one image in a track: M + M^T on the diagonal block
-#pragma unroll
-          for (int i = 0; i < 6; ++i)
-#pragma unroll
-            for (int j = i; j < 6; ++j) {
-              const double s = M[6 * i + j] + M[6 * j + i];
-              M[6 * i + j] = s;
-              M[6 * j + i] = s;
-            }
-        }
-        blk = __ldg(pv.pair_block + pair0 + a * L - (a * (a - 1)) / 2 + (b - a));
-      } else {
-#pragma unroll
-        for (int j = 0; j < 36; ++j) M[j] = 0.0;
-      }
-      scatter_block36(T, blk, has_b, M, lane);
-    }
+  const double e0 = Li[0] * g[0], e1 = Li[1] * g[0] + Li[2] * g[1], e2 = Li[3] * g[0] + Li[4] * g[1] + Li[5] * g[2];
+  for (int k = beg; k < end; ++k) {
+    ObsLin o;
+    ImgConst ic;
+    track_obs(pv, pose, Xp, k, o, ic);
+    double Q[9], Z[9];
+    sym3_mul_mat(o.N, ic.R, Q);
+    mul_chol_inverse_t(Q, Li, Z);
+    double2* dst = reinterpret_cast<double2*>(fac + (size_t)k * FAC_STRIDE);
+    dst[0] = make_double2(Z[0], Z[1]);
+    dst[1] = make_double2(Z[2], Z[3]);
+    dst[2] = make_double2(Z[4], Z[5]);
+    dst[3] = make_double2(Z[6], Z[7]);
+    dst[4] = make_double2(Z[8], o.prot[0]);
+    dst[5] = make_double2(o.prot[1], o.prot[2]);
+    dst[6] = make_double2(e0, e1);
+    dst[7] = make_double2(e2, 0.0);
   }
 }
 
@@ -437,43 +341,132 @@ __global__ void __launch_bounds__(1024) k_pt_scalars_gmax(const double* __restri
 // ================================================================================================
 // reduced camera system
 // ================================================================================================
-// one CTA per block row: S = Hcc + D - T on the diagonal, -T off it, identity on fixed coordinates
-__global__ void __launch_bounds__(128) k_s_finalize(ProblemView pv, const double* __restrict__ Hc,
-                                                    const double* __restrict__ gc, const double* __restrict__ c_img,
-                                                    LmDiag lm, const double* __restrict__ T,
-                                                    const double* __restrict__ rhs_acc, double* __restrict__ S,
-                                                    double* __restrict__ rhs) {
-  const int i = blockIdx.x;
-  const int r0 = pv.s_row_ptr[i], r1 = pv.s_row_ptr[i + 1];
-  const unsigned mi = pv.img_free_mask[i];
-  const int total = (r1 - r0) * 36;
-  for (int idx = threadIdx.x; idx < total; idx += 128) {
-    const int blk = r0 + idx / 36, e = idx % 36, r = e / 6, c = e % 6;
-    const int j = pv.s_col[blk];
-    const bool fr = (mi >> r) & 1u;
+struct Fac {
+  double Z[9], p[3], e[3];
+};
+__device__ __forceinline__ void load_fac(const double* __restrict__ fac, int k, Fac& f) {
+  const double2* s = reinterpret_cast<const double2*>(fac + (size_t)k * FAC_STRIDE);
+  const double2 a = s[0], b = s[1], c = s[2], d = s[3], e = s[4], g = s[5], h = s[6], i = s[7];
+  f.Z[0] = a.x; f.Z[1] = a.y; f.Z[2] = b.x; f.Z[3] = b.y; f.Z[4] = c.x; f.Z[5] = c.y; f.Z[6] = d.x; f.Z[7] = d.y;
+  f.Z[8] = e.x; f.p[0] = e.y; f.p[1] = g.x; f.p[2] = g.y; f.e[0] = h.x; f.e[1] = h.y; f.e[2] = i.x;
+}
+
+constexpr int SB_THREADS = 128;
+
+// One CTA per upper block (i <= j) of the reduced camera system, no atomics, fixed summation order:
+//   T(i,j) = sum over the tracks seen by both images of G_a^T (Z_a Z_b^T) G_b
+// is accumulated in registers over the block's item list (pairs of factor slots, sorted by track),
+// reduced across the CTA (shuffle transpose + shared memory), and written once as
+//   S(i,i) = Hcc_i + D_i - T(i,i),  S(i,j) = -T(i,j),  S(j,i) = S(i,j)^T,  rhs_i = gc_i - sum G_a^T Z_a e
+// with identity rows / zero rhs on fixed tangent coordinates (gauge, bundle_adjustment.py:114-121).
+__global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, const double* __restrict__ fac,
+                                                             const double* __restrict__ Hc,
+                                                             const double* __restrict__ gc,
+                                                             const double* __restrict__ c_img, LmDiag lm,
+                                                             double* __restrict__ S, double* __restrict__ rhs) {
+  const int u = blockIdx.x;
+  const int blk = pv.u_block[u];
+  const int i = pv.s_row[blk], j = pv.s_col[blk];
+  const bool diag = (i == j);
+  const int it0 = pv.u_item_ptr[u], it1 = pv.u_item_ptr[u + 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+  double M[36];
+#pragma unroll
+  for (int k = 0; k < 36; ++k) M[k] = 0.0;
+  double rv[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+
+  for (int it = it0 + (int)threadIdx.x; it < it1; it += SB_THREADS) {
+    const int ka = __ldg(pv.item_a + it), kb = __ldg(pv.item_b + it);
+    Fac fa;
+    load_fac(fac, ka, fa);
+    double K[9], Mi[36];
+    if (ka == kb) {
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+          K[3 * r + c] = fa.Z[3 * r] * fa.Z[3 * c] + fa.Z[3 * r + 1] * fa.Z[3 * c + 1] + fa.Z[3 * r + 2] * fa.Z[3 * c + 2];
+      gt_k_g(fa.p, K, fa.p, Mi);
+      double ze[3], ge[6];
+      ze[0] = fa.Z[0] * fa.e[0] + fa.Z[1] * fa.e[1] + fa.Z[2] * fa.e[2];
+      ze[1] = fa.Z[3] * fa.e[0] + fa.Z[4] * fa.e[1] + fa.Z[5] * fa.e[2];
+      ze[2] = fa.Z[6] * fa.e[0] + fa.Z[7] * fa.e[1] + fa.Z[8] * fa.e[2];
+      gt_vec(fa.p, ze, ge);
+#pragma unroll
+      for (int k = 0; k < 6; ++k) rv[k] += ge[k];
+#pragma unroll
+      for (int k = 0; k < 36; ++k) M[k] += Mi[k];
+    } else {
+      Fac fb;
+      load_fac(fac, kb, fb);
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+          K[3 * r + c] = fa.Z[3 * r] * fb.Z[3 * c] + fa.Z[3 * r + 1] * fb.Z[3 * c + 1] + fa.Z[3 * r + 2] * fb.Z[3 * c + 2];
+      gt_k_g(fa.p, K, fb.p, Mi);
+      if (diag) {  // one image observing a track twice: both orientations land on the diagonal block
+#pragma unroll
+        for (int r = 0; r < 6; ++r)
+#pragma unroll
+          for (int c = 0; c < 6; ++c) M[6 * r + c] += Mi[6 * r + c] + Mi[6 * c + r];
+      } else {
+#pragma unroll
+        for (int k = 0; k < 36; ++k) M[k] += Mi[k];
+      }
+    }
+  }
+
+  // ---- CTA reduction: lane e of every warp ends with entry e (e < 32), entries 32..35 by butterfly
+  __shared__ double sm[SB_THREADS / 32][44];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    double t = M[32 + k];
+    for (int off = 16; off > 0; off >>= 1) t += __shfl_xor_sync(FULL, t, off);
+    if (lane == k) sm[warp][32 + k] = t;
+  }
+  if (diag) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      double t = rv[k];
+      for (int off = 16; off > 0; off >>= 1) t += __shfl_xor_sync(FULL, t, off);
+      if (lane == k) sm[warp][36 + k] = t;
+    }
+  }
+  sm[warp][lane] = warp_transpose_reduce32(M, lane);
+  __syncthreads();
+  if (threadIdx.x < 42) {
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < SB_THREADS / 32; ++w) t += sm[w][threadIdx.x];
+    sm[0][threadIdx.x] = t;  // only this thread touches column threadIdx.x after the barrier
+  }
+  __syncthreads();
+
+  // ---- epilogue
+  const unsigned mi = pv.img_free_mask[i], mj = pv.img_free_mask[j];
+  if (threadIdx.x < 36) {
+    const int e = threadIdx.x, r = e / 6, c = e % 6;
+    const bool fr = (mi >> r) & 1u, fc = (mj >> c) & 1u;
     double val;
-    if (j == i) {
-      const bool fc = (mi >> c) & 1u;
+    if (diag) {
       if (fr && fc) {
-        const int u = upper_idx(r < c ? r : c, r < c ? c : r);
-        val = Hc[(size_t)i * 21 + u] - 0.5 * (T[(size_t)blk * 36 + e] + T[(size_t)blk * 36 + c * 6 + r]);
-        if (r == c) val += lm_damping(Hc[(size_t)i * 21 + u], c_img[(size_t)i * 6 + r], lm.radius, lm.lo, lm.hi);
+        const int uidx = upper_idx(r < c ? r : c, r < c ? c : r);
+        val = Hc[(size_t)i * 21 + uidx] - 0.5 * (sm[0][e] + sm[0][c * 6 + r]);
+        if (r == c) val += lm_damping(Hc[(size_t)i * 21 + uidx], c_img[(size_t)i * 6 + r], lm.radius, lm.lo, lm.hi);
       } else {
         val = (r == c) ? 1.0 : 0.0;
       }
+      S[(size_t)blk * 36 + e] = val;
     } else {
-      const bool fc = (pv.img_free_mask[j] >> c) & 1u;
-      if (fr && fc) {
-        val = (i < j) ? -T[(size_t)blk * 36 + e] : -T[(size_t)pv.s_transpose[blk] * 36 + c * 6 + r];
-      } else {
-        val = 0.0;
-      }
+      val = (fr && fc) ? -sm[0][e] : 0.0;
+      S[(size_t)blk * 36 + e] = val;
+      S[(size_t)pv.s_transpose[blk] * 36 + c * 6 + r] = val;
     }
-    S[(size_t)blk * 36 + e] = val;
-  }
-  if (threadIdx.x < 6) {
-    const int r = threadIdx.x;
-    rhs[(size_t)i * 6 + r] = ((mi >> r) & 1u) ? gc[(size_t)i * 6 + r] - rhs_acc[(size_t)i * 6 + r] : 0.0;
+  } else if (diag && threadIdx.x >= 64 && threadIdx.x < 70) {
+    const int r = threadIdx.x - 64;
+    rhs[(size_t)i * 6 + r] = ((mi >> r) & 1u) ? gc[(size_t)i * 6 + r] - sm[0][36 + r] : 0.0;
   }
 }
 
@@ -864,19 +857,19 @@ void launch_img_scalars(const ProblemView& pv, const double* img_part, const dou
   k_img_scalars<<<1, 1024, 0, st>>>(pv.C, img_part, gc, scal);
 }
 int points_grid(int P) { return (P + PT_THREADS - 1) / PT_THREADS; }
-void launch_points_schur(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,
-                         int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* T,
-                         double* rhs_acc, double* pt_part, double* scal, int do_schur, cudaStream_t st) {
+void launch_points(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,
+                   int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* fac,
+                   double* pt_part, double* scal, int write_factors, cudaStream_t st) {
   if (pv.P > 0)
-    k_points_schur<<<points_grid(pv.P), PT_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp,
-                                                              gp, Hinv, T, rhs_acc, pt_part, scal, do_schur);
+    k_points<<<points_grid(pv.P), PT_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp,
+                                                       Hinv, fac, pt_part, scal, write_factors);
 }
 void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaStream_t st) {
   k_pt_scalars_gmax<<<1, 1024, 0, st>>>(pt_part, nblk, scal);
 }
-void launch_s_finalize(const ProblemView& pv, const double* Hc, const double* gc, const double* c_img, LmDiag lm,
-                       const double* T, const double* rhs_acc, double* S, double* rhs, double* Minv, cudaStream_t st) {
-  k_s_finalize<<<pv.C, 128, 0, st>>>(pv, Hc, gc, c_img, lm, T, rhs_acc, S, rhs);
+void launch_schur_blocks(const ProblemView& pv, const double* fac, const double* Hc, const double* gc,
+                         const double* c_img, LmDiag lm, double* S, double* rhs, double* Minv, cudaStream_t st) {
+  k_schur_blocks<<<pv.U, SB_THREADS, 0, st>>>(pv, fac, Hc, gc, c_img, lm, S, rhs);
   k_block_inverse<<<(pv.C + 127) / 128, 128, 0, st>>>(pv, S, Minv);
 }
 int pcg_grid(int device, int C) {

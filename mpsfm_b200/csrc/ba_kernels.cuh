@@ -29,9 +29,10 @@ enum Scal {
 constexpr int MPBA_MAX_PRM = 12;
 constexpr int IMG_PART = 32;  // doubles per image-chunk partial: 21 Hcc + 6 gc + cost_free + cost_fixed (+pad)
 constexpr int PT_PART = 4;    // doubles per track-CTA partial
+constexpr int FAC_STRIDE = 16; // doubles per Schur factor record (128 B per observation)
 
 struct ProblemView {
-  int C, K, P, N, B, num_chunks;
+  int C, K, P, N, B, U, num_chunks;
   const int32_t* img_camera;
   const uint8_t* img_free_mask;
   const double* img_shift_scale;
@@ -54,8 +55,11 @@ struct ProblemView {
   const int32_t* s_col;
   const int32_t* s_diag;
   const int32_t* s_transpose;
-  const int32_t* pair_ptr;
-  const int32_t* pair_block;
+  const int32_t* s_row;
+  const int32_t* u_block;
+  const int32_t* u_item_ptr;
+  const int32_t* item_a;
+  const int32_t* item_b;
   LossSpec loss;
 };
 
@@ -71,17 +75,16 @@ void launch_img_finalize(const ProblemView& pv, const double* chunk_part, double
 void launch_img_scalars(const ProblemView& pv, const double* img_part, const double* gc, double* scal,
                         cudaStream_t st);
 
-// ---- track order: Hpp, gp, point-block inverse, Schur complement scatter ----------------------
-void launch_points_schur(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,
-                         int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* T,
-                         double* rhs_acc, double* pt_part, double* scal, int do_schur, cudaStream_t st);
+// ---- track order: Hpp, gp, point-block Cholesky, Schur factors ------------------------------------
+void launch_points(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,
+                   int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* fac,
+                   double* pt_part, double* scal, int write_factors, cudaStream_t st);
 int points_grid(int P);
 void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaStream_t st);
 
 // ---- reduced camera system ----------------------------------------------------------------------
-void launch_s_finalize(const ProblemView& pv, const double* Hc, const double* gc, const double* c_img, LmDiag lm,
-                       const double* T, const double* rhs_acc, double* S, double* rhs, double* Minv,
-                       cudaStream_t st);
+void launch_schur_blocks(const ProblemView& pv, const double* fac, const double* Hc, const double* gc,
+                         const double* c_img, LmDiag lm, double* S, double* rhs, double* Minv, cudaStream_t st);
 // returns cudaError from the cooperative launch
 cudaError_t launch_pcg(const ProblemView& pv, const double* S, const double* Minv, const double* rhs, double* y,
                        double* vec_r, double* vec_z, double* vec_p0, double* vec_p1, double* vec_q, double* partial,

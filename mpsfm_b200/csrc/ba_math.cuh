@@ -324,9 +324,10 @@ MPBA_HD void sym3_mul_mat(const double N[6], const double R[9], double Q[9]) {
   }
 }
 
-// inverse of a symmetric positive definite 3x3 through its Cholesky factor (what Ceres' Schur
-// eliminator does with Eigen's LLT on the e-block); returns false if not positive definite.
-MPBA_HD bool sym3_inverse(const double H[6], double Hi[6]) {
+// Cholesky of a symmetric positive definite 3x3 (what Ceres' Schur eliminator does with Eigen's LLT
+// on the e-block): returns Li = L^-1 (lower: i00, i10, i11, i20, i21, i22) so that H^-1 = Li^T Li;
+// false if H is not positive definite.
+MPBA_HD bool sym3_chol_inverse(const double H[6], double Li[6]) {
   const double a = H[0], b = H[1], c = H[2], d = H[3], e = H[4], f = H[5];
   if (!(a > 0.0)) return false;
   const double l00 = sqrt(a), l10 = b / l00, l20 = c / l00;
@@ -336,19 +337,41 @@ MPBA_HD bool sym3_inverse(const double H[6], double Hi[6]) {
   const double t22 = f - l20 * l20 - l21 * l21;
   if (!(t22 > 0.0)) return false;
   const double l22 = sqrt(t22);
-  // inverse of L (lower)
   const double i00 = 1.0 / l00, i11 = 1.0 / l11, i22 = 1.0 / l22;
   const double i10 = -l10 * i00 * i11;
   const double i21 = -l21 * i11 * i22;
   const double i20 = -(l20 * i00 + l21 * i10) * i22;
-  // H^-1 = L^-T L^-1
+  Li[0] = i00; Li[1] = i10; Li[2] = i11; Li[3] = i20; Li[4] = i21; Li[5] = i22;
+  return true;
+}
+
+// H^-1 = Li^T Li as (xx, xy, xz, yy, yz, zz)
+MPBA_HD void sym3_from_chol_inverse(const double Li[6], double Hi[6]) {
+  const double i00 = Li[0], i10 = Li[1], i11 = Li[2], i20 = Li[3], i21 = Li[4], i22 = Li[5];
   Hi[0] = i00 * i00 + i10 * i10 + i20 * i20;
   Hi[1] = i10 * i11 + i20 * i21;
   Hi[2] = i20 * i22;
   Hi[3] = i11 * i11 + i21 * i21;
   Hi[4] = i21 * i22;
   Hi[5] = i22 * i22;
+}
+
+MPBA_HD bool sym3_inverse(const double H[6], double Hi[6]) {
+  double Li[6];
+  if (!sym3_chol_inverse(H, Li)) return false;
+  sym3_from_chol_inverse(Li, Hi);
   return true;
+}
+
+// Z = Q Li^T (3x3 row-major), so that Za Zb^T = Qa H^-1 Qb^T
+MPBA_HD void mul_chol_inverse_t(const double Q[9], const double Li[6], double Z[9]) {
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const double q0 = Q[3 * r], q1 = Q[3 * r + 1], q2 = Q[3 * r + 2];
+    Z[3 * r] = q0 * Li[0];
+    Z[3 * r + 1] = q0 * Li[1] + q1 * Li[2];
+    Z[3 * r + 2] = q0 * Li[3] + q1 * Li[4] + q2 * Li[5];
+  }
 }
 
 // ------------------------------------------------------------------------------------------------

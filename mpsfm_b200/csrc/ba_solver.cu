@@ -26,7 +26,7 @@ enum KernelSlot {
   KS_REDUCE, KS_EVALUATE, KS_MISC, KS_SPARE0, KS_SPARE1
 };
 static const char* kKernelNames[MPBA_NUM_KERNELS] = {
-    "img_chunks", "img_finalize", "points_schur", "s_finalize", "pcg", "cam_update", "back_substitute",
+    "img_chunks", "img_finalize", "points", "schur_blocks", "pcg", "cam_update", "back_substitute",
     "reduce", "evaluate", "misc", "spare0", "spare1"};
 
 struct TimedEvent {
@@ -99,7 +99,7 @@ void flush_timers(mpba_handle* h) {
 size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Workspace {
-  double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *img_part, *c_img, *c_pt, *Hpp, *gp, *Hinv, *T, *S, *rhs_acc,
+  double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *img_part, *c_img, *c_pt, *Hpp, *gp, *Hinv, *fac, *S,
       *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal;
   size_t bytes = 0;
 };
@@ -127,9 +127,8 @@ void carve(const mpba_problem* p, char* base, Workspace& w) {
   w.Hpp = take(P * 6);
   w.gp = take(P * 3);
   w.Hinv = take(P * 6);
-  w.T = take(B * 36);
+  w.fac = take((p->flags & MPBA_FLAG_STRUCTURE_ONLY) ? 0 : (size_t)p->num_obs * FAC_STRIDE);
   w.S = take(B * 36);
-  w.rhs_acc = take(C * 6);
   w.rhs = take(C * 6);
   w.Minv = take(C * 36);
   w.y = take(C * 6);
@@ -158,8 +157,9 @@ int check_problem(mpba_handle* h, const mpba_problem* p) {
     return fail(h, MPBA_E_INVALID, "image-order chunk arrays must not be NULL");
   if (p->num_blocks < p->num_images || !p->s_row_ptr || !p->s_col || !p->s_diag || !p->s_transpose)
     return fail(h, MPBA_E_INVALID, "reduced camera system structure missing (needs at least the diagonal blocks)");
-  if (p->num_obs > 0 && (!p->pair_ptr || !p->pair_block))
-    return fail(h, MPBA_E_INVALID, "pair_ptr / pair_block must not be NULL");
+  if (!(p->flags & MPBA_FLAG_STRUCTURE_ONLY) &&
+      (!p->s_row || p->num_upper < p->num_images || !p->u_block || !p->u_item_ptr || (p->num_obs > 0 && (!p->item_a || !p->item_b))))
+    return fail(h, MPBA_E_INVALID, "Schur work lists (s_row, u_block, u_item_ptr, item_a, item_b) missing");
   if (p->reproj_loss < 0 || p->reproj_loss > 3 || p->depth_loss < 0 || p->depth_loss > 3)
     return fail(h, MPBA_E_INVALID, "unknown loss type");
   return MPBA_OK;
@@ -174,7 +174,8 @@ ProblemView view_of(const mpba_problem* p) {
   v.pm_img = p->pm_img; v.pm_xy = p->pm_xy; v.pm_depth = p->pm_depth; v.img_ptr = p->img_ptr; v.cm_pt = p->cm_pt;
   v.cm_xy = p->cm_xy; v.cm_depth = p->cm_depth; v.chunk_img = p->chunk_img; v.chunk_begin = p->chunk_begin;
   v.chunk_end = p->chunk_end; v.img_chunk_ptr = p->img_chunk_ptr; v.s_row_ptr = p->s_row_ptr; v.s_col = p->s_col;
-  v.s_diag = p->s_diag; v.s_transpose = p->s_transpose; v.pair_ptr = p->pair_ptr; v.pair_block = p->pair_block;
+  v.s_diag = p->s_diag; v.s_transpose = p->s_transpose; v.s_row = p->s_row; v.U = p->num_upper;
+  v.u_block = p->u_block; v.u_item_ptr = p->u_item_ptr; v.item_a = p->item_a; v.item_b = p->item_b;
   v.loss.reproj_loss = p->reproj_loss; v.loss.depth_loss = p->depth_loss;
   v.loss.reproj_scale = p->reproj_loss_scale; v.loss.reproj_weight = p->reproj_loss_weight;
   return v;
@@ -234,16 +235,11 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
                               const mpba_options* opt, bool want_system) {
   mpba_handle* h = c.h;
   const bool schur = want_system && !c.structure_only;
-  if (schur) {
-    Timer t(h, KS_MISC, 0);
-    CU(cudaMemsetAsync(c.w.T, 0, (size_t)c.pv.B * 36 * sizeof(double), h->stream));
-    CU(cudaMemsetAsync(c.w.rhs_acc, 0, (size_t)c.pv.C * 6 * sizeof(double), h->stream));
-  }
   CU(cudaMemsetAsync(c.w.scal + S_BAD_POINTS, 0, sizeof(double), h->stream));
   {
     Timer t(h, KS_POINTS_SCHUR);
-    launch_points_schur(c.pv, pose, X, lm, c.w.c_pt, compute_scaling, opt->jacobi_scaling, c.w.Hpp, c.w.gp, c.w.Hinv,
-                        c.w.T, c.w.rhs_acc, c.w.pt_part, c.w.scal, schur ? 1 : 0, h->stream);
+    launch_points(c.pv, pose, X, lm, c.w.c_pt, compute_scaling, opt->jacobi_scaling, c.w.Hpp, c.w.gp, c.w.Hinv, c.w.fac,
+                  c.w.pt_part, c.w.scal, schur ? 1 : 0, h->stream);
   }
   {
     Timer t(h, KS_REDUCE);
@@ -253,8 +249,7 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
   if (schur) {
     {
       Timer t(h, KS_S_FINALIZE, 2);
-      launch_s_finalize(c.pv, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.T, c.w.rhs_acc, c.w.S, c.w.rhs, c.w.Minv,
-                        h->stream);
+      launch_schur_blocks(c.pv, c.w.fac, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.S, c.w.rhs, c.w.Minv, h->stream);
     }
     {
       Timer t(h, KS_PCG);

@@ -61,7 +61,8 @@ class MpbaProblem(C.Structure):
         ("img_chunk_ptr", C.c_void_p),
         ("num_blocks", C.c_int32),
         ("s_row_ptr", C.c_void_p), ("s_col", C.c_void_p), ("s_diag", C.c_void_p), ("s_transpose", C.c_void_p),
-        ("pair_ptr", C.c_void_p), ("pair_block", C.c_void_p),
+        ("s_row", C.c_void_p), ("num_upper", C.c_int32),
+        ("u_block", C.c_void_p), ("u_item_ptr", C.c_void_p), ("item_a", C.c_void_p), ("item_b", C.c_void_p),
         ("reproj_loss", C.c_int32), ("depth_loss", C.c_int32),
         ("reproj_loss_scale", C.c_double), ("reproj_loss_weight", C.c_double),
         ("flags", C.c_int32), ("reserved", C.c_int32),
@@ -189,8 +190,11 @@ class HostLayout:
     s_col: np.ndarray
     s_diag: np.ndarray
     s_transpose: np.ndarray
-    pair_ptr: np.ndarray
-    pair_block: np.ndarray
+    s_row: np.ndarray
+    u_block: np.ndarray
+    u_item_ptr: np.ndarray
+    item_a: np.ndarray
+    item_b: np.ndarray
     reproj_loss: int
     depth_loss: int
     reproj_loss_scale: float
@@ -259,13 +263,16 @@ def build_layout(problem: BundleProblem) -> HostLayout:
     chunk_begin = (img_ptr[chunk_img] + local * MPBA_CHUNK).astype(np.int32)
     chunk_end = np.minimum(chunk_begin.astype(np.int64) + MPBA_CHUNK, img_ptr[chunk_img + 1]).astype(np.int32)
 
-    # ---- reduced camera system structure and per-track pair -> block map
+    # ---- reduced camera system structure and the Schur work lists (one unit per upper block)
     structure_only = bool(np.all(pr.img_free_mask == 0))
     active = (pr.pt_const == 0)
     L = np.where(active, pt_cnt, 0).astype(np.int64)
     npairs = L * (L + 1) // 2
     pair_ptr = _ptr_from_counts(npairs)
-    pair_key = np.empty(int(pair_ptr[-1]), dtype=np.int64)
+    n_items = 0 if structure_only else int(pair_ptr[-1])
+    pair_key = np.empty(n_items, dtype=np.int64)
+    item_a = np.empty(n_items, dtype=np.int32)
+    item_b = np.empty(n_items, dtype=np.int32)
     if not structure_only:
         for ell in np.unique(L):
             ell = int(ell)
@@ -275,24 +282,33 @@ def build_layout(problem: BundleProblem) -> HostLayout:
             slots = pt_ptr[pts].astype(np.int64)[:, None] + np.arange(ell)[None, :]
             imgs = pm_img[slots].astype(np.int64)  # [n, ell], ascending in every row
             ia, ib = np.triu_indices(ell)  # row-major over a, then b >= a
-            keys = imgs[:, ia] * Cn + imgs[:, ib]
-            dst = pair_ptr[pts].astype(np.int64)[:, None] + np.arange(ia.shape[0])[None, :]
-            pair_key[dst.reshape(-1)] = keys.reshape(-1)
+            dst = (pair_ptr[pts].astype(np.int64)[:, None] + np.arange(ia.shape[0])[None, :]).reshape(-1)
+            pair_key[dst] = (imgs[:, ia] * Cn + imgs[:, ib]).reshape(-1)
+            item_a[dst] = slots[:, ia].reshape(-1)
+            item_b[dst] = slots[:, ib].reshape(-1)
     diag_keys = np.arange(Cn, dtype=np.int64) * (Cn + 1)
     if structure_only:
         all_keys = diag_keys
-        pair_block = np.zeros(pair_key.shape[0], dtype=np.int32)
+        item_block = np.zeros(0, dtype=np.int32)
     else:
         upper = np.unique(pair_key)
         ui, uj = upper // Cn, upper % Cn
         lower = (uj * Cn + ui)[ui != uj]
         all_keys = np.unique(np.concatenate([upper, lower, diag_keys]))
-        pair_block = np.searchsorted(all_keys, pair_key).astype(np.int32)
+        item_block = np.searchsorted(all_keys, pair_key).astype(np.int32)
+    del pair_key
     rows, cols = all_keys // Cn, all_keys % Cn
     s_row_ptr = _ptr_from_counts(np.bincount(rows, minlength=Cn))
     s_col = cols.astype(np.int32)
+    s_row = rows.astype(np.int32)
     s_diag = np.searchsorted(all_keys, diag_keys).astype(np.int32)
     s_transpose = np.searchsorted(all_keys, cols * Cn + rows).astype(np.int32)
+    u_block = np.flatnonzero(rows <= cols).astype(np.int32)
+    # items were generated track by track, so a stable sort by block leaves every unit sorted by track
+    order = np.argsort(item_block, kind="stable")
+    item_a, item_b = item_a[order], item_b[order]
+    u_item_ptr = _ptr_from_counts(np.bincount(item_block, minlength=all_keys.shape[0])[u_block])
+    del order, item_block
 
     pose = np.zeros((Cn, 8))
     pose[:, :4] = pr.img_q
@@ -311,7 +327,7 @@ def build_layout(problem: BundleProblem) -> HostLayout:
         img_ptr=img_ptr, cm_pt=np.ascontiguousarray(cm_pt), cm_xy=cm_xy, cm_depth=cm_depth, cm_src=cm_src,
         chunk_img=chunk_img, chunk_begin=chunk_begin, chunk_end=chunk_end, img_chunk_ptr=img_chunk_ptr,
         s_row_ptr=s_row_ptr, s_col=s_col, s_diag=s_diag, s_transpose=s_transpose,
-        pair_ptr=pair_ptr, pair_block=pair_block,
+        s_row=s_row, u_block=u_block, u_item_ptr=u_item_ptr, item_a=item_a, item_b=item_b,
         reproj_loss=int(pr.reproj_loss), depth_loss=int(pr.depth_loss),
         reproj_loss_scale=float(pr.reproj_loss_scale), reproj_loss_weight=float(pr.reproj_loss_weight),
         flags=FLAG_STRUCTURE_ONLY if structure_only else 0,
@@ -325,7 +341,7 @@ _DEVICE_FIELDS = (
     "img_pose", "img_camera", "img_free_mask", "img_shift_scale", "cam_model", "cam_params", "pt_xyz", "pt_const",
     "pt_ptr", "pm_img", "pm_xy", "pm_depth", "pm_src", "img_ptr", "cm_pt", "cm_xy", "cm_depth",
     "chunk_img", "chunk_begin", "chunk_end", "img_chunk_ptr", "s_row_ptr", "s_col", "s_diag", "s_transpose",
-    "pair_ptr", "pair_block",
+    "s_row", "u_block", "u_item_ptr", "item_a", "item_b",
 )
 
 
@@ -372,8 +388,9 @@ class BundleAdjuster:
                     t = t.pin_memory()
                 self.buf[name] = t.to(self.device, non_blocking=pinned)
                 self.h2d_bytes += arr.nbytes
-            if lay.pair_block.shape[0] == 0:
-                self.buf["pair_block"] = torch.zeros(1, dtype=torch.int32, device=self.device)
+            for name in ("item_a", "item_b"):
+                if self.buf[name].numel() == 0:
+                    self.buf[name] = torch.zeros(1, dtype=torch.int32, device=self.device)
             self.handle = C.c_void_p()
             rc = self.lib.mpba_create(C.byref(self.handle), device, None)
             if rc != 0:
@@ -385,6 +402,7 @@ class BundleAdjuster:
                 setattr(self.prob, name, self.buf[name].data_ptr())
             self.prob.num_chunks = lay.num_chunks
             self.prob.num_blocks = lay.num_blocks
+            self.prob.num_upper = int(lay.u_block.shape[0])
             self.prob.reproj_loss, self.prob.depth_loss = lay.reproj_loss, lay.depth_loss
             self.prob.reproj_loss_scale, self.prob.reproj_loss_weight = lay.reproj_loss_scale, lay.reproj_loss_weight
             self.prob.flags = lay.flags

@@ -78,18 +78,23 @@ def test_layout_orders_and_structure(seed):
     assert all((j, i) in keys for i, j in keys)
     assert all(lay.s_col[lay.s_diag[i]] == i and rows[lay.s_diag[i]] == i for i in range(Cn))
     assert np.array_equal(rows[lay.s_transpose], lay.s_col) and np.array_equal(lay.s_col[lay.s_transpose], rows)
+    assert np.array_equal(lay.s_row, rows)
+    # Schur work lists: one unit per upper block; every (track, a <= b) pair of a variable point appears
+    # exactly once, in the unit of block (img_a, img_b), sorted by track inside the unit
+    assert np.array_equal(lay.u_block, np.flatnonzero(rows <= lay.s_col))
+    expect = set()
     for p in range(P):
-        imgs = lay.pm_img[lay.pt_ptr[p]:lay.pt_ptr[p + 1]]
         if prob.pt_const[p]:
-            assert lay.pair_ptr[p + 1] == lay.pair_ptr[p]
             continue
-        k = lay.pair_ptr[p]
-        for a in range(len(imgs)):
-            for b in range(a, len(imgs)):
-                blk = lay.pair_block[k]
-                assert rows[blk] == imgs[a] and lay.s_col[blk] == imgs[b]
-                k += 1
-        assert k == lay.pair_ptr[p + 1]
+        for a in range(lay.pt_ptr[p], lay.pt_ptr[p + 1]):
+            for b in range(a, lay.pt_ptr[p + 1]):
+                expect.add((a, b))
+    got = set(zip(lay.item_a.tolist(), lay.item_b.tolist()))
+    assert got == expect and len(lay.item_a) == len(expect)
+    for u, blk in enumerate(lay.u_block):
+        sl = slice(lay.u_item_ptr[u], lay.u_item_ptr[u + 1])
+        assert np.all(lay.pm_img[lay.item_a[sl]] == rows[blk]) and np.all(lay.pm_img[lay.item_b[sl]] == lay.s_col[blk])
+        assert np.all(np.diff(lay.item_a[sl]) >= 0)
 
 
 def test_layout_edge_cases():
