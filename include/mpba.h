@@ -124,7 +124,7 @@ typedef struct mpba_problem {
    * bundle_adjustment.py:276-283) -- the normal equations are block diagonal in the points and
    * the reduced camera system is skipped */
   int32_t flags;
-  int32_t reserved;
+  int32_t s_max_row_blocks;     /* max blocks in one row of S (0 = unknown): sizes the PCG's shared-memory staging */
 } mpba_problem;
 
 #define MPBA_FLAG_STRUCTURE_ONLY 1

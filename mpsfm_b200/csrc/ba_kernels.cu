@@ -517,20 +517,29 @@ __global__ void __launch_bounds__(128) k_block_inverse(ProblemView pv, const dou
 }
 
 // ---- persistent cooperative PCG on the block-CSR reduced camera system --------------------------
+// Block-Jacobi preconditioned conjugate gradients, one launch per linear solve.  The system is small
+// (6C unknowns, a few MB of 6x6 blocks) and the solve is latency bound, so the kernel is built around
+// the cost of a grid-wide exchange:
+//   * each CTA owns a contiguous range of block rows and keeps everything row-local in shared memory
+//     for the whole solve: its blocks of S and their column indices (when they fit; L2 otherwise), its
+//     rows of M^-1 and of x, r, q.  Per iteration only z and p cross CTAs (L2, ld.cg / st.cg),
+//   * two grid barriers per iteration instead of three: p <- z + beta p is never published, every CTA
+//     rebuilds the entries of p it gathers from z and the previous p (double buffered),
+//   * a barrier is one atomic arrive + spin on a monotonic counter; the dot-product partials ride on
+//     it through per-CTA slots that every CTA then sums in the same fixed order (deterministic).
 struct PcgArgs {
-  int C;
+  int C, rows_per_cta, max_local_blocks;
   const int32_t* row_ptr;
   const int32_t* col;
   const double* S;
   const double* Minv;
   const double* rhs;
   double* x;
-  double* r;
   double* z;
   double* p0;
   double* p1;
-  double* q;
   double* partial;  // [2][gridDim.x]
+  unsigned* bar;    // zeroed before the launch
   double* scal;
   double tol;
   int max_iter;
@@ -538,78 +547,128 @@ struct PcgArgs {
 
 constexpr int PCG_THREADS = 256;
 
-__device__ __forceinline__ double grid_sum(cg::grid_group& grid, double part, double* partial_buf, double* sm) {
+__device__ __forceinline__ double grid_reduce(double part, double* slots, unsigned* bar, unsigned& gen, double* sm) {
   const double b = block_sum<PCG_THREADS / 32>(part, sm);
-  if (threadIdx.x == 0) partial_buf[blockIdx.x] = b;
-  grid.sync();
+  gen += gridDim.x;
+  if (threadIdx.x == 0) {
+    __stcg(slots + blockIdx.x, b);
+    __threadfence();
+    atomicAdd(bar, 1u);
+    while (*reinterpret_cast<volatile unsigned*>(bar) < gen) {
+    }
+  }
+  __syncthreads();
   double v = 0.0;
-  for (int i = threadIdx.x; i < (int)gridDim.x; i += PCG_THREADS) v += partial_buf[i];
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += PCG_THREADS) v += __ldcg(slots + i);
   return block_sum<PCG_THREADS / 32>(v, sm);
 }
 
+__device__ __forceinline__ void ldcg6(const double* p, double (&v)[6]) {
+  const double2* s = reinterpret_cast<const double2*>(p);
+  const double2 a = __ldcg(s), b = __ldcg(s + 1), c = __ldcg(s + 2);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y;
+}
+
+template <bool SMEM>
 __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
-  cg::grid_group grid = cg::this_grid();
+  extern __shared__ double s_dyn[];
   __shared__ double sm[PCG_THREADS / 32 + 1];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int wpb = PCG_THREADS / 32;
-  const int gw = blockIdx.x * wpb + warp, nw = gridDim.x * wpb;
+  constexpr int WPB = PCG_THREADS / 32;
+  const int row0 = min(A.C, (int)blockIdx.x * A.rows_per_cta);
+  const int row1 = min(A.C, row0 + A.rows_per_cta);
+  const int nrows = row1 - row0;
+  const int blk_base = A.row_ptr[row0];
+  const int nblk = A.row_ptr[row1] - blk_base;
+  // shared memory carve: Minv | x | r | q | rowptr | [S | col]
+  double* s_minv = s_dyn;
+  double* s_x = s_minv + (size_t)A.rows_per_cta * 36;
+  double* s_r = s_x + (size_t)A.rows_per_cta * 6;
+  double* s_q = s_r + (size_t)A.rows_per_cta * 6;
+  int* s_rowptr = reinterpret_cast<int*>(s_q + (size_t)A.rows_per_cta * 6);
+  double* s_S = reinterpret_cast<double*>(s_rowptr + ((A.rows_per_cta + 2) & ~1));
+  int* s_col = reinterpret_cast<int*>(s_S + (SMEM ? (size_t)A.max_local_blocks * 36 : 0));
+
+  for (int k = threadIdx.x; k < nrows * 36; k += PCG_THREADS) s_minv[k] = A.Minv[(size_t)row0 * 36 + k];
+  for (int k = threadIdx.x; k <= nrows; k += PCG_THREADS) s_rowptr[k] = A.row_ptr[row0 + k] - blk_base;
+  if (SMEM) {
+    const double* src = A.S + (size_t)blk_base * 36;
+    for (int k = threadIdx.x; k < nblk * 36; k += PCG_THREADS) s_S[k] = src[k];
+    for (int k = threadIdx.x; k < nblk; k += PCG_THREADS) s_col[k] = A.col[blk_base + k];
+  }
+  __syncthreads();
+  const double* Sbase = SMEM ? s_S : (A.S + (size_t)blk_base * 36);
+  const int* colbase = SMEM ? s_col : (A.col + blk_base);
+
   double* part0 = A.partial;
   double* part1 = A.partial + gridDim.x;
   const int r6 = lane % 6, kb0 = lane / 6;
+  unsigned gen = 0;
+  long long t_spmv = 0, t_red = 0, t_upd = 0;
 
-  // x = 0, r = b, z = M^-1 r, p = z
+  // x = 0, r = b, z = M^-1 r, p_old = 0
   double part = 0.0;
-  for (int row = gw; row < A.C; row += nw) {
+  for (int lr = warp; lr < nrows; lr += WPB) {
+    const int row = row0 + lr;
     const double rr = lane < 6 ? A.rhs[(size_t)row * 6 + lane] : 0.0;
     double zz = 0.0;
 #pragma unroll
     for (int c = 0; c < 6; ++c) {
       const double rc = __shfl_sync(FULL, rr, c);
-      if (lane < 6) zz += A.Minv[(size_t)row * 36 + lane * 6 + c] * rc;
+      if (lane < 6) zz += s_minv[lr * 36 + lane * 6 + c] * rc;
     }
     if (lane < 6) {
-      A.x[(size_t)row * 6 + lane] = 0.0;
-      A.r[(size_t)row * 6 + lane] = rr;
-      A.z[(size_t)row * 6 + lane] = zz;
-      A.p0[(size_t)row * 6 + lane] = zz;
+      s_x[lr * 6 + lane] = 0.0;
+      s_r[lr * 6 + lane] = rr;
+      __stcg(A.z + (size_t)row * 6 + lane, zz);
+      __stcg(A.p0 + (size_t)row * 6 + lane, 0.0);
       part += rr * zz;
     }
   }
-  const double rz0 = grid_sum(grid, part, part1, sm);
-  double rz = rz0;
+  const double rz0 = grid_reduce(part, part1, A.bar, gen, sm);
+  double rz = rz0, beta = 0.0;
   int iters = 0, flag = 1;
   double res = 1.0;
   if (!(rz0 > 0.0) || !isfinite(rz0)) {
     flag = (rz0 == 0.0) ? 0 : 2;
     res = 0.0;
   } else {
-    double* pc = A.p0;
-    double* pn = A.p1;
+    double* pold = A.p0;
+    double* pnew = A.p1;
     for (int it = 0; it < A.max_iter; ++it) {
-      // q = S p, p'q
+      const long long c0 = clock64();
+      // p = z + beta p_old (rebuilt where gathered); q = S p; p'q
       part = 0.0;
-      for (int row = gw; row < A.C; row += nw) {
-        const int b0 = A.row_ptr[row], b1 = A.row_ptr[row + 1];
+      for (int lr = warp; lr < nrows; lr += WPB) {
+        const int row = row0 + lr;
+        const int b0 = s_rowptr[lr], b1 = s_rowptr[lr + 1];
         double acc = 0.0;
         if (lane < 30) {
+#pragma unroll 4
           for (int blk = b0 + kb0; blk < b1; blk += 5) {
-            const int col = __ldg(A.col + blk);
-            const double2* Sb = reinterpret_cast<const double2*>(A.S + (size_t)blk * 36 + r6 * 6);
-            const double2* pcol = reinterpret_cast<const double2*>(pc + (size_t)col * 6);
-            const double2 s0 = Sb[0], s1 = Sb[1], s2 = Sb[2];
-            const double2 v0 = pcol[0], v1 = pcol[1], v2 = pcol[2];
-            acc += s0.x * v0.x + s0.y * v0.y + s1.x * v1.x + s1.y * v1.y + s2.x * v2.x + s2.y * v2.y;
+            const int col = colbase[blk];
+            double zc[6], pc[6];
+            ldcg6(A.z + (size_t)col * 6, zc);
+            ldcg6(pold + (size_t)col * 6, pc);
+            const double* Sb = Sbase + (size_t)blk * 36 + r6 * 6;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) acc += Sb[c] * (zc[c] + beta * pc[c]);
           }
         }
         const double a1 = __shfl_sync(FULL, acc, r6 + 6), a2 = __shfl_sync(FULL, acc, r6 + 12),
                      a3 = __shfl_sync(FULL, acc, r6 + 18), a4 = __shfl_sync(FULL, acc, r6 + 24);
         if (lane < 6) {
+          const size_t o = (size_t)row * 6 + lane;
           const double qv = acc + a1 + a2 + a3 + a4;
-          A.q[(size_t)row * 6 + lane] = qv;
-          part += pc[(size_t)row * 6 + lane] * qv;
+          const double pi = __ldcg(A.z + o) + beta * __ldcg(pold + o);
+          __stcg(pnew + o, pi);
+          s_q[lr * 6 + lane] = qv;
+          part += pi * qv;
         }
       }
-      const double pq = grid_sum(grid, part, part0, sm);
+      const long long c1 = clock64();
+      const double pq = grid_reduce(part, part0, A.bar, gen, sm);
+      const long long c2 = clock64();
       if (!(pq > 0.0) || !isfinite(pq)) {
         flag = 2;
         break;
@@ -617,26 +676,32 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
       const double alpha = rz / pq;
       // x += alpha p, r -= alpha q, z = M^-1 r
       part = 0.0;
-      for (int row = gw; row < A.C; row += nw) {
+      for (int lr = warp; lr < nrows; lr += WPB) {
+        const int row = row0 + lr;
         double rr = 0.0;
         if (lane < 6) {
           const size_t o = (size_t)row * 6 + lane;
-          A.x[o] += alpha * pc[o];
-          rr = A.r[o] - alpha * A.q[o];
-          A.r[o] = rr;
+          s_x[lr * 6 + lane] += alpha * __ldcg(pnew + o);
+          rr = s_r[lr * 6 + lane] - alpha * s_q[lr * 6 + lane];
+          s_r[lr * 6 + lane] = rr;
         }
         double zz = 0.0;
 #pragma unroll
         for (int c = 0; c < 6; ++c) {
           const double rc = __shfl_sync(FULL, rr, c);
-          if (lane < 6) zz += A.Minv[(size_t)row * 36 + lane * 6 + c] * rc;
+          if (lane < 6) zz += s_minv[lr * 36 + lane * 6 + c] * rc;
         }
         if (lane < 6) {
-          A.z[(size_t)row * 6 + lane] = zz;
+          __stcg(A.z + (size_t)row * 6 + lane, zz);
           part += rr * zz;
         }
       }
-      const double rz_new = grid_sum(grid, part, part1, sm);
+      const long long c3 = clock64();
+      const double rz_new = grid_reduce(part, part1, A.bar, gen, sm);
+      const long long c4 = clock64();
+      t_spmv += c1 - c0;
+      t_upd += c3 - c2;
+      t_red += (c2 - c1) + (c4 - c3);
       iters = it + 1;
       res = sqrt(fabs(rz_new) / rz0);
       if (!isfinite(rz_new)) {
@@ -647,25 +712,22 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
         flag = 0;
         break;
       }
-      const double beta = rz_new / rz;
+      beta = rz_new / rz;
       rz = rz_new;
-      // p <- z + beta p  (other buffer: readers of the old p may still be in flight elsewhere)
-      for (int row = gw; row < A.C; row += nw) {
-        if (lane < 6) {
-          const size_t o = (size_t)row * 6 + lane;
-          pn[o] = A.z[o] + beta * pc[o];
-        }
-      }
-      double* t = pc;
-      pc = pn;
-      pn = t;
-      grid.sync();
+      double* t = pold;
+      pold = pnew;
+      pnew = t;
     }
   }
+  for (int lr = warp; lr < nrows; lr += WPB)
+    if (lane < 6) A.x[(size_t)(row0 + lr) * 6 + lane] = s_x[lr * 6 + lane];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     A.scal[S_PCG_ITERS] = (double)iters;
     A.scal[S_PCG_FLAG] = (double)flag;
     A.scal[S_PCG_RES] = res;
+    A.scal[S_PCG_CYC_SPMV] = (double)t_spmv;
+    A.scal[S_PCG_CYC_REDUCE] = (double)t_red;
+    A.scal[S_PCG_CYC_UPDATE] = (double)t_upd;
   }
 }
 
@@ -872,25 +934,43 @@ void launch_schur_blocks(const ProblemView& pv, const double* fac, const double*
   k_schur_blocks<<<pv.U, SB_THREADS, 0, st>>>(pv, fac, Hc, gc, c_img, lm, S, rhs);
   k_block_inverse<<<(pv.C + 127) / 128, 128, 0, st>>>(pv, S, Minv);
 }
-int pcg_grid(int device, int C) {
-  int sms = 0, per_sm = 0;
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg, PCG_THREADS, 0);
-  if (per_sm < 1) per_sm = 1;
-  const int want = (C + (PCG_THREADS / 32) - 1) / (PCG_THREADS / 32);
-  int grid = want < sms ? want : sms;  // one CTA per SM at most: grid.sync cost grows with the CTA count
+PcgPlan pcg_plan(int device, int C, int max_row_blocks) {
+  static int sms = 0, smem_optin = 0;
+  if (!sms) {
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    cudaFuncSetAttribute(k_pcg<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 1024);
+    cudaFuncSetAttribute(k_pcg<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 1024);
+  }
+  PcgPlan pl;
+  const int wpb = PCG_THREADS / 32;
+  int grid = (C + wpb - 1) / wpb;  // at least one block row per warp
+  if (grid > sms) grid = sms;      // one CTA per SM: co-residency for the grid barrier
   if (grid < 1) grid = 1;
-  return grid;
+  pl.rows_per_cta = (C + grid - 1) / grid;
+  pl.grid = (C + pl.rows_per_cta - 1) / pl.rows_per_cta;
+  const size_t rows = (size_t)pl.rows_per_cta;
+  const size_t base = rows * (36 + 18) * sizeof(double) + ((rows + 2) & ~(size_t)1) * sizeof(int);
+  pl.max_local_blocks = (int)(rows * (size_t)(max_row_blocks > 0 ? max_row_blocks : 1 << 16));
+  const size_t with_s = base + (size_t)pl.max_local_blocks * (36 * sizeof(double) + sizeof(int)) + 16;
+  pl.use_smem = (max_row_blocks > 0 && with_s <= (size_t)(smem_optin - 1024)) ? 1 : 0;
+  pl.smem_bytes = pl.use_smem ? with_s : base + 16;
+  return pl;
 }
-cudaError_t launch_pcg(const ProblemView& pv, const double* S, const double* Minv, const double* rhs, double* y,
-                       double* vec_r, double* vec_z, double* vec_p0, double* vec_p1, double* vec_q, double* partial,
-                       double* scal, double tol, int max_iter, int grid, cudaStream_t st) {
+cudaError_t launch_pcg(const ProblemView& pv, const PcgPlan& pl, const double* S, const double* Minv, const double* rhs,
+                       double* y, double* vec_z, double* vec_p0, double* vec_p1, double* partial, unsigned* bar,
+                       double* scal, double tol, int max_iter, cudaStream_t st) {
   PcgArgs a;
-  a.C = pv.C; a.row_ptr = pv.s_row_ptr; a.col = pv.s_col; a.S = S; a.Minv = Minv; a.rhs = rhs; a.x = y;
-  a.r = vec_r; a.z = vec_z; a.p0 = vec_p0; a.p1 = vec_p1; a.q = vec_q; a.partial = partial; a.scal = scal;
+  a.C = pv.C; a.rows_per_cta = pl.rows_per_cta; a.max_local_blocks = pl.max_local_blocks;
+  a.row_ptr = pv.s_row_ptr; a.col = pv.s_col; a.S = S; a.Minv = Minv; a.rhs = rhs; a.x = y;
+  a.z = vec_z; a.p0 = vec_p0; a.p1 = vec_p1; a.partial = partial; a.bar = bar; a.scal = scal;
   a.tol = tol; a.max_iter = max_iter;
+  cudaError_t e = cudaMemsetAsync(bar, 0, sizeof(unsigned), st);
+  if (e != cudaSuccess) return e;
   void* args[] = {&a};
-  return cudaLaunchCooperativeKernel((void*)k_pcg, dim3(grid), dim3(PCG_THREADS), args, 0, st);
+  if (pl.use_smem)
+    return cudaLaunchCooperativeKernel((void*)k_pcg<true>, dim3(pl.grid), dim3(PCG_THREADS), args, pl.smem_bytes, st);
+  return cudaLaunchCooperativeKernel((void*)k_pcg<false>, dim3(pl.grid), dim3(PCG_THREADS), args, pl.smem_bytes, st);
 }
 void launch_cam_update(const ProblemView& pv, const double* pose, const double* y, double* pose_cand, double* scal,
                        cudaStream_t st) {

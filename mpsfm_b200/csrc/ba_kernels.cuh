@@ -23,6 +23,7 @@ enum Scal {
   S_PCG_FLAG = 10,   // 0 converged, 1 iteration cap, 2 breakdown (p'Sp <= 0 or non-finite)
   S_PCG_RES = 11,    // final sqrt(r'M^-1 r / b'M^-1 b)
   S_BAD_POINTS = 12, // number of point blocks whose damped Hpp was not positive definite
+  S_PCG_CYC_SPMV = 13, S_PCG_CYC_REDUCE = 14, S_PCG_CYC_UPDATE = 15,  // SM cycles CTA 0 spent per phase
   S_COUNT = 16
 };
 
@@ -85,11 +86,15 @@ void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaS
 // ---- reduced camera system ----------------------------------------------------------------------
 void launch_schur_blocks(const ProblemView& pv, const double* fac, const double* Hc, const double* gc,
                          const double* c_img, LmDiag lm, double* S, double* rhs, double* Minv, cudaStream_t st);
+struct PcgPlan {
+  int grid, rows_per_cta, use_smem, max_local_blocks;
+  size_t smem_bytes;
+};
+PcgPlan pcg_plan(int device, int C, int max_row_blocks);
 // returns cudaError from the cooperative launch
-cudaError_t launch_pcg(const ProblemView& pv, const double* S, const double* Minv, const double* rhs, double* y,
-                       double* vec_r, double* vec_z, double* vec_p0, double* vec_p1, double* vec_q, double* partial,
-                       double* scal, double tol, int max_iter, int grid, cudaStream_t st);
-int pcg_grid(int device, int C);
+cudaError_t launch_pcg(const ProblemView& pv, const PcgPlan& pl, const double* S, const double* Minv, const double* rhs,
+                       double* y, double* vec_z, double* vec_p0, double* vec_p1, double* partial, unsigned* bar,
+                       double* scal, double tol, int max_iter, cudaStream_t st);
 
 // ---- step ---------------------------------------------------------------------------------------
 void launch_cam_update(const ProblemView& pv, const double* pose, const double* y, double* pose_cand, double* scal,

@@ -137,7 +137,7 @@ void carve(const mpba_problem* p, char* base, Workspace& w) {
   w.vp0 = take(C * 6);
   w.vp1 = take(C * 6);
   w.vq = take(C * 6);
-  w.partial = take(2 * 2048);
+  w.partial = take(2 * 2048 + 32);
   w.pt_part = take(nblk * PT_PART + 8);
   w.scal = take(S_COUNT);
   w.bytes = off;
@@ -187,6 +187,7 @@ struct Ctx {
   Workspace w;
   int nblk;
   int structure_only;
+  int max_row_blocks;
 };
 
 int begin(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes, Ctx& c) {
@@ -203,6 +204,7 @@ int begin(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t work
   carve(prob, static_cast<char*>(workspace), c.w);
   c.nblk = points_grid(prob->num_points);
   c.structure_only = prob->flags & MPBA_FLAG_STRUCTURE_ONLY;
+  c.max_row_blocks = prob->s_max_row_blocks;
   h->launch_count = 0;
   return MPBA_OK;
 }
@@ -253,9 +255,10 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
     }
     {
       Timer t(h, KS_PCG);
-      const int grid = pcg_grid(h->device, c.pv.C);
-      cudaError_t e = launch_pcg(c.pv, c.w.S, c.w.Minv, c.w.rhs, c.w.y, c.w.vr, c.w.vz, c.w.vp0, c.w.vp1, c.w.vq,
-                                 c.w.partial, c.w.scal, opt->pcg_tolerance, opt->pcg_max_iterations, grid, h->stream);
+      const PcgPlan pl = pcg_plan(h->device, c.pv.C, c.max_row_blocks);
+      cudaError_t e = launch_pcg(c.pv, pl, c.w.S, c.w.Minv, c.w.rhs, c.w.y, c.w.vz, c.w.vp0, c.w.vp1,
+                                 c.w.partial, reinterpret_cast<unsigned*>(c.w.partial + 2 * 2048), c.w.scal,
+                                 opt->pcg_tolerance, opt->pcg_max_iterations, h->stream);
       if (e != cudaSuccess) return fail(h, MPBA_E_CUDA, std::string("cooperative PCG launch: ") + cudaGetErrorString(e));
     }
   } else {
@@ -595,6 +598,9 @@ int mpba_solve(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t
       it.trust_region_radius = radius;
       push(it);
     }
+    if (opt.verbose > 1)
+      fprintf(stderr, "[mpba]     pcg cycles on CTA 0: spmv %.0f reduce %.0f update %.0f (%d iterations)\n",
+              s[S_PCG_CYC_SPMV], s[S_PCG_CYC_REDUCE], s[S_PCG_CYC_UPDATE], (int)s[S_PCG_ITERS]);
     if (opt.verbose)
       fprintf(stderr, "[mpba] %3d cost %.9e dcost %.3e |step| %.3e rho %.3e radius %.3e pcg %d (%s)\n", iteration,
               last.cost, last.cost_change, last.step_norm, last.relative_decrease, last.trust_region_radius,

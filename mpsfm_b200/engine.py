@@ -65,7 +65,7 @@ class MpbaProblem(C.Structure):
         ("u_block", C.c_void_p), ("u_item_ptr", C.c_void_p), ("item_a", C.c_void_p), ("item_b", C.c_void_p),
         ("reproj_loss", C.c_int32), ("depth_loss", C.c_int32),
         ("reproj_loss_scale", C.c_double), ("reproj_loss_weight", C.c_double),
-        ("flags", C.c_int32), ("reserved", C.c_int32),
+        ("flags", C.c_int32), ("s_max_row_blocks", C.c_int32),
     ]
 
 
@@ -406,6 +406,7 @@ class BundleAdjuster:
             self.prob.reproj_loss, self.prob.depth_loss = lay.reproj_loss, lay.depth_loss
             self.prob.reproj_loss_scale, self.prob.reproj_loss_weight = lay.reproj_loss_scale, lay.reproj_loss_weight
             self.prob.flags = lay.flags
+            self.prob.s_max_row_blocks = int(np.max(np.diff(lay.s_row_ptr))) if lay.C else 0
             nbytes = C.c_size_t()
             self._check(self.lib.mpba_workspace_bytes(C.byref(self.prob), C.byref(nbytes)))
             self.workspace = torch.empty(max(int(nbytes.value), 256), dtype=torch.uint8, device=self.device)
