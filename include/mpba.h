@@ -150,6 +150,9 @@ typedef struct mpba_options {
   double pcg_tolerance;                    /* 1e-12: stop when sqrt(r'M^-1 r / b'M^-1 b) <= tol */
   int32_t profile;                         /* 1: CUDA-event time every kernel launch (see mpba_kernel_times) */
   int32_t verbose;
+  int32_t pcg_kernel;                      /* 0: automatic (cluster-resident when S fits one 16-CTA cluster,
+                                              grid-wide otherwise), 1: force grid-wide, 2: prefer cluster */
+  int32_t reserved;
 } mpba_options;
 
 /* ceres::IterationSummary subset, one row per LM iteration (row 0 = initial evaluation) */

@@ -24,7 +24,8 @@ enum Scal {
   S_PCG_RES = 11,    // final sqrt(r'M^-1 r / b'M^-1 b)
   S_BAD_POINTS = 12, // number of point blocks whose damped Hpp was not positive definite
   S_PCG_CYC_SPMV = 13, S_PCG_CYC_REDUCE = 14, S_PCG_CYC_UPDATE = 15,  // SM cycles CTA 0 spent per phase
-  S_COUNT = 16
+  S_PCG_CYC_DETAIL = 16,  // 7 slots: cluster PCG cycles of CTA 0: sync A, halo, products, sync B, row sums, sync C, update
+  S_COUNT = 24
 };
 
 constexpr int MPBA_MAX_PRM = 12;
@@ -95,6 +96,49 @@ PcgPlan pcg_plan(int device, int C, int max_row_blocks);
 cudaError_t launch_pcg(const ProblemView& pv, const PcgPlan& pl, const double* S, const double* Minv, const double* rhs,
                        double* y, double* vec_z, double* vec_p0, double* vec_p1, double* partial, unsigned* bar,
                        double* scal, double tol, int max_iter, cudaStream_t st);
+
+// cluster-resident PCG (pcg_cluster.cu): one thread-block cluster of `cl` CTAs, upper blocks of S in
+// registers, exchanges through distributed shared memory.  The plan arrays are built on the host from
+// the block-CSR structure (ba_solver.cu: build_pcg_cluster_plan) and live in the workspace.
+constexpr int PCGC_THREADS = 384;
+// shared-memory carve of k_pcg_cluster as 32-bit offsets from the dynamic base (doubles; the last three in
+// ints): kept in the kernel argument block = constant bank, so they cost no registers next to the 6x6
+// block of S every thread holds
+struct PcgClusterCarve {
+  int dep, x, r, u, p, s, w, minv, sdiag, halo, extra, parts, red;
+  int rp;     // row pointers of the owned rows, relative to the first owned full block
+  int hdesc;  // halo source: owner CTA << 20 | local row at the owner
+  int xmeta;  // spilled blocks: rowl, halo, depA, tcta, tidx
+};
+struct PcgClusterArgs {
+  int C;
+  PcgClusterCarve m;
+  int max_rows, max_full, max_halo, max_extra;  // per-CTA maxima: uniform shared-memory layout across the cluster
+  const int32_t* row_ptr;       // [C+1] block-CSR row pointers of S (problem)
+  const int32_t* s_diag;        // [C]   block index of the diagonal block of every row (problem)
+  const int32_t* cta_row_ptr;   // [cl+1] rows owned by CTA k
+  const int32_t* cta_blk_ptr;   // [cl+1] upper blocks of CTA k in the ub_* arrays
+  const int32_t* cta_halo_ptr;  // [cl+1]
+  const int32_t* ub_sblk;       // block index in S
+  const int32_t* ub_rowl;       // row of the block, local to its CTA
+  const int32_t* ub_halo;       // halo slot holding u of the block's column
+  const int32_t* ub_depA;       // deposit slot (local) of S_ij u_j
+  const int32_t* ub_tcta;       // CTA owning row j
+  const int32_t* ub_tidx;       // deposit slot of S_ij^T u_i at that CTA
+  const int32_t* halo_cta;      // owner CTA of the halo row
+  const int32_t* halo_rowl;     // its local row index there
+  const double* S;
+  const double* Minv;
+  const double* rhs;
+  double* x;
+  double* scal;
+  double tol;
+  int max_iter;
+};
+size_t pcg_cluster_carve(PcgClusterArgs& a);  // fills a.m from the maxima, returns the dynamic shared-memory bytes
+int pcg_cluster_max_smem(int device);
+bool pcg_cluster_fits(int device, int cl, size_t smem_bytes);
+cudaError_t launch_pcg_cluster(const PcgClusterArgs& a, int cl, size_t smem_bytes, cudaStream_t st);
 
 // ---- step ---------------------------------------------------------------------------------------
 void launch_cam_update(const ProblemView& pv, const double* pose, const double* y, double* pose_cand, double* scal,

@@ -13,6 +13,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <algorithm>
 #include <string>
 #include <vector>
 
@@ -47,6 +48,8 @@ struct mpba_handle {
   int64_t launch_count = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int pcg_grid_sms = 0;
+  int32_t* h_stage = nullptr;  // pinned staging for the PCG cluster plan
+  size_t h_stage_ints = 0;
 };
 
 namespace {
@@ -101,8 +104,15 @@ size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 struct Workspace {
   double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *img_part, *c_img, *c_pt, *Hpp, *gp, *Hinv, *fac, *S,
       *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal;
+  int32_t* plan = nullptr;  // PCG cluster plan (pcg_cluster.cu)
+  size_t plan_ints = 0;
   size_t bytes = 0;
 };
+
+size_t plan_capacity_ints(const mpba_problem* p) {
+  if (p->flags & MPBA_FLAG_STRUCTURE_ONLY) return 0;
+  return 8 * (size_t)p->num_upper + 3 * 17 + 64;
+}
 
 // bump allocation; base == nullptr just measures
 void carve(const mpba_problem* p, char* base, Workspace& w) {
@@ -140,6 +150,8 @@ void carve(const mpba_problem* p, char* base, Workspace& w) {
   w.partial = take(2 * 2048 + 32);
   w.pt_part = take(nblk * PT_PART + 8);
   w.scal = take(S_COUNT);
+  w.plan_ints = plan_capacity_ints(p);
+  w.plan = reinterpret_cast<int32_t*>(take((w.plan_ints + 1) / 2));
   w.bytes = off;
 }
 
@@ -188,6 +200,10 @@ struct Ctx {
   int nblk;
   int structure_only;
   int max_row_blocks;
+  // cluster PCG plan for this call (built by build_pcg_cluster_plan); cl == 0: use the grid kernel
+  int cl = 0;
+  size_t cl_smem = 0;
+  PcgClusterArgs cla;
 };
 
 int begin(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes, Ctx& c) {
@@ -233,6 +249,152 @@ int fetch_scalars(Ctx& c) {
   return MPBA_OK;
 }
 
+// Partition the block rows of S over the CTAs of one cluster and lay out the deposit / halo slots of
+// the cluster-resident PCG (pcg_cluster.cu).  Runs once per C-ABI call on the host: it needs the
+// block-CSR structure (two small device-to-host copies), costs O(num_blocks) and uploads ~8 ints per
+// upper block.  Leaves c.cl == 0 when the system does not fit one cluster (the grid kernel is used).
+int build_pcg_cluster_plan(Ctx& c, const mpba_problem* prob, int pcg_kernel) {
+  mpba_handle* h = c.h;
+  c.cl = 0;
+  if (c.structure_only || pcg_kernel == 1) return MPBA_OK;
+  const int C = prob->num_images, B = prob->num_blocks;
+  std::vector<int32_t> rp(C + 1), col(B);
+  CU(cudaMemcpyAsync(rp.data(), prob->s_row_ptr, (C + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaMemcpyAsync(col.data(), prob->s_col, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  if (rp[0] != 0 || rp[C] != B) return fail(h, MPBA_E_INVALID, "s_row_ptr does not span num_blocks");
+  std::vector<int> nup(C, 0);
+  int U = 0;
+  for (int i = 0; i < C; ++i) {
+    for (int b = rp[i]; b < rp[i + 1]; ++b) {
+      if (col[b] < 0 || col[b] >= C) return fail(h, MPBA_E_INVALID, "s_col out of range");
+      if (col[b] > i) ++nup[i];  // strictly upper: the diagonal block is applied by the row owner
+    }
+    U += nup[i];
+  }
+  if ((size_t)(8 * (size_t)U + 3 * 17 + 64) > c.w.plan_ints) return MPBA_OK;  // inconsistent num_upper: stay on the grid kernel
+
+  const int max_smem = pcg_cluster_max_smem(h->device);
+  for (int cl = 1; cl <= 16; cl *= 2) {
+    // contiguous rows, balanced by upper-block count
+    std::vector<int> crow(cl + 1, C);
+    crow[0] = 0;
+    {
+      const double target = (double)(U + C) / cl;  // weight of a row: its upper blocks + 1 (row work)
+      int k = 1;
+      long long acc = 0;
+      for (int i = 0; i < C && k < cl; ++i) {
+        acc += nup[i] + 1;
+        while (k < cl && acc >= target * k) crow[k++] = i + 1;
+      }
+    }
+    std::vector<int> owner(C);
+    for (int k = 0; k < cl; ++k)
+      for (int i = crow[k]; i < crow[k + 1]; ++i) owner[i] = k;
+    int max_rows = 1, max_full = 1, max_blk = 0;
+    for (int k = 0; k < cl; ++k) {
+      max_rows = std::max(max_rows, crow[k + 1] - crow[k]);
+      max_full = std::max(max_full, rp[crow[k + 1]] - rp[crow[k]]);
+      int nb = 0;
+      for (int i = crow[k]; i < crow[k + 1]; ++i) nb += nup[i];
+      max_blk = std::max(max_blk, nb);
+    }
+    if (max_blk > PCGC_THREADS && cl < 16) continue;  // prefer every block in registers
+    if (max_rows >= (1 << 20)) return MPBA_OK;
+    // halo lists and block records
+    std::vector<int32_t> cta_blk(cl + 1, 0), cta_halo(cl + 1, 0);
+    std::vector<int32_t> ub_sblk, ub_rowl, ub_halo, ub_depA, ub_tcta, ub_tidx, halo_cta, halo_rowl;
+    ub_sblk.reserve(U);
+    std::vector<int> slot_of(C, -1), touched;
+    int max_halo = 1;
+    for (int k = 0; k < cl; ++k) {
+      touched.clear();
+      const int full0 = rp[crow[k]];
+      for (int i = crow[k]; i < crow[k + 1]; ++i) {
+        for (int b = rp[i]; b < rp[i + 1]; ++b) {
+          const int j = col[b];
+          if (j <= i) continue;
+          if (slot_of[j] < 0) {
+            slot_of[j] = (int)touched.size();
+            touched.push_back(j);
+            halo_cta.push_back(owner[j]);
+            halo_rowl.push_back(j - crow[owner[j]]);
+          }
+          ub_sblk.push_back(b);
+          ub_rowl.push_back(i - crow[k]);
+          ub_halo.push_back(slot_of[j]);
+          ub_depA.push_back(b - full0);
+          {
+            // slot of column i in the full row j
+            const int32_t* lo = col.data() + rp[j];
+            const int32_t* hi = col.data() + rp[j + 1];
+            const int32_t* it = std::lower_bound(lo, hi, (int32_t)i);
+            if (it == hi || *it != i) return fail(h, MPBA_E_INVALID, "reduced camera system structure is not symmetric");
+            ub_tcta.push_back(owner[j]);
+            ub_tidx.push_back((int)(it - col.data()) - rp[crow[owner[j]]]);
+          }
+        }
+      }
+      for (int j : touched) slot_of[j] = -1;
+      max_halo = std::max(max_halo, (int)touched.size());
+      cta_blk[k + 1] = (int32_t)ub_sblk.size();
+      cta_halo[k + 1] = (int32_t)halo_cta.size();
+    }
+    PcgClusterArgs a;
+    memset(&a, 0, sizeof(a));
+    a.C = C;
+    a.max_rows = max_rows;
+    a.max_full = max_full;
+    a.max_halo = max_halo;
+    a.max_extra = std::max(1, max_blk - PCGC_THREADS);
+    const size_t smem = pcg_cluster_carve(a);
+    if ((int)smem > max_smem || !pcg_cluster_fits(h->device, cl, smem)) {
+      if (cl == 16) return MPBA_OK;
+      continue;
+    }
+    // pack, stage, upload
+    const size_t nU = ub_sblk.size(), nH = halo_cta.size();
+    const size_t total = 3 * (size_t)(cl + 1) + 6 * nU + 2 * nH;
+    if (total > c.w.plan_ints) return MPBA_OK;
+    if (h->h_stage_ints < total) {
+      if (h->h_stage) cudaFreeHost(h->h_stage);
+      h->h_stage = nullptr;
+      h->h_stage_ints = 0;
+      CU(cudaMallocHost(&h->h_stage, total * sizeof(int32_t)));
+      h->h_stage_ints = total;
+    }
+    int32_t* st = h->h_stage;
+    int32_t* dev = c.w.plan;
+    size_t off = 0;
+    auto put = [&](const std::vector<int32_t>& v) -> const int32_t* {
+      if (!v.empty()) memcpy(st + off, v.data(), v.size() * sizeof(int32_t));
+      const int32_t* d = dev + off;
+      off += v.size();
+      return d;
+    };
+    std::vector<int32_t> crow32(crow.begin(), crow.end());
+    a.cta_row_ptr = put(crow32);
+    a.cta_blk_ptr = put(cta_blk);
+    a.cta_halo_ptr = put(cta_halo);
+    a.ub_sblk = put(ub_sblk);
+    a.ub_rowl = put(ub_rowl);
+    a.ub_halo = put(ub_halo);
+    a.ub_depA = put(ub_depA);
+    a.ub_tcta = put(ub_tcta);
+    a.ub_tidx = put(ub_tidx);
+    a.halo_cta = put(halo_cta);
+    a.halo_rowl = put(halo_rowl);
+    CU(cudaMemcpyAsync(dev, st, off * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    a.row_ptr = prob->s_row_ptr;
+    a.s_diag = prob->s_diag;
+    c.cla = a;
+    c.cl = cl;
+    c.cl_smem = smem;
+    return MPBA_OK;
+  }
+  return MPBA_OK;
+}
+
 int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int kset, LmDiag lm, int compute_scaling,
                               const mpba_options* opt, bool want_system) {
   mpba_handle* h = c.h;
@@ -255,11 +417,19 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
     }
     {
       Timer t(h, KS_PCG);
-      const PcgPlan pl = pcg_plan(h->device, c.pv.C, c.max_row_blocks);
-      cudaError_t e = launch_pcg(c.pv, pl, c.w.S, c.w.Minv, c.w.rhs, c.w.y, c.w.vz, c.w.vp0, c.w.vp1,
-                                 c.w.partial, reinterpret_cast<unsigned*>(c.w.partial + 2 * 2048), c.w.scal,
-                                 opt->pcg_tolerance, opt->pcg_max_iterations, h->stream);
-      if (e != cudaSuccess) return fail(h, MPBA_E_CUDA, std::string("cooperative PCG launch: ") + cudaGetErrorString(e));
+      cudaError_t e;
+      if (c.cl > 0) {
+        PcgClusterArgs a = c.cla;
+        a.S = c.w.S; a.Minv = c.w.Minv; a.rhs = c.w.rhs; a.x = c.w.y; a.scal = c.w.scal;
+        a.tol = opt->pcg_tolerance; a.max_iter = opt->pcg_max_iterations;
+        e = launch_pcg_cluster(a, c.cl, c.cl_smem, h->stream);
+      } else {
+        const PcgPlan pl = pcg_plan(h->device, c.pv.C, c.max_row_blocks);
+        e = launch_pcg(c.pv, pl, c.w.S, c.w.Minv, c.w.rhs, c.w.y, c.w.vz, c.w.vp0, c.w.vp1, c.w.partial,
+                       reinterpret_cast<unsigned*>(c.w.partial + 2 * 2048), c.w.scal, opt->pcg_tolerance,
+                       opt->pcg_max_iterations, h->stream);
+      }
+      if (e != cudaSuccess) return fail(h, MPBA_E_CUDA, std::string("PCG launch: ") + cudaGetErrorString(e));
     }
   } else {
     // all poses constant (refine_3d_points, bundle_adjustment.py:276-283): no reduced system, y_c = 0
@@ -297,6 +467,8 @@ void mpba_default_options(mpba_options* o) {
   o->pcg_tolerance = 1e-12;
   o->profile = 0;
   o->verbose = 0;
+  o->pcg_kernel = 0;
+  o->reserved = 0;
 }
 
 int mpba_create(mpba_handle** out, int device, void* cuda_stream) {
@@ -327,6 +499,7 @@ void mpba_destroy(mpba_handle* h) {
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->h_scal) cudaFreeHost(h->h_scal);
+  if (h->h_stage) cudaFreeHost(h->h_stage);
   delete h;
 }
 
@@ -417,6 +590,8 @@ int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspac
   reset_profile(h, 0);
   mpba_options opt;
   if (opt_in) opt = *opt_in; else mpba_default_options(&opt);
+  rc = build_pcg_cluster_plan(c, prob, opt.pcg_kernel);
+  if (rc) return rc;
   launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[0], h->stream);
   enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 1, opt.jacobi_scaling);
   LmDiag lm{radius, opt.min_lm_diagonal, opt.max_lm_diagonal};
@@ -441,6 +616,8 @@ int mpba_solve(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t
   mpba_options opt;
   if (opt_in) opt = *opt_in; else mpba_default_options(&opt);
   reset_profile(h, opt.profile);
+  rc = build_pcg_cluster_plan(c, prob, opt.pcg_kernel);
+  if (rc) return rc;
   mpba_iteration* its = sum->iterations;
   const int cap = its ? sum->capacity : 0;
   int nrows = 0;
@@ -598,9 +775,13 @@ int mpba_solve(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t
       it.trust_region_radius = radius;
       push(it);
     }
-    if (opt.verbose > 1)
+    if (opt.verbose > 1) {
       fprintf(stderr, "[mpba]     pcg cycles on CTA 0: spmv %.0f reduce %.0f update %.0f (%d iterations)\n",
               s[S_PCG_CYC_SPMV], s[S_PCG_CYC_REDUCE], s[S_PCG_CYC_UPDATE], (int)s[S_PCG_ITERS]);
+      if (c.cl > 0)
+        fprintf(stderr, "[mpba]     cluster of %d: syncA %.0f halo %.0f products %.0f syncB %.0f rowsum %.0f syncC %.0f update %.0f\n",
+                c.cl, s[16], s[17], s[18], s[19], s[20], s[21], s[22]);
+    }
     if (opt.verbose)
       fprintf(stderr, "[mpba] %3d cost %.9e dcost %.3e |step| %.3e rho %.3e radius %.3e pcg %d (%s)\n", iteration,
               last.cost, last.cost_change, last.step_norm, last.relative_decrease, last.trust_region_radius,

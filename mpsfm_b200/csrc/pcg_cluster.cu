@@ -1,0 +1,425 @@
+// pcg_cluster.cu -- block-Jacobi PCG on the reduced camera system inside ONE thread-block cluster.
+//
+// The reduced camera system S y = b of a bundle-adjustment problem with up to a few thousand images
+// is small (a few MB of 6x6 blocks) and its conjugate-gradient solve is a chain of ~10^2..10^3
+// dependent iterations: it is bound by the latency of one "exchange + reduce" step, not by bandwidth.
+// The grid-wide variant (k_pcg in ba_kernels.cu) pays ~5 L2 round trips (~0.35 us each) per barrier;
+// here the whole solve runs in a cluster of up to 16 CTAs on one GPC, where an exchange is a
+// distributed-shared-memory access (~215 cycles) and a barrier is barrier.cluster (~380 cycles):
+//
+//   * S is symmetric: only the upper blocks (i <= j) are kept, ONE BLOCK PER THREAD IN REGISTERS
+//     (36 doubles) for the whole solve (further blocks of a CTA spill to shared memory).  Per iteration a
+//     thread forms S_ij u_j for row i and S_ij^T u_i for row j and deposits both 6-vectors into fixed
+//     slots of the row owners' shared memory (local or remote store) -- no atomics, the row sums are
+//     taken in slot (= column) order, so the result is deterministic,
+//   * the recurrences are the single-reduction form of PCG (Chronopoulos & Gear): one SpMV and ONE
+//     fused reduction (gamma = r.u, delta = w.u) per iteration, three cluster barriers in total:
+//         A: u published        -> halo gather, block products, deposits
+//         B: deposits complete  -> w = S u (row sums), partial gamma / delta to every CTA
+//         C: partials complete  -> alpha, beta; p, s, x, r, u = M^-1 r updates (row local)
+//   * every CTA computes the same alpha / beta from the same partials in the same order, so the
+//     termination decision is uniform without a broadcast.
+//
+// Iterates coincide with textbook PCG in exact arithmetic; the iteration count semantics (number of
+// x updates, relative residual sqrt(r'M^-1 r / b'M^-1 b)) are those of k_pcg.
+#include <cooperative_groups.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#include "ba_kernels.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace mpba {
+
+namespace {
+
+constexpr int T = PCGC_THREADS;
+constexpr unsigned FULL = 0xffffffffu;
+
+// a = S v (row product), t = S^T v2 (column product) of one 6x6 row-major block
+__device__ __forceinline__ void block_products(const double (&S)[36], const double (&uj)[6], const double (&ui)[6],
+                                               double (&a)[6], double (&t)[6]) {
+#pragma unroll
+  for (int r = 0; r < 6; ++r) {
+    double acc = 0.0;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) acc += S[6 * r + c] * uj[c];
+    a[r] = acc;
+  }
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    double acc = 0.0;
+#pragma unroll
+    for (int r = 0; r < 6; ++r) acc += S[6 * r + c] * ui[r];
+    t[c] = acc;
+  }
+}
+
+__device__ __forceinline__ void store6(double* dst, const double (&v)[6]) {
+  double2* d = reinterpret_cast<double2*>(dst);
+  d[0] = make_double2(v[0], v[1]);
+  d[1] = make_double2(v[2], v[3]);
+  d[2] = make_double2(v[4], v[5]);
+}
+__device__ __forceinline__ void load6(const double* src, double (&v)[6]) {
+  const double2* s = reinterpret_cast<const double2*>(src);
+  const double2 a = s[0], b = s[1], c = s[2];
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y;
+}
+
+// row items: warp w, lane l < 30 -> row slot 5 w + l / 6 (+ 5 * warps per pass), component l % 6, so the six
+// components of a row sit in one warp and M^-1 r is a shuffle product
+constexpr int ROWS_PER_PASS = 5 * (T / 32);
+
+__global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
+  extern __shared__ __align__(16) double smem[];
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = (int)cluster.block_rank();
+  const int CL = (int)cluster.num_blocks();
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const PcgClusterCarve& m = A.m;  // offsets sit in the constant bank: no registers
+  int* const smi = reinterpret_cast<int*>(smem);
+
+  const int row0 = A.cta_row_ptr[rank], row1 = A.cta_row_ptr[rank + 1];
+  const int nrows = row1 - row0;
+  const int ub0 = A.cta_blk_ptr[rank], nub = A.cta_blk_ptr[rank + 1] - ub0;
+  const int h0 = A.cta_halo_ptr[rank], nhalo = A.cta_halo_ptr[rank + 1] - h0;
+  const int full0 = A.row_ptr[row0];
+
+  // ---- one-time loads: my register block, spilled blocks, diagonal blocks, M^-1 rows, r = b
+  double Sreg[36];
+  const bool have = tid < nub;
+  if (have) {
+    const double2* src = reinterpret_cast<const double2*>(A.S + (size_t)A.ub_sblk[ub0 + tid] * 36);
+#pragma unroll
+    for (int e = 0; e < 18; ++e) {
+      const double2 v = src[e];
+      Sreg[2 * e] = v.x;
+      Sreg[2 * e + 1] = v.y;
+    }
+  } else {
+#pragma unroll
+    for (int e = 0; e < 36; ++e) Sreg[e] = 0.0;
+  }
+  const int nextra = nub > T ? nub - T : 0;
+  for (int k = tid; k < nextra * 36; k += T) {
+    const int b = k / 36, e = k % 36;
+    smem[m.extra + (size_t)e * A.max_extra + b] = A.S[(size_t)A.ub_sblk[ub0 + T + b] * 36 + e];
+  }
+  for (int k = tid; k < nrows * 36; k += T) {
+    smem[m.minv + k] = A.Minv[(size_t)row0 * 36 + k];
+    smem[m.sdiag + k] = A.S[(size_t)A.s_diag[row0 + k / 36] * 36 + k % 36];
+  }
+  for (int k = tid; k <= nrows; k += T) smi[m.rp + k] = A.row_ptr[row0 + k] - full0;
+  for (int k = tid; k < nhalo; k += T) smi[m.hdesc + k] = (A.halo_cta[h0 + k] << 20) | A.halo_rowl[h0 + k];
+  for (int k = tid; k < nub; k += T) {  // metadata of register blocks (k < T) and spilled blocks alike
+    const int g = ub0 + k;
+    smi[m.xmeta + 5 * k] = A.ub_rowl[g];
+    smi[m.xmeta + 5 * k + 1] = A.ub_halo[g];
+    smi[m.xmeta + 5 * k + 2] = A.ub_depA[g];
+    smi[m.xmeta + 5 * k + 3] = A.ub_tcta[g];
+    smi[m.xmeta + 5 * k + 4] = A.ub_tidx[g];
+  }
+  for (int k = tid; k < A.max_full * 6; k += T) smem[m.dep + k] = 0.0;  // the diagonal slots stay zero
+  for (int k = tid; k < nrows * 6; k += T) {
+    smem[m.r + k] = A.rhs[(size_t)row0 * 6 + k];
+    smem[m.x + k] = 0.0;
+    smem[m.p + k] = 0.0;
+    smem[m.s + k] = 0.0;
+  }
+  __syncthreads();
+  const int sub = lane / 6, comp = lane % 6, base_lane = 6 * sub;
+  const bool row_lane = lane < 30;
+  for (int lr0 = 0; lr0 < nrows; lr0 += ROWS_PER_PASS) {
+    const int lr = lr0 + 5 * warp + sub;
+    const bool act = row_lane && lr < nrows;
+    const double rv = act ? smem[m.r + lr * 6 + comp] : 0.0;
+    double z = 0.0;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      const double rj = __shfl_sync(FULL, rv, base_lane + j);
+      if (act) z += smem[m.minv + lr * 36 + comp * 6 + j] * rj;
+    }
+    if (act) smem[m.u + lr * 6 + comp] = z;
+  }
+
+  double gamma0 = 0.0, tol2g0 = 0.0, inv_gamma_prev = 0.0, inv_alpha_prev = 0.0, last_gamma = 0.0;
+  int iters = 0, flag = 1;
+#ifdef MPBA_PCG_TIMING
+  long long tA = 0, tH = 0, tP = 0, tB = 0, tR = 0, tC = 0, tU = 0;
+#define TICK(v) const long long v = clock64()
+#else
+#define TICK(v)
+#endif
+  for (int k = 0;; ++k) {
+    TICK(c0);
+    cluster.sync();  // A: every CTA's u is in place
+    TICK(c1);
+    // halo: the u rows this CTA's blocks multiply with, pulled once per iteration
+    for (int q = tid; q < nhalo * 3; q += T) {
+      const int hs = q / 3, part = q % 3;
+      const int hd = smi[m.hdesc + hs];
+      const int owner = hd >> 20, rl = hd & 0xfffff;
+      const double* src = ((owner == rank) ? smem : cluster.map_shared_rank(smem, owner)) + m.u;
+      reinterpret_cast<double2*>(smem + m.halo + (size_t)hs * 6)[part] =
+          reinterpret_cast<const double2*>(src + (size_t)rl * 6)[part];
+    }
+    __syncthreads();
+    TICK(c2);
+    // off-diagonal block products and deposits: S_ij u_j -> row i (local), S_ij^T u_i -> row j
+    if (have) {
+      double uj[6], ui[6], a[6], t[6];
+      const int* md = smi + m.xmeta + 5 * tid;
+      load6(smem + m.halo + md[1] * 6, uj);
+      load6(smem + m.u + md[0] * 6, ui);
+      block_products(Sreg, uj, ui, a, t);
+      store6(smem + m.dep + md[2] * 6, a);
+      const int tc = md[3];
+      double* dst = ((tc == rank) ? smem : cluster.map_shared_rank(smem, tc)) + m.dep;
+      store6(dst + md[4] * 6, t);
+    }
+    for (int b = tid; b < nextra; b += T) {
+      double uj[6], ui[6], a[6], t[6];
+      const int* md = smi + m.xmeta + 5 * (T + b);
+      load6(smem + m.halo + md[1] * 6, uj);
+      load6(smem + m.u + md[0] * 6, ui);
+#pragma unroll
+      for (int e = 0; e < 6; ++e) a[e] = t[e] = 0.0;
+#pragma unroll
+      for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int cc = 0; cc < 6; ++cc) {
+          const double sv = smem[m.extra + (size_t)(6 * r + cc) * A.max_extra + b];  // one read feeds both products
+          a[r] += sv * uj[cc];
+          t[cc] += sv * ui[r];
+        }
+      store6(smem + m.dep + md[2] * 6, a);
+      const int tc = md[3];
+      double* dst = ((tc == rank) ? smem : cluster.map_shared_rank(smem, tc)) + m.dep;
+      store6(dst + md[4] * 6, t);
+    }
+    TICK(c3);
+    cluster.sync();  // B: all deposits landed
+    TICK(c4);
+    // w = S u on the owned rows (diagonal block from shared memory + deposits in column order); dot partials
+    double pg = 0.0, pd = 0.0;
+    for (int lr0 = 0; lr0 < nrows; lr0 += ROWS_PER_PASS) {
+      const int lr = lr0 + 5 * warp + sub;
+      if (row_lane && lr < nrows) {
+        const int s0 = smi[m.rp + lr], s1 = smi[m.rp + lr + 1];
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+        int sl = s0;
+        for (; sl + 3 < s1; sl += 4) {
+          a0 += smem[m.dep + (size_t)sl * 6 + comp];
+          a1 += smem[m.dep + (size_t)(sl + 1) * 6 + comp];
+          a2 += smem[m.dep + (size_t)(sl + 2) * 6 + comp];
+          a3 += smem[m.dep + (size_t)(sl + 3) * 6 + comp];
+        }
+        for (; sl < s1; ++sl) a0 += smem[m.dep + (size_t)sl * 6 + comp];
+        double dg = 0.0;
+#pragma unroll
+        for (int j = 0; j < 6; ++j) dg += smem[m.sdiag + lr * 36 + comp * 6 + j] * smem[m.u + lr * 6 + j];
+        const double acc = ((a0 + a1) + (a2 + a3)) + dg;
+        smem[m.w + lr * 6 + comp] = acc;
+        const double uu = smem[m.u + lr * 6 + comp];
+        pg += smem[m.r + lr * 6 + comp] * uu;
+        pd += acc * uu;
+      }
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+      pg += __shfl_down_sync(FULL, pg, off);
+      pd += __shfl_down_sync(FULL, pd, off);
+    }
+    if (lane == 0) reinterpret_cast<double2*>(smem + m.red)[warp] = make_double2(pg, pd);
+    __syncthreads();
+    if (warp == 0) {  // warp 0 folds the warp partials (fixed tree) and lane k delivers the result to CTA k
+      double2 v = lane < T / 32 ? reinterpret_cast<const double2*>(smem + m.red)[lane] : make_double2(0.0, 0.0);
+      for (int off = 8; off > 0; off >>= 1) {
+        v.x += __shfl_down_sync(FULL, v.x, off);
+        v.y += __shfl_down_sync(FULL, v.y, off);
+      }
+      v.x = __shfl_sync(FULL, v.x, 0);
+      v.y = __shfl_sync(FULL, v.y, 0);
+      if (lane < CL) {
+        double* dst = ((lane == rank) ? smem : cluster.map_shared_rank(smem, lane)) + m.parts;
+        reinterpret_cast<double2*>(dst)[rank] = v;
+      }
+    }
+    TICK(c5);
+    cluster.sync();  // C: partials of every CTA are here
+    TICK(c6);
+#ifdef MPBA_PCG_TIMING
+    tA += c1 - c0; tH += c2 - c1; tP += c3 - c2; tB += c4 - c3; tR += c5 - c4; tC += c6 - c5;
+#endif
+    double gamma = 0.0, delta = 0.0;
+    {
+      double2 v = lane < CL ? reinterpret_cast<const double2*>(smem + m.parts)[lane] : make_double2(0.0, 0.0);
+      for (int off = 8; off > 0; off >>= 1) {
+        v.x += __shfl_down_sync(FULL, v.x, off);
+        v.y += __shfl_down_sync(FULL, v.y, off);
+      }
+      gamma = __shfl_sync(FULL, v.x, 0);
+      delta = __shfl_sync(FULL, v.y, 0);
+    }
+    if (k == 0) {
+      gamma0 = gamma;
+      tol2g0 = A.tol * A.tol * gamma0;
+      if (!(gamma0 > 0.0) || !isfinite(gamma0)) {
+        flag = (gamma0 == 0.0) ? 0 : 2;
+        last_gamma = 0.0;
+        break;
+      }
+    }
+    last_gamma = gamma;
+    if (!isfinite(gamma)) {
+      flag = 2;
+      break;
+    }
+    iters = k;
+    if (k > 0 && fabs(gamma) <= tol2g0) {
+      flag = 0;
+      break;
+    }
+    if (k >= A.max_iter) {
+      flag = 1;
+      break;
+    }
+    // beta = gamma / gamma_prev, alpha = gamma / (delta - beta gamma / alpha_prev): one division on the
+    // critical path, the reciprocals for the next iteration are taken off it
+    const double beta = gamma * inv_gamma_prev;
+    const double denom = delta - beta * gamma * inv_alpha_prev;
+    if (!(denom > 0.0) || !isfinite(denom)) {
+      flag = 2;
+      break;
+    }
+    const double alpha = gamma / denom;
+    for (int lr0 = 0; lr0 < nrows; lr0 += ROWS_PER_PASS) {
+      const int lr = lr0 + 5 * warp + sub;
+      const bool act = row_lane && lr < nrows;
+      double rn = 0.0;
+      if (act) {
+        const int o = lr * 6 + comp;
+        const double pn = smem[m.u + o] + beta * smem[m.p + o];
+        const double sn = smem[m.w + o] + beta * smem[m.s + o];
+        smem[m.p + o] = pn;
+        smem[m.s + o] = sn;
+        smem[m.x + o] += alpha * pn;
+        rn = smem[m.r + o] - alpha * sn;
+        smem[m.r + o] = rn;
+      }
+      double z = 0.0;
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        const double rj = __shfl_sync(FULL, rn, base_lane + j);
+        if (act) z += smem[m.minv + lr * 36 + comp * 6 + j] * rj;
+      }
+      if (act) smem[m.u + lr * 6 + comp] = z;
+    }
+    inv_gamma_prev = 1.0 / gamma;
+    inv_alpha_prev = denom * inv_gamma_prev;
+#ifdef MPBA_PCG_TIMING
+    tU += clock64() - c6;
+#endif
+  }
+  for (int q = tid; q < nrows * 6; q += T) A.x[(size_t)row0 * 6 + q] = smem[m.x + q];
+  if (rank == 0 && tid == 0) {
+    A.scal[S_PCG_ITERS] = (double)iters;
+    A.scal[S_PCG_FLAG] = (double)flag;
+    A.scal[S_PCG_RES] = gamma0 > 0.0 ? sqrt(fabs(last_gamma) / gamma0) : 0.0;
+#ifdef MPBA_PCG_TIMING
+    A.scal[S_PCG_CYC_SPMV] = (double)(tH + tP);
+    A.scal[S_PCG_CYC_REDUCE] = (double)(tA + tB + tC);
+    A.scal[S_PCG_CYC_UPDATE] = (double)(tR + tU);
+    A.scal[S_PCG_CYC_DETAIL] = (double)tA;
+    A.scal[S_PCG_CYC_DETAIL + 1] = (double)tH;
+    A.scal[S_PCG_CYC_DETAIL + 2] = (double)tP;
+    A.scal[S_PCG_CYC_DETAIL + 3] = (double)tB;
+    A.scal[S_PCG_CYC_DETAIL + 4] = (double)tR;
+    A.scal[S_PCG_CYC_DETAIL + 5] = (double)tC;
+    A.scal[S_PCG_CYC_DETAIL + 6] = (double)tU;
+#else
+    for (int e = 0; e < 3; ++e) A.scal[S_PCG_CYC_SPMV + e] = 0.0;
+#endif
+  }
+  cluster.sync();  // no CTA may exit while a peer can still touch its shared memory
+}
+
+}  // namespace
+
+size_t pcg_cluster_carve(PcgClusterArgs& A) {
+  PcgClusterCarve& c = A.m;
+  int o = 0;
+  c.dep = o;   o += A.max_full * 6;
+  c.x = o;     o += A.max_rows * 6;
+  c.r = o;     o += A.max_rows * 6;
+  c.u = o;     o += A.max_rows * 6;
+  c.p = o;     o += A.max_rows * 6;
+  c.s = o;     o += A.max_rows * 6;
+  c.w = o;     o += A.max_rows * 6;
+  c.minv = o;  o += A.max_rows * 36;
+  c.sdiag = o; o += A.max_rows * 36;
+  c.halo = o;  o += A.max_halo * 6;
+  c.extra = o; o += A.max_extra * 36;
+  c.parts = o; o += 2 * 16;
+  c.red = o;   o += 2 * (T / 32) + 2;
+  o += o & 1;
+  c.rp = 2 * o;
+  c.hdesc = c.rp + A.max_rows + 2;
+  c.xmeta = c.hdesc + A.max_halo;
+  const size_t ints = (size_t)c.xmeta + 5 * ((size_t)T + A.max_extra) + 2;
+  return ints * sizeof(int) + 16;
+}
+
+int pcg_cluster_max_smem(int device) {
+  static int optin = 0;
+  if (!optin) {
+    cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    cudaFuncSetAttribute(k_pcg_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
+    cudaFuncSetAttribute(k_pcg_cluster, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+  }
+  return optin;
+}
+
+// can a cluster of `cl` CTAs with this much shared memory be co-scheduled on this device?
+bool pcg_cluster_fits(int device, int cl, size_t smem_bytes) {
+  if ((int)smem_bytes > pcg_cluster_max_smem(device)) return false;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(cl);
+  cfg.blockDim = dim3(T);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = cl;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  int n = 0;
+  const cudaError_t e = cudaOccupancyMaxActiveClusters(&n, k_pcg_cluster, &cfg);
+  if (e != cudaSuccess) {
+    if (getenv("MPBA_DEBUG")) fprintf(stderr, "[mpba] cluster of %d, %zu B smem: %s\n", cl, smem_bytes, cudaGetErrorString(e));
+    cudaGetLastError();
+    return false;
+  }
+  if (getenv("MPBA_DEBUG")) fprintf(stderr, "[mpba] cluster of %d, %zu B smem: %d active clusters\n", cl, smem_bytes, n);
+  return n >= 1;
+}
+
+cudaError_t launch_pcg_cluster(const PcgClusterArgs& a, int cl, size_t smem_bytes, cudaStream_t st) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(cl);
+  cfg.blockDim = dim3(T);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = cl;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, k_pcg_cluster, a);
+}
+
+}  // namespace mpba
