@@ -209,6 +209,13 @@ int mpba_evaluate(mpba_handle* h, const mpba_problem* prob, void* workspace, siz
 int mpba_linearize(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
                    double* Hcc, double* gc, double* Hpp, double* gp, double* cost);
 
+/* 3x3 covariance of every variable point conditioned on the poses, (Hpp)^-1 of the undamped, unscaled
+ * normal equations at the current state: cov [P][6] (xx,xy,xz,yy,yz,zz), device pointer; zeros for constant
+ * points and for blocks that are not positive definite.  Replaces pycolmap.estimate_ba_covariance with
+ * BACovarianceOptionsParams.POINTS (mpsfm/sfm/mapper/bundle_adjustment.py:244-261). */
+int mpba_point_covariances(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
+                           double* cov);
+
 /* Reduced camera system for LM damping lambda_j = clamp(c_j^2 H_jj)/ (radius c_j^2) with Jacobi
  * scaling c taken at the current state: S [B][36], rhs [C][6], and its PCG solution y [C][6]
  * (any may be NULL).  pcg_iterations is a HOST pointer. */

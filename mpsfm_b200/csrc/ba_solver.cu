@@ -581,6 +581,27 @@ int mpba_linearize(mpba_handle* h, const mpba_problem* prob, void* workspace, si
   return MPBA_OK;
 }
 
+int mpba_point_covariances(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
+                           double* cov) {
+  Ctx c;
+  int rc = begin(h, prob, workspace, workspace_bytes, c);
+  if (rc) return rc;
+  if (!cov) return fail(h, MPBA_E_INVALID, "cov is NULL");
+  reset_profile(h, 0);
+  mpba_options opt;
+  mpba_default_options(&opt);
+  opt.jacobi_scaling = 0;
+  launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[0], h->stream);
+  // undamped: an infinite trust-region radius makes the LM diagonal vanish
+  LmDiag lm{INFINITY, opt.min_lm_diagonal, opt.max_lm_diagonal};
+  rc = enqueue_points_and_system(c, c.w.pose[0], prob->pt_xyz, 0, lm, 1, &opt, false);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(cov, c.w.Hinv, (size_t)c.pv.P * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  CU(cudaGetLastError());
+  return MPBA_OK;
+}
+
 int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
                         const mpba_options* opt_in, double radius, double* S, double* rhs, double* y,
                         int32_t* pcg_iterations) {

@@ -106,7 +106,7 @@ class MpbaSummary(C.Structure):
 EXPORTS = (
     "mpba_version", "mpba_create", "mpba_destroy", "mpba_last_error", "mpba_default_options",
     "mpba_workspace_bytes", "mpba_evaluate", "mpba_linearize", "mpba_reduced_system", "mpba_solve",
-    "mpba_kernel_times", "mpba_kernel_name",
+    "mpba_kernel_times", "mpba_kernel_name", "mpba_point_covariances",
 )
 
 _lib = None
@@ -135,6 +135,7 @@ def load_library(path: Optional[str] = None):
                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, _dp]
     lib.mpba_reduced_system.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t,
                                         C.POINTER(MpbaOptions), C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, _ip]
+    lib.mpba_point_covariances.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t, C.c_void_p]
     lib.mpba_solve.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t,
                                C.POINTER(MpbaOptions), C.POINTER(MpbaSummary)]
     lib.mpba_kernel_times.argtypes = [C.c_void_p, _dp, C.POINTER(C.c_int64)]
@@ -492,6 +493,19 @@ class BundleAdjuster:
         H3[:, 2, 0], H3[:, 2, 1], H3[:, 2, 2] = h6[:, 2], h6[:, 4], h6[:, 5]
         return (Hcc.cpu().numpy().reshape(lay.C, 6, 6), gc.cpu().numpy(), H3, gp.cpu().numpy()[: lay.P],
                 float(cost[0]), float(cost[1]))
+
+    def point_covariances(self):
+        """[P,3,3] covariance of every variable point conditioned on the poses (zeros for constant points)."""
+        torch, lay = self.torch, self.layout
+        cov = torch.empty((max(lay.P, 1), 6), dtype=torch.float64, device=self.device)
+        ws, wsn = self._ws()
+        self._check(self.lib.mpba_point_covariances(self.handle, C.byref(self.prob), ws, wsn, cov.data_ptr()))
+        c6 = cov.cpu().numpy()[: lay.P]
+        out = np.empty((lay.P, 3, 3))
+        out[:, 0, 0], out[:, 0, 1], out[:, 0, 2] = c6[:, 0], c6[:, 1], c6[:, 2]
+        out[:, 1, 0], out[:, 1, 1], out[:, 1, 2] = c6[:, 1], c6[:, 3], c6[:, 4]
+        out[:, 2, 0], out[:, 2, 1], out[:, 2, 2] = c6[:, 2], c6[:, 4], c6[:, 5]
+        return out
 
     def reduced_system(self, radius: float = 1e4, options: Optional[MpbaOptions] = None):
         """(S blocks [B,6,6], rhs [C,6], y [C,6], pcg_iterations) of the damped normal equations."""

@@ -1,0 +1,425 @@
+"""Drop-in for the reference's pyceres-backed bundle-adjustment ``Optimizer``.
+
+Same constructor, ``default_conf`` keys, methods, return shapes and in-place update semantics as
+``mpsfm.sfm.mapper.bundle_adjustment.Optimizer`` (/root/reference/mpsfm/sfm/mapper/bundle_adjustment.py:18-333);
+the Ceres problem the reference assembles through pycolmap / pyceres is assembled here as arrays
+(:class:`mpsfm_b200.problem.BundleProblem`) and solved by the sm_100a kernels behind ``include/mpba.h``.
+
+What replaces what:
+
+=====================================================  ==========================================================
+reference (bundle_adjustment.py)                        here
+=====================================================  ==========================================================
+``pycolmap.BundleAdjustmentConfig`` + ``create_default_bundle_adjuster`` (:85-104)   ``assemble()`` rows "reprojection"
+per-image depth selection + ``create_depth_bundle_adjuster`` (:124-176)             ``assemble()`` rows "depth prior"
+``set_parameter_block_constant`` / manifolds (:111-122, :178-182)                   ``img_free_mask`` / ``pt_const``
+``pyceres.solve`` SPARSE_SCHUR (:285-293)                                           ``engine.BundleAdjuster.solve``
+in-place update through aliased parameter blocks                                    ``_write_back()``
+``estimate_ba_covariance`` (:244-261)                                               ``engine.BundleAdjuster.point_covariances``
+=====================================================  ==========================================================
+
+There is no CPU path for the solve: without ``libmpba.so`` and a CUDA device ``ba`` / ``refine_3d_points`` /
+``calculate_point_covs`` raise :class:`mpsfm_b200.engine.EngineUnavailable`.  ``assemble()`` itself is host
+code (as it is in the reference) and runs anywhere, which is what the golden-vector tests use.
+"""
+
+from __future__ import annotations
+
+import dataclasses
+
+import numpy as np
+
+from .conf import BaseClass
+from .problem import FREE_ALL, FREE_FIX_TX, FREE_NONE, MAX_CAMERA_PARAMS, BundleProblem, CameraModel, LossType
+
+
+def fit_robust_gaussian_mad(data):
+    """bundle_adjustment.py:10-15"""
+    mu = np.median(data)
+    mad = np.median(np.abs(data - mu))
+    return mu, 1.4826 * mad
+
+
+def _model_id(model) -> int:
+    """pycolmap.CameraModelId / its name / its integer value -> COLMAP model id."""
+    if hasattr(model, "name"):
+        model = model.name
+    if isinstance(model, str):
+        return int(CameraModel[model.split(".")[-1]])
+    return int(model)
+
+
+@dataclasses.dataclass
+class Assembly:
+    """The array form of one Ceres problem plus the maps back to the reconstruction."""
+
+    problem: BundleProblem
+    image_ids: list  # problem image index -> image id; the bundle's optim_ids first (same order), then images
+    #                  outside the bundle that only contribute constant-pose residuals of variable points
+    num_optim_images: int
+    point_ids: np.ndarray  # problem point index -> point3D id
+    obs_image_id: np.ndarray  # [N] image id of every reprojection residual block, in the order they are added
+    obs_point2D_idx: np.ndarray  # [N]
+    obs_point3D_id: np.ndarray  # [N]
+    depth_rows: dict  # image id -> {"p2Ds","p3Ds","depths","magnitudes","params"}: the arguments the reference
+    #                   hands to pycolmap.create_depth_bundle_adjuster (:163-176)
+    kp_std: float
+    variable_points: list  # explicit variable points (local mode, :88-91)
+
+
+class Optimizer(BaseClass):
+    """Optimizer class for Bundle Adjustment (B200 engine)."""
+
+    default_conf = {
+        # --- the reference's keys and defaults (bundle_adjustment.py:21-36)
+        "depth_loss_name": "cauchy",
+        "ref3d_loss_name": "trivial",
+        "reproj_loss_name": "SOFT_L1",
+        "reproj_loss_scale": 1.5,
+        "scale_filter": True,
+        "scale_filter_factor": 1.5,
+        "metric_scale_filter": True,
+        "rob_std": 2,
+        "truncation_mode": "mad",  # [quantile, mad]
+        "gross_outliers": False,
+        "single_rescale": True,
+        "min_truncation_mult": None,
+        "verbose": 0,
+        # --- new, engine-only knobs (nested dict: stays open under the struct freeze, existing YAMLs still load)
+        "gpu": {"device": 0, "pcg_tolerance": 1e-12, "pcg_max_iterations": 2000, "max_num_iterations": 50},
+    }
+
+    def _init(self, mpsfm_rec, correspondences=None):
+        self.mpsfm_rec = mpsfm_rec
+        self.correspondences = correspondences
+        self.truncation_multiplier = 1
+        self.get_loss = {"trivial": LossType.TRIVIAL, "cauchy": LossType.CAUCHY, "softl1": LossType.SOFT_L1,
+                         "huber": LossType.HUBER}
+        self.last_summary = None
+        self.last_assembly = None
+
+    # ------------------------------------------------------------------------------------------
+    # problem assembly (host, like the reference)
+    # ------------------------------------------------------------------------------------------
+    def assemble(self, bundle, fix_pose, fix_scale=True, mode=None, depth_loss_name=None, allow_scale_filter=False,
+                 param_multiplier=1, depth_type="update", all_points_variable=False, reproj_loss=None,
+                 with_depth=True, **kw) -> Assembly:
+        """Array form of ``Optimizer.__build_problem`` (:67-185) up to, not including, the solve."""
+        conf, rec = self.conf, self.mpsfm_rec
+        optim_ids = list(bundle["optim_ids"])
+        depth_loss_name = depth_loss_name or conf.depth_loss_name
+        depth_loss = self.get_loss[depth_loss_name]
+        in_config = set(optim_ids)
+
+        # --- BundleAdjustmentConfig (:85-94)
+        if all_points_variable:  # calculate_point_covs (:249-250)
+            variable_points = list(bundle["pts3D"])
+        elif mode == "local":
+            variable_points = [p for p in bundle["pts3D"] if rec.points3D[p].track.length() < 15]
+        else:
+            variable_points = []
+        kp_std = float(np.median([rec.images[imid].kp_std for imid in optim_ids]))
+
+        # --- reprojection residual blocks of the images in the config (COLMAP AddImageToProblem)
+        image_ids = list(optim_ids)
+        image_index = {imid: k for k, imid in enumerate(image_ids)}
+        o_img, o_p2d, o_p3d, o_xy = [], [], [], []
+        img_obs_offset, img_p2ds = {}, {}
+        n = 0
+        for imid in optim_ids:
+            image = rec.images[imid]
+            q = image.cam_from_world.rotation.quat
+            q /= np.linalg.norm(q)  # COLMAP normalises the quaternion in place before adding the image
+            p2ds = np.asarray(image.get_observation_point2D_idxs(), dtype=np.int64)
+            img_obs_offset[imid], img_p2ds[imid] = n, p2ds
+            if p2ds.size == 0:
+                continue
+            o_img.append(np.full(p2ds.size, imid, dtype=np.int64))
+            o_p2d.append(p2ds)
+            o_p3d.append(np.asarray(image.point3D_ids(p2ds), dtype=np.uint64).astype(np.int64))
+            o_xy.append(np.asarray(image.keypoint_coordinates(p2ds), dtype=np.float64).reshape(-1, 2))
+            n += p2ds.size
+        cat = lambda parts, dt, shape: (np.concatenate(parts) if parts else np.zeros(shape, dtype=dt))  # noqa: E731
+        obs_img_id = cat(o_img, np.int64, (0,))
+        obs_p2d = cat(o_p2d, np.int64, (0,))
+        obs_p3d = cat(o_p3d, np.int64, (0,))
+        obs_xy = cat(o_xy, np.float64, (0, 2))
+
+        # --- explicit variable points: constant-pose residuals from images outside the config
+        #     (COLMAP AddPointToProblem), then ParameterizePoints: a point whose track is not completely
+        #     inside the problem is constant
+        point_ids, inverse, counts = np.unique(obs_p3d, return_inverse=True, return_counts=True)
+        n_in_problem = dict(zip(point_ids.tolist(), counts.tolist()))
+        x_img, x_p2d, x_p3d, x_xy = [], [], [], []
+        for pid in variable_points:
+            track = rec.points3D[pid].track
+            if n_in_problem.get(pid, 0) == track.length():
+                continue
+            for el in track.elements:
+                if el.image_id in in_config:
+                    continue
+                n_in_problem[pid] = n_in_problem.get(pid, 0) + 1
+                if el.image_id not in image_index:
+                    image_index[el.image_id] = len(image_ids)
+                    image_ids.append(el.image_id)
+                x_img.append(el.image_id)
+                x_p2d.append(el.point2D_idx)
+                x_p3d.append(pid)
+                x_xy.append(np.asarray(rec.images[el.image_id].keypoint_coordinates([el.point2D_idx])).reshape(2))
+        if x_img:
+            obs_img_id = np.concatenate([obs_img_id, np.asarray(x_img, dtype=np.int64)])
+            obs_p2d = np.concatenate([obs_p2d, np.asarray(x_p2d, dtype=np.int64)])
+            obs_p3d = np.concatenate([obs_p3d, np.asarray(x_p3d, dtype=np.int64)])
+            obs_xy = np.concatenate([obs_xy, np.asarray(x_xy, dtype=np.float64).reshape(-1, 2)])
+            point_ids, inverse = np.unique(obs_p3d, return_inverse=True)
+        pt_const = np.array([1 if rec.points3D[int(pid)].track.length() > n_in_problem[int(pid)] else 0
+                             for pid in point_ids], dtype=np.uint8)
+
+        # --- images: poses, gauge (:111-122), cameras (intrinsics constant, :92-94)
+        C = len(image_ids)
+        img_q, img_t = np.empty((C, 4)), np.empty((C, 3))
+        free = np.zeros(C, dtype=np.uint8)
+        cam_ids = []
+        for k, imid in enumerate(image_ids):
+            image = rec.images[imid]
+            img_q[k] = image.cam_from_world.rotation.quat
+            img_t[k] = image.cam_from_world.translation
+            cam_ids.append(image.camera_id)
+            if k >= len(optim_ids) or fix_pose or k == 0:
+                free[k] = FREE_NONE
+            elif k == 1:
+                free[k] = FREE_FIX_TX
+            else:
+                free[k] = FREE_ALL
+        uniq_cams = list(dict.fromkeys(cam_ids))
+        cam_row = {c: r for r, c in enumerate(uniq_cams)}
+        cam_model = np.array([_model_id(rec.rec.cameras[c].model) for c in uniq_cams], dtype=np.int32)
+        cam_params = np.zeros((len(uniq_cams), MAX_CAMERA_PARAMS))
+        for r, c in enumerate(uniq_cams):
+            prm = np.asarray(rec.rec.cameras[c].params, dtype=np.float64)
+            cam_params[r, : prm.size] = prm
+
+        # --- depth-prior residual blocks (:124-176)
+        depth_rows = {}
+        d_obs, d_d, d_w, d_a = [], [], [], []
+        pm = param_multiplier * self.truncation_multiplier  # :109
+        if with_depth:
+            for imid in optim_ids:
+                image = rec.images[imid]
+                if image.depth is None or not image.depth.activated:
+                    continue
+                p2Ds = img_p2ds[imid]
+                if p2Ds.size == 0:
+                    continue
+                kps = np.asarray(image.keypoint_coordinates(p2Ds), dtype=np.float64).reshape(-1, 2)
+                valid = np.asarray(image.depth.valid_at_kps(kps), dtype=bool)
+                kps = kps[valid]
+                depths = np.asarray(image.depth.data_at_kps(kps) if depth_type == "update"
+                                    else image.depth.data_prior_at_kps(kps), dtype=np.float64)
+                p2Ds = p2Ds[valid]
+                p3Ds = np.asarray(image.point3D_ids(p2Ds), dtype=np.uint64).astype(np.int64)
+                depth3d = np.asarray(rec.project_image_3d_points(imid, p3Ds)[3], dtype=np.float64) if p2Ds.size else np.zeros(0)
+                mask = depths > 0
+                if allow_scale_filter and conf.scale_filter:
+                    div = depths / depth3d
+                    mask = mask & (div < conf.scale_filter_factor) & (div > (1 / conf.scale_filter_factor))
+                uu = image.depth.uncertainty_update
+                variances = (np.asarray(uu, dtype=np.float64)[p2Ds] if isinstance(uu, np.ndarray)
+                             else np.array([uu[i] for i in p2Ds], dtype=np.float64))
+                if conf.gross_outliers:
+                    whitened = np.abs(np.log(depths).clip(1e-6, None) - np.log(depth3d).clip(1e-6, None)) / variances**0.5
+                    mask = mask & (whitened < 3)
+                if np.sum(mask) == 0:
+                    self.log("No valid points for depth regularizing", level=1)
+                    continue
+                depths, p2Ds, variances, p3Ds = depths[mask], p2Ds[mask], variances[mask], p3Ds[mask]
+                inv_uncert = 1 / variances.clip(1e-6, None)
+                m = pm * conf.rob_std
+                params = m * variances**0.5 / depths  # :160 loss scale a
+                magnitudes = depths**2 * inv_uncert  # :161 ScaledLoss weight w
+                depth_rows[imid] = {"p2Ds": p2Ds, "p3Ds": p3Ds, "depths": depths, "magnitudes": magnitudes, "params": params}
+                d_obs.append(img_obs_offset[imid] + np.searchsorted(img_p2ds[imid], p2Ds))
+                d_d.append(depths)
+                d_w.append(magnitudes)
+                d_a.append(params)
+
+        problem = BundleProblem(
+            img_q=img_q, img_t=img_t,
+            img_camera=np.array([cam_row[c] for c in cam_ids], dtype=np.int32),
+            img_free_mask=free, cam_model=cam_model, cam_params=cam_params,
+            pt_xyz=rec.point3D_coordinates([int(p) for p in point_ids]) if point_ids.size else np.zeros((0, 3)),
+            pt_const=pt_const,
+            obs_img=np.array([image_index[int(i)] for i in obs_img_id], dtype=np.int32),
+            obs_pt=inverse.astype(np.int32), obs_xy=obs_xy,
+            depth_obs=cat(d_obs, np.int64, (0,)).astype(np.int32), depth_d=cat(d_d, np.float64, (0,)),
+            depth_w=cat(d_w, np.float64, (0,)), depth_a=cat(d_a, np.float64, (0,)),
+            shift_scale=np.zeros((C, 2)),  # :83; both coordinates constant at every call site (:176-182)
+            reproj_loss=LossType.parse(reproj_loss if reproj_loss is not None else conf.reproj_loss_name),
+            reproj_loss_scale=float(conf.reproj_loss_scale * kp_std),  # :101
+            reproj_loss_weight=float(1 / kp_std**2),  # :99
+            depth_loss=depth_loss,
+        )
+        if not fix_scale:
+            raise NotImplementedError("fix_scale=False is never used by the reference's call sites (:263-283)")
+        return Assembly(problem=problem, image_ids=image_ids, num_optim_images=len(optim_ids), point_ids=point_ids,
+                        obs_image_id=obs_img_id, obs_point2D_idx=obs_p2d, obs_point3D_id=obs_p3d,
+                        depth_rows=depth_rows, kp_std=kp_std, variable_points=variable_points)
+
+    # ------------------------------------------------------------------------------------------
+    # solve + in-place update
+    # ------------------------------------------------------------------------------------------
+    def solve(self, assembly: Assembly):
+        """``Optimizer.solve`` (:285-293): SPARSE_SCHUR with Ceres defaults -> LM + Schur + PCG on the GPU."""
+        from . import engine
+
+        g = self.conf.gpu
+        ba = engine.BundleAdjuster(assembly.problem, device=int(g["device"]))
+        try:
+            opt = engine.default_options(pcg_tolerance=float(g["pcg_tolerance"]),
+                                         pcg_max_iterations=int(g["pcg_max_iterations"]),
+                                         max_num_iterations=int(g["max_num_iterations"]),
+                                         verbose=1 if self.conf.verbose > 3 else 0)
+            summary = ba.solve(opt)
+            q, t, X = ba.state()
+        finally:
+            ba.close()
+        self._write_back(assembly, q, t, X)
+        self.last_summary = summary
+        self.log(summary.brief_report(), level=2)
+        return summary
+
+    def _write_back(self, assembly: Assembly, q, t, X):
+        """Ceres parameter blocks alias pycolmap memory in the reference; here the non-constant blocks are
+        copied back into the very same numpy buffers."""
+        rec, pr = self.mpsfm_rec, assembly.problem
+        for k in range(assembly.num_optim_images):
+            mask = int(pr.img_free_mask[k])
+            if mask == 0:
+                continue
+            pose = rec.images[assembly.image_ids[k]].cam_from_world
+            if mask & 0b000111:
+                pose.rotation.quat[:] = q[k]
+            if mask & 0b111000:
+                pose.translation[:] = t[k]
+        for j in np.flatnonzero(pr.pt_const == 0):
+            rec.points3D[int(assembly.point_ids[j])].xyz[:] = X[j]
+
+    def __build_problem(self, bundle, fix_pose, fix_scale, **kwargs):
+        assembly = self.assemble(bundle, fix_pose, fix_scale, **kwargs)
+        self.last_assembly = assembly
+        summary = self.solve(assembly)
+        shift_scale = {imid: np.array([0.0, 0.0]) for imid in bundle["optim_ids"]}
+        return summary, shift_scale
+
+    # ------------------------------------------------------------------------------------------
+    # the entry points the mapper calls (base.py:456-648)
+    # ------------------------------------------------------------------------------------------
+    def ba(self, bundle, mode, **kwargs):
+        """Optimizes per frame data and 3d points in entire reconstruction (:263-266)."""
+        problem, _ = self.__build_problem(bundle, fix_pose=False, fix_scale=True, mode=mode, **kwargs)
+        return problem, True
+
+    def refine_3d_points(self, bundle, **kwargs):
+        """Refines triangulated 3d points with depth maps keeping poses fixed (:276-283)."""
+        problem, _ = self.__build_problem(bundle, fix_pose=True, fix_scale=True,
+                                          depth_loss_name=self.conf.ref3d_loss_name, **kwargs)
+        return problem, True
+
+    def calculate_point_covs(self, bundle):
+        """3x3 covariance of every point of the bundle (:244-261): TRIVIAL loss with magnitude 1/kp_std^2,
+        all points of the bundle variable, intrinsics constant; COLMAP's POINTS covariance is conditioned on
+        the poses, i.e. the inverse of the point's own normal-equation block."""
+        from . import engine
+
+        assembly = self.assemble(bundle, fix_pose=False, all_points_variable=True, reproj_loss=LossType.TRIVIAL,
+                                 with_depth=False)
+        ba = engine.BundleAdjuster(assembly.problem, device=int(self.conf.gpu["device"]))
+        try:
+            covs = ba.point_covariances()
+        finally:
+            ba.close()
+        index = {int(pid): j for j, pid in enumerate(assembly.point_ids)}
+        for p3Did in bundle["pts3D"]:
+            j = index.get(int(p3Did))
+            if j is not None:
+                self.mpsfm_rec.point_covs.data[p3Did] = covs[j]
+
+    def optimize_prior_shiftscale(self, bundle, **kwargs):
+        """Closed-form per-image log-scale of the depth prior (:268-274, :187-242)."""
+        shift_scale, success = self.__build_shiftscale_problem(bundle, **kwargs)
+        if not success:
+            return None, False
+        shift_scale = {imid: (shift, np.exp(scale)) for imid, (shift, scale) in shift_scale.items()}
+        return shift_scale, True
+
+    def __yield_problem_parameters(self, optim_ids, proj_depths=False):
+        for imid in optim_ids:  # :50-65
+            image = self.mpsfm_rec.images[imid]
+            pt2D_ids = image.get_observation_point2D_idxs()
+            kps_with3D = image.keypoint_coordinates(pt2D_ids)
+            kwargs = {"imid": imid, "image": image, "pt3D_ids": image.point3D_ids(pt2D_ids), "kps": kps_with3D}
+            kwargs["obsdepths"] = image.depth.data_prior_at_kps(kps_with3D)
+            kwargs["valid"] = image.depth.valid_at_kps(kps_with3D)
+            if proj_depths:
+                kwargs["projdepths"] = self.mpsfm_rec.project_image_3d_points(imid, kwargs["pt3D_ids"])[3]
+            yield kwargs
+
+    def __build_shiftscale_problem(self, bundle, allow_scale_filter=False, allow_metric_scale_filter=False):
+        conf, rec = self.conf, self.mpsfm_rec
+        shift_scale = {}
+        for kw in self.__yield_problem_parameters(bundle["optim_ids"], proj_depths=conf.scale_filter or conf.metric_scale_filter):
+            pose = kw["image"].cam_from_world
+            imid, p3dids = kw["imid"], kw["pt3D_ids"]
+            if (conf.scale_filter_factor or conf.metric_scale_filter) and (
+                "ref_id" in bundle and imid != bundle["ref_id"] and conf.single_rescale
+            ):
+                continue  # :204-207
+            if allow_metric_scale_filter and conf.metric_scale_filter and (
+                (imid == bundle["ref_id"]) or (not conf.single_rescale)
+            ):  # :208-232
+                scale = kw["projdepths"] / (kw["obsdepths"].clip(1e-6, None))
+                proposed_scale = scale * rec.images[imid].depth.scale
+                map_scale = np.mean([rec.images[i].depth.scale for i in bundle["optim_ids"] if i != imid])
+                div = map_scale / proposed_scale
+                valid = (div < 1.5) * (div > (1 / 1.5))
+                presum = kw["valid"].sum()
+                kw["valid"] = kw["valid"] * valid
+                if kw["valid"].sum() == 0:
+                    print("WARNING: Settin all points as outliers for metric scale optim and using map scale!!")
+                    shift_scale[imid] = np.array([0.0, np.log(map_scale / rec.images[imid].depth.scale)])
+                    return shift_scale, True
+                self.log(f"Setting {presum - kw['valid'].sum()}points as outliers for metric scale optim, out of {presum}", level=3)
+            if allow_scale_filter and conf.scale_filter and not allow_metric_scale_filter:  # :233-238
+                div = kw["obsdepths"] / kw["projdepths"]
+                kw["valid"] = kw["valid"] * ((div < conf.scale_filter_factor) * (div > (1 / conf.scale_filter_factor)))
+            z = (pose * rec.point3D_coordinates(p3dids))[:, -1]
+            z = z[kw["valid"]]
+            odepth = kw["obsdepths"][kw["valid"]]
+            shift_scale[imid] = np.array([0.0, np.median(np.log((z / odepth).clip(1e-6, None)))])  # :239-241
+        return shift_scale, True
+
+    def update_truncation_multiplier(self, imids):
+        """Robust spread (1.4826 MAD) of the whitened log-depth discrepancy over the given images (:295-333)."""
+        D, D3d, dstds = [], [], []
+        for imid in imids:
+            image = self.mpsfm_rec.images[imid]
+            p2Ds = np.asarray(image.get_observation_point2D_idxs(), dtype=np.int64)
+            kps = np.asarray(image.keypoint_coordinates(p2Ds), dtype=np.float64).reshape(-1, 2)
+            valid = np.asarray(image.depth.valid_at_kps(kps), dtype=bool)
+            depths = np.asarray(image.depth.data_at_kps(kps[valid]), dtype=np.float64)
+            p2Ds = p2Ds[valid]
+            p3Ds = np.asarray(image.point3D_ids(p2Ds), dtype=np.uint64).astype(np.int64)
+            mask = depths > 0
+            depth3d = self.mpsfm_rec.project_image_3d_points(imid, [int(p) for p in p3Ds[mask]])[3]
+            uu = image.depth.uncertainty_update
+            variances = (np.asarray(uu, dtype=np.float64)[p2Ds[mask]] if isinstance(uu, np.ndarray)
+                         else np.array([uu[i] for i in p2Ds[mask]], dtype=np.float64))
+            D.append(depths[mask])
+            D3d.append(np.asarray(depth3d, dtype=np.float64))
+            dstds.append(variances**0.5)
+        depths, depth3ds, dstds = np.concatenate(D), np.concatenate(D3d), np.concatenate(dstds)
+        log_stds = np.clip(dstds / depths, 1e-6, None)
+        _, sigma = fit_robust_gaussian_mad((np.log(depths) - np.log(depth3ds)) / log_stds)
+        self.truncation_multiplier = sigma
+        if self.conf.min_truncation_mult is not None:
+            self.truncation_multiplier = max(self.truncation_multiplier, self.conf.min_truncation_mult)
