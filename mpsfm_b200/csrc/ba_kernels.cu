@@ -352,6 +352,17 @@ __device__ __forceinline__ void load_fac(const double* __restrict__ fac, int k, 
 }
 
 constexpr int SB_THREADS = 128;
+constexpr size_t SB_STAGE_BYTES = 2 * 16 * SB_THREADS * sizeof(double2);
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
 
 // One CTA per upper block (i <= j) of the reduced camera system, no atomics, fixed summation order:
 //   T(i,j) = sum over the tracks seen by both images of G_a^T (Z_a Z_b^T) G_b
@@ -376,47 +387,138 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
   for (int k = 0; k < 36; ++k) M[k] = 0.0;
   double rv[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
 
-  for (int it = it0 + (int)threadIdx.x; it < it1; it += SB_THREADS) {
-    const int ka = __ldg(pv.item_a + it), kb = __ldg(pv.item_b + it);
-    Fac fa;
-    load_fac(fac, ka, fa);
-    double K[9], Mi[36];
-    if (ka == kb) {
+  // Every thread owns one item per 128-item tile.  Its two factor records (2 x 128 B, random gathers) are
+  // staged through shared memory with cp.async two tiles deep, so the loads of tile t+1 are in flight while
+  // tile t is multiplied: the kernel is bound by fp64 issue / L2 bandwidth instead of gather latency, at any
+  // occupancy.  A thread only ever reads back what it copied itself -> no CTA barrier in the loop.  Layout
+  // [buffer][16-byte chunk][thread]: conflict free for the copies and for the reads.
+  extern __shared__ __align__(16) double2 stage[];  // [2][16][SB_THREADS]
+  const int tid = threadIdx.x;
+  auto issue = [&](int buf, int ka, int kb) {
+    const double2* sa = reinterpret_cast<const double2*>(fac + (size_t)ka * FAC_STRIDE);
+    const double2* sb = reinterpret_cast<const double2*>(fac + (size_t)kb * FAC_STRIDE);
+    double2* dst = stage + (size_t)buf * 16 * SB_THREADS + tid;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) cp_async16(dst + c * SB_THREADS, sa + c);
+    if (kb != ka) {
+#pragma unroll
+      for (int c = 0; c < 6; ++c) cp_async16(dst + (8 + c) * SB_THREADS, sb + c);  // Z and p_rot of b; e is not needed
+    }
+  };
+  int it = it0 + tid;
+  int ka = 0, kb = 0, ka1 = 0, kb1 = 0;
+  if (it < it1) {
+    ka = __ldg(pv.item_a + it);
+    kb = __ldg(pv.item_b + it);
+    issue(0, ka, kb);
+  }
+  cp_async_commit();
+  if (it + SB_THREADS < it1) {
+    ka1 = __ldg(pv.item_a + it + SB_THREADS);
+    kb1 = __ldg(pv.item_b + it + SB_THREADS);
+  }
+  for (int tile = 0;; ++tile) {
+    const int base = it0 + tile * SB_THREADS;
+    if (base >= it1) break;
+    const bool cur = it < it1, nxt = it + SB_THREADS < it1;
+    if (nxt) issue((tile + 1) & 1, ka1, kb1);
+    cp_async_commit();
+    int ka2 = 0, kb2 = 0;
+    if (it + 2 * SB_THREADS < it1) {
+      ka2 = __ldg(pv.item_a + it + 2 * SB_THREADS);
+      kb2 = __ldg(pv.item_b + it + 2 * SB_THREADS);
+    }
+    cp_async_wait<1>();
+    if (cur) {
+      const double2* src = stage + (size_t)(tile & 1) * 16 * SB_THREADS + tid;
+      double za[9], zb[9], qa[3], qb[3];
+      {
+        const double2 c0 = src[0], c1 = src[SB_THREADS], c2 = src[2 * SB_THREADS], c3 = src[3 * SB_THREADS],
+                      c4 = src[4 * SB_THREADS], c5 = src[5 * SB_THREADS];
+        za[0] = c0.x; za[1] = c0.y; za[2] = c1.x; za[3] = c1.y; za[4] = c2.x; za[5] = c2.y; za[6] = c3.x; za[7] = c3.y;
+        za[8] = c4.x; qa[0] = 2.0 * c4.y; qa[1] = 2.0 * c5.x; qa[2] = 2.0 * c5.y;
+      }
+      const bool same = (ka == kb);
+      if (same) {
+        const double2 c6 = src[6 * SB_THREADS], c7 = src[7 * SB_THREADS];
+        const double e0 = c6.x, e1 = c6.y, e2 = c7.x;
+        // rhs: G_a^T (Z_a e)
+        const double z0 = za[0] * e0 + za[1] * e1 + za[2] * e2, z1 = za[3] * e0 + za[4] * e1 + za[5] * e2,
+                     z2 = za[6] * e0 + za[7] * e1 + za[8] * e2;
+        rv[0] += qa[1] * z2 - qa[2] * z1;
+        rv[1] += qa[2] * z0 - qa[0] * z2;
+        rv[2] += qa[0] * z1 - qa[1] * z0;
+        rv[3] += z0; rv[4] += z1; rv[5] += z2;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) zb[k] = za[k];
+        qb[0] = qa[0]; qb[1] = qa[1]; qb[2] = qa[2];
+      } else {
+        const double2 c0 = src[8 * SB_THREADS], c1 = src[9 * SB_THREADS], c2 = src[10 * SB_THREADS],
+                      c3 = src[11 * SB_THREADS], c4 = src[12 * SB_THREADS], c5 = src[13 * SB_THREADS];
+        zb[0] = c0.x; zb[1] = c0.y; zb[2] = c1.x; zb[3] = c1.y; zb[4] = c2.x; zb[5] = c2.y; zb[6] = c3.x; zb[7] = c3.y;
+        zb[8] = c4.x; qb[0] = 2.0 * c4.y; qb[1] = 2.0 * c5.x; qb[2] = 2.0 * c5.y;
+      }
+      // K = Za Zb^T;  M += [Pa^T K Pb, Pa^T K; K Pb, K]  with P = -2 [p]x, q = 2 p:
+      //   (K P)[r]   = ( q_y K[r][2] - q_z K[r][1],  q_z K[r][0] - q_x K[r][2],  q_x K[r][1] - q_y K[r][0] )
+      //   (P^T Y)[.][c] = ( q_y Y[2][c] - q_z Y[1][c],  q_z Y[0][c] - q_x Y[2][c],  q_x Y[1][c] - q_y Y[0][c] )
+      double K[9], KP[9];
 #pragma unroll
       for (int r = 0; r < 3; ++r)
 #pragma unroll
         for (int c = 0; c < 3; ++c)
-          K[3 * r + c] = fa.Z[3 * r] * fa.Z[3 * c] + fa.Z[3 * r + 1] * fa.Z[3 * c + 1] + fa.Z[3 * r + 2] * fa.Z[3 * c + 2];
-      gt_k_g(fa.p, K, fa.p, Mi);
-      double ze[3], ge[6];
-      ze[0] = fa.Z[0] * fa.e[0] + fa.Z[1] * fa.e[1] + fa.Z[2] * fa.e[2];
-      ze[1] = fa.Z[3] * fa.e[0] + fa.Z[4] * fa.e[1] + fa.Z[5] * fa.e[2];
-      ze[2] = fa.Z[6] * fa.e[0] + fa.Z[7] * fa.e[1] + fa.Z[8] * fa.e[2];
-      gt_vec(fa.p, ze, ge);
+          K[3 * r + c] = za[3 * r] * zb[3 * c] + za[3 * r + 1] * zb[3 * c + 1] + za[3 * r + 2] * zb[3 * c + 2];
 #pragma unroll
-      for (int k = 0; k < 6; ++k) rv[k] += ge[k];
+      for (int r = 0; r < 3; ++r) {
+        KP[3 * r] = qb[1] * K[3 * r + 2] - qb[2] * K[3 * r + 1];
+        KP[3 * r + 1] = qb[2] * K[3 * r] - qb[0] * K[3 * r + 2];
+        KP[3 * r + 2] = qb[0] * K[3 * r + 1] - qb[1] * K[3 * r];
+      }
+      if (!diag || same) {
 #pragma unroll
-      for (int k = 0; k < 36; ++k) M[k] += Mi[k];
-    } else {
-      Fac fb;
-      load_fac(fac, kb, fb);
+        for (int c = 0; c < 3; ++c) {
+          // rows 0..2: P_a^T [KP | K], rows 3..5: [KP | K]
+          M[c] += qa[1] * KP[6 + c] - qa[2] * KP[3 + c];
+          M[6 + c] += qa[2] * KP[c] - qa[0] * KP[6 + c];
+          M[12 + c] += qa[0] * KP[3 + c] - qa[1] * KP[c];
+          M[3 + c] += qa[1] * K[6 + c] - qa[2] * K[3 + c];
+          M[9 + c] += qa[2] * K[c] - qa[0] * K[6 + c];
+          M[15 + c] += qa[0] * K[3 + c] - qa[1] * K[c];
+          M[18 + c] += KP[c];
+          M[24 + c] += KP[3 + c];
+          M[30 + c] += KP[6 + c];
+          M[21 + c] += K[c];
+          M[27 + c] += K[3 + c];
+          M[33 + c] += K[6 + c];
+        }
+      } else {
+        // one image observing a track twice: both orientations land on the diagonal block (rare)
+        double Mi[36];
 #pragma unroll
-      for (int r = 0; r < 3; ++r)
-#pragma unroll
-        for (int c = 0; c < 3; ++c)
-          K[3 * r + c] = fa.Z[3 * r] * fb.Z[3 * c] + fa.Z[3 * r + 1] * fb.Z[3 * c + 1] + fa.Z[3 * r + 2] * fb.Z[3 * c + 2];
-      gt_k_g(fa.p, K, fb.p, Mi);
-      if (diag) {  // one image observing a track twice: both orientations land on the diagonal block
+        for (int c = 0; c < 3; ++c) {
+          Mi[c] = qa[1] * KP[6 + c] - qa[2] * KP[3 + c];
+          Mi[6 + c] = qa[2] * KP[c] - qa[0] * KP[6 + c];
+          Mi[12 + c] = qa[0] * KP[3 + c] - qa[1] * KP[c];
+          Mi[3 + c] = qa[1] * K[6 + c] - qa[2] * K[3 + c];
+          Mi[9 + c] = qa[2] * K[c] - qa[0] * K[6 + c];
+          Mi[15 + c] = qa[0] * K[3 + c] - qa[1] * K[c];
+          Mi[18 + c] = KP[c];
+          Mi[24 + c] = KP[3 + c];
+          Mi[30 + c] = KP[6 + c];
+          Mi[21 + c] = K[c];
+          Mi[27 + c] = K[3 + c];
+          Mi[33 + c] = K[6 + c];
+        }
 #pragma unroll
         for (int r = 0; r < 6; ++r)
 #pragma unroll
           for (int c = 0; c < 6; ++c) M[6 * r + c] += Mi[6 * r + c] + Mi[6 * c + r];
-      } else {
-#pragma unroll
-        for (int k = 0; k < 36; ++k) M[k] += Mi[k];
       }
     }
+    it += SB_THREADS;
+    ka = ka1; kb = kb1;
+    ka1 = ka2; kb1 = kb2;
   }
+  cp_async_wait<0>();
 
   // ---- CTA reduction: lane e of every warp ends with entry e (e < 32), entries 32..35 by butterfly
   __shared__ double sm[SB_THREADS / 32][44];
@@ -931,7 +1033,12 @@ void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaS
 }
 void launch_schur_blocks(const ProblemView& pv, const double* fac, const double* Hc, const double* gc,
                          const double* c_img, LmDiag lm, double* S, double* rhs, double* Minv, cudaStream_t st) {
-  k_schur_blocks<<<pv.U, SB_THREADS, 0, st>>>(pv, fac, Hc, gc, c_img, lm, S, rhs);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(k_schur_blocks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_STAGE_BYTES);
+    attr_set = true;
+  }
+  k_schur_blocks<<<pv.U, SB_THREADS, SB_STAGE_BYTES, st>>>(pv, fac, Hc, gc, c_img, lm, S, rhs);
   k_block_inverse<<<(pv.C + 127) / 128, 128, 0, st>>>(pv, S, Minv);
 }
 PcgPlan pcg_plan(int device, int C, int max_row_blocks) {
