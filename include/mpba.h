@@ -152,7 +152,8 @@ typedef struct mpba_options {
   int32_t verbose;
   int32_t pcg_kernel;                      /* 0: automatic (cluster-resident when S fits one 16-CTA cluster,
                                               grid-wide otherwise), 1: force grid-wide, 2: prefer cluster */
-  int32_t reserved;
+  int32_t pcg_coarse;                      /* 0: two-level preconditioner (block-Jacobi + gauge-mode coarse space over
+                                              groups of images) with the cluster kernel, 1: block-Jacobi only */
 } mpba_options;
 
 /* ceres::IterationSummary subset, one row per LM iteration (row 0 = initial evaluation) */

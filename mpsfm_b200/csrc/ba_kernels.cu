@@ -1032,13 +1032,15 @@ void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaS
   k_pt_scalars_gmax<<<1, 1024, 0, st>>>(pt_part, nblk, scal);
 }
 void launch_schur_blocks(const ProblemView& pv, const double* fac, const double* Hc, const double* gc,
-                         const double* c_img, LmDiag lm, double* S, double* rhs, double* Minv, cudaStream_t st) {
+                         const double* c_img, LmDiag lm, double* S, double* rhs, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_schur_blocks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_STAGE_BYTES);
     attr_set = true;
   }
   k_schur_blocks<<<pv.U, SB_THREADS, SB_STAGE_BYTES, st>>>(pv, fac, Hc, gc, c_img, lm, S, rhs);
+}
+void launch_block_inverse(const ProblemView& pv, const double* S, double* Minv, cudaStream_t st) {
   k_block_inverse<<<(pv.C + 127) / 128, 128, 0, st>>>(pv, S, Minv);
 }
 PcgPlan pcg_plan(int device, int C, int max_row_blocks) {

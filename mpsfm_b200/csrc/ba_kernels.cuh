@@ -86,7 +86,8 @@ void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaS
 
 // ---- reduced camera system ----------------------------------------------------------------------
 void launch_schur_blocks(const ProblemView& pv, const double* fac, const double* Hc, const double* gc,
-                         const double* c_img, LmDiag lm, double* S, double* rhs, double* Minv, cudaStream_t st);
+                         const double* c_img, LmDiag lm, double* S, double* rhs, cudaStream_t st);
+void launch_block_inverse(const ProblemView& pv, const double* S, double* Minv, cudaStream_t st);
 struct PcgPlan {
   int grid, rows_per_cta, use_smem, max_local_blocks;
   size_t smem_bytes;
@@ -106,6 +107,8 @@ constexpr int PCGC_THREADS = 384;
 // block of S every thread holds
 struct PcgClusterCarve {
   int dep, x, r, u, p, s, w, minv, sdiag, halo, extra, parts, red;
+  int zloc, ainv, rcall, ec, glrp;  // (glrp: int view, local row pointers of the owned groups)
+  // two-level preconditioner: Z rows of the owned images, owned rows of A_c^-1, Z^T r, e_c
   int rp;     // row pointers of the owned rows, relative to the first owned full block
   int hdesc;  // halo source: owner CTA << 20 | local row at the owner
   int xmeta;  // spilled blocks: rowl, halo, depA, tcta, tidx
@@ -114,6 +117,11 @@ struct PcgClusterArgs {
   int C;
   PcgClusterCarve m;
   int max_rows, max_full, max_halo, max_extra;  // per-CTA maxima: uniform shared-memory layout across the cluster
+  // coarse space (coarse.cu): G groups of consecutive images, gpc per CTA (G = cl * gpc), nc = 7 G; G == 0: off
+  int G, gpc, nc;
+  const int32_t* grp_row_ptr;   // [G+1] first image of every group
+  const double* Zc;             // [C][6][7] gauge modes
+  const double* Ainv;           // [nc][nc] (Z^T S Z)^-1
   const int32_t* row_ptr;       // [C+1] block-CSR row pointers of S (problem)
   const int32_t* s_diag;        // [C]   block index of the diagonal block of every row (problem)
   const int32_t* cta_row_ptr;   // [cl+1] rows owned by CTA k
@@ -139,6 +147,19 @@ size_t pcg_cluster_carve(PcgClusterArgs& a);  // fills a.m from the maxima, retu
 int pcg_cluster_max_smem(int device);
 bool pcg_cluster_fits(int device, int cl, size_t smem_bytes);
 cudaError_t launch_pcg_cluster(const PcgClusterArgs& a, int cl, size_t smem_bytes, cudaStream_t st);
+
+// coarse space of the two-level preconditioner (coarse.cu)
+constexpr int COARSE_MAX_GROUPS = 18;  // 7 * 18 = 126 <= 128: a 4 x 4 register tile per thread in k_coarse_invert
+constexpr int COARSE_MAX_DIM = 7 * COARSE_MAX_GROUPS;
+constexpr int COARSE_SPLIT = 8;  // partial coarse matrices of k_coarse_assemble, added in order by k_coarse_invert  // the dense inverse is formed by one CTA in shared memory
+struct CoarsePlan {
+  int G;
+  const int32_t* cb_ptr;   // [G*G+1] fine blocks of every coarse block (gi, gj)
+  const int32_t* cb_fine;  // [B] block indices of S, grouped by coarse block, CSR order inside
+};
+cudaError_t launch_coarse_setup(const CoarsePlan& cp, int C, const double* pose, const uint8_t* free_mask,
+                                const int32_t* s_row, const int32_t* s_col, const double* S, double* Zc, double* Ac,
+                                double* Ainv, cudaStream_t st);
 
 // ---- step ---------------------------------------------------------------------------------------
 void launch_cam_update(const ProblemView& pv, const double* pose, const double* y, double* pose_cand, double* scal,

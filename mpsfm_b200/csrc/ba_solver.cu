@@ -24,11 +24,11 @@ using namespace mpba;
 
 enum KernelSlot {
   KS_IMG_CHUNKS = 0, KS_IMG_FINALIZE, KS_POINTS_SCHUR, KS_S_FINALIZE, KS_PCG, KS_CAM_UPDATE, KS_BACK_SUBSTITUTE,
-  KS_REDUCE, KS_EVALUATE, KS_MISC, KS_SPARE0, KS_SPARE1
+  KS_REDUCE, KS_EVALUATE, KS_MISC, KS_COARSE, KS_BLOCK_INVERSE
 };
 static const char* kKernelNames[MPBA_NUM_KERNELS] = {
     "img_chunks", "img_finalize", "points", "schur_blocks", "pcg", "cam_update", "back_substitute",
-    "reduce", "evaluate", "misc", "spare0", "spare1"};
+    "reduce", "evaluate", "misc", "coarse_setup", "block_inverse"};
 
 struct TimedEvent {
   cudaEvent_t a, b;
@@ -104,6 +104,7 @@ size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 struct Workspace {
   double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *img_part, *c_img, *c_pt, *Hpp, *gp, *Hinv, *fac, *S,
       *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal;
+  double *Zc = nullptr, *Ac = nullptr, *Ainv = nullptr;  // coarse space (coarse.cu)
   int32_t* plan = nullptr;  // PCG cluster plan (pcg_cluster.cu)
   size_t plan_ints = 0;
   size_t bytes = 0;
@@ -111,7 +112,7 @@ struct Workspace {
 
 size_t plan_capacity_ints(const mpba_problem* p) {
   if (p->flags & MPBA_FLAG_STRUCTURE_ONLY) return 0;
-  return 8 * (size_t)p->num_upper + 3 * 17 + 64;
+  return 8 * (size_t)p->num_upper + 3 * 17 + 64 + (size_t)p->num_blocks + COARSE_MAX_GROUPS * COARSE_MAX_GROUPS + COARSE_MAX_GROUPS + 8;
 }
 
 // bump allocation; base == nullptr just measures
@@ -150,6 +151,12 @@ void carve(const mpba_problem* p, char* base, Workspace& w) {
   w.partial = take(2 * 2048 + 32);
   w.pt_part = take(nblk * PT_PART + 8);
   w.scal = take(S_COUNT);
+  {
+    const bool so = (p->flags & MPBA_FLAG_STRUCTURE_ONLY) != 0;
+    w.Zc = take(so ? 0 : C * 42);
+    w.Ac = take(so ? 0 : (size_t)COARSE_SPLIT * COARSE_MAX_DIM * COARSE_MAX_DIM);
+    w.Ainv = take(so ? 0 : (size_t)COARSE_MAX_DIM * COARSE_MAX_DIM);
+  }
   w.plan_ints = plan_capacity_ints(p);
   w.plan = reinterpret_cast<int32_t*>(take((w.plan_ints + 1) / 2));
   w.bytes = off;
@@ -204,6 +211,7 @@ struct Ctx {
   int cl = 0;
   size_t cl_smem = 0;
   PcgClusterArgs cla;
+  CoarsePlan coarse;  // coarse.G == 0: block-Jacobi only
 };
 
 int begin(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes, Ctx& c) {
@@ -253,9 +261,10 @@ int fetch_scalars(Ctx& c) {
 // the cluster-resident PCG (pcg_cluster.cu).  Runs once per C-ABI call on the host: it needs the
 // block-CSR structure (two small device-to-host copies), costs O(num_blocks) and uploads ~8 ints per
 // upper block.  Leaves c.cl == 0 when the system does not fit one cluster (the grid kernel is used).
-int build_pcg_cluster_plan(Ctx& c, const mpba_problem* prob, int pcg_kernel) {
+int build_pcg_cluster_plan(Ctx& c, const mpba_problem* prob, int pcg_kernel, int pcg_coarse) {
   mpba_handle* h = c.h;
   c.cl = 0;
+  c.coarse.G = 0;
   if (c.structure_only || pcg_kernel == 1) return MPBA_OK;
   const int C = prob->num_images, B = prob->num_blocks;
   std::vector<int32_t> rp(C + 1), col(B);
@@ -272,7 +281,7 @@ int build_pcg_cluster_plan(Ctx& c, const mpba_problem* prob, int pcg_kernel) {
     }
     U += nup[i];
   }
-  if ((size_t)(8 * (size_t)U + 3 * 17 + 64) > c.w.plan_ints) return MPBA_OK;  // inconsistent num_upper: stay on the grid kernel
+  if (plan_capacity_ints(prob) > c.w.plan_ints || (size_t)(8 * (size_t)U + 3 * 17 + 64) > c.w.plan_ints) return MPBA_OK;
 
   const int max_smem = pcg_cluster_max_smem(h->device);
   for (int cl = 1; cl <= 16; cl *= 2) {
@@ -347,14 +356,46 @@ int build_pcg_cluster_plan(Ctx& c, const mpba_problem* prob, int pcg_kernel) {
     a.max_full = max_full;
     a.max_halo = max_halo;
     a.max_extra = std::max(1, max_blk - PCGC_THREADS);
-    const size_t smem = pcg_cluster_carve(a);
+    // coarse space: gpc groups of consecutive images per CTA, at least two images per group
+    int min_rows = C;
+    for (int k = 0; k < cl; ++k) min_rows = std::min(min_rows, crow[k + 1] - crow[k]);
+    int gpc = (pcg_coarse == 1 || C < 8) ? 0 : std::min(COARSE_MAX_GROUPS / cl, std::max(min_rows / 2, 0));
+    size_t smem = 0;
+    for (;; --gpc) {
+      a.gpc = gpc > 0 ? gpc : 0;
+      a.G = a.gpc * cl;
+      a.nc = 7 * a.G;
+      smem = pcg_cluster_carve(a);
+      if (a.gpc == 0 || (int)smem <= max_smem) break;
+    }
     if ((int)smem > max_smem || !pcg_cluster_fits(h->device, cl, smem)) {
       if (cl == 16) return MPBA_OK;
       continue;
     }
+    std::vector<int32_t> grp_row, cb_ptr, cb_fine;
+    if (a.G) {
+      const int G = a.G;
+      grp_row.resize(G + 1);
+      std::vector<int> grp_of(C);
+      for (int k = 0; k < cl; ++k) {
+        const int r0 = crow[k], nr = crow[k + 1] - crow[k];
+        for (int g = 0; g <= a.gpc; ++g) grp_row[k * a.gpc + g] = r0 + (int)((long long)nr * g / a.gpc);
+      }
+      grp_row[G] = C;
+      for (int g = 0; g < G; ++g)
+        for (int i = grp_row[g]; i < grp_row[g + 1]; ++i) grp_of[i] = g;
+      cb_ptr.assign((size_t)G * G + 1, 0);
+      for (int i = 0; i < C; ++i)
+        for (int b = rp[i]; b < rp[i + 1]; ++b) ++cb_ptr[(size_t)grp_of[i] * G + grp_of[col[b]] + 1];
+      for (size_t k = 0; k < (size_t)G * G; ++k) cb_ptr[k + 1] += cb_ptr[k];
+      cb_fine.resize(B);
+      std::vector<int32_t> fill(cb_ptr.begin(), cb_ptr.end() - 1);
+      for (int i = 0; i < C; ++i)
+        for (int b = rp[i]; b < rp[i + 1]; ++b) cb_fine[fill[(size_t)grp_of[i] * G + grp_of[col[b]]]++] = b;
+    }
     // pack, stage, upload
     const size_t nU = ub_sblk.size(), nH = halo_cta.size();
-    const size_t total = 3 * (size_t)(cl + 1) + 6 * nU + 2 * nH;
+    const size_t total = 3 * (size_t)(cl + 1) + 6 * nU + 2 * nH + grp_row.size() + cb_ptr.size() + cb_fine.size();
     if (total > c.w.plan_ints) return MPBA_OK;
     if (h->h_stage_ints < total) {
       if (h->h_stage) cudaFreeHost(h->h_stage);
@@ -384,6 +425,12 @@ int build_pcg_cluster_plan(Ctx& c, const mpba_problem* prob, int pcg_kernel) {
     a.ub_tidx = put(ub_tidx);
     a.halo_cta = put(halo_cta);
     a.halo_rowl = put(halo_rowl);
+    a.grp_row_ptr = put(grp_row);
+    c.coarse.G = a.G;
+    c.coarse.cb_ptr = put(cb_ptr);
+    c.coarse.cb_fine = put(cb_fine);
+    a.Zc = c.w.Zc;
+    a.Ainv = c.w.Ainv;
     CU(cudaMemcpyAsync(dev, st, off * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
     a.row_ptr = prob->s_row_ptr;
     a.s_diag = prob->s_diag;
@@ -412,8 +459,18 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
   if (!want_system) return MPBA_OK;
   if (schur) {
     {
-      Timer t(h, KS_S_FINALIZE, 2);
-      launch_schur_blocks(c.pv, c.w.fac, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.S, c.w.rhs, c.w.Minv, h->stream);
+      Timer t(h, KS_S_FINALIZE);
+      launch_schur_blocks(c.pv, c.w.fac, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.S, c.w.rhs, h->stream);
+    }
+    {
+      Timer t(h, KS_BLOCK_INVERSE);
+      launch_block_inverse(c.pv, c.w.S, c.w.Minv, h->stream);
+    }
+    if (c.cl > 0 && c.coarse.G > 0) {
+      Timer t(h, KS_COARSE, 3);
+      cudaError_t e = launch_coarse_setup(c.coarse, c.pv.C, pose, c.pv.img_free_mask, c.pv.s_row, c.pv.s_col, c.w.S,
+                                          c.w.Zc, c.w.Ac, c.w.Ainv, h->stream);
+      if (e != cudaSuccess) return fail(h, MPBA_E_CUDA, std::string("coarse setup: ") + cudaGetErrorString(e));
     }
     {
       Timer t(h, KS_PCG);
@@ -468,7 +525,7 @@ void mpba_default_options(mpba_options* o) {
   o->profile = 0;
   o->verbose = 0;
   o->pcg_kernel = 0;
-  o->reserved = 0;
+  o->pcg_coarse = 0;
 }
 
 int mpba_create(mpba_handle** out, int device, void* cuda_stream) {
@@ -611,7 +668,7 @@ int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspac
   reset_profile(h, 0);
   mpba_options opt;
   if (opt_in) opt = *opt_in; else mpba_default_options(&opt);
-  rc = build_pcg_cluster_plan(c, prob, opt.pcg_kernel);
+  rc = build_pcg_cluster_plan(c, prob, opt.pcg_kernel, opt.pcg_coarse);
   if (rc) return rc;
   launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[0], h->stream);
   enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 1, opt.jacobi_scaling);
@@ -637,7 +694,7 @@ int mpba_solve(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t
   mpba_options opt;
   if (opt_in) opt = *opt_in; else mpba_default_options(&opt);
   reset_profile(h, opt.profile);
-  rc = build_pcg_cluster_plan(c, prob, opt.pcg_kernel);
+  rc = build_pcg_cluster_plan(c, prob, opt.pcg_kernel, opt.pcg_coarse);
   if (rc) return rc;
   mpba_iteration* its = sum->iterations;
   const int cap = its ? sum->capacity : 0;

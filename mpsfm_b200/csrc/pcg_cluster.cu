@@ -68,6 +68,73 @@ __device__ __forceinline__ void load6(const double* src, double (&v)[6]) {
   v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y;
 }
 
+// u = M^-1 r on the owned rows, r and u in shared memory.  M^-1 = blockdiag(S)^-1 + Z (Z^T S Z)^-1 Z^T (coarse.cu);
+// without a coarse space (A.G == 0) only the block-Jacobi term.  Contains one cluster barrier when A.G != 0: every
+// CTA must call it at the same point.  Z^T r of a group is formed by one warp (fixed order) and stored to every
+// CTA; each CTA then multiplies its own rows of A_c^-1.
+__device__ __forceinline__ void apply_precond(double* smem, const int* smi, const PcgClusterArgs& A,
+                                              cg::cluster_group& cluster, int rank, int CL, int nrows) {
+  const PcgClusterCarve& m = A.m;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __syncthreads();  // r is complete
+  if (A.G) {
+    const int ntask = A.gpc * 7;
+    for (int task = warp; task < ntask; task += T / 32) {
+      const int gl = task / 7, a = task - 7 * gl;
+      const int i0 = smi[m.glrp + gl] * 6, i1 = smi[m.glrp + gl + 1] * 6;
+      double acc = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;  // independent chains: the loop is shared-memory latency bound
+      int idx = i0 + lane;
+      for (; idx + 96 < i1; idx += 128) {
+        acc += smem[m.zloc + idx * 7 + a] * smem[m.r + idx];
+        acc1 += smem[m.zloc + (idx + 32) * 7 + a] * smem[m.r + idx + 32];
+        acc2 += smem[m.zloc + (idx + 64) * 7 + a] * smem[m.r + idx + 64];
+        acc3 += smem[m.zloc + (idx + 96) * 7 + a] * smem[m.r + idx + 96];
+      }
+      for (; idx < i1; idx += 32) acc += smem[m.zloc + idx * 7 + a] * smem[m.r + idx];
+      acc = (acc + acc1) + (acc2 + acc3);
+      for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(FULL, acc, off);
+      if (lane < CL) {
+        double* dst = ((lane == rank) ? smem : cluster.map_shared_rank(smem, lane)) + m.rcall;
+        dst[(rank * A.gpc + gl) * 7 + a] = acc;
+      }
+    }
+    cluster.sync();  // D: Z^T r of every group is everywhere
+    for (int task = warp; task < ntask; task += T / 32) {
+      double acc = 0.0, acc1 = 0.0;
+      int k = lane;
+      for (; k + 32 < A.nc; k += 64) {
+        acc += smem[m.ainv + task * A.nc + k] * smem[m.rcall + k];
+        acc1 += smem[m.ainv + task * A.nc + k + 32] * smem[m.rcall + k + 32];
+      }
+      if (k < A.nc) acc += smem[m.ainv + task * A.nc + k] * smem[m.rcall + k];
+      acc += acc1;
+      for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(FULL, acc, off);
+      if (lane == 0) smem[m.ec + task] = acc;
+    }
+    __syncthreads();
+  }
+  for (int q = tid; q < nrows * 6; q += T) {
+    const int lr = q / 6, c = q - 6 * lr;
+    double z = 0.0, z1 = 0.0, zc0 = 0.0, zc1 = 0.0;
+#pragma unroll
+    for (int j = 0; j < 6; j += 2) {
+      z += smem[m.minv + lr * 36 + c * 6 + j] * smem[m.r + lr * 6 + j];
+      z1 += smem[m.minv + lr * 36 + c * 6 + j + 1] * smem[m.r + lr * 6 + j + 1];
+    }
+    if (A.G) {
+      int gl = 0;
+      while (lr >= smi[m.glrp + gl + 1]) ++gl;
+#pragma unroll
+      for (int a = 0; a < 6; a += 2) {
+        zc0 += smem[m.zloc + q * 7 + a] * smem[m.ec + gl * 7 + a];
+        zc1 += smem[m.zloc + q * 7 + a + 1] * smem[m.ec + gl * 7 + a + 1];
+      }
+      zc0 += smem[m.zloc + q * 7 + 6] * smem[m.ec + gl * 7 + 6];
+    }
+    smem[m.u + q] = (z + z1) + (zc0 + zc1);
+  }
+}
+
 // row items: warp w, lane l < 30 -> row slot 5 w + l / 6 (+ 5 * warps per pass), component l % 6, so the six
 // components of a row sit in one warp and M^-1 r is a shuffle product
 constexpr int ROWS_PER_PASS = 5 * (T / 32);
@@ -128,21 +195,14 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
     smem[m.p + k] = 0.0;
     smem[m.s + k] = 0.0;
   }
-  __syncthreads();
-  const int sub = lane / 6, comp = lane % 6, base_lane = 6 * sub;
-  const bool row_lane = lane < 30;
-  for (int lr0 = 0; lr0 < nrows; lr0 += ROWS_PER_PASS) {
-    const int lr = lr0 + 5 * warp + sub;
-    const bool act = row_lane && lr < nrows;
-    const double rv = act ? smem[m.r + lr * 6 + comp] : 0.0;
-    double z = 0.0;
-#pragma unroll
-    for (int j = 0; j < 6; ++j) {
-      const double rj = __shfl_sync(FULL, rv, base_lane + j);
-      if (act) z += smem[m.minv + lr * 36 + comp * 6 + j] * rj;
-    }
-    if (act) smem[m.u + lr * 6 + comp] = z;
+  if (A.G) {
+    for (int k = tid; k < nrows * 42; k += T) smem[m.zloc + k] = A.Zc[(size_t)row0 * 42 + k];
+    for (int k = tid; k < A.gpc * 7 * A.nc; k += T) smem[m.ainv + k] = A.Ainv[(size_t)rank * A.gpc * 7 * A.nc + k];
+    for (int k = tid; k <= A.gpc; k += T) smi[m.glrp + k] = A.grp_row_ptr[rank * A.gpc + k] - row0;
   }
+  const int sub = lane / 6, comp = lane % 6;
+  const bool row_lane = lane < 30;
+  apply_precond(smem, smi, A, cluster, rank, CL, nrows);
 
   double gamma0 = 0.0, tol2g0 = 0.0, inv_gamma_prev = 0.0, inv_alpha_prev = 0.0, last_gamma = 0.0;
   int iters = 0, flag = 1;
@@ -297,7 +357,6 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
     for (int lr0 = 0; lr0 < nrows; lr0 += ROWS_PER_PASS) {
       const int lr = lr0 + 5 * warp + sub;
       const bool act = row_lane && lr < nrows;
-      double rn = 0.0;
       if (act) {
         const int o = lr * 6 + comp;
         const double pn = smem[m.u + o] + beta * smem[m.p + o];
@@ -305,17 +364,10 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
         smem[m.p + o] = pn;
         smem[m.s + o] = sn;
         smem[m.x + o] += alpha * pn;
-        rn = smem[m.r + o] - alpha * sn;
-        smem[m.r + o] = rn;
+        smem[m.r + o] -= alpha * sn;
       }
-      double z = 0.0;
-#pragma unroll
-      for (int j = 0; j < 6; ++j) {
-        const double rj = __shfl_sync(FULL, rn, base_lane + j);
-        if (act) z += smem[m.minv + lr * 36 + comp * 6 + j] * rj;
-      }
-      if (act) smem[m.u + lr * 6 + comp] = z;
     }
+    apply_precond(smem, smi, A, cluster, rank, CL, nrows);
     inv_gamma_prev = 1.0 / gamma;
     inv_alpha_prev = denom * inv_gamma_prev;
 #ifdef MPBA_PCG_TIMING
@@ -363,7 +415,13 @@ size_t pcg_cluster_carve(PcgClusterArgs& A) {
   c.extra = o; o += A.max_extra * 36;
   c.parts = o; o += 2 * 16;
   c.red = o;   o += 2 * (T / 32) + 2;
+  c.zloc = o;  o += A.G ? A.max_rows * 42 : 0;
+  c.ainv = o;  o += A.gpc * 7 * A.nc;
+  c.rcall = o; o += A.nc;
+  c.ec = o;    o += A.gpc * 7;
   o += o & 1;
+  c.glrp = 2 * o;
+  o += (A.gpc + 4) / 2;
   c.rp = 2 * o;
   c.hdesc = c.rp + A.max_rows + 2;
   c.xmeta = c.hdesc + A.max_halo;

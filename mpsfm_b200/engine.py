@@ -78,7 +78,7 @@ class MpbaOptions(C.Structure):
         ("min_lm_diagonal", C.c_double), ("max_lm_diagonal", C.c_double),
         ("function_tolerance", C.c_double), ("gradient_tolerance", C.c_double),
         ("parameter_tolerance", C.c_double), ("pcg_tolerance", C.c_double),
-        ("profile", C.c_int32), ("verbose", C.c_int32), ("pcg_kernel", C.c_int32), ("reserved", C.c_int32),
+        ("profile", C.c_int32), ("verbose", C.c_int32), ("pcg_kernel", C.c_int32), ("pcg_coarse", C.c_int32),
     ]
 
 
