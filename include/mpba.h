@@ -184,7 +184,7 @@ typedef struct mpba_summary {
 } mpba_summary;
 
 /* names of the kernels for mpba_kernel_times, in slot order */
-#define MPBA_NUM_KERNELS 12
+#define MPBA_NUM_KERNELS 13
 
 typedef struct mpba_handle mpba_handle;
 
@@ -228,6 +228,40 @@ int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspac
  * and pt_xyz in place to the best state visited. */
 int mpba_solve(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
                const mpba_options* opt, mpba_summary* summary);
+
+/* ---- sharded solve: one process per GPU, one problem across `world` GPUs of a box ---------------------------
+ * BASELINE.json north star: "observations are sharded by camera across the GPUs ... the partial reduced-camera-
+ * system blocks ... are combined with NCCL allreduce over NVLink".  The path has two reduction keys, so every rank
+ * holds two shards of the observations ("Multi-GPU"):
+ *   image order: the chunks of its OWN images  [img_begin, img_end)  -> Hcc, gc, cost of those images,
+ *   track order: the tracks of its OWN points  [pt_begin, pt_end)    -> Hpp, gp, Schur factors, back-substitution.
+ * In the rank's mpba_problem every per-image / per-point array is still indexed globally (num_images, num_points
+ * are the global counts; poses, points and the structure of the reduced camera system are replicated), img_ptr /
+ * img_chunk_ptr / pt_ptr are global-length with EMPTY ranges for what the rank does not own, and the
+ * observation arrays, chunk lists and Schur item lists hold the rank's own entries only (local slot numbers).
+ * pt_begin = rank * pt_stride (equal counts for the all-gather of the candidate points; the padded point
+ * buffers live in the workspace, pt_xyz itself holds num_points entries).
+ * Collectives per LM iteration, on the handle's stream: all-reduce of the image blocks (27 C doubles) and of the
+ * partial reduced camera system (36 B + 6 C), all-gather of the candidate points (4 pt_stride per rank) and of
+ * one block of 24 scalars.  The reduced system is then solved redundantly by every rank (bitwise identical). */
+typedef struct mpba_shard {
+  int32_t rank, world;
+  int32_t pt_begin, pt_end, pt_stride;
+  int32_t img_begin, img_end;
+  int32_t reserved;
+} mpba_shard;
+
+#define MPBA_UNIQUE_ID_BYTES 128
+/* rank 0 creates the id (ncclGetUniqueId), the caller broadcasts it (torch.distributed / MPI / files), every rank
+ * calls mpba_comm_init (ncclCommInitRank).  NCCL is taken from the process (the libnccl.so.2 PyTorch already
+ * loaded) or dlopen'ed from nccl_library (NULL: default search path).  HOST pointers. */
+int mpba_comm_unique_id(void* id, const char* nccl_library);
+int mpba_comm_init(mpba_handle* h, int world, int rank, const void* id, const char* nccl_library);
+int mpba_workspace_bytes_sharded(const mpba_problem* prob, const mpba_shard* shard, size_t* bytes);
+/* mpba_solve over the shards; every rank calls it with its own problem / shard and gets the full solution
+ * (img_pose, pt_xyz) and the same summary. */
+int mpba_solve_sharded(mpba_handle* h, const mpba_problem* prob, const mpba_shard* shard, void* workspace,
+                       size_t workspace_bytes, const mpba_options* opt, mpba_summary* summary);
 
 /* After a call with opt->profile: per-kernel summed device ms and launch counts (HOST arrays of
  * MPBA_NUM_KERNELS); names from mpba_kernel_name(slot). */

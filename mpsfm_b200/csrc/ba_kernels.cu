@@ -147,8 +147,7 @@ __global__ void __launch_bounds__(256) k_img_chunks(ProblemView pv, const double
 // one thread per (image, value): sums the image's chunk partials in chunk order
 __global__ void __launch_bounds__(256) k_img_finalize(ProblemView pv, const double* __restrict__ chunk_part,
                                                       double* __restrict__ Hc, double* __restrict__ gc,
-                                                      double* __restrict__ img_part, double* __restrict__ c_img,
-                                                      int compute_scaling, int jacobi_scaling) {
+                                                      double* __restrict__ img_part) {
   const int gid = blockIdx.x * 256 + threadIdx.x;
   const int i = gid >> 5, v = gid & 31;
   if (i >= pv.C || v >= 29) return;
@@ -163,7 +162,6 @@ __global__ void __launch_bounds__(256) k_img_finalize(ProblemView pv, const doub
     const bool fr = (mask >> r) & 1u, fc = (mask >> c) & 1u;
     const double val = (fr && fc) ? s : 0.0;
     Hc[(size_t)i * 21 + v] = val;
-    if (r == c && compute_scaling) c_img[(size_t)i * 6 + r] = fr ? (jacobi_scaling ? 1.0 / (1.0 + sqrt(val)) : 1.0) : 0.0;
   } else if (v < 27) {
     const int r = v - 21;
     gc[(size_t)i * 6 + r] = ((mask >> r) & 1u) ? s : 0.0;
@@ -172,8 +170,11 @@ __global__ void __launch_bounds__(256) k_img_finalize(ProblemView pv, const doub
   }
 }
 
-__global__ void __launch_bounds__(1024) k_img_scalars(int C, const double* __restrict__ img_part,
-                                                      const double* __restrict__ gc, double* __restrict__ scal) {
+__global__ void __launch_bounds__(1024) k_img_scalars(int C, const uint8_t* __restrict__ free_mask,
+                                                      const double* __restrict__ img_part,
+                                                      const double* __restrict__ Hc, const double* __restrict__ gc,
+                                                      double* __restrict__ c_img, int compute_scaling,
+                                                      int jacobi_scaling, double* __restrict__ scal) {
   __shared__ double sm[33];
   double cf = 0.0, cx = 0.0, gm = 0.0;
   for (int i = threadIdx.x; i < C; i += 1024) {
@@ -181,6 +182,15 @@ __global__ void __launch_bounds__(1024) k_img_scalars(int C, const double* __res
     cx += img_part[2 * (size_t)i + 1];
 #pragma unroll
     for (int j = 0; j < 6; ++j) gm = fmax(gm, fabs(gc[(size_t)i * 6 + j]));
+    if (compute_scaling) {
+      // Jacobi column scales c_j = 1 / (1 + |J_j|) of the image blocks (Ceres: fixed at iteration 0)
+      const unsigned mask = free_mask[i];
+#pragma unroll
+      for (int r = 0; r < 6; ++r) {
+        const double val = Hc[(size_t)i * 21 + upper_idx(r, r)];
+        c_img[(size_t)i * 6 + r] = ((mask >> r) & 1u) ? (jacobi_scaling ? 1.0 / (1.0 + sqrt(val)) : 1.0) : 0.0;
+      }
+    }
   }
   cf = block_sum<32>(cf, sm);
   cx = block_sum<32>(cx, sm);
@@ -234,8 +244,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_points(ProblemView pv, const dou
                                                        double* __restrict__ gp, double* __restrict__ Hinv,
                                                        double* __restrict__ fac, double* __restrict__ pt_part,
                                                        double* __restrict__ scal, int write_factors) {
-  const int p = blockIdx.x * PT_THREADS + threadIdx.x;
-  const bool valid = p < pv.P;
+  const int p = pv.p0 + blockIdx.x * PT_THREADS + threadIdx.x;
+  const bool valid = p < pv.p1;
   const bool active = valid && pv.pt_const[p] == 0;
   int beg = 0, end = 0;
   if (active) {
@@ -374,7 +384,8 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
                                                              const double* __restrict__ Hc,
                                                              const double* __restrict__ gc,
                                                              const double* __restrict__ c_img, LmDiag lm,
-                                                             double* __restrict__ S, double* __restrict__ rhs) {
+                                                             double* __restrict__ S, double* __restrict__ rhs,
+                                                             int partial) {
   const int u = blockIdx.x;
   const int blk = pv.u_block[u];
   const int i = pv.s_row[blk], j = pv.s_col[blk];
@@ -552,7 +563,10 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
     const int e = threadIdx.x, r = e / 6, c = e % 6;
     const bool fr = (mi >> r) & 1u, fc = (mj >> c) & 1u;
     double val;
-    if (diag) {
+    if (diag && partial) {
+      // this rank's tracks only; k_schur_finish completes the block after the all-reduce
+      S[(size_t)blk * 36 + e] = (fr && fc) ? -0.5 * (sm[0][e] + sm[0][c * 6 + r]) : 0.0;
+    } else if (diag) {
       if (fr && fc) {
         const int uidx = upper_idx(r < c ? r : c, r < c ? c : r);
         val = Hc[(size_t)i * 21 + uidx] - 0.5 * (sm[0][e] + sm[0][c * 6 + r]);
@@ -568,8 +582,50 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
     }
   } else if (diag && threadIdx.x >= 64 && threadIdx.x < 70) {
     const int r = threadIdx.x - 64;
-    rhs[(size_t)i * 6 + r] = ((mi >> r) & 1u) ? gc[(size_t)i * 6 + r] - sm[0][36 + r] : 0.0;
+    rhs[(size_t)i * 6 + r] = ((mi >> r) & 1u) ? (partial ? 0.0 : gc[(size_t)i * 6 + r]) - sm[0][36 + r] : 0.0;
   }
+}
+
+// Sharded solve, after the all-reduce of the partial blocks: S(i,i) += Hcc_i + D_i, rhs_i += gc_i, identity rows
+// on fixed tangent coordinates.  One thread per entry of a diagonal block (+ 6 for rhs).
+__global__ void __launch_bounds__(64) k_schur_finish(ProblemView pv, const double* __restrict__ Hc,
+                                                     const double* __restrict__ gc, const double* __restrict__ c_img,
+                                                     LmDiag lm, double* __restrict__ S, double* __restrict__ rhs) {
+  const int i = blockIdx.x;
+  const unsigned mi = pv.img_free_mask[i];
+  const int blk = pv.s_diag[i];
+  if (threadIdx.x < 36) {
+    const int e = threadIdx.x, r = e / 6, c = e % 6;
+    const bool fr = (mi >> r) & 1u, fc = (mi >> c) & 1u;
+    double val;
+    if (fr && fc) {
+      const int uidx = upper_idx(r < c ? r : c, r < c ? c : r);
+      val = Hc[(size_t)i * 21 + uidx] + S[(size_t)blk * 36 + e];
+      if (r == c) val += lm_damping(Hc[(size_t)i * 21 + uidx], c_img[(size_t)i * 6 + r], lm.radius, lm.lo, lm.hi);
+    } else {
+      val = (r == c) ? 1.0 : 0.0;
+    }
+    S[(size_t)blk * 36 + e] = val;
+  } else if (threadIdx.x < 42) {
+    const int r = threadIdx.x - 36;
+    rhs[(size_t)i * 6 + r] = ((mi >> r) & 1u) ? gc[(size_t)i * 6 + r] + rhs[(size_t)i * 6 + r] : 0.0;
+  }
+}
+
+// Per-rank scalar blocks, all-gathered -> one block, identical on every rank (fixed rank order).
+__global__ void k_combine_scalars(const double* __restrict__ scal_all, int world, double* __restrict__ scal) {
+  const int k = threadIdx.x;
+  if (k >= S_COUNT) return;
+  const bool is_sum = k == S_MCC || k == S_STEP2_P || k == S_XNORM2_P || k == S_STEP2_C || k == S_XNORM2_C ||
+                      k == S_BAD_POINTS;
+  const bool is_max = k == S_GMAX_P;
+  if (!is_sum && !is_max) return;  // cost, |gc|, PCG scalars are computed from replicated data
+  double v = 0.0;
+  for (int r = 0; r < world; ++r) {
+    const double x = scal_all[(size_t)r * S_COUNT + k];
+    v = is_sum ? v + x : fmax(v, x);
+  }
+  scal[k] = v;
 }
 
 // block-Jacobi preconditioner: inverse of each 6x6 diagonal block through its Cholesky factor
@@ -845,7 +901,8 @@ __global__ void __launch_bounds__(256) k_cam_update(ProblemView pv, const double
     const double* ps = pose + (size_t)i * 8;
     const double* yi = y + (size_t)i * 6;
     const unsigned mask = pv.img_free_mask[i];
-    const bool used = pv.img_ptr[i + 1] > pv.img_ptr[i];
+    // step norms of a sharded solve are summed over the ranks: every image counts at its owner only
+    const bool used = i >= pv.i0 && i < pv.i1 && pv.img_ptr[i + 1] > pv.img_ptr[i];
     const double q[4] = {ps[0], ps[1], ps[2], ps[3]};
     const double d[3] = {-yi[0], -yi[1], -yi[2]};
     double qn[4];
@@ -883,8 +940,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_back_substitute(ProblemView pv, 
                                                                 const double* __restrict__ Hinv,
                                                                 double* __restrict__ X_cand,
                                                                 double* __restrict__ pt_part) {
-  const int p = blockIdx.x * PT_THREADS + threadIdx.x;
-  const bool valid = p < pv.P;
+  const int p = pv.p0 + blockIdx.x * PT_THREADS + threadIdx.x;
+  const bool valid = p < pv.p1;
   double mcc = 0.0, step2 = 0.0, xn2 = 0.0;
   if (valid) {
     const bool is_const = pv.pt_const[p] != 0;
@@ -968,8 +1025,8 @@ __global__ void __launch_bounds__(1024) k_pt_scalars_step(const double* __restri
 __global__ void __launch_bounds__(PT_THREADS) k_evaluate(ProblemView pv, const double* __restrict__ pose,
                                                          const double* __restrict__ X, double* __restrict__ r_reproj,
                                                          double* __restrict__ r_depth) {
-  const int p = blockIdx.x * PT_THREADS + threadIdx.x;
-  if (p >= pv.P) return;
+  const int p = pv.p0 + blockIdx.x * PT_THREADS + threadIdx.x;
+  if (p >= pv.p1) return;
   double Xp[3];
   load_point(X, p, Xp);
   const size_t N = (size_t)pv.N;
@@ -1013,32 +1070,41 @@ void launch_img_chunks(const ProblemView& pv, const double* pose, const double* 
   if (pv.num_chunks > 0) k_img_chunks<<<pv.num_chunks, 256, 0, st>>>(pv, pose, X, chunk_part);
 }
 void launch_img_finalize(const ProblemView& pv, const double* chunk_part, double* Hc, double* gc, double* img_part,
-                         double* c_img, int compute_scaling, int jacobi_scaling, cudaStream_t st) {
+                         cudaStream_t st) {
   const int n = pv.C * 32;
-  k_img_finalize<<<(n + 255) / 256, 256, 0, st>>>(pv, chunk_part, Hc, gc, img_part, c_img, compute_scaling, jacobi_scaling);
+  k_img_finalize<<<(n + 255) / 256, 256, 0, st>>>(pv, chunk_part, Hc, gc, img_part);
 }
-void launch_img_scalars(const ProblemView& pv, const double* img_part, const double* gc, double* scal, cudaStream_t st) {
-  k_img_scalars<<<1, 1024, 0, st>>>(pv.C, img_part, gc, scal);
+void launch_img_scalars(const ProblemView& pv, const double* img_part, const double* Hc, const double* gc,
+                        double* c_img, int compute_scaling, int jacobi_scaling, double* scal, cudaStream_t st) {
+  k_img_scalars<<<1, 1024, 0, st>>>(pv.C, pv.img_free_mask, img_part, Hc, gc, c_img, compute_scaling, jacobi_scaling,
+                                    scal);
 }
 int points_grid(int P) { return (P + PT_THREADS - 1) / PT_THREADS; }
 void launch_points(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,
                    int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* fac,
                    double* pt_part, double* scal, int write_factors, cudaStream_t st) {
-  if (pv.P > 0)
-    k_points<<<points_grid(pv.P), PT_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp,
+  if (pv.p1 > pv.p0)
+    k_points<<<points_grid(pv.p1 - pv.p0), PT_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp,
                                                        Hinv, fac, pt_part, scal, write_factors);
 }
 void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaStream_t st) {
   k_pt_scalars_gmax<<<1, 1024, 0, st>>>(pt_part, nblk, scal);
 }
 void launch_schur_blocks(const ProblemView& pv, const double* fac, const double* Hc, const double* gc,
-                         const double* c_img, LmDiag lm, double* S, double* rhs, cudaStream_t st) {
+                         const double* c_img, LmDiag lm, double* S, double* rhs, int partial, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_schur_blocks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_STAGE_BYTES);
     attr_set = true;
   }
-  k_schur_blocks<<<pv.U, SB_THREADS, SB_STAGE_BYTES, st>>>(pv, fac, Hc, gc, c_img, lm, S, rhs);
+  k_schur_blocks<<<pv.U, SB_THREADS, SB_STAGE_BYTES, st>>>(pv, fac, Hc, gc, c_img, lm, S, rhs, partial);
+}
+void launch_schur_finish(const ProblemView& pv, const double* Hc, const double* gc, const double* c_img, LmDiag lm,
+                         double* S, double* rhs, cudaStream_t st) {
+  k_schur_finish<<<pv.C, 64, 0, st>>>(pv, Hc, gc, c_img, lm, S, rhs);
+}
+void launch_combine_scalars(const double* scal_all, int world, double* scal, cudaStream_t st) {
+  k_combine_scalars<<<1, 32, 0, st>>>(scal_all, world, scal);
 }
 void launch_block_inverse(const ProblemView& pv, const double* S, double* Minv, cudaStream_t st) {
   k_block_inverse<<<(pv.C + 127) / 128, 128, 0, st>>>(pv, S, Minv);
@@ -1088,15 +1154,15 @@ void launch_cam_update(const ProblemView& pv, const double* pose, const double* 
 void launch_back_substitute(const ProblemView& pv, const double* pose, const double* X, const double* y,
                             const double* Hpp, const double* gp, const double* Hinv, double* X_cand, double* pt_part,
                             cudaStream_t st) {
-  if (pv.P > 0)
-    k_back_substitute<<<points_grid(pv.P), PT_THREADS, 0, st>>>(pv, pose, X, y, Hpp, gp, Hinv, X_cand, pt_part);
+  if (pv.p1 > pv.p0)
+    k_back_substitute<<<points_grid(pv.p1 - pv.p0), PT_THREADS, 0, st>>>(pv, pose, X, y, Hpp, gp, Hinv, X_cand, pt_part);
 }
 void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, cudaStream_t st) {
   k_pt_scalars_step<<<1, 1024, 0, st>>>(pt_part, nblk, scal);
 }
 void launch_evaluate(const ProblemView& pv, const double* pose, const double* X, double* r_reproj, double* r_depth,
                      cudaStream_t st) {
-  if (pv.P > 0) k_evaluate<<<points_grid(pv.P), PT_THREADS, 0, st>>>(pv, pose, X, r_reproj, r_depth);
+  if (pv.p1 > pv.p0) k_evaluate<<<points_grid(pv.p1 - pv.p0), PT_THREADS, 0, st>>>(pv, pose, X, r_reproj, r_depth);
 }
 void launch_normalize_poses(int C, const double* in, double* out, cudaStream_t st) {
   if (C > 0) k_normalize_poses<<<(C + 127) / 128, 128, 0, st>>>(C, in, out);

@@ -35,6 +35,9 @@ constexpr int FAC_STRIDE = 16; // doubles per Schur factor record (128 B per obs
 
 struct ProblemView {
   int C, K, P, N, B, U, num_chunks;
+  // owned ranges of a sharded solve (mpba_shard): tracks of points outside [p0, p1) and image-order chunks of
+  // images outside [i0, i1) live on other ranks.  Unsharded: [0, P) and [0, C).
+  int p0, p1, i0, i1;
   const int32_t* img_camera;
   const uint8_t* img_free_mask;
   const double* img_shift_scale;
@@ -73,20 +76,28 @@ struct LmDiag {
 void launch_img_chunks(const ProblemView& pv, const double* pose, const double* X, double* chunk_part,
                        cudaStream_t st);
 void launch_img_finalize(const ProblemView& pv, const double* chunk_part, double* Hc, double* gc, double* img_part,
-                         double* c_img, int compute_scaling, int jacobi_scaling, cudaStream_t st);
-void launch_img_scalars(const ProblemView& pv, const double* img_part, const double* gc, double* scal,
-                        cudaStream_t st);
+                         cudaStream_t st);
+// cost / gradient-max scalars and (compute_scaling) the Jacobi column scales of the image blocks; runs after the
+// image blocks are complete (in a sharded solve: after their all-reduce)
+void launch_img_scalars(const ProblemView& pv, const double* img_part, const double* Hc, const double* gc,
+                        double* c_img, int compute_scaling, int jacobi_scaling, double* scal, cudaStream_t st);
 
 // ---- track order: Hpp, gp, point-block Cholesky, Schur factors ------------------------------------
 void launch_points(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,
                    int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* fac,
                    double* pt_part, double* scal, int write_factors, cudaStream_t st);
-int points_grid(int P);
+int points_grid(int num_owned_points);
 void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaStream_t st);
 
 // ---- reduced camera system ----------------------------------------------------------------------
+// partial != 0 (sharded solve): S / rhs receive only this rank's -sum over its own tracks; after the all-reduce
+// launch_schur_finish adds Hcc + D, gc and the identity rows of fixed tangent coordinates.
 void launch_schur_blocks(const ProblemView& pv, const double* fac, const double* Hc, const double* gc,
-                         const double* c_img, LmDiag lm, double* S, double* rhs, cudaStream_t st);
+                         const double* c_img, LmDiag lm, double* S, double* rhs, int partial, cudaStream_t st);
+void launch_schur_finish(const ProblemView& pv, const double* Hc, const double* gc, const double* c_img, LmDiag lm,
+                         double* S, double* rhs, cudaStream_t st);
+// scal_all [world][S_COUNT] (all-gathered per-rank scalar blocks) -> scal: sums / max in rank order
+void launch_combine_scalars(const double* scal_all, int world, double* scal, cudaStream_t st);
 void launch_block_inverse(const ProblemView& pv, const double* S, double* Minv, cudaStream_t st);
 struct PcgPlan {
   int grid, rows_per_cta, use_smem, max_local_blocks;

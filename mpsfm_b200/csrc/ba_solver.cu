@@ -19,16 +19,17 @@
 
 #include "../../include/mpba.h"
 #include "ba_kernels.cuh"
+#include "nccl_dyn.h"
 
 using namespace mpba;
 
 enum KernelSlot {
   KS_IMG_CHUNKS = 0, KS_IMG_FINALIZE, KS_POINTS_SCHUR, KS_S_FINALIZE, KS_PCG, KS_CAM_UPDATE, KS_BACK_SUBSTITUTE,
-  KS_REDUCE, KS_EVALUATE, KS_MISC, KS_COARSE, KS_BLOCK_INVERSE
+  KS_REDUCE, KS_EVALUATE, KS_MISC, KS_COARSE, KS_BLOCK_INVERSE, KS_COLLECTIVE
 };
 static const char* kKernelNames[MPBA_NUM_KERNELS] = {
     "img_chunks", "img_finalize", "points", "schur_blocks", "pcg", "cam_update", "back_substitute",
-    "reduce", "evaluate", "misc", "coarse_setup", "block_inverse"};
+    "reduce", "evaluate", "misc", "coarse_setup", "block_inverse", "nccl_collectives"};
 
 struct TimedEvent {
   cudaEvent_t a, b;
@@ -50,6 +51,9 @@ struct mpba_handle {
   int pcg_grid_sms = 0;
   int32_t* h_stage = nullptr;  // pinned staging for the PCG cluster plan
   size_t h_stage_ints = 0;
+  // sharded solve (mpba_comm_init)
+  ncclComm_t comm = nullptr;
+  int rank = 0, world = 1;
 };
 
 namespace {
@@ -58,6 +62,13 @@ int fail(mpba_handle* h, int code, const std::string& msg) {
   if (h) h->err = msg;
   return code;
 }
+
+#define NC(call)                                                                                       \
+  do {                                                                                                 \
+    ncclResult_t e_ = (call);                                                                          \
+    if (e_ != ncclSuccess)                                                                             \
+      return fail(h, MPBA_E_NCCL, std::string(#call) + ": " + nccl_api().GetErrorString(e_));          \
+  } while (0)
 
 #define CU(call)                                                                                       \
   do {                                                                                                 \
@@ -103,7 +114,7 @@ size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Workspace {
   double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *img_part, *c_img, *c_pt, *Hpp, *gp, *Hinv, *fac, *S,
-      *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal;
+      *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal, *scal_all;
   double *Zc = nullptr, *Ac = nullptr, *Ainv = nullptr;  // coarse space (coarse.cu)
   int32_t* plan = nullptr;  // PCG cluster plan (pcg_cluster.cu)
   size_t plan_ints = 0;
@@ -115,8 +126,9 @@ size_t plan_capacity_ints(const mpba_problem* p) {
   return 8 * (size_t)p->num_upper + 3 * 17 + 64 + (size_t)p->num_blocks + COARSE_MAX_GROUPS * COARSE_MAX_GROUPS + COARSE_MAX_GROUPS + 8;
 }
 
-// bump allocation; base == nullptr just measures
-void carve(const mpba_problem* p, char* base, Workspace& w) {
+// bump allocation; base == nullptr just measures.  sh != nullptr: sharded solve (per-point partial buffers cover
+// the owned points only, the point buffers are padded to world * pt_stride for the all-gather).
+void carve(const mpba_problem* p, const mpba_shard* sh, char* base, Workspace& w) {
   size_t off = 0;
   auto take = [&](size_t n_doubles) -> double* {
     double* ptr = base ? reinterpret_cast<double*>(base + off) : nullptr;
@@ -124,10 +136,11 @@ void carve(const mpba_problem* p, char* base, Workspace& w) {
     return ptr;
   };
   const size_t C = p->num_images, P = p->num_points, B = p->num_blocks;
-  const size_t nblk = (size_t)points_grid((int)P);
+  const size_t nblk = (size_t)points_grid(sh ? sh->pt_end - sh->pt_begin : (int)P);
+  const size_t Ppad = sh ? std::max(P, (size_t)sh->world * (size_t)sh->pt_stride) : P;
   for (int k = 0; k < 2; ++k) {
     w.pose[k] = take(C * 8);
-    w.X[k] = take(P * 4);
+    w.X[k] = take(Ppad * 4);
     w.Hc[k] = take(C * 21);
     w.gc[k] = take(C * 6);
   }
@@ -151,6 +164,7 @@ void carve(const mpba_problem* p, char* base, Workspace& w) {
   w.partial = take(2 * 2048 + 32);
   w.pt_part = take(nblk * PT_PART + 8);
   w.scal = take(S_COUNT);
+  w.scal_all = take(sh ? (size_t)sh->world * S_COUNT : 0);
   {
     const bool so = (p->flags & MPBA_FLAG_STRUCTURE_ONLY) != 0;
     w.Zc = take(so ? 0 : C * 42);
@@ -197,6 +211,7 @@ ProblemView view_of(const mpba_problem* p) {
   v.u_block = p->u_block; v.u_item_ptr = p->u_item_ptr; v.item_a = p->item_a; v.item_b = p->item_b;
   v.loss.reproj_loss = p->reproj_loss; v.loss.depth_loss = p->depth_loss;
   v.loss.reproj_scale = p->reproj_loss_scale; v.loss.reproj_weight = p->reproj_loss_weight;
+  v.p0 = 0; v.p1 = v.P; v.i0 = 0; v.i1 = v.C;
   return v;
 }
 
@@ -212,40 +227,92 @@ struct Ctx {
   size_t cl_smem = 0;
   PcgClusterArgs cla;
   CoarsePlan coarse;  // coarse.G == 0: block-Jacobi only
+  const mpba_shard* sh = nullptr;  // sharded solve
 };
 
-int begin(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes, Ctx& c) {
+int check_shard(mpba_handle* h, const mpba_problem* p, const mpba_shard* sh) {
+  if (!sh) return MPBA_OK;
+  if (!h->comm || h->world != sh->world || h->rank != sh->rank)
+    return fail(h, MPBA_E_NCCL, "sharded solve: call mpba_comm_init with the same world / rank first");
+  if (sh->world < 1 || sh->rank < 0 || sh->rank >= sh->world) return fail(h, MPBA_E_INVALID, "bad shard rank / world");
+  if (sh->pt_begin < 0 || sh->pt_end < sh->pt_begin || sh->pt_end > p->num_points || sh->pt_stride < 0 ||
+      sh->pt_begin != std::min<int64_t>((int64_t)sh->rank * sh->pt_stride, p->num_points) ||
+      sh->pt_end - sh->pt_begin > sh->pt_stride ||
+      (int64_t)sh->world * sh->pt_stride < p->num_points)
+    return fail(h, MPBA_E_INVALID, "shard point range must be [rank * pt_stride, ...) inside num_points, world * pt_stride >= num_points");
+  if (sh->img_begin < 0 || sh->img_end < sh->img_begin || sh->img_end > p->num_images)
+    return fail(h, MPBA_E_INVALID, "shard image range outside num_images");
+  return MPBA_OK;
+}
+
+int begin(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes, Ctx& c,
+          const mpba_shard* sh = nullptr) {
   if (!h) return MPBA_E_INVALID;
   int rc = check_problem(h, prob);
   if (rc) return rc;
+  rc = check_shard(h, prob, sh);
+  if (rc) return rc;
   Workspace probe;
-  carve(prob, nullptr, probe);
+  carve(prob, sh, nullptr, probe);
   if (!workspace || workspace_bytes < probe.bytes)
     return fail(h, MPBA_E_WORKSPACE, "workspace too small: need " + std::to_string(probe.bytes) + " bytes");
   CU(cudaSetDevice(h->device));
   c.h = h;
   c.pv = view_of(prob);
-  carve(prob, static_cast<char*>(workspace), c.w);
-  c.nblk = points_grid(prob->num_points);
+  carve(prob, sh, static_cast<char*>(workspace), c.w);
+  c.sh = sh;
+  if (sh) {
+    c.pv.p0 = sh->pt_begin; c.pv.p1 = sh->pt_end; c.pv.i0 = sh->img_begin; c.pv.i1 = sh->img_end;
+  }
+  c.nblk = points_grid(c.pv.p1 - c.pv.p0);
   c.structure_only = prob->flags & MPBA_FLAG_STRUCTURE_ONLY;
   c.max_row_blocks = prob->s_max_row_blocks;
   h->launch_count = 0;
   return MPBA_OK;
 }
 
-// cost / Hcc / gc of state (pose, X) into buffer set k
-void enqueue_image_pass(Ctx& c, const double* pose, const double* X, int k, int compute_scaling, int jacobi) {
+// cost / Hcc / gc of state (pose, X) into buffer set k.  Sharded: every rank reduces the chunks of its own images
+// (zeros elsewhere), the image blocks are then all-reduced -- a sum with exact zeros, so the result is the owner's
+// value bit for bit on every rank.
+int enqueue_image_pass(Ctx& c, const double* pose, const double* X, int k, int compute_scaling, int jacobi) {
   mpba_handle* h = c.h;
   {
     Timer t(h, KS_IMG_CHUNKS);
     launch_img_chunks(c.pv, pose, X, c.w.chunk_part, h->stream);
   }
-  {
-    Timer t(h, KS_IMG_FINALIZE, 2);
-    launch_img_finalize(c.pv, c.w.chunk_part, c.w.Hc[k], c.w.gc[k], c.w.img_part, c.w.c_img, compute_scaling, jacobi,
-                        h->stream);
-    launch_img_scalars(c.pv, c.w.img_part, c.w.gc[k], c.w.scal, h->stream);
+  if (c.sh) {
+    {
+      Timer t(h, KS_IMG_FINALIZE, 1);
+      launch_img_finalize(c.pv, c.w.chunk_part, c.w.Hc[k], c.w.gc[k], c.w.img_part, h->stream);
+    }
+    Timer t(h, KS_COLLECTIVE);
+    NcclApi& nc = nccl_api();
+    const size_t C = (size_t)c.pv.C;
+    NC(nc.GroupStart());
+    NC(nc.AllReduce(c.w.Hc[k], c.w.Hc[k], C * 21, ncclDouble, ncclSum, h->comm, h->stream));
+    NC(nc.AllReduce(c.w.gc[k], c.w.gc[k], C * 6, ncclDouble, ncclSum, h->comm, h->stream));
+    NC(nc.AllReduce(c.w.img_part, c.w.img_part, C * 2, ncclDouble, ncclSum, h->comm, h->stream));
+    NC(nc.GroupEnd());
+  } else {
+    Timer t(h, KS_IMG_FINALIZE, 1);
+    launch_img_finalize(c.pv, c.w.chunk_part, c.w.Hc[k], c.w.gc[k], c.w.img_part, h->stream);
   }
+  {
+    Timer t(h, KS_IMG_FINALIZE, 1);
+    launch_img_scalars(c.pv, c.w.img_part, c.w.Hc[k], c.w.gc[k], c.w.c_img, compute_scaling, jacobi, c.w.scal,
+                       h->stream);
+  }
+  return MPBA_OK;
+}
+
+// sharded: the per-rank sums of the point passes and of the camera step -> one block, identical on every rank
+int combine_scalars(Ctx& c) {
+  mpba_handle* h = c.h;
+  if (!c.sh) return MPBA_OK;
+  Timer t(h, KS_COLLECTIVE, 2);
+  NC(nccl_api().AllGather(c.w.scal, c.w.scal_all, S_COUNT, ncclDouble, h->comm, h->stream));
+  launch_combine_scalars(c.w.scal_all, c.sh->world, c.w.scal, h->stream);
+  return MPBA_OK;
 }
 
 int fetch_scalars(Ctx& c) {
@@ -460,7 +527,19 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
   if (schur) {
     {
       Timer t(h, KS_S_FINALIZE);
-      launch_schur_blocks(c.pv, c.w.fac, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.S, c.w.rhs, h->stream);
+      launch_schur_blocks(c.pv, c.w.fac, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.S, c.w.rhs, c.sh ? 1 : 0,
+                          h->stream);
+    }
+    if (c.sh) {
+      // partial reduced camera system of this rank's tracks -> all-reduce -> + Hcc + D, + gc (north star:
+      // "the partial reduced-camera-system blocks ... are combined with NCCL allreduce")
+      Timer t(h, KS_COLLECTIVE, 2);
+      NcclApi& nc = nccl_api();
+      NC(nc.GroupStart());
+      NC(nc.AllReduce(c.w.S, c.w.S, (size_t)c.pv.B * 36, ncclDouble, ncclSum, h->comm, h->stream));
+      NC(nc.AllReduce(c.w.rhs, c.w.rhs, (size_t)c.pv.C * 6, ncclDouble, ncclSum, h->comm, h->stream));
+      NC(nc.GroupEnd());
+      launch_schur_finish(c.pv, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.S, c.w.rhs, h->stream);
     }
     {
       Timer t(h, KS_BLOCK_INVERSE);
@@ -557,6 +636,7 @@ void mpba_destroy(mpba_handle* h) {
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->h_scal) cudaFreeHost(h->h_scal);
   if (h->h_stage) cudaFreeHost(h->h_stage);
+  if (h->comm) nccl_api().CommDestroy(h->comm);
   delete h;
 }
 
@@ -565,8 +645,47 @@ const char* mpba_last_error(const mpba_handle* h) { return h ? h->err.c_str() : 
 int mpba_workspace_bytes(const mpba_problem* prob, size_t* bytes) {
   if (!prob || !bytes) return MPBA_E_INVALID;
   Workspace w;
-  carve(prob, nullptr, w);
+  carve(prob, nullptr, nullptr, w);
   *bytes = w.bytes;
+  return MPBA_OK;
+}
+
+int mpba_workspace_bytes_sharded(const mpba_problem* prob, const mpba_shard* shard, size_t* bytes) {
+  if (!prob || !bytes || !shard) return MPBA_E_INVALID;
+  Workspace w;
+  carve(prob, shard, nullptr, w);
+  *bytes = w.bytes;
+  return MPBA_OK;
+}
+
+int mpba_comm_unique_id(void* id, const char* nccl_library) {
+  if (!id) return MPBA_E_INVALID;
+  static_assert(sizeof(ncclUniqueId) <= MPBA_UNIQUE_ID_BYTES, "ncclUniqueId larger than MPBA_UNIQUE_ID_BYTES");
+  NcclApi& nc = nccl_api();
+  if (!nc.load(nccl_library).empty()) return MPBA_E_NCCL;
+  ncclUniqueId uid;
+  if (nc.GetUniqueId(&uid) != ncclSuccess) return MPBA_E_NCCL;
+  memset(id, 0, MPBA_UNIQUE_ID_BYTES);
+  memcpy(id, &uid, sizeof(uid));
+  return MPBA_OK;
+}
+
+int mpba_comm_init(mpba_handle* h, int world, int rank, const void* id, const char* nccl_library) {
+  if (!h) return MPBA_E_INVALID;
+  if (!id || world < 1 || rank < 0 || rank >= world) return fail(h, MPBA_E_INVALID, "mpba_comm_init: bad world / rank / id");
+  NcclApi& nc = nccl_api();
+  const std::string err = nc.load(nccl_library);
+  if (!err.empty()) return fail(h, MPBA_E_NCCL, err);
+  CU(cudaSetDevice(h->device));
+  if (h->comm) {
+    nc.CommDestroy(h->comm);
+    h->comm = nullptr;
+  }
+  ncclUniqueId uid;
+  memcpy(&uid, id, sizeof(uid));
+  NC(nc.CommInitRank(&h->comm, world, uid, rank));
+  h->world = world;
+  h->rank = rank;
   return MPBA_OK;
 }
 
@@ -602,7 +721,8 @@ int mpba_evaluate(mpba_handle* h, const mpba_problem* prob, void* workspace, siz
     Timer t(h, KS_EVALUATE);
     launch_evaluate(c.pv, c.w.pose[0], prob->pt_xyz, r_reproj, r_depth, h->stream);
   }
-  enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 0, 1);
+  rc = enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 0, 1);
+  if (rc) return rc;
   rc = fetch_scalars(c);
   if (rc) return rc;
   if (cost) {
@@ -621,7 +741,8 @@ int mpba_linearize(mpba_handle* h, const mpba_problem* prob, void* workspace, si
   mpba_options opt;
   mpba_default_options(&opt);
   launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[0], h->stream);
-  enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 1, 1);
+  rc = enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 1, 1);
+  if (rc) return rc;
   LmDiag lm{opt.initial_trust_region_radius, opt.min_lm_diagonal, opt.max_lm_diagonal};
   rc = enqueue_points_and_system(c, c.w.pose[0], prob->pt_xyz, 0, lm, 1, &opt, false);
   if (rc) return rc;
@@ -671,7 +792,8 @@ int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspac
   rc = build_pcg_cluster_plan(c, prob, opt.pcg_kernel, opt.pcg_coarse);
   if (rc) return rc;
   launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[0], h->stream);
-  enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 1, opt.jacobi_scaling);
+  rc = enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 1, opt.jacobi_scaling);
+  if (rc) return rc;
   LmDiag lm{radius, opt.min_lm_diagonal, opt.max_lm_diagonal};
   rc = enqueue_points_and_system(c, c.w.pose[0], prob->pt_xyz, 0, lm, 1, &opt, true);
   if (rc) return rc;
@@ -685,10 +807,10 @@ int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspac
   return MPBA_OK;
 }
 
-int mpba_solve(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
-               const mpba_options* opt_in, mpba_summary* sum) {
+static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard* shard, void* workspace,
+                      size_t workspace_bytes, const mpba_options* opt_in, mpba_summary* sum) {
   Ctx c;
-  int rc = begin(h, prob, workspace, workspace_bytes, c);
+  int rc = begin(h, prob, workspace, workspace_bytes, c, shard);
   if (rc) return rc;
   if (!sum) return fail(h, MPBA_E_INVALID, "summary is NULL");
   mpba_options opt;
@@ -719,7 +841,8 @@ int mpba_solve(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t
     CU(cudaMemcpyAsync(c.w.X[cur], prob->pt_xyz, (size_t)c.pv.P * 4 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
 
   // ---- iteration zero
-  enqueue_image_pass(c, c.w.pose[cur], c.w.X[cur], cur, 1, opt.jacobi_scaling);
+  rc = enqueue_image_pass(c, c.w.pose[cur], c.w.X[cur], cur, 1, opt.jacobi_scaling);
+  if (rc) return rc;
   rc = fetch_scalars(c);
   if (rc) return rc;
   double x_cost = 0.5 * h->h_scal[S_COST_FREE];
@@ -773,8 +896,17 @@ int mpba_solve(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t
       Timer t(h, KS_REDUCE);
       launch_pt_scalars_step(c.w.pt_part, c.nblk, c.w.scal, h->stream);
     }
+    if (c.sh) {
+      // every rank wrote the candidates of its own points: all-gather in place (equal counts, pt_stride per rank)
+      Timer t(h, KS_COLLECTIVE);
+      const size_t cnt = (size_t)c.sh->pt_stride * 4;
+      NC(nccl_api().AllGather(c.w.X[cand] + (size_t)c.sh->rank * cnt, c.w.X[cand], cnt, ncclDouble, h->comm, h->stream));
+    }
     // cost (and, in case the step is accepted, Hcc / gc) at the candidate
-    enqueue_image_pass(c, c.w.pose[cand], c.w.X[cand], cand, 0, opt.jacobi_scaling);
+    rc = enqueue_image_pass(c, c.w.pose[cand], c.w.X[cand], cand, 0, opt.jacobi_scaling);
+    if (rc) return rc;
+    rc = combine_scalars(c);
+    if (rc) return rc;
     rc = fetch_scalars(c);
     if (rc) return rc;
     const double* s = h->h_scal;
@@ -895,6 +1027,18 @@ int mpba_solve(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t
   sum->solve_ms = ms;
   snprintf(sum->message, sizeof(sum->message), "%s", msg);
   return MPBA_OK;
+}
+
+int mpba_solve(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
+               const mpba_options* opt_in, mpba_summary* sum) {
+  return solve_impl(h, prob, nullptr, workspace, workspace_bytes, opt_in, sum);
+}
+
+int mpba_solve_sharded(mpba_handle* h, const mpba_problem* prob, const mpba_shard* shard, void* workspace,
+                       size_t workspace_bytes, const mpba_options* opt_in, mpba_summary* sum) {
+  if (!h) return MPBA_E_INVALID;
+  if (!shard) return fail(h, MPBA_E_INVALID, "shard is NULL");
+  return solve_impl(h, prob, shard, workspace, workspace_bytes, opt_in, sum);
 }
 
 }  // extern "C"

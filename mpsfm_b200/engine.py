@@ -28,7 +28,8 @@ from .problem import MAX_CAMERA_PARAMS, BundleProblem
 
 _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libmpba.so")
 MPBA_CHUNK = 1024
-MPBA_NUM_KERNELS = 12
+MPBA_NUM_KERNELS = 13
+MPBA_UNIQUE_ID_BYTES = 128
 FLAG_STRUCTURE_ONLY = 1
 
 TERMINATION = {0: "CONVERGENCE", 1: "NO_CONVERGENCE", 2: "FAILURE"}
@@ -66,6 +67,14 @@ class MpbaProblem(C.Structure):
         ("reproj_loss", C.c_int32), ("depth_loss", C.c_int32),
         ("reproj_loss_scale", C.c_double), ("reproj_loss_weight", C.c_double),
         ("flags", C.c_int32), ("s_max_row_blocks", C.c_int32),
+    ]
+
+
+class MpbaShard(C.Structure):
+    _fields_ = [
+        ("rank", C.c_int32), ("world", C.c_int32),
+        ("pt_begin", C.c_int32), ("pt_end", C.c_int32), ("pt_stride", C.c_int32),
+        ("img_begin", C.c_int32), ("img_end", C.c_int32), ("reserved", C.c_int32),
     ]
 
 
@@ -107,6 +116,7 @@ EXPORTS = (
     "mpba_version", "mpba_create", "mpba_destroy", "mpba_last_error", "mpba_default_options",
     "mpba_workspace_bytes", "mpba_evaluate", "mpba_linearize", "mpba_reduced_system", "mpba_solve",
     "mpba_kernel_times", "mpba_kernel_name", "mpba_point_covariances",
+    "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
 )
 
 _lib = None
@@ -138,6 +148,11 @@ def load_library(path: Optional[str] = None):
     lib.mpba_point_covariances.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t, C.c_void_p]
     lib.mpba_solve.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t,
                                C.POINTER(MpbaOptions), C.POINTER(MpbaSummary)]
+    lib.mpba_comm_unique_id.argtypes = [C.c_void_p, C.c_char_p]
+    lib.mpba_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_char_p]
+    lib.mpba_workspace_bytes_sharded.argtypes = [C.POINTER(MpbaProblem), C.POINTER(MpbaShard), C.POINTER(C.c_size_t)]
+    lib.mpba_solve_sharded.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.POINTER(MpbaShard), C.c_void_p, C.c_size_t,
+                                       C.POINTER(MpbaOptions), C.POINTER(MpbaSummary)]
     lib.mpba_kernel_times.argtypes = [C.c_void_p, _dp, C.POINTER(C.c_int64)]
     lib.mpba_kernel_name.argtypes = [C.c_int]
     lib.mpba_kernel_name.restype = C.c_char_p
@@ -336,6 +351,94 @@ def build_layout(problem: BundleProblem) -> HostLayout:
 
 
 # ----------------------------------------------------------------------------------------------
+# sharding (include/mpba.h: mpba_shard; DESIGN.md "Multi-GPU")
+# ----------------------------------------------------------------------------------------------
+@dataclasses.dataclass
+class ShardSpec:
+    rank: int
+    world: int
+    pt_begin: int
+    pt_end: int
+    pt_stride: int
+    img_begin: int
+    img_end: int
+
+
+def shard_ranges(lay: HostLayout, world: int):
+    """Owned ranges of every rank: images in contiguous ranges balanced by observation count (north star:
+    "observations are sharded by camera"), points in equal contiguous ranges (equal counts for the all-gather)."""
+    if world < 1:
+        raise ValueError("world must be >= 1")
+    targets = (np.arange(world + 1, dtype=np.int64) * int(lay.N)) // world
+    ib = np.searchsorted(lay.img_ptr.astype(np.int64), targets, side="left").astype(np.int64)
+    ib[0], ib[-1] = 0, lay.C
+    ib = np.maximum.accumulate(np.clip(ib, 0, lay.C))
+    stride = (lay.P + world - 1) // world if lay.P else 0
+    out = []
+    for r in range(world):
+        p0 = min(r * stride, lay.P)
+        out.append(ShardSpec(rank=r, world=world, pt_begin=p0, pt_end=min(p0 + stride, lay.P), pt_stride=stride,
+                             img_begin=int(ib[r]), img_end=int(ib[r + 1])))
+    return out
+
+
+def shard_layout(lay: HostLayout, rank: int, world: int):
+    """The rank's share of a layout: image-order chunks of its own images, tracks (and Schur items) of its own
+    points; poses, points and the reduced-system structure stay global.  Returns (HostLayout, ShardSpec)."""
+    spec = shard_ranges(lay, world)[rank]
+    s0, s1 = int(lay.pt_ptr[spec.pt_begin]), int(lay.pt_ptr[spec.pt_end])
+    c0, c1 = int(lay.img_ptr[spec.img_begin]), int(lay.img_ptr[spec.img_end])
+    n_loc = max(s1 - s0, c1 - c0, 1)  # one stride for both orders (the [3][N] depth rows use num_obs)
+
+    def pad1(a, fill=0):
+        out = np.full((n_loc,) + a.shape[1:], fill, dtype=a.dtype)
+        out[: a.shape[0]] = a
+        return out
+
+    def pad_rows(a):
+        out = np.zeros((a.shape[0], n_loc), dtype=a.dtype)
+        out[:, : a.shape[1]] = a
+        out[0, a.shape[1]:] = 1.0  # d = 1 on padding (never read: no slot points there)
+        return out
+
+    ch0, ch1 = int(lay.img_chunk_ptr[spec.img_begin]), int(lay.img_chunk_ptr[spec.img_end])
+    U = int(lay.u_block.shape[0])
+    if lay.item_a.shape[0]:
+        unit_of_item = np.repeat(np.arange(U, dtype=np.int64), np.diff(lay.u_item_ptr.astype(np.int64)))
+        keep = (lay.item_a >= s0) & (lay.item_a < s1)
+        item_a = (lay.item_a[keep].astype(np.int64) - s0).astype(np.int32)
+        item_b = (lay.item_b[keep].astype(np.int64) - s0).astype(np.int32)
+        u_item_ptr = _ptr_from_counts(np.bincount(unit_of_item[keep], minlength=U))
+    else:
+        item_a, item_b = lay.item_a, lay.item_b
+        u_item_ptr = np.zeros(U + 1, dtype=np.int32)
+    out = dataclasses.replace(
+        lay, N=n_loc,
+        pt_ptr=np.clip(lay.pt_ptr.astype(np.int64) - s0, 0, s1 - s0).astype(np.int32),
+        pm_img=pad1(lay.pm_img[s0:s1]), pm_xy=pad1(lay.pm_xy[s0:s1]), pm_depth=pad_rows(lay.pm_depth[:, s0:s1]),
+        pm_src=pad1(lay.pm_src[s0:s1], -1),
+        img_ptr=np.clip(lay.img_ptr.astype(np.int64) - c0, 0, c1 - c0).astype(np.int32),
+        cm_pt=pad1(lay.cm_pt[c0:c1]), cm_xy=pad1(lay.cm_xy[c0:c1]), cm_depth=pad_rows(lay.cm_depth[:, c0:c1]),
+        cm_src=pad1(lay.cm_src[c0:c1], -1),
+        chunk_img=lay.chunk_img[ch0:ch1].copy(),
+        chunk_begin=(lay.chunk_begin[ch0:ch1].astype(np.int64) - c0).astype(np.int32),
+        chunk_end=(lay.chunk_end[ch0:ch1].astype(np.int64) - c0).astype(np.int32),
+        img_chunk_ptr=np.clip(lay.img_chunk_ptr.astype(np.int64) - ch0, 0, ch1 - ch0).astype(np.int32),
+        u_item_ptr=u_item_ptr, item_a=item_a, item_b=item_b,
+    )
+    return out, spec
+
+
+def broadcast_bytes(payload: bytes, src: int = 0) -> bytes:
+    """Carry a small host blob (the NCCL id) from ``src`` to every rank over torch.distributed (any backend)."""
+    import torch.distributed as dist
+
+    box = [payload]
+    dist.broadcast_object_list(box, src=src)
+    return box[0]
+
+
+# ----------------------------------------------------------------------------------------------
 # device side
 # ----------------------------------------------------------------------------------------------
 _DEVICE_FIELDS = (
@@ -367,9 +470,14 @@ class SolveSummary:
 
 
 class BundleAdjuster:
-    """One problem resident on one GPU: buffers (torch), handle and workspace."""
+    """One problem resident on one GPU: buffers (torch), handle and workspace.
 
-    def __init__(self, problem, device: int = 0, layout: Optional[HostLayout] = None, pinned: bool = False):
+    ``shard=(rank, world)``: this process holds one shard of the problem (``shard_layout``) and ``solve`` runs
+    ``mpba_solve_sharded`` together with the other ranks; ``torch.distributed`` must be initialised (any backend:
+    it only carries the 128-byte NCCL id from rank 0 to the others)."""
+
+    def __init__(self, problem, device: int = 0, layout: Optional[HostLayout] = None, pinned: bool = False,
+                 shard: Optional[tuple] = None):
         import torch
 
         self.lib = load_library()
@@ -378,6 +486,12 @@ class BundleAdjuster:
         self.torch = torch
         self.device = torch.device("cuda", device)
         self.layout = layout if layout is not None else build_layout(problem)
+        self.full_layout = self.layout
+        self.shard = None
+        if shard is not None:  # world == 1 is allowed: the sharded code path on one GPU (tests)
+            self.layout, spec = shard_layout(self.full_layout, int(shard[0]), int(shard[1]))
+            self.shard = MpbaShard(rank=spec.rank, world=spec.world, pt_begin=spec.pt_begin, pt_end=spec.pt_end,
+                                   pt_stride=spec.pt_stride, img_begin=spec.img_begin, img_end=spec.img_end)
         lay = self.layout
         self.buf = {}
         self.h2d_bytes = 0
@@ -389,7 +503,7 @@ class BundleAdjuster:
                     t = t.pin_memory()
                 self.buf[name] = t.to(self.device, non_blocking=pinned)
                 self.h2d_bytes += arr.nbytes
-            for name in ("item_a", "item_b"):
+            for name in ("item_a", "item_b", "chunk_img", "chunk_begin", "chunk_end"):
                 if self.buf[name].numel() == 0:
                     self.buf[name] = torch.zeros(1, dtype=torch.int32, device=self.device)
             self.handle = C.c_void_p()
@@ -409,13 +523,37 @@ class BundleAdjuster:
             self.prob.flags = lay.flags
             self.prob.s_max_row_blocks = int(np.max(np.diff(lay.s_row_ptr))) if lay.C else 0
             nbytes = C.c_size_t()
-            self._check(self.lib.mpba_workspace_bytes(C.byref(self.prob), C.byref(nbytes)))
+            if self.shard is not None:
+                self._init_comm()
+                self._check(self.lib.mpba_workspace_bytes_sharded(C.byref(self.prob), C.byref(self.shard), C.byref(nbytes)))
+            else:
+                self._check(self.lib.mpba_workspace_bytes(C.byref(self.prob), C.byref(nbytes)))
             self.workspace = torch.empty(max(int(nbytes.value), 256), dtype=torch.uint8, device=self.device)
             self.workspace_bytes = int(nbytes.value)
         self._pose0 = self.buf["img_pose"].clone()
         self._xyz0 = self.buf["pt_xyz"].clone()
 
     # -- plumbing
+    def _init_comm(self):
+        """NCCL communicator of the library: rank 0 draws the id, torch.distributed carries it to the others."""
+        import torch.distributed as dist
+
+        have_group = dist.is_available() and dist.is_initialized()
+        if self.shard.world > 1 and not have_group:
+            raise EngineError("sharded solve needs an initialised torch.distributed process group")
+        ident = (C.c_uint8 * MPBA_UNIQUE_ID_BYTES)()
+        if self.shard.rank == 0:
+            rc = self.lib.mpba_comm_unique_id(ident, None)
+            if rc != 0:
+                raise EngineUnavailable(f"mpba_comm_unique_id failed with code {rc} (libnccl not loadable)")
+        if self.shard.world > 1:
+            ident = (C.c_uint8 * MPBA_UNIQUE_ID_BYTES).from_buffer_copy(broadcast_bytes(bytes(ident), src=0))
+        self._check(self.lib.mpba_comm_init(self.handle, self.shard.world, self.shard.rank, ident, None))
+
+    def _require_unsharded(self, what: str):
+        if self.shard is not None:
+            raise EngineError(f"{what} is a single-GPU entry point; a sharded BundleAdjuster only solves")
+
     def _check(self, rc: int):
         if rc != 0:
             msg = self.lib.mpba_last_error(self.handle)
@@ -459,6 +597,7 @@ class BundleAdjuster:
     def evaluate(self):
         """Raw residuals in NATURAL observation order: (reproj [N,2], depth [N] (nan where no prior),
         cost, fixed_cost)."""
+        self._require_unsharded("evaluate")
         torch, lay = self.torch, self.layout
         rr = torch.empty((lay.N, 2), dtype=torch.float64, device=self.device)
         rd = torch.empty((lay.N,), dtype=torch.float64, device=self.device)
@@ -477,6 +616,7 @@ class BundleAdjuster:
 
     def linearize(self):
         """(Hcc [C,6,6], gc [C,6], Hpp [P,3,3], gp [P,3], cost, fixed_cost) at the current state."""
+        self._require_unsharded("linearize")
         torch, lay = self.torch, self.layout
         Hcc = torch.empty((lay.C, 36), dtype=torch.float64, device=self.device)
         gc = torch.empty((lay.C, 6), dtype=torch.float64, device=self.device)
@@ -496,6 +636,7 @@ class BundleAdjuster:
 
     def point_covariances(self):
         """[P,3,3] covariance of every variable point conditioned on the poses (zeros for constant points)."""
+        self._require_unsharded("point_covariances")
         torch, lay = self.torch, self.layout
         cov = torch.empty((max(lay.P, 1), 6), dtype=torch.float64, device=self.device)
         ws, wsn = self._ws()
@@ -509,6 +650,7 @@ class BundleAdjuster:
 
     def reduced_system(self, radius: float = 1e4, options: Optional[MpbaOptions] = None):
         """(S blocks [B,6,6], rhs [C,6], y [C,6], pcg_iterations) of the damped normal equations."""
+        self._require_unsharded("reduced_system")
         torch, lay = self.torch, self.layout
         S = torch.empty((lay.num_blocks, 36), dtype=torch.float64, device=self.device)
         rhs = torch.empty((lay.C, 6), dtype=torch.float64, device=self.device)
@@ -529,7 +671,11 @@ class BundleAdjuster:
         sm.iterations = C.cast(rows, C.POINTER(MpbaIteration))
         sm.capacity = cap
         ws, wsn = self._ws()
-        self._check(self.lib.mpba_solve(self.handle, C.byref(self.prob), ws, wsn, C.byref(opt), C.byref(sm)))
+        if self.shard is not None:
+            self._check(self.lib.mpba_solve_sharded(self.handle, C.byref(self.prob), C.byref(self.shard), ws, wsn,
+                                                    C.byref(opt), C.byref(sm)))
+        else:
+            self._check(self.lib.mpba_solve(self.handle, C.byref(self.prob), ws, wsn, C.byref(opt), C.byref(sm)))
         n = min(sm.num_iterations + 1, cap)
         its = []
         for k in range(n):
