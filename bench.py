@@ -93,20 +93,27 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def algorithmic_bytes(lay):
-    """Algorithmic HBM bytes per launch of each pass (fixed before measuring)."""
-    N, P, C, B = lay.N, lay.P, lay.C, lay.num_blocks
+def algorithmic_bytes(lay, spec=None):
+    """Algorithmic HBM bytes per launch of each pass (fixed before measuring).
+    Sharded (spec): this rank's observations in each order, its own points, the points its images touch."""
+    C, B = lay.C, lay.num_blocks
     n_items = int(lay.item_a.shape[0])
-    n_act = int(lay.u_item_ptr[-1] and np.count_nonzero(lay.pt_const == 0))
+    if spec is None:
+        n_trk = n_img = lay.N
+        p_own = p_touch = lay.P
+    else:
+        n_trk, n_img = int(lay.pt_ptr[-1]), int(lay.img_ptr[-1])
+        p_own = spec.pt_end - spec.pt_begin
+        p_touch = int(np.unique(lay.cm_pt[:n_img]).shape[0])
     return {
         # 4 (point idx) + 16 (xy) + 24 (d,w,a) per observation, every point read at least once (32 B), chunk partials
-        "img_chunks": 44 * N + 32 * P + 256 * lay.num_chunks + 64 * C,
+        "img_chunks": 44 * n_img + 32 * p_touch + 256 * lay.num_chunks + 64 * C,
         # 4 (image idx) + 16 + 24 in and one 128 B Schur factor out per observation; per point: xyz, pt_ptr, c_pt in,
         # Hpp / gp / Hinv out
-        "points": (44 + 128) * N + (32 + 4 + 24 + 48 + 24 + 48) * P + 64 * C,
+        "points": (44 + 128) * n_trk + (32 + 4 + 24 + 48 + 24 + 48) * p_own + 64 * C,
         # every factor read at least once, 8 B per item, every block of S written once
-        "schur_blocks": 128 * N + 8 * n_items + 288 * B + (168 + 48 + 48) * C,
-        "back_substitute": 44 * N + (32 + 4 + 48 + 24 + 48 + 32) * P + 48 * C,
+        "schur_blocks": 128 * n_trk + 8 * n_items + 288 * B + (168 + 48 + 48) * C,
+        "back_substitute": 44 * n_trk + (32 + 4 + 48 + 24 + 48 + 32) * p_own + 48 * C,
     }
 
 
@@ -198,13 +205,19 @@ def run_gpu(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: mpsfm_b200 has no CPU fallback")
 
+    # N > 1: ONE scene of the named shape, sharded over the ranks (strong scaling; mpba_solve_sharded).
+    # --sharding replicas: every rank solves its own scene of that shape (weak scaling, no collective).
+    sharded = world > 1 and args.sharding == "shard"
     t0 = time.perf_counter()
-    prob = make_config(args.workload, seed=rank)  # weak scaling: every rank owns one scene of the named shape
+    prob = make_config(args.workload, seed=0 if sharded else rank)
     t_scene = time.perf_counter() - t0
     t0 = time.perf_counter()
-    lay = engine.build_layout(prob)
+    full = engine.build_layout(prob)
     t_layout = time.perf_counter() - t0
-    ba = engine.BundleAdjuster(prob, device=local, layout=lay)
+    shard = (rank, world) if sharded else None
+    ba = engine.BundleAdjuster(prob, device=local, layout=full, shard=shard)
+    lay = ba.layout
+    spec = engine.shard_ranges(full, world)[rank] if sharded else None
     opt = engine.default_options(profile=1, pcg_tolerance=args.pcg_tol, pcg_max_iterations=args.pcg_max_iter)
 
     def barrier():
@@ -240,34 +253,41 @@ def run_gpu(args):
     last = s
 
     # ---- end to end: host buffers -> device -> solve -> host
+    # the caller's arrays sit in pinned host memory (allocated once, like the device buffers); every step copies
+    # the WHOLE problem host -> device, solves, and reads poses + points back
     h2d = d2h = 0
     e2e_iters = 0
+    ba.close()
+    del ba
+    ba2 = engine.BundleAdjuster(prob, device=local, layout=full, pinned=True, shard=shard)
+    ba2.solve(opt)  # warm-up of the new handle (communicator, plans)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        ba2 = engine.BundleAdjuster(prob, device=local, layout=lay, pinned=True)
+        h2d = ba2.upload()
         s2 = ba2.solve(opt)
         q, t, X = ba2.state()
         e2e_iters += s2.num_iterations
-        h2d = ba2.h2d_bytes
         d2h = lay.C * 64 + lay.P * 32
-        ba2.close()
-        del ba2
     barrier()
     e2e_s = time.perf_counter() - t0
+    ba2.close()
 
     if dist is not None:
         red = torch.tensor([ms_total, e2e_s], dtype=torch.float64, device="cuda")
         dist.all_reduce(red, op=dist.ReduceOp.MAX)
         ms_total, e2e_s = float(red[0]), float(red[1])
-        cnt = torch.tensor([iters, e2e_iters, launches], dtype=torch.float64, device="cuda")
+        cnt = torch.tensor([iters, e2e_iters, launches, h2d, d2h], dtype=torch.float64, device="cuda")
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-        iters, e2e_iters, launches = int(cnt[0]), int(cnt[1]), int(cnt[2])
+        if sharded:  # one job: its LM iterations count once; launches and copies are summed over the ranks
+            launches, h2d, d2h = int(cnt[2]), int(cnt[3]), int(cnt[4])
+        else:
+            iters, e2e_iters, launches, h2d, d2h = (int(x) for x in cnt)
     if rank != 0:
         return
 
     peak, peak_src = _peaks()
-    ab = algorithmic_bytes(lay)
+    ab = algorithmic_bytes(lay, spec)
     top = max((k for k in ktimes if k in ab), key=lambda k: ktimes[k][0], default=None)
     roof = None
     per_kernel = {}
@@ -286,11 +306,14 @@ def run_gpu(args):
     C_, P_, L_ = CONFIGS[args.workload]
     line = {
         "metric": METRIC, "value": iters / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+        "scaling": "strong" if sharded else "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {
             "workload": args.workload, "images": C_, "points": P_, "observations": P_ * L_,
-            "sharding": "one scene per rank" if world > 1 else "single GPU",
+            "sharding": ("one scene sharded over the ranks: image-order chunks by camera, tracks by point, NCCL "
+                         "all-reduce of the partial reduced camera system (mpba_solve_sharded)") if sharded
+            else ("one scene per rank" if world > 1 else "single GPU"),
             "camera_model": prob.cam_model.tolist(), "reproj_loss": int(prob.reproj_loss), "depth_loss": int(prob.depth_loss),
             "l2": "inputs larger than L2" if lay.N * 88 > 126e6 else "inputs fit in L2 (small workload; see DESIGN.md)",
             "lm_iterations_per_solve": last.num_iterations, "termination": last.message,
@@ -321,6 +344,7 @@ def main():
     ap.add_argument("--pcg-max-iter", dest="pcg_max_iter", type=int, default=2000)
     ap.add_argument("--ref-obs", dest="ref_obs", type=int, default=40_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sharding", default="shard", choices=["shard", "replicas"])
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -494,6 +494,7 @@ class BundleAdjuster:
                                    pt_stride=spec.pt_stride, img_begin=spec.img_begin, img_end=spec.img_end)
         lay = self.layout
         self.buf = {}
+        self.host = {}  # pinned staging copies of the problem arrays (pinned=True): source of upload()
         self.h2d_bytes = 0
         with torch.cuda.device(self.device):
             for name in _DEVICE_FIELDS:
@@ -501,6 +502,7 @@ class BundleAdjuster:
                 t = torch.from_numpy(arr)
                 if pinned:
                     t = t.pin_memory()
+                    self.host[name] = t
                 self.buf[name] = t.to(self.device, non_blocking=pinned)
                 self.h2d_bytes += arr.nbytes
             for name in ("item_a", "item_b", "chunk_img", "chunk_begin", "chunk_end"):
@@ -569,6 +571,18 @@ class BundleAdjuster:
             self.close()
         except Exception:
             pass
+
+    def upload(self):
+        """Host -> device copy of the whole problem (every array of mpba_problem, initial poses and points
+        included) from the pinned staging buffers, on the current stream: the H2D leg of an end-to-end solve."""
+        if not self.host:
+            raise EngineError("upload() needs a BundleAdjuster created with pinned=True")
+        n = 0
+        for name, t in self.host.items():
+            if t.numel():
+                self.buf[name].copy_(t, non_blocking=True)
+                n += t.numel() * t.element_size()
+        return n
 
     def reset_state(self):
         """Restore the poses / points the problem was created with (device-to-device)."""
