@@ -31,7 +31,7 @@ struct ImgConst {
   double R[9];
   const double* prm;
   int model;
-  double b, s;
+  double b, es;  // depth prior shift, exp(log-scale) (slot 7 of the pose record)
 };
 
 __device__ __forceinline__ void load_img(const ProblemView& pv, const double* __restrict__ pose, int img, ImgConst& ic) {
@@ -43,9 +43,8 @@ __device__ __forceinline__ void load_img(const ProblemView& pv, const double* __
   const int cam = __ldg(pv.img_camera + img);
   ic.model = __ldg(pv.cam_model + cam);
   ic.prm = pv.cam_params + (size_t)MPBA_MAX_PRM * cam;
-  const double2 ss = __ldg(reinterpret_cast<const double2*>(pv.img_shift_scale) + img);
-  ic.b = ss.x;
-  ic.s = ss.y;
+  ic.b = __ldg(pv.img_shift_scale + 2 * (size_t)img);
+  ic.es = d.y;
 }
 
 __device__ __forceinline__ void load_point(const double* __restrict__ X, int p, double out[3]) {
@@ -115,7 +114,7 @@ __global__ void __launch_bounds__(256) k_img_chunks(ProblemView pv, const double
     const double2 o2 = __ldg(xy + k);
     const double d = __ldg(dd + k), w = __ldg(dd + N + k), a = __ldg(dd + 2 * N + k);
     ObsLin o;
-    linearize_obs<true, true>(ic.pose, ic.R, Xp, ic.model, prm, o2.x, o2.y, d, w, a, ic.b, ic.s, pv.loss, o);
+    linearize_obs<true, true>(ic.pose, ic.R, Xp, ic.model, prm, o2.x, o2.y, d, w, a, ic.b, ic.es, pv.loss, o);
     double H[21], g[6];
     gt_n_g_upper(o.prot, o.N, H);
     gt_vec(o.prot, o.h, g);
@@ -227,7 +226,7 @@ __device__ __forceinline__ void track_obs(const ProblemView& pv, const double* _
   const double2 o2 = __ldg(reinterpret_cast<const double2*>(pv.pm_xy) + k);
   const size_t N = (size_t)pv.N;
   const double d = __ldg(pv.pm_depth + k), w = __ldg(pv.pm_depth + N + k), a = __ldg(pv.pm_depth + 2 * N + k);
-  linearize_obs<true, false>(ic.pose, ic.R, Xp, ic.model, ic.prm, o2.x, o2.y, d, w, a, ic.b, ic.s, pv.loss, o);
+  linearize_obs<true, false>(ic.pose, ic.R, Xp, ic.model, ic.prm, o2.x, o2.y, d, w, a, ic.b, ic.es, pv.loss, o);
 }
 
 constexpr int PT_THREADS = 128;
@@ -362,7 +361,9 @@ __device__ __forceinline__ void load_fac(const double* __restrict__ fac, int k, 
 }
 
 constexpr int SB_THREADS = 128;
-constexpr size_t SB_STAGE_BYTES = 2 * 16 * SB_THREADS * sizeof(double2);
+// per warp and buffer: 32 items x (record a: 8 chunks, record b: 8 chunks) of 16 bytes = 8 KB; two buffers, 4 warps
+constexpr int SB_WARP_CHUNKS = 512;
+constexpr size_t SB_STAGE_BYTES = 2 * (SB_THREADS / 32) * SB_WARP_CHUNKS * sizeof(double2);
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
@@ -372,6 +373,24 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
+
+// Gather of 128-byte factor records by a warp: lane = (record-in-group-of-4 << 3 | 16-byte chunk), so one
+// instruction moves four whole 128-byte lines (4 L1 wavefronts, every 32-byte sector requested once) instead
+// of 32 lanes touching 32 different lines for 16 bytes each (32 wavefronts, every sector requested twice --
+// what the first version of this kernel did, and what bound it: ncu l1tex 87 %, 5.7 GB of L2 reads for 2.9 GB
+// of records).  Record i of the warp lands in shared memory at row i with its chunks XOR-swizzled by (i & 7):
+// the copies of one instruction fill four rows, and lane i reading chunk c of ITS row hits 8 distinct 16-byte
+// columns per quarter warp -> no bank conflicts either way.
+__device__ __forceinline__ void warp_gather_records(const double2* __restrict__ fac2, int slot, int nchunks,
+                                                    double2* rows /* [32][8] */, int lane) {
+  const int g = lane >> 3, c = lane & 7;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int item = 4 * j + g;
+    const int s = __shfl_sync(FULL, slot, item);
+    if (s >= 0 && c < nchunks) cp_async16(rows + item * 8 + (c ^ (item & 7)), fac2 + (size_t)s * 8 + c);
+  }
 }
 
 // One CTA per upper block (i <= j) of the reduced camera system, no atomics, fixed summation order:
@@ -398,31 +417,25 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
   for (int k = 0; k < 36; ++k) M[k] = 0.0;
   double rv[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
 
-  // Every thread owns one item per 128-item tile.  Its two factor records (2 x 128 B, random gathers) are
-  // staged through shared memory with cp.async two tiles deep, so the loads of tile t+1 are in flight while
-  // tile t is multiplied: the kernel is bound by fp64 issue / L2 bandwidth instead of gather latency, at any
-  // occupancy.  A thread only ever reads back what it copied itself -> no CTA barrier in the loop.  Layout
-  // [buffer][16-byte chunk][thread]: conflict free for the copies and for the reads.
-  extern __shared__ __align__(16) double2 stage[];  // [2][16][SB_THREADS]
+  // Every thread owns one item per 128-item tile; the two factor records of the items of a warp are gathered
+  // by the warp together (warp_gather_records) into its own shared-memory rows with cp.async, two tiles deep,
+  // so the loads of tile t+1 are in flight while tile t is multiplied.  Only warp-level synchronisation.
+  extern __shared__ __align__(16) double2 stage[];  // [warp][2 buffers][a rows 32x8 | b rows 32x8]
+  const double2* fac2 = reinterpret_cast<const double2*>(fac);
+  double2* wst = stage + (size_t)warp * 2 * SB_WARP_CHUNKS;
   const int tid = threadIdx.x;
   auto issue = [&](int buf, int ka, int kb) {
-    const double2* sa = reinterpret_cast<const double2*>(fac + (size_t)ka * FAC_STRIDE);
-    const double2* sb = reinterpret_cast<const double2*>(fac + (size_t)kb * FAC_STRIDE);
-    double2* dst = stage + (size_t)buf * 16 * SB_THREADS + tid;
-#pragma unroll
-    for (int c = 0; c < 8; ++c) cp_async16(dst + c * SB_THREADS, sa + c);
-    if (kb != ka) {
-#pragma unroll
-      for (int c = 0; c < 6; ++c) cp_async16(dst + (8 + c) * SB_THREADS, sb + c);  // Z and p_rot of b; e is not needed
-    }
+    double2* rows = wst + buf * SB_WARP_CHUNKS;
+    warp_gather_records(fac2, ka, 8, rows, lane);
+    warp_gather_records(fac2, kb == ka ? -1 : kb, 6, rows + 256, lane);  // Z and p_rot of b; e is not needed
   };
   int it = it0 + tid;
-  int ka = 0, kb = 0, ka1 = 0, kb1 = 0;
+  int ka = -1, kb = -1, ka1 = -1, kb1 = -1;
   if (it < it1) {
     ka = __ldg(pv.item_a + it);
     kb = __ldg(pv.item_b + it);
-    issue(0, ka, kb);
   }
+  issue(0, ka, kb);
   cp_async_commit();
   if (it + SB_THREADS < it1) {
     ka1 = __ldg(pv.item_a + it + SB_THREADS);
@@ -431,27 +444,30 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
   for (int tile = 0;; ++tile) {
     const int base = it0 + tile * SB_THREADS;
     if (base >= it1) break;
-    const bool cur = it < it1, nxt = it + SB_THREADS < it1;
-    if (nxt) issue((tile + 1) & 1, ka1, kb1);
+    const bool cur = it < it1;
+    __syncwarp();  // the rows about to be overwritten were read two tiles ago by every lane
+    issue((tile + 1) & 1, ka1, kb1);
     cp_async_commit();
-    int ka2 = 0, kb2 = 0;
+    int ka2 = -1, kb2 = -1;
     if (it + 2 * SB_THREADS < it1) {
       ka2 = __ldg(pv.item_a + it + 2 * SB_THREADS);
       kb2 = __ldg(pv.item_b + it + 2 * SB_THREADS);
     }
     cp_async_wait<1>();
+    __syncwarp();  // every lane's copies of this tile have landed
     if (cur) {
-      const double2* src = stage + (size_t)(tile & 1) * 16 * SB_THREADS + tid;
+      const double2* src = wst + (tile & 1) * SB_WARP_CHUNKS + lane * 8;
+      const int sw = lane & 7;
       double za[9], zb[9], qa[3], qb[3];
       {
-        const double2 c0 = src[0], c1 = src[SB_THREADS], c2 = src[2 * SB_THREADS], c3 = src[3 * SB_THREADS],
-                      c4 = src[4 * SB_THREADS], c5 = src[5 * SB_THREADS];
+        const double2 c0 = src[0 ^ sw], c1 = src[1 ^ sw], c2 = src[2 ^ sw], c3 = src[3 ^ sw], c4 = src[4 ^ sw],
+                      c5 = src[5 ^ sw];
         za[0] = c0.x; za[1] = c0.y; za[2] = c1.x; za[3] = c1.y; za[4] = c2.x; za[5] = c2.y; za[6] = c3.x; za[7] = c3.y;
         za[8] = c4.x; qa[0] = 2.0 * c4.y; qa[1] = 2.0 * c5.x; qa[2] = 2.0 * c5.y;
       }
       const bool same = (ka == kb);
       if (same) {
-        const double2 c6 = src[6 * SB_THREADS], c7 = src[7 * SB_THREADS];
+        const double2 c6 = src[6 ^ sw], c7 = src[7 ^ sw];
         const double e0 = c6.x, e1 = c6.y, e2 = c7.x;
         // rhs: G_a^T (Z_a e)
         const double z0 = za[0] * e0 + za[1] * e1 + za[2] * e2, z1 = za[3] * e0 + za[4] * e1 + za[5] * e2,
@@ -464,8 +480,8 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
         for (int k = 0; k < 9; ++k) zb[k] = za[k];
         qb[0] = qa[0]; qb[1] = qa[1]; qb[2] = qa[2];
       } else {
-        const double2 c0 = src[8 * SB_THREADS], c1 = src[9 * SB_THREADS], c2 = src[10 * SB_THREADS],
-                      c3 = src[11 * SB_THREADS], c4 = src[12 * SB_THREADS], c5 = src[13 * SB_THREADS];
+        const double2 c0 = src[256 + (0 ^ sw)], c1 = src[256 + (1 ^ sw)], c2 = src[256 + (2 ^ sw)],
+                      c3 = src[256 + (3 ^ sw)], c4 = src[256 + (4 ^ sw)], c5 = src[256 + (5 ^ sw)];
         zb[0] = c0.x; zb[1] = c0.y; zb[2] = c1.x; zb[3] = c1.y; zb[4] = c2.x; zb[5] = c2.y; zb[6] = c3.x; zb[7] = c3.y;
         zb[8] = c4.x; qb[0] = 2.0 * c4.y; qb[1] = 2.0 * c5.x; qb[2] = 2.0 * c5.y;
       }
@@ -1037,21 +1053,23 @@ __global__ void __launch_bounds__(PT_THREADS) k_evaluate(ProblemView pv, const d
     const double2 o2 = __ldg(reinterpret_cast<const double2*>(pv.pm_xy) + k);
     const double d = __ldg(pv.pm_depth + k), w = __ldg(pv.pm_depth + N + k), a = __ldg(pv.pm_depth + 2 * N + k);
     ObsLin o;
-    linearize_obs<false, false>(ic.pose, ic.R, Xp, ic.model, ic.prm, o2.x, o2.y, d, w, a, ic.b, ic.s, pv.loss, o);
+    linearize_obs<false, false>(ic.pose, ic.R, Xp, ic.model, ic.prm, o2.x, o2.y, d, w, a, ic.b, ic.es, pv.loss, o);
     if (r_reproj) reinterpret_cast<double2*>(r_reproj)[k] = make_double2(o.r[0], o.r[1]);
     if (r_depth) r_depth[k] = o.r[2];
   }
 }
 
 // COLMAP normalises every quaternion before it enters the problem
-__global__ void k_normalize_poses(int C, const double* __restrict__ in, double* __restrict__ out) {
+__global__ void k_normalize_poses(int C, const double* __restrict__ in, const double* __restrict__ shift_scale,
+                                  double* __restrict__ out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= C) return;
   const double* s = in + (size_t)i * 8;
   const double n = sqrt(s[0] * s[0] + s[1] * s[1] + s[2] * s[2] + s[3] * s[3]);
   double* o = out + (size_t)i * 8;
   o[0] = s[0] / n; o[1] = s[1] / n; o[2] = s[2] / n; o[3] = s[3] / n;
-  o[4] = s[4]; o[5] = s[5]; o[6] = s[6]; o[7] = 0.0;
+  o[4] = s[4]; o[5] = s[5]; o[6] = s[6];
+  o[7] = exp(shift_scale[2 * (size_t)i + 1]);  // exp(log-scale) of the depth prior: constant block, one exp per image
 }
 
 __global__ void k_expand_hcc(int C, const double* __restrict__ Hc, double* __restrict__ H36) {
@@ -1164,8 +1182,8 @@ void launch_evaluate(const ProblemView& pv, const double* pose, const double* X,
                      cudaStream_t st) {
   if (pv.p1 > pv.p0) k_evaluate<<<points_grid(pv.p1 - pv.p0), PT_THREADS, 0, st>>>(pv, pose, X, r_reproj, r_depth);
 }
-void launch_normalize_poses(int C, const double* in, double* out, cudaStream_t st) {
-  if (C > 0) k_normalize_poses<<<(C + 127) / 128, 128, 0, st>>>(C, in, out);
+void launch_normalize_poses(int C, const double* in, const double* shift_scale, double* out, cudaStream_t st) {
+  if (C > 0) k_normalize_poses<<<(C + 127) / 128, 128, 0, st>>>(C, in, shift_scale, out);
 }
 void launch_expand_hcc(int C, const double* Hc, double* Hcc36, cudaStream_t st) {
   if (C > 0) k_expand_hcc<<<(C * 36 + 255) / 256, 256, 0, st>>>(C, Hc, Hcc36);

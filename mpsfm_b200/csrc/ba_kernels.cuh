@@ -183,7 +183,8 @@ void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, cudaS
 // ---- misc ---------------------------------------------------------------------------------------
 void launch_evaluate(const ProblemView& pv, const double* pose, const double* X, double* r_reproj, double* r_depth,
                      cudaStream_t st);
-void launch_normalize_poses(int C, const double* in, double* out, cudaStream_t st);
+// unit quaternions (COLMAP normalises before adding to the problem) + exp(log-scale) into slot 7
+void launch_normalize_poses(int C, const double* in, const double* shift_scale, double* out, cudaStream_t st);
 void launch_expand_hcc(int C, const double* Hc, double* Hcc36, cudaStream_t st);
 
 }  // namespace mpba

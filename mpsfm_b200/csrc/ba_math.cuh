@@ -389,10 +389,11 @@ struct ObsLin {
 };
 
 // One observation.  pose = {qx,qy,qz,qw,tx,ty,tz}, R = rotmat(q), X the point, (d, w, a) the depth
-// prior (w == 0: none), (b, s) the image's shift / log-scale.
+// prior (w == 0: none), (b, es) the image's shift and exp(log-scale) (the kernels keep exp(s) in slot 7 of the
+// pose record: one exp per image and state instead of one per observation).
 template <bool WANT_JAC, bool WANT_RHO>
 MPBA_HD void linearize_obs(const double* pose, const double R[9], const double X[3], int model, const double* prm,
-                           double ox, double oy, double d, double w, double a, double b, double s,
+                           double ox, double oy, double d, double w, double a, double b, double es,
                            const LossSpec& ls, ObsLin& o) {
   o.prot[0] = R[0] * X[0] + R[1] * X[1] + R[2] * X[2];
   o.prot[1] = R[3] * X[0] + R[4] * X[1] + R[5] * X[2];
@@ -428,7 +429,7 @@ MPBA_HD void linearize_obs(const double* pose, const double R[9], const double X
   }
   o.r[2] = 0.0;
   if (w > 0.0) {
-    const double r2 = log((exp(s) * d + b) * iz);
+    const double r2 = log((es * d + b) * iz);
     o.r[2] = r2;
     double rhod, rhod1;
     loss_eval<WANT_RHO>(ls.depth_loss, a, w, r2 * r2, rhod, rhod1);

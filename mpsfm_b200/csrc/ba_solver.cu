@@ -715,7 +715,7 @@ int mpba_evaluate(mpba_handle* h, const mpba_problem* prob, void* workspace, siz
   reset_profile(h, 0);
   {
     Timer t(h, KS_MISC);
-    launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[0], h->stream);
+    launch_normalize_poses(c.pv.C, prob->img_pose, prob->img_shift_scale, c.w.pose[0], h->stream);
   }
   if (r_reproj || r_depth) {
     Timer t(h, KS_EVALUATE);
@@ -740,7 +740,7 @@ int mpba_linearize(mpba_handle* h, const mpba_problem* prob, void* workspace, si
   reset_profile(h, 0);
   mpba_options opt;
   mpba_default_options(&opt);
-  launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[0], h->stream);
+  launch_normalize_poses(c.pv.C, prob->img_pose, prob->img_shift_scale, c.w.pose[0], h->stream);
   rc = enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 1, 1);
   if (rc) return rc;
   LmDiag lm{opt.initial_trust_region_radius, opt.min_lm_diagonal, opt.max_lm_diagonal};
@@ -769,7 +769,7 @@ int mpba_point_covariances(mpba_handle* h, const mpba_problem* prob, void* works
   mpba_options opt;
   mpba_default_options(&opt);
   opt.jacobi_scaling = 0;
-  launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[0], h->stream);
+  launch_normalize_poses(c.pv.C, prob->img_pose, prob->img_shift_scale, c.w.pose[0], h->stream);
   // undamped: an infinite trust-region radius makes the LM diagonal vanish
   LmDiag lm{INFINITY, opt.min_lm_diagonal, opt.max_lm_diagonal};
   rc = enqueue_points_and_system(c, c.w.pose[0], prob->pt_xyz, 0, lm, 1, &opt, false);
@@ -791,7 +791,7 @@ int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspac
   if (opt_in) opt = *opt_in; else mpba_default_options(&opt);
   rc = build_pcg_cluster_plan(c, prob, opt.pcg_kernel, opt.pcg_coarse);
   if (rc) return rc;
-  launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[0], h->stream);
+  launch_normalize_poses(c.pv.C, prob->img_pose, prob->img_shift_scale, c.w.pose[0], h->stream);
   rc = enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 1, opt.jacobi_scaling);
   if (rc) return rc;
   LmDiag lm{radius, opt.min_lm_diagonal, opt.max_lm_diagonal};
@@ -835,7 +835,7 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
 
   CU(cudaEventRecord(h->ev0, h->stream));
   int cur = 0;
-  launch_normalize_poses(c.pv.C, prob->img_pose, c.w.pose[cur], h->stream);
+  launch_normalize_poses(c.pv.C, prob->img_pose, prob->img_shift_scale, c.w.pose[cur], h->stream);
   h->launch_count += 1;
   if (c.pv.P > 0)
     CU(cudaMemcpyAsync(c.w.X[cur], prob->pt_xyz, (size_t)c.pv.P * 4 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));

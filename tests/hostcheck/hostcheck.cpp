@@ -21,10 +21,10 @@ void hc_obs(int n, const double* pose, const double* X, const int* model, const 
     for (int k = 0; k < 3; ++k) o.h[k] = 0;
     if (want_jac)
       linearize_obs<true, true>(pose + 8 * i, R, X + 3 * i, model[i], prm + 12 * i, xy[2 * i], xy[2 * i + 1], dwa[3 * i],
-                                dwa[3 * i + 1], dwa[3 * i + 2], bs[2 * i], bs[2 * i + 1], ls, o);
+                                dwa[3 * i + 1], dwa[3 * i + 2], bs[2 * i], exp(bs[2 * i + 1]), ls, o);
     else
       linearize_obs<false, true>(pose + 8 * i, R, X + 3 * i, model[i], prm + 12 * i, xy[2 * i], xy[2 * i + 1], dwa[3 * i],
-                                 dwa[3 * i + 1], dwa[3 * i + 2], bs[2 * i], bs[2 * i + 1], ls, o);
+                                 dwa[3 * i + 1], dwa[3 * i + 2], bs[2 * i], exp(bs[2 * i + 1]), ls, o);
     double* d = out + 48 * i;
     for (int k = 0; k < 6; ++k) d[k] = o.N[k];
     for (int k = 0; k < 3; ++k) d[6 + k] = o.h[k];
