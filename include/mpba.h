@@ -14,6 +14,7 @@
  *   - all floating point data is IEEE double, all indices int32,
  *   - every call returns 0 on success or a negative MPBA_E_* code; the message is available from
  *     mpba_last_error(); nothing throws across the boundary,
+ *   - img_pose slot 7 is scratch: a solve leaves exp(log-scale) of the image's depth prior there,
  *   - a handle is bound to one device and one stream and is not thread-safe,
  *   - there is no CPU fallback: without a CUDA device mpba_create fails with MPBA_E_CUDA.
  */
@@ -125,6 +126,14 @@ typedef struct mpba_problem {
    * the reduced camera system is skipped */
   int32_t flags;
   int32_t s_max_row_blocks;     /* max blocks in one row of S (0 = unknown): sizes the PCG's shared-memory staging */
+
+  /* track-order warp packing (mpba_pack_tracks): the track-order passes run one thread per observation and one
+   * warp per group of WHOLE consecutive tracks, tracks track_warp_first[w] .. track_warp_first[w+1] - 1, with at
+   * most 32 observations and 32 tracks per group (a longer track is a group of its own).  Covers the owned
+   * tracks: track_warp_first[0] = 0 (sharded: pt_begin), track_warp_first[num_track_warps] = num_points (pt_end). */
+  int32_t num_track_warps;
+  int32_t reserved;
+  const int32_t* track_warp_first; /* [num_track_warps + 1] */
 } mpba_problem;
 
 #define MPBA_FLAG_STRUCTURE_ONLY 1
@@ -195,6 +204,11 @@ int mpba_create(mpba_handle** out, int device, void* cuda_stream /* cudaStream_t
 void mpba_destroy(mpba_handle* h);
 const char* mpba_last_error(const mpba_handle* h);
 void mpba_default_options(mpba_options* opt);
+
+/* HOST helper: greedy packing of the tracks pt_begin .. pt_end - 1 (HOST array pt_ptr, global indices) into
+ * warp groups as mpba_problem.track_warp_first wants them.  first must hold pt_end - pt_begin + 1 entries;
+ * *num_warps receives the number of groups. */
+int mpba_pack_tracks(const int32_t* pt_ptr, int32_t pt_begin, int32_t pt_end, int32_t* first, int32_t* num_warps);
 
 /* bytes of device workspace mpba_* calls need for this problem */
 int mpba_workspace_bytes(const mpba_problem* prob, size_t* bytes);

@@ -229,112 +229,277 @@ __device__ __forceinline__ void track_obs(const ProblemView& pv, const double* _
   linearize_obs<true, false>(ic.pose, ic.R, Xp, ic.model, ic.prm, o2.x, o2.y, d, w, a, ic.b, ic.es, pv.loss, o);
 }
 
-constexpr int PT_THREADS = 128;
+constexpr int PT_THREADS = 128;  // k_evaluate: one thread per track
+constexpr int PW_THREADS = 128;  // track-order passes: one thread per OBSERVATION, one warp per packed group of tracks
+constexpr int PW_WARPS = PW_THREADS / 32;
+constexpr int LINV_STRIDE = 9;  // per point: L^-1 (6, lower) and e = L^-1 gp (3)
 
-// One thread per track.  Pass 1: Hpp = sum R^T N R, gp = sum R^T h, damped Cholesky Hpp + D = L L^T.
-// Pass 2 (write_factors): one 128-byte Schur factor per observation,
-//     fac[k] = { Z = N R L^-T (9), p_rot (3), e = L^-1 gp (3), 0 },
-// from which k_schur_blocks forms  W_a Hpp^-1 W_b^T = G_a^T (Z_a Z_b^T) G_b  and
-// W_a Hpp^-1 gp = G_a^T Z_a e  without ever storing the 6x3 W blocks.
-__global__ void __launch_bounds__(PT_THREADS) k_points(ProblemView pv, const double* __restrict__ pose,
+// ---- one warp = a packed group of whole tracks (mpba_pack_tracks: <= 32 observations and <= 32 tracks, or one
+// single longer track).  Lane l is observation slot base + l AND (for l < number of tracks) track t0 + l.
+struct WarpTracks {
+  int t0, nt, base, n;  // first track, tracks, first slot, observations
+  // per track lane
+  int start, len;       // first observation lane / observations of track t0 + lane
+  bool cst;             // constant point
+  // per observation lane
+  bool has;             // lane < n
+  int tl;               // lane holding this observation's track
+  int seg_end;          // one past the last observation lane of the track
+  bool tcst;            // the track is a constant point
+};
+
+__device__ __forceinline__ void warp_tracks_setup(const ProblemView& pv, int w, int lane, WarpTracks& wt) {
+  wt.t0 = __ldg(pv.tw_first + w);
+  wt.nt = __ldg(pv.tw_first + w + 1) - wt.t0;
+  wt.base = __ldg(pv.pt_ptr + wt.t0);
+  wt.n = __ldg(pv.pt_ptr + wt.t0 + wt.nt) - wt.base;
+  wt.start = 0; wt.len = 0; wt.cst = true;
+  if (lane < wt.nt) {
+    const int a = __ldg(pv.pt_ptr + wt.t0 + lane), b = __ldg(pv.pt_ptr + wt.t0 + lane + 1);
+    wt.start = a - wt.base;
+    wt.len = b - a;
+    wt.cst = pv.pt_const[wt.t0 + lane] != 0;
+  }
+  wt.has = lane < wt.n;
+  wt.tl = 0; wt.seg_end = wt.n; wt.tcst = true;
+  if (wt.n <= 32) {
+    const bool nonempty = wt.len > 0;
+    const unsigned ne = __ballot_sync(FULL, nonempty);                              // track lanes with observations
+    const unsigned heads = __reduce_or_sync(FULL, nonempty ? (1u << wt.start) : 0u);  // their first observation lanes
+    const int rank = __popc(heads & (0xffffffffu >> (31 - lane)));                  // non-empty tracks starting <= lane
+    wt.tl = wt.has ? __fns(ne, 0, rank) : 0;
+    const unsigned above = (lane == 31) ? 0u : (heads & (0xffffffffu << (lane + 1)));
+    wt.seg_end = above ? (__ffs(above) - 1) : wt.n;
+    wt.tcst = __shfl_sync(FULL, wt.cst ? 1 : 0, wt.tl) != 0;
+  }
+}
+
+// sum over the observation lanes of every track, delivered to the track's first observation lane (fixed tree)
+template <int NV>
+__device__ __forceinline__ void segmented_reduce(double (&v)[NV], int lane, int seg_end) {
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const bool take = lane + off < seg_end;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const double t = __shfl_down_sync(FULL, v[j], off);
+      if (take) v[j] += t;
+    }
+  }
+}
+
+template <int NV>
+__device__ __forceinline__ void warp_allreduce(double (&v)[NV]) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+    for (int j = 0; j < NV; ++j) v[j] += __shfl_xor_sync(FULL, v[j], off);
+}
+
+// Hpp / gp contributions of one linearised observation: v = [R^T N R (6 upper), R^T h (3)], Q = N R
+__device__ __forceinline__ void point_terms(const ObsLin& o, const double* R, double Q[9], double v[9]) {
+  sym3_mul_mat(o.N, R, Q);
+  v[0] = R[0] * Q[0] + R[3] * Q[3] + R[6] * Q[6];
+  v[1] = R[0] * Q[1] + R[3] * Q[4] + R[6] * Q[7];
+  v[2] = R[0] * Q[2] + R[3] * Q[5] + R[6] * Q[8];
+  v[3] = R[1] * Q[1] + R[4] * Q[4] + R[7] * Q[7];
+  v[4] = R[1] * Q[2] + R[4] * Q[5] + R[7] * Q[8];
+  v[5] = R[2] * Q[2] + R[5] * Q[5] + R[8] * Q[8];
+  v[6] = R[0] * o.h[0] + R[3] * o.h[1] + R[6] * o.h[2];
+  v[7] = R[1] * o.h[0] + R[4] * o.h[1] + R[7] * o.h[2];
+  v[8] = R[2] * o.h[0] + R[5] * o.h[1] + R[8] * o.h[2];
+}
+
+// Per point, from the complete sums: Jacobi scale, LM damping, Cholesky of Hpp + D, Hpp^-1; writes the point's
+// rows of c_pt / Hpp / gp / Hinv / Linv and returns L^-1 (Li), e = L^-1 gp.
+__device__ __forceinline__ void finalize_point(int p, bool active, const double Hp[6], const double g[3], LmDiag lm,
+                                               double* __restrict__ c_pt, int compute_scaling, int jacobi_scaling,
+                                               double* __restrict__ Hpp, double* __restrict__ gp,
+                                               double* __restrict__ Hinv, double* __restrict__ Linv,
+                                               double* __restrict__ scal, double Li[6], double e[3]) {
+  double Hi[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+  for (int j = 0; j < 6; ++j) Li[j] = 0.0;
+  double c[3] = {0.0, 0.0, 0.0};
+  if (compute_scaling) {
+    if (active) {
+      c[0] = jacobi_scaling ? 1.0 / (1.0 + sqrt(Hp[0])) : 1.0;
+      c[1] = jacobi_scaling ? 1.0 / (1.0 + sqrt(Hp[3])) : 1.0;
+      c[2] = jacobi_scaling ? 1.0 / (1.0 + sqrt(Hp[5])) : 1.0;
+    }
+    c_pt[(size_t)p * 3] = c[0]; c_pt[(size_t)p * 3 + 1] = c[1]; c_pt[(size_t)p * 3 + 2] = c[2];
+  } else {
+    c[0] = c_pt[(size_t)p * 3]; c[1] = c_pt[(size_t)p * 3 + 1]; c[2] = c_pt[(size_t)p * 3 + 2];
+  }
+  if (active) {
+    double Hd[6] = {Hp[0], Hp[1], Hp[2], Hp[3], Hp[4], Hp[5]};
+    Hd[0] += lm_damping(Hp[0], c[0], lm.radius, lm.lo, lm.hi);
+    Hd[3] += lm_damping(Hp[3], c[1], lm.radius, lm.lo, lm.hi);
+    Hd[5] += lm_damping(Hp[5], c[2], lm.radius, lm.lo, lm.hi);
+    if (sym3_chol_inverse(Hd, Li)) {
+      sym3_from_chol_inverse(Li, Hi);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) Li[j] = 0.0;
+      atomicAdd(scal + S_BAD_POINTS, 1.0);  // failure counter, not arithmetic
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    Hpp[(size_t)p * 6 + j] = Hp[j];
+    Hinv[(size_t)p * 6 + j] = Hi[j];
+    Linv[(size_t)p * LINV_STRIDE + j] = Li[j];
+  }
+#pragma unroll
+  for (int j = 0; j < 3; ++j) gp[(size_t)p * 3 + j] = g[j];
+  e[0] = Li[0] * g[0];
+  e[1] = Li[1] * g[0] + Li[2] * g[1];
+  e[2] = Li[3] * g[0] + Li[4] * g[1] + Li[5] * g[2];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) Linv[(size_t)p * LINV_STRIDE + 6 + j] = e[j];
+}
+
+__device__ __forceinline__ void pack_factor(const double Q[9], const double Li[6], const double prot[3],
+                                            const double e[3], double2 rec[8]) {
+  double Z[9];
+  mul_chol_inverse_t(Q, Li, Z);
+  rec[0] = make_double2(Z[0], Z[1]);
+  rec[1] = make_double2(Z[2], Z[3]);
+  rec[2] = make_double2(Z[4], Z[5]);
+  rec[3] = make_double2(Z[6], Z[7]);
+  rec[4] = make_double2(Z[8], prot[0]);
+  rec[5] = make_double2(prot[1], prot[2]);
+  rec[6] = make_double2(e[0], e[1]);
+  rec[7] = make_double2(e[2], 0.0);
+}
+
+// Track-order pass, one thread per observation (north star item 2: warp-shuffle segmented reductions keyed by
+// point).  Every observation is linearised ONCE; Hpp = sum R^T N R and gp = sum R^T h of a track are reduced over
+// its lanes with a segmented shuffle tree, the track's lane factors Hpp + D = L L^T and hands L^-1 and
+// e = L^-1 gp back to the observation lanes, which write one 128-byte Schur factor each,
+//     fac[k] = { Z = N R L^-T (9), p_rot (3), e (3), 0 },
+// from which k_schur_blocks forms  W_a Hpp^-1 W_b^T = G_a^T (Z_a Z_b^T) G_b  and  W_a Hpp^-1 gp = G_a^T Z_a e
+// without ever storing the 6x3 W blocks, and k_back_substitute the point steps.  The records of a warp go
+// through swizzled shared-memory rows so that the stores leave as whole 128-byte lines.
+__global__ void __launch_bounds__(PW_THREADS) k_points(ProblemView pv, const double* __restrict__ pose,
                                                        const double* __restrict__ X, LmDiag lm,
                                                        double* __restrict__ c_pt, int compute_scaling,
                                                        int jacobi_scaling, double* __restrict__ Hpp,
                                                        double* __restrict__ gp, double* __restrict__ Hinv,
-                                                       double* __restrict__ fac, double* __restrict__ pt_part,
-                                                       double* __restrict__ scal, int write_factors) {
-  const int p = pv.p0 + blockIdx.x * PT_THREADS + threadIdx.x;
-  const bool valid = p < pv.p1;
-  const bool active = valid && pv.pt_const[p] == 0;
-  int beg = 0, end = 0;
-  if (active) {
-    beg = pv.pt_ptr[p];
-    end = pv.pt_ptr[p + 1];
-  }
-  const int L = end - beg;
-  double Xp[3] = {0.0, 0.0, 0.0};
-  if (active) load_point(X, p, Xp);
-
-  double Hp[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, g[3] = {0.0, 0.0, 0.0};
-  for (int k = beg; k < end; ++k) {
-    ObsLin o;
-    ImgConst ic;
-    track_obs(pv, pose, Xp, k, o, ic);
-    double Q[9];
-    sym3_mul_mat(o.N, ic.R, Q);
-    const double* R = ic.R;
-    Hp[0] += R[0] * Q[0] + R[3] * Q[3] + R[6] * Q[6];
-    Hp[1] += R[0] * Q[1] + R[3] * Q[4] + R[6] * Q[7];
-    Hp[2] += R[0] * Q[2] + R[3] * Q[5] + R[6] * Q[8];
-    Hp[3] += R[1] * Q[1] + R[4] * Q[4] + R[7] * Q[7];
-    Hp[4] += R[1] * Q[2] + R[4] * Q[5] + R[7] * Q[8];
-    Hp[5] += R[2] * Q[2] + R[5] * Q[5] + R[8] * Q[8];
-    g[0] += R[0] * o.h[0] + R[3] * o.h[1] + R[6] * o.h[2];
-    g[1] += R[1] * o.h[0] + R[4] * o.h[1] + R[7] * o.h[2];
-    g[2] += R[2] * o.h[0] + R[5] * o.h[1] + R[8] * o.h[2];
-  }
-
-  double Hi[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, Li[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-  bool solvable = false;
-  if (valid) {
-    double c[3] = {0.0, 0.0, 0.0};
-    if (compute_scaling) {
-      if (active && L > 0) {
-        c[0] = jacobi_scaling ? 1.0 / (1.0 + sqrt(Hp[0])) : 1.0;
-        c[1] = jacobi_scaling ? 1.0 / (1.0 + sqrt(Hp[3])) : 1.0;
-        c[2] = jacobi_scaling ? 1.0 / (1.0 + sqrt(Hp[5])) : 1.0;
+                                                       double* __restrict__ Linv, double* __restrict__ fac,
+                                                       double* __restrict__ pt_part, double* __restrict__ scal,
+                                                       int write_factors) {
+  __shared__ __align__(16) double2 rows_all[PW_WARPS][256];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int w = blockIdx.x * PW_WARPS + warp;
+  double gmax = 0.0;
+  if (w < pv.num_track_warps) {
+    WarpTracks wt;
+    warp_tracks_setup(pv, w, lane, wt);
+    double2* fac2 = reinterpret_cast<double2*>(fac);
+    if (wt.n <= 32) {
+      // ---- observation lanes: linearise, reduce over the track
+      const bool act = wt.has && !wt.tcst;
+      double v[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, Q[9], prot[3] = {0.0, 0.0, 0.0};
+      if (act) {
+        double Xp[3];
+        load_point(X, wt.t0 + wt.tl, Xp);
+        ObsLin o;
+        ImgConst ic;
+        track_obs(pv, pose, Xp, wt.base + lane, o, ic);
+        point_terms(o, ic.R, Q, v);
+        prot[0] = o.prot[0]; prot[1] = o.prot[1]; prot[2] = o.prot[2];
       }
-      c_pt[(size_t)p * 3] = c[0]; c_pt[(size_t)p * 3 + 1] = c[1]; c_pt[(size_t)p * 3 + 2] = c[2];
+      segmented_reduce<9>(v, lane, wt.seg_end);
+      // ---- track lanes: fetch the sums from the first observation lane, factor, write the point's rows
+      double Hp[6], g[3];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) Hp[j] = __shfl_sync(FULL, v[j], wt.start);
+#pragma unroll
+      for (int j = 0; j < 3; ++j) g[j] = __shfl_sync(FULL, v[6 + j], wt.start);
+      double Li[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, e[3] = {0.0, 0.0, 0.0};
+      if (lane < wt.nt) {
+        const bool active = !wt.cst && wt.len > 0;
+        if (!active) {
+#pragma unroll
+          for (int j = 0; j < 6; ++j) Hp[j] = 0.0;
+          g[0] = g[1] = g[2] = 0.0;
+        }
+        finalize_point(wt.t0 + lane, active, Hp, g, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv,
+                       scal, Li, e);
+        gmax = fmax(fabs(g[0]), fmax(fabs(g[1]), fabs(g[2])));
+      }
+      if (write_factors) {
+        // ---- back to the observation lanes: L^-1 and e of their track, one factor record each
+        double Lo[6], eo[3];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) Lo[j] = __shfl_sync(FULL, Li[j], wt.tl);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) eo[j] = __shfl_sync(FULL, e[j], wt.tl);
+        double2* rows = rows_all[warp];
+        if (act) {
+          double2 rec[8];
+          pack_factor(Q, Lo, prot, eo, rec);
+          const int sw = lane & 7;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) rows[lane * 8 + (c ^ sw)] = rec[c];
+        }
+        const unsigned actmask = __ballot_sync(FULL, act);  // (also orders the shared-memory writes in the warp)
+        const int g4 = lane >> 3, c = lane & 7;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int item = 4 * j + g4;
+          if ((actmask >> item) & 1u) fac2[(size_t)(wt.base + item) * 8 + c] = rows[item * 8 + (c ^ (item & 7))];
+        }
+      }
     } else {
-      c[0] = c_pt[(size_t)p * 3]; c[1] = c_pt[(size_t)p * 3 + 1]; c[2] = c_pt[(size_t)p * 3 + 2];
-    }
-    if (active && L > 0) {
-      double Hd[6] = {Hp[0], Hp[1], Hp[2], Hp[3], Hp[4], Hp[5]};
-      Hd[0] += lm_damping(Hp[0], c[0], lm.radius, lm.lo, lm.hi);
-      Hd[3] += lm_damping(Hp[3], c[1], lm.radius, lm.lo, lm.hi);
-      Hd[5] += lm_damping(Hp[5], c[2], lm.radius, lm.lo, lm.hi);
-      solvable = sym3_chol_inverse(Hd, Li);
-      if (solvable) {
-        sym3_from_chol_inverse(Li, Hi);
-      } else {
+      // ---- one long track (> 32 observations): rounds of 32, whole-warp sums, second sweep for the factors
+      const int p = wt.t0;
+      const bool active = pv.pt_const[p] == 0;
+      double Xp[3] = {0.0, 0.0, 0.0};
+      if (active) load_point(X, p, Xp);
+      double v[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+      if (active) {
+        for (int k = lane; k < wt.n; k += 32) {
+          ObsLin o;
+          ImgConst ic;
+          track_obs(pv, pose, Xp, wt.base + k, o, ic);
+          double Q[9], t[9];
+          point_terms(o, ic.R, Q, t);
 #pragma unroll
-        for (int j = 0; j < 6; ++j) Li[j] = 0.0;
-        atomicAdd(scal + S_BAD_POINTS, 1.0);  // failure counter, not arithmetic
+          for (int j = 0; j < 9; ++j) v[j] += t[j];
+        }
+      }
+      warp_allreduce<9>(v);
+      double Li[6], e[3];
+      if (lane == 0) {
+        finalize_point(p, active, v, v + 6, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, scal, Li, e);
+        gmax = fmax(fabs(v[6]), fmax(fabs(v[7]), fabs(v[8])));
+      }
+#pragma unroll
+      for (int j = 0; j < 6; ++j) Li[j] = __shfl_sync(FULL, Li[j], 0);
+#pragma unroll
+      for (int j = 0; j < 3; ++j) e[j] = __shfl_sync(FULL, e[j], 0);
+      if (write_factors && active) {
+        for (int k = lane; k < wt.n; k += 32) {
+          ObsLin o;
+          ImgConst ic;
+          track_obs(pv, pose, Xp, wt.base + k, o, ic);
+          double Q[9], t[9];
+          point_terms(o, ic.R, Q, t);
+          double2 rec[8];
+          pack_factor(Q, Li, o.prot, e, rec);
+          double2* dst = fac2 + (size_t)(wt.base + k) * 8;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) dst[c] = rec[c];
+        }
       }
     }
-#pragma unroll
-    for (int j = 0; j < 6; ++j) {
-      Hpp[(size_t)p * 6 + j] = Hp[j];
-      Hinv[(size_t)p * 6 + j] = Hi[j];
-    }
-#pragma unroll
-    for (int j = 0; j < 3; ++j) gp[(size_t)p * 3 + j] = g[j];
   }
-
   {
-    __shared__ double smx[PT_THREADS / 32 + 1];
-    const double m = block_max<PT_THREADS / 32>(fmax(fabs(g[0]), fmax(fabs(g[1]), fabs(g[2]))), smx);
+    __shared__ double smx[PW_WARPS + 1];
+    const double m = block_max<PW_WARPS>(gmax, smx);
     if (threadIdx.x == 0) pt_part[(size_t)blockIdx.x * PT_PART] = m;
-  }
-  if (!write_factors) return;
-
-  const double e0 = Li[0] * g[0], e1 = Li[1] * g[0] + Li[2] * g[1], e2 = Li[3] * g[0] + Li[4] * g[1] + Li[5] * g[2];
-  for (int k = beg; k < end; ++k) {
-    ObsLin o;
-    ImgConst ic;
-    track_obs(pv, pose, Xp, k, o, ic);
-    double Q[9], Z[9];
-    sym3_mul_mat(o.N, ic.R, Q);
-    mul_chol_inverse_t(Q, Li, Z);
-    double2* dst = reinterpret_cast<double2*>(fac + (size_t)k * FAC_STRIDE);
-    dst[0] = make_double2(Z[0], Z[1]);
-    dst[1] = make_double2(Z[2], Z[3]);
-    dst[2] = make_double2(Z[4], Z[5]);
-    dst[3] = make_double2(Z[6], Z[7]);
-    dst[4] = make_double2(Z[8], o.prot[0]);
-    dst[5] = make_double2(o.prot[1], o.prot[2]);
-    dst[6] = make_double2(e0, e1);
-    dst[7] = make_double2(e2, 0.0);
   }
 }
 
@@ -350,16 +515,6 @@ __global__ void __launch_bounds__(1024) k_pt_scalars_gmax(const double* __restri
 // ================================================================================================
 // reduced camera system
 // ================================================================================================
-struct Fac {
-  double Z[9], p[3], e[3];
-};
-__device__ __forceinline__ void load_fac(const double* __restrict__ fac, int k, Fac& f) {
-  const double2* s = reinterpret_cast<const double2*>(fac + (size_t)k * FAC_STRIDE);
-  const double2 a = s[0], b = s[1], c = s[2], d = s[3], e = s[4], g = s[5], h = s[6], i = s[7];
-  f.Z[0] = a.x; f.Z[1] = a.y; f.Z[2] = b.x; f.Z[3] = b.y; f.Z[4] = c.x; f.Z[5] = c.y; f.Z[6] = d.x; f.Z[7] = d.y;
-  f.Z[8] = e.x; f.p[0] = e.y; f.p[1] = g.x; f.p[2] = g.y; f.e[0] = h.x; f.e[1] = h.y; f.e[2] = i.x;
-}
-
 constexpr int SB_THREADS = 128;
 // per warp and buffer: 32 items x (record a: 8 chunks, record b: 8 chunks) of 16 bytes = 8 KB; two buffers, 4 warps
 constexpr int SB_WARP_CHUNKS = 512;
@@ -909,10 +1064,12 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
 // step
 // ================================================================================================
 __global__ void __launch_bounds__(256) k_cam_update(ProblemView pv, const double* __restrict__ pose,
-                                                    const double* __restrict__ y, double* __restrict__ pose_cand,
+                                                    const double* __restrict__ y, const double* __restrict__ Hc,
+                                                    const double* __restrict__ gc, const double* __restrict__ c_img,
+                                                    LmDiag lm, double* __restrict__ pose_cand,
                                                     double* __restrict__ scal) {
   __shared__ double sm[9];
-  double step2 = 0.0, xn2 = 0.0;
+  double step2 = 0.0, xn2 = 0.0, mcc = 0.0;
   for (int i = threadIdx.x; i < pv.C; i += 256) {
     const double* ps = pose + (size_t)i * 8;
     const double* yi = y + (size_t)i * 6;
@@ -936,79 +1093,146 @@ __global__ void __launch_bounds__(256) k_cam_update(ProblemView pv, const double
       step2 += (t0 - ps[4]) * (t0 - ps[4]) + (t1 - ps[5]) * (t1 - ps[5]) + (t2 - ps[6]) * (t2 - ps[6]);
       xn2 += ps[4] * ps[4] + ps[5] * ps[5] + ps[6] * ps[6];
     }
+    // image part of the model cost change (g'y + y'Dy) / 2 over the free tangent coordinates (all images,
+    // replicated in a sharded solve: gc / Hc are complete on every rank)
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+      if ((mask >> r) & 1u) {
+        const double dj = lm_damping(Hc[(size_t)i * 21 + upper_idx(r, r)], c_img[(size_t)i * 6 + r], lm.radius, lm.lo, lm.hi);
+        mcc += 0.5 * (gc[(size_t)i * 6 + r] * yi[r] + dj * yi[r] * yi[r]);
+      }
+    }
   }
   step2 = block_sum<8>(step2, sm);
   xn2 = block_sum<8>(xn2, sm);
+  mcc = block_sum<8>(mcc, sm);
   if (threadIdx.x == 0) {
     scal[S_STEP2_C] = step2;
     scal[S_XNORM2_C] = xn2;
+    scal[S_MCC_C] = mcc;
   }
 }
 
-// y_p = Hpp^-1 (gp - sum_a W_a^T y_c(a)); X_cand = X - y_p; model cost change of the whole step:
-//   sum_obs (v.h - v'Nv/2), v = G y_c + R y_p
-//     = sum_a (g_a.h_a - g_a'N_a g_a / 2) + y_p.gp - y_p.wty - y_p'Hpp y_p / 2,   g_a = G_a y_c(a).
-__global__ void __launch_bounds__(PT_THREADS) k_back_substitute(ProblemView pv, const double* __restrict__ pose,
-                                                                const double* __restrict__ X,
+// Back-substitution from the stored Schur factors, one thread per observation (same warp packing as k_points).
+// With Hpp + D = L L^T, Z_a = N_a R_a L^-T, e = L^-1 gp and g_a = G_a y_c(a) (p_rot is in the record):
+//     y_p = (Hpp + D)^-1 (gp - sum_a W_a^T y_c(a)) = L^-T (e - sum_a Z_a^T g_a),      X_cand = X - y_p.
+// No re-linearisation: the pass reads one 128-byte record per observation (warp-cooperative gather) and 48 bytes of
+// y_c.  The model cost change uses the normal equations the step solves, (H + D) y = g:
+//     g'y - y'Hy/2 = (g'y + y'Dy) / 2
+// (exact up to the PCG residual, 1e-12 relative by default); the point part is summed here, the image part in
+// k_cam_update.
+__device__ __forceinline__ void point_step(int p, bool active, const double* __restrict__ X, const double zg[3],
+                                           const double* __restrict__ Linv, const double* __restrict__ Hpp,
+                                           const double* __restrict__ gp, const double* __restrict__ c_pt, LmDiag lm,
+                                           double* __restrict__ X_cand, double& mcc, double& step2, double& xn2) {
+  double Xp[3];
+  load_point(X, p, Xp);
+  double yp[3] = {0.0, 0.0, 0.0};
+  if (active) {
+    double Li[6];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) Li[j] = Linv[(size_t)p * LINV_STRIDE + j];
+    const double u[3] = {Linv[(size_t)p * LINV_STRIDE + 6] - zg[0], Linv[(size_t)p * LINV_STRIDE + 7] - zg[1],
+                         Linv[(size_t)p * LINV_STRIDE + 8] - zg[2]};
+    // y_p = L^-T u,  u = e - sum Z^T g  (Li = L^-1, lower: 00, 10, 11, 20, 21, 22)
+    yp[0] = Li[0] * u[0] + Li[1] * u[1] + Li[3] * u[2];
+    yp[1] = Li[2] * u[1] + Li[4] * u[2];
+    yp[2] = Li[5] * u[2];
+    const double h0 = Hpp[(size_t)p * 6], h3 = Hpp[(size_t)p * 6 + 3], h5 = Hpp[(size_t)p * 6 + 5];
+    const double d0 = lm_damping(h0, c_pt[(size_t)p * 3], lm.radius, lm.lo, lm.hi),
+                 d1 = lm_damping(h3, c_pt[(size_t)p * 3 + 1], lm.radius, lm.lo, lm.hi),
+                 d2 = lm_damping(h5, c_pt[(size_t)p * 3 + 2], lm.radius, lm.lo, lm.hi);
+    mcc = 0.5 * (gp[(size_t)p * 3] * yp[0] + gp[(size_t)p * 3 + 1] * yp[1] + gp[(size_t)p * 3 + 2] * yp[2] +
+                 d0 * yp[0] * yp[0] + d1 * yp[1] * yp[1] + d2 * yp[2] * yp[2]);
+    step2 = yp[0] * yp[0] + yp[1] * yp[1] + yp[2] * yp[2];
+    xn2 = Xp[0] * Xp[0] + Xp[1] * Xp[1] + Xp[2] * Xp[2];
+  }
+  double2* out = reinterpret_cast<double2*>(X_cand + 4 * (size_t)p);
+  out[0] = make_double2(Xp[0] - yp[0], Xp[1] - yp[1]);
+  out[1] = make_double2(Xp[2] - yp[2], 0.0);
+}
+
+// s = Z^T (G y_c) of one observation from its record (Z 9, p_rot 3) and the image's y (6)
+__device__ __forceinline__ void obs_zt_g(const double Z[9], const double prot[3], const double* __restrict__ y, int img,
+                                         double s[3]) {
+  const double2* yi = reinterpret_cast<const double2*>(y + (size_t)img * 6);
+  const double2 a = __ldg(yi), b = __ldg(yi + 1), c = __ldg(yi + 2);
+  const double yc[6] = {a.x, a.y, b.x, b.y, c.x, c.y};
+  double ga[3];
+  g_vec(prot, yc, ga);
+  s[0] = Z[0] * ga[0] + Z[3] * ga[1] + Z[6] * ga[2];
+  s[1] = Z[1] * ga[0] + Z[4] * ga[1] + Z[7] * ga[2];
+  s[2] = Z[2] * ga[0] + Z[5] * ga[1] + Z[8] * ga[2];
+}
+
+__global__ void __launch_bounds__(PW_THREADS) k_back_substitute(ProblemView pv, const double* __restrict__ X,
                                                                 const double* __restrict__ y,
                                                                 const double* __restrict__ Hpp,
                                                                 const double* __restrict__ gp,
-                                                                const double* __restrict__ Hinv,
-                                                                double* __restrict__ X_cand,
+                                                                const double* __restrict__ Linv,
+                                                                const double* __restrict__ c_pt,
+                                                                const double* __restrict__ fac, int use_factors,
+                                                                LmDiag lm, double* __restrict__ X_cand,
                                                                 double* __restrict__ pt_part) {
-  const int p = pv.p0 + blockIdx.x * PT_THREADS + threadIdx.x;
-  const bool valid = p < pv.p1;
+  __shared__ __align__(16) double2 rows_all[PW_WARPS][256];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int w = blockIdx.x * PW_WARPS + warp;
   double mcc = 0.0, step2 = 0.0, xn2 = 0.0;
-  if (valid) {
-    const bool is_const = pv.pt_const[p] != 0;
-    const int beg = pv.pt_ptr[p], end = pv.pt_ptr[p + 1];
-    double Xp[3];
-    load_point(X, p, Xp);
-    double wty[3] = {0.0, 0.0, 0.0};
-    for (int k = beg; k < end; ++k) {
-      ObsLin o;
-      ImgConst ic;
-      track_obs(pv, pose, Xp, k, o, ic);
-      const int img = __ldg(pv.pm_img + k);
-      const double* yi = y + (size_t)img * 6;
-      const double yc[6] = {__ldg(yi), __ldg(yi + 1), __ldg(yi + 2), __ldg(yi + 3), __ldg(yi + 4), __ldg(yi + 5)};
-      double ga[3], Ng[3];
-      g_vec(o.prot, yc, ga);
-      sym3_mul_vec(o.N, ga, Ng);
-      mcc += ga[0] * o.h[0] + ga[1] * o.h[1] + ga[2] * o.h[2] - 0.5 * (ga[0] * Ng[0] + ga[1] * Ng[1] + ga[2] * Ng[2]);
-      // wty += Q^T ga = R^T (N ga)
-      const double* R = ic.R;
-      wty[0] += R[0] * Ng[0] + R[3] * Ng[1] + R[6] * Ng[2];
-      wty[1] += R[1] * Ng[0] + R[4] * Ng[1] + R[7] * Ng[2];
-      wty[2] += R[2] * Ng[0] + R[5] * Ng[1] + R[8] * Ng[2];
-    }
-    double yp[3] = {0.0, 0.0, 0.0};
-    if (!is_const && end > beg) {
-      double Hi[6], Hp[6], g[3];
-#pragma unroll
-      for (int j = 0; j < 6; ++j) {
-        Hi[j] = Hinv[(size_t)p * 6 + j];
-        Hp[j] = Hpp[(size_t)p * 6 + j];
+  if (w < pv.num_track_warps) {
+    WarpTracks wt;
+    warp_tracks_setup(pv, w, lane, wt);
+    const double2* fac2 = reinterpret_cast<const double2*>(fac);
+    if (wt.n <= 32) {
+      const bool act = wt.has && !wt.tcst && use_factors;  // no factors: all poses constant, y_c = 0
+      double2* rows = rows_all[warp];
+      warp_gather_records(fac2, act ? wt.base + lane : -1, 6, rows, lane);
+      cp_async_commit();
+      const int img = act ? __ldg(pv.pm_img + wt.base + lane) : 0;
+      cp_async_wait<0>();
+      __syncwarp();
+      double v[3] = {0.0, 0.0, 0.0};  // Z^T g of this observation
+      if (act) {
+        const double2* src = rows + lane * 8;
+        const int sw = lane & 7;
+        const double2 c0 = src[0 ^ sw], c1 = src[1 ^ sw], c2 = src[2 ^ sw], c3 = src[3 ^ sw], c4 = src[4 ^ sw],
+                      c5 = src[5 ^ sw];
+        const double Z[9] = {c0.x, c0.y, c1.x, c1.y, c2.x, c2.y, c3.x, c3.y, c4.x};
+        const double prot[3] = {c4.y, c5.x, c5.y};
+        obs_zt_g(Z, prot, y, img, v);
       }
+      segmented_reduce<3>(v, lane, wt.seg_end);
+      double u[3];
 #pragma unroll
-      for (int j = 0; j < 3; ++j) g[j] = gp[(size_t)p * 3 + j];
-      const double rr[3] = {g[0] - wty[0], g[1] - wty[1], g[2] - wty[2]};
-      sym3_mul_vec(Hi, rr, yp);
-      double Hy[3];
-      sym3_mul_vec(Hp, yp, Hy);
-      mcc += yp[0] * (g[0] - wty[0]) + yp[1] * (g[1] - wty[1]) + yp[2] * (g[2] - wty[2]) -
-             0.5 * (yp[0] * Hy[0] + yp[1] * Hy[1] + yp[2] * Hy[2]);
-      step2 = yp[0] * yp[0] + yp[1] * yp[1] + yp[2] * yp[2];
-      xn2 = Xp[0] * Xp[0] + Xp[1] * Xp[1] + Xp[2] * Xp[2];
+      for (int j = 0; j < 3; ++j) u[j] = __shfl_sync(FULL, v[j], wt.start);
+      if (lane < wt.nt) {
+        const bool active = !wt.cst && wt.len > 0;
+        point_step(wt.t0 + lane, active, X, u, Linv, Hpp, gp, c_pt, lm, X_cand, mcc, step2, xn2);
+      }
+    } else {
+      const int p = wt.t0;
+      const bool active = pv.pt_const[p] == 0;
+      double s3[3] = {0.0, 0.0, 0.0};
+      if (active && use_factors) {
+        for (int k = lane; k < wt.n; k += 32) {
+          const double2* src = fac2 + (size_t)(wt.base + k) * 8;
+          const double2 c0 = src[0], c1 = src[1], c2 = src[2], c3 = src[3], c4 = src[4], c5 = src[5];
+          const double Z[9] = {c0.x, c0.y, c1.x, c1.y, c2.x, c2.y, c3.x, c3.y, c4.x};
+          const double prot[3] = {c4.y, c5.x, c5.y};
+          double t[3];
+          obs_zt_g(Z, prot, y, __ldg(pv.pm_img + wt.base + k), t);
+          s3[0] += t[0]; s3[1] += t[1]; s3[2] += t[2];
+        }
+      }
+      warp_allreduce<3>(s3);
+      if (lane == 0) {
+        point_step(p, active, X, s3, Linv, Hpp, gp, c_pt, lm, X_cand, mcc, step2, xn2);
+      }
     }
-    double2* out = reinterpret_cast<double2*>(X_cand + 4 * (size_t)p);
-    out[0] = make_double2(Xp[0] - yp[0], Xp[1] - yp[1]);
-    out[1] = make_double2(Xp[2] - yp[2], 0.0);
   }
-  __shared__ double sm[PT_THREADS / 32 + 1];
-  mcc = block_sum<PT_THREADS / 32>(mcc, sm);
-  step2 = block_sum<PT_THREADS / 32>(step2, sm);
-  xn2 = block_sum<PT_THREADS / 32>(xn2, sm);
+  __shared__ double sm[PW_WARPS + 1];
+  mcc = block_sum<PW_WARPS>(mcc, sm);
+  step2 = block_sum<PW_WARPS>(step2, sm);
+  xn2 = block_sum<PW_WARPS>(xn2, sm);
   if (threadIdx.x == 0) {
     pt_part[(size_t)blockIdx.x * PT_PART + 1] = mcc;
     pt_part[(size_t)blockIdx.x * PT_PART + 2] = step2;
@@ -1098,12 +1322,14 @@ void launch_img_scalars(const ProblemView& pv, const double* img_part, const dou
                                     scal);
 }
 int points_grid(int P) { return (P + PT_THREADS - 1) / PT_THREADS; }
+int track_warp_grid(int num_track_warps) { return (num_track_warps + PW_WARPS - 1) / PW_WARPS; }
 void launch_points(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,
-                   int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* fac,
-                   double* pt_part, double* scal, int write_factors, cudaStream_t st) {
-  if (pv.p1 > pv.p0)
-    k_points<<<points_grid(pv.p1 - pv.p0), PT_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp,
-                                                       Hinv, fac, pt_part, scal, write_factors);
+                   int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* Linv,
+                   double* fac, double* pt_part, double* scal, int write_factors, cudaStream_t st) {
+  if (pv.num_track_warps > 0)
+    k_points<<<track_warp_grid(pv.num_track_warps), PW_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling,
+                                                                         jacobi_scaling, Hpp, gp, Hinv, Linv, fac,
+                                                                         pt_part, scal, write_factors);
 }
 void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaStream_t st) {
   k_pt_scalars_gmax<<<1, 1024, 0, st>>>(pt_part, nblk, scal);
@@ -1165,15 +1391,16 @@ cudaError_t launch_pcg(const ProblemView& pv, const PcgPlan& pl, const double* S
     return cudaLaunchCooperativeKernel((void*)k_pcg<true>, dim3(pl.grid), dim3(PCG_THREADS), args, pl.smem_bytes, st);
   return cudaLaunchCooperativeKernel((void*)k_pcg<false>, dim3(pl.grid), dim3(PCG_THREADS), args, pl.smem_bytes, st);
 }
-void launch_cam_update(const ProblemView& pv, const double* pose, const double* y, double* pose_cand, double* scal,
-                       cudaStream_t st) {
-  k_cam_update<<<1, 256, 0, st>>>(pv, pose, y, pose_cand, scal);
+void launch_cam_update(const ProblemView& pv, const double* pose, const double* y, const double* Hc, const double* gc,
+                       const double* c_img, LmDiag lm, double* pose_cand, double* scal, cudaStream_t st) {
+  k_cam_update<<<1, 256, 0, st>>>(pv, pose, y, Hc, gc, c_img, lm, pose_cand, scal);
 }
-void launch_back_substitute(const ProblemView& pv, const double* pose, const double* X, const double* y,
-                            const double* Hpp, const double* gp, const double* Hinv, double* X_cand, double* pt_part,
-                            cudaStream_t st) {
-  if (pv.p1 > pv.p0)
-    k_back_substitute<<<points_grid(pv.p1 - pv.p0), PT_THREADS, 0, st>>>(pv, pose, X, y, Hpp, gp, Hinv, X_cand, pt_part);
+void launch_back_substitute(const ProblemView& pv, const double* X, const double* y, const double* Hpp,
+                            const double* gp, const double* Linv, const double* c_pt, const double* fac,
+                            int use_factors, LmDiag lm, double* X_cand, double* pt_part, cudaStream_t st) {
+  if (pv.num_track_warps > 0)
+    k_back_substitute<<<track_warp_grid(pv.num_track_warps), PW_THREADS, 0, st>>>(pv, X, y, Hpp, gp, Linv, c_pt, fac,
+                                                                                  use_factors, lm, X_cand, pt_part);
 }
 void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, cudaStream_t st) {
   k_pt_scalars_step<<<1, 1024, 0, st>>>(pt_part, nblk, scal);

@@ -25,6 +25,7 @@ enum Scal {
   S_BAD_POINTS = 12, // number of point blocks whose damped Hpp was not positive definite
   S_PCG_CYC_SPMV = 13, S_PCG_CYC_REDUCE = 14, S_PCG_CYC_UPDATE = 15,  // SM cycles CTA 0 spent per phase
   S_PCG_CYC_DETAIL = 16,  // 7 slots: cluster PCG cycles of CTA 0: sync A, halo, products, sync B, row sums, sync C, update
+  S_MCC_C = 23,      // image part of the model cost change (k_cam_update; replicated in a sharded solve)
   S_COUNT = 24
 };
 
@@ -38,6 +39,9 @@ struct ProblemView {
   // owned ranges of a sharded solve (mpba_shard): tracks of points outside [p0, p1) and image-order chunks of
   // images outside [i0, i1) live on other ranks.  Unsharded: [0, P) and [0, C).
   int p0, p1, i0, i1;
+  // track-order warp packing (mpba_pack_tracks): warp w owns the whole tracks tw_first[w] .. tw_first[w+1]
+  int num_track_warps;
+  const int32_t* tw_first;
   const int32_t* img_camera;
   const uint8_t* img_free_mask;
   const double* img_shift_scale;
@@ -84,9 +88,10 @@ void launch_img_scalars(const ProblemView& pv, const double* img_part, const dou
 
 // ---- track order: Hpp, gp, point-block Cholesky, Schur factors ------------------------------------
 void launch_points(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,
-                   int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* fac,
-                   double* pt_part, double* scal, int write_factors, cudaStream_t st);
-int points_grid(int num_owned_points);
+                   int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* Linv,
+                   double* fac, double* pt_part, double* scal, int write_factors, cudaStream_t st);
+int points_grid(int num_owned_points);  // k_evaluate: one thread per track
+int track_warp_grid(int num_track_warps);  // k_points / k_back_substitute: CTAs (= rows of pt_part)
 void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaStream_t st);
 
 // ---- reduced camera system ----------------------------------------------------------------------
@@ -173,11 +178,12 @@ cudaError_t launch_coarse_setup(const CoarsePlan& cp, int C, const double* pose,
                                 double* Ainv, cudaStream_t st);
 
 // ---- step ---------------------------------------------------------------------------------------
-void launch_cam_update(const ProblemView& pv, const double* pose, const double* y, double* pose_cand, double* scal,
-                       cudaStream_t st);
-void launch_back_substitute(const ProblemView& pv, const double* pose, const double* X, const double* y,
-                            const double* Hpp, const double* gp, const double* Hinv, double* X_cand, double* pt_part,
-                            cudaStream_t st);
+// q (+) -y, t - y, step norms, and the image part of the model cost change (g'y + y'Dy) / 2
+void launch_cam_update(const ProblemView& pv, const double* pose, const double* y, const double* Hc, const double* gc,
+                       const double* c_img, LmDiag lm, double* pose_cand, double* scal, cudaStream_t st);
+void launch_back_substitute(const ProblemView& pv, const double* X, const double* y, const double* Hpp,
+                            const double* gp, const double* Linv, const double* c_pt, const double* fac,
+                            int use_factors, LmDiag lm, double* X_cand, double* pt_part, cudaStream_t st);
 void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, cudaStream_t st);
 
 // ---- misc ---------------------------------------------------------------------------------------

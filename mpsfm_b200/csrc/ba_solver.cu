@@ -114,7 +114,7 @@ size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Workspace {
   double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *img_part, *c_img, *c_pt, *Hpp, *gp, *Hinv, *fac, *S,
-      *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal, *scal_all;
+      *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal, *scal_all, *Linv;
   double *Zc = nullptr, *Ac = nullptr, *Ainv = nullptr;  // coarse space (coarse.cu)
   int32_t* plan = nullptr;  // PCG cluster plan (pcg_cluster.cu)
   size_t plan_ints = 0;
@@ -136,7 +136,7 @@ void carve(const mpba_problem* p, const mpba_shard* sh, char* base, Workspace& w
     return ptr;
   };
   const size_t C = p->num_images, P = p->num_points, B = p->num_blocks;
-  const size_t nblk = (size_t)points_grid(sh ? sh->pt_end - sh->pt_begin : (int)P);
+  const size_t nblk = (size_t)track_warp_grid(p->num_track_warps);
   const size_t Ppad = sh ? std::max(P, (size_t)sh->world * (size_t)sh->pt_stride) : P;
   for (int k = 0; k < 2; ++k) {
     w.pose[k] = take(C * 8);
@@ -151,6 +151,7 @@ void carve(const mpba_problem* p, const mpba_shard* sh, char* base, Workspace& w
   w.Hpp = take(P * 6);
   w.gp = take(P * 3);
   w.Hinv = take(P * 6);
+  w.Linv = take(P * 9);
   w.fac = take((p->flags & MPBA_FLAG_STRUCTURE_ONLY) ? 0 : (size_t)p->num_obs * FAC_STRIDE);
   w.S = take(B * 36);
   w.rhs = take(C * 6);
@@ -193,6 +194,8 @@ int check_problem(mpba_handle* h, const mpba_problem* p) {
   if (!(p->flags & MPBA_FLAG_STRUCTURE_ONLY) &&
       (!p->s_row || p->num_upper < p->num_images || !p->u_block || !p->u_item_ptr || (p->num_obs > 0 && (!p->item_a || !p->item_b))))
     return fail(h, MPBA_E_INVALID, "Schur work lists (s_row, u_block, u_item_ptr, item_a, item_b) missing");
+  if (p->num_points > 0 && (p->num_track_warps <= 0 || !p->track_warp_first))
+    return fail(h, MPBA_E_INVALID, "track_warp_first missing (mpba_pack_tracks)");
   if (p->reproj_loss < 0 || p->reproj_loss > 3 || p->depth_loss < 0 || p->depth_loss > 3)
     return fail(h, MPBA_E_INVALID, "unknown loss type");
   return MPBA_OK;
@@ -212,6 +215,7 @@ ProblemView view_of(const mpba_problem* p) {
   v.loss.reproj_loss = p->reproj_loss; v.loss.depth_loss = p->depth_loss;
   v.loss.reproj_scale = p->reproj_loss_scale; v.loss.reproj_weight = p->reproj_loss_weight;
   v.p0 = 0; v.p1 = v.P; v.i0 = 0; v.i1 = v.C;
+  v.num_track_warps = p->num_track_warps; v.tw_first = p->track_warp_first;
   return v;
 }
 
@@ -264,7 +268,7 @@ int begin(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t work
   if (sh) {
     c.pv.p0 = sh->pt_begin; c.pv.p1 = sh->pt_end; c.pv.i0 = sh->img_begin; c.pv.i1 = sh->img_end;
   }
-  c.nblk = points_grid(c.pv.p1 - c.pv.p0);
+  c.nblk = track_warp_grid(c.pv.num_track_warps);
   c.structure_only = prob->flags & MPBA_FLAG_STRUCTURE_ONLY;
   c.max_row_blocks = prob->s_max_row_blocks;
   h->launch_count = 0;
@@ -516,7 +520,7 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
   CU(cudaMemsetAsync(c.w.scal + S_BAD_POINTS, 0, sizeof(double), h->stream));
   {
     Timer t(h, KS_POINTS_SCHUR);
-    launch_points(c.pv, pose, X, lm, c.w.c_pt, compute_scaling, opt->jacobi_scaling, c.w.Hpp, c.w.gp, c.w.Hinv, c.w.fac,
+    launch_points(c.pv, pose, X, lm, c.w.c_pt, compute_scaling, opt->jacobi_scaling, c.w.Hpp, c.w.gp, c.w.Hinv, c.w.Linv, c.w.fac,
                   c.w.pt_part, c.w.scal, schur ? 1 : 0, h->stream);
   }
   {
@@ -641,6 +645,23 @@ void mpba_destroy(mpba_handle* h) {
 }
 
 const char* mpba_last_error(const mpba_handle* h) { return h ? h->err.c_str() : "invalid handle"; }
+
+int mpba_pack_tracks(const int32_t* pt_ptr, int32_t pt_begin, int32_t pt_end, int32_t* first, int32_t* num_warps) {
+  if (!pt_ptr || !first || !num_warps || pt_begin < 0 || pt_end < pt_begin) return MPBA_E_INVALID;
+  int32_t nw = 0;
+  int32_t t = pt_begin;
+  while (t < pt_end) {
+    first[nw++] = t;
+    const int64_t s0 = pt_ptr[t];
+    int32_t e = t + 1;  // a track longer than 32 observations is a group of its own
+    while (e < pt_end && e - t < 32 && (int64_t)pt_ptr[e + 1] - s0 <= 32) ++e;
+    if ((int64_t)pt_ptr[t + 1] - s0 > 32) e = t + 1;
+    t = e;
+  }
+  first[nw] = pt_end;
+  *num_warps = nw;
+  return MPBA_OK;
+}
 
 int mpba_workspace_bytes(const mpba_problem* prob, size_t* bytes) {
   if (!prob || !bytes) return MPBA_E_INVALID;
@@ -885,11 +906,13 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
     first = false;
     {
       Timer t(h, KS_CAM_UPDATE);
-      launch_cam_update(c.pv, c.w.pose[cur], c.w.y, c.w.pose[cand], c.w.scal, h->stream);
+      launch_cam_update(c.pv, c.w.pose[cur], c.w.y, c.w.Hc[cur], c.w.gc[cur], c.w.c_img, lm, c.w.pose[cand], c.w.scal,
+                        h->stream);
     }
     {
       Timer t(h, KS_BACK_SUBSTITUTE);
-      launch_back_substitute(c.pv, c.w.pose[cur], c.w.X[cur], c.w.y, c.w.Hpp, c.w.gp, c.w.Hinv, c.w.X[cand],
+      launch_back_substitute(c.pv, c.w.X[cur], c.w.y, c.w.Hpp, c.w.gp, c.w.Linv, c.w.c_pt, c.w.fac,
+                             c.structure_only ? 0 : 1, lm, c.w.X[cand],
                              c.w.pt_part, h->stream);
     }
     {
@@ -929,7 +952,7 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
     it.pcg_iterations = (int32_t)s[S_PCG_ITERS];
     total_pcg += it.pcg_iterations;
     ++iteration;
-    const double mcc = s[S_MCC];
+    const double mcc = s[S_MCC] + s[S_MCC_C];  // points + images: (g'y + y'Dy) / 2
     bool ok = s[S_PCG_FLAG] != 2.0 && s[S_BAD_POINTS] == 0.0 && isfinite(mcc) && isfinite(s[S_STEP2_P]) &&
               isfinite(s[S_STEP2_C]) && mcc > 0.0;
     it.step_is_valid = ok ? 1 : 0;

@@ -67,6 +67,7 @@ class MpbaProblem(C.Structure):
         ("reproj_loss", C.c_int32), ("depth_loss", C.c_int32),
         ("reproj_loss_scale", C.c_double), ("reproj_loss_weight", C.c_double),
         ("flags", C.c_int32), ("s_max_row_blocks", C.c_int32),
+        ("num_track_warps", C.c_int32), ("reserved", C.c_int32), ("track_warp_first", C.c_void_p),
     ]
 
 
@@ -116,7 +117,7 @@ EXPORTS = (
     "mpba_version", "mpba_create", "mpba_destroy", "mpba_last_error", "mpba_default_options",
     "mpba_workspace_bytes", "mpba_evaluate", "mpba_linearize", "mpba_reduced_system", "mpba_solve",
     "mpba_kernel_times", "mpba_kernel_name", "mpba_point_covariances",
-    "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
+    "mpba_pack_tracks", "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
 )
 
 _lib = None
@@ -148,6 +149,7 @@ def load_library(path: Optional[str] = None):
     lib.mpba_point_covariances.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t, C.c_void_p]
     lib.mpba_solve.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t,
                                C.POINTER(MpbaOptions), C.POINTER(MpbaSummary)]
+    lib.mpba_pack_tracks.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_int32)]
     lib.mpba_comm_unique_id.argtypes = [C.c_void_p, C.c_char_p]
     lib.mpba_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_char_p]
     lib.mpba_workspace_bytes_sharded.argtypes = [C.POINTER(MpbaProblem), C.POINTER(MpbaShard), C.POINTER(C.c_size_t)]
@@ -211,6 +213,7 @@ class HostLayout:
     u_item_ptr: np.ndarray
     item_a: np.ndarray
     item_b: np.ndarray
+    track_warp_first: np.ndarray  # [num_track_warps + 1] (mpba_pack_tracks)
     reproj_loss: int
     depth_loss: int
     reproj_loss_scale: float
@@ -224,6 +227,19 @@ class HostLayout:
     @property
     def num_chunks(self) -> int:
         return int(self.chunk_img.shape[0])
+
+
+def pack_tracks(pt_ptr: np.ndarray, pt_begin: int, pt_end: int) -> np.ndarray:
+    """Warp groups of whole tracks for the track-order passes (host helper of libmpba.so: a sequential greedy
+    scan, <= 32 observations and <= 32 tracks per group)."""
+    lib = load_library()
+    ptr = np.ascontiguousarray(pt_ptr, dtype=np.int32)
+    first = np.empty(pt_end - pt_begin + 1, dtype=np.int32)
+    nw = C.c_int32()
+    rc = lib.mpba_pack_tracks(ptr.ctypes.data, int(pt_begin), int(pt_end), first.ctypes.data, C.byref(nw))
+    if rc != 0:
+        raise EngineError(f"mpba_pack_tracks failed with code {rc}")
+    return first[: nw.value + 1].copy()
 
 
 def _ptr_from_counts(counts: np.ndarray) -> np.ndarray:
@@ -344,6 +360,7 @@ def build_layout(problem: BundleProblem) -> HostLayout:
         chunk_img=chunk_img, chunk_begin=chunk_begin, chunk_end=chunk_end, img_chunk_ptr=img_chunk_ptr,
         s_row_ptr=s_row_ptr, s_col=s_col, s_diag=s_diag, s_transpose=s_transpose,
         s_row=s_row, u_block=u_block, u_item_ptr=u_item_ptr, item_a=item_a, item_b=item_b,
+        track_warp_first=pack_tracks(pt_ptr, 0, P),
         reproj_loss=int(pr.reproj_loss), depth_loss=int(pr.depth_loss),
         reproj_loss_scale=float(pr.reproj_loss_scale), reproj_loss_weight=float(pr.reproj_loss_weight),
         flags=FLAG_STRUCTURE_ONLY if structure_only else 0,
@@ -426,6 +443,7 @@ def shard_layout(lay: HostLayout, rank: int, world: int):
         img_chunk_ptr=np.clip(lay.img_chunk_ptr.astype(np.int64) - ch0, 0, ch1 - ch0).astype(np.int32),
         u_item_ptr=u_item_ptr, item_a=item_a, item_b=item_b,
     )
+    out.track_warp_first = pack_tracks(out.pt_ptr, spec.pt_begin, spec.pt_end)
     return out, spec
 
 
@@ -445,7 +463,7 @@ _DEVICE_FIELDS = (
     "img_pose", "img_camera", "img_free_mask", "img_shift_scale", "cam_model", "cam_params", "pt_xyz", "pt_const",
     "pt_ptr", "pm_img", "pm_xy", "pm_depth", "pm_src", "img_ptr", "cm_pt", "cm_xy", "cm_depth",
     "chunk_img", "chunk_begin", "chunk_end", "img_chunk_ptr", "s_row_ptr", "s_col", "s_diag", "s_transpose",
-    "s_row", "u_block", "u_item_ptr", "item_a", "item_b",
+    "s_row", "u_block", "u_item_ptr", "item_a", "item_b", "track_warp_first",
 )
 
 
@@ -520,6 +538,7 @@ class BundleAdjuster:
             self.prob.num_chunks = lay.num_chunks
             self.prob.num_blocks = lay.num_blocks
             self.prob.num_upper = int(lay.u_block.shape[0])
+            self.prob.num_track_warps = int(lay.track_warp_first.shape[0]) - 1
             self.prob.reproj_loss, self.prob.depth_loss = lay.reproj_loss, lay.depth_loss
             self.prob.reproj_loss_scale, self.prob.reproj_loss_weight = lay.reproj_loss_scale, lay.reproj_loss_weight
             self.prob.flags = lay.flags
