@@ -340,7 +340,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg3")
-    ap.add_argument("--pcg-tol", dest="pcg_tol", type=float, default=1e-12)
+    ap.add_argument("--pcg-tol", dest="pcg_tol", type=float, default=1e-10)
     ap.add_argument("--pcg-max-iter", dest="pcg_max_iter", type=int, default=2000)
     ap.add_argument("--ref-obs", dest="ref_obs", type=int, default=40_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -14,7 +14,8 @@
  *   - all floating point data is IEEE double, all indices int32,
  *   - every call returns 0 on success or a negative MPBA_E_* code; the message is available from
  *     mpba_last_error(); nothing throws across the boundary,
- *   - img_pose slot 7 is scratch: a solve leaves exp(log-scale) of the image's depth prior there,
+ *   - slot 7 of an img_pose record and slot 3 of a pt_xyz record are scratch: a solve leaves exp(log-scale) of
+ *     the image's depth prior / the point's constant flag there,
  *   - a handle is bound to one device and one stream and is not thread-safe,
  *   - there is no CPU fallback: without a CUDA device mpba_create fails with MPBA_E_CUDA.
  */
@@ -156,7 +157,9 @@ typedef struct mpba_options {
   double function_tolerance;               /* 1e-6 */
   double gradient_tolerance;               /* 1e-10 */
   double parameter_tolerance;              /* 1e-8 */
-  double pcg_tolerance;                    /* 1e-12: stop when sqrt(r'M^-1 r / b'M^-1 b) <= tol */
+  double pcg_tolerance;                    /* 1e-10: stop when sqrt(r'M^-1 r / b'M^-1 b) <= tol.  The step minimises
+                                              the quadratic model, so a relative step error eps moves the cost by
+                                              O(eps^2): 1e-10 leaves the LM trajectory on the exact-solve one to ~1e-13 */
   int32_t profile;                         /* 1: CUDA-event time every kernel launch (see mpba_kernel_times) */
   int32_t verbose;
   int32_t pcg_kernel;                      /* 0: automatic (cluster-resident when S fits one 16-CTA cluster,

@@ -95,9 +95,6 @@ __global__ void __launch_bounds__(256) k_img_chunks(ProblemView pv, const double
   const int beg = pv.chunk_begin[c], end = pv.chunk_end[c];
   ImgConst ic;
   load_img(pv, pose, img, ic);
-  double prm[MPBA_MAX_PRM];
-#pragma unroll
-  for (int j = 0; j < MPBA_MAX_PRM; ++j) prm[j] = __ldg(ic.prm + j);
   const bool img_const = pv.img_free_mask[img] == 0;
   const double2* xy = reinterpret_cast<const double2*>(pv.cm_xy);
   const double* dd = pv.cm_depth;
@@ -107,14 +104,33 @@ __global__ void __launch_bounds__(256) k_img_chunks(ProblemView pv, const double
 #pragma unroll
   for (int j = 0; j < 29; ++j) acc[j] = 0.0;
 
-  for (int k = beg + (int)threadIdx.x; k < end; k += 256) {
+  // Software pipeline: the operands of the thread's NEXT observation (index -> point gather, xy, depth row) are
+  // in flight while the current one is linearised -- with 8 warps per SM (236 registers) nothing else hides the
+  // DRAM + L2 round trip of the dependent gather.  Slot 3 of a point record carries its constant flag.
+  struct Operands {
+    double2 xa, xb, o2;
+    double d, w, a;
+  };
+  auto fetch = [&](int k, Operands& op) {
     const int pt = __ldg(pv.cm_pt + k);
-    double Xp[3];
-    load_point(X, pt, Xp);
-    const double2 o2 = __ldg(xy + k);
-    const double d = __ldg(dd + k), w = __ldg(dd + N + k), a = __ldg(dd + 2 * N + k);
+    const double2* xp = reinterpret_cast<const double2*>(X + 4 * (size_t)pt);
+    op.xa = __ldg(xp);
+    op.xb = __ldg(xp + 1);
+    op.o2 = __ldg(xy + k);
+    op.d = __ldg(dd + k);
+    op.w = __ldg(dd + N + k);
+    op.a = __ldg(dd + 2 * N + k);
+  };
+  int k = beg + (int)threadIdx.x;
+  Operands cur, nxt;
+  if (k < end) fetch(k, cur);
+  for (; k < end; k += 256) {
+    const bool more = k + 256 < end;
+    if (more) fetch(k + 256, nxt);
+    const double Xp[3] = {cur.xa.x, cur.xa.y, cur.xb.x};
     ObsLin o;
-    linearize_obs<true, true>(ic.pose, ic.R, Xp, ic.model, prm, o2.x, o2.y, d, w, a, ic.b, ic.es, pv.loss, o);
+    linearize_obs<true, true>(ic.pose, ic.R, Xp, ic.model, ic.prm, cur.o2.x, cur.o2.y, cur.d, cur.w, cur.a, ic.b, ic.es,
+                              pv.loss, o);
     double H[21], g[6];
     gt_n_g_upper(o.prot, o.N, H);
     gt_vec(o.prot, o.h, g);
@@ -122,8 +138,9 @@ __global__ void __launch_bounds__(256) k_img_chunks(ProblemView pv, const double
     for (int j = 0; j < 21; ++j) acc[j] += H[j];
 #pragma unroll
     for (int j = 0; j < 6; ++j) acc[21 + j] += g[j];
-    const bool fixed = img_const && (pv.pt_const[pt] != 0);
+    const bool fixed = img_const && (cur.xb.y != 0.0);
     if (fixed) acc[28] += o.rho; else acc[27] += o.rho;
+    if (more) cur = nxt;
   }
 
   __shared__ double sm[8][IMG_PART];
@@ -248,7 +265,8 @@ struct WarpTracks {
   bool tcst;            // the track is a constant point
 };
 
-__device__ __forceinline__ void warp_tracks_setup(const ProblemView& pv, int w, int lane, WarpTracks& wt) {
+__device__ __forceinline__ void warp_tracks_setup(const ProblemView& pv, int w, int lane, WarpTracks& wt,
+                                                  int* scratch /* 32 ints of shared memory of this warp */) {
   wt.t0 = __ldg(pv.tw_first + w);
   wt.nt = __ldg(pv.tw_first + w + 1) - wt.t0;
   wt.base = __ldg(pv.pt_ptr + wt.t0);
@@ -264,10 +282,12 @@ __device__ __forceinline__ void warp_tracks_setup(const ProblemView& pv, int w, 
   wt.tl = 0; wt.seg_end = wt.n; wt.tcst = true;
   if (wt.n <= 32) {
     const bool nonempty = wt.len > 0;
-    const unsigned ne = __ballot_sync(FULL, nonempty);                              // track lanes with observations
-    const unsigned heads = __reduce_or_sync(FULL, nonempty ? (1u << wt.start) : 0u);  // their first observation lanes
-    const int rank = __popc(heads & (0xffffffffu >> (31 - lane)));                  // non-empty tracks starting <= lane
-    wt.tl = wt.has ? __fns(ne, 0, rank) : 0;
+    const unsigned heads = __reduce_or_sync(FULL, nonempty ? (1u << wt.start) : 0u);  // first observation lanes
+    if (nonempty) scratch[wt.start] = lane;  // a track lane tells its first observation lane who it is
+    __syncwarp();
+    const unsigned le = heads & (0xffffffffu >> (31 - lane));
+    wt.tl = (wt.has && le) ? scratch[31 - __clz(le)] : 0;
+    __syncwarp();
     const unsigned above = (lane == 31) ? 0u : (heads & (0xffffffffu << (lane + 1)));
     wt.seg_end = above ? (__ffs(above) - 1) : wt.n;
     wt.tcst = __shfl_sync(FULL, wt.cst ? 1 : 0, wt.tl) != 0;
@@ -395,7 +415,7 @@ __global__ void __launch_bounds__(PW_THREADS) k_points(ProblemView pv, const dou
   double gmax = 0.0;
   if (w < pv.num_track_warps) {
     WarpTracks wt;
-    warp_tracks_setup(pv, w, lane, wt);
+    warp_tracks_setup(pv, w, lane, wt, reinterpret_cast<int*>(rows_all[warp]));
     double2* fac2 = reinterpret_cast<double2*>(fac);
     if (wt.n <= 32) {
       // ---- observation lanes: linearise, reduce over the track
@@ -1125,8 +1145,9 @@ __device__ __forceinline__ void point_step(int p, bool active, const double* __r
                                            const double* __restrict__ Linv, const double* __restrict__ Hpp,
                                            const double* __restrict__ gp, const double* __restrict__ c_pt, LmDiag lm,
                                            double* __restrict__ X_cand, double& mcc, double& step2, double& xn2) {
-  double Xp[3];
-  load_point(X, p, Xp);
+  const double2* xp = reinterpret_cast<const double2*>(X + 4 * (size_t)p);
+  const double2 xa = __ldg(xp), xb = __ldg(xp + 1);
+  const double Xp[3] = {xa.x, xa.y, xb.x};
   double yp[3] = {0.0, 0.0, 0.0};
   if (active) {
     double Li[6];
@@ -1149,7 +1170,7 @@ __device__ __forceinline__ void point_step(int p, bool active, const double* __r
   }
   double2* out = reinterpret_cast<double2*>(X_cand + 4 * (size_t)p);
   out[0] = make_double2(Xp[0] - yp[0], Xp[1] - yp[1]);
-  out[1] = make_double2(Xp[2] - yp[2], 0.0);
+  out[1] = make_double2(Xp[2] - yp[2], xb.y);  // slot 3: the point's constant flag travels with it
 }
 
 // s = Z^T (G y_c) of one observation from its record (Z 9, p_rot 3) and the image's y (6)
@@ -1180,7 +1201,7 @@ __global__ void __launch_bounds__(PW_THREADS) k_back_substitute(ProblemView pv, 
   double mcc = 0.0, step2 = 0.0, xn2 = 0.0;
   if (w < pv.num_track_warps) {
     WarpTracks wt;
-    warp_tracks_setup(pv, w, lane, wt);
+    warp_tracks_setup(pv, w, lane, wt, reinterpret_cast<int*>(rows_all[warp]));
     const double2* fac2 = reinterpret_cast<const double2*>(fac);
     if (wt.n <= 32) {
       const bool act = wt.has && !wt.tcst && use_factors;  // no factors: all poses constant, y_c = 0
@@ -1294,6 +1315,12 @@ __global__ void k_normalize_poses(int C, const double* __restrict__ in, const do
   o[0] = s[0] / n; o[1] = s[1] / n; o[2] = s[2] / n; o[3] = s[3] / n;
   o[4] = s[4]; o[5] = s[5]; o[6] = s[6];
   o[7] = exp(shift_scale[2 * (size_t)i + 1]);  // exp(log-scale) of the depth prior: constant block, one exp per image
+}
+
+// slot 3 of every point record <- 1.0 for a constant point, 0.0 otherwise (read by k_img_chunks with the gather)
+__global__ void k_flag_points(int P, const uint8_t* __restrict__ pt_const, double* __restrict__ X) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < P) X[4 * (size_t)p + 3] = pt_const[p] ? 1.0 : 0.0;
 }
 
 __global__ void k_expand_hcc(int C, const double* __restrict__ Hc, double* __restrict__ H36) {
@@ -1411,6 +1438,9 @@ void launch_evaluate(const ProblemView& pv, const double* pose, const double* X,
 }
 void launch_normalize_poses(int C, const double* in, const double* shift_scale, double* out, cudaStream_t st) {
   if (C > 0) k_normalize_poses<<<(C + 127) / 128, 128, 0, st>>>(C, in, shift_scale, out);
+}
+void launch_flag_points(int P, const uint8_t* pt_const, double* X, cudaStream_t st) {
+  if (P > 0) k_flag_points<<<(P + 255) / 256, 256, 0, st>>>(P, pt_const, X);
 }
 void launch_expand_hcc(int C, const double* Hc, double* Hcc36, cudaStream_t st) {
   if (C > 0) k_expand_hcc<<<(C * 36 + 255) / 256, 256, 0, st>>>(C, Hc, Hcc36);

@@ -191,6 +191,7 @@ void launch_evaluate(const ProblemView& pv, const double* pose, const double* X,
                      cudaStream_t st);
 // unit quaternions (COLMAP normalises before adding to the problem) + exp(log-scale) into slot 7
 void launch_normalize_poses(int C, const double* in, const double* shift_scale, double* out, cudaStream_t st);
+void launch_flag_points(int P, const uint8_t* pt_const, double* X, cudaStream_t st);
 void launch_expand_hcc(int C, const double* Hc, double* Hcc36, cudaStream_t st);
 
 }  // namespace mpba

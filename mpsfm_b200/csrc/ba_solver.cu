@@ -275,6 +275,17 @@ int begin(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t work
   return MPBA_OK;
 }
 
+// working copy of the caller's points, slot 3 of every record = constant flag (read by the image-order pass)
+int stage_points(Ctx& c, const mpba_problem* prob, double* X) {
+  mpba_handle* h = c.h;
+  if (c.pv.P > 0) {
+    CU(cudaMemcpyAsync(X, prob->pt_xyz, (size_t)c.pv.P * 4 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    launch_flag_points(c.pv.P, c.pv.pt_const, X, h->stream);
+    h->launch_count += 1;
+  }
+  return MPBA_OK;
+}
+
 // cost / Hcc / gc of state (pose, X) into buffer set k.  Sharded: every rank reduces the chunks of its own images
 // (zeros elsewhere), the image blocks are then all-reduced -- a sum with exact zeros, so the result is the owner's
 // value bit for bit on every rank.
@@ -604,7 +615,7 @@ void mpba_default_options(mpba_options* o) {
   o->function_tolerance = 1e-6;
   o->gradient_tolerance = 1e-10;
   o->parameter_tolerance = 1e-8;
-  o->pcg_tolerance = 1e-12;
+  o->pcg_tolerance = 1e-10;
   o->profile = 0;
   o->verbose = 0;
   o->pcg_kernel = 0;
@@ -738,11 +749,13 @@ int mpba_evaluate(mpba_handle* h, const mpba_problem* prob, void* workspace, siz
     Timer t(h, KS_MISC);
     launch_normalize_poses(c.pv.C, prob->img_pose, prob->img_shift_scale, c.w.pose[0], h->stream);
   }
+  rc = stage_points(c, prob, c.w.X[0]);
+  if (rc) return rc;
   if (r_reproj || r_depth) {
     Timer t(h, KS_EVALUATE);
-    launch_evaluate(c.pv, c.w.pose[0], prob->pt_xyz, r_reproj, r_depth, h->stream);
+    launch_evaluate(c.pv, c.w.pose[0], c.w.X[0], r_reproj, r_depth, h->stream);
   }
-  rc = enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 0, 1);
+  rc = enqueue_image_pass(c, c.w.pose[0], c.w.X[0], 0, 0, 1);
   if (rc) return rc;
   rc = fetch_scalars(c);
   if (rc) return rc;
@@ -762,10 +775,12 @@ int mpba_linearize(mpba_handle* h, const mpba_problem* prob, void* workspace, si
   mpba_options opt;
   mpba_default_options(&opt);
   launch_normalize_poses(c.pv.C, prob->img_pose, prob->img_shift_scale, c.w.pose[0], h->stream);
-  rc = enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 1, 1);
+  rc = stage_points(c, prob, c.w.X[0]);
+  if (rc) return rc;
+  rc = enqueue_image_pass(c, c.w.pose[0], c.w.X[0], 0, 1, 1);
   if (rc) return rc;
   LmDiag lm{opt.initial_trust_region_radius, opt.min_lm_diagonal, opt.max_lm_diagonal};
-  rc = enqueue_points_and_system(c, c.w.pose[0], prob->pt_xyz, 0, lm, 1, &opt, false);
+  rc = enqueue_points_and_system(c, c.w.pose[0], c.w.X[0], 0, lm, 1, &opt, false);
   if (rc) return rc;
   if (Hcc) launch_expand_hcc(c.pv.C, c.w.Hc[0], Hcc, h->stream);
   if (gc) CU(cudaMemcpyAsync(gc, c.w.gc[0], (size_t)c.pv.C * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
@@ -791,9 +806,11 @@ int mpba_point_covariances(mpba_handle* h, const mpba_problem* prob, void* works
   mpba_default_options(&opt);
   opt.jacobi_scaling = 0;
   launch_normalize_poses(c.pv.C, prob->img_pose, prob->img_shift_scale, c.w.pose[0], h->stream);
+  rc = stage_points(c, prob, c.w.X[0]);
+  if (rc) return rc;
   // undamped: an infinite trust-region radius makes the LM diagonal vanish
   LmDiag lm{INFINITY, opt.min_lm_diagonal, opt.max_lm_diagonal};
-  rc = enqueue_points_and_system(c, c.w.pose[0], prob->pt_xyz, 0, lm, 1, &opt, false);
+  rc = enqueue_points_and_system(c, c.w.pose[0], c.w.X[0], 0, lm, 1, &opt, false);
   if (rc) return rc;
   CU(cudaMemcpyAsync(cov, c.w.Hinv, (size_t)c.pv.P * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
   CU(cudaStreamSynchronize(h->stream));
@@ -813,10 +830,12 @@ int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspac
   rc = build_pcg_cluster_plan(c, prob, opt.pcg_kernel, opt.pcg_coarse);
   if (rc) return rc;
   launch_normalize_poses(c.pv.C, prob->img_pose, prob->img_shift_scale, c.w.pose[0], h->stream);
-  rc = enqueue_image_pass(c, c.w.pose[0], prob->pt_xyz, 0, 1, opt.jacobi_scaling);
+  rc = stage_points(c, prob, c.w.X[0]);
+  if (rc) return rc;
+  rc = enqueue_image_pass(c, c.w.pose[0], c.w.X[0], 0, 1, opt.jacobi_scaling);
   if (rc) return rc;
   LmDiag lm{radius, opt.min_lm_diagonal, opt.max_lm_diagonal};
-  rc = enqueue_points_and_system(c, c.w.pose[0], prob->pt_xyz, 0, lm, 1, &opt, true);
+  rc = enqueue_points_and_system(c, c.w.pose[0], c.w.X[0], 0, lm, 1, &opt, true);
   if (rc) return rc;
   if (c.structure_only) return fail(h, MPBA_E_INVALID, "no reduced camera system: all poses are constant");
   if (S) CU(cudaMemcpyAsync(S, c.w.S, (size_t)c.pv.B * 36 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
@@ -858,8 +877,8 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
   int cur = 0;
   launch_normalize_poses(c.pv.C, prob->img_pose, prob->img_shift_scale, c.w.pose[cur], h->stream);
   h->launch_count += 1;
-  if (c.pv.P > 0)
-    CU(cudaMemcpyAsync(c.w.X[cur], prob->pt_xyz, (size_t)c.pv.P * 4 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  rc = stage_points(c, prob, c.w.X[cur]);
+  if (rc) return rc;
 
   // ---- iteration zero
   rc = enqueue_image_pass(c, c.w.pose[cur], c.w.X[cur], cur, 1, opt.jacobi_scaling);

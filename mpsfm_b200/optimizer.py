@@ -86,7 +86,7 @@ class Optimizer(BaseClass):
         "min_truncation_mult": None,
         "verbose": 0,
         # --- new, engine-only knobs (nested dict: stays open under the struct freeze, existing YAMLs still load)
-        "gpu": {"device": 0, "pcg_tolerance": 1e-12, "pcg_max_iterations": 2000, "max_num_iterations": 50},
+        "gpu": {"device": 0, "pcg_tolerance": 1e-10, "pcg_max_iterations": 2000, "max_num_iterations": 50},
     }
 
     def _init(self, mpsfm_rec, correspondences=None):

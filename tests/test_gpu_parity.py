@@ -83,7 +83,7 @@ def test_reduced_camera_system_and_pcg(scene):
     prob, ba = scene
     ba.reset_state()
     radius = 1e4
-    S_blocks, rhs, y, iters = ba.reduced_system(radius)
+    S_blocks, rhs, y, iters = ba.reduced_system(radius, engine.default_options(pcg_tolerance=1e-12))
     ne, Dc2, Dp2, c_img, c_pt = _oracle_first_system(prob, radius)
     S_o, rhs_o, _ = ne.schur_system(Dc2, Dp2)
     # oracle works in Jacobi-scaled variables: S_unscaled = diag(1/c) S_scaled diag(1/c) on free coordinates
@@ -189,9 +189,9 @@ def test_cluster_and_grid_pcg_agree(shape):
     recurrence rounds differently); the two-level preconditioner (coarse.cu) needs fewer iterations."""
     prob = make_scene(*shape, seed=5)
     ba = engine.BundleAdjuster(prob, device=0)
-    S1, rhs1, y1, it1 = ba.reduced_system(1e4, engine.default_options(pcg_kernel=1))
-    S0, rhs0, y0, it0 = ba.reduced_system(1e4, engine.default_options(pcg_kernel=0, pcg_coarse=1))
-    S2, rhs2, y2, it2 = ba.reduced_system(1e4, engine.default_options())
+    S1, rhs1, y1, it1 = ba.reduced_system(1e4, engine.default_options(pcg_kernel=1, pcg_tolerance=1e-12))
+    S0, rhs0, y0, it0 = ba.reduced_system(1e4, engine.default_options(pcg_kernel=0, pcg_coarse=1, pcg_tolerance=1e-12))
+    S2, rhs2, y2, it2 = ba.reduced_system(1e4, engine.default_options(pcg_tolerance=1e-12))
     assert np.array_equal(S0, S1) and np.array_equal(rhs0, rhs1) and np.array_equal(S0, S2)
     assert abs(it0 - it1) <= 2, (it0, it1)
     assert np.max(np.abs(y0 - y1)) <= 1e-9 * np.max(np.abs(y1))
@@ -204,5 +204,5 @@ def test_cluster_and_grid_pcg_agree(shape):
     if shape[0] >= 40:
         assert it2 < 0.6 * it0, (it2, it0)
     # deterministic: bitwise identical on a second run
-    _, _, y2b, it2b = ba.reduced_system(1e4, engine.default_options())
+    _, _, y2b, it2b = ba.reduced_system(1e4, engine.default_options(pcg_tolerance=1e-12))
     assert it2b == it2 and np.array_equal(y2, y2b)
