@@ -393,29 +393,19 @@ __device__ __forceinline__ void pack_factor(const double Q[9], const double Li[6
   rec[7] = make_double2(e[2], 0.0);
 }
 
-// Track-order pass, one thread per observation (north star item 2: warp-shuffle segmented reductions keyed by
-// point).  Every observation is linearised ONCE; Hpp = sum R^T N R and gp = sum R^T h of a track are reduced over
-// its lanes with a segmented shuffle tree, the track's lane factors Hpp + D = L L^T and hands L^-1 and
-// e = L^-1 gp back to the observation lanes, which write one 128-byte Schur factor each,
-//     fac[k] = { Z = N R L^-T (9), p_rot (3), e (3), 0 },
-// from which k_schur_blocks forms  W_a Hpp^-1 W_b^T = G_a^T (Z_a Z_b^T) G_b  and  W_a Hpp^-1 gp = G_a^T Z_a e
-// without ever storing the 6x3 W blocks, and k_back_substitute the point steps.  The records of a warp go
-// through swizzled shared-memory rows so that the stores leave as whole 128-byte lines.
-__global__ void __launch_bounds__(PW_THREADS) k_points(ProblemView pv, const double* __restrict__ pose,
-                                                       const double* __restrict__ X, LmDiag lm,
-                                                       double* __restrict__ c_pt, int compute_scaling,
-                                                       int jacobi_scaling, double* __restrict__ Hpp,
-                                                       double* __restrict__ gp, double* __restrict__ Hinv,
-                                                       double* __restrict__ Linv, double* __restrict__ fac,
-                                                       double* __restrict__ pt_part, double* __restrict__ scal,
-                                                       int write_factors) {
-  __shared__ __align__(16) double2 rows_all[PW_WARPS][256];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int w = blockIdx.x * PW_WARPS + warp;
+// ---- warp path of the track-order pass: the tracks of ONE warp group (used when a CTA's groups hold a track
+// longer than 32 observations).  Sums by segmented shuffle tree (<= 32 observations) or whole-warp rounds.
+__device__ __noinline__ double points_warp_path(const ProblemView& pv, const double* __restrict__ pose,
+                                                const double* __restrict__ X, LmDiag lm, double* __restrict__ c_pt,
+                                                int compute_scaling, int jacobi_scaling, double* __restrict__ Hpp,
+                                                double* __restrict__ gp, double* __restrict__ Hinv,
+                                                double* __restrict__ Linv, double* __restrict__ fac,
+                                                double* __restrict__ scal, int write_factors, double2* rows_w, int w,
+                                                int lane) {
   double gmax = 0.0;
   if (w < pv.num_track_warps) {
     WarpTracks wt;
-    warp_tracks_setup(pv, w, lane, wt, reinterpret_cast<int*>(rows_all[warp]));
+    warp_tracks_setup(pv, w, lane, wt, reinterpret_cast<int*>(rows_w));
     double2* fac2 = reinterpret_cast<double2*>(fac);
     if (wt.n <= 32) {
       // ---- observation lanes: linearise, reduce over the track
@@ -456,7 +446,7 @@ __global__ void __launch_bounds__(PW_THREADS) k_points(ProblemView pv, const dou
         for (int j = 0; j < 6; ++j) Lo[j] = __shfl_sync(FULL, Li[j], wt.tl);
 #pragma unroll
         for (int j = 0; j < 3; ++j) eo[j] = __shfl_sync(FULL, e[j], wt.tl);
-        double2* rows = rows_all[warp];
+        double2* rows = rows_w;
         if (act) {
           double2 rec[8];
           pack_factor(Q, Lo, prot, eo, rec);
@@ -515,6 +505,119 @@ __global__ void __launch_bounds__(PW_THREADS) k_points(ProblemView pv, const dou
         }
       }
     }
+  }
+  return gmax;
+}
+
+// Track-order pass, one thread per OBSERVATION, one CTA per four consecutive warp groups of whole tracks
+// (mpba_pack_tracks: <= 128 observations, <= 128 tracks, contiguous slots).  Every observation is linearised ONCE:
+//   1. track threads publish the track of every observation slot of the CTA (shared memory),
+//   2. observation threads linearise and leave R^T N R (6) and R^T h (3) in shared memory, keeping Q = N R, p_rot,
+//   3. track threads add their observations in slot order (deterministic), damp, factor Hpp + D = L L^T, write the
+//      point's rows (c_pt, Hpp, gp, Hpp^-1, L^-1, e = L^-1 gp) and publish L^-1, e,
+//   4. observation threads write one 128-byte Schur factor each,
+//        fac[k] = { Z = N R L^-T (9), p_rot (3), e (3), 0 },
+//      from which k_schur_blocks forms  W_a Hpp^-1 W_b^T = G_a^T (Z_a Z_b^T) G_b  and  W_a Hpp^-1 gp = G_a^T Z_a e
+//      without ever storing the 6x3 W blocks, and k_back_substitute the point steps.  The records of a warp go
+//      through swizzled shared-memory rows so that the stores leave as whole 128-byte lines.
+// The reductions are keyed by point without atomics (north star item 2); the per-point algebra runs on densely
+// packed track threads instead of a few lanes of every warp.
+__global__ void __launch_bounds__(PW_THREADS) k_points(ProblemView pv, const double* __restrict__ pose,
+                                                       const double* __restrict__ X, LmDiag lm,
+                                                       double* __restrict__ c_pt, int compute_scaling,
+                                                       int jacobi_scaling, double* __restrict__ Hpp,
+                                                       double* __restrict__ gp, double* __restrict__ Hinv,
+                                                       double* __restrict__ Linv, double* __restrict__ fac,
+                                                       double* __restrict__ pt_part, double* __restrict__ scal,
+                                                       int write_factors) {
+  __shared__ __align__(16) double2 rows_all[PW_WARPS][256];
+  __shared__ double s_v[PW_THREADS][9];
+  __shared__ double s_le[PW_THREADS][9];
+  __shared__ short s_track[PW_THREADS];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g0 = blockIdx.x * PW_WARPS, g1 = min(g0 + PW_WARPS, pv.num_track_warps);
+  const int T0 = __ldg(pv.tw_first + g0), nt = __ldg(pv.tw_first + g1) - T0;
+  const int base = __ldg(pv.pt_ptr + T0), n = __ldg(pv.pt_ptr + T0 + nt) - base;
+  double gmax = 0.0;
+  if (n <= PW_THREADS) {
+    // ---- 1. who owns which slot
+    int start = 0, len = 0;
+    bool cst = true;
+    if (tid < nt) {
+      const int a = __ldg(pv.pt_ptr + T0 + tid), b = __ldg(pv.pt_ptr + T0 + tid + 1);
+      start = a - base;
+      len = b - a;
+      cst = pv.pt_const[T0 + tid] != 0;
+      for (int k = 0; k < len; ++k) s_track[start + k] = cst ? (short)-1 : (short)tid;
+    }
+    __syncthreads();
+    // ---- 2. observations
+    const int tr = tid < n ? (int)s_track[tid] : -1;
+    const bool act = tr >= 0;
+    double Q[9], prot[3] = {0.0, 0.0, 0.0};
+    if (act) {
+      double Xp[3];
+      load_point(X, T0 + tr, Xp);
+      ObsLin o;
+      ImgConst ic;
+      track_obs(pv, pose, Xp, base + tid, o, ic);
+      double v[9];
+      point_terms(o, ic.R, Q, v);
+#pragma unroll
+      for (int j = 0; j < 9; ++j) s_v[tid][j] = v[j];
+      prot[0] = o.prot[0]; prot[1] = o.prot[1]; prot[2] = o.prot[2];
+    }
+    __syncthreads();
+    // ---- 3. points
+    if (tid < nt) {
+      const bool active = !cst && len > 0;
+      double v[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+      if (active) {
+        for (int k = 0; k < len; ++k) {
+#pragma unroll
+          for (int j = 0; j < 9; ++j) v[j] += s_v[start + k][j];
+        }
+      }
+      double Li[6], e[3];
+      finalize_point(T0 + tid, active, v, v + 6, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, scal,
+                     Li, e);
+#pragma unroll
+      for (int j = 0; j < 6; ++j) s_le[tid][j] = Li[j];
+#pragma unroll
+      for (int j = 0; j < 3; ++j) s_le[tid][6 + j] = e[j];
+      gmax = fmax(fabs(v[6]), fmax(fabs(v[7]), fabs(v[8])));
+    }
+    if (write_factors) {
+      __syncthreads();
+      // ---- 4. Schur factors
+      double2* rows = rows_all[warp];
+      if (act) {
+        double Lo[6], eo[3];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) Lo[j] = s_le[tr][j];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) eo[j] = s_le[tr][6 + j];
+        double2 rec[8];
+        pack_factor(Q, Lo, prot, eo, rec);
+        const int sw = lane & 7;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) rows[lane * 8 + (c ^ sw)] = rec[c];
+      }
+      const unsigned actmask = __ballot_sync(FULL, act);  // (also orders the shared-memory writes in the warp)
+      double2* fac2 = reinterpret_cast<double2*>(fac);
+      const int g4 = lane >> 3, c = lane & 7;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int item = 4 * j + g4;
+        if ((actmask >> item) & 1u)
+          fac2[(size_t)(base + 32 * warp + item) * 8 + c] = rows[item * 8 + (c ^ (item & 7))];
+      }
+    }
+  } else {
+    const int w = g0 + warp;
+    if (w < g1)
+      gmax = points_warp_path(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, fac, scal,
+                              write_factors, rows_all[warp], w, lane);
   }
   {
     __shared__ double smx[PW_WARPS + 1];
