@@ -13,6 +13,7 @@
 // Jacobians are never stored: every pass recomputes N, h, p_rot (ba_math.cuh) from the 52-byte
 // observation record and the cache-resident pose, which is cheaper than streaming 144-byte W blocks.
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include "ba_kernels.cuh"
 
@@ -249,6 +250,9 @@ __device__ __forceinline__ void track_obs(const ProblemView& pv, const double* _
 constexpr int PT_THREADS = 128;  // k_evaluate: one thread per track
 constexpr int PW_THREADS = 128;  // track-order passes: one thread per OBSERVATION, one warp per packed group of tracks
 constexpr int PW_WARPS = PW_THREADS / 32;
+#ifndef MPBA_POINTS_MINB
+#define MPBA_POINTS_MINB 4
+#endif
 constexpr int LINV_STRIDE = 9;  // per point: L^-1 (6, lower) and e = L^-1 gp (3)
 
 // ---- one warp = a packed group of whole tracks (mpba_pack_tracks: <= 32 observations and <= 32 tracks, or one
@@ -522,14 +526,14 @@ __device__ __noinline__ double points_warp_path(const ProblemView& pv, const dou
 //      through swizzled shared-memory rows so that the stores leave as whole 128-byte lines.
 // The reductions are keyed by point without atomics (north star item 2); the per-point algebra runs on densely
 // packed track threads instead of a few lanes of every warp.
-__global__ void __launch_bounds__(PW_THREADS) k_points(ProblemView pv, const double* __restrict__ pose,
+__global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(ProblemView pv, const double* __restrict__ pose,
                                                        const double* __restrict__ X, LmDiag lm,
                                                        double* __restrict__ c_pt, int compute_scaling,
                                                        int jacobi_scaling, double* __restrict__ Hpp,
                                                        double* __restrict__ gp, double* __restrict__ Hinv,
                                                        double* __restrict__ Linv, double* __restrict__ fac,
                                                        double* __restrict__ pt_part, double* __restrict__ scal,
-                                                       int write_factors) {
+                                                       int write_factors, int force_warp_path) {
   __shared__ __align__(16) double2 rows_all[PW_WARPS][256];
   __shared__ double s_v[PW_THREADS][9];
   __shared__ double s_le[PW_THREADS][9];
@@ -539,7 +543,7 @@ __global__ void __launch_bounds__(PW_THREADS) k_points(ProblemView pv, const dou
   const int T0 = __ldg(pv.tw_first + g0), nt = __ldg(pv.tw_first + g1) - T0;
   const int base = __ldg(pv.pt_ptr + T0), n = __ldg(pv.pt_ptr + T0 + nt) - base;
   double gmax = 0.0;
-  if (n <= PW_THREADS) {
+  if (n <= PW_THREADS && !force_warp_path) {
     // ---- 1. who owns which slot
     int start = 0, len = 0;
     bool cst = true;
@@ -1456,10 +1460,11 @@ int track_warp_grid(int num_track_warps) { return (num_track_warps + PW_WARPS - 
 void launch_points(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,
                    int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* Linv,
                    double* fac, double* pt_part, double* scal, int write_factors, cudaStream_t st) {
+  static const int force_warp = getenv("MPBA_POINTS_WARP") ? atoi(getenv("MPBA_POINTS_WARP")) : 0;
   if (pv.num_track_warps > 0)
     k_points<<<track_warp_grid(pv.num_track_warps), PW_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling,
                                                                          jacobi_scaling, Hpp, gp, Hinv, Linv, fac,
-                                                                         pt_part, scal, write_factors);
+                                                                         pt_part, scal, write_factors, force_warp);
 }
 void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaStream_t st) {
   k_pt_scalars_gmax<<<1, 1024, 0, st>>>(pt_part, nblk, scal);

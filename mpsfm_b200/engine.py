@@ -26,7 +26,7 @@ import numpy as np
 
 from .problem import MAX_CAMERA_PARAMS, BundleProblem
 
-_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libmpba.so")
+_LIB_PATH = os.environ.get("MPBA_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libmpba.so")
 MPBA_CHUNK = 1024
 MPBA_NUM_KERNELS = 13
 MPBA_UNIQUE_ID_BYTES = 128
