@@ -185,3 +185,16 @@ def test_emulated_lm_step_matches_oracle(hostcheck):
     assert np.allclose(-yc, step_c_o, rtol=1e-7, atol=1e-12)
     assert np.allclose(-yp, step_p_o, rtol=1e-7, atol=1e-12)
     assert abs(mcc - mcc_o) <= 1e-9 * abs(mcc_o)
+
+    # ---- what k_points / k_back_substitute / k_cam_update do since the Schur factors are stored:
+    #   Hpp + D = L L^T,  Z_a = N_a R_a L^-T,  e = L^-1 gp,  y_p = L^-T (e - sum_a Z_a^T G_a y_c),
+    #   model cost change = (g'y + y'Dy) / 2  (the normal equations the step solves)
+    Linv = np.zeros_like(Hd)
+    Linv[act] = np.linalg.inv(np.linalg.cholesky(Hd[act]))
+    Z = np.einsum("nij,nkj->nik", Q, Linv[op])  # Q L^-T
+    e = np.einsum("pij,pj->pi", Linv, gp)
+    ztg = lm.segment_sum(op, np.einsum("nki,nk->ni", Z, ga) * act[op][:, None], P)
+    yp_f = np.einsum("pji,pj->pi", Linv, e - ztg)
+    assert np.allclose(yp_f, yp, rtol=1e-9, atol=1e-13)
+    mcc_f = 0.5 * (np.sum(gp * yp_f) + np.sum(lam_p * yp_f**2) + np.sum(gc * yc) + np.sum(lam_c * freec * yc**2))
+    assert abs(mcc_f - mcc_o) <= 1e-9 * abs(mcc_o)
