@@ -109,11 +109,13 @@ def algorithmic_bytes(lay, spec=None):
         # 4 (point idx) + 16 (xy) + 24 (d,w,a) per observation, every point read at least once (32 B), chunk partials
         "img_chunks": 44 * n_img + 32 * p_touch + 256 * lay.num_chunks + 64 * C,
         # 4 (image idx) + 16 + 24 in and one 128 B Schur factor out per observation; per point: xyz, pt_ptr, c_pt in,
-        # Hpp / gp / Hinv out
-        "points": (44 + 128) * n_trk + (32 + 4 + 24 + 48 + 24 + 48) * p_own + 64 * C,
+        # Hpp / gp / Hinv / (L^-1, e) out
+        "points": (44 + 128) * n_trk + (32 + 4 + 24 + 48 + 24 + 48 + 72) * p_own + 64 * C,
         # every factor read at least once, 8 B per item, every block of S written once
         "schur_blocks": 128 * n_trk + 8 * n_items + 288 * B + (168 + 48 + 48) * C,
-        "back_substitute": 44 * n_trk + (32 + 4 + 48 + 24 + 48 + 32) * p_own + 48 * C,
+        # Z and p_rot of the factor (96 B) + image index per observation; per point: xyz, pt_ptr, (L^-1, e), diag Hpp,
+        # gp, c_pt in, candidate out; y of every image
+        "back_substitute": (96 + 4) * n_trk + (32 + 4 + 72 + 24 + 24 + 24 + 32) * p_own + 48 * C,
     }
 
 
@@ -298,8 +300,14 @@ def run_gpu(args):
     if top:
         ms, n = ktimes[top]
         achieved = ab[top] / (ms / n * 1e-3) / 1e9
+        traffic = None  # DRAM bytes per launch of that kernel from the committed ncu --set full capture (1 GPU only)
+        try:
+            if world == 1:
+                traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json"))).get(args.workload, {}).get(top)
+        except Exception:
+            traffic = None
         roof = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": ab[top],
+                "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": ab[top],
                 "avg_launch_ms": ms / n, "frac_of_nominal_8TBps": achieved / 8000.0}
 
     cpu = cpu_baseline_sample(args.workload) if (world == 1 and not args.no_cpu_baseline) else None
