@@ -357,11 +357,11 @@ __device__ __forceinline__ void finalize_point(int p, bool active, const double 
   }
   if (active) {
     double Hd[6] = {Hp[0], Hp[1], Hp[2], Hp[3], Hp[4], Hp[5]};
-    Hd[0] += lm_damping(Hp[0], c[0], lm.radius, lm.lo, lm.hi);
-    Hd[3] += lm_damping(Hp[3], c[1], lm.radius, lm.lo, lm.hi);
-    Hd[5] += lm_damping(Hp[5], c[2], lm.radius, lm.lo, lm.hi);
+    Hd[0] += lm_damping_fast(Hp[0], c[0], lm.radius, lm.inv_radius, lm.lo, lm.hi);
+    Hd[3] += lm_damping_fast(Hp[3], c[1], lm.radius, lm.inv_radius, lm.lo, lm.hi);
+    Hd[5] += lm_damping_fast(Hp[5], c[2], lm.radius, lm.inv_radius, lm.lo, lm.hi);
     if (sym3_chol_inverse(Hd, Li)) {
-      sym3_from_chol_inverse(Li, Hi);
+      if (Hinv) sym3_from_chol_inverse(Li, Hi);
     } else {
 #pragma unroll
       for (int j = 0; j < 6; ++j) Li[j] = 0.0;
@@ -371,7 +371,7 @@ __device__ __forceinline__ void finalize_point(int p, bool active, const double 
 #pragma unroll
   for (int j = 0; j < 6; ++j) {
     Hpp[(size_t)p * 6 + j] = Hp[j];
-    Hinv[(size_t)p * 6 + j] = Hi[j];
+    if (Hinv) Hinv[(size_t)p * 6 + j] = Hi[j];  // only the covariance / linearize entry points ask for it
     Linv[(size_t)p * LINV_STRIDE + j] = Li[j];
   }
 #pragma unroll
@@ -537,14 +537,13 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
   __shared__ __align__(16) double2 rows_all[PW_WARPS][256];
   __shared__ double s_v[PW_THREADS][9];
   __shared__ double s_le[PW_THREADS][9];
-  __shared__ short s_track[PW_THREADS];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g0 = blockIdx.x * PW_WARPS, g1 = min(g0 + PW_WARPS, pv.num_track_warps);
-  const int T0 = __ldg(pv.tw_first + g0), nt = __ldg(pv.tw_first + g1) - T0;
-  const int base = __ldg(pv.pt_ptr + T0), n = __ldg(pv.pt_ptr + T0 + nt) - base;
+  const int4 desc = __ldg(pv.cta_desc + blockIdx.x);  // one load instead of the tw_first -> pt_ptr chain
+  const int T0 = desc.x, nt = desc.y, base = desc.z, n = desc.w;
   double gmax = 0.0;
   if (n <= PW_THREADS && !force_warp_path) {
-    // ---- 1. who owns which slot
+    // track threads: their slot range and constant flag (independent loads, needed after the first barrier)
     int start = 0, len = 0;
     bool cst = true;
     if (tid < nt) {
@@ -552,27 +551,30 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
       start = a - base;
       len = b - a;
       cst = pv.pt_const[T0 + tid] != 0;
-      for (int k = 0; k < len; ++k) s_track[start + k] = cst ? (short)-1 : (short)tid;
     }
-    __syncthreads();
-    // ---- 2. observations
-    const int tr = tid < n ? (int)s_track[tid] : -1;
-    const bool act = tr >= 0;
+    // ---- 1. observations: point of the slot (pm_pt), gather, linearise, leave R^T N R / R^T h in shared memory
+    int tr = -1;
     double Q[9], prot[3] = {0.0, 0.0, 0.0};
-    if (act) {
-      double Xp[3];
-      load_point(X, T0 + tr, Xp);
-      ObsLin o;
-      ImgConst ic;
-      track_obs(pv, pose, Xp, base + tid, o, ic);
-      double v[9];
-      point_terms(o, ic.R, Q, v);
+    if (tid < n) {
+      const int pt = __ldg(pv.pm_pt + base + tid);
+      const double2* xp = reinterpret_cast<const double2*>(X + 4 * (size_t)pt);
+      const double2 xa = __ldg(xp), xb = __ldg(xp + 1);
+      if (xb.y == 0.0) {  // slot 3: constant flag
+        tr = pt - T0;
+        const double Xp[3] = {xa.x, xa.y, xb.x};
+        ObsLin o;
+        ImgConst ic;
+        track_obs(pv, pose, Xp, base + tid, o, ic);
+        double v[9];
+        point_terms(o, ic.R, Q, v);
 #pragma unroll
-      for (int j = 0; j < 9; ++j) s_v[tid][j] = v[j];
-      prot[0] = o.prot[0]; prot[1] = o.prot[1]; prot[2] = o.prot[2];
+        for (int j = 0; j < 9; ++j) s_v[tid][j] = v[j];
+        prot[0] = o.prot[0]; prot[1] = o.prot[1]; prot[2] = o.prot[2];
+      }
     }
+    const bool act = tr >= 0;
     __syncthreads();
-    // ---- 3. points
+    // ---- 2. points
     if (tid < nt) {
       const bool active = !cst && len > 0;
       double v[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
@@ -593,7 +595,7 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
     }
     if (write_factors) {
       __syncthreads();
-      // ---- 4. Schur factors
+      // ---- 3. Schur factors
       double2* rows = rows_all[warp];
       if (act) {
         double Lo[6], eo[3];
@@ -1248,12 +1250,10 @@ __global__ void __launch_bounds__(256) k_cam_update(ProblemView pv, const double
 //     g'y - y'Hy/2 = (g'y + y'Dy) / 2
 // (exact up to the PCG residual, 1e-12 relative by default); the point part is summed here, the image part in
 // k_cam_update.
-__device__ __forceinline__ void point_step(int p, bool active, const double* __restrict__ X, const double zg[3],
+__device__ __forceinline__ void point_step(int p, bool active, double2 xa, double2 xb, const double zg[3],
                                            const double* __restrict__ Linv, const double* __restrict__ Hpp,
                                            const double* __restrict__ gp, const double* __restrict__ c_pt, LmDiag lm,
                                            double* __restrict__ X_cand, double& mcc, double& step2, double& xn2) {
-  const double2* xp = reinterpret_cast<const double2*>(X + 4 * (size_t)p);
-  const double2 xa = __ldg(xp), xb = __ldg(xp + 1);
   const double Xp[3] = {xa.x, xa.y, xb.x};
   double yp[3] = {0.0, 0.0, 0.0};
   if (active) {
@@ -1267,9 +1267,9 @@ __device__ __forceinline__ void point_step(int p, bool active, const double* __r
     yp[1] = Li[2] * u[1] + Li[4] * u[2];
     yp[2] = Li[5] * u[2];
     const double h0 = Hpp[(size_t)p * 6], h3 = Hpp[(size_t)p * 6 + 3], h5 = Hpp[(size_t)p * 6 + 5];
-    const double d0 = lm_damping(h0, c_pt[(size_t)p * 3], lm.radius, lm.lo, lm.hi),
-                 d1 = lm_damping(h3, c_pt[(size_t)p * 3 + 1], lm.radius, lm.lo, lm.hi),
-                 d2 = lm_damping(h5, c_pt[(size_t)p * 3 + 2], lm.radius, lm.lo, lm.hi);
+    const double d0 = lm_damping_fast(h0, c_pt[(size_t)p * 3], lm.radius, lm.inv_radius, lm.lo, lm.hi),
+                 d1 = lm_damping_fast(h3, c_pt[(size_t)p * 3 + 1], lm.radius, lm.inv_radius, lm.lo, lm.hi),
+                 d2 = lm_damping_fast(h5, c_pt[(size_t)p * 3 + 2], lm.radius, lm.inv_radius, lm.lo, lm.hi);
     mcc = 0.5 * (gp[(size_t)p * 3] * yp[0] + gp[(size_t)p * 3 + 1] * yp[1] + gp[(size_t)p * 3 + 2] * yp[2] +
                  d0 * yp[0] * yp[0] + d1 * yp[1] * yp[1] + d2 * yp[2] * yp[2]);
     step2 = yp[0] * yp[0] + yp[1] * yp[1] + yp[2] * yp[2];
@@ -1307,15 +1307,34 @@ __global__ void __launch_bounds__(PW_THREADS) k_back_substitute(ProblemView pv, 
   const int w = blockIdx.x * PW_WARPS + warp;
   double mcc = 0.0, step2 = 0.0, xn2 = 0.0;
   if (w < pv.num_track_warps) {
-    WarpTracks wt;
-    warp_tracks_setup(pv, w, lane, wt, reinterpret_cast<int*>(rows_all[warp]));
+    const int4 desc = __ldg(pv.warp_desc + w);  // {first track, tracks, first slot, observations}
     const double2* fac2 = reinterpret_cast<const double2*>(fac);
-    if (wt.n <= 32) {
-      const bool act = wt.has && !wt.tcst && use_factors;  // no factors: all poses constant, y_c = 0
+    if (desc.w <= 32) {
+      // Lane = observation slot.  Tracks are runs of equal point index: heads by comparing with the left lane;
+      // the head lane of a track also does the track's point step.  (Points without observations are never
+      // touched: both point buffers hold their coordinates from the start of the solve.)
+      const int base = desc.z, n = desc.w;
+      const bool has = lane < n;
+      const int pt = has ? __ldg(pv.pm_pt + base + lane) : -1;
+      const int img = has ? __ldg(pv.pm_img + base + lane) : 0;
+      const int left = __shfl_up_sync(FULL, pt, 1);
+      const bool head = has && (lane == 0 || pt != left);
+      const unsigned heads = __ballot_sync(FULL, head);
+      double2 xa = make_double2(0.0, 0.0), xb = make_double2(0.0, 1.0);
+      if (head) {
+        const double2* xp = reinterpret_cast<const double2*>(X + 4 * (size_t)pt);
+        xa = __ldg(xp);
+        xb = __ldg(xp + 1);
+      }
+      const unsigned le = heads & (0xffffffffu >> (31 - lane));
+      const int seg_start = le ? 31 - __clz(le) : 0;
+      const unsigned above = (lane == 31) ? 0u : (heads & (0xffffffffu << (lane + 1)));
+      const int seg_end = above ? (__ffs(above) - 1) : n;
+      const bool free_pt = __shfl_sync(FULL, xb.y == 0.0 ? 1 : 0, seg_start) != 0;  // slot 3: constant flag
+      const bool act = has && free_pt && use_factors;  // no factors: all poses constant, y_c = 0
       double2* rows = rows_all[warp];
-      warp_gather_records(fac2, act ? wt.base + lane : -1, 6, rows, lane);
+      warp_gather_records(fac2, act ? base + lane : -1, 6, rows, lane);
       cp_async_commit();
-      const int img = act ? __ldg(pv.pm_img + wt.base + lane) : 0;
       cp_async_wait<0>();
       __syncwarp();
       double v[3] = {0.0, 0.0, 0.0};  // Z^T g of this observation
@@ -1328,15 +1347,11 @@ __global__ void __launch_bounds__(PW_THREADS) k_back_substitute(ProblemView pv, 
         const double prot[3] = {c4.y, c5.x, c5.y};
         obs_zt_g(Z, prot, y, img, v);
       }
-      segmented_reduce<3>(v, lane, wt.seg_end);
-      double u[3];
-#pragma unroll
-      for (int j = 0; j < 3; ++j) u[j] = __shfl_sync(FULL, v[j], wt.start);
-      if (lane < wt.nt) {
-        const bool active = !wt.cst && wt.len > 0;
-        point_step(wt.t0 + lane, active, X, u, Linv, Hpp, gp, c_pt, lm, X_cand, mcc, step2, xn2);
-      }
+      segmented_reduce<3>(v, lane, seg_end);
+      if (head) point_step(pt, free_pt, xa, xb, v, Linv, Hpp, gp, c_pt, lm, X_cand, mcc, step2, xn2);
     } else {
+      WarpTracks wt;
+      warp_tracks_setup(pv, w, lane, wt, reinterpret_cast<int*>(rows_all[warp]));
       const int p = wt.t0;
       const bool active = pv.pt_const[p] == 0;
       double s3[3] = {0.0, 0.0, 0.0};
@@ -1353,7 +1368,8 @@ __global__ void __launch_bounds__(PW_THREADS) k_back_substitute(ProblemView pv, 
       }
       warp_allreduce<3>(s3);
       if (lane == 0) {
-        point_step(p, active, X, s3, Linv, Hpp, gp, c_pt, lm, X_cand, mcc, step2, xn2);
+        const double2* xp = reinterpret_cast<const double2*>(X + 4 * (size_t)p);
+        point_step(p, active, __ldg(xp), __ldg(xp + 1), s3, Linv, Hpp, gp, c_pt, lm, X_cand, mcc, step2, xn2);
       }
     }
   }
@@ -1424,6 +1440,27 @@ __global__ void k_normalize_poses(int C, const double* __restrict__ in, const do
   o[7] = exp(shift_scale[2 * (size_t)i + 1]);  // exp(log-scale) of the depth prior: constant block, one exp per image
 }
 
+// Once per call: the point of every (owned) track-order slot and the CTA descriptors of the track-order passes.
+__global__ void k_track_setup(ProblemView pv, int32_t* __restrict__ pm_pt, int4* __restrict__ cta_desc,
+                              int4* __restrict__ warp_desc) {
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int p = pv.p0 + gid;
+  if (p < pv.p1)
+    for (int k = pv.pt_ptr[p]; k < pv.pt_ptr[p + 1]; ++k) pm_pt[k] = p;
+  const int nb = (pv.num_track_warps + PW_WARPS - 1) / PW_WARPS;
+  if (gid < nb) {
+    const int g0 = gid * PW_WARPS, g1 = min(g0 + PW_WARPS, pv.num_track_warps);
+    const int T0 = pv.tw_first[g0], T1 = pv.tw_first[g1];
+    const int base = pv.pt_ptr[T0];
+    cta_desc[gid] = make_int4(T0, T1 - T0, base, pv.pt_ptr[T1] - base);
+  }
+  if (gid < pv.num_track_warps) {
+    const int T0 = pv.tw_first[gid], T1 = pv.tw_first[gid + 1];
+    const int base = pv.pt_ptr[T0];
+    warp_desc[gid] = make_int4(T0, T1 - T0, base, pv.pt_ptr[T1] - base);
+  }
+}
+
 // slot 3 of every point record <- 1.0 for a constant point, 0.0 otherwise (read by k_img_chunks with the gather)
 __global__ void k_flag_points(int P, const uint8_t* __restrict__ pt_const, double* __restrict__ X) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1457,6 +1494,10 @@ void launch_img_scalars(const ProblemView& pv, const double* img_part, const dou
 }
 int points_grid(int P) { return (P + PT_THREADS - 1) / PT_THREADS; }
 int track_warp_grid(int num_track_warps) { return (num_track_warps + PW_WARPS - 1) / PW_WARPS; }
+void launch_track_setup(const ProblemView& pv, int32_t* pm_pt, int4* cta_desc, int4* warp_desc, cudaStream_t st) {
+  const int n = max(pv.p1 - pv.p0, pv.num_track_warps);
+  if (n > 0) k_track_setup<<<(n + 255) / 256, 256, 0, st>>>(pv, pm_pt, cta_desc, warp_desc);
+}
 void launch_points(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,
                    int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* Linv,
                    double* fac, double* pt_part, double* scal, int write_factors, cudaStream_t st) {

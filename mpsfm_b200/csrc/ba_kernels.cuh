@@ -42,6 +42,11 @@ struct ProblemView {
   // track-order warp packing (mpba_pack_tracks): warp w owns the whole tracks tw_first[w] .. tw_first[w+1]
   int num_track_warps;
   const int32_t* tw_first;
+  // built on the device once per call (launch_track_setup, workspace): point of every track-order slot, and per
+  // CTA of the track-order passes {first track, tracks, first slot, observations}
+  const int32_t* pm_pt;
+  const int4* cta_desc;
+  const int4* warp_desc;  // the same per warp group
   const int32_t* img_camera;
   const uint8_t* img_free_mask;
   const double* img_shift_scale;
@@ -73,8 +78,9 @@ struct ProblemView {
 };
 
 struct LmDiag {
-  double radius, lo, hi;
+  double radius, lo, hi, inv_radius;
 };
+inline LmDiag make_lm(double radius, double lo, double hi) { return LmDiag{radius, lo, hi, 1.0 / radius}; }
 
 // ---- image order: Hcc, gc, cost ------------------------------------------------------------
 void launch_img_chunks(const ProblemView& pv, const double* pose, const double* X, double* chunk_part,
@@ -91,7 +97,8 @@ void launch_points(const ProblemView& pv, const double* pose, const double* X, L
                    int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* Linv,
                    double* fac, double* pt_part, double* scal, int write_factors, cudaStream_t st);
 int points_grid(int num_owned_points);  // k_evaluate: one thread per track
-int track_warp_grid(int num_track_warps);  // k_points / k_back_substitute: CTAs (= rows of pt_part)
+int track_warp_grid(int num_track_warps);
+void launch_track_setup(const ProblemView& pv, int32_t* pm_pt, int4* cta_desc, int4* warp_desc, cudaStream_t st);  // k_points / k_back_substitute: CTAs (= rows of pt_part)
 void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaStream_t st);
 
 // ---- reduced camera system ----------------------------------------------------------------------

@@ -327,17 +327,25 @@ MPBA_HD void sym3_mul_mat(const double N[6], const double R[9], double Q[9]) {
 // Cholesky of a symmetric positive definite 3x3 (what Ceres' Schur eliminator does with Eigen's LLT
 // on the e-block): returns Li = L^-1 (lower: i00, i10, i11, i20, i21, i22) so that H^-1 = Li^T Li;
 // false if H is not positive definite.
+// The factor is formed through reciprocal square roots (three rsqrt instead of three sqrt + six divisions: the
+// per-point algebra sits on the critical path of k_points).
+MPBA_HD double mpba_rsqrt(double x) {
+#ifdef __CUDA_ARCH__
+  return rsqrt(x);
+#else
+  return 1.0 / sqrt(x);
+#endif
+}
 MPBA_HD bool sym3_chol_inverse(const double H[6], double Li[6]) {
   const double a = H[0], b = H[1], c = H[2], d = H[3], e = H[4], f = H[5];
   if (!(a > 0.0)) return false;
-  const double l00 = sqrt(a), l10 = b / l00, l20 = c / l00;
+  const double i00 = mpba_rsqrt(a), l10 = b * i00, l20 = c * i00;
   const double t11 = d - l10 * l10;
   if (!(t11 > 0.0)) return false;
-  const double l11 = sqrt(t11), l21 = (e - l20 * l10) / l11;
+  const double i11 = mpba_rsqrt(t11), l21 = (e - l20 * l10) * i11;
   const double t22 = f - l20 * l20 - l21 * l21;
   if (!(t22 > 0.0)) return false;
-  const double l22 = sqrt(t22);
-  const double i00 = 1.0 / l00, i11 = 1.0 / l11, i22 = 1.0 / l22;
+  const double i22 = mpba_rsqrt(t22);
   const double i10 = -l10 * i00 * i11;
   const double i21 = -l21 * i11 * i22;
   const double i20 = -(l20 * i00 + l21 * i10) * i22;
@@ -506,6 +514,14 @@ MPBA_HD void gt_k_g(const double pa[3], const double K[9], const double pb[3], d
 // Ceres LM damping of one tangent coordinate in unscaled variables:
 //   scaled system adds clamp(c^2 H_jj, lo, hi) / radius to the diagonal of diag(c) H diag(c),
 //   i.e. the unscaled one adds clamp(c^2 H_jj) / (radius c^2).
+// same value up to rounding without a division in the common (unclamped) case: clamp(c^2 h) / (radius c^2) = h / radius
+MPBA_HD double lm_damping_fast(double hjj, double c, double radius, double inv_radius, double lo, double hi) {
+  const double cc = c * c, t = cc * hjj;
+  if (t < lo) return lo / (radius * cc);
+  if (t > hi) return hi / (radius * cc);
+  return hjj * inv_radius;
+}
+
 MPBA_HD double lm_damping(double hjj, double c, double radius, double lo, double hi) {
   const double cc = c * c;
   double dj = cc * hjj;

@@ -116,6 +116,9 @@ struct Workspace {
   double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *img_part, *c_img, *c_pt, *Hpp, *gp, *Hinv, *fac, *S,
       *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal, *scal_all, *Linv;
   double *Zc = nullptr, *Ac = nullptr, *Ainv = nullptr;  // coarse space (coarse.cu)
+  int32_t* pm_pt = nullptr;   // point of every track-order slot (launch_track_setup)
+  int4* cta_desc = nullptr;   // per CTA of the track-order passes
+  int4* warp_desc = nullptr;  // per warp group
   int32_t* plan = nullptr;  // PCG cluster plan (pcg_cluster.cu)
   size_t plan_ints = 0;
   size_t bytes = 0;
@@ -172,6 +175,9 @@ void carve(const mpba_problem* p, const mpba_shard* sh, char* base, Workspace& w
     w.Ac = take(so ? 0 : (size_t)COARSE_SPLIT * COARSE_MAX_DIM * COARSE_MAX_DIM);
     w.Ainv = take(so ? 0 : (size_t)COARSE_MAX_DIM * COARSE_MAX_DIM);
   }
+  w.pm_pt = reinterpret_cast<int32_t*>(take(((size_t)p->num_obs + 1) / 2 + 1));
+  w.cta_desc = reinterpret_cast<int4*>(take(2 * nblk + 2));
+  w.warp_desc = reinterpret_cast<int4*>(take(2 * (size_t)p->num_track_warps + 2));
   w.plan_ints = plan_capacity_ints(p);
   w.plan = reinterpret_cast<int32_t*>(take((w.plan_ints + 1) / 2));
   w.bytes = off;
@@ -232,6 +238,7 @@ struct Ctx {
   PcgClusterArgs cla;
   CoarsePlan coarse;  // coarse.G == 0: block-Jacobi only
   const mpba_shard* sh = nullptr;  // sharded solve
+  bool want_hinv = false;          // Hpp^-1 rows requested (mpba_point_covariances)
 };
 
 int check_shard(mpba_handle* h, const mpba_problem* p, const mpba_shard* sh) {
@@ -269,6 +276,10 @@ int begin(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t work
     c.pv.p0 = sh->pt_begin; c.pv.p1 = sh->pt_end; c.pv.i0 = sh->img_begin; c.pv.i1 = sh->img_end;
   }
   c.nblk = track_warp_grid(c.pv.num_track_warps);
+  c.pv.pm_pt = c.w.pm_pt;
+  c.pv.cta_desc = c.w.cta_desc;
+  c.pv.warp_desc = c.w.warp_desc;
+  if (c.pv.num_track_warps > 0) launch_track_setup(c.pv, c.w.pm_pt, c.w.cta_desc, c.w.warp_desc, h->stream);
   c.structure_only = prob->flags & MPBA_FLAG_STRUCTURE_ONLY;
   c.max_row_blocks = prob->s_max_row_blocks;
   h->launch_count = 0;
@@ -531,7 +542,8 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
   CU(cudaMemsetAsync(c.w.scal + S_BAD_POINTS, 0, sizeof(double), h->stream));
   {
     Timer t(h, KS_POINTS_SCHUR);
-    launch_points(c.pv, pose, X, lm, c.w.c_pt, compute_scaling, opt->jacobi_scaling, c.w.Hpp, c.w.gp, c.w.Hinv, c.w.Linv, c.w.fac,
+    launch_points(c.pv, pose, X, lm, c.w.c_pt, compute_scaling, opt->jacobi_scaling, c.w.Hpp, c.w.gp,
+                  c.want_hinv ? c.w.Hinv : nullptr, c.w.Linv, c.w.fac,
                   c.w.pt_part, c.w.scal, schur ? 1 : 0, h->stream);
   }
   {
@@ -779,7 +791,7 @@ int mpba_linearize(mpba_handle* h, const mpba_problem* prob, void* workspace, si
   if (rc) return rc;
   rc = enqueue_image_pass(c, c.w.pose[0], c.w.X[0], 0, 1, 1);
   if (rc) return rc;
-  LmDiag lm{opt.initial_trust_region_radius, opt.min_lm_diagonal, opt.max_lm_diagonal};
+  const LmDiag lm = make_lm(opt.initial_trust_region_radius, opt.min_lm_diagonal, opt.max_lm_diagonal);
   rc = enqueue_points_and_system(c, c.w.pose[0], c.w.X[0], 0, lm, 1, &opt, false);
   if (rc) return rc;
   if (Hcc) launch_expand_hcc(c.pv.C, c.w.Hc[0], Hcc, h->stream);
@@ -801,6 +813,7 @@ int mpba_point_covariances(mpba_handle* h, const mpba_problem* prob, void* works
   int rc = begin(h, prob, workspace, workspace_bytes, c);
   if (rc) return rc;
   if (!cov) return fail(h, MPBA_E_INVALID, "cov is NULL");
+  c.want_hinv = true;
   reset_profile(h, 0);
   mpba_options opt;
   mpba_default_options(&opt);
@@ -809,7 +822,7 @@ int mpba_point_covariances(mpba_handle* h, const mpba_problem* prob, void* works
   rc = stage_points(c, prob, c.w.X[0]);
   if (rc) return rc;
   // undamped: an infinite trust-region radius makes the LM diagonal vanish
-  LmDiag lm{INFINITY, opt.min_lm_diagonal, opt.max_lm_diagonal};
+  const LmDiag lm = make_lm(INFINITY, opt.min_lm_diagonal, opt.max_lm_diagonal);
   rc = enqueue_points_and_system(c, c.w.pose[0], c.w.X[0], 0, lm, 1, &opt, false);
   if (rc) return rc;
   CU(cudaMemcpyAsync(cov, c.w.Hinv, (size_t)c.pv.P * 6 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
@@ -834,7 +847,7 @@ int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspac
   if (rc) return rc;
   rc = enqueue_image_pass(c, c.w.pose[0], c.w.X[0], 0, 1, opt.jacobi_scaling);
   if (rc) return rc;
-  LmDiag lm{radius, opt.min_lm_diagonal, opt.max_lm_diagonal};
+  const LmDiag lm = make_lm(radius, opt.min_lm_diagonal, opt.max_lm_diagonal);
   rc = enqueue_points_and_system(c, c.w.pose[0], c.w.X[0], 0, lm, 1, &opt, true);
   if (rc) return rc;
   if (c.structure_only) return fail(h, MPBA_E_INVALID, "no reduced camera system: all poses are constant");
@@ -879,6 +892,9 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
   h->launch_count += 1;
   rc = stage_points(c, prob, c.w.X[cur]);
   if (rc) return rc;
+  // points without observations are never written by the back-substitution: both buffers carry them
+  if (c.pv.P > 0)
+    CU(cudaMemcpyAsync(c.w.X[cur ^ 1], c.w.X[cur], (size_t)c.pv.P * 4 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
 
   // ---- iteration zero
   rc = enqueue_image_pass(c, c.w.pose[cur], c.w.X[cur], cur, 1, opt.jacobi_scaling);
@@ -919,7 +935,7 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
 
   while (termination < 0) {
     const int cand = cur ^ 1;
-    LmDiag lm{radius, opt.min_lm_diagonal, opt.max_lm_diagonal};
+    const LmDiag lm = make_lm(radius, opt.min_lm_diagonal, opt.max_lm_diagonal);
     rc = enqueue_points_and_system(c, c.w.pose[cur], c.w.X[cur], cur, lm, first ? 1 : 0, &opt, true);
     if (rc) return rc;
     first = false;
