@@ -280,6 +280,17 @@ int mpba_workspace_bytes_sharded(const mpba_problem* prob, const mpba_shard* sha
 int mpba_solve_sharded(mpba_handle* h, const mpba_problem* prob, const mpba_shard* shard, void* workspace,
                        size_t workspace_bytes, const mpba_options* opt, mpba_summary* summary);
 
+/* ---- problem assembly on the device (the step before the solve in the reference) --------------------------------
+ * Batched PriorUtils._data_at_kps (mpsfm/sfm/scene/image/mixins/priorutils.py:49-62; called for depth, variance
+ * and validity maps at bundle_adjustment.py:132-135, 215): out[k] = bilinear sample (fp64, align_corners = True,
+ * zero padding) of map map_of[k] at kps[k] * (sx, sy) of that map; valid_at_kps is `out == 1` on a 0/1 map.
+ * Same operation order as torch.nn.functional.grid_sample, no fused multiply-adds.  maps: the H x W row-major
+ * maps back to back; map_offset[m] in doubles; map_hw[m] = {H, W}; map_scale[m] = {sx, sy}.  DEVICE pointers;
+ * runs on cuda_stream (NULL: default stream) and returns after it completed. */
+int mpba_sample_maps(mpba_handle* h, int32_t n, const double* kps, const int32_t* map_of, int32_t num_maps,
+                     const int64_t* map_offset, const int32_t* map_hw, const double* map_scale, const double* maps,
+                     double* out, void* cuda_stream);
+
 /* After a call with opt->profile: per-kernel summed device ms and launch counts (HOST arrays of
  * MPBA_NUM_KERNELS); names from mpba_kernel_name(slot). */
 int mpba_kernel_times(const mpba_handle* h, double* ms, int64_t* launches);

@@ -399,7 +399,7 @@ __device__ __forceinline__ void pack_factor(const double Q[9], const double Li[6
 
 // ---- warp path of the track-order pass: the tracks of ONE warp group (used when a CTA's groups hold a track
 // longer than 32 observations).  Sums by segmented shuffle tree (<= 32 observations) or whole-warp rounds.
-__device__ __noinline__ double points_warp_path(const ProblemView& pv, const double* __restrict__ pose,
+__device__ __noinline__ double points_warp_path(const ProblemView pv, const double* __restrict__ pose,
                                                 const double* __restrict__ X, LmDiag lm, double* __restrict__ c_pt,
                                                 int compute_scaling, int jacobi_scaling, double* __restrict__ Hpp,
                                                 double* __restrict__ gp, double* __restrict__ Hinv,

@@ -117,7 +117,7 @@ EXPORTS = (
     "mpba_version", "mpba_create", "mpba_destroy", "mpba_last_error", "mpba_default_options",
     "mpba_workspace_bytes", "mpba_evaluate", "mpba_linearize", "mpba_reduced_system", "mpba_solve",
     "mpba_kernel_times", "mpba_kernel_name", "mpba_point_covariances",
-    "mpba_pack_tracks", "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
+    "mpba_pack_tracks", "mpba_sample_maps", "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
 )
 
 _lib = None
@@ -149,6 +149,8 @@ def load_library(path: Optional[str] = None):
     lib.mpba_point_covariances.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t, C.c_void_p]
     lib.mpba_solve.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t,
                                C.POINTER(MpbaOptions), C.POINTER(MpbaSummary)]
+    lib.mpba_sample_maps.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.mpba_pack_tracks.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_int32)]
     lib.mpba_comm_unique_id.argtypes = [C.c_void_p, C.c_char_p]
     lib.mpba_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_char_p]
@@ -728,6 +730,44 @@ class BundleAdjuster:
         n = (C.c_int64 * MPBA_NUM_KERNELS)()
         self._check(self.lib.mpba_kernel_times(self.handle, ms, n))
         return {self.lib.mpba_kernel_name(i).decode(): (ms[i], int(n[i])) for i in range(MPBA_NUM_KERNELS) if n[i]}
+
+
+def sample_maps(kps_per_map, maps, scales, device: int = 0):
+    """GPU ``PriorUtils._data_at_kps`` for a whole bundle in one launch (mpba_sample_maps).
+
+    kps_per_map: list of [n_m, 2] keypoints (original pixel scale), maps: list of [H_m, W_m] arrays (depth, variance
+    or 0/1 validity), scales: list of (sx, sy).  Returns the list of [n_m] sampled values (float64)."""
+    import torch
+
+    lib = load_library()
+    if not torch.cuda.is_available():
+        raise EngineUnavailable("no CUDA device: mpsfm_b200 has no CPU fallback")
+    if not (len(kps_per_map) == len(maps) == len(scales)):
+        raise ValueError("kps_per_map, maps and scales must have one entry per map")
+    M = len(maps)
+    counts = [int(np.asarray(k).reshape(-1, 2).shape[0]) for k in kps_per_map]
+    n = int(sum(counts))
+    if n == 0:
+        return [np.zeros(0) for _ in range(M)]
+    kps = np.ascontiguousarray(np.concatenate([np.asarray(k, dtype=np.float64).reshape(-1, 2) for k in kps_per_map]))
+    map_of = np.repeat(np.arange(M, dtype=np.int32), counts)
+    flat = [np.ascontiguousarray(np.asarray(m, dtype=np.float64)) for m in maps]
+    hw = np.array([m.shape[:2] for m in flat], dtype=np.int32)
+    offset = np.zeros(M, dtype=np.int64)
+    offset[1:] = np.cumsum([m.size for m in flat])[:-1]
+    dev = torch.device("cuda", device)
+    with torch.cuda.device(dev):
+        t = {k: torch.from_numpy(v).to(dev) for k, v in dict(
+            kps=kps, map_of=map_of, offset=offset, hw=hw, scale=np.asarray(scales, dtype=np.float64).reshape(M, 2),
+            maps=np.concatenate([m.reshape(-1) for m in flat])).items()}
+        out = torch.empty(n, dtype=torch.float64, device=dev)
+        rc = lib.mpba_sample_maps(None, n, t["kps"].data_ptr(), t["map_of"].data_ptr(), M, t["offset"].data_ptr(),
+                                  t["hw"].data_ptr(), t["scale"].data_ptr(), t["maps"].data_ptr(), out.data_ptr(),
+                                  C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        if rc != 0:
+            raise EngineError(f"mpba_sample_maps failed with code {rc}")
+        res = out.cpu().numpy()
+    return np.split(res, np.cumsum(counts)[:-1])
 
 
 def dense_reduced_system(layout: HostLayout, S_blocks: np.ndarray) -> np.ndarray:

@@ -86,8 +86,38 @@ class Optimizer(BaseClass):
         "min_truncation_mult": None,
         "verbose": 0,
         # --- new, engine-only knobs (nested dict: stays open under the struct freeze, existing YAMLs still load)
-        "gpu": {"device": 0, "pcg_tolerance": 1e-10, "pcg_max_iterations": 2000, "max_num_iterations": 50},
+        "gpu": {"device": 0, "pcg_tolerance": 1e-10, "pcg_max_iterations": 2000, "max_num_iterations": 50,
+                # sample the depth / validity maps of the whole bundle in ONE kernel launch (mpba_sample_maps) instead
+                # of the reference's three torch.grid_sample calls per image (priorutils.py:49-62)
+                "sample_on_device": False},
     }
+
+    def _sample_bundle_on_device(self, optim_ids, img_p2ds, depth_type):
+        """{imid: (valid [n] bool, depth [n])} for every activated image of the bundle from one mpba_sample_maps
+        launch, or None when the option is off.  Same values as image.depth.valid_at_kps / data_at_kps /
+        data_prior_at_kps (bundle_adjustment.py:130-135): the kernel keeps torch.grid_sample's operation order."""
+        g = self.conf["gpu"] if "gpu" in self.conf else {}
+        if not bool(g.get("sample_on_device", False)):
+            return None
+        rec = self.mpsfm_rec
+        ids, kps, vmaps, dmaps, scales = [], [], [], [], []
+        for imid in optim_ids:
+            image = rec.images[imid]
+            if image.depth is None or not image.depth.activated or img_p2ds[imid].size == 0:
+                continue
+            ids.append(imid)
+            kps.append(np.asarray(image.keypoint_coordinates(img_p2ds[imid]), dtype=np.float64).reshape(-1, 2))
+            vmaps.append(np.asarray(image.depth.valid, dtype=np.float64))
+            dmaps.append(np.asarray(image.depth.data if depth_type == "update" else image.depth.data_prior, dtype=np.float64))
+            cam = image.depth.camera
+            scales.append((float(cam.sx), float(cam.sy)))
+        if not ids:
+            return {}
+        from . import engine
+
+        out = engine.sample_maps(kps + kps, vmaps + dmaps, scales + scales, device=int(g.get("device", 0)))
+        n = len(ids)
+        return {imid: (out[i] == 1, out[n + i]) for i, imid in enumerate(ids)}
 
     def _init(self, mpsfm_rec, correspondences=None):
         self.mpsfm_rec = mpsfm_rec
@@ -203,6 +233,7 @@ class Optimizer(BaseClass):
         depth_rows = {}
         d_obs, d_d, d_w, d_a = [], [], [], []
         pm = param_multiplier * self.truncation_multiplier  # :109
+        sampled = self._sample_bundle_on_device(optim_ids, img_p2ds, depth_type) if with_depth else None
         if with_depth:
             for imid in optim_ids:
                 image = rec.images[imid]
@@ -211,11 +242,15 @@ class Optimizer(BaseClass):
                 p2Ds = img_p2ds[imid]
                 if p2Ds.size == 0:
                     continue
-                kps = np.asarray(image.keypoint_coordinates(p2Ds), dtype=np.float64).reshape(-1, 2)
-                valid = np.asarray(image.depth.valid_at_kps(kps), dtype=bool)
-                kps = kps[valid]
-                depths = np.asarray(image.depth.data_at_kps(kps) if depth_type == "update"
-                                    else image.depth.data_prior_at_kps(kps), dtype=np.float64)
+                if sampled is not None:
+                    valid, depths = sampled[imid]
+                    depths = depths[valid]
+                else:
+                    kps = np.asarray(image.keypoint_coordinates(p2Ds), dtype=np.float64).reshape(-1, 2)
+                    valid = np.asarray(image.depth.valid_at_kps(kps), dtype=bool)
+                    kps = kps[valid]
+                    depths = np.asarray(image.depth.data_at_kps(kps) if depth_type == "update"
+                                        else image.depth.data_prior_at_kps(kps), dtype=np.float64)
                 p2Ds = p2Ds[valid]
                 p3Ds = np.asarray(image.point3D_ids(p2Ds), dtype=np.uint64).astype(np.int64)
                 depth3d = np.asarray(rec.project_image_3d_points(imid, p3Ds)[3], dtype=np.float64) if p2Ds.size else np.zeros(0)

@@ -13,5 +13,6 @@ ap.add_argument("--workload", default="cfg3")
 ap.add_argument("--iters", type=int, default=2)
 a = ap.parse_args()
 ba = engine.BundleAdjuster(make_config(a.workload, seed=0), device=0)
-s = ba.solve(engine.default_options(max_num_iterations=a.iters))
+s = ba.solve(engine.default_options(max_num_iterations=a.iters, profile=1))
 print(s.brief_report(), "launches", s.kernel_launches)
+print({k: round(1e3 * ms / n, 1) for k, (ms, n) in ba.kernel_times().items()})
