@@ -1001,9 +1001,16 @@ struct PcgArgs {
   double* scal;
   double tol;
   int max_iter;
+  // two-level preconditioner (coarse.cu): G groups of consecutive CTAs' rows, nc = 7 G gauge modes; G == 0: off
+  int G, nc;
+  const int32_t* grp_row_ptr;  // [G+1] first row of every group (CTA boundaries)
+  const double* Zc;            // [C][6][7]
+  const double* Ainv;          // [nc][nc] (Z^T S Z)^-1, symmetric
+  double* tpart;               // [gridDim.x][8] per-CTA Z^T r of its rows (one group per CTA)
 };
 
 constexpr int PCG_THREADS = 256;
+constexpr int PCG_MAX_NC = COARSE_MAX_DIM;
 
 __device__ __forceinline__ double grid_reduce(double part, double* slots, unsigned* bar, unsigned& gen, double* sm) {
   const double b = block_sum<PCG_THREADS / 32>(part, sm);
@@ -1064,8 +1071,68 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
   unsigned gen = 0;
   long long t_spmv = 0, t_red = 0, t_upd = 0;
 
+  // ---- two-level preconditioner  z = M^-1 r + Z (Z^T S Z)^-1 Z^T r  (coarse.cu).  Every CTA's rows lie in ONE
+  // group, so its Z^T r is 7 numbers; they travel with the r'M^-1 r partial through the same grid barrier, then
+  // every CTA forms t = Z^T r (all groups, fixed order), e = A^-1 t (redundantly: nc^2 multiply-adds), and
+  //     r'z = r'M^-1 r + t'e,        z_i = (M^-1 r)_i + Z_i e_g      for its own rows,
+  // publishes z and meets the others at one more barrier before the next product.
+  __shared__ double s_t[PCG_MAX_NC], s_e[PCG_MAX_NC], s_tw[PCG_THREADS / 32][8], s_te[PCG_THREADS / 32 + 1];
+  const bool coarse = A.G > 0;
+  int my_group = 0;
+  if (coarse)
+    for (int g = 0; g < A.G; ++g)
+      if (row0 >= A.grp_row_ptr[g]) my_group = g;
+  double* s_zj = s_q;  // M^-1 r of the own rows lives in the q rows between the update and the coarse step
+  // per-CTA Z^T r: lanes 0..6 of every warp accumulate over the warp's rows, warps folded in order
+  auto coarse_publish_t = [&](const double (&tacc)[1]) {
+    if (lane < 7) s_tw[warp][lane] = tacc[0];
+    __syncthreads();
+    if (threadIdx.x < 7) {
+      double t = 0.0;
+#pragma unroll
+      for (int w = 0; w < PCG_THREADS / 32; ++w) t += s_tw[w][threadIdx.x];
+      __stcg(A.tpart + (size_t)blockIdx.x * 8 + threadIdx.x, t);
+    }
+  };
+  // after the barrier: t, e, t'e; returns t'e (same value in every thread of every CTA)
+  auto coarse_solve = [&]() -> double {
+    const int nc = A.nc;
+    for (int k = threadIdx.x; k < nc; k += PCG_THREADS) {
+      const int g = k / 7, m = k % 7;
+      // CTAs of group g: those whose first row lies in [grp_row_ptr[g], grp_row_ptr[g+1])
+      const int c0 = (A.grp_row_ptr[g] + A.rows_per_cta - 1) / A.rows_per_cta;
+      const int c1 = min((int)gridDim.x, (A.grp_row_ptr[g + 1] + A.rows_per_cta - 1) / A.rows_per_cta);
+      double t = 0.0;
+      for (int cta = c0; cta < c1; ++cta) t += __ldcg(A.tpart + (size_t)cta * 8 + m);
+      s_t[k] = t;
+    }
+    __syncthreads();
+    double te = 0.0;
+    for (int j = threadIdx.x; j < nc; j += PCG_THREADS) {
+      double e = 0.0;
+      for (int k = 0; k < nc; ++k) e += __ldg(A.Ainv + (size_t)k * nc + j) * s_t[k];  // symmetric: column j = row j
+      s_e[j] = e;
+      te += s_t[j] * e;
+    }
+    te = block_sum<PCG_THREADS / 32>(te, s_te);
+    return te;
+  };
+  // z_i = zj_i + Z_i e_g for the own rows, published for the other CTAs' products
+  auto coarse_apply_z = [&]() {
+    for (int lr = warp; lr < nrows; lr += WPB) {
+      const int row = row0 + lr;
+      if (lane < 6) {
+        const double* Zi = A.Zc + (size_t)row * 42 + lane * 7;
+        double zz = s_zj[lr * 6 + lane];
+#pragma unroll
+        for (int m = 0; m < 7; ++m) zz += __ldg(Zi + m) * s_e[my_group * 7 + m];
+        __stcg(A.z + (size_t)row * 6 + lane, zz);
+      }
+    }
+  };
+
   // x = 0, r = b, z = M^-1 r, p_old = 0
-  double part = 0.0;
+  double part = 0.0, tacc0 = 0.0;
   for (int lr = warp; lr < nrows; lr += WPB) {
     const int row = row0 + lr;
     const double rr = lane < 6 ? A.rhs[(size_t)row * 6 + lane] : 0.0;
@@ -1078,12 +1145,30 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
     if (lane < 6) {
       s_x[lr * 6 + lane] = 0.0;
       s_r[lr * 6 + lane] = rr;
-      __stcg(A.z + (size_t)row * 6 + lane, zz);
+      if (coarse) s_zj[lr * 6 + lane] = zz; else __stcg(A.z + (size_t)row * 6 + lane, zz);
       __stcg(A.p0 + (size_t)row * 6 + lane, 0.0);
       part += rr * zz;
     }
+    if (coarse) {
+      double a = 0.0;
+#pragma unroll
+      for (int r = 0; r < 6; ++r) {
+        const double rc = __shfl_sync(FULL, rr, r);
+        if (lane < 7) a += __ldg(A.Zc + (size_t)row * 42 + r * 7 + lane) * rc;
+      }
+      tacc0 += a;
+    }
   }
-  const double rz0 = grid_reduce(part, part1, A.bar, gen, sm);
+  if (coarse) {
+    const double tt[1] = {tacc0};
+    coarse_publish_t(tt);
+  }
+  double rz0 = grid_reduce(part, part1, A.bar, gen, sm);
+  if (coarse) {
+    rz0 += coarse_solve();
+    coarse_apply_z();
+    (void)grid_reduce(0.0, part0, A.bar, gen, sm);  // z of every CTA is visible
+  }
   double rz = rz0, beta = 0.0;
   int iters = 0, flag = 1;
   double res = 1.0;
@@ -1134,6 +1219,7 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
       const double alpha = rz / pq;
       // x += alpha p, r -= alpha q, z = M^-1 r
       part = 0.0;
+      double tacc = 0.0;
       for (int lr = warp; lr < nrows; lr += WPB) {
         const int row = row0 + lr;
         double rr = 0.0;
@@ -1150,12 +1236,26 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
           if (lane < 6) zz += s_minv[lr * 36 + lane * 6 + c] * rc;
         }
         if (lane < 6) {
-          __stcg(A.z + (size_t)row * 6 + lane, zz);
+          if (coarse) s_zj[lr * 6 + lane] = zz; else __stcg(A.z + (size_t)row * 6 + lane, zz);
           part += rr * zz;
         }
+        if (coarse) {
+          double a = 0.0;
+#pragma unroll
+          for (int r = 0; r < 6; ++r) {
+            const double rc = __shfl_sync(FULL, rr, r);
+            if (lane < 7) a += __ldg(A.Zc + (size_t)row * 42 + r * 7 + lane) * rc;
+          }
+          tacc += a;
+        }
+      }
+      if (coarse) {
+        const double tt[1] = {tacc};
+        coarse_publish_t(tt);
       }
       const long long c3 = clock64();
-      const double rz_new = grid_reduce(part, part1, A.bar, gen, sm);
+      double rz_new = grid_reduce(part, part1, A.bar, gen, sm);
+      if (coarse) rz_new += coarse_solve();
       const long long c4 = clock64();
       t_spmv += c1 - c0;
       t_upd += c3 - c2;
@@ -1169,6 +1269,10 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
       if (res <= A.tol) {
         flag = 0;
         break;
+      }
+      if (coarse) {
+        coarse_apply_z();
+        (void)grid_reduce(0.0, part0, A.bar, gen, sm);  // z of every CTA is visible
       }
       beta = rz_new / rz;
       rz = rz_new;
@@ -1534,8 +1638,8 @@ PcgPlan pcg_plan(int device, int C, int max_row_blocks) {
   if (!sms) {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
-    cudaFuncSetAttribute(k_pcg<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 1024);
-    cudaFuncSetAttribute(k_pcg<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 1024);
+    cudaFuncSetAttribute(k_pcg<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 4096);
+    cudaFuncSetAttribute(k_pcg<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 4096);
   }
   PcgPlan pl;
   const int wpb = PCG_THREADS / 32;
@@ -1548,14 +1652,15 @@ PcgPlan pcg_plan(int device, int C, int max_row_blocks) {
   const size_t base = rows * (36 + 18) * sizeof(double) + ((rows + 2) & ~(size_t)1) * sizeof(int);
   pl.max_local_blocks = (int)(rows * (size_t)(max_row_blocks > 0 ? max_row_blocks : 1 << 16));
   const size_t with_s = base + (size_t)pl.max_local_blocks * (36 * sizeof(double) + sizeof(int)) + 16;
-  pl.use_smem = (max_row_blocks > 0 && with_s <= (size_t)(smem_optin - 1024)) ? 1 : 0;
+  pl.use_smem = (max_row_blocks > 0 && with_s <= (size_t)(smem_optin - 4096)) ? 1 : 0;
   pl.smem_bytes = pl.use_smem ? with_s : base + 16;
   return pl;
 }
 cudaError_t launch_pcg(const ProblemView& pv, const PcgPlan& pl, const double* S, const double* Minv, const double* rhs,
                        double* y, double* vec_z, double* vec_p0, double* vec_p1, double* partial, unsigned* bar,
-                       double* scal, double tol, int max_iter, cudaStream_t st) {
+                       double* scal, double tol, int max_iter, const PcgGridCoarse& co, cudaStream_t st) {
   PcgArgs a;
+  a.G = co.G; a.nc = 7 * co.G; a.grp_row_ptr = co.grp_row_ptr; a.Zc = co.Zc; a.Ainv = co.Ainv; a.tpart = co.tpart;
   a.C = pv.C; a.rows_per_cta = pl.rows_per_cta; a.max_local_blocks = pl.max_local_blocks;
   a.row_ptr = pv.s_row_ptr; a.col = pv.s_col; a.S = S; a.Minv = Minv; a.rhs = rhs; a.x = y;
   a.z = vec_z; a.p0 = vec_p0; a.p1 = vec_p1; a.partial = partial; a.bar = bar; a.scal = scal;

@@ -116,10 +116,18 @@ struct PcgPlan {
   size_t smem_bytes;
 };
 PcgPlan pcg_plan(int device, int C, int max_row_blocks);
+// two-level preconditioner of the grid kernel: G groups of consecutive CTAs (G == 0: block-Jacobi only)
+struct PcgGridCoarse {
+  int G = 0;
+  const int32_t* grp_row_ptr = nullptr;  // [G+1], device
+  const double* Zc = nullptr;
+  const double* Ainv = nullptr;
+  double* tpart = nullptr;  // [grid][8]
+};
 // returns cudaError from the cooperative launch
 cudaError_t launch_pcg(const ProblemView& pv, const PcgPlan& pl, const double* S, const double* Minv, const double* rhs,
                        double* y, double* vec_z, double* vec_p0, double* vec_p1, double* partial, unsigned* bar,
-                       double* scal, double tol, int max_iter, cudaStream_t st);
+                       double* scal, double tol, int max_iter, const PcgGridCoarse& co, cudaStream_t st);
 
 // cluster-resident PCG (pcg_cluster.cu): one thread-block cluster of `cl` CTAs, upper blocks of S in
 // registers, exchanges through distributed shared memory.  The plan arrays are built on the host from

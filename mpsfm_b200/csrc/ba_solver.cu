@@ -115,7 +115,7 @@ size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Workspace {
   double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *img_part, *c_img, *c_pt, *Hpp, *gp, *Hinv, *fac, *S,
-      *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal, *scal_all, *Linv;
+      *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal, *scal_all, *Linv, *tpart;
   double *Zc = nullptr, *Ac = nullptr, *Ainv = nullptr;  // coarse space (coarse.cu)
   int32_t* pm_pt = nullptr;   // point of every track-order slot (launch_track_setup)
   int4* cta_desc = nullptr;   // per CTA of the track-order passes
@@ -167,6 +167,7 @@ void carve(const mpba_problem* p, const mpba_shard* sh, char* base, Workspace& w
   w.vp1 = take(C * 6);
   w.vq = take(C * 6);
   w.partial = take(2 * 2048 + 32);
+  w.tpart = take(8 * 1024);
   w.pt_part = take(nblk * PT_PART + 8);
   w.scal = take(S_COUNT);
   w.scal_all = take(sh ? (size_t)sh->world * S_COUNT : 0);
@@ -238,6 +239,7 @@ struct Ctx {
   size_t cl_smem = 0;
   PcgClusterArgs cla;
   CoarsePlan coarse;  // coarse.G == 0: block-Jacobi only
+  PcgGridCoarse gridco;  // grid kernel: groups of CTAs (build_grid_coarse_plan)
   const mpba_shard* sh = nullptr;  // sharded solve
   bool want_hinv = false;          // Hpp^-1 rows requested (mpba_point_covariances)
 };
@@ -536,6 +538,61 @@ int build_pcg_cluster_plan(Ctx& c, const mpba_problem* prob, int pcg_kernel, int
   return MPBA_OK;
 }
 
+// Coarse space for the grid-wide PCG (systems beyond one cluster): G groups of consecutive CTAs' rows, so that every
+// CTA contributes to exactly one group.  Same coarse kernels (coarse.cu) as the cluster path.
+int build_grid_coarse_plan(Ctx& c, const mpba_problem* prob, int pcg_coarse) {
+  mpba_handle* h = c.h;
+  c.gridco = PcgGridCoarse();
+  if (c.structure_only || c.cl > 0 || pcg_coarse == 1) return MPBA_OK;
+  const int C = prob->num_images, B = prob->num_blocks;
+  const PcgPlan pl = pcg_plan(h->device, C, c.max_row_blocks);
+  const int G = std::min(COARSE_MAX_GROUPS, pl.grid);
+  if (G < 2 || pl.grid > 1024) return MPBA_OK;
+  std::vector<int32_t> rp(C + 1), col(B);
+  CU(cudaMemcpyAsync(rp.data(), prob->s_row_ptr, (C + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaMemcpyAsync(col.data(), prob->s_col, (size_t)B * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  std::vector<int32_t> grp_row(G + 1), grp_of(C);
+  for (int g = 0; g <= G; ++g) grp_row[g] = std::min(C, (int)((long long)pl.grid * g / G) * pl.rows_per_cta);
+  grp_row[G] = C;
+  for (int g = 0; g < G; ++g)
+    for (int i = grp_row[g]; i < grp_row[g + 1]; ++i) grp_of[i] = g;
+  std::vector<int32_t> cb_ptr((size_t)G * G + 1, 0), cb_fine(B);
+  for (int i = 0; i < C; ++i)
+    for (int b = rp[i]; b < rp[i + 1]; ++b) ++cb_ptr[(size_t)grp_of[i] * G + grp_of[col[b]] + 1];
+  for (size_t k = 0; k < (size_t)G * G; ++k) cb_ptr[k + 1] += cb_ptr[k];
+  std::vector<int32_t> fill(cb_ptr.begin(), cb_ptr.end() - 1);
+  for (int i = 0; i < C; ++i)
+    for (int b = rp[i]; b < rp[i + 1]; ++b) cb_fine[fill[(size_t)grp_of[i] * G + grp_of[col[b]]]++] = b;
+  const size_t total = grp_row.size() + cb_ptr.size() + cb_fine.size();
+  if (total > c.w.plan_ints) return MPBA_OK;
+  if (h->h_stage_ints < total) {
+    if (h->h_stage) cudaFreeHost(h->h_stage);
+    h->h_stage = nullptr;
+    h->h_stage_ints = 0;
+    CU(cudaMallocHost(&h->h_stage, total * sizeof(int32_t)));
+    h->h_stage_ints = total;
+  }
+  int32_t* st = h->h_stage;
+  size_t off = 0;
+  auto put = [&](const std::vector<int32_t>& v) -> const int32_t* {
+    memcpy(st + off, v.data(), v.size() * sizeof(int32_t));
+    const int32_t* d = c.w.plan + off;
+    off += v.size();
+    return d;
+  };
+  c.gridco.grp_row_ptr = put(grp_row);
+  c.coarse.cb_ptr = put(cb_ptr);
+  c.coarse.cb_fine = put(cb_fine);
+  CU(cudaMemcpyAsync(c.w.plan, st, off * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+  c.coarse.G = G;
+  c.gridco.G = G;
+  c.gridco.Zc = c.w.Zc;
+  c.gridco.Ainv = c.w.Ainv;
+  c.gridco.tpart = c.w.tpart;
+  return MPBA_OK;
+}
+
 int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int kset, LmDiag lm, int compute_scaling,
                               const mpba_options* opt, bool want_system) {
   mpba_handle* h = c.h;
@@ -575,7 +632,7 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
     }
     // (rebuilding the coarse space only every k-th LM iteration was measured at cfg3: k = 2 gains nothing, k = 4
     // costs 30 % more PCG iterations)
-    if (c.cl > 0 && c.coarse.G > 0) {
+    if (c.coarse.G > 0) {
       Timer t(h, KS_COARSE, 3);
       cudaError_t e = launch_coarse_setup(c.coarse, c.pv.C, pose, c.pv.img_free_mask, c.pv.s_row, c.pv.s_col, c.w.S,
                                           c.w.Zc, c.w.Ac, c.w.Ainv, h->stream);
@@ -593,7 +650,7 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
         const PcgPlan pl = pcg_plan(h->device, c.pv.C, c.max_row_blocks);
         e = launch_pcg(c.pv, pl, c.w.S, c.w.Minv, c.w.rhs, c.w.y, c.w.vz, c.w.vp0, c.w.vp1, c.w.partial,
                        reinterpret_cast<unsigned*>(c.w.partial + 2 * 2048), c.w.scal, opt->pcg_tolerance,
-                       opt->pcg_max_iterations, h->stream);
+                       opt->pcg_max_iterations, c.gridco, h->stream);
       }
       if (e != cudaSuccess) return fail(h, MPBA_E_CUDA, std::string("PCG launch: ") + cudaGetErrorString(e));
     }
@@ -845,6 +902,8 @@ int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspac
   if (opt_in) opt = *opt_in; else mpba_default_options(&opt);
   rc = build_pcg_cluster_plan(c, prob, opt.pcg_kernel, opt.pcg_coarse);
   if (rc) return rc;
+  rc = build_grid_coarse_plan(c, prob, opt.pcg_coarse);
+  if (rc) return rc;
   launch_normalize_poses(c.pv.C, prob->img_pose, prob->img_shift_scale, c.w.pose[0], h->stream);
   rc = stage_points(c, prob, c.w.X[0]);
   if (rc) return rc;
@@ -873,6 +932,8 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
   if (opt_in) opt = *opt_in; else mpba_default_options(&opt);
   reset_profile(h, opt.profile);
   rc = build_pcg_cluster_plan(c, prob, opt.pcg_kernel, opt.pcg_coarse);
+  if (rc) return rc;
+  rc = build_grid_coarse_plan(c, prob, opt.pcg_coarse);
   if (rc) return rc;
   mpba_iteration* its = sum->iterations;
   const int cap = its ? sum->capacity : 0;

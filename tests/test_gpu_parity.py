@@ -189,7 +189,8 @@ def test_cluster_and_grid_pcg_agree(shape):
     recurrence rounds differently); the two-level preconditioner (coarse.cu) needs fewer iterations."""
     prob = make_scene(*shape, seed=5)
     ba = engine.BundleAdjuster(prob, device=0)
-    S1, rhs1, y1, it1 = ba.reduced_system(1e4, engine.default_options(pcg_kernel=1, pcg_tolerance=1e-12))
+    S1, rhs1, y1, it1 = ba.reduced_system(1e4, engine.default_options(pcg_kernel=1, pcg_coarse=1, pcg_tolerance=1e-12))
+    S3, rhs3, y3, it3 = ba.reduced_system(1e4, engine.default_options(pcg_kernel=1, pcg_tolerance=1e-12))  # grid, two-level
     S0, rhs0, y0, it0 = ba.reduced_system(1e4, engine.default_options(pcg_kernel=0, pcg_coarse=1, pcg_tolerance=1e-12))
     S2, rhs2, y2, it2 = ba.reduced_system(1e4, engine.default_options(pcg_tolerance=1e-12))
     assert np.array_equal(S0, S1) and np.array_equal(rhs0, rhs1) and np.array_equal(S0, S2)
@@ -201,8 +202,11 @@ def test_cluster_and_grid_pcg_agree(shape):
     assert np.max(np.abs(y0.reshape(-1) - y_ref)) <= 1e-8 * np.max(np.abs(y_ref))
     assert np.max(np.abs(y2.reshape(-1) - y_ref)) <= 1e-8 * np.max(np.abs(y_ref))
     assert it2 <= it0
+    assert np.max(np.abs(y3.reshape(-1) - y_ref)) <= 1e-8 * np.max(np.abs(y_ref))
+    assert it3 <= it1
     if shape[0] >= 40:
         assert it2 < 0.6 * it0, (it2, it0)
+        assert it3 < 0.7 * it1, (it3, it1)
     # deterministic: bitwise identical on a second run
     _, _, y2b, it2b = ba.reduced_system(1e4, engine.default_options(pcg_tolerance=1e-12))
     assert it2b == it2 and np.array_equal(y2, y2b)
