@@ -89,7 +89,10 @@ __device__ __forceinline__ double block_max(double v, double* sm) {
 // ================================================================================================
 // image order
 // ================================================================================================
-__global__ void __launch_bounds__(256) k_img_chunks(ProblemView pv, const double* __restrict__ pose,
+#ifndef MPBA_IMG_MINB
+#define MPBA_IMG_MINB 1
+#endif
+__global__ void __launch_bounds__(256, MPBA_IMG_MINB) k_img_chunks(ProblemView pv, const double* __restrict__ pose,
                                                     const double* __restrict__ X, double* __restrict__ chunk_part) {
   const int c = blockIdx.x;
   const int img = pv.chunk_img[c];
@@ -636,7 +639,14 @@ __global__ void __launch_bounds__(1024) k_pt_scalars_gmax(const double* __restri
                                                           double* __restrict__ scal) {
   __shared__ double sm[33];
   double gm = 0.0;
-  for (int i = threadIdx.x; i < nblk; i += 1024) gm = fmax(gm, pt_part[(size_t)i * PT_PART]);
+  // four independent loads in flight per thread: the kernel is one CTA and nothing but load latency
+  int i = threadIdx.x;
+  for (; i + 3 * 1024 < nblk; i += 4 * 1024) {
+    const double a = pt_part[(size_t)i * PT_PART], b = pt_part[(size_t)(i + 1024) * PT_PART],
+                 c = pt_part[(size_t)(i + 2048) * PT_PART], d = pt_part[(size_t)(i + 3072) * PT_PART];
+    gm = fmax(fmax(gm, a), fmax(b, fmax(c, d)));
+  }
+  for (; i < nblk; i += 1024) gm = fmax(gm, pt_part[(size_t)i * PT_PART]);
   gm = block_max<32>(gm, sm);
   if (threadIdx.x == 0) scal[S_GMAX_P] = gm;
 }
@@ -1296,14 +1306,14 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
 // ================================================================================================
 // step
 // ================================================================================================
-__global__ void __launch_bounds__(256) k_cam_update(ProblemView pv, const double* __restrict__ pose,
+__global__ void __launch_bounds__(1024) k_cam_update(ProblemView pv, const double* __restrict__ pose,
                                                     const double* __restrict__ y, const double* __restrict__ Hc,
                                                     const double* __restrict__ gc, const double* __restrict__ c_img,
                                                     LmDiag lm, double* __restrict__ pose_cand,
                                                     double* __restrict__ scal) {
-  __shared__ double sm[9];
+  __shared__ double sm[33];
   double step2 = 0.0, xn2 = 0.0, mcc = 0.0;
-  for (int i = threadIdx.x; i < pv.C; i += 256) {
+  for (int i = threadIdx.x; i < pv.C; i += 1024) {
     const double* ps = pose + (size_t)i * 8;
     const double* yi = y + (size_t)i * 6;
     const unsigned mask = pv.img_free_mask[i];
@@ -1336,9 +1346,9 @@ __global__ void __launch_bounds__(256) k_cam_update(ProblemView pv, const double
       }
     }
   }
-  step2 = block_sum<8>(step2, sm);
-  xn2 = block_sum<8>(xn2, sm);
-  mcc = block_sum<8>(mcc, sm);
+  step2 = block_sum<32>(step2, sm);
+  xn2 = block_sum<32>(xn2, sm);
+  mcc = block_sum<32>(mcc, sm);
   if (threadIdx.x == 0) {
     scal[S_STEP2_C] = step2;
     scal[S_XNORM2_C] = xn2;
@@ -1492,7 +1502,16 @@ __global__ void __launch_bounds__(1024) k_pt_scalars_step(const double* __restri
                                                           double* __restrict__ scal) {
   __shared__ double sm[33];
   double a = 0.0, b = 0.0, c = 0.0;
-  for (int i = threadIdx.x; i < nblk; i += 1024) {
+  // two rows in flight per thread (same per-thread summation order as a plain loop: row i, then row i + 1024)
+  int i = threadIdx.x;
+  for (; i + 1024 < nblk; i += 2 * 1024) {
+    const double* p0 = pt_part + (size_t)i * PT_PART;
+    const double* p1 = pt_part + (size_t)(i + 1024) * PT_PART;
+    const double a0 = p0[1], b0 = p0[2], c0 = p0[3], a1 = p1[1], b1 = p1[2], c1 = p1[3];
+    a += a0; b += b0; c += c0;
+    a += a1; b += b1; c += c1;
+  }
+  for (; i < nblk; i += 1024) {
     a += pt_part[(size_t)i * PT_PART + 1];
     b += pt_part[(size_t)i * PT_PART + 2];
     c += pt_part[(size_t)i * PT_PART + 3];
@@ -1674,7 +1693,7 @@ cudaError_t launch_pcg(const ProblemView& pv, const PcgPlan& pl, const double* S
 }
 void launch_cam_update(const ProblemView& pv, const double* pose, const double* y, const double* Hc, const double* gc,
                        const double* c_img, LmDiag lm, double* pose_cand, double* scal, cudaStream_t st) {
-  k_cam_update<<<1, 256, 0, st>>>(pv, pose, y, Hc, gc, c_img, lm, pose_cand, scal);
+  k_cam_update<<<1, 1024, 0, st>>>(pv, pose, y, Hc, gc, c_img, lm, pose_cand, scal);
 }
 void launch_back_substitute(const ProblemView& pv, const double* X, const double* y, const double* Hpp,
                             const double* gp, const double* Linv, const double* c_pt, const double* fac,
