@@ -119,39 +119,45 @@ def algorithmic_bytes(lay, spec=None):
     }
 
 
-def cpu_baseline_sample(workload: str, max_iters: int = 2, obs_target: int = 60_000):
-    """Oracle (numpy port of the reference's Ceres path) on a bounded sample of the workload's shape."""
+def cpu_baseline_sample(workload: str, max_iters: int = 3, obs_cap: int = 6_000_000, layout=None):
+    """The CPU port of the path (oracle/cpu_port: C++17 + OpenMP, all host threads) on a bounded sample: the first
+    `max_iters` LM iterations of the workload's own scene when it has at most `obs_cap` observations, else of a scene
+    of the same generator scaled down to that size (it/s then scaled by the observation ratio)."""
+    from mpsfm_b200 import engine, synthetic
     from mpsfm_b200.problem import CameraModel, LossType
     from mpsfm_b200.synthetic import CONFIGS
-    from oracle import lm
-
-    from mpsfm_b200 import synthetic
+    from oracle import cpu_port
 
     C, P, L = CONFIGS[workload]
-    scale = max(1.0, (P * L) / obs_target)
-    Cs, Ps = max(12, int(round(C / scale))), max(100, int(round(P / scale)))
-    kw = {}
-    if workload in ("cfg3", "cfg4", "cfg5", "target10m"):
-        kw["model"] = CameraModel.SIMPLE_RADIAL
-    if workload == "cfg3":
-        kw["reproj_loss"] = LossType.CAUCHY
-    prob = synthetic.make_scene(Cs, Ps, L, seed=0, **kw)
-    t0 = time.perf_counter()
-    summ = lm.solve(prob, lm.Options(max_num_iterations=max_iters))
-    dt = time.perf_counter() - t0
-    its = len(summ.iterations) - 1
     n_full = P * L
-    it_s_sample = its / dt
+    scale = max(1.0, n_full / obs_cap)
+    if layout is None or scale > 1.0:
+        kw = {}
+        if workload in ("cfg3", "cfg4", "cfg5", "target10m"):
+            kw["model"] = CameraModel.SIMPLE_RADIAL
+        if workload == "cfg3":
+            kw["reproj_loss"] = LossType.CAUCHY
+        Cs, Ps = max(12, int(round(C / scale))), max(100, int(round(P / scale)))
+        layout = engine.build_layout(synthetic.make_scene(Cs, Ps, L, seed=0, **kw))
+    threads = cpu_port.max_threads()
+    cpu_port.solve(layout, max_num_iterations=1)  # warm-up: page in, spin up the thread pool
+    t0 = time.perf_counter()
+    summ, _, _, _ = cpu_port.solve(layout, max_num_iterations=max_iters)
+    dt = time.perf_counter() - t0
+    its = summ["num_iterations"]
+    it_s = its / dt
     return {
-        "value": it_s_sample * prob.num_obs / n_full,
+        "value": it_s * layout.N / n_full,
         "unit": UNIT,
-        "cores": int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1)),
+        "cores": threads,
         "kind": "port",
-        "sample": (f"numpy oracle (oracle/lm.py, exact Schur + Cholesky), {its} LM iterations on a {Cs} img / {Ps} pt / "
-                   f"{prob.num_obs} obs scene of the same generator ({dt:.1f} s); it/s scaled by obs ratio "
-                   f"{prob.num_obs}/{n_full} (cost per LM iteration is linear in observations at fixed track length)"),
-        "sample_it_per_s": it_s_sample,
-        "sample_obs": int(prob.num_obs),
+        "sample": (f"oracle/cpu_port (C++17/OpenMP port of the Ceres path, Schur complement + block-Jacobi PCG to 1e-10; "
+                   f"pycolmap / pyceres / Ceres are not installable here), {threads} threads, first {its} LM iterations of a "
+                   f"{layout.C} img / {layout.P} pt / {layout.N} obs scene of the workload's generator in {dt:.1f} s"
+                   + ("" if layout.N == n_full else f"; it/s scaled by the observation ratio {layout.N}/{n_full}")),
+        "sample_it_per_s": it_s,
+        "sample_obs": int(layout.N),
+        "sample_pcg_iterations": summ["total_pcg_iterations"],
     }
 
 
@@ -159,19 +165,16 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    times, iters, info = [], 0, None
-    for k in range(args.warmup + args.steps):
-        t0 = time.perf_counter()
-        info = cpu_baseline_sample(args.workload, max_iters=1, obs_target=args.ref_obs)
-        dt = time.perf_counter() - t0
-        if k >= args.warmup:
-            times.append(dt)
-    val = float(np.mean([info["value"]])) if info else 0.0
-    # value from the mean step time of the timed steps (one LM iteration per step on the sample)
-    mean_dt = float(np.mean(times)) if times else float("nan")
     from mpsfm_b200.synthetic import CONFIGS
 
     C, P, L = CONFIGS[args.workload]
+    times, info = [], None
+    for k in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        info = cpu_baseline_sample(args.workload, max_iters=2, obs_cap=args.ref_obs)
+        if k >= args.warmup:
+            times.append(1.0 / info["sample_it_per_s"])  # seconds per LM iteration on the sample
+    mean_dt = float(np.mean(times)) if times else float("nan")
     val = (1.0 / mean_dt) * info["sample_obs"] / (P * L)
     info["value"] = val
     line = {
@@ -179,8 +182,9 @@ def run_reference(args):
         "warmup": args.warmup, "ms_per_step": mean_dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": args.workload, "images": C, "points": P, "observations": P * L,
-                   "note": "pycolmap/pyceres/Ceres are not installable here; the reference arm is the numpy oracle "
-                           "(same algorithm, exact Schur solve) on a bounded sample, scaled by observation count"},
+                   "note": "pycolmap / pyceres / Ceres are not installable here; the reference arm is the C++/OpenMP port "
+                           "of the same algorithm (oracle/cpu_port) on all host threads; a step = the first 2 LM "
+                           "iterations of a bounded sample of the workload's scene"},
         "cpu_baseline": info,
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -322,7 +326,7 @@ def run_gpu(args):
                 "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": ab[top],
                 "avg_launch_ms": ms / n, "frac_of_nominal_8TBps": achieved / 8000.0}
 
-    cpu = cpu_baseline_sample(args.workload) if (world == 1 and not args.no_cpu_baseline) else None
+    cpu = cpu_baseline_sample(args.workload, layout=full) if (world == 1 and not args.no_cpu_baseline) else None
     C_, P_, L_ = CONFIGS[args.workload]
     line = {
         "metric": METRIC, "value": iters / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -363,7 +367,8 @@ def main():
     ap.add_argument("--workload", default="cfg3")
     ap.add_argument("--pcg-tol", dest="pcg_tol", type=float, default=1e-10)
     ap.add_argument("--pcg-max-iter", dest="pcg_max_iter", type=int, default=2000)
-    ap.add_argument("--ref-obs", dest="ref_obs", type=int, default=40_000)
+    ap.add_argument("--ref-obs", dest="ref_obs", type=int, default=1_000_000,
+                    help="reference arm: observations of the bounded sample scene")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sharding", default="shard", choices=["shard", "replicas"])
     args = ap.parse_args()

@@ -89,16 +89,25 @@ __device__ __forceinline__ double block_max(double v, double* sm) {
 // ================================================================================================
 // image order
 // ================================================================================================
+#ifndef MPBA_IMG_THREADS
+#define MPBA_IMG_THREADS 256
+#endif
+constexpr int IMG_THREADS = MPBA_IMG_THREADS;
+constexpr int IMG_WARPS = IMG_THREADS / 32;
 #ifndef MPBA_IMG_MINB
 #define MPBA_IMG_MINB 1
 #endif
-__global__ void __launch_bounds__(256, MPBA_IMG_MINB) k_img_chunks(ProblemView pv, const double* __restrict__ pose,
+__global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(ProblemView pv, const double* __restrict__ pose,
                                                     const double* __restrict__ X, double* __restrict__ chunk_part) {
   const int c = blockIdx.x;
   const int img = pv.chunk_img[c];
   const int beg = pv.chunk_begin[c], end = pv.chunk_end[c];
-  ImgConst ic;
-  load_img(pv, pose, img, ic);
+  // the image's constants (pose, rotation matrix, prior shift / scale) are CTA-uniform: they live in shared
+  // memory (broadcast reads) instead of ~40 registers of every thread
+  __shared__ ImgConst s_ic;
+  if (threadIdx.x == 0) load_img(pv, pose, img, s_ic);
+  __syncthreads();
+  const ImgConst& ic = s_ic;
   const bool img_const = pv.img_free_mask[img] == 0;
   const double2* xy = reinterpret_cast<const double2*>(pv.cm_xy);
   const double* dd = pv.cm_depth;
@@ -128,9 +137,9 @@ __global__ void __launch_bounds__(256, MPBA_IMG_MINB) k_img_chunks(ProblemView p
   int k = beg + (int)threadIdx.x;
   Operands cur, nxt;
   if (k < end) fetch(k, cur);
-  for (; k < end; k += 256) {
-    const bool more = k + 256 < end;
-    if (more) fetch(k + 256, nxt);
+  for (; k < end; k += IMG_THREADS) {
+    const bool more = k + IMG_THREADS < end;
+    if (more) fetch(k + IMG_THREADS, nxt);
     const double Xp[3] = {cur.xa.x, cur.xa.y, cur.xb.x};
     ObsLin o;
     linearize_obs<true, true>(ic.pose, ic.R, Xp, ic.model, ic.prm, cur.o2.x, cur.o2.y, cur.d, cur.w, cur.a, ic.b, ic.es,
@@ -147,7 +156,7 @@ __global__ void __launch_bounds__(256, MPBA_IMG_MINB) k_img_chunks(ProblemView p
     if (more) cur = nxt;
   }
 
-  __shared__ double sm[8][IMG_PART];
+  __shared__ double sm[IMG_WARPS][IMG_PART];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int j = 0; j < 29; ++j) {
@@ -159,7 +168,7 @@ __global__ void __launch_bounds__(256, MPBA_IMG_MINB) k_img_chunks(ProblemView p
   if (threadIdx.x < 29) {
     double s = 0.0;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) s += sm[w][threadIdx.x];
+    for (int w = 0; w < IMG_WARPS; ++w) s += sm[w][threadIdx.x];
     chunk_part[(size_t)c * IMG_PART + threadIdx.x] = s;
   }
 }
@@ -1603,7 +1612,7 @@ __global__ void k_expand_hcc(int C, const double* __restrict__ Hc, double* __res
 // launchers
 // ================================================================================================
 void launch_img_chunks(const ProblemView& pv, const double* pose, const double* X, double* chunk_part, cudaStream_t st) {
-  if (pv.num_chunks > 0) k_img_chunks<<<pv.num_chunks, 256, 0, st>>>(pv, pose, X, chunk_part);
+  if (pv.num_chunks > 0) k_img_chunks<<<pv.num_chunks, IMG_THREADS, 0, st>>>(pv, pose, X, chunk_part);
 }
 void launch_img_finalize(const ProblemView& pv, const double* chunk_part, double* Hc, double* gc, double* img_part,
                          cudaStream_t st) {
