@@ -90,12 +90,12 @@ __device__ __forceinline__ double block_max(double v, double* sm) {
 // image order
 // ================================================================================================
 #ifndef MPBA_IMG_THREADS
-#define MPBA_IMG_THREADS 256
+#define MPBA_IMG_THREADS 128
 #endif
 constexpr int IMG_THREADS = MPBA_IMG_THREADS;
 constexpr int IMG_WARPS = IMG_THREADS / 32;
 #ifndef MPBA_IMG_MINB
-#define MPBA_IMG_MINB 1
+#define MPBA_IMG_MINB 3
 #endif
 __global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(ProblemView pv, const double* __restrict__ pose,
                                                     const double* __restrict__ X, double* __restrict__ chunk_part) {
@@ -118,8 +118,8 @@ __global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(Probl
   for (int j = 0; j < 29; ++j) acc[j] = 0.0;
 
   // Software pipeline: the operands of the thread's NEXT observation (index -> point gather, xy, depth row) are
-  // in flight while the current one is linearised -- with 8 warps per SM (236 registers) nothing else hides the
-  // DRAM + L2 round trip of the dependent gather.  Slot 3 of a point record carries its constant flag.
+  // in flight while the current one is linearised -- with 12 warps per SM (168 registers, three 128-thread CTAs)
+  // nothing else hides the DRAM + L2 round trip of the dependent gather.  Slot 3 of a point record carries its constant flag.
   struct Operands {
     double2 xa, xb, o2;
     double d, w, a;
