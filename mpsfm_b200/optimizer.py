@@ -89,7 +89,9 @@ class Optimizer(BaseClass):
         "gpu": {"device": 0, "pcg_tolerance": 1e-10, "pcg_max_iterations": 2000, "max_num_iterations": 50,
                 # sample the depth / validity maps of the whole bundle in ONE kernel launch (mpba_sample_maps) instead
                 # of the reference's three torch.grid_sample calls per image (priorutils.py:49-62)
-                "sample_on_device": False},
+                "sample_on_device": False,
+                # under torchrun: shard every solve over the ranks' GPUs (mpba_solve_sharded)
+                "sharded": False},
     }
 
     def _sample_bundle_on_device(self, optim_ids, img_p2ds, depth_type):
@@ -308,7 +310,15 @@ class Optimizer(BaseClass):
         from . import engine
 
         g = self.conf.gpu
-        ba = engine.BundleAdjuster(assembly.problem, device=int(g["device"]))
+        shard = None
+        if bool(g.get("sharded", False)):
+            # one process per GPU (torchrun), every rank running the same mapper: the solve is sharded over the
+            # ranks (mpba_solve_sharded) and every rank receives the full, bit-identical solution
+            import torch.distributed as dist
+
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+                shard = (dist.get_rank(), dist.get_world_size())
+        ba = engine.BundleAdjuster(assembly.problem, device=int(g["device"]), shard=shard)
         try:
             opt = engine.default_options(pcg_tolerance=float(g["pcg_tolerance"]),
                                          pcg_max_iterations=int(g["pcg_max_iterations"]),

@@ -64,3 +64,17 @@ def test_two_gpus_match_one(extra):
     assert out.returncode == 0 and lines, out.stdout[-2000:] + out.stderr[-2000:]
     res = json.loads(lines[-1])
     assert res["ok"] and res["replicas_identical"], res
+
+
+def test_structure_only_through_the_sharded_path():
+    """refine_3d_points (all poses constant): no reduced system, only the image-block all-reduce and the point
+    all-gather remain."""
+    prob = make_scene(10, 500, 5, seed=2, depth_loss=LossType.TRIVIAL)
+    prob.img_free_mask[:] = 0
+    lay = engine.build_layout(prob)
+    a = engine.BundleAdjuster(prob, device=0, layout=lay)
+    sa = a.solve()
+    b = engine.BundleAdjuster(prob, device=0, layout=lay, shard=(0, 1))
+    sb = b.solve()
+    assert sa.num_iterations == sb.num_iterations and abs(sa.final_cost - sb.final_cost) <= 1e-12 * sa.final_cost
+    assert np.max(np.abs(a.state()[2] - b.state()[2])) <= 1e-10
