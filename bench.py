@@ -119,7 +119,7 @@ def algorithmic_bytes(lay, spec=None):
     }
 
 
-def cpu_baseline_sample(workload: str, max_iters: int = 3, obs_cap: int = 6_000_000, layout=None):
+def cpu_baseline_sample(workload: str, max_iters: int = 10, obs_cap: int = 6_000_000, layout=None):
     """The CPU port of the path (oracle/cpu_port: C++17 + OpenMP, all host threads) on a bounded sample: the first
     `max_iters` LM iterations of the workload's own scene when it has at most `obs_cap` observations, else of a scene
     of the same generator scaled down to that size (it/s then scaled by the observation ratio)."""
