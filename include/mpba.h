@@ -291,6 +291,36 @@ int mpba_sample_maps(mpba_handle* h, int32_t n, const double* kps, const int32_t
                      const int64_t* map_offset, const int32_t* map_hw, const double* map_scale, const double* maps,
                      double* out, void* cuda_stream);
 
+/* Per-observation depth-prior terms of a whole bundle in one launch: the arithmetic of the per-image Python loops at
+ * bundle_adjustment.py:136-161 (__build_problem), :239-241 (__build_shiftscale_problem) and :311-330
+ * (update_truncation_multiplier).  For sample k of image img_of[k]:
+ *   z        = row3[img] . (xyz[k], 1)      row3 = third row of cam_from_world.matrix() (utils/geometry.py:13-19)
+ *   mask     = d > 0  [and 1/f < d/z < f if scale_filter_factor = f > 0]  [and |clip(log d,1e-6) - clip(log z,1e-6)|
+ *              / sqrt(v) < 3 if gross_outliers]                                          (:139-147)
+ *   w        = d*d * (1 / max(v, 1e-6)),   a = loss_multiplier * sqrt(v) / d              (:156-161)
+ *   logratio = log(max(z / d, 1e-6))                                                      (:241)
+ *   whitened = (log d - log z) / max(sqrt(v) / d, 1e-6)                                   (:326-330)
+ * Every output pointer may be NULL (not computed).  w and a are bit-identical to numpy's (IEEE mul / div / sqrt in
+ * the reference's order); z, logratio and whitened agree to the last ulps (BLAS matmul order, libm log).
+ * DEVICE pointers; runs on cuda_stream and returns after it completed. */
+int mpba_depth_prior_terms(mpba_handle* h, int32_t n, const int32_t* img_of, int32_t num_images, const double* row3,
+                           const double* xyz, const double* depth, const double* variance, double scale_filter_factor,
+                           int32_t gross_outliers, double loss_multiplier, double* out_z, uint8_t* out_mask,
+                           double* out_w, double* out_a, double* out_logratio, double* out_whitened,
+                           void* cuda_stream);
+
+/* Exact segmented median (numpy.median semantics: mean of the two middle order statistics, NaN if the segment
+ * holds a NaN or is empty) and, if out_mad != NULL, the median absolute deviation median(|x - median|) of every
+ * segment: optimize_prior_shiftscale's per-image np.median (bundle_adjustment.py:239-241) with one segment per
+ * image, fit_robust_gaussian_mad (:10-15) with one segment over all registered images.  Radix select on the
+ * order-preserving 64-bit key, 8 passes of one byte, both middle ranks at once; bit-exact against numpy.
+ * seg_ptr: int32[num_segments + 1], values[seg_ptr[s] .. seg_ptr[s+1]) is segment s.  DEVICE pointers; the
+ * workspace (mpba_segmented_median_workspace_bytes, 256-byte aligned) is caller-owned. */
+int mpba_segmented_median_workspace_bytes(int32_t n, int32_t num_segments, size_t* bytes);
+int mpba_segmented_median(mpba_handle* h, int32_t n, const double* values, int32_t num_segments,
+                          const int32_t* seg_ptr, void* workspace, size_t workspace_bytes, double* out_median,
+                          double* out_mad, void* cuda_stream);
+
 /* After a call with opt->profile: per-kernel summed device ms and launch counts (HOST arrays of
  * MPBA_NUM_KERNELS); names from mpba_kernel_name(slot). */
 int mpba_kernel_times(const mpba_handle* h, double* ms, int64_t* launches);

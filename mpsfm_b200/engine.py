@@ -117,7 +117,8 @@ EXPORTS = (
     "mpba_version", "mpba_create", "mpba_destroy", "mpba_last_error", "mpba_default_options",
     "mpba_workspace_bytes", "mpba_evaluate", "mpba_linearize", "mpba_reduced_system", "mpba_solve",
     "mpba_kernel_times", "mpba_kernel_name", "mpba_point_covariances",
-    "mpba_pack_tracks", "mpba_sample_maps", "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
+    "mpba_pack_tracks", "mpba_sample_maps", "mpba_depth_prior_terms", "mpba_segmented_median_workspace_bytes",
+    "mpba_segmented_median", "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
 )
 
 _lib = None
@@ -151,6 +152,12 @@ def load_library(path: Optional[str] = None):
                                C.POINTER(MpbaOptions), C.POINTER(MpbaSummary)]
     lib.mpba_sample_maps.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.mpba_depth_prior_terms.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_double, C.c_int32, C.c_double, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.mpba_segmented_median_workspace_bytes.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_size_t)]
+    lib.mpba_segmented_median.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t,
+                                          C.c_void_p, C.c_void_p, C.c_void_p]
     lib.mpba_pack_tracks.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_int32)]
     lib.mpba_comm_unique_id.argtypes = [C.c_void_p, C.c_char_p]
     lib.mpba_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_char_p]
@@ -768,6 +775,94 @@ def sample_maps(kps_per_map, maps, scales, device: int = 0):
             raise EngineError(f"mpba_sample_maps failed with code {rc}")
         res = out.cpu().numpy()
     return np.split(res, np.cumsum(counts)[:-1])
+
+
+PRIOR_TERMS = ("z", "mask", "w", "a", "logratio", "whitened")
+
+
+def depth_prior_terms(img_of, row3, xyz, depth, variance, scale_filter_factor: float = 0.0, gross_outliers: bool = False,
+                      loss_multiplier: float = 1.0, want=PRIOR_TERMS, device: int = 0, as_torch: bool = False):
+    """Depth-prior terms of every sampled observation of a bundle in one launch (mpba_depth_prior_terms): z-depth,
+    selection mask, ScaledLoss weight ``w``, loss scale ``a`` (bundle_adjustment.py:136-161), the log ratio of
+    optimize_prior_shiftscale (:241) and the whitened log discrepancy of update_truncation_multiplier (:326-330).
+
+    img_of [n] int32: image row of each sample; row3 [num_images, 4]: third row of cam_from_world.matrix();
+    xyz [n, 3]; depth, variance [n].  Returns {name: array} for the names in ``want``."""
+    import torch
+
+    lib = load_library()
+    if not torch.cuda.is_available():
+        raise EngineUnavailable("no CUDA device: mpsfm_b200 has no CPU fallback")
+    bad = [w for w in want if w not in PRIOR_TERMS]
+    if bad:
+        raise ValueError(f"unknown terms {bad}")
+    dev = torch.device("cuda", device)
+
+    def put(a, dt, shape):
+        if isinstance(a, torch.Tensor):
+            return a.to(device=dev, dtype=dt).reshape(shape).contiguous()
+        return torch.from_numpy(np.ascontiguousarray(np.asarray(a), dtype={torch.float64: np.float64, torch.int32: np.int32}[dt]).reshape(shape)).to(dev)
+
+    with torch.cuda.device(dev):
+        t_img = put(img_of, torch.int32, (-1,))
+        n = int(t_img.numel())
+        t_row = put(row3, torch.float64, (-1, 4))
+        t_xyz, t_d, t_v = put(xyz, torch.float64, (n, 3)), put(depth, torch.float64, (n,)), put(variance, torch.float64, (n,))
+        out = {w: torch.empty(n, dtype=torch.uint8 if w == "mask" else torch.float64, device=dev) for w in want}
+        ptr = lambda w: out[w].data_ptr() if w in out else None  # noqa: E731
+        rc = lib.mpba_depth_prior_terms(None, n, t_img.data_ptr(), int(t_row.shape[0]), t_row.data_ptr(), t_xyz.data_ptr(),
+                                        t_d.data_ptr(), t_v.data_ptr(), float(scale_filter_factor), int(bool(gross_outliers)),
+                                        float(loss_multiplier), ptr("z"), ptr("mask"), ptr("w"), ptr("a"), ptr("logratio"),
+                                        ptr("whitened"), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        if rc != 0:
+            raise EngineError(f"mpba_depth_prior_terms failed with code {rc}")
+        if as_torch:
+            return out
+        res = {w: v.cpu().numpy() for w, v in out.items()}
+    if "mask" in res:
+        res["mask"] = res["mask"].astype(bool)
+    return res
+
+
+def segmented_median(values, seg_ptr, mad: bool = False, device: int = 0):
+    """Exact ``np.median`` of every segment ``values[seg_ptr[s]:seg_ptr[s+1]]`` on the GPU (mpba_segmented_median);
+    with ``mad`` also ``np.median(np.abs(x - median))`` per segment (fit_robust_gaussian_mad,
+    bundle_adjustment.py:10-15).  values: numpy array or CUDA tensor (float64).  Returns median [S] (and mad [S])."""
+    import torch
+
+    lib = load_library()
+    if not torch.cuda.is_available():
+        raise EngineUnavailable("no CUDA device: mpsfm_b200 has no CPU fallback")
+    dev = torch.device("cuda", device)
+    seg = np.ascontiguousarray(np.asarray(seg_ptr, dtype=np.int64))
+    if seg.ndim != 1 or seg.size < 1 or np.any(np.diff(seg) < 0) or seg[0] < 0:
+        raise ValueError("seg_ptr must be a non-decreasing offset array")
+    S = int(seg.size - 1)
+    with torch.cuda.device(dev):
+        if isinstance(values, torch.Tensor):
+            t_val = values.to(device=dev, dtype=torch.float64).reshape(-1).contiguous()
+        else:
+            t_val = torch.from_numpy(np.ascontiguousarray(np.asarray(values, dtype=np.float64).reshape(-1))).to(dev)
+        n = int(t_val.numel())
+        if seg[-1] > n or n >= 2**31:
+            raise ValueError("seg_ptr runs past the values")
+        t_seg = torch.from_numpy(seg.astype(np.int32)).to(dev)
+        nbytes = C.c_size_t(0)
+        rc = lib.mpba_segmented_median_workspace_bytes(n, S, C.byref(nbytes))
+        if rc != 0:
+            raise EngineError(f"mpba_segmented_median_workspace_bytes failed with code {rc}")
+        ws = torch.empty(int(nbytes.value) + 256, dtype=torch.uint8, device=dev)
+        ws_ptr = (ws.data_ptr() + 255) & ~255
+        med = torch.empty(S, dtype=torch.float64, device=dev)
+        t_mad = torch.empty(S, dtype=torch.float64, device=dev) if mad else None
+        rc = lib.mpba_segmented_median(None, n, t_val.data_ptr() if n else None, S, t_seg.data_ptr(), ws_ptr,
+                                       int(nbytes.value), med.data_ptr(), t_mad.data_ptr() if mad else None,
+                                       C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        if rc != 0:
+            raise EngineError(f"mpba_segmented_median failed with code {rc}")
+        if mad:
+            return med.cpu().numpy(), t_mad.cpu().numpy()
+        return med.cpu().numpy()
 
 
 def dense_reduced_system(layout: HostLayout, S_blocks: np.ndarray) -> np.ndarray:

@@ -90,6 +90,10 @@ class Optimizer(BaseClass):
                 # sample the depth / validity maps of the whole bundle in ONE kernel launch (mpba_sample_maps) instead
                 # of the reference's three torch.grid_sample calls per image (priorutils.py:49-62)
                 "sample_on_device": False,
+                # depth-prior masks / weights of the whole bundle in one launch (mpba_depth_prior_terms) and the
+                # medians of optimize_prior_shiftscale / update_truncation_multiplier on the GPU
+                # (mpba_segmented_median) instead of per-image numpy
+                "stats_on_device": False,
                 # under torchrun: shard every solve over the ranks' GPUs (mpba_solve_sharded)
                 "sharded": False},
     }
@@ -120,6 +124,57 @@ class Optimizer(BaseClass):
         out = engine.sample_maps(kps + kps, vmaps + dmaps, scales + scales, device=int(g.get("device", 0)))
         n = len(ids)
         return {imid: (out[i] == 1, out[n + i]) for i, imid in enumerate(ids)}
+
+    def _stats_on_device(self) -> bool:
+        g = self.conf["gpu"] if "gpu" in self.conf else {}
+        return bool(g.get("stats_on_device", False))
+
+    def _row3_xyz(self, rows_imid_p3ds):
+        """(img_of, row3, xyz, counts) of the samples of several images: third row of cam_from_world.matrix() per
+        image (what project3D reads for the depth, utils/geometry.py:13-19) and the world points."""
+        rec = self.mpsfm_rec
+        row3 = np.array([np.asarray(rec.images[imid].cam_from_world.matrix(), dtype=np.float64)[2] for imid, _ in rows_imid_p3ds]
+                        ).reshape(-1, 4)
+        counts = [int(len(p3Ds)) for _, p3Ds in rows_imid_p3ds]
+        img_of = np.repeat(np.arange(len(counts), dtype=np.int32), counts)
+        xyz = [np.asarray(rec.point3D_coordinates([int(p) for p in p3Ds]), dtype=np.float64).reshape(-1, 3)
+               for _, p3Ds in rows_imid_p3ds if len(p3Ds)]
+        xyz = np.concatenate(xyz) if xyz else np.zeros((0, 3))
+        return img_of, row3, xyz, counts
+
+    def _prior_terms(self, rows, scale_f, gross, m):
+        """[(mask, w, a)] per image of ``rows`` = [(imid, p2Ds, p3Ds, depths, variances)] (:136-161)."""
+        rec = self.mpsfm_rec
+        if not rows:
+            return []
+        if self._stats_on_device():
+            from . import engine
+
+            img_of, row3, xyz, counts = self._row3_xyz([(r[0], r[2]) for r in rows])
+            out = engine.depth_prior_terms(img_of, row3, xyz, np.concatenate([r[3] for r in rows]),
+                                           np.concatenate([r[4] for r in rows]), scale_filter_factor=scale_f,
+                                           gross_outliers=gross, loss_multiplier=m, want=("mask", "w", "a"),
+                                           device=int(self.conf.gpu.get("device", 0)))
+            cuts = np.cumsum(counts)[:-1]
+            return list(zip(np.split(out["mask"], cuts), np.split(out["w"], cuts), np.split(out["a"], cuts)))
+        terms = []
+        for imid, p2Ds, p3Ds, depths, variances in rows:
+            with np.errstate(divide="ignore", invalid="ignore"):
+                mask = depths > 0
+                if scale_f > 0 or gross:
+                    depth3d = (np.asarray(rec.project_image_3d_points(imid, p3Ds)[3], dtype=np.float64)
+                               if p2Ds.size else np.zeros(0))
+                if scale_f > 0:
+                    div = depths / depth3d
+                    mask = mask & (div < scale_f) & (div > (1 / scale_f))
+                if gross:
+                    whitened = np.abs(np.log(depths).clip(1e-6, None) - np.log(depth3d).clip(1e-6, None)) / variances**0.5
+                    mask = mask & (whitened < 3)
+                inv_uncert = 1 / variances.clip(1e-6, None)
+                params = m * variances**0.5 / depths  # :160 loss scale a
+                magnitudes = depths**2 * inv_uncert  # :161 ScaledLoss weight w
+            terms.append((mask, magnitudes, params))
+        return terms
 
     def _init(self, mpsfm_rec, correspondences=None):
         self.mpsfm_rec = mpsfm_rec
@@ -237,6 +292,8 @@ class Optimizer(BaseClass):
         pm = param_multiplier * self.truncation_multiplier  # :109
         sampled = self._sample_bundle_on_device(optim_ids, img_p2ds, depth_type) if with_depth else None
         if with_depth:
+            # phase 1 (per image, host): which observations carry a valid prior sample (:126-135, :143)
+            rows = []
             for imid in optim_ids:
                 image = rec.images[imid]
                 if image.depth is None or not image.depth.activated:
@@ -255,25 +312,22 @@ class Optimizer(BaseClass):
                                         else image.depth.data_prior_at_kps(kps), dtype=np.float64)
                 p2Ds = p2Ds[valid]
                 p3Ds = np.asarray(image.point3D_ids(p2Ds), dtype=np.uint64).astype(np.int64)
-                depth3d = np.asarray(rec.project_image_3d_points(imid, p3Ds)[3], dtype=np.float64) if p2Ds.size else np.zeros(0)
-                mask = depths > 0
-                if allow_scale_filter and conf.scale_filter:
-                    div = depths / depth3d
-                    mask = mask & (div < conf.scale_filter_factor) & (div > (1 / conf.scale_filter_factor))
                 uu = image.depth.uncertainty_update
                 variances = (np.asarray(uu, dtype=np.float64)[p2Ds] if isinstance(uu, np.ndarray)
                              else np.array([uu[i] for i in p2Ds], dtype=np.float64))
-                if conf.gross_outliers:
-                    whitened = np.abs(np.log(depths).clip(1e-6, None) - np.log(depth3d).clip(1e-6, None)) / variances**0.5
-                    mask = mask & (whitened < 3)
+                rows.append((imid, p2Ds, p3Ds, depths, variances))
+            # phase 2: masks (:139-147), loss scale a and weight w (:156-161) -- one launch for the bundle
+            #          (mpba_depth_prior_terms) or the reference's per-image numpy
+            scale_f = float(conf.scale_filter_factor) if (allow_scale_filter and conf.scale_filter) else 0.0
+            m = pm * conf.rob_std
+            terms = self._prior_terms(rows, scale_f, bool(conf.gross_outliers), m)
+            # phase 3 (per image): keep the selected observations
+            for (imid, p2Ds, p3Ds, depths, variances), (mask, magnitudes, params) in zip(rows, terms):
                 if np.sum(mask) == 0:
                     self.log("No valid points for depth regularizing", level=1)
                     continue
-                depths, p2Ds, variances, p3Ds = depths[mask], p2Ds[mask], variances[mask], p3Ds[mask]
-                inv_uncert = 1 / variances.clip(1e-6, None)
-                m = pm * conf.rob_std
-                params = m * variances**0.5 / depths  # :160 loss scale a
-                magnitudes = depths**2 * inv_uncert  # :161 ScaledLoss weight w
+                depths, p2Ds, p3Ds = depths[mask], p2Ds[mask], p3Ds[mask]
+                magnitudes, params = magnitudes[mask], params[mask]
                 depth_rows[imid] = {"p2Ds": p2Ds, "p3Ds": p3Ds, "depths": depths, "magnitudes": magnitudes, "params": params}
                 d_obs.append(img_obs_offset[imid] + np.searchsorted(img_p2ds[imid], p2Ds))
                 d_d.append(depths)
@@ -412,6 +466,7 @@ class Optimizer(BaseClass):
     def __build_shiftscale_problem(self, bundle, allow_scale_filter=False, allow_metric_scale_filter=False):
         conf, rec = self.conf, self.mpsfm_rec
         shift_scale = {}
+        pending = []  # gpu.stats_on_device: (imid, p3D ids, prior depths) of the images still to be reduced
         for kw in self.__yield_problem_parameters(bundle["optim_ids"], proj_depths=conf.scale_filter or conf.metric_scale_filter):
             pose = kw["image"].cam_from_world
             imid, p3dids = kw["imid"], kw["pt3D_ids"]
@@ -432,20 +487,37 @@ class Optimizer(BaseClass):
                 if kw["valid"].sum() == 0:
                     print("WARNING: Settin all points as outliers for metric scale optim and using map scale!!")
                     shift_scale[imid] = np.array([0.0, np.log(map_scale / rec.images[imid].depth.scale)])
-                    return shift_scale, True
+                    break  # the reference returns here (:224-226); images reduced so far are kept
                 self.log(f"Setting {presum - kw['valid'].sum()}points as outliers for metric scale optim, out of {presum}", level=3)
             if allow_scale_filter and conf.scale_filter and not allow_metric_scale_filter:  # :233-238
                 div = kw["obsdepths"] / kw["projdepths"]
                 kw["valid"] = kw["valid"] * ((div < conf.scale_filter_factor) * (div > (1 / conf.scale_filter_factor)))
+            if self._stats_on_device():
+                keep = np.asarray(kw["valid"], dtype=bool)
+                pending.append((imid, np.asarray(p3dids)[keep], np.asarray(kw["obsdepths"], dtype=np.float64)[keep]))
+                continue
             z = (pose * rec.point3D_coordinates(p3dids))[:, -1]
             z = z[kw["valid"]]
             odepth = kw["obsdepths"][kw["valid"]]
             shift_scale[imid] = np.array([0.0, np.median(np.log((z / odepth).clip(1e-6, None)))])  # :239-241
+        if pending:
+            # every image's log(z / d) in one launch, then one segmented median (one segment per image)
+            from . import engine
+
+            device = int(self.conf.gpu.get("device", 0))
+            img_of, row3, xyz, counts = self._row3_xyz([(imid, p3Ds) for imid, p3Ds, _ in pending])
+            odepth = np.concatenate([d for _, _, d in pending])
+            terms = engine.depth_prior_terms(img_of, row3, xyz, odepth, np.ones_like(odepth), want=("logratio",),
+                                             device=device, as_torch=True)
+            med = engine.segmented_median(terms["logratio"], np.concatenate([[0], np.cumsum(counts)]), device=device)
+            for (imid, _, _), value in zip(pending, med):
+                shift_scale[imid] = np.array([0.0, float(value)])
         return shift_scale, True
 
     def update_truncation_multiplier(self, imids):
         """Robust spread (1.4826 MAD) of the whitened log-depth discrepancy over the given images (:295-333)."""
-        D, D3d, dstds = [], [], []
+        D, D3d, dstds, P3, V = [], [], [], [], []
+        on_device = self._stats_on_device()
         for imid in imids:
             image = self.mpsfm_rec.images[imid]
             p2Ds = np.asarray(image.get_observation_point2D_idxs(), dtype=np.int64)
@@ -455,16 +527,30 @@ class Optimizer(BaseClass):
             p2Ds = p2Ds[valid]
             p3Ds = np.asarray(image.point3D_ids(p2Ds), dtype=np.uint64).astype(np.int64)
             mask = depths > 0
-            depth3d = self.mpsfm_rec.project_image_3d_points(imid, [int(p) for p in p3Ds[mask]])[3]
+            P3.append(p3Ds[mask])
+            depth3d = np.zeros(0) if on_device else self.mpsfm_rec.project_image_3d_points(imid, [int(p) for p in p3Ds[mask]])[3]
             uu = image.depth.uncertainty_update
             variances = (np.asarray(uu, dtype=np.float64)[p2Ds[mask]] if isinstance(uu, np.ndarray)
                          else np.array([uu[i] for i in p2Ds[mask]], dtype=np.float64))
             D.append(depths[mask])
             D3d.append(np.asarray(depth3d, dtype=np.float64))
             dstds.append(variances**0.5)
-        depths, depth3ds, dstds = np.concatenate(D), np.concatenate(D3d), np.concatenate(dstds)
-        log_stds = np.clip(dstds / depths, 1e-6, None)
-        _, sigma = fit_robust_gaussian_mad((np.log(depths) - np.log(depth3ds)) / log_stds)
+            V.append(variances)
+        if on_device:
+            # whitened log discrepancy of every sample in one launch, then median and MAD as one radix select each
+            from . import engine
+
+            device = int(self.conf.gpu.get("device", 0))
+            img_of, row3, xyz, _ = self._row3_xyz(list(zip(imids, P3)))
+            depths, dvars = np.concatenate(D), np.concatenate(V)
+            terms = engine.depth_prior_terms(img_of, row3, xyz, depths, dvars, want=("whitened",), device=device,
+                                             as_torch=True)
+            _, mad = engine.segmented_median(terms["whitened"], [0, depths.size], mad=True, device=device)
+            sigma = 1.4826 * float(mad[0])
+        else:
+            depths, depth3ds, dstds = np.concatenate(D), np.concatenate(D3d), np.concatenate(dstds)
+            log_stds = np.clip(dstds / depths, 1e-6, None)
+            _, sigma = fit_robust_gaussian_mad((np.log(depths) - np.log(depth3ds)) / log_stds)
         self.truncation_multiplier = sigma
         if self.conf.min_truncation_mult is not None:
             self.truncation_multiplier = max(self.truncation_multiplier, self.conf.min_truncation_mult)

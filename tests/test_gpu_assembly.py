@@ -60,3 +60,38 @@ def test_optimizer_assembly_with_device_sampling_equals_the_reference_objects_pa
     assert np.array_equal(pa.depth_obs, pb.depth_obs)  # the same observations carry a prior (validity bit-exact)
     assert np.array_equal(pa.depth_d, pb.depth_d) and np.array_equal(pa.depth_w, pb.depth_w)
     assert np.array_equal(pa.depth_a, pb.depth_a)
+
+
+def test_optimizer_stats_on_device_equal_the_numpy_path():
+    """gpu.stats_on_device: depth-prior masks / weights (mpba_depth_prior_terms) and the medians of
+    optimize_prior_shiftscale / update_truncation_multiplier (mpba_segmented_median) against the reference's
+    per-image numpy on the same scene objects."""
+    from scene_factory import build_scene
+
+    from mpsfm_b200.optimizer import Optimizer
+
+    rec = build_scene(seed=6, num_images=8, num_points=300)
+    ids = [3, 1, 2, 4, 5, 6, 7, 8]
+    bundle = {"optim_ids": ids, "pts3D": set(rec.points3D)}
+    host, dev = Optimizer({}, rec, None), Optimizer({"gpu": {"stats_on_device": True, "sample_on_device": True}}, rec, None)
+    for kw in ({}, {"allow_scale_filter": True}):
+        pa = host.assemble(bundle, fix_pose=False, mode="global", **kw).problem
+        pb = dev.assemble(bundle, fix_pose=False, mode="global", **kw).problem
+        assert pa.num_depth > 0 and np.array_equal(pa.depth_obs, pb.depth_obs)
+        assert np.array_equal(pa.depth_d, pb.depth_d)
+        assert np.array_equal(pa.depth_w, pb.depth_w) and np.array_equal(pa.depth_a, pb.depth_a)  # IEEE order kept
+
+    host.update_truncation_multiplier(ids)
+    dev.update_truncation_multiplier(ids)
+    assert host.truncation_multiplier > 0
+    assert abs(host.truncation_multiplier - dev.truncation_multiplier) <= 1e-12 * host.truncation_multiplier
+
+    for kw in ({}, {"allow_scale_filter": True}):
+        for ref_id in ids[:3]:
+            b = dict(bundle, ref_id=ref_id)
+            sa, oka = host.optimize_prior_shiftscale(b, **kw)
+            sb, okb = dev.optimize_prior_shiftscale(b, **kw)
+            assert oka and okb and sa.keys() == sb.keys() and len(sa) > 0
+            for imid in sa:
+                assert sa[imid][0] == sb[imid][0] == 0.0
+                assert abs(sa[imid][1] - sb[imid][1]) <= 1e-13 * abs(sa[imid][1])
