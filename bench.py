@@ -289,6 +289,14 @@ def run_gpu(args):
         d2h = lay.C * 64 + lay.P * 32
     barrier()
     e2e_s = time.perf_counter() - t0
+    # one more, untimed, step with a synchronize after every leg: where the end-to-end time goes
+    torch.cuda.synchronize()
+    tb = [time.perf_counter()]
+    ba2.upload(); torch.cuda.synchronize(); tb.append(time.perf_counter())
+    ba2.solve(opt); torch.cuda.synchronize(); tb.append(time.perf_counter())
+    ba2.state(); tb.append(time.perf_counter())
+    e2e_legs = {"upload_ms": round(1e3 * (tb[1] - tb[0]), 3), "solve_ms": round(1e3 * (tb[2] - tb[1]), 3),
+                "readback_ms": round(1e3 * (tb[3] - tb[2]), 3)}
     ba2.close()
 
     if dist is not None:
@@ -348,7 +356,7 @@ def run_gpu(args):
         "ms_per_lm_iteration": ms_total / max(iters, 1),
         "ms_per_step_with_kernel_events": ms_total_prof / args.steps,
         "e2e": {"value": e2e_iters / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": 1e3 * e2e_s / args.steps},
+                "ms_per_step": 1e3 * e2e_s / args.steps, "legs_of_one_extra_step": e2e_legs},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": roof,

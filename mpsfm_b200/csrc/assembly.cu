@@ -59,7 +59,32 @@ __global__ void __launch_bounds__(256) k_sample_maps(int n, const double* __rest
   out[k] = acc;
 }
 
+// image-order copies of the per-observation inputs from the track-order ones: dst[i] = src[perm[i]]
+__global__ void __launch_bounds__(256) k_gather_observations(int n, const int32_t* __restrict__ perm,
+                                                             const double2* __restrict__ src_xy,
+                                                             const double* __restrict__ src_depth,
+                                                             double2* __restrict__ dst_xy, double* __restrict__ dst_depth) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  const int j = __ldg(perm + i);
+  dst_xy[i] = __ldg(src_xy + j);
+#pragma unroll
+  for (int r = 0; r < 3; ++r) dst_depth[(size_t)r * n + i] = __ldg(src_depth + (size_t)r * n + j);
+}
+
 }  // namespace
+
+extern "C" int mpba_gather_observations(mpba_handle* h, int32_t n, const int32_t* perm, const double* src_xy,
+                                        const double* src_depth, double* dst_xy, double* dst_depth, void* cuda_stream) {
+  (void)h;
+  if (n < 0) return MPBA_E_INVALID;
+  if (n == 0) return MPBA_OK;
+  if (!perm || !src_xy || !src_depth || !dst_xy || !dst_depth) return MPBA_E_INVALID;
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  k_gather_observations<<<(n + 255) / 256, 256, 0, st>>>(n, perm, reinterpret_cast<const double2*>(src_xy), src_depth,
+                                                         reinterpret_cast<double2*>(dst_xy), dst_depth);
+  return cudaGetLastError() == cudaSuccess ? MPBA_OK : MPBA_E_CUDA;
+}
 
 extern "C" int mpba_sample_maps(mpba_handle* h, int32_t n, const double* kps, const int32_t* map_of, int32_t num_maps,
                                 const int64_t* map_offset, const int32_t* map_hw, const double* map_scale,

@@ -118,7 +118,7 @@ EXPORTS = (
     "mpba_workspace_bytes", "mpba_evaluate", "mpba_linearize", "mpba_reduced_system", "mpba_solve",
     "mpba_kernel_times", "mpba_kernel_name", "mpba_point_covariances",
     "mpba_pack_tracks", "mpba_sample_maps", "mpba_depth_prior_terms", "mpba_segmented_median_workspace_bytes",
-    "mpba_segmented_median", "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
+    "mpba_segmented_median", "mpba_gather_observations", "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
 )
 
 _lib = None
@@ -158,6 +158,8 @@ def load_library(path: Optional[str] = None):
     lib.mpba_segmented_median_workspace_bytes.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_size_t)]
     lib.mpba_segmented_median.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t,
                                           C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.mpba_gather_observations.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_void_p]
     lib.mpba_pack_tracks.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_int32)]
     lib.mpba_comm_unique_id.argtypes = [C.c_void_p, C.c_char_p]
     lib.mpba_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_char_p]
@@ -523,15 +525,26 @@ class BundleAdjuster:
         self.buf = {}
         self.host = {}  # pinned staging copies of the problem arrays (pinned=True): source of upload()
         self.h2d_bytes = 0
+        # an unsharded problem holds the same observations in both orders: upload() sends the track order and a
+        # permutation, the image-order xy / depth arrays are gathered on the device (mpba_gather_observations)
+        self._derive_cm = bool(pinned and self.shard is None and lay.N > 0)
         with torch.cuda.device(self.device):
             for name in _DEVICE_FIELDS:
                 arr = np.ascontiguousarray(getattr(lay, name))
                 t = torch.from_numpy(arr)
-                if pinned:
+                if pinned and not (self._derive_cm and name in ("cm_xy", "cm_depth")):
                     t = t.pin_memory()
                     self.host[name] = t
                 self.buf[name] = t.to(self.device, non_blocking=pinned)
                 self.h2d_bytes += arr.nbytes
+            if self._derive_cm:
+                pm_pos = np.empty(lay.N, dtype=np.int32)
+                pm_pos[lay.pm_src] = np.arange(lay.N, dtype=np.int32)
+                self.host["cm_pm"] = torch.from_numpy(np.ascontiguousarray(pm_pos[lay.cm_src])).pin_memory()
+                self.buf["cm_pm"] = self.host["cm_pm"].to(self.device, non_blocking=True)
+            if pinned:
+                self._pose_host = torch.empty((lay.C, 8), dtype=torch.float64).pin_memory()
+                self._xyz_host = torch.empty((lay.P, 4), dtype=torch.float64).pin_memory()
             for name in ("item_a", "item_b", "chunk_img", "chunk_begin", "chunk_end"):
                 if self.buf[name].numel() == 0:
                     self.buf[name] = torch.zeros(1, dtype=torch.int32, device=self.device)
@@ -610,6 +623,11 @@ class BundleAdjuster:
             if t.numel():
                 self.buf[name].copy_(t, non_blocking=True)
                 n += t.numel() * t.element_size()
+        if self._derive_cm:
+            self._check(self.lib.mpba_gather_observations(
+                self.handle, self.layout.N, self.buf["cm_pm"].data_ptr(), self.buf["pm_xy"].data_ptr(),
+                self.buf["pm_depth"].data_ptr(), self.buf["cm_xy"].data_ptr(), self.buf["cm_depth"].data_ptr(),
+                C.c_void_p(self.torch.cuda.current_stream().cuda_stream)))
         return n
 
     def reset_state(self):
@@ -628,8 +646,14 @@ class BundleAdjuster:
 
     def state(self):
         """(img_q [C,4], img_t [C,3], pt_xyz [P,3]) as numpy (device -> host)."""
-        pose = self.buf["img_pose"].cpu().numpy()
-        xyz = self.buf["pt_xyz"].cpu().numpy()
+        if self.host:  # pinned result buffers: one DMA each, no pageable staging
+            self._pose_host.copy_(self.buf["img_pose"], non_blocking=True)
+            self._xyz_host.copy_(self.buf["pt_xyz"], non_blocking=True)
+            self.torch.cuda.current_stream().synchronize()
+            pose, xyz = self._pose_host.numpy(), self._xyz_host.numpy()
+        else:
+            pose = self.buf["img_pose"].cpu().numpy()
+            xyz = self.buf["pt_xyz"].cpu().numpy()
         return pose[:, :4].copy(), pose[:, 4:7].copy(), xyz[:, :3].copy()
 
     def _ws(self):

@@ -74,3 +74,23 @@ def test_two_images_minimal_gauge():
     osum = lm.solve(prob)
     assert summ.num_iterations == len(osum.iterations) - 1
     assert abs(summ.final_cost - osum.final_cost) <= 1e-6 * max(osum.final_cost, 1e-12)
+
+
+def test_upload_derives_the_image_order_arrays_on_the_device():
+    """pinned staging: upload() sends the track order + a permutation and mpba_gather_observations rebuilds
+    cm_xy / cm_depth; the result must be the host layout's arrays bit for bit, and the solve unchanged."""
+    prob = make_scene(12, 900, 5, seed=8, depth_prior=True)
+    plain = engine.BundleAdjuster(prob, device=0)
+    ref = plain.solve()
+    ba = engine.BundleAdjuster(prob, device=0, pinned=True)
+    assert "cm_xy" not in ba.host and "cm_pm" in ba.host
+    ba.buf["cm_xy"].fill_(float("nan"))
+    ba.buf["cm_depth"].fill_(float("nan"))
+    nbytes = ba.upload()
+    assert nbytes < plain.h2d_bytes
+    assert np.array_equal(ba.buf["cm_xy"].cpu().numpy(), ba.layout.cm_xy)
+    assert np.array_equal(ba.buf["cm_depth"].cpu().numpy(), ba.layout.cm_depth)
+    summ = ba.solve()
+    assert summ.num_iterations == ref.num_iterations and summ.final_cost == ref.final_cost
+    for a, b in zip(ba.state(), plain.state()):
+        assert np.array_equal(a, b)
