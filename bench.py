@@ -119,7 +119,7 @@ def algorithmic_bytes(lay, spec=None):
     }
 
 
-def cpu_baseline_sample(workload: str, max_iters: int = 10, obs_cap: int = 6_000_000, layout=None):
+def cpu_baseline_sample(workload: str, max_iters: int = 10, obs_cap: int = 6_000_000, layout=None, pcg_tol: float = 1e-10):
     """The CPU port of the path (oracle/cpu_port: C++17 + OpenMP, all host threads) on a bounded sample: the first
     `max_iters` LM iterations of the workload's own scene when it has at most `obs_cap` observations, else of a scene
     of the same generator scaled down to that size (it/s then scaled by the observation ratio)."""
@@ -140,9 +140,9 @@ def cpu_baseline_sample(workload: str, max_iters: int = 10, obs_cap: int = 6_000
         Cs, Ps = max(12, int(round(C / scale))), max(100, int(round(P / scale)))
         layout = engine.build_layout(synthetic.make_scene(Cs, Ps, L, seed=0, **kw))
     threads = cpu_port.max_threads()
-    cpu_port.solve(layout, max_num_iterations=1)  # warm-up: page in, spin up the thread pool
+    cpu_port.solve(layout, max_num_iterations=1, pcg_tolerance=pcg_tol)  # warm-up: page in, spin up the thread pool
     t0 = time.perf_counter()
-    summ, _, _, _ = cpu_port.solve(layout, max_num_iterations=max_iters)
+    summ, _, _, _ = cpu_port.solve(layout, max_num_iterations=max_iters, pcg_tolerance=pcg_tol)
     dt = time.perf_counter() - t0
     its = summ["num_iterations"]
     it_s = its / dt
@@ -151,7 +151,7 @@ def cpu_baseline_sample(workload: str, max_iters: int = 10, obs_cap: int = 6_000
         "unit": UNIT,
         "cores": threads,
         "kind": "port",
-        "sample": (f"oracle/cpu_port (C++17/OpenMP port of the Ceres path, Schur complement + block-Jacobi PCG to 1e-10; "
+        "sample": (f"oracle/cpu_port (C++17/OpenMP port of the Ceres path, Schur complement + block-Jacobi PCG to {pcg_tol:g}; "
                    f"pycolmap / pyceres / Ceres are not installable here), {threads} threads, first {its} LM iterations of a "
                    f"{layout.C} img / {layout.P} pt / {layout.N} obs scene of the workload's generator in {dt:.1f} s"
                    + ("" if layout.N == n_full else f"; it/s scaled by the observation ratio {layout.N}/{n_full}")),
@@ -171,7 +171,7 @@ def run_reference(args):
     times, info = [], None
     for k in range(args.warmup + args.steps):
         t0 = time.perf_counter()
-        info = cpu_baseline_sample(args.workload, max_iters=2, obs_cap=args.ref_obs)
+        info = cpu_baseline_sample(args.workload, max_iters=2, obs_cap=args.ref_obs, pcg_tol=args.pcg_tol)
         if k >= args.warmup:
             times.append(1.0 / info["sample_it_per_s"])  # seconds per LM iteration on the sample
     mean_dt = float(np.mean(times)) if times else float("nan")
@@ -286,7 +286,7 @@ def run_gpu(args):
         s2 = ba2.solve(opt)
         q, t, X = ba2.state()
         e2e_iters += s2.num_iterations
-        d2h = lay.C * 64 + lay.P * 32
+        d2h = lay.C * 64 + lay.P * 24
     barrier()
     e2e_s = time.perf_counter() - t0
     # one more, untimed, step with a synchronize after every leg: where the end-to-end time goes
@@ -334,7 +334,7 @@ def run_gpu(args):
                 "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": ab[top],
                 "avg_launch_ms": ms / n, "frac_of_nominal_8TBps": achieved / 8000.0}
 
-    cpu = cpu_baseline_sample(args.workload, layout=full) if (world == 1 and not args.no_cpu_baseline) else None
+    cpu = cpu_baseline_sample(args.workload, layout=full, pcg_tol=args.pcg_tol) if (world == 1 and not args.no_cpu_baseline) else None
     C_, P_, L_ = CONFIGS[args.workload]
     line = {
         "metric": METRIC, "value": iters / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,

@@ -544,7 +544,7 @@ class BundleAdjuster:
                 self.buf["cm_pm"] = self.host["cm_pm"].to(self.device, non_blocking=True)
             if pinned:
                 self._pose_host = torch.empty((lay.C, 8), dtype=torch.float64).pin_memory()
-                self._xyz_host = torch.empty((lay.P, 4), dtype=torch.float64).pin_memory()
+                self._xyz_host = torch.empty((lay.P, 3), dtype=torch.float64).pin_memory()
             for name in ("item_a", "item_b", "chunk_img", "chunk_begin", "chunk_end"):
                 if self.buf[name].numel() == 0:
                     self.buf[name] = torch.zeros(1, dtype=torch.int32, device=self.device)
@@ -646,11 +646,14 @@ class BundleAdjuster:
 
     def state(self):
         """(img_q [C,4], img_t [C,3], pt_xyz [P,3]) as numpy (device -> host)."""
-        if self.host:  # pinned result buffers: one DMA each, no pageable staging
+        if self.host:
+            # pinned result buffers: the padded records are packed on the device, one DMA each, and the host
+            # only does contiguous copies out of the staging buffers
             self._pose_host.copy_(self.buf["img_pose"], non_blocking=True)
-            self._xyz_host.copy_(self.buf["pt_xyz"], non_blocking=True)
+            self._xyz_host.copy_(self.buf["pt_xyz"][:, :3], non_blocking=True)
             self.torch.cuda.current_stream().synchronize()
-            pose, xyz = self._pose_host.numpy(), self._xyz_host.numpy()
+            pose = self._pose_host.numpy()
+            return pose[:, :4].copy(), pose[:, 4:7].copy(), self._xyz_host.numpy().copy()
         else:
             pose = self.buf["img_pose"].cpu().numpy()
             xyz = self.buf["pt_xyz"].cpu().numpy()
