@@ -291,6 +291,33 @@ int mpba_sample_maps(mpba_handle* h, int32_t n, const double* kps, const int32_t
                      const int64_t* map_offset, const int32_t* map_hw, const double* map_scale, const double* maps,
                      double* out, void* cuda_stream);
 
+/* ---- host side of the boundary: the index arrays of mpba_problem from the caller's natural observation list ----
+ * What COLMAP's AddImageToProblem + Ceres' block ordering / Schur structure analysis do for the reference
+ * (bundle_adjustment.py:104, :285-293) is this call: both observation orders (stable counting sorts: track order by
+ * (point, image), image order by (image, point)), the image-order chunks, the block-CSR structure of the reduced
+ * camera system over co-visible image pairs, the Schur work lists (items of a unit sorted by track) and the warp
+ * groups of mpba_pack_tracks.  HOST pointers in, HOST arrays out (owned by the returned object, valid until
+ * mpba_host_layout_destroy); multi-threaded (MPBA_HOST_THREADS, default: all hardware threads).
+ * cm_pm[i] = track-order slot of image-order slot i (mpba_gather_observations' permutation). */
+typedef struct mpba_host_layout mpba_host_layout;
+typedef struct mpba_host_layout_view {
+  int32_t num_images, num_points, num_obs;
+  int32_t num_chunks, num_blocks, num_upper, num_track_warps;
+  int64_t num_items;
+  const int32_t *pt_ptr, *pm_img, *pm_src, *img_ptr, *cm_pt, *cm_src, *cm_pm;
+  const int32_t *chunk_img, *chunk_begin, *chunk_end, *img_chunk_ptr;
+  const int32_t *s_row_ptr, *s_col, *s_diag, *s_transpose, *s_row, *u_block, *u_item_ptr, *item_a, *item_b;
+  const int32_t *track_warp_first;
+} mpba_host_layout_view;
+int mpba_host_layout_create(int32_t num_images, int32_t num_points, int32_t num_obs, const int32_t* obs_img,
+                            const int32_t* obs_pt, const uint8_t* pt_const, int32_t structure_only,
+                            mpba_host_layout** out, mpba_host_layout_view* view);
+void mpba_host_layout_destroy(mpba_host_layout* layout);
+/* value arrays of one observation order: out_xy[k] = obs_xy[src[k]], out_depth[r][k] = {d, w, a}[r][src[k]]
+ * (src = pm_src or cm_src).  HOST pointers. */
+int mpba_host_gather(int32_t num_obs, const int32_t* src, const double* obs_xy, const double* d, const double* w,
+                     const double* a, double* out_xy, double* out_depth);
+
 /* The problem holds every observation twice (track order pm_*, image order cm_*).  A caller whose arrays live on the
  * host uploads one order plus a 4-byte permutation and derives the other on the device: dst_xy[i] =
  * src_xy[perm[i]], dst_depth[r][i] = src_depth[r][perm[i]] (r = 0..2, the [3][n] layout of pm_depth / cm_depth).

@@ -118,7 +118,8 @@ EXPORTS = (
     "mpba_workspace_bytes", "mpba_evaluate", "mpba_linearize", "mpba_reduced_system", "mpba_solve",
     "mpba_kernel_times", "mpba_kernel_name", "mpba_point_covariances",
     "mpba_pack_tracks", "mpba_sample_maps", "mpba_depth_prior_terms", "mpba_segmented_median_workspace_bytes",
-    "mpba_segmented_median", "mpba_gather_observations", "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
+    "mpba_segmented_median", "mpba_gather_observations", "mpba_host_layout_create", "mpba_host_layout_destroy",
+    "mpba_host_gather", "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
 )
 
 _lib = None
@@ -158,6 +159,11 @@ def load_library(path: Optional[str] = None):
     lib.mpba_segmented_median_workspace_bytes.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_size_t)]
     lib.mpba_segmented_median.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t,
                                           C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.mpba_host_layout_create.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                                            C.POINTER(C.c_void_p), C.c_void_p]
+    lib.mpba_host_layout_destroy.argtypes = [C.c_void_p]
+    lib.mpba_host_layout_destroy.restype = None
+    lib.mpba_host_gather.argtypes = [C.c_int32] + [C.c_void_p] * 7
     lib.mpba_gather_observations.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                              C.c_void_p, C.c_void_p]
     lib.mpba_pack_tracks.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_int32)]
@@ -261,12 +267,83 @@ def _ptr_from_counts(counts: np.ndarray) -> np.ndarray:
     return out.astype(np.int32)
 
 
-def build_layout(problem: BundleProblem) -> HostLayout:
-    """Sort the observations into the two orders and build the reduced-system structure.
+class MpbaHostLayoutView(C.Structure):
+    _fields_ = ([(n, C.c_int32) for n in ("num_images", "num_points", "num_obs", "num_chunks", "num_blocks", "num_upper",
+                                         "num_track_warps")]
+                + [("num_items", C.c_int64)]
+                + [(n, C.POINTER(C.c_int32)) for n in (
+                    "pt_ptr", "pm_img", "pm_src", "img_ptr", "cm_pt", "cm_src", "cm_pm", "chunk_img", "chunk_begin",
+                    "chunk_end", "img_chunk_ptr", "s_row_ptr", "s_col", "s_diag", "s_transpose", "s_row", "u_block",
+                    "u_item_ptr", "item_a", "item_b", "track_warp_first")])
 
-    The natural observation index of every slot is kept (``pm_src`` / ``cm_src``): per-residual
-    outputs are mapped back through it, which is the "correspondence / track indexing bit-exact"
-    gate of BASELINE.json."""
+
+def build_layout(problem: BundleProblem) -> HostLayout:
+    """Sort the observations into the two orders and build the reduced-system structure: the native, multi-threaded
+    builder of libmpba.so (mpba_host_layout_create / mpba_host_gather, csrc/host_layout.cpp).
+
+    The natural observation index of every slot is kept (``pm_src`` / ``cm_src``): per-residual outputs are mapped
+    back through it, which is the "correspondence / track indexing bit-exact" gate of BASELINE.json.
+    ``build_layout_numpy`` states the same layout in numpy; tests/test_host_layout.py holds the two equal."""
+    lib = load_library()
+    pr = problem.normalized()
+    pr.validate()
+    Cn, P, N = pr.num_images, pr.num_points, pr.num_obs
+    K = int(pr.cam_model.shape[0])
+    if pr.num_depth and not np.all(pr.depth_w > 0):
+        raise ValueError("depth prior weights must be > 0 (w == 0 marks 'no prior' in the device layout)")
+    obs_img = np.ascontiguousarray(pr.obs_img, dtype=np.int32)
+    obs_pt = np.ascontiguousarray(pr.obs_pt, dtype=np.int32)
+    pt_const = np.ascontiguousarray(pr.pt_const, dtype=np.uint8)
+    structure_only = bool(np.all(pr.img_free_mask == 0))
+    view, handle = MpbaHostLayoutView(), C.c_void_p()
+    rc = lib.mpba_host_layout_create(Cn, P, N, obs_img.ctypes.data, obs_pt.ctypes.data, pt_const.ctypes.data,
+                                     int(structure_only), C.byref(handle), C.byref(view))
+    if rc != 0:
+        raise ValueError(f"mpba_host_layout_create failed with code {rc} (index out of range, or more than 2^31-1 "
+                         "Schur items: shard the problem across GPUs)")
+    try:
+        def take(name, n):
+            return np.ctypeslib.as_array(getattr(view, name), shape=(n,)).copy() if n else np.zeros(0, dtype=np.int32)
+
+        B, U = view.num_blocks, view.num_upper
+        idx = {name: take(name, n) for name, n in (
+            ("pt_ptr", P + 1), ("pm_img", N), ("pm_src", N), ("img_ptr", Cn + 1), ("cm_pt", N), ("cm_src", N),
+            ("chunk_img", view.num_chunks), ("chunk_begin", view.num_chunks), ("chunk_end", view.num_chunks),
+            ("img_chunk_ptr", Cn + 1), ("s_row_ptr", Cn + 1), ("s_col", B), ("s_diag", Cn), ("s_transpose", B),
+            ("s_row", B), ("u_block", U), ("u_item_ptr", U + 1), ("item_a", view.num_items),
+            ("item_b", view.num_items), ("track_warp_first", view.num_track_warps + 1))}
+    finally:
+        lib.mpba_host_layout_destroy(handle)
+    d, w, a = np.ones(N), np.zeros(N), np.ones(N)
+    d[pr.depth_obs], w[pr.depth_obs], a[pr.depth_obs] = pr.depth_d, pr.depth_w, pr.depth_a
+    obs_xy = np.ascontiguousarray(pr.obs_xy, dtype=np.float64)
+    vals = {}
+    for order in ("pm", "cm"):
+        xy, dep = np.empty((N, 2)), np.empty((3, N))
+        rc = lib.mpba_host_gather(N, idx[order + "_src"].ctypes.data, obs_xy.ctypes.data, d.ctypes.data, w.ctypes.data,
+                                  a.ctypes.data, xy.ctypes.data, dep.ctypes.data)
+        if rc != 0:
+            raise EngineError(f"mpba_host_gather failed with code {rc}")
+        vals[order] = (xy, dep)
+    pose = np.zeros((Cn, 8))
+    pose[:, :4], pose[:, 4:7] = pr.img_q, pr.img_t
+    xyz = np.zeros((P, 4))
+    xyz[:, :3] = pr.pt_xyz
+    params = np.zeros((K, MAX_CAMERA_PARAMS))
+    params[:, : pr.cam_params.shape[1]] = pr.cam_params
+    return HostLayout(
+        C=Cn, K=K, P=P, N=N,
+        img_pose=pose, img_camera=pr.img_camera, img_free_mask=pr.img_free_mask,
+        img_shift_scale=np.ascontiguousarray(pr.shift_scale), cam_model=pr.cam_model, cam_params=params,
+        pt_xyz=xyz, pt_const=pr.pt_const,
+        pm_xy=vals["pm"][0], pm_depth=vals["pm"][1], cm_xy=vals["cm"][0], cm_depth=vals["cm"][1],
+        reproj_loss=int(pr.reproj_loss), depth_loss=int(pr.depth_loss),
+        reproj_loss_scale=float(pr.reproj_loss_scale), reproj_loss_weight=float(pr.reproj_loss_weight),
+        flags=FLAG_STRUCTURE_ONLY if structure_only else 0, **idx)
+
+
+def build_layout_numpy(problem: BundleProblem) -> HostLayout:
+    """The same layout stated in numpy (general sorts): the checker of the native builder."""
     pr = problem.normalized()
     pr.validate()
     Cn, P, N = pr.num_images, pr.num_points, pr.num_obs

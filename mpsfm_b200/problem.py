@@ -185,7 +185,7 @@ class BundleProblem:
         if nd:
             if self.depth_obs.min() < 0 or self.depth_obs.max() >= N:
                 raise ValueError("depth_obs out of range")
-            if np.unique(self.depth_obs).size != nd:
+            if int(np.bincount(self.depth_obs, minlength=N).max()) > 1:
                 raise ValueError("at most one depth prior per observation")
             if not np.all(self.depth_d > 0):
                 raise ValueError("depth priors must be > 0 (bundle_adjustment.py:139)")
