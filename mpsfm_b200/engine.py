@@ -236,6 +236,7 @@ class HostLayout:
     reproj_loss_scale: float
     reproj_loss_weight: float
     flags: int
+    cm_pm: Optional[np.ndarray] = None  # [N] track-order slot of every image-order slot (unsharded layouts)
 
     @property
     def num_blocks(self) -> int:
@@ -307,7 +308,7 @@ def build_layout(problem: BundleProblem) -> HostLayout:
 
         B, U = view.num_blocks, view.num_upper
         idx = {name: take(name, n) for name, n in (
-            ("pt_ptr", P + 1), ("pm_img", N), ("pm_src", N), ("img_ptr", Cn + 1), ("cm_pt", N), ("cm_src", N),
+            ("pt_ptr", P + 1), ("pm_img", N), ("pm_src", N), ("img_ptr", Cn + 1), ("cm_pt", N), ("cm_src", N), ("cm_pm", N),
             ("chunk_img", view.num_chunks), ("chunk_begin", view.num_chunks), ("chunk_end", view.num_chunks),
             ("img_chunk_ptr", Cn + 1), ("s_row_ptr", Cn + 1), ("s_col", B), ("s_diag", Cn), ("s_transpose", B),
             ("s_row", B), ("u_block", U), ("u_item_ptr", U + 1), ("item_a", view.num_items),
@@ -437,8 +438,11 @@ def build_layout_numpy(problem: BundleProblem) -> HostLayout:
     xyz[:, :3] = pr.pt_xyz
     params = np.zeros((K, MAX_CAMERA_PARAMS))
     params[:, : pr.cam_params.shape[1]] = pr.cam_params
+    pm_pos = np.empty(N, dtype=np.int32)
+    pm_pos[pm_src] = np.arange(N, dtype=np.int32)
 
     return HostLayout(
+        cm_pm=pm_pos[cm_src],
         C=Cn, K=K, P=P, N=N,
         img_pose=pose, img_camera=pr.img_camera, img_free_mask=pr.img_free_mask,
         img_shift_scale=np.ascontiguousarray(pr.shift_scale), cam_model=pr.cam_model, cam_params=params,
@@ -529,7 +533,7 @@ def shard_layout(lay: HostLayout, rank: int, world: int):
         chunk_begin=(lay.chunk_begin[ch0:ch1].astype(np.int64) - c0).astype(np.int32),
         chunk_end=(lay.chunk_end[ch0:ch1].astype(np.int64) - c0).astype(np.int32),
         img_chunk_ptr=np.clip(lay.img_chunk_ptr.astype(np.int64) - ch0, 0, ch1 - ch0).astype(np.int32),
-        u_item_ptr=u_item_ptr, item_a=item_a, item_b=item_b,
+        u_item_ptr=u_item_ptr, item_a=item_a, item_b=item_b, cm_pm=None,
     )
     out.track_warp_first = pack_tracks(out.pt_ptr, spec.pt_begin, spec.pt_end)
     return out, spec
@@ -615,9 +619,13 @@ class BundleAdjuster:
                 self.buf[name] = t.to(self.device, non_blocking=pinned)
                 self.h2d_bytes += arr.nbytes
             if self._derive_cm:
-                pm_pos = np.empty(lay.N, dtype=np.int32)
-                pm_pos[lay.pm_src] = np.arange(lay.N, dtype=np.int32)
-                self.host["cm_pm"] = torch.from_numpy(np.ascontiguousarray(pm_pos[lay.cm_src])).pin_memory()
+                if lay.cm_pm is not None:
+                    cm_pm = lay.cm_pm
+                else:
+                    pm_pos = np.empty(lay.N, dtype=np.int32)
+                    pm_pos[lay.pm_src] = np.arange(lay.N, dtype=np.int32)
+                    cm_pm = pm_pos[lay.cm_src]
+                self.host["cm_pm"] = torch.from_numpy(np.ascontiguousarray(cm_pm, dtype=np.int32)).pin_memory()
                 self.buf["cm_pm"] = self.host["cm_pm"].to(self.device, non_blocking=True)
             if pinned:
                 self._pose_host = torch.empty((lay.C, 8), dtype=torch.float64).pin_memory()
