@@ -278,7 +278,9 @@ def run_gpu(args):
     ba.close()
     del ba
     ba2 = engine.BundleAdjuster(prob, device=local, layout=full, pinned=True, shard=shard)
-    ba2.solve(opt)  # warm-up of the new handle (communicator, plans)
+    ba2.upload()
+    ba2.solve(opt)  # warm-up of the new handle (communicator, plans), of the staging copies and the read-back
+    ba2.state()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
