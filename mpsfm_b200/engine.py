@@ -17,6 +17,7 @@ Layout built here:
 
 from __future__ import annotations
 
+import atexit
 import ctypes as C
 import dataclasses
 import os
@@ -579,6 +580,23 @@ class SolveSummary:
                 f"{self.final_cost:.6e}, termination {self.termination} ({self.message})")
 
 
+# handles of closed (unsharded) BundleAdjusters, per device: a mapper solves hundreds of bundles one after the other,
+# and a handle (pinned scalar block, events, pinned plan staging) carries no per-problem state
+_FREE_HANDLES = {}
+
+
+def _release_handles():
+    lib = _lib
+    for handles in _FREE_HANDLES.values():
+        while handles:
+            h = handles.pop()
+            if lib is not None:
+                lib.mpba_destroy(h)
+
+
+atexit.register(_release_handles)
+
+
 class BundleAdjuster:
     """One problem resident on one GPU: buffers (torch), handle and workspace.
 
@@ -633,10 +651,14 @@ class BundleAdjuster:
             for name in ("item_a", "item_b", "chunk_img", "chunk_begin", "chunk_end"):
                 if self.buf[name].numel() == 0:
                     self.buf[name] = torch.zeros(1, dtype=torch.int32, device=self.device)
-            self.handle = C.c_void_p()
-            rc = self.lib.mpba_create(C.byref(self.handle), device, None)
-            if rc != 0:
-                raise EngineUnavailable(f"mpba_create failed with code {rc} (no usable CUDA device {device})")
+            free = _FREE_HANDLES.setdefault(int(device), [])
+            if free and self.shard is None:
+                self.handle = free.pop()
+            else:
+                self.handle = C.c_void_p()
+                rc = self.lib.mpba_create(C.byref(self.handle), device, None)
+                if rc != 0:
+                    raise EngineUnavailable(f"mpba_create failed with code {rc} (no usable CUDA device {device})")
             self.prob = MpbaProblem()
             self.prob.num_images, self.prob.num_cameras = lay.C, lay.K
             self.prob.num_points, self.prob.num_obs = lay.P, lay.N
@@ -689,7 +711,11 @@ class BundleAdjuster:
 
     def close(self):
         if getattr(self, "handle", None) is not None and self.handle.value:
-            self.lib.mpba_destroy(self.handle)
+            free = _FREE_HANDLES.setdefault(int(self.device.index), [])
+            if self.shard is None and len(free) < 4:
+                free.append(self.handle)  # reused by the next BundleAdjuster on this device
+            else:
+                self.lib.mpba_destroy(self.handle)
             self.handle = C.c_void_p()
 
     def __del__(self):
