@@ -1028,7 +1028,7 @@ struct PcgArgs {
   double* tpart;               // [gridDim.x][8] per-CTA Z^T r of its rows (one group per CTA)
 };
 
-constexpr int PCG_THREADS = 256;
+constexpr int PCG_THREADS = 512;  // 16 warps: one block row per warp and round, ~2 rounds at 5 000 images
 constexpr int PCG_MAX_NC = COARSE_MAX_DIM;
 
 __device__ __forceinline__ double grid_reduce(double part, double* slots, unsigned* bar, unsigned& gen, double* sm) {
@@ -1064,12 +1064,13 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
   const int nrows = row1 - row0;
   const int blk_base = A.row_ptr[row0];
   const int nblk = A.row_ptr[row1] - blk_base;
-  // shared memory carve: Minv | x | r | q | rowptr | [S | col]
+  // shared memory carve: Minv | x | r | q | p | rowptr | [S | col]
   double* s_minv = s_dyn;
   double* s_x = s_minv + (size_t)A.rows_per_cta * 36;
   double* s_r = s_x + (size_t)A.rows_per_cta * 6;
   double* s_q = s_r + (size_t)A.rows_per_cta * 6;
-  int* s_rowptr = reinterpret_cast<int*>(s_q + (size_t)A.rows_per_cta * 6);
+  double* s_p = s_q + (size_t)A.rows_per_cta * 6;
+  int* s_rowptr = reinterpret_cast<int*>(s_p + (size_t)A.rows_per_cta * 6);
   double* s_S = reinterpret_cast<double*>(s_rowptr + ((A.rows_per_cta + 2) & ~1));
   int* s_col = reinterpret_cast<int*>(s_S + (SMEM ? (size_t)A.max_local_blocks * 36 : 0));
 
@@ -1121,17 +1122,43 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
       // CTAs of group g: those whose first row lies in [grp_row_ptr[g], grp_row_ptr[g+1])
       const int c0 = (A.grp_row_ptr[g] + A.rows_per_cta - 1) / A.rows_per_cta;
       const int c1 = min((int)gridDim.x, (A.grp_row_ptr[g + 1] + A.rows_per_cta - 1) / A.rows_per_cta);
-      double t = 0.0;
-      for (int cta = c0; cta < c1; ++cta) t += __ldcg(A.tpart + (size_t)cta * 8 + m);
-      s_t[k] = t;
+      double t = 0.0, t1 = 0.0;  // fixed order, two loads in flight
+      int cta = c0;
+      for (; cta + 1 < c1; cta += 2) {
+        t += __ldcg(A.tpart + (size_t)cta * 8 + m);
+        t1 += __ldcg(A.tpart + (size_t)(cta + 1) * 8 + m);
+      }
+      if (cta < c1) t += __ldcg(A.tpart + (size_t)cta * 8 + m);
+      s_t[k] = t + t1;
     }
     __syncthreads();
+    // e = A^-1 t: the warps split the outputs, the lanes split k along a ROW of the symmetric matrix (coalesced),
+    // eight outputs' loads in flight per lane -- A^-1 comes from L2 (shared memory is full of S)
     double te = 0.0;
-    for (int j = threadIdx.x; j < nc; j += PCG_THREADS) {
-      double e = 0.0;
-      for (int k = 0; k < nc; ++k) e += __ldg(A.Ainv + (size_t)k * nc + j) * s_t[k];  // symmetric: column j = row j
-      s_e[j] = e;
-      te += s_t[j] * e;
+    constexpr int KQ = (PCG_MAX_NC + 31) / 32;
+    for (int j0 = warp * 8; j0 < nc; j0 += WPB * 8) {
+      double acc[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        acc[u] = 0.0;
+        const int j = j0 + u;
+#pragma unroll
+        for (int q = 0; q < KQ; ++q) {
+          const int k = lane + 32 * q;
+          if (j < nc && k < nc) acc[u] += __ldg(A.Ainv + (size_t)j * nc + k) * s_t[k];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        double v = acc[u];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(FULL, v, off);
+        const int j = j0 + u;
+        if (lane == 0 && j < nc) {
+          s_e[j] = v;
+          te += s_t[j] * v;
+        }
+      }
     }
     te = block_sum<PCG_THREADS / 32>(te, s_te);
     return te;
@@ -1224,6 +1251,7 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
           const double qv = acc + a1 + a2 + a3 + a4;
           const double pi = __ldcg(A.z + o) + beta * __ldcg(pold + o);
           __stcg(pnew + o, pi);
+          s_p[lr * 6 + lane] = pi;
           s_q[lr * 6 + lane] = qv;
           part += pi * qv;
         }
@@ -1243,8 +1271,7 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
         const int row = row0 + lr;
         double rr = 0.0;
         if (lane < 6) {
-          const size_t o = (size_t)row * 6 + lane;
-          s_x[lr * 6 + lane] += alpha * __ldcg(pnew + o);
+          s_x[lr * 6 + lane] += alpha * s_p[lr * 6 + lane];
           rr = s_r[lr * 6 + lane] - alpha * s_q[lr * 6 + lane];
           s_r[lr * 6 + lane] = rr;
         }
@@ -1670,14 +1697,13 @@ PcgPlan pcg_plan(int device, int C, int max_row_blocks) {
     cudaFuncSetAttribute(k_pcg<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 4096);
   }
   PcgPlan pl;
-  const int wpb = PCG_THREADS / 32;
-  int grid = (C + wpb - 1) / wpb;  // at least one block row per warp
+  int grid = (C + 7) / 8;          // at least eight block rows per CTA
   if (grid > sms) grid = sms;      // one CTA per SM: co-residency for the grid barrier
   if (grid < 1) grid = 1;
   pl.rows_per_cta = (C + grid - 1) / grid;
   pl.grid = (C + pl.rows_per_cta - 1) / pl.rows_per_cta;
   const size_t rows = (size_t)pl.rows_per_cta;
-  const size_t base = rows * (36 + 18) * sizeof(double) + ((rows + 2) & ~(size_t)1) * sizeof(int);
+  const size_t base = rows * (36 + 24) * sizeof(double) + ((rows + 2) & ~(size_t)1) * sizeof(int);
   pl.max_local_blocks = (int)(rows * (size_t)(max_row_blocks > 0 ? max_row_blocks : 1 << 16));
   const size_t with_s = base + (size_t)pl.max_local_blocks * (36 * sizeof(double) + sizeof(int)) + 16;
   pl.use_smem = (max_row_blocks > 0 && with_s <= (size_t)(smem_optin - 4096)) ? 1 : 0;
