@@ -1096,12 +1096,15 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
   // every CTA forms t = Z^T r (all groups, fixed order), e = A^-1 t (redundantly: nc^2 multiply-adds), and
   //     r'z = r'M^-1 r + t'e,        z_i = (M^-1 r)_i + Z_i e_g      for its own rows,
   // publishes z and meets the others at one more barrier before the next product.
-  __shared__ double s_t[PCG_MAX_NC], s_e[PCG_MAX_NC], s_tw[PCG_THREADS / 32][8], s_te[PCG_THREADS / 32 + 1];
+  __shared__ double s_t[PCG_MAX_NC], s_e[PCG_MAX_NC], s_tw[PCG_THREADS / 32][8];
+  __shared__ double s_ainv[7 * PCG_MAX_NC];  // the own group's seven rows of (Z^T S Z)^-1
   const bool coarse = A.G > 0;
   int my_group = 0;
   if (coarse)
     for (int g = 0; g < A.G; ++g)
       if (row0 >= A.grp_row_ptr[g]) my_group = g;
+  if (coarse)
+    for (int k = threadIdx.x; k < 7 * A.nc; k += PCG_THREADS) s_ainv[k] = A.Ainv[(size_t)my_group * 7 * A.nc + k];
   double* s_zj = s_q;  // M^-1 r of the own rows lives in the q rows between the update and the coarse step
   // per-CTA Z^T r: lanes 0..6 of every warp accumulate over the warp's rows, warps folded in order
   auto coarse_publish_t = [&](const double (&tacc)[1]) {
@@ -1114,7 +1117,7 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
       __stcg(A.tpart + (size_t)blockIdx.x * 8 + threadIdx.x, t);
     }
   };
-  // after the barrier: t, e, t'e; returns t'e (same value in every thread of every CTA)
+  // after the exchange: t (all groups), e of the own group; returns this CTA's share of t'e (thread 0 only)
   auto coarse_solve = [&]() -> double {
     const int nc = A.nc;
     for (int k = threadIdx.x; k < nc; k += PCG_THREADS) {
@@ -1132,35 +1135,21 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
       s_t[k] = t + t1;
     }
     __syncthreads();
-    // e = A^-1 t: the warps split the outputs, the lanes split k along a ROW of the symmetric matrix (coalesced),
-    // eight outputs' loads in flight per lane -- A^-1 comes from L2 (shared memory is full of S)
-    double te = 0.0;
-    constexpr int KQ = (PCG_MAX_NC + 31) / 32;
-    for (int j0 = warp * 8; j0 < nc; j0 += WPB * 8) {
-      double acc[8];
+    // e_g = rows of A^-1 of the OWN group (shared memory) times t: warp m forms e_g[m], lanes split k
+    if (warp < 7) {
+      double acc = 0.0;
+      for (int k = lane; k < nc; k += 32) acc += s_ainv[warp * nc + k] * s_t[k];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        acc[u] = 0.0;
-        const int j = j0 + u;
-#pragma unroll
-        for (int q = 0; q < KQ; ++q) {
-          const int k = lane + 32 * q;
-          if (j < nc && k < nc) acc[u] += __ldg(A.Ainv + (size_t)j * nc + k) * s_t[k];
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        double v = acc[u];
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(FULL, v, off);
-        const int j = j0 + u;
-        if (lane == 0 && j < nc) {
-          s_e[j] = v;
-          te += s_t[j] * v;
-        }
-      }
+      for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(FULL, acc, off);
+      if (lane == 0) s_e[my_group * 7 + warp] = acc;
     }
-    te = block_sum<PCG_THREADS / 32>(te, s_te);
+    __syncthreads();
+    // this group's share of t'e, counted once (by the group's first CTA); the sum rides on the next exchange
+    double te = 0.0;
+    if (threadIdx.x == 0 && row0 == A.grp_row_ptr[my_group]) {
+#pragma unroll
+      for (int m = 0; m < 7; ++m) te += s_t[my_group * 7 + m] * s_e[my_group * 7 + m];
+    }
     return te;
   };
   // z_i = zj_i + Z_i e_g for the own rows, published for the other CTAs' products
@@ -1211,9 +1200,9 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
   }
   double rz0 = grid_reduce(part, part1, A.bar, gen, sm);
   if (coarse) {
-    rz0 += coarse_solve();
+    const double te0 = coarse_solve();
     coarse_apply_z();
-    (void)grid_reduce(0.0, part0, A.bar, gen, sm);  // z of every CTA is visible
+    rz0 += grid_reduce(te0, part0, A.bar, gen, sm);  // z of every CTA is visible; t'e summed over the groups
   }
   double rz = rz0, beta = 0.0;
   int iters = 0, flag = 1;
@@ -1301,7 +1290,11 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
       }
       const long long c3 = clock64();
       double rz_new = grid_reduce(part, part1, A.bar, gen, sm);
-      if (coarse) rz_new += coarse_solve();
+      if (coarse) {  // r'z = r'M^-1 r + t'e: the second term arrives with the exchange that publishes z
+        const double te_part = coarse_solve();
+        coarse_apply_z();
+        rz_new += grid_reduce(te_part, part0, A.bar, gen, sm);
+      }
       const long long c4 = clock64();
       t_spmv += c1 - c0;
       t_upd += c3 - c2;
@@ -1315,10 +1308,6 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
       if (res <= A.tol) {
         flag = 0;
         break;
-      }
-      if (coarse) {
-        coarse_apply_z();
-        (void)grid_reduce(0.0, part0, A.bar, gen, sm);  // z of every CTA is visible
       }
       beta = rz_new / rz;
       rz = rz_new;
@@ -1693,8 +1682,8 @@ PcgPlan pcg_plan(int device, int C, int max_row_blocks) {
   if (!sms) {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
-    cudaFuncSetAttribute(k_pcg<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 4096);
-    cudaFuncSetAttribute(k_pcg<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 4096);
+    cudaFuncSetAttribute(k_pcg<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 12288);
+    cudaFuncSetAttribute(k_pcg<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 12288);
   }
   PcgPlan pl;
   int grid = (C + 7) / 8;          // at least eight block rows per CTA
@@ -1706,7 +1695,7 @@ PcgPlan pcg_plan(int device, int C, int max_row_blocks) {
   const size_t base = rows * (36 + 24) * sizeof(double) + ((rows + 2) & ~(size_t)1) * sizeof(int);
   pl.max_local_blocks = (int)(rows * (size_t)(max_row_blocks > 0 ? max_row_blocks : 1 << 16));
   const size_t with_s = base + (size_t)pl.max_local_blocks * (36 * sizeof(double) + sizeof(int)) + 16;
-  pl.use_smem = (max_row_blocks > 0 && with_s <= (size_t)(smem_optin - 4096)) ? 1 : 0;
+  pl.use_smem = (max_row_blocks > 0 && with_s <= (size_t)(smem_optin - 12288)) ? 1 : 0;
   pl.smem_bytes = pl.use_smem ? with_s : base + 16;
   return pl;
 }
