@@ -389,4 +389,11 @@ def main():
 
 
 if __name__ == "__main__":
+    # stdout carries the ONE JSON line and nothing else: libraries that print to file descriptor 1 (NCCL's version
+    # banner under NCCL_DEBUG, for one) are sent to stderr for the whole run
+    sys.stdout.flush()
+    _json_fd = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(_json_fd, "w", buffering=1)
     main()
+    sys.stdout.flush()
