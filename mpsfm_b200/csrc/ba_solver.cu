@@ -59,6 +59,11 @@ struct mpba_handle {
 
 namespace {
 
+// Coarse groups of the two-level preconditioner: beyond 18 groups (126 modes) the dense inverse of the coarse matrix
+// moves from one CTA to a four-CTA cluster (one cluster barrier per pivot, ~270 us for 224 modes), which only pays
+// when the PCG iterations it saves are many: large systems.
+int coarse_max_groups(int num_images) { return num_images >= 600 ? COARSE_MAX_GROUPS : 18; }
+
 int fail(mpba_handle* h, int code, const std::string& msg) {
   if (h) h->err = msg;
   return code;
@@ -455,7 +460,7 @@ int build_pcg_cluster_plan(Ctx& c, const mpba_problem* prob, int pcg_kernel, int
     // coarse space: gpc groups of consecutive images per CTA, at least two images per group
     int min_rows = C;
     for (int k = 0; k < cl; ++k) min_rows = std::min(min_rows, crow[k + 1] - crow[k]);
-    int gpc = (pcg_coarse == 1 || C < 8) ? 0 : std::min(COARSE_MAX_GROUPS / cl, std::max(min_rows / 2, 0));
+    int gpc = (pcg_coarse == 1 || C < 8) ? 0 : std::min(coarse_max_groups(C) / cl, std::max(min_rows / 2, 0));
     size_t smem = 0;
     for (;; --gpc) {
       a.gpc = gpc > 0 ? gpc : 0;
@@ -546,7 +551,7 @@ int build_grid_coarse_plan(Ctx& c, const mpba_problem* prob, int pcg_coarse) {
   if (c.structure_only || c.cl > 0 || pcg_coarse == 1) return MPBA_OK;
   const int C = prob->num_images, B = prob->num_blocks;
   const PcgPlan pl = pcg_plan(h->device, C, c.max_row_blocks);
-  const int G = std::min(COARSE_MAX_GROUPS, pl.grid);
+  const int G = std::min(coarse_max_groups(C), pl.grid);
   if (G < 2 || pl.grid > 1024) return MPBA_OK;
   std::vector<int32_t> rp(C + 1), col(B);
   CU(cudaMemcpyAsync(rp.data(), prob->s_row_ptr, (C + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));

@@ -14,7 +14,11 @@
 // Three small kernels per linear solve:  k_coarse_modes (Z_i, 6x7 per image),  k_coarse_assemble (A_c = Z^T S Z,
 // one CTA per coarse block, fixed summation order),  k_coarse_invert (dense in-place Gauss-Jordan in shared memory,
 // one CTA; a vanishing pivot drops that mode instead of failing).  The application lives in pcg_cluster.cu.
+#include <cooperative_groups.h>
+
 #include "ba_kernels.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace mpba {
 
@@ -107,7 +111,8 @@ __global__ void __launch_bounds__(64 * CA_SLICES) k_coarse_assemble(int G, const
 // (dependent mode: a group with fewer free coordinates than modes) is dropped: its row and column of the
 // inverse are zero.  The reciprocal is a float seed + two Newton steps (this is a preconditioner).  The result
 // is symmetrised on the way out.
-constexpr int GJ_Q = (COARSE_MAX_DIM + 31) / 32;
+constexpr int GJ_SINGLE_MAX = 128;  // largest system the one-CTA kernel holds (4 x 4 register tile per thread)
+constexpr int GJ_Q = GJ_SINGLE_MAX / 32;
 __device__ __forceinline__ double fast_rcp(double a) {
   double x = (double)(1.0f / (float)a);
   x = x * (2.0 - a * x);
@@ -195,6 +200,101 @@ __global__ void __launch_bounds__(1024) k_coarse_invert(int n, const double* __r
     for (int j = lane; j < n; j += 32) Ainv[(size_t)i * n + j] = 0.5 * (T[(size_t)i * ld + j] + T[(size_t)j * ld + i]);
 }
 
+// The same elimination for 128 < n <= 224 on a CLUSTER of four CTAs: CTA r owns the row slots {2r, 2r+1} (rows
+// w + 32 (2r + qi)), 2 x 7 entries per thread, so every warp still holds whole rows and the pivot column is a
+// shuffle.  The owner of pivot row p scales it and stores it into the double-buffered row of ALL four CTAs through
+// distributed shared memory; one cluster barrier per pivot.  The raw inverse goes to global memory and
+// k_coarse_symmetrize averages it with its transpose.
+constexpr int GJC_CTAS = 4, GJC_QR = 2, GJC_QC = 7;
+static_assert(GJC_CTAS * GJC_QR * 32 >= COARSE_MAX_DIM && GJC_QC * 32 >= COARSE_MAX_DIM, "cluster inverse too small");
+__global__ void __cluster_dims__(GJC_CTAS, 1, 1) __launch_bounds__(1024)
+    k_coarse_invert_cluster(int n, const double* Ac_part, double* raw) {  // raw may alias Ac_part (see the launcher)
+  __shared__ double prow[2][32 * GJC_QC];
+  __shared__ double s_inv[2];
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = (int)cluster.block_rank();
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double a[GJC_QR][GJC_QC], d0[GJC_QR];
+#pragma unroll
+  for (int qi = 0; qi < GJC_QR; ++qi)
+#pragma unroll
+    for (int qj = 0; qj < GJC_QC; ++qj) {
+      const int i = warp + 32 * (rank * GJC_QR + qi), j = lane + 32 * qj;
+      double v = 0.0;
+      if (i < n && j < n) {
+#pragma unroll
+        for (int sp = 0; sp < COARSE_SPLIT; ++sp) v += Ac_part[(size_t)sp * n * n + (size_t)i * n + j];
+      }
+      a[qi][qj] = v;
+    }
+#pragma unroll
+  for (int qi = 0; qi < GJC_QR; ++qi) {  // original diagonal of the owned rows: threshold of the pivot test
+    const int i = warp + 32 * (rank * GJC_QR + qi);
+    double dv = 0.0;
+#pragma unroll
+    for (int qj = 0; qj < GJC_QC; ++qj)
+      if (lane + 32 * qj == i) dv = a[qi][qj];
+    d0[qi] = __shfl_sync(0xffffffffu, dv, i & 31);
+  }
+  cluster.sync();  // every CTA has read its inputs (raw may alias them) and is resident
+#pragma unroll
+  for (int PQ = 0; PQ < GJC_QC; ++PQ) {
+    const int owner = PQ / GJC_QR;
+    const int lq = PQ % GJC_QR;  // compile-time after unrolling
+    for (int pw = 0; pw < 32; ++pw) {
+      const int p = 32 * PQ + pw;
+      if (p >= n) break;
+      const bool mine = rank == owner && warp == pw;
+      if (mine) {  // owner of row p: scale it and deliver it to the four CTAs
+        const double piv = __shfl_sync(0xffffffffu, a[lq][PQ], pw);
+        const double dp = d0[lq];
+        const double inv = (piv > 1e-13 * dp && dp > 0.0) ? fast_rcp(piv) : 0.0;
+#pragma unroll 1
+        for (int r = 0; r < GJC_CTAS; ++r) {  // (not unrolled: four sets of remote addresses would be kept live)
+          double* dst = cluster.map_shared_rank(&prow[p & 1][0], r);
+#pragma unroll
+          for (int qj = 0; qj < GJC_QC; ++qj) dst[lane + 32 * qj] = a[lq][qj] * inv;
+          if (lane == 0) *cluster.map_shared_rank(&s_inv[p & 1], r) = inv;
+        }
+      }
+      double f[GJC_QR];
+#pragma unroll
+      for (int qi = 0; qi < GJC_QR; ++qi) f[qi] = __shfl_sync(0xffffffffu, a[qi][PQ], pw);  // column p of my rows
+      if (mine) f[lq] = 0.0;  // row p itself is replaced below
+      cluster.sync();
+      const double inv = s_inv[p & 1];
+      const double* rp = &prow[p & 1][lane];  // read where used: 2 x 7 entries per thread leave no room for a copy
+#pragma unroll
+      for (int qj = 0; qj < GJC_QC; ++qj) {
+        const double r = rp[32 * qj];
+#pragma unroll
+        for (int qi = 0; qi < GJC_QR; ++qi) a[qi][qj] -= f[qi] * r;
+        if (mine) a[lq][qj] = r;  // row p: the scaled pivot row
+      }
+      if (lane == pw) {  // column p: -f / pivot, 1 / pivot on the diagonal
+#pragma unroll
+        for (int qi = 0; qi < GJC_QR; ++qi) a[qi][PQ] = -f[qi] * inv;
+        if (mine) a[lq][PQ] = inv;
+      }
+    }
+  }
+  cluster.sync();  // nobody leaves while a peer may still write its shared memory
+#pragma unroll
+  for (int qi = 0; qi < GJC_QR; ++qi)
+#pragma unroll
+    for (int qj = 0; qj < GJC_QC; ++qj) {
+      const int i = warp + 32 * (rank * GJC_QR + qi), j = lane + 32 * qj;
+      if (i < n && j < n) raw[(size_t)i * n + j] = a[qi][qj];
+    }
+}
+
+__global__ void __launch_bounds__(256) k_coarse_symmetrize(int n, const double* __restrict__ raw, double* __restrict__ Ainv) {
+  const int k = blockIdx.x * 256 + threadIdx.x;
+  if (k >= n * n) return;
+  const int i = k / n, j = k - i * n;
+  Ainv[k] = 0.5 * (raw[k] + raw[(size_t)j * n + i]);
+}
+
 }  // namespace
 
 size_t coarse_invert_smem_bytes(int n) { return (size_t)n * (n | 1) * sizeof(double); }
@@ -205,13 +305,19 @@ cudaError_t launch_coarse_setup(const CoarsePlan& cp, int C, const double* pose,
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_coarse_invert, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)coarse_invert_smem_bytes(COARSE_MAX_DIM));
+                         (int)coarse_invert_smem_bytes(GJ_SINGLE_MAX));
     attr_set = true;
   }
   const int n = 7 * cp.G;
   k_coarse_modes<<<(C + 127) / 128, 128, 0, st>>>(C, pose, free_mask, Zc);
   k_coarse_assemble<<<dim3(cp.G * cp.G, COARSE_SPLIT), 64 * CA_SLICES, 0, st>>>(cp.G, cp.cb_ptr, cp.cb_fine, s_row, s_col, S, Zc, Ac);
-  k_coarse_invert<<<1, 1024, coarse_invert_smem_bytes(n), st>>>(n, Ac, Ainv);
+  if (n <= GJ_SINGLE_MAX) {
+    k_coarse_invert<<<1, 1024, coarse_invert_smem_bytes(n), st>>>(n, Ac, Ainv);
+  } else {
+    // the partial matrices are read into registers before the first cluster barrier: slice 0 is reused for the raw inverse
+    k_coarse_invert_cluster<<<GJC_CTAS, 1024, 0, st>>>(n, Ac, Ac);
+    k_coarse_symmetrize<<<(n * n + 255) / 256, 256, 0, st>>>(n, Ac, Ainv);
+  }
   return cudaGetLastError();
 }
 
