@@ -180,7 +180,7 @@ bool pcg_cluster_fits(int device, int cl, size_t smem_bytes);
 cudaError_t launch_pcg_cluster(const PcgClusterArgs& a, int cl, size_t smem_bytes, cudaStream_t st);
 
 // coarse space of the two-level preconditioner (coarse.cu)
-constexpr int COARSE_MAX_GROUPS = 32;  // 7 * 18 = 126 <= 128: a 4 x 4 register tile per thread in k_coarse_invert
+constexpr int COARSE_MAX_GROUPS = 32;  // 7 * 32 = 224 modes: 7 column slots of 32 lanes in k_coarse_invert_cluster (<= 18 groups: one CTA)
 constexpr int COARSE_MAX_DIM = 7 * COARSE_MAX_GROUPS;
 constexpr int COARSE_SPLIT = 8;  // partial coarse matrices of k_coarse_assemble, added in order by k_coarse_invert  // the dense inverse is formed by one CTA in shared memory
 struct CoarsePlan {

@@ -12,8 +12,8 @@
 // 16 groups, 100 images 149 -> 31.
 //
 // Three small kernels per linear solve:  k_coarse_modes (Z_i, 6x7 per image),  k_coarse_assemble (A_c = Z^T S Z,
-// one CTA per coarse block, fixed summation order),  k_coarse_invert (dense in-place Gauss-Jordan in shared memory,
-// one CTA; a vanishing pivot drops that mode instead of failing).  The application lives in pcg_cluster.cu.
+// one CTA per coarse block, fixed summation order),  k_coarse_invert (dense in-place Gauss-Jordan in registers,
+// one CTA up to 128 modes, a four-CTA cluster up to 224; a vanishing pivot drops that mode instead of failing).  The application lives in pcg_cluster.cu.
 #include <cooperative_groups.h>
 
 #include "ba_kernels.cuh"
