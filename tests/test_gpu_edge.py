@@ -94,3 +94,24 @@ def test_upload_derives_the_image_order_arrays_on_the_device():
     assert summ.num_iterations == ref.num_iterations and summ.final_cost == ref.final_cost
     for a, b in zip(ba.state(), plain.state()):
         assert np.array_equal(a, b)
+
+
+def test_large_coarse_space_cluster_inverse_matches_block_jacobi_and_oracle():
+    """>= 600 images: 32 coarse groups (224 modes), the coarse matrix is inverted by the four-CTA cluster kernel.
+    Both PCG kernels with that preconditioner must land on the block-Jacobi-only solve and on the exact-solve
+    oracle (same LM iteration count, cost <= 1e-6, poses <= 1e-6)."""
+    prob = make_scene(640, 6000, 4, seed=3)
+    osum = lm.solve(prob)
+    results = {}
+    for name, kw in (("cluster", dict(pcg_kernel=0, pcg_coarse=0)), ("grid", dict(pcg_kernel=1, pcg_coarse=0)),
+                     ("jacobi", dict(pcg_kernel=0, pcg_coarse=1))):
+        ba = engine.BundleAdjuster(prob, device=0)
+        summ = ba.solve(engine.default_options(pcg_max_iterations=6000, **kw))
+        results[name] = (summ, ba.state())
+        ba.close()
+        assert summ.num_iterations == len(osum.iterations) - 1, name
+        assert abs(summ.final_cost - osum.final_cost) <= 1e-6 * osum.final_cost, name
+        assert np.max(np.abs(results[name][1][1] - osum.state.t)) < 1e-6, name
+    # the coarse space is what it is for: far fewer PCG iterations than block-Jacobi alone
+    assert results["cluster"][0].total_pcg_iterations < 0.5 * results["jacobi"][0].total_pcg_iterations
+    assert results["grid"][0].total_pcg_iterations < 0.5 * results["jacobi"][0].total_pcg_iterations
