@@ -202,15 +202,15 @@ __global__ void __launch_bounds__(1024) k_coarse_invert(int n, const double* __r
 
 // The same elimination for 128 < n <= 224 on a CLUSTER of four CTAs: CTA r owns the row slots {2r, 2r+1} (rows
 // w + 32 (2r + qi)), 2 x 7 entries per thread, so every warp still holds whole rows and the pivot column is a
-// shuffle.  The owner of pivot row p scales it and stores it into the double-buffered row of ALL four CTAs through
-// distributed shared memory; one cluster barrier per pivot.  The raw inverse goes to global memory and
+// shuffle.  The owner of a pivot row scales it and stores it into the double-buffered rows of ALL four CTAs through
+// distributed shared memory; pivots go in pairs, one cluster barrier per pair.  The raw inverse goes to global memory and
 // k_coarse_symmetrize averages it with its transpose.
 constexpr int GJC_CTAS = 4, GJC_QR = 2, GJC_QC = 7;
 static_assert(GJC_CTAS * GJC_QR * 32 >= COARSE_MAX_DIM && GJC_QC * 32 >= COARSE_MAX_DIM, "cluster inverse too small");
 __global__ void __cluster_dims__(GJC_CTAS, 1, 1) __launch_bounds__(1024)
     k_coarse_invert_cluster(int n, const double* Ac_part, double* raw) {  // raw may alias Ac_part (see the launcher)
-  __shared__ double prow[2][32 * GJC_QC];
-  __shared__ double s_inv[2];
+  __shared__ double prow[2][2][32 * GJC_QC];  // [buffer][pivot of the pair][column]
+  __shared__ double s_inv[2][2];
   cg::cluster_group cluster = cg::this_cluster();
   const int rank = (int)cluster.block_rank();
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -241,41 +241,76 @@ __global__ void __cluster_dims__(GJC_CTAS, 1, 1) __launch_bounds__(1024)
   for (int PQ = 0; PQ < GJC_QC; ++PQ) {
     const int owner = PQ / GJC_QR;
     const int lq = PQ % GJC_QR;  // compile-time after unrolling
-    for (int pw = 0; pw < 32; ++pw) {
+    // Pivots are taken in PAIRS (p, p + 1: rows of two neighbouring warps of the same CTA) with ONE cluster barrier
+    // per pair: the owner of row p leaves its scaled row in its own CTA's buffer first, the owner of row p + 1 (met
+    // at a two-warp named barrier) applies pivot p to its row privately, scales it, and both rows go out together.
+    // After the barrier every thread runs the two elimination steps exactly as in the one-by-one algorithm.
+    for (int pw = 0; pw < 32; pw += 2) {
       const int p = 32 * PQ + pw;
       if (p >= n) break;
-      const bool mine = rank == owner && warp == pw;
-      if (mine) {  // owner of row p: scale it and deliver it to the four CTAs
+      const bool has_q = p + 1 < n;
+      const int buf = (p >> 1) & 1;
+      const bool mine_p = rank == owner && warp == pw;
+      const bool mine_q = has_q && rank == owner && warp == pw + 1;
+      if (mine_p) {
         const double piv = __shfl_sync(0xffffffffu, a[lq][PQ], pw);
         const double dp = d0[lq];
         const double inv = (piv > 1e-13 * dp && dp > 0.0) ? fast_rcp(piv) : 0.0;
+#pragma unroll
+        for (int qj = 0; qj < GJC_QC; ++qj) prow[buf][0][lane + 32 * qj] = a[lq][qj] * inv;
+        if (lane == 0) s_inv[buf][0] = inv;
+        if (has_q) asm volatile("bar.sync 1, 64;" ::: "memory");  // row p is in place for the next warp
 #pragma unroll 1
-        for (int r = 0; r < GJC_CTAS; ++r) {  // (not unrolled: four sets of remote addresses would be kept live)
-          double* dst = cluster.map_shared_rank(&prow[p & 1][0], r);
+        for (int r = 0; r < GJC_CTAS; ++r) {  // (not unrolled: the remote addresses would be kept live)
+          if (r == rank) continue;
+          double* dst = cluster.map_shared_rank(&prow[buf][0][0], r);
 #pragma unroll
           for (int qj = 0; qj < GJC_QC; ++qj) dst[lane + 32 * qj] = a[lq][qj] * inv;
-          if (lane == 0) *cluster.map_shared_rank(&s_inv[p & 1], r) = inv;
+          if (lane == 0) *cluster.map_shared_rank(&s_inv[buf][0], r) = inv;
         }
       }
-      double f[GJC_QR];
+      if (mine_q) {
+        asm volatile("bar.sync 1, 64;" ::: "memory");
+        const double inv_p = s_inv[buf][0];
+        const double fq = __shfl_sync(0xffffffffu, a[lq][PQ], pw);
+        double t[GJC_QC];  // row p + 1 after pivot p
 #pragma unroll
-      for (int qi = 0; qi < GJC_QR; ++qi) f[qi] = __shfl_sync(0xffffffffu, a[qi][PQ], pw);  // column p of my rows
-      if (mine) f[lq] = 0.0;  // row p itself is replaced below
+        for (int qj = 0; qj < GJC_QC; ++qj) t[qj] = a[lq][qj] - fq * prow[buf][0][lane + 32 * qj];
+        if (lane == pw) t[PQ] = -fq * inv_p;
+        const double piv = __shfl_sync(0xffffffffu, t[PQ], pw + 1);
+        const double dp = d0[lq];
+        const double inv = (piv > 1e-13 * dp && dp > 0.0) ? fast_rcp(piv) : 0.0;
+#pragma unroll 1
+        for (int r = 0; r < GJC_CTAS; ++r) {
+          double* dst = cluster.map_shared_rank(&prow[buf][1][0], r);
+#pragma unroll
+          for (int qj = 0; qj < GJC_QC; ++qj) dst[lane + 32 * qj] = t[qj] * inv;
+          if (lane == 0) *cluster.map_shared_rank(&s_inv[buf][1], r) = inv;
+        }
+      }
       cluster.sync();
-      const double inv = s_inv[p & 1];
-      const double* rp = &prow[p & 1][lane];  // read where used: 2 x 7 entries per thread leave no room for a copy
+      auto eliminate = [&](int set, int pl, bool mine) {
+        double f[GJC_QR];
 #pragma unroll
-      for (int qj = 0; qj < GJC_QC; ++qj) {
-        const double r = rp[32 * qj];
+        for (int qi = 0; qi < GJC_QR; ++qi) f[qi] = __shfl_sync(0xffffffffu, a[qi][PQ], pl);  // pivot column of my rows
+        if (mine) f[lq] = 0.0;  // the pivot row itself is replaced below
+        const double inv = s_inv[buf][set];
+        const double* rp = &prow[buf][set][lane];  // read where used: 2 x 7 entries per thread leave no room for a copy
 #pragma unroll
-        for (int qi = 0; qi < GJC_QR; ++qi) a[qi][qj] -= f[qi] * r;
-        if (mine) a[lq][qj] = r;  // row p: the scaled pivot row
-      }
-      if (lane == pw) {  // column p: -f / pivot, 1 / pivot on the diagonal
+        for (int qj = 0; qj < GJC_QC; ++qj) {
+          const double r = rp[32 * qj];
 #pragma unroll
-        for (int qi = 0; qi < GJC_QR; ++qi) a[qi][PQ] = -f[qi] * inv;
-        if (mine) a[lq][PQ] = inv;
-      }
+          for (int qi = 0; qi < GJC_QR; ++qi) a[qi][qj] -= f[qi] * r;
+          if (mine) a[lq][qj] = r;  // pivot row: the scaled row
+        }
+        if (lane == pl) {  // pivot column: -f / pivot, 1 / pivot on the diagonal
+#pragma unroll
+          for (int qi = 0; qi < GJC_QR; ++qi) a[qi][PQ] = -f[qi] * inv;
+          if (mine) a[lq][PQ] = inv;
+        }
+      };
+      eliminate(0, pw, mine_p);
+      if (has_q) eliminate(1, pw + 1, mine_q);
     }
   }
   cluster.sync();  // nobody leaves while a peer may still write its shared memory
