@@ -222,6 +222,19 @@ int mpba_workspace_bytes(const mpba_problem* prob, size_t* bytes);
 int mpba_evaluate(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
                   double* r_reproj, double* r_depth, double* cost);
 
+/* Post-BA track filter at the current state.  Replaces pycolmap's
+ * ObservationManager.filter_points3D(max_reproj_error, min_tri_angle, point3D_ids) as the mapper calls it after
+ * every bundle (mpsfm/sfm/mapper/base.py:700-711 filter_bundle, :772-797 filter_local_points3D), restating COLMAP's
+ * rule per track: observations with reprojection error > max_reproj_error [pixels] go (a point behind the camera has
+ * infinite error); a track left with < 2 observations loses its point; a point whose kept observations have no pair
+ * of projection centres subtending >= min_tri_angle_deg at the point goes too.
+ * pt_select [P] (1 = filter this point; NULL = all) -- unselected points are reported kept and not evaluated.
+ * Device outputs: obs_keep [N] in TRACK order, pt_keep [P], pt_error [P] = mean kept reprojection error (-1 for
+ * removed / unselected points).  num_filtered (HOST, may be NULL) = observations removed, counted as COLMAP does. */
+int mpba_filter_tracks(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
+                       double max_reproj_error, double min_tri_angle_deg, const uint8_t* pt_select, uint8_t* obs_keep,
+                       uint8_t* pt_keep, double* pt_error, int64_t* num_filtered);
+
 /* Normal-equation blocks at the current state (unscaled, undamped), device outputs:
  * Hcc [C][36], gc [C][6], Hpp [P][6] (xx,xy,xz,yy,yz,zz), gp [P][3]; cost as above. */
 int mpba_linearize(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,

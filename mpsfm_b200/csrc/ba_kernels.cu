@@ -1575,6 +1575,37 @@ __global__ void __launch_bounds__(PT_THREADS) k_evaluate(ProblemView pv, const d
   }
 }
 
+// Post-BA track filter (ba_math.cuh: filter_track), one thread per track like k_evaluate: the pass runs once per
+// bundle, not per LM iteration.  Unselected points are reported as kept and not evaluated (error -1).  The count of
+// removed observations is an integer sum, so the double atomicAdd is exact and order independent.
+__global__ void __launch_bounds__(PT_THREADS) k_filter_tracks(ProblemView pv, const double* __restrict__ pose,
+                                                              const double* __restrict__ X, double max_err2,
+                                                              double min_angle, const uint8_t* __restrict__ pt_select,
+                                                              uint8_t* obs_keep, uint8_t* __restrict__ pt_keep,
+                                                              double* __restrict__ pt_error,
+                                                              double* __restrict__ scal) {
+  const int p = pv.p0 + blockIdx.x * PT_THREADS + threadIdx.x;
+  int filtered = 0;
+  if (p < pv.p1) {
+    const int k0 = pv.pt_ptr[p], k1 = pv.pt_ptr[p + 1];
+    bool alive = true;
+    double err = -1.0;
+    if (pt_select == nullptr || pt_select[p] != 0) {
+      double Xp[3];
+      load_point(X, p, Xp);
+      alive = filter_track(pose, pv.img_camera, pv.cam_model, pv.cam_params, MPBA_MAX_PRM, pv.pm_img, pv.pm_xy, k0, k1,
+                           Xp, max_err2, min_angle, obs_keep, err, filtered);
+    } else {
+      for (int k = k0; k < k1; ++k) obs_keep[k] = 1;
+    }
+    pt_keep[p] = alive ? 1 : 0;
+    pt_error[p] = err;
+  }
+  __shared__ double sm[PT_THREADS / 32 + 1];
+  const double total = block_sum<PT_THREADS / 32>((double)filtered, sm);
+  if (threadIdx.x == 0 && total != 0.0) atomicAdd(scal + S_FILTERED, total);
+}
+
 // COLMAP normalises every quaternion before it enters the problem
 __global__ void k_normalize_poses(int C, const double* __restrict__ in, const double* __restrict__ shift_scale,
                                   double* __restrict__ out) {
@@ -1732,6 +1763,13 @@ void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, cudaS
 void launch_evaluate(const ProblemView& pv, const double* pose, const double* X, double* r_reproj, double* r_depth,
                      cudaStream_t st) {
   if (pv.p1 > pv.p0) k_evaluate<<<points_grid(pv.p1 - pv.p0), PT_THREADS, 0, st>>>(pv, pose, X, r_reproj, r_depth);
+}
+void launch_filter_tracks(const ProblemView& pv, const double* pose, const double* X, double max_err2, double min_angle,
+                          const uint8_t* pt_select, uint8_t* obs_keep, uint8_t* pt_keep, double* pt_error, double* scal,
+                          cudaStream_t st) {
+  if (pv.p1 > pv.p0)
+    k_filter_tracks<<<points_grid(pv.p1 - pv.p0), PT_THREADS, 0, st>>>(pv, pose, X, max_err2, min_angle, pt_select,
+                                                                       obs_keep, pt_keep, pt_error, scal);
 }
 void launch_normalize_poses(int C, const double* in, const double* shift_scale, double* out, cudaStream_t st) {
   if (C > 0) k_normalize_poses<<<(C + 127) / 128, 128, 0, st>>>(C, in, shift_scale, out);

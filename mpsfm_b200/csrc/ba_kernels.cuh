@@ -20,6 +20,7 @@ enum Scal {
   S_STEP2_C = 7,     // ambient |q - q_cand|^2 + |t - t_cand|^2 over active image blocks
   S_XNORM2_C = 8,
   S_PCG_ITERS = 9,
+  S_FILTERED = 9,     // mpba_filter_tracks only (no PCG runs in that call): observations removed
   S_PCG_FLAG = 10,   // 0 converged, 1 iteration cap, 2 breakdown (p'Sp <= 0 or non-finite)
   S_PCG_RES = 11,    // final sqrt(r'M^-1 r / b'M^-1 b)
   S_BAD_POINTS = 12, // number of point blocks whose damped Hpp was not positive definite
@@ -204,6 +205,10 @@ void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, cudaS
 // ---- misc ---------------------------------------------------------------------------------------
 void launch_evaluate(const ProblemView& pv, const double* pose, const double* X, double* r_reproj, double* r_depth,
                      cudaStream_t st);
+// post-BA track filter (COLMAP FilterPoints3D rule, ba_math.cuh: filter_track); scal[S_FILTERED] += removed observations
+void launch_filter_tracks(const ProblemView& pv, const double* pose, const double* X, double max_err2, double min_angle,
+                          const uint8_t* pt_select, uint8_t* obs_keep, uint8_t* pt_keep, double* pt_error, double* scal,
+                          cudaStream_t st);
 // unit quaternions (COLMAP normalises before adding to the problem) + exp(log-scale) into slot 7
 void launch_normalize_poses(int C, const double* in, const double* shift_scale, double* out, cudaStream_t st);
 void launch_flag_points(int P, const uint8_t* pt_const, double* X, cudaStream_t st);

@@ -21,6 +21,7 @@
 
 #include <float.h>
 #include <math.h>
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __CUDACC__
@@ -527,6 +528,108 @@ MPBA_HD double lm_damping(double hjj, double c, double radius, double lo, double
   double dj = cc * hjj;
   dj = dj < lo ? lo : (dj > hi ? hi : dj);
   return dj / (radius * cc);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Post-BA track filter.  The reference calls pycolmap's
+// ObservationManager.filter_points3D(max_reproj_error, min_tri_angle, point3D_ids) after every bundle
+// (mpsfm/sfm/mapper/base.py:700-711, 772-797); this restates COLMAP's published two-phase rule per track:
+//   1. an observation whose squared reprojection error exceeds max_err^2 is deleted (a point at
+//      z < DBL_EPSILON in the camera frame has error DBL_MAX); a track left with fewer than two
+//      observations deletes its point; a surviving point's error is the mean of the kept errors,
+//   2. a surviving point whose kept observations have no pair of projection centres c = -R^T t that
+//      subtends at least min_tri_angle at the point is deleted.
+// num_filtered counts observations as COLMAP does (whole track when the point goes).
+
+// squared reprojection error of X in the image with pose = {qx,qy,qz,qw,tx,ty,tz}
+MPBA_HD double reproj_error2(const double* pose, int model, const double* prm, const double X[3], double ox,
+                             double oy) {
+  double R[9];
+  quat_to_rotmat(pose, R);
+  const double px = R[0] * X[0] + R[1] * X[1] + R[2] * X[2] + pose[4];
+  const double py = R[3] * X[0] + R[4] * X[1] + R[5] * X[2] + pose[5];
+  const double pz = R[6] * X[0] + R[7] * X[1] + R[8] * X[2] + pose[6];
+  if (pz < DBL_EPSILON) return DBL_MAX;
+  double x, y;
+  img_from_cam_generic<double>(model, prm, px / pz, py / pz, x, y);
+  const double r0 = x - ox, r1 = y - oy;
+  return r0 * r0 + r1 * r1;
+}
+
+MPBA_HD void projection_center(const double* pose, double c[3]) {
+  double R[9];
+  quat_to_rotmat(pose, R);
+  c[0] = -(R[0] * pose[4] + R[3] * pose[5] + R[6] * pose[6]);
+  c[1] = -(R[1] * pose[4] + R[4] * pose[5] + R[7] * pose[6]);
+  c[2] = -(R[2] * pose[4] + R[5] * pose[5] + R[8] * pose[6]);
+}
+
+// angle at X between the rays to c1 and c2, folded into [0, pi/2]; law of cosines on squared lengths, the ratio is
+// NOT clamped (a ratio pushed past 1 by rounding gives nan, which fails every ">= min angle" test, as in COLMAP)
+MPBA_HD double triangulation_angle(const double c1[3], const double c2[3], const double X[3]) {
+  double b2 = 0.0, r1 = 0.0, r2 = 0.0;
+  for (int j = 0; j < 3; ++j) {
+    const double b = c1[j] - c2[j], u = X[j] - c1[j], v = X[j] - c2[j];
+    b2 += b * b;
+    r1 += u * u;
+    r2 += v * v;
+  }
+  const double den = 2.0 * sqrt(r1 * r2);
+  if (den == 0.0) return 0.0;
+  const double ang = fabs(acos((r1 + r2 - b2) / den));
+  const double oth = 3.14159265358979323846 - ang;
+  return oth < ang ? oth : ang;
+}
+
+// One track: observations k0 .. k1 (track order) of point X.  pose8 [C][8] (unit quaternions), keep [N] gets 1 / 0
+// per observation.  Returns true when the point survives; err = mean kept reprojection error (-1 when it does not),
+// filtered = observations removed.
+MPBA_HD bool filter_track(const double* pose8, const int32_t* img_camera, const int32_t* cam_model,
+                          const double* cam_params, int max_prm, const int32_t* pm_img, const double* pm_xy, int k0,
+                          int k1, const double X[3], double max_err2, double min_angle, uint8_t* keep, double& err,
+                          int& filtered) {
+  const int len = k1 - k0;
+  int kept = 0;
+  double sum = 0.0;
+  for (int k = k0; k < k1; ++k) {
+    const int img = pm_img[k], cam = img_camera[img];
+    const double e2 = reproj_error2(pose8 + 8 * (size_t)img, cam_model[cam], cam_params + (size_t)max_prm * cam, X,
+                                    pm_xy[2 * (size_t)k], pm_xy[2 * (size_t)k + 1]);
+    const bool ok = !(e2 > max_err2);
+    keep[k] = ok ? 1 : 0;
+    if (ok) {
+      sum += sqrt(e2);
+      ++kept;
+    }
+  }
+  bool alive = kept >= 2;  // COLMAP: deleted when (len - kept) >= len - 1, which covers len < 2
+  if (alive) {
+    filtered = len - kept;
+    err = sum / kept;
+    alive = false;
+    for (int a = k0 + 1; a < k1 && !alive; ++a) {
+      if (!keep[a]) continue;
+      double ca[3];
+      projection_center(pose8 + 8 * (size_t)pm_img[a], ca);
+      for (int b = k0; b < a; ++b) {
+        if (!keep[b]) continue;
+        double cb[3];
+        projection_center(pose8 + 8 * (size_t)pm_img[b], cb);
+        if (triangulation_angle(ca, cb, X) >= min_angle) {
+          alive = true;
+          break;
+        }
+      }
+    }
+    if (!alive) filtered += kept;
+  } else {
+    filtered = len;
+  }
+  if (!alive) {
+    for (int k = k0; k < k1; ++k) keep[k] = 0;
+    err = -1.0;
+  }
+  return alive;
 }
 
 }  // namespace mpba

@@ -843,6 +843,34 @@ int mpba_evaluate(mpba_handle* h, const mpba_problem* prob, void* workspace, siz
   return MPBA_OK;
 }
 
+int mpba_filter_tracks(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
+                       double max_reproj_error, double min_tri_angle_deg, const uint8_t* pt_select, uint8_t* obs_keep,
+                       uint8_t* pt_keep, double* pt_error, int64_t* num_filtered) {
+  Ctx c;
+  int rc = begin(h, prob, workspace, workspace_bytes, c);
+  if (rc) return rc;
+  if (!obs_keep || !pt_keep || !pt_error)
+    return fail(h, MPBA_E_INVALID, "mpba_filter_tracks: obs_keep, pt_keep and pt_error are required");
+  reset_profile(h, 0);
+  {
+    Timer t(h, KS_MISC);
+    launch_normalize_poses(c.pv.C, prob->img_pose, prob->img_shift_scale, c.w.pose[0], h->stream);
+  }
+  rc = stage_points(c, prob, c.w.X[0]);
+  if (rc) return rc;
+  CU(cudaMemsetAsync(c.w.scal, 0, S_COUNT * sizeof(double), h->stream));
+  {
+    Timer t(h, KS_EVALUATE);
+    const double deg = 3.14159265358979323846 / 180.0;
+    launch_filter_tracks(c.pv, c.w.pose[0], c.w.X[0], max_reproj_error * max_reproj_error, min_tri_angle_deg * deg,
+                         pt_select, obs_keep, pt_keep, pt_error, c.w.scal, h->stream);
+  }
+  rc = fetch_scalars(c);
+  if (rc) return rc;
+  if (num_filtered) *num_filtered = (int64_t)h->h_scal[S_FILTERED];
+  return MPBA_OK;
+}
+
 int mpba_linearize(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes, double* Hcc,
                    double* gc, double* Hpp, double* gp, double* cost) {
   Ctx c;

@@ -117,7 +117,7 @@ class MpbaSummary(C.Structure):
 EXPORTS = (
     "mpba_version", "mpba_create", "mpba_destroy", "mpba_last_error", "mpba_default_options",
     "mpba_workspace_bytes", "mpba_evaluate", "mpba_linearize", "mpba_reduced_system", "mpba_solve",
-    "mpba_kernel_times", "mpba_kernel_name", "mpba_point_covariances",
+    "mpba_kernel_times", "mpba_kernel_name", "mpba_point_covariances", "mpba_filter_tracks",
     "mpba_pack_tracks", "mpba_sample_maps", "mpba_depth_prior_terms", "mpba_segmented_median_workspace_bytes",
     "mpba_segmented_median", "mpba_gather_observations", "mpba_host_layout_create", "mpba_host_layout_destroy",
     "mpba_host_gather", "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
@@ -150,6 +150,8 @@ def load_library(path: Optional[str] = None):
     lib.mpba_reduced_system.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t,
                                         C.POINTER(MpbaOptions), C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, _ip]
     lib.mpba_point_covariances.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.mpba_filter_tracks.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t, C.c_double, C.c_double,
+                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]
     lib.mpba_solve.argtypes = [C.c_void_p, C.POINTER(MpbaProblem), C.c_void_p, C.c_size_t,
                                C.POINTER(MpbaOptions), C.POINTER(MpbaSummary)]
     lib.mpba_sample_maps.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
@@ -813,6 +815,32 @@ class BundleAdjuster:
         H3[:, 2, 0], H3[:, 2, 1], H3[:, 2, 2] = h6[:, 2], h6[:, 4], h6[:, 5]
         return (Hcc.cpu().numpy().reshape(lay.C, 6, 6), gc.cpu().numpy(), H3, gp.cpu().numpy()[: lay.P],
                 float(cost[0]), float(cost[1]))
+
+    def filter_tracks(self, max_reproj_error: float, min_tri_angle: float, select=None):
+        """Post-BA track filter at the current state: pycolmap's ``obs.filter_points3D(max_reproj_error,
+        min_tri_angle, point3D_ids)`` (mpsfm/sfm/mapper/base.py:700-711, 772-797) as one pass over the resident arrays.
+        ``select`` [P] bool = the point3D_ids argument (None: every point).  Returns (obs_keep [N] bool in NATURAL
+        observation order, pt_keep [P] bool, pt_error [P] (mean kept reprojection error, -1 for removed / unselected
+        points), num_filtered)."""
+        self._require_unsharded("filter_tracks")
+        torch, lay = self.torch, self.layout
+        ok = torch.empty((max(lay.N, 1),), dtype=torch.uint8, device=self.device)
+        pk = torch.empty((max(lay.P, 1),), dtype=torch.uint8, device=self.device)
+        pe = torch.empty((max(lay.P, 1),), dtype=torch.float64, device=self.device)
+        sel = None
+        if select is not None:
+            sel_h = np.ascontiguousarray(np.asarray(select).astype(np.uint8).reshape(-1))
+            if sel_h.shape[0] != lay.P:
+                raise ValueError("select must have one entry per point")
+            sel = torch.from_numpy(sel_h if lay.P else np.zeros(1, np.uint8)).to(self.device)
+        nf = C.c_int64(0)
+        ws, wsn = self._ws()
+        self._check(self.lib.mpba_filter_tracks(self.handle, C.byref(self.prob), ws, wsn, float(max_reproj_error),
+                                                float(min_tri_angle), sel.data_ptr() if sel is not None else None,
+                                                ok.data_ptr(), pk.data_ptr(), pe.data_ptr(), C.byref(nf)))
+        obs_keep = np.empty(lay.N, dtype=bool)
+        obs_keep[lay.pm_src.astype(np.int64)] = ok.cpu().numpy()[: lay.N] != 0
+        return obs_keep, pk.cpu().numpy()[: lay.P] != 0, pe.cpu().numpy()[: lay.P].copy(), int(nf.value)
 
     def point_covariances(self):
         """[P,3,3] covariance of every variable point conditioned on the poses (zeros for constant points)."""

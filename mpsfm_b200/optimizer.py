@@ -443,6 +443,69 @@ class Optimizer(BaseClass):
             if j is not None:
                 self.mpsfm_rec.point_covs.data[p3Did] = covs[j]
 
+    def filter_points3D(self, max_reproj_error, min_tri_angle, point3D_ids):
+        """``mpsfm_rec.obs.filter_points3D(max_reproj_error, min_tri_angle, point3D_ids)`` as the mapper calls it after
+        every bundle (mpsfm/sfm/mapper/base.py:700-711 ``filter_bundle``, :772-797 ``filter_local_points3D``), on the
+        GPU: one ``mpba_filter_tracks`` pass over the tracks of ``point3D_ids``, then the same in-place edits pycolmap's
+        ObservationManager makes (``delete_observation``, ``delete_point3D``, ``point3D.error``).  Returns the number
+        of filtered observations."""
+        from . import engine
+
+        rec = self.mpsfm_rec
+        pids = [int(p) for p in point3D_ids if int(p) in rec.points3D]
+        if not pids:
+            return 0
+        image_index, image_ids = {}, []
+        o_img, o_pt, o_el, o_xy = [], [], [], []
+        for j, pid in enumerate(pids):
+            for el in rec.points3D[pid].track.elements:
+                if el.image_id not in image_index:
+                    image_index[el.image_id] = len(image_ids)
+                    image_ids.append(el.image_id)
+                o_img.append(image_index[el.image_id])
+                o_pt.append(j)
+                o_el.append((el.image_id, el.point2D_idx))
+                o_xy.append(np.asarray(rec.images[el.image_id].keypoint_coordinates([el.point2D_idx])).reshape(2))
+        C = len(image_ids)
+        img_q, img_t = np.empty((C, 4)), np.empty((C, 3))
+        cam_ids = []
+        for k, imid in enumerate(image_ids):
+            image = rec.images[imid]
+            img_q[k] = image.cam_from_world.rotation.quat
+            img_t[k] = image.cam_from_world.translation
+            cam_ids.append(image.camera_id)
+        uniq_cams = list(dict.fromkeys(cam_ids))
+        cam_row = {c: r for r, c in enumerate(uniq_cams)}
+        cam_params = np.zeros((max(len(uniq_cams), 1), MAX_CAMERA_PARAMS))
+        for r, c in enumerate(uniq_cams):
+            prm = np.asarray(rec.rec.cameras[c].params, dtype=np.float64)
+            cam_params[r, : prm.size] = prm
+        none = np.zeros(0)
+        problem = BundleProblem(
+            img_q=img_q, img_t=img_t, img_camera=np.array([cam_row[c] for c in cam_ids], dtype=np.int32),
+            img_free_mask=np.full(C, FREE_NONE, dtype=np.uint8),
+            cam_model=np.array([_model_id(rec.rec.cameras[c].model) for c in uniq_cams] or [0], dtype=np.int32),
+            cam_params=cam_params, pt_xyz=rec.point3D_coordinates(pids), pt_const=np.zeros(len(pids), dtype=np.uint8),
+            obs_img=np.asarray(o_img, dtype=np.int32), obs_pt=np.asarray(o_pt, dtype=np.int32),
+            obs_xy=np.asarray(o_xy, dtype=np.float64).reshape(-1, 2), depth_obs=none.astype(np.int32), depth_d=none,
+            depth_w=none, depth_a=none, shift_scale=np.zeros((C, 2)), reproj_loss=LossType.TRIVIAL,
+            depth_loss=LossType.TRIVIAL).normalized()
+        ba = engine.BundleAdjuster(problem, device=int(self.conf.gpu["device"]))
+        try:
+            obs_keep, pt_keep, pt_error, num_filtered = ba.filter_tracks(max_reproj_error, min_tri_angle)
+        finally:
+            ba.close()
+        obs = rec.obs
+        for j, pid in enumerate(pids):
+            if not pt_keep[j]:
+                obs.delete_point3D(pid)
+            else:
+                rec.points3D[pid].error = float(pt_error[j])
+        for k in np.flatnonzero(~obs_keep):
+            if pt_keep[o_pt[k]]:
+                obs.delete_observation(*o_el[k])
+        return num_filtered
+
     def optimize_prior_shiftscale(self, bundle, **kwargs):
         """Closed-form per-image log-scale of the depth prior (:268-274, :187-242)."""
         shift_scale, success = self.__build_shiftscale_problem(bundle, **kwargs)

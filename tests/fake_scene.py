@@ -191,6 +191,24 @@ def numpy_project(image, camera, points3D):
     return project3D_colmap(image.cam_from_world.matrix(), camera.calibration_matrix(), np.asarray(points3D, dtype=np.float64))
 
 
+class ObservationManager:
+    """The two pycolmap ObservationManager edits the track filter makes (``rec.obs`` in MpsfmReconstruction)."""
+
+    def __init__(self, rec):
+        self._rec = rec
+
+    def delete_observation(self, image_id, point2D_idx):
+        p2d = self._rec.images[image_id].points2D[point2D_idx]
+        track = self._rec.points3D[p2d.point3D_id].track
+        track.elements = [e for e in track.elements if (e.image_id, e.point2D_idx) != (image_id, point2D_idx)]
+        p2d.point3D_id = INVALID_POINT3D
+
+    def delete_point3D(self, point3D_id):
+        for e in self._rec.points3D[point3D_id].track.elements:
+            self._rec.images[e.image_id].points2D[e.point2D_idx].point3D_id = INVALID_POINT3D
+        del self._rec.points3D[point3D_id]
+
+
 class Reconstruction:
     """Stand-in for MpsfmReconstruction (+ the wrapped pycolmap.Reconstruction as ``.rec``)."""
 
@@ -202,6 +220,7 @@ class Reconstruction:
         self.rec = _Rec()
         self.point_covs = PointCovs()
         self._next_point3D_id = 1
+        self.obs = ObservationManager(self)
 
     @property
     def cameras(self):

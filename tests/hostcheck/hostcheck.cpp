@@ -51,4 +51,27 @@ void hc_project(int model, const double* prm, double u, double v, double* xy, do
   xy[2] = x2;
   xy[3] = y2;
 }
+// the post-BA track filter exactly as k_filter_tracks runs it (ba_math.cuh: filter_track), track-order arrays
+long long hc_filter_tracks(int P, const int* pt_ptr, const double* pose8, const int* img_camera, const int* cam_model,
+                           const double* cam_params, const int* pm_img, const double* pm_xy, const double* X,
+                           double max_err, double min_deg, const unsigned char* select, unsigned char* obs_keep,
+                           unsigned char* pt_keep, double* pt_error) {
+  long long total = 0;
+  for (int p = 0; p < P; ++p) {
+    const int k0 = pt_ptr[p], k1 = pt_ptr[p + 1];
+    bool alive = true;
+    double err = -1.0;
+    int filtered = 0;
+    if (!select || select[p]) {
+      alive = filter_track(pose8, img_camera, cam_model, cam_params, 12, pm_img, pm_xy, k0, k1, X + 3 * (size_t)p,
+                           max_err * max_err, min_deg * (3.14159265358979323846 / 180.0), obs_keep, err, filtered);
+    } else {
+      for (int k = k0; k < k1; ++k) obs_keep[k] = 1;
+    }
+    pt_keep[p] = alive ? 1 : 0;
+    pt_error[p] = err;
+    total += filtered;
+  }
+  return total;
+}
 }
