@@ -93,12 +93,24 @@ __device__ __forceinline__ double block_max(double v, double* sm) {
 #define MPBA_IMG_THREADS 128
 #endif
 constexpr int IMG_THREADS = MPBA_IMG_THREADS;
+// one 128-byte line per thread slot `tid - slot`; slot advances by the number of lines of the range
+__device__ __forceinline__ void l2_prefetch_range(const void* p, size_t bytes, int& slot, int tid) {
+  const uintptr_t a0 = reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)127, a1 = reinterpret_cast<uintptr_t>(p) + bytes;
+  const int lines = (int)((a1 - a0 + 127) >> 7);
+  const int i = tid - slot;
+  if (i >= 0 && i < lines) asm volatile("prefetch.global.L2 [%0];" ::"l"(a0 + ((uintptr_t)i << 7)));
+  slot += lines;
+}
 constexpr int IMG_WARPS = IMG_THREADS / 32;
 #ifndef MPBA_IMG_MINB
 #define MPBA_IMG_MINB 3
 #endif
+#ifndef MPBA_IMG_PREFETCH_DEFAULT
+#define MPBA_IMG_PREFETCH_DEFAULT 444  // one wave: 148 SMs x 3 CTAs
+#endif
 __global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(ProblemView pv, const double* __restrict__ pose,
-                                                    const double* __restrict__ X, double* __restrict__ chunk_part) {
+                                                    const double* __restrict__ X, double* __restrict__ chunk_part,
+                                                    int prefetch_ahead) {
   const int c = blockIdx.x;
   const int img = pv.chunk_img[c];
   const int beg = pv.chunk_begin[c], end = pv.chunk_end[c];
@@ -170,6 +182,19 @@ __global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(Probl
 #pragma unroll
     for (int w = 0; w < IMG_WARPS; ++w) s += sm[w][threadIdx.x];
     chunk_part[(size_t)c * IMG_PART + threadIdx.x] = s;
+  }
+  // L2 prefetch of the sequential streams of the chunk prefetch_ahead CTAs later (see prefetch_track_cta)
+  if (prefetch_ahead > 0 && c + prefetch_ahead < (int)gridDim.x) {
+    const size_t b2 = (size_t)__ldg(pv.chunk_begin + c + prefetch_ahead);
+    const size_t n2 = (size_t)__ldg(pv.chunk_end + c + prefetch_ahead) - b2;
+    for (int t = threadIdx.x; t < 384; t += IMG_THREADS) {
+      int slot = 0;
+      l2_prefetch_range(pv.cm_pt + b2, n2 * 4, slot, t);
+      l2_prefetch_range(pv.cm_xy + 2 * b2, n2 * 16, slot, t);
+      l2_prefetch_range(dd + b2, n2 * 8, slot, t);
+      l2_prefetch_range(dd + N + b2, n2 * 8, slot, t);
+      l2_prefetch_range(dd + 2 * N + b2, n2 * 8, slot, t);
+    }
   }
 }
 
@@ -264,6 +289,12 @@ constexpr int PW_THREADS = 128;  // track-order passes: one thread per OBSERVATI
 constexpr int PW_WARPS = PW_THREADS / 32;
 #ifndef MPBA_POINTS_MINB
 #define MPBA_POINTS_MINB 4
+#endif
+#ifndef MPBA_POINTS_PREFETCH_DEFAULT
+#define MPBA_POINTS_PREFETCH_DEFAULT 592  // one wave: 148 SMs x 4 CTAs (sweep: profiles/r01_prefetch_sweep_cfg3.json)
+#endif
+#ifndef MPBA_BACKSUB_PREFETCH_DEFAULT
+#define MPBA_BACKSUB_PREFETCH_DEFAULT 333
 #endif
 constexpr int LINV_STRIDE = 9;  // per point: L^-1 (6, lower) and e = L^-1 gp (3)
 
@@ -525,6 +556,23 @@ __device__ __noinline__ double points_warp_path(const ProblemView pv, const doub
   return gmax;
 }
 
+// ---- L2 prefetch of a later CTA's operands.  The track-order streams are sequential, but every CTA starts with a
+// chain of dependent loads (descriptor -> slot indices -> point / pose records) that each miss to DRAM; a CTA that
+// runs one wave earlier asks L2 for those lines, so the chain of the later CTA costs L2 hits instead.
+__device__ __forceinline__ void prefetch_track_cta(const ProblemView& pv, const double* X, int4 d, int tid) {
+  const size_t T0 = (size_t)d.x, nt = (size_t)d.y, base = (size_t)d.z, n = (size_t)d.w, N = (size_t)pv.N;
+  int slot = 0;
+  l2_prefetch_range(pv.pm_xy + 2 * base, n * 16, slot, tid);
+  l2_prefetch_range(pv.pm_depth + base, n * 8, slot, tid);
+  l2_prefetch_range(pv.pm_depth + N + base, n * 8, slot, tid);
+  l2_prefetch_range(pv.pm_depth + 2 * N + base, n * 8, slot, tid);
+  l2_prefetch_range(X + 4 * T0, nt * 32, slot, tid);
+  l2_prefetch_range(pv.pm_pt + base, n * 4, slot, tid);
+  l2_prefetch_range(pv.pm_img + base, n * 4, slot, tid);
+  l2_prefetch_range(pv.pt_ptr + T0, (nt + 1) * 4, slot, tid);
+  l2_prefetch_range(pv.pt_const + T0, nt, slot, tid);
+}
+
 // Track-order pass, one thread per OBSERVATION, one CTA per four consecutive warp groups of whole tracks
 // (mpba_pack_tracks: <= 128 observations, <= 128 tracks, contiguous slots).  Every observation is linearised ONCE:
 //   1. track threads publish the track of every observation slot of the CTA (shared memory),
@@ -545,16 +593,24 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
                                                        double* __restrict__ gp, double* __restrict__ Hinv,
                                                        double* __restrict__ Linv, double* __restrict__ fac,
                                                        double* __restrict__ pt_part, double* __restrict__ scal,
-                                                       int write_factors, int force_warp_path) {
+                                                       int write_factors, int force_warp_path, int prefetch_ahead) {
   __shared__ __align__(16) double2 rows_all[PW_WARPS][256];
   __shared__ double s_v[PW_THREADS][9];
   __shared__ double s_le[PW_THREADS][9];
+  __shared__ __align__(16) int4 s_next;  // descriptor of the CTA prefetch_ahead blocks later
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g0 = blockIdx.x * PW_WARPS, g1 = min(g0 + PW_WARPS, pv.num_track_warps);
   const int4 desc = __ldg(pv.cta_desc + blockIdx.x);  // one load instead of the tw_first -> pt_ptr chain
   const int T0 = desc.x, nt = desc.y, base = desc.z, n = desc.w;
   double gmax = 0.0;
   if (n <= PW_THREADS && !force_warp_path) {
+    const bool pf = prefetch_ahead > 0 && blockIdx.x + prefetch_ahead < gridDim.x;
+    if (pf && tid == PW_THREADS - 1) {  // asynchronous: lands in shared memory while the CTA linearises
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(&s_next);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(pv.cta_desc + blockIdx.x + prefetch_ahead)
+                   : "memory");
+      asm volatile("cp.async.commit_group;\n" ::: "memory");
+    }
     // track threads: their slot range and constant flag (independent loads, needed after the first barrier)
     int start = 0, len = 0;
     bool cst = true;
@@ -585,7 +641,9 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
       }
     }
     const bool act = tr >= 0;
+    if (pf && tid == PW_THREADS - 1) asm volatile("cp.async.wait_group 0;\n" ::: "memory");
     __syncthreads();
+    if (pf) prefetch_track_cta(pv, X, s_next, tid);
     // ---- 2. points
     if (tid < nt) {
       const bool active = !cst && len > 0;
@@ -1440,13 +1498,29 @@ __global__ void __launch_bounds__(PW_THREADS) k_back_substitute(ProblemView pv, 
                                                                 const double* __restrict__ c_pt,
                                                                 const double* __restrict__ fac, int use_factors,
                                                                 LmDiag lm, double* __restrict__ X_cand,
-                                                                double* __restrict__ pt_part) {
+                                                                double* __restrict__ pt_part, int prefetch_ahead) {
   __shared__ __align__(16) double2 rows_all[PW_WARPS][256];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * PW_WARPS + warp;
   double mcc = 0.0, step2 = 0.0, xn2 = 0.0;
   if (w < pv.num_track_warps) {
     const int4 desc = __ldg(pv.warp_desc + w);  // {first track, tracks, first slot, observations}
+    // L2 prefetch (see prefetch_track_cta) of the group this warp position handles prefetch_ahead CTAs later
+    const int wf = w + prefetch_ahead * PW_WARPS;
+    if (prefetch_ahead > 0 && wf < pv.num_track_warps) {
+      const int4 fd = __ldg(pv.warp_desc + wf);
+      const size_t T0 = (size_t)fd.x, nt = (size_t)fd.y, fb = (size_t)fd.z, fn = (size_t)min(fd.w, 64);
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        int slot = 0;
+        const int t = lane + 32 * r;
+        if (use_factors) l2_prefetch_range(fac + FAC_STRIDE * fb, fn * FAC_STRIDE * 8, slot, t);
+        l2_prefetch_range(X + 4 * T0, nt * 32, slot, t);
+        l2_prefetch_range(Linv + LINV_STRIDE * T0, nt * LINV_STRIDE * 8, slot, t);
+        l2_prefetch_range(pv.pm_pt + fb, fn * 4, slot, t);
+        l2_prefetch_range(pv.pm_img + fb, fn * 4, slot, t);
+      }
+    }
     const double2* fac2 = reinterpret_cast<const double2*>(fac);
     if (desc.w <= 32) {
       // Lane = observation slot.  Tracks are runs of equal point index: heads by comparing with the left lane;
@@ -1659,7 +1733,10 @@ __global__ void k_expand_hcc(int C, const double* __restrict__ Hc, double* __res
 // launchers
 // ================================================================================================
 void launch_img_chunks(const ProblemView& pv, const double* pose, const double* X, double* chunk_part, cudaStream_t st) {
-  if (pv.num_chunks > 0) k_img_chunks<<<pv.num_chunks, IMG_THREADS, 0, st>>>(pv, pose, X, chunk_part);
+  const char* pf_env = getenv("MPBA_IMG_PREFETCH");  // CTAs of lookahead of the L2 prefetch (0: off)
+  const int prefetch_ahead = pf_env ? atoi(pf_env) : MPBA_IMG_PREFETCH_DEFAULT;
+  if (pv.num_chunks > 0)
+    k_img_chunks<<<pv.num_chunks, IMG_THREADS, 0, st>>>(pv, pose, X, chunk_part, prefetch_ahead);
 }
 void launch_img_finalize(const ProblemView& pv, const double* chunk_part, double* Hc, double* gc, double* img_part,
                          cudaStream_t st) {
@@ -1681,10 +1758,13 @@ void launch_points(const ProblemView& pv, const double* pose, const double* X, L
                    int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* Linv,
                    double* fac, double* pt_part, double* scal, int write_factors, cudaStream_t st) {
   static const int force_warp = getenv("MPBA_POINTS_WARP") ? atoi(getenv("MPBA_POINTS_WARP")) : 0;
+  const char* pf_env = getenv("MPBA_POINTS_PREFETCH");  // CTAs of lookahead of the L2 prefetch (0: off)
+  const int prefetch_ahead = pf_env ? atoi(pf_env) : MPBA_POINTS_PREFETCH_DEFAULT;
   if (pv.num_track_warps > 0)
     k_points<<<track_warp_grid(pv.num_track_warps), PW_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling,
                                                                          jacobi_scaling, Hpp, gp, Hinv, Linv, fac,
-                                                                         pt_part, scal, write_factors, force_warp);
+                                                                         pt_part, scal, write_factors, force_warp,
+                                                                         prefetch_ahead);
 }
 void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaStream_t st) {
   k_pt_scalars_gmax<<<1, 1024, 0, st>>>(pt_part, nblk, scal);
@@ -1753,9 +1833,12 @@ void launch_cam_update(const ProblemView& pv, const double* pose, const double* 
 void launch_back_substitute(const ProblemView& pv, const double* X, const double* y, const double* Hpp,
                             const double* gp, const double* Linv, const double* c_pt, const double* fac,
                             int use_factors, LmDiag lm, double* X_cand, double* pt_part, cudaStream_t st) {
+  const char* pf_env = getenv("MPBA_BACKSUB_PREFETCH");  // CTAs of lookahead of the L2 prefetch (0: off)
+  const int prefetch_ahead = pf_env ? atoi(pf_env) : MPBA_BACKSUB_PREFETCH_DEFAULT;
   if (pv.num_track_warps > 0)
     k_back_substitute<<<track_warp_grid(pv.num_track_warps), PW_THREADS, 0, st>>>(pv, X, y, Hpp, gp, Linv, c_pt, fac,
-                                                                                  use_factors, lm, X_cand, pt_part);
+                                                                                  use_factors, lm, X_cand, pt_part,
+                                                                                  prefetch_ahead);
 }
 void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, cudaStream_t st) {
   k_pt_scalars_step<<<1, 1024, 0, st>>>(pt_part, nblk, scal);

@@ -42,10 +42,17 @@ def test_selection_and_state_after_a_solve():
     sel = np.arange(prob.num_points) % 3 != 1
     want = filtering.filter_points3D(prob, prob.img_q, prob.img_t, prob.pt_xyz, 4.0, 1.5, select=sel)
     _check(ba.filter_tracks(4.0, 1.5, select=sel), want)
+    ba.close()
+    # the filter reads the handle's CURRENT state: after a solve that is the refined one
+    prob = make_scene(8, 300, 4, seed=1, outlier_frac=0.1)
+    ba = engine.BundleAdjuster(prob, device=0)
+    before = ba.filter_tracks(4.0, 1.5)
     ba.solve()
     q, t, X = ba.state()
     want = filtering.filter_points3D(prob, q, t, X, 4.0, 1.5)
-    _check(ba.filter_tracks(4.0, 1.5), want)
+    after = ba.filter_tracks(4.0, 1.5)
+    _check(after, want)
+    assert after[1].sum() > before[1].sum()  # the noisy start state loses more points than the refined one
 
 
 def test_filter_is_idempotent_at_scale():
