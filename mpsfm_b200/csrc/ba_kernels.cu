@@ -293,9 +293,6 @@ constexpr int PW_WARPS = PW_THREADS / 32;
 #ifndef MPBA_POINTS_PREFETCH_DEFAULT
 #define MPBA_POINTS_PREFETCH_DEFAULT 592  // one wave: 148 SMs x 4 CTAs (sweep: profiles/r01_prefetch_sweep_cfg3.json)
 #endif
-#ifndef MPBA_POINTS_PERSISTENT_DEFAULT
-#define MPBA_POINTS_PERSISTENT_DEFAULT 0
-#endif
 #ifndef MPBA_BACKSUB_PREFETCH_DEFAULT
 #define MPBA_BACKSUB_PREFETCH_DEFAULT 333
 #endif
@@ -702,170 +699,6 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
     __shared__ double smx[PW_WARPS + 1];
     const double m = block_max<PW_WARPS>(gmax, smx);
     if (threadIdx.x == 0) pt_part[(size_t)blockIdx.x * PT_PART] = m;
-  }
-}
-
-// ---- persistent variant of k_points.  One CTA per resident slot (grid = SMs x MPBA_POINTS_MINB) walks the track
-// groups g = blockIdx.x, blockIdx.x + gridDim.x, ...  While group g is linearised, the per-slot operands of the next
-// group (point / image index, keypoint, depth-prior row) and the descriptor of the one after it are already on their
-// way into shared memory (cp.async, double buffered; the point records and track pointers are asked into L2), so a
-// group starts from shared memory instead of the chain of dependent misses a fresh CTA pays.  Same arithmetic in the
-// same order as k_points: bitwise identical results.
-struct PointsStage {  // operands of one group, one slot per thread
-  int pt[PW_THREADS], img[PW_THREADS];
-  double2 xy[PW_THREADS];
-  double d[PW_THREADS], w[PW_THREADS], a[PW_THREADS];
-};
-template <int BYTES>
-__device__ __forceinline__ void cp_async_ca(void* smem_dst, const void* gmem_src) {
-  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-  asm volatile("cp.async.ca.shared.global [%0], [%1], %2;\n" ::"r"(d), "l"(gmem_src), "n"(BYTES) : "memory");
-}
-
-__global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points_persistent(
-    ProblemView pv, const double* __restrict__ pose, const double* __restrict__ X, LmDiag lm, double* __restrict__ c_pt,
-    int compute_scaling, int jacobi_scaling, double* __restrict__ Hpp, double* __restrict__ gp,
-    double* __restrict__ Hinv, double* __restrict__ Linv, double* __restrict__ fac, double* __restrict__ pt_part,
-    double* __restrict__ scal, int write_factors, int force_warp_path, int num_groups) {
-  __shared__ __align__(16) double2 rows_all[PW_WARPS][256];
-  __shared__ double s_v[PW_THREADS][9];
-  __shared__ double s_le[PW_THREADS][9];
-  __shared__ __align__(16) PointsStage s_op[2];
-  __shared__ __align__(16) int4 s_desc[3];  // ring: this group, the next, the one after
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const size_t N = (size_t)pv.N;
-  const int G = (int)gridDim.x;
-  auto stage = [&](int buf, const int4 d) {
-    if (force_warp_path || d.w > PW_THREADS) return;
-    if (tid < d.w) {
-      const size_t k = (size_t)d.z + tid;
-      PointsStage& o = s_op[buf];
-      cp_async_ca<4>(&o.pt[tid], pv.pm_pt + k);
-      cp_async_ca<4>(&o.img[tid], pv.pm_img + k);
-      cp_async_ca<16>(&o.xy[tid], reinterpret_cast<const double2*>(pv.pm_xy) + k);
-      cp_async_ca<8>(&o.d[tid], pv.pm_depth + k);
-      cp_async_ca<8>(&o.w[tid], pv.pm_depth + N + k);
-      cp_async_ca<8>(&o.a[tid], pv.pm_depth + 2 * N + k);
-    }
-    int slot = 0;
-    l2_prefetch_range(X + 4 * (size_t)d.x, (size_t)d.y * 32, slot, tid);
-    l2_prefetch_range(pv.pt_ptr + d.x, ((size_t)d.y + 1) * 4, slot, tid);
-    l2_prefetch_range(pv.pt_const + d.x, (size_t)d.y, slot, tid);
-  };
-  double gmax = 0.0;
-  int g = blockIdx.x;
-  if (g < num_groups) {
-    const int4 d0 = __ldg(pv.cta_desc + g);
-    if (tid == 0) s_desc[0] = d0;
-    stage(0, d0);
-    if (tid == 0 && g + G < num_groups) cp_async_ca<16>(&s_desc[1], pv.cta_desc + g + G);
-    asm volatile("cp.async.commit_group;\n" ::: "memory");
-  }
-  for (int it = 0; g < num_groups; g += G, ++it) {
-    const int cur = it % 3, nxt = (it + 1) % 3, aft = (it + 2) % 3, buf = it & 1;
-    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-    __syncthreads();  // descriptors visible; every thread is done with the previous group's shared memory
-    const int4 desc = s_desc[cur];
-    if (g + G < num_groups) {
-      stage(buf ^ 1, s_desc[nxt]);
-      if (tid == 0 && g + 2 * G < num_groups) cp_async_ca<16>(&s_desc[aft], pv.cta_desc + g + 2 * G);
-      asm volatile("cp.async.commit_group;\n" ::: "memory");
-    }
-    const int T0 = desc.x, nt = desc.y, base = desc.z, n = desc.w;
-    if (n <= PW_THREADS && !force_warp_path) {
-      int start = 0, len = 0;
-      bool cst = true;
-      if (tid < nt) {
-        const int a = __ldg(pv.pt_ptr + T0 + tid), b = __ldg(pv.pt_ptr + T0 + tid + 1);
-        start = a - base;
-        len = b - a;
-        cst = pv.pt_const[T0 + tid] != 0;
-      }
-      // ---- 1. observations (operands of this thread's slot were copied by this very thread)
-      int tr = -1;
-      double Q[9], prot[3] = {0.0, 0.0, 0.0};
-      if (tid < n) {
-        const PointsStage& op = s_op[buf];
-        const int pt = op.pt[tid];
-        const double2* xp = reinterpret_cast<const double2*>(X + 4 * (size_t)pt);
-        const double2 xa = __ldg(xp), xb = __ldg(xp + 1);
-        if (xb.y == 0.0) {  // slot 3: constant flag
-          tr = pt - T0;
-          const double Xp[3] = {xa.x, xa.y, xb.x};
-          ObsLin o;
-          ImgConst ic;
-          load_img(pv, pose, op.img[tid], ic);
-          const double2 o2 = op.xy[tid];
-          linearize_obs<true, false>(ic.pose, ic.R, Xp, ic.model, ic.prm, o2.x, o2.y, op.d[tid], op.w[tid], op.a[tid],
-                                     ic.b, ic.es, pv.loss, o);
-          double v[9];
-          point_terms(o, ic.R, Q, v);
-#pragma unroll
-          for (int j = 0; j < 9; ++j) s_v[tid][j] = v[j];
-          prot[0] = o.prot[0]; prot[1] = o.prot[1]; prot[2] = o.prot[2];
-        }
-      }
-      const bool act = tr >= 0;
-      __syncthreads();
-      // ---- 2. points
-      if (tid < nt) {
-        const bool active = !cst && len > 0;
-        double v[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-        if (active) {
-          for (int k = 0; k < len; ++k) {
-#pragma unroll
-            for (int j = 0; j < 9; ++j) v[j] += s_v[start + k][j];
-          }
-        }
-        double Li[6], e[3];
-        finalize_point(T0 + tid, active, v, v + 6, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, scal,
-                       Li, e);
-#pragma unroll
-        for (int j = 0; j < 6; ++j) s_le[tid][j] = Li[j];
-#pragma unroll
-        for (int j = 0; j < 3; ++j) s_le[tid][6 + j] = e[j];
-        gmax = fmax(gmax, fmax(fabs(v[6]), fmax(fabs(v[7]), fabs(v[8]))));
-      }
-      if (write_factors) {
-        __syncthreads();
-        // ---- 3. Schur factors
-        double2* rows = rows_all[warp];
-        if (act) {
-          double Lo[6], eo[3];
-#pragma unroll
-          for (int j = 0; j < 6; ++j) Lo[j] = s_le[tr][j];
-#pragma unroll
-          for (int j = 0; j < 3; ++j) eo[j] = s_le[tr][6 + j];
-          double2 rec[8];
-          pack_factor(Q, Lo, prot, eo, rec);
-          const int sw = lane & 7;
-#pragma unroll
-          for (int c = 0; c < 8; ++c) rows[lane * 8 + (c ^ sw)] = rec[c];
-        }
-        const unsigned actmask = __ballot_sync(FULL, act);  // (also orders the shared-memory writes in the warp)
-        double2* fac2 = reinterpret_cast<double2*>(fac);
-        const int g4 = lane >> 3, c = lane & 7;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int item = 4 * j + g4;
-          if ((actmask >> item) & 1u)
-            fac2[(size_t)(base + 32 * warp + item) * 8 + c] = rows[item * 8 + (c ^ (item & 7))];
-        }
-      }
-    } else {
-      const int w = g * PW_WARPS + warp;
-      if (w < min((g + 1) * PW_WARPS, pv.num_track_warps))
-        gmax = fmax(gmax, points_warp_path(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv,
-                                           fac, scal, write_factors, rows_all[warp], w, lane));
-    }
-  }
-  {
-    __shared__ double smx[PW_WARPS + 1];
-    const double m = block_max<PW_WARPS>(gmax, smx);
-    if (tid == 0) pt_part[(size_t)blockIdx.x * PT_PART] = m;
-    // the slots of the other groups this CTA walked are neutral for k_pt_scalars_gmax (a max of magnitudes)
-    for (long long g2 = (long long)blockIdx.x + (long long)G * (1 + tid); g2 < num_groups; g2 += (long long)G * PW_THREADS)
-      pt_part[(size_t)g2 * PT_PART] = 0.0;
   }
 }
 
@@ -1927,21 +1760,6 @@ void launch_points(const ProblemView& pv, const double* pose, const double* X, L
   static const int force_warp = getenv("MPBA_POINTS_WARP") ? atoi(getenv("MPBA_POINTS_WARP")) : 0;
   const char* pf_env = getenv("MPBA_POINTS_PREFETCH");  // CTAs of lookahead of the L2 prefetch (0: off)
   const int prefetch_ahead = pf_env ? atoi(pf_env) : MPBA_POINTS_PREFETCH_DEFAULT;
-  const char* ps_env = getenv("MPBA_POINTS_PERSISTENT");
-  const int persistent = ps_env ? atoi(ps_env) : MPBA_POINTS_PERSISTENT_DEFAULT;
-  if (persistent && pv.num_track_warps > 0) {
-    static int sms = 0;
-    if (!sms) {
-      int dev = 0;
-      cudaGetDevice(&dev);
-      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    }
-    const int groups = track_warp_grid(pv.num_track_warps);
-    const int grid = min(groups, sms * MPBA_POINTS_MINB * (persistent > 1 ? persistent : 1));
-    k_points_persistent<<<grid, PW_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp,
-                                                     Hinv, Linv, fac, pt_part, scal, write_factors, force_warp, groups);
-    return;
-  }
   if (pv.num_track_warps > 0)
     k_points<<<track_warp_grid(pv.num_track_warps), PW_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling,
                                                                          jacobi_scaling, Hpp, gp, Hinv, Linv, fac,

@@ -19,14 +19,12 @@ ap.add_argument("--iters", type=int, default=6)
 ap.add_argument("--points", default="0,148,296,592,1184,2368,4736")
 ap.add_argument("--backsub", default="0,333,666,1332,2664,5328")
 ap.add_argument("--img", default="0,111,222,444,888")
-ap.add_argument("--persistent", default="", help="also time k_points_persistent with these grid multipliers")
 a = ap.parse_args()
 ba = engine.BundleAdjuster(make_config(a.workload, seed=0), device=0)
 
 
-def run(pp, bp, ip=0, persistent=0):
+def run(pp, bp, ip=0):
     os.environ["MPBA_POINTS_PREFETCH"], os.environ["MPBA_BACKSUB_PREFETCH"] = str(pp), str(bp)
-    os.environ["MPBA_POINTS_PERSISTENT"] = str(persistent)
     os.environ["MPBA_IMG_PREFETCH"] = str(ip)
     best = None
     for _ in range(3):
@@ -36,7 +34,7 @@ def run(pp, bp, ip=0, persistent=0):
         key = lambda d: d["points"] + d["back_substitute"] + d["img_chunks"]  # noqa: E731
         if best is None or key(t) < key(best):
             best = t
-    return {"points_prefetch": pp, "backsub_prefetch": bp, "img_prefetch": ip, "points_persistent": persistent, "points_us": round(best["points"], 1),
+    return {"points_prefetch": pp, "backsub_prefetch": bp, "img_prefetch": ip, "points_us": round(best["points"], 1),
             "back_substitute_us": round(best["back_substitute"], 1), "schur_blocks_us": round(best["schur_blocks"], 1),
             "img_chunks_us": round(best["img_chunks"], 1), "final_cost": repr(s.final_cost)}
 
@@ -48,6 +46,5 @@ bb = min([rows[0]] + rows[len(a.points.split(",")):], key=lambda r: r["back_subs
 rows += [run(0, 0, int(i)) for i in a.img.split(",")[1:]]
 bi = min([rows[0]] + [r for r in rows if r["img_prefetch"]], key=lambda r: r["img_chunks_us"])["img_prefetch"]
 rows.append(run(bp, bb, bi))
-rows += [run(bp, bb, bi, int(v)) for v in a.persistent.split(",") if v]
 print(json.dumps({"workload": a.workload, "lm_iterations": a.iters, "rows": rows,
                   "bitwise_same_cost": len({r["final_cost"] for r in rows}) == 1}, indent=1))
