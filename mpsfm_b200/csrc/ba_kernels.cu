@@ -285,7 +285,10 @@ __device__ __forceinline__ void track_obs(const ProblemView& pv, const double* _
 }
 
 constexpr int PT_THREADS = 128;  // k_evaluate: one thread per track
-constexpr int PW_THREADS = 128;  // track-order passes: one thread per OBSERVATION, one warp per packed group of tracks
+#ifndef MPBA_PW_THREADS
+#define MPBA_PW_THREADS 128
+#endif
+constexpr int PW_THREADS = MPBA_PW_THREADS;  // track-order passes: one thread per OBSERVATION, one warp per packed group of tracks
 constexpr int PW_WARPS = PW_THREADS / 32;
 #ifndef MPBA_POINTS_MINB
 #define MPBA_POINTS_MINB 4
@@ -643,7 +646,7 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
     const bool act = tr >= 0;
     if (pf && tid == PW_THREADS - 1) asm volatile("cp.async.wait_group 0;\n" ::: "memory");
     __syncthreads();
-    if (pf) prefetch_track_cta(pv, X, s_next, tid);
+    if (pf && tid < 64) prefetch_track_cta(pv, X, s_next, tid);  // ~60 lines per CTA: two warps cover them
     // ---- 2. points
     if (tid < nt) {
       const bool active = !cst && len > 0;
