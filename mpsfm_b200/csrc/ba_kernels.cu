@@ -95,6 +95,7 @@ __device__ __forceinline__ double block_max(double v, double* sm) {
 constexpr int IMG_THREADS = MPBA_IMG_THREADS;
 // one 128-byte line per thread slot `tid - slot`; slot advances by the number of lines of the range
 __device__ __forceinline__ void l2_prefetch_range(const void* p, size_t bytes, int& slot, int tid) {
+  if (bytes == 0) return;  // never touch a line past the end of an array
   const uintptr_t a0 = reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)127, a1 = reinterpret_cast<uintptr_t>(p) + bytes;
   const int lines = (int)((a1 - a0 + 127) >> 7);
   const int i = tid - slot;
