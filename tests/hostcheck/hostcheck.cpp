@@ -74,4 +74,10 @@ long long hc_filter_tracks(int P, const int* pt_ptr, const double* pose8, const 
   }
   return total;
 }
+double hc_reproj_error2(const double* pose, int model, const double* prm, const double* X, double ox, double oy) {
+  return reproj_error2(pose, model, prm, X, ox, oy);
+}
+double hc_triangulation_angle(const double* c1, const double* c2, const double* X) {
+  return triangulation_angle(c1, c2, X);
+}
 }

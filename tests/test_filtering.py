@@ -176,3 +176,56 @@ def test_optimizer_filter_points3D_host_logic(hostcheck, monkeypatch):
     for pid in pids & set(rec.points3D):
         assert rec.points3D[pid].track.length() >= 2 and 0 <= rec.points3D[pid].error <= 3.0
     assert Optimizer({}, rec, None).filter_points3D(3.0, 1.5, pids) == 0  # idempotent
+
+
+def test_reprojection_error_of_all_camera_models_and_angle_edge_cases(hostcheck):
+    """reproj_error2 (ba_math.cuh) for the 11 COLMAP models against the oracle's projection; points behind the camera;
+    triangulation_angle on exact and degenerate configurations."""
+    from oracle import camera_models, geometry
+
+    hostcheck.hc_reproj_error2.restype = C.c_double
+    hostcheck.hc_triangulation_angle.restype = C.c_double
+    params = {
+        0: [900.0, 500.0, 400.0], 1: [900.0, 950.0, 500.0, 400.0], 2: [900.0, 500.0, 400.0, 0.05],
+        3: [900.0, 500.0, 400.0, 0.05, -0.01], 4: [900.0, 950.0, 500.0, 400.0, 0.05, -0.01, 1e-3, -2e-3],
+        5: [900.0, 950.0, 500.0, 400.0, 0.02, -0.01, 3e-3, -1e-3],
+        6: [900.0, 950.0, 500.0, 400.0, 0.05, -0.01, 1e-3, -2e-3, 3e-3, 0.02, -4e-3, 1e-3],
+        7: [900.0, 950.0, 500.0, 400.0, 0.9], 8: [900.0, 500.0, 400.0, 0.03], 9: [900.0, 500.0, 400.0, 0.03, -0.004],
+        10: [900.0, 950.0, 500.0, 400.0, 0.02, -0.01, 1e-3, -2e-3, 3e-3, -1e-3, 2e-3, -3e-3],
+    }
+    rng = np.random.default_rng(1)
+    for model, p in params.items():
+        prm = np.zeros(12)
+        prm[: len(p)] = p
+        for _ in range(20):
+            q = rng.standard_normal(4)
+            q /= np.linalg.norm(q)
+            t = rng.standard_normal(3)
+            pc = np.array([rng.uniform(-0.4, 0.4), rng.uniform(-0.3, 0.3), 1.0]) * rng.uniform(2.0, 30.0)
+            X = geometry.rotmat(q[None])[0].T @ (pc - t)
+            obs = rng.uniform(0, 1000, 2)
+            pose = np.concatenate([q, t, [1.0]])
+            got = hostcheck.hc_reproj_error2(_p(pose), C.c_int(model), _p(prm), _p(np.ascontiguousarray(X)),
+                                             C.c_double(obs[0]), C.c_double(obs[1]))
+            xy = camera_models.img_from_cam_values(np.array([model]), prm[None], pc[None])[0]
+            want = float(np.sum((xy - obs) ** 2))
+            assert abs(got - want) <= 1e-9 * want
+        # behind the camera (and exactly on the principal plane): COLMAP's "infinite" error
+        for z in (-1.0, 0.0, 1e-17):
+            pose = np.array([0.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0, 1.0])
+            got = hostcheck.hc_reproj_error2(_p(pose), C.c_int(model), _p(prm), _p(np.array([0.1, 0.2, z])),
+                                             C.c_double(0.0), C.c_double(0.0))
+            assert got == np.finfo(np.float64).max
+    ang = lambda a, b, x: hostcheck.hc_triangulation_angle(_p(np.array(a, float)), _p(np.array(b, float)),  # noqa: E731
+                                                           _p(np.array(x, float)))
+    assert abs(ang([1, 0, 0], [0, 1, 0], [0, 0, 0]) - np.pi / 2) < 1e-15          # right angle
+    assert abs(ang([1, 0, 0], [-1, 0, 0], [0, 1, 0]) - np.pi / 2) < 1e-15
+    assert abs(ang([1, 0, 0], [-1, 0, 0], [0, 0.1, 0]) - 2 * np.arctan(0.1)) < 1e-14  # obtuse folds to pi - angle
+    assert ang([0, 0, 0], [0, 0, 0], [0, 0, 0]) == 0.0                            # zero denominator
+    assert ang([1, 2, 3], [4, 5, 6], [1, 2, 3]) == 0.0                            # point on a projection centre
+    a = ang([0, 0, 0], [1e-9, 0, 0], [0, 0, 1e3])                                  # nearly parallel rays
+    assert np.isnan(a) or 0.0 <= a < 1e-8
+    for _ in range(50):
+        c1, c2, x = rng.standard_normal((3, 3))
+        want = filtering.triangulation_angle(c1, c2, x)
+        assert abs(ang(c1, c2, x) - want) <= 1e-14
