@@ -506,6 +506,35 @@ class Optimizer(BaseClass):
                 obs.delete_observation(*o_el[k])
         return num_filtered
 
+    def filter_all_points3D(self, max_reproj_error, min_tri_angle):
+        """``mpsfm_rec.obs.filter_all_points3D`` (mpsfm/sfm/mapper/base.py:748-755): the same rule over every point."""
+        return self.filter_points3D(max_reproj_error, min_tri_angle, set(self.mpsfm_rec.points3D))
+
+    def find_invalid_depth_points(self, imids):
+        """Per image, the 3D points whose keypoint falls on an invalid depth pixel (base.py:757-767)."""
+        collect_risky_p3d = []
+        for imid in imids:
+            image = self.mpsfm_rec.images[imid]
+            pt2D_ids = image.get_observation_point2D_idxs()
+            kps_with3D = image.keypoint_coordinates(pt2D_ids)
+            p3d_ids = np.array(image.point3D_ids(pt2D_ids))
+            valid = np.asarray(image.depth.valid_at_kps(kps_with3D), dtype=bool).reshape(-1)
+            collect_risky_p3d.append(set(int(p) for p in p3d_ids[~valid]))
+        return collect_risky_p3d
+
+    def filter_local_points3D(self, local_bundle, filter_max_reproj_error, filter_min_tri_angle):
+        """``MpsfmMapper.filter_local_points3D`` (base.py:769-797) on the GPU filter: points whose keypoints have no
+        valid depth in every image of the bundle are held to COLMAP's default 1.5 degrees, the bundle's points (and
+        its constant points) to ``filter_min_tri_angle``.  Returns the number of filtered observations."""
+        collect_risky_p3d = self.find_invalid_depth_points(local_bundle["optim_ids"])
+        collect_risky_p3d = set.intersection(*collect_risky_p3d)
+        pts3d = local_bundle["pts3D"]
+        if "constpoints" in local_bundle:
+            pts3d = pts3d.union(local_bundle["constpoints"])
+        num_changed_observations = self.filter_points3D(filter_max_reproj_error, 1.5, collect_risky_p3d)  # default colmap
+        num_changed_observations += self.filter_points3D(filter_max_reproj_error, filter_min_tri_angle, pts3d)
+        return num_changed_observations
+
     def optimize_prior_shiftscale(self, bundle, **kwargs):
         """Closed-form per-image log-scale of the depth prior (:268-274, :187-242)."""
         shift_scale, success = self.__build_shiftscale_problem(bundle, **kwargs)

@@ -229,3 +229,59 @@ def test_reprojection_error_of_all_camera_models_and_angle_edge_cases(hostcheck)
         c1, c2, x = rng.standard_normal((3, 3))
         want = filtering.triangulation_angle(c1, c2, x)
         assert abs(ang(c1, c2, x) - want) <= 1e-14
+
+
+def test_filter_local_points3D_follows_the_mapper(hostcheck, monkeypatch):
+    """MpsfmMapper.filter_local_points3D (reference base.py:769-797) on the Optimizer: risky points (no valid depth in
+    any bundle image) at 1.5 degrees, then the bundle's points at the configured angle."""
+    import copy
+
+    from scene_factory import build_scene
+
+    from mpsfm_b200 import engine
+    from mpsfm_b200.optimizer import Optimizer
+
+    class HostAdjuster:
+        def __init__(self, problem, device=0):
+            self.problem = problem
+
+        def filter_tracks(self, max_err, min_deg, select=None):
+            return host_filter(hostcheck, self.problem, max_err, min_deg, select)
+
+        def close(self):
+            pass
+
+    monkeypatch.setattr(engine, "BundleAdjuster", HostAdjuster)
+    rec = build_scene(seed=4, num_images=8, num_points=260, pose_noise=(0.0, 0.0), point_noise=0.0)
+    rng = np.random.default_rng(2)
+    for pid in list(rec.points3D)[::7]:
+        rec.points3D[pid].xyz += rng.normal(0, 0.4, 3)
+    optim_ids = [5, 4, 6]
+    ref = rec.images[5]
+    pts = set(ref.point3D_ids(ref.get_observation_point2D_idxs()))
+    allp = set()
+    for i in optim_ids:
+        allp |= set(rec.images[i].point3D_ids(rec.images[i].get_observation_point2D_idxs()))
+    bundle = {"optim_ids": optim_ids, "pts3D": pts, "constpoints": allp - pts, "ref_id": 5}
+    opt = Optimizer({}, rec, None)
+    risky = opt.find_invalid_depth_points(optim_ids)
+    assert len(risky) == 3 and all(isinstance(r, set) for r in risky)
+    for imid, r in zip(optim_ids, risky):  # restated independently from the image's own accessors
+        im = rec.images[imid]
+        idx = im.get_observation_point2D_idxs()
+        valid = np.asarray(im.depth.valid_at_kps(im.keypoint_coordinates(idx))).reshape(-1)
+        assert r == {p for p, v in zip(im.point3D_ids(idx), valid) if not v}
+    # expectation: the two pycolmap calls of the reference, through the single-call method on a copy
+    rec2 = copy.deepcopy(rec)
+    opt2 = Optimizer({}, rec2, None)
+    want = opt2.filter_points3D(3.0, 1.5, set.intersection(*risky)) + opt2.filter_points3D(3.0, 2.5, allp)
+    got = opt.filter_local_points3D(bundle, 3.0, 2.5)
+    assert got == want and got > 0
+    assert set(rec.points3D) == set(rec2.points3D)
+    for pid in rec.points3D:
+        a = [(e.image_id, e.point2D_idx) for e in rec.points3D[pid].track.elements]
+        b = [(e.image_id, e.point2D_idx) for e in rec2.points3D[pid].track.elements]
+        assert a == b
+    assert all(rec.points3D[p].track.length() >= 2 for p in rec.points3D)
+    n_before = len(rec.points3D)
+    assert opt.filter_all_points3D(3.0, 2.5) >= 0 and len(rec.points3D) <= n_before
