@@ -119,72 +119,114 @@ def algorithmic_bytes(lay, spec=None):
     }
 
 
-def cpu_baseline_sample(workload: str, max_iters: int = 10, obs_cap: int = 6_000_000, layout=None, pcg_tol: float = 1e-10):
-    """The CPU port of the path (oracle/cpu_port: C++17 + OpenMP, all host threads) on a bounded sample: the first
-    `max_iters` LM iterations of the workload's own scene when it has at most `obs_cap` observations, else of a scene
-    of the same generator scaled down to that size (it/s then scaled by the observation ratio)."""
+def _pyceres_reference_sample(layout_problem):
+    """The REAL reference stack (pycolmap + pyceres, bundle_adjustment.py:104, :285-293) when this box carries it
+    (oracle/pyceres_reference.py; it does not in this image).  Returns None otherwise."""
+    try:
+        from oracle import pyceres_reference as ref
+
+        if not ref.available() or layout_problem is None:
+            return None
+        r = ref.solve(layout_problem)
+        return r
+    except Exception:
+        return None
+
+
+def cpu_baseline_sample(workload: str, max_iters: int = 50, layout=None, pcg_tol: float = 1e-10, budget_s: float = 30.0,
+                        problem=None, probe: bool = True, rate=None):
+    """The CPU arm on the WORKLOAD'S OWN scene (same generator, same seed, same size as the GPU arm -- no
+    extrapolation): oracle/cpu_port (C++17 + OpenMP port of the reference's Ceres path, exact envelope-Cholesky
+    solve of the reduced camera system like SPARSE_SCHUR) on every host thread, the first `max_iters` LM iterations
+    of the solve.  `budget_s` bounds the sample: one LM iteration is timed first and max_iters is cut so that the
+    sample takes about that long.  kind = "reference" only when pycolmap + pyceres are importable on the box."""
     from mpsfm_b200 import engine, synthetic
-    from mpsfm_b200.problem import CameraModel, LossType
     from mpsfm_b200.synthetic import CONFIGS
     from oracle import cpu_port
 
     C, P, L = CONFIGS[workload]
-    n_full = P * L
-    scale = max(1.0, n_full / obs_cap)
-    if layout is None or scale > 1.0:
-        kw = {}
-        if workload in ("cfg3", "cfg4", "cfg5", "target10m"):
-            kw["model"] = CameraModel.SIMPLE_RADIAL
-        if workload == "cfg3":
-            kw["reproj_loss"] = LossType.CAUCHY
-        Cs, Ps = max(12, int(round(C / scale))), max(100, int(round(P / scale)))
-        layout = engine.build_layout(synthetic.make_scene(Cs, Ps, L, seed=0, **kw))
+    if layout is None:
+        problem = synthetic.make_config(workload, seed=0)
+        layout = engine.build_layout(problem)
+    real = _pyceres_reference_sample(problem)
+    if real is not None:
+        return {"value": real["iterations"] / real["seconds"], "unit": UNIT, "cores": os.cpu_count(), "kind": "reference",
+                "sample": f"pycolmap.create_default_bundle_adjuster + pyceres.solve (SPARSE_SCHUR, num_threads=-1) on the "
+                          f"whole {workload} scene: {real['iterations']} LM iterations in {real['seconds']:.1f} s; {real['report']}",
+                "sample_it_per_s": real["iterations"] / real["seconds"], "sample_obs": int(layout.N),
+                "final_cost": real["final_cost"]}
     threads = cpu_port.max_threads()
-    cpu_port.solve(layout, max_num_iterations=1, pcg_tolerance=pcg_tol)  # warm-up: page in, spin up the thread pool
+    if probe or not rate:
+        cpu_port.solve(layout, max_num_iterations=1, pcg_tolerance=pcg_tol)  # warm-up (page in, thread pool)
+        t0 = time.perf_counter()
+        cpu_port.solve(layout, max_num_iterations=2, pcg_tolerance=pcg_tol)  # probe: seconds per LM iteration
+        rate = 2.0 / max(time.perf_counter() - t0, 1e-6)
+    iters_cap = int(max(2, min(max_iters, budget_s * rate)))
     t0 = time.perf_counter()
-    summ, _, _, _ = cpu_port.solve(layout, max_num_iterations=max_iters, pcg_tolerance=pcg_tol)
+    summ, _, _, _ = cpu_port.solve(layout, max_num_iterations=iters_cap, pcg_tolerance=pcg_tol)
     dt = time.perf_counter() - t0
     its = summ["num_iterations"]
     it_s = its / dt
+    whole = summ["termination"] != 1  # not cut by the iteration cap: the whole solve ran
     return {
-        "value": it_s * layout.N / n_full,
+        "value": it_s,
         "unit": UNIT,
         "cores": threads,
         "kind": "port",
-        "sample": (f"oracle/cpu_port (C++17/OpenMP port of the Ceres path, Schur complement + block-Jacobi PCG to {pcg_tol:g}; "
-                   f"pycolmap / pyceres / Ceres are not installable here), {threads} threads, first {its} LM iterations of a "
-                   f"{layout.C} img / {layout.P} pt / {layout.N} obs scene of the workload's generator in {dt:.1f} s"
-                   + ("" if layout.N == n_full else f"; it/s scaled by the observation ratio {layout.N}/{n_full}")),
+        "sample": (f"oracle/cpu_port (C++17/OpenMP port of the reference's Ceres path: trust-region LM, Schur "
+                   f"elimination, exact envelope Cholesky of the reduced camera system under RCM ordering; pycolmap / "
+                   f"pyceres / Ceres are not installable here), {threads} threads, "
+                   + ("the whole solve" if whole else f"the first {its} LM iterations")
+                   + f" of the workload's own scene ({layout.C} img / {layout.P} pt / {layout.N} obs, seed 0): "
+                     f"{its} LM iterations in {dt:.1f} s"),
         "sample_it_per_s": it_s,
         "sample_obs": int(layout.N),
-        "sample_pcg_iterations": summ["total_pcg_iterations"],
+        "sample_lm_iterations": its,
+        "whole_solve": bool(whole),
+        "final_cost": summ["final_cost"],
     }
 
 
 def run_reference(args):
+    """Reference arm: the reference's CPU path on the SAME config, metric and unit as the GPU arm.  A step = one BA
+    solve of the named scene on all host threads (cut to a bounded number of LM iterations only when one solve would
+    exceed --ref-budget seconds).  Under torchrun rank 0 alone runs it -- with every host thread, not the
+    OMP_NUM_THREADS=1 torchrun exports."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    os.environ.pop("OMP_NUM_THREADS", None)
+    from mpsfm_b200 import engine, synthetic
     from mpsfm_b200.synthetic import CONFIGS
 
     C, P, L = CONFIGS[args.workload]
-    times, info = [], None
+    problem = synthetic.make_config(args.workload, seed=0)
+    layout = engine.build_layout(problem)
+    times, iters, info = [], [], None
+    # the whole arm is bounded to about --ref-total seconds: every step gets an equal share (at most --ref-budget)
+    per_step = min(args.ref_budget, args.ref_total / max(args.warmup + args.steps, 1))
     for k in range(args.warmup + args.steps):
-        t0 = time.perf_counter()
-        info = cpu_baseline_sample(args.workload, max_iters=2, obs_cap=args.ref_obs, pcg_tol=args.pcg_tol)
+        info = cpu_baseline_sample(args.workload, layout=layout, problem=problem, pcg_tol=args.pcg_tol,
+                                   budget_s=per_step, probe=(k == 0), rate=(info or {}).get("sample_it_per_s"))
         if k >= args.warmup:
-            times.append(1.0 / info["sample_it_per_s"])  # seconds per LM iteration on the sample
-    mean_dt = float(np.mean(times)) if times else float("nan")
-    val = (1.0 / mean_dt) * info["sample_obs"] / (P * L)
+            times.append(info["sample_lm_iterations"] / info["sample_it_per_s"] if "sample_lm_iterations" in info
+                         else 1.0 / info["sample_it_per_s"])
+            iters.append(info.get("sample_lm_iterations", 1))
+    total_s = float(np.sum(times)) if times else float("nan")
+    val = float(np.sum(iters)) / total_s
     info["value"] = val
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": mean_dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": 1e3 * total_s / max(len(times), 1), "higher_is_better": True,
+        "scaling": "strong" if args.gpus > 1 else "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": args.workload, "images": C, "points": P, "observations": P * L,
-                   "note": "pycolmap / pyceres / Ceres are not installable here; the reference arm is the C++/OpenMP port "
-                           "of the same algorithm (oracle/cpu_port) on all host threads; a step = the first 2 LM "
-                           "iterations of a bounded sample of the workload's scene"},
+                   "same_config_as_gpu_arm": True,
+                   "note": ("the reference's solver stack (pycolmap fork + Ceres 2.1 + pyceres) is not installable here; "
+                            "kind 'port' = oracle/cpu_port, the same algorithm in C++/OpenMP on all host threads, on the "
+                            "workload's own scene (seed 0, full size); a step = one solve, cut to the first LM iterations "
+                            "that fit --ref-budget seconds when it would take longer"),
+                   "lm_iterations_per_step": info.get("sample_lm_iterations"), "final_cost": info.get("final_cost")},
         "cpu_baseline": info,
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -316,13 +358,24 @@ def run_gpu(args):
 
     peak, peak_src = _peaks()
     ab = algorithmic_bytes(lay, spec)
-    top = max((k for k in ktimes if k in ab), key=lambda k: ktimes[k][0], default=None)
+    # the reduced-system solve by SURVEY 8(d)'s K3 formula: k PCG iterations x (288 B + 240 C) per launch; its setup
+    # kernels read S once.  They are latency bound: the fraction is reported, not hidden.
+    if "pcg" in ktimes and ktimes["pcg"][1]:
+        ab["pcg"] = int(pcg_iters / max(iters, 1) * (288 * lay.num_blocks + 240 * lay.C))
+        ab["coarse_setup"] = 288 * lay.num_blocks + 336 * lay.C
+        ab["block_inverse"] = (288 + 288) * lay.C
+    stream = ("img_chunks", "img_cost", "points", "schur_blocks", "back_substitute")
+    top = max((k for k in ktimes if k in ab and k in stream), key=lambda k: ktimes[k][0], default=None)
     roof = None
     per_kernel = {}
+    ms_all = sum(v[0] for v in ktimes.values()) or 1.0
     for k, (ms, n) in sorted(ktimes.items(), key=lambda kv: -kv[1][0]):
-        per_kernel[k] = {"ms_total": round(ms, 3), "launches": n, "avg_us": round(1e3 * ms / max(n, 1), 2)}
-        if k in ab:
-            per_kernel[k]["algorithmic_GBps"] = round(ab[k] / (ms / n * 1e-3) / 1e9, 1)
+        per_kernel[k] = {"ms_total": round(ms, 3), "launches": n, "avg_us": round(1e3 * ms / max(n, 1), 2),
+                         "share_of_kernel_time": round(ms / ms_all, 4)}
+        if k in ab and n:
+            gbs = ab[k] / (ms / n * 1e-3) / 1e9
+            per_kernel[k].update(algorithmic_bytes_per_launch=int(ab[k]), algorithmic_GBps=round(gbs, 1),
+                                 frac_of_measured_hbm=round(gbs / peak, 4))
     if top:
         ms, n = ktimes[top]
         achieved = ab[top] / (ms / n * 1e-3) / 1e9
@@ -336,7 +389,8 @@ def run_gpu(args):
                 "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": ab[top],
                 "avg_launch_ms": ms / n, "frac_of_nominal_8TBps": achieved / 8000.0}
 
-    cpu = cpu_baseline_sample(args.workload, layout=full, pcg_tol=args.pcg_tol) if (world == 1 and not args.no_cpu_baseline) else None
+    cpu = (cpu_baseline_sample(args.workload, layout=full, problem=prob, pcg_tol=args.pcg_tol, budget_s=args.ref_budget)
+           if (world == 1 and not args.no_cpu_baseline) else None)
     C_, P_, L_ = CONFIGS[args.workload]
     line = {
         "metric": METRIC, "value": iters / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -377,8 +431,10 @@ def main():
     ap.add_argument("--workload", default="cfg3")
     ap.add_argument("--pcg-tol", dest="pcg_tol", type=float, default=1e-10)
     ap.add_argument("--pcg-max-iter", dest="pcg_max_iter", type=int, default=2000)
-    ap.add_argument("--ref-obs", dest="ref_obs", type=int, default=1_000_000,
-                    help="reference arm: observations of the bounded sample scene")
+    ap.add_argument("--ref-budget", dest="ref_budget", type=float, default=30.0,
+                    help="CPU arm: seconds one step may take; longer solves are cut to their first LM iterations")
+    ap.add_argument("--ref-total", dest="ref_total", type=float, default=150.0,
+                    help="reference arm: seconds all its steps together may take (bounds --ref-budget per step)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sharding", default="shard", choices=["shard", "replicas"])
     args = ap.parse_args()

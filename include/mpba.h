@@ -166,6 +166,12 @@ typedef struct mpba_options {
                                               grid-wide otherwise), 1: force grid-wide, 2: prefer cluster */
   int32_t pcg_coarse;                      /* 0: two-level preconditioner (block-Jacobi + gauge-mode coarse space over
                                               groups of images) with the cluster kernel, 1: block-Jacobi only */
+  int32_t behind_camera;                   /* point at z < epsilon in the camera frame.  0 (default): COLMAP >= 3.11's
+                                              ReprojErrorCostFunctor -- ImgFromCam fails and the block contributes a ZERO
+                                              residual and Jacobian; such observations are counted in
+                                              mpba_summary.num_behind_camera.  1: strict -- the projection is evaluated as
+                                              written (inf / nan) and a non-finite initial cost returns MPBA_E_NUMERIC */
+  int32_t reserved;
 } mpba_options;
 
 /* ceres::IterationSummary subset, one row per LM iteration (row 0 = initial evaluation) */
@@ -191,7 +197,7 @@ typedef struct mpba_summary {
   double solve_ms;           /* device time of the whole call (CUDA events) */
   mpba_iteration* iterations;/* HOST buffer with capacity rows, caller-owned; may be NULL */
   int32_t capacity;
-  int32_t reserved;
+  int32_t num_behind_camera; /* observations at z < epsilon in their camera frame at the returned state */
   char message[128];
 } mpba_summary;
 
@@ -255,7 +261,12 @@ int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspac
                         int32_t* pcg_iterations);
 
 /* Trust-region Levenberg-Marquardt (Ceres 2.1 TrustRegionMinimizer semantics); updates img_pose
- * and pt_xyz in place to the best state visited. */
+ * and pt_xyz in place to the best state visited.
+ * Error convention of the reference (bundle_adjustment.py:266, :283, :285-293): pyceres.solve never raises, a
+ * failed solve is only visible in the summary.  Likewise here: a non-finite initial cost (e.g. a depth prior on a
+ * point with z <= 0, or nan inputs) returns MPBA_OK with termination = MPBA_FAILURE and leaves img_pose / pt_xyz
+ * untouched, as Ceres does when the initial residual evaluation fails.  (opt->behind_camera = 1 restores the loud
+ * MPBA_E_NUMERIC.) */
 int mpba_solve(mpba_handle* h, const mpba_problem* prob, void* workspace, size_t workspace_bytes,
                const mpba_options* opt, mpba_summary* summary);
 

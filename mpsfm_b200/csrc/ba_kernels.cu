@@ -1684,6 +1684,29 @@ __global__ void __launch_bounds__(PT_THREADS) k_filter_tracks(ProblemView pv, co
   if (threadIdx.x == 0 && total != 0.0) atomicAdd(scal + S_FILTERED, total);
 }
 
+// Observations whose point sits at z < epsilon in the camera frame (the reprojection blocks the COLMAP >= 3.11 rule
+// zeroes, ba_math.cuh: linearize_obs): one thread per owned track like k_evaluate, once per solve.  Integer count, so
+// the double atomicAdd is exact and order independent.
+__global__ void __launch_bounds__(PT_THREADS) k_count_behind(ProblemView pv, const double* __restrict__ pose,
+                                                             const double* __restrict__ X, double* __restrict__ out) {
+  const int p = pv.p0 + blockIdx.x * PT_THREADS + threadIdx.x;
+  int behind = 0;
+  if (p < pv.p1) {
+    double Xp[3];
+    load_point(X, p, Xp);
+    for (int k = pv.pt_ptr[p]; k < pv.pt_ptr[p + 1]; ++k) {
+      const double* ps = pose + 8 * (size_t)__ldg(pv.pm_img + k);
+      double R[9];
+      quat_to_rotmat(ps, R);
+      const double pz = R[6] * Xp[0] + R[7] * Xp[1] + R[8] * Xp[2] + ps[6];
+      behind += pz < DBL_EPSILON ? 1 : 0;
+    }
+  }
+  __shared__ double sm[PT_THREADS / 32 + 1];
+  const double total = block_sum<PT_THREADS / 32>((double)behind, sm);
+  if (threadIdx.x == 0 && total != 0.0) atomicAdd(out, total);
+}
+
 // COLMAP normalises every quaternion before it enters the problem
 __global__ void k_normalize_poses(int C, const double* __restrict__ in, const double* __restrict__ shift_scale,
                                   double* __restrict__ out) {
@@ -1737,8 +1760,8 @@ __global__ void k_expand_hcc(int C, const double* __restrict__ Hc, double* __res
 // launchers
 // ================================================================================================
 void launch_img_chunks(const ProblemView& pv, const double* pose, const double* X, double* chunk_part, cudaStream_t st) {
-  const char* pf_env = getenv("MPBA_IMG_PREFETCH");  // CTAs of lookahead of the L2 prefetch (0: off)
-  const int prefetch_ahead = pf_env ? atoi(pf_env) : MPBA_IMG_PREFETCH_DEFAULT;
+  // CTAs of lookahead of the L2 prefetch (0: off); the environment is read once per process
+  static const int prefetch_ahead = getenv("MPBA_IMG_PREFETCH") ? atoi(getenv("MPBA_IMG_PREFETCH")) : MPBA_IMG_PREFETCH_DEFAULT;
   if (pv.num_chunks > 0)
     k_img_chunks<<<pv.num_chunks, IMG_THREADS, 0, st>>>(pv, pose, X, chunk_part, prefetch_ahead);
 }
@@ -1762,8 +1785,7 @@ void launch_points(const ProblemView& pv, const double* pose, const double* X, L
                    int compute_scaling, int jacobi_scaling, double* Hpp, double* gp, double* Hinv, double* Linv,
                    double* fac, double* pt_part, double* scal, int write_factors, cudaStream_t st) {
   static const int force_warp = getenv("MPBA_POINTS_WARP") ? atoi(getenv("MPBA_POINTS_WARP")) : 0;
-  const char* pf_env = getenv("MPBA_POINTS_PREFETCH");  // CTAs of lookahead of the L2 prefetch (0: off)
-  const int prefetch_ahead = pf_env ? atoi(pf_env) : MPBA_POINTS_PREFETCH_DEFAULT;
+  static const int prefetch_ahead = getenv("MPBA_POINTS_PREFETCH") ? atoi(getenv("MPBA_POINTS_PREFETCH")) : MPBA_POINTS_PREFETCH_DEFAULT;
   if (pv.num_track_warps > 0)
     k_points<<<track_warp_grid(pv.num_track_warps), PW_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling,
                                                                          jacobi_scaling, Hpp, gp, Hinv, Linv, fac,
@@ -1837,8 +1859,7 @@ void launch_cam_update(const ProblemView& pv, const double* pose, const double* 
 void launch_back_substitute(const ProblemView& pv, const double* X, const double* y, const double* Hpp,
                             const double* gp, const double* Linv, const double* c_pt, const double* fac,
                             int use_factors, LmDiag lm, double* X_cand, double* pt_part, cudaStream_t st) {
-  const char* pf_env = getenv("MPBA_BACKSUB_PREFETCH");  // CTAs of lookahead of the L2 prefetch (0: off)
-  const int prefetch_ahead = pf_env ? atoi(pf_env) : MPBA_BACKSUB_PREFETCH_DEFAULT;
+  static const int prefetch_ahead = getenv("MPBA_BACKSUB_PREFETCH") ? atoi(getenv("MPBA_BACKSUB_PREFETCH")) : MPBA_BACKSUB_PREFETCH_DEFAULT;
   if (pv.num_track_warps > 0)
     k_back_substitute<<<track_warp_grid(pv.num_track_warps), PW_THREADS, 0, st>>>(pv, X, y, Hpp, gp, Linv, c_pt, fac,
                                                                                   use_factors, lm, X_cand, pt_part,
@@ -1857,6 +1878,9 @@ void launch_filter_tracks(const ProblemView& pv, const double* pose, const doubl
   if (pv.p1 > pv.p0)
     k_filter_tracks<<<points_grid(pv.p1 - pv.p0), PT_THREADS, 0, st>>>(pv, pose, X, max_err2, min_angle, pt_select,
                                                                        obs_keep, pt_keep, pt_error, scal);
+}
+void launch_count_behind(const ProblemView& pv, const double* pose, const double* X, double* out, cudaStream_t st) {
+  if (pv.p1 > pv.p0) k_count_behind<<<points_grid(pv.p1 - pv.p0), PT_THREADS, 0, st>>>(pv, pose, X, out);
 }
 void launch_normalize_poses(int C, const double* in, const double* shift_scale, double* out, cudaStream_t st) {
   if (C > 0) k_normalize_poses<<<(C + 127) / 128, 128, 0, st>>>(C, in, shift_scale, out);

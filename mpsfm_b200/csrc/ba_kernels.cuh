@@ -209,6 +209,8 @@ void launch_evaluate(const ProblemView& pv, const double* pose, const double* X,
 void launch_filter_tracks(const ProblemView& pv, const double* pose, const double* X, double max_err2, double min_angle,
                           const uint8_t* pt_select, uint8_t* obs_keep, uint8_t* pt_keep, double* pt_error, double* scal,
                           cudaStream_t st);
+// out[0] += observations of this rank's tracks whose point is at z < epsilon in the camera frame
+void launch_count_behind(const ProblemView& pv, const double* pose, const double* X, double* out, cudaStream_t st);
 // unit quaternions (COLMAP normalises before adding to the problem) + exp(log-scale) into slot 7
 void launch_normalize_poses(int C, const double* in, const double* shift_scale, double* out, cudaStream_t st);
 void launch_flag_points(int P, const uint8_t* pt_const, double* X, cudaStream_t st);

@@ -387,6 +387,10 @@ MPBA_HD void mul_chol_inverse_t(const double Q[9], const double Li[6], double Z[
 struct LossSpec {
   int reproj_loss, depth_loss;
   double reproj_scale, reproj_weight;
+  // 0 (default): COLMAP >= 3.11's ReprojErrorCostFunctor -- ImgFromCam fails for a point at z < epsilon in the camera
+  // frame and the functor then returns a ZERO residual (and, through the jets, a zero Jacobian) instead of inf;
+  // 1: strict -- the projection is evaluated as written (inf / nan residual, the solve reports it)
+  int behind_strict;
 };
 
 struct ObsLin {
@@ -409,32 +413,42 @@ MPBA_HD void linearize_obs(const double* pose, const double R[9], const double X
   o.prot[2] = R[6] * X[0] + R[7] * X[1] + R[8] * X[2];
   const double px = o.prot[0] + pose[4], py = o.prot[1] + pose[5], pz = o.prot[2] + pose[6];
   const double iz = 1.0 / pz, u = px * iz, v = py * iz;
-  double x, y, D[4];
-  if (WANT_JAC) {
-    img_from_cam_jac(model, prm, u, v, x, y, D);
-  } else {
-    img_from_cam_generic<double>(model, prm, u, v, x, y);
+  const bool behind = !ls.behind_strict && pz < DBL_EPSILON;
+  double r0 = 0.0, r1 = 0.0, rho = 0.0, rho1 = 0.0;
+  double x, y, D[4] = {0.0, 0.0, 0.0, 0.0};
+  if (!behind) {
+    if (WANT_JAC) {
+      img_from_cam_jac(model, prm, u, v, x, y, D);
+    } else {
+      img_from_cam_generic<double>(model, prm, u, v, x, y);
+    }
+    r0 = x - ox;
+    r1 = y - oy;
+    loss_eval<WANT_RHO>(ls.reproj_loss, ls.reproj_scale, ls.reproj_weight, r0 * r0 + r1 * r1, rho, rho1);
   }
-  const double r0 = x - ox, r1 = y - oy;
   o.r[0] = r0;
   o.r[1] = r1;
-  double rho, rho1;
-  loss_eval<WANT_RHO>(ls.reproj_loss, ls.reproj_scale, ls.reproj_weight, r0 * r0 + r1 * r1, rho, rho1);
   o.rho = rho;
   double a0[3], a1[3];
   if (WANT_JAC) {
-    // rows of d(x,y)/dp = D * [[1/z, 0, -u/z], [0, 1/z, -v/z]]
-    a0[0] = D[0] * iz; a0[1] = D[1] * iz; a0[2] = -(D[0] * u + D[1] * v) * iz;
-    a1[0] = D[2] * iz; a1[1] = D[3] * iz; a1[2] = -(D[2] * u + D[3] * v) * iz;
-    o.N[0] = rho1 * (a0[0] * a0[0] + a1[0] * a1[0]);
-    o.N[1] = rho1 * (a0[0] * a0[1] + a1[0] * a1[1]);
-    o.N[2] = rho1 * (a0[0] * a0[2] + a1[0] * a1[2]);
-    o.N[3] = rho1 * (a0[1] * a0[1] + a1[1] * a1[1]);
-    o.N[4] = rho1 * (a0[1] * a0[2] + a1[1] * a1[2]);
-    o.N[5] = rho1 * (a0[2] * a0[2] + a1[2] * a1[2]);
-    o.h[0] = rho1 * (a0[0] * r0 + a1[0] * r1);
-    o.h[1] = rho1 * (a0[1] * r0 + a1[1] * r1);
-    o.h[2] = rho1 * (a0[2] * r0 + a1[2] * r1);
+    if (behind) {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) o.N[j] = 0.0;
+      o.h[0] = o.h[1] = o.h[2] = 0.0;
+    } else {
+      // rows of d(x,y)/dp = D * [[1/z, 0, -u/z], [0, 1/z, -v/z]]
+      a0[0] = D[0] * iz; a0[1] = D[1] * iz; a0[2] = -(D[0] * u + D[1] * v) * iz;
+      a1[0] = D[2] * iz; a1[1] = D[3] * iz; a1[2] = -(D[2] * u + D[3] * v) * iz;
+      o.N[0] = rho1 * (a0[0] * a0[0] + a1[0] * a1[0]);
+      o.N[1] = rho1 * (a0[0] * a0[1] + a1[0] * a1[1]);
+      o.N[2] = rho1 * (a0[0] * a0[2] + a1[0] * a1[2]);
+      o.N[3] = rho1 * (a0[1] * a0[1] + a1[1] * a1[1]);
+      o.N[4] = rho1 * (a0[1] * a0[2] + a1[1] * a1[2]);
+      o.N[5] = rho1 * (a0[2] * a0[2] + a1[2] * a1[2]);
+      o.h[0] = rho1 * (a0[0] * r0 + a1[0] * r1);
+      o.h[1] = rho1 * (a0[1] * r0 + a1[1] * r1);
+      o.h[2] = rho1 * (a0[2] * r0 + a1[2] * r1);
+    }
   }
   o.r[2] = 0.0;
   if (w > 0.0) {

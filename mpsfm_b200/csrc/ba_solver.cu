@@ -227,6 +227,7 @@ ProblemView view_of(const mpba_problem* p) {
   v.u_block = p->u_block; v.u_item_ptr = p->u_item_ptr; v.item_a = p->item_a; v.item_b = p->item_b;
   v.loss.reproj_loss = p->reproj_loss; v.loss.depth_loss = p->depth_loss;
   v.loss.reproj_scale = p->reproj_loss_scale; v.loss.reproj_weight = p->reproj_loss_weight;
+  v.loss.behind_strict = 0;
   v.p0 = 0; v.p1 = v.P; v.i0 = 0; v.i1 = v.C;
   v.num_track_warps = p->num_track_warps; v.tw_first = p->track_warp_first;
   return v;
@@ -697,6 +698,7 @@ void mpba_default_options(mpba_options* o) {
   o->verbose = 0;
   o->pcg_kernel = 0;
   o->pcg_coarse = 0;
+  o->behind_camera = 0;
 }
 
 int mpba_create(mpba_handle** out, int device, void* cuda_stream) {
@@ -964,10 +966,12 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
   mpba_options opt;
   if (opt_in) opt = *opt_in; else mpba_default_options(&opt);
   reset_profile(h, opt.profile);
+  c.pv.loss.behind_strict = opt.behind_camera == 1 ? 1 : 0;
   rc = build_pcg_cluster_plan(c, prob, opt.pcg_kernel, opt.pcg_coarse);
   if (rc) return rc;
   rc = build_grid_coarse_plan(c, prob, opt.pcg_coarse);
   if (rc) return rc;
+  sum->num_behind_camera = 0;
   mpba_iteration* its = sum->iterations;
   const int cap = its ? sum->capacity : 0;
   int nrows = 0;
@@ -1003,12 +1007,28 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
   const double fixed_cost = 0.5 * h->h_scal[S_COST_FIXED];
   double gmax_c = h->h_scal[S_GMAX_C];
   if (!isfinite(x_cost)) {
+    // Ceres: "Residual and Jacobian evaluation failed" at iteration 0 -> FAILURE, user parameters untouched, and
+    // pyceres.solve does not raise (bundle_adjustment.py:285-293 only logs the summary).  Same here; the loud
+    // return is kept for behind_camera = 1.
     snprintf(sum->message, sizeof(sum->message), "Initial cost is not finite.");
     sum->termination = MPBA_FAILURE;
     sum->initial_cost = sum->final_cost = x_cost;
     sum->fixed_cost = fixed_cost;
     sum->num_iterations = 0;
-    return fail(h, MPBA_E_NUMERIC, "initial cost is not finite (point behind a camera or bad input)");
+    sum->num_successful_steps = sum->num_unsuccessful_steps = 0;
+    sum->total_pcg_iterations = 0;
+    sum->kernel_launches = h->launch_count;
+    sum->solve_ms = 0.0;
+    if (nrows == 0) {
+      mpba_iteration it0;
+      memset(&it0, 0, sizeof(it0));
+      it0.cost = x_cost;
+      push(it0);
+    }
+    if (opt.behind_camera == 1)
+      return fail(h, MPBA_E_NUMERIC, "initial cost is not finite (point behind a camera or bad input)");
+    h->err = "initial cost is not finite: solve skipped, state untouched";
+    return MPBA_OK;
   }
   double radius = opt.initial_trust_region_radius, decrease_factor = 2.0;
   double minimum_cost = x_cost;
@@ -1164,11 +1184,18 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
   CU(cudaMemcpyAsync(prob->img_pose, c.w.pose[cur], (size_t)c.pv.C * 8 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
   if (c.pv.P > 0)
     CU(cudaMemcpyAsync(prob->pt_xyz, c.w.X[cur], (size_t)c.pv.P * 4 * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+  // observations the COLMAP >= 3.11 rule zeroed at the returned state (one launch per solve)
+  CU(cudaMemsetAsync(c.w.scal, 0, sizeof(double), h->stream));
+  launch_count_behind(c.pv, c.w.pose[cur], c.w.X[cur], c.w.scal, h->stream);
+  h->launch_count += 1;
+  if (c.sh && c.sh->world > 1) NC(nccl_api().AllReduce(c.w.scal, c.w.scal, 1, ncclDouble, ncclSum, h->comm, h->stream));
+  CU(cudaMemcpyAsync(h->h_scal, c.w.scal, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaEventRecord(h->ev1, h->stream));
   CU(cudaStreamSynchronize(h->stream));
   if (h->profile) flush_timers(h);
   float ms = 0.f;
   cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+  sum->num_behind_camera = (int32_t)h->h_scal[0];
 
   sum->initial_cost = initial_cost_free + fixed_cost;
   sum->final_cost = minimum_cost + fixed_cost;

@@ -90,6 +90,7 @@ class MpbaOptions(C.Structure):
         ("function_tolerance", C.c_double), ("gradient_tolerance", C.c_double),
         ("parameter_tolerance", C.c_double), ("pcg_tolerance", C.c_double),
         ("profile", C.c_int32), ("verbose", C.c_int32), ("pcg_kernel", C.c_int32), ("pcg_coarse", C.c_int32),
+        ("behind_camera", C.c_int32), ("reserved", C.c_int32),
     ]
 
 
@@ -109,7 +110,7 @@ class MpbaSummary(C.Structure):
         ("num_successful_steps", C.c_int32), ("num_unsuccessful_steps", C.c_int32),
         ("total_pcg_iterations", C.c_int64), ("kernel_launches", C.c_int64),
         ("solve_ms", C.c_double),
-        ("iterations", C.POINTER(MpbaIteration)), ("capacity", C.c_int32), ("reserved", C.c_int32),
+        ("iterations", C.POINTER(MpbaIteration)), ("capacity", C.c_int32), ("num_behind_camera", C.c_int32),
         ("message", C.c_char * 128),
     ]
 
@@ -576,6 +577,7 @@ class SolveSummary:
     kernel_launches: int
     solve_ms: float
     iterations: list  # of dicts
+    num_behind_camera: int = 0  # observations at z < epsilon in their camera frame at the returned state
 
     def brief_report(self) -> str:
         return (f"mpba: iterations {self.num_iterations}, initial cost {self.initial_cost:.6e}, final cost "
@@ -895,6 +897,7 @@ class BundleAdjuster:
             num_iterations=sm.num_iterations, num_successful_steps=sm.num_successful_steps,
             num_unsuccessful_steps=sm.num_unsuccessful_steps, total_pcg_iterations=int(sm.total_pcg_iterations),
             kernel_launches=int(sm.kernel_launches), solve_ms=sm.solve_ms, iterations=its,
+            num_behind_camera=int(sm.num_behind_camera),
         )
 
     def kernel_times(self):

@@ -329,7 +329,12 @@ class Optimizer(BaseClass):
                 depths, p2Ds, p3Ds = depths[mask], p2Ds[mask], p3Ds[mask]
                 magnitudes, params = magnitudes[mask], params[mask]
                 depth_rows[imid] = {"p2Ds": p2Ds, "p3Ds": p3Ds, "depths": depths, "magnitudes": magnitudes, "params": params}
-                d_obs.append(img_obs_offset[imid] + np.searchsorted(img_p2ds[imid], p2Ds))
+                pos = np.searchsorted(img_p2ds[imid], p2Ds)
+                if not np.array_equal(img_p2ds[imid][np.minimum(pos, img_p2ds[imid].size - 1)], p2Ds):
+                    # get_observation_point2D_idxs() of this pycolmap build is not ascending: look the rows up
+                    where = {int(v): k for k, v in enumerate(img_p2ds[imid])}
+                    pos = np.array([where[int(v)] for v in p2Ds], dtype=np.int64)
+                d_obs.append(img_obs_offset[imid] + pos)
                 d_d.append(depths)
                 d_w.append(magnitudes)
                 d_a.append(params)
@@ -382,7 +387,12 @@ class Optimizer(BaseClass):
             q, t, X = ba.state()
         finally:
             ba.close()
-        self._write_back(assembly, q, t, X)
+        if summary.termination == "FAILURE" and summary.num_iterations == 0:
+            # Ceres' FAILURE at the initial evaluation (e.g. a depth prior on a point with z <= 0): pyceres.solve
+            # does not raise and the reference ignores the summary (:285-293, :266, :283) -- parameters stay put
+            self.log(f"bundle adjustment skipped: {summary.message}", level=1)
+        else:
+            self._write_back(assembly, q, t, X)
         self.last_summary = summary
         self.log(summary.brief_report(), level=2)
         return summary

@@ -20,6 +20,12 @@ DEFAULT_PARAMS = {
     CameraModel.SIMPLE_RADIAL: [1200.0, 800.0, 600.0, 0.02],
     CameraModel.RADIAL: [1200.0, 800.0, 600.0, 0.02, -0.005],
     CameraModel.OPENCV: [1200.0, 1190.0, 800.0, 600.0, 0.02, -0.005, 1e-3, -5e-4],
+    CameraModel.OPENCV_FISHEYE: [1200.0, 1190.0, 800.0, 600.0, 0.02, -0.01, 3e-3, -1e-3],
+    CameraModel.FULL_OPENCV: [1200.0, 1190.0, 800.0, 600.0, 0.05, -0.01, 1e-3, -2e-3, 3e-3, 0.02, -4e-3, 1e-3],
+    CameraModel.FOV: [1200.0, 1190.0, 800.0, 600.0, 0.9],
+    CameraModel.SIMPLE_RADIAL_FISHEYE: [1200.0, 800.0, 600.0, 0.03],
+    CameraModel.RADIAL_FISHEYE: [1200.0, 800.0, 600.0, 0.03, -0.004],
+    CameraModel.THIN_PRISM_FISHEYE: [1200.0, 1190.0, 800.0, 600.0, 0.02, -0.01, 1e-3, -2e-3, 3e-3, -1e-3, 2e-3, -3e-3],
 }
 
 # named shapes: (images, points, observations per point)
@@ -111,6 +117,38 @@ def _distort(model: CameraModel, params, u, v):
         du = u * rad + 2 * p[6] * u * v + p[7] * (r2 + 2 * u * u)
         dv = v * rad + 2 * p[7] * u * v + p[6] * (r2 + 2 * v * v)
         return p[0] * (u + du) + p[2], p[1] * (v + dv) + p[3]
+    if model == CameraModel.FULL_OPENCV:
+        r4 = r2 * r2
+        rad = (1 + p[4] * r2 + p[5] * r4 + p[8] * r4 * r2) / (1 + p[9] * r2 + p[10] * r4 + p[11] * r4 * r2)
+        x = u * rad + 2 * p[6] * u * v + p[7] * (r2 + 2 * u * u)
+        y = v * rad + 2 * p[7] * u * v + p[6] * (r2 + 2 * v * v)
+        return p[0] * x + p[2], p[1] * y + p[3]
+    if model == CameraModel.FOV:
+        # the generator only draws omega, r well inside the closed-form branch (COLMAP switches to series below 1e-4)
+        r = np.sqrt(r2)
+        f = np.arctan(2 * r * np.tan(p[4] / 2)) / (r * p[4])
+        return p[0] * u * f + p[2], p[1] * v * f + p[3]
+    # fisheye family: (u, v) scaled by theta_d / r, theta = atan(r)
+    r = np.sqrt(r2)
+    th = np.arctan(r)
+    t2 = th * th
+    if model == CameraModel.OPENCV_FISHEYE:
+        s = th * (1 + t2 * (p[4] + t2 * (p[5] + t2 * (p[6] + t2 * p[7])))) / r
+        return p[0] * u * s + p[2], p[1] * v * s + p[3]
+    if model == CameraModel.SIMPLE_RADIAL_FISHEYE:
+        s = th * (1 + p[3] * t2) / r
+        return p[0] * u * s + p[1], p[0] * v * s + p[2]
+    if model == CameraModel.RADIAL_FISHEYE:
+        s = th * (1 + t2 * (p[3] + t2 * p[4])) / r
+        return p[0] * u * s + p[1], p[0] * v * s + p[2]
+    if model == CameraModel.THIN_PRISM_FISHEYE:
+        uu, vv = u * th / r, v * th / r
+        q2 = uu * uu + vv * vv
+        q4 = q2 * q2
+        rad = p[4] * q2 + p[5] * q4 + p[8] * q4 * q2 + p[9] * q4 * q4
+        du = uu * rad + 2 * p[6] * uu * vv + p[7] * (q2 + 2 * uu * uu) + p[10] * q2
+        dv = vv * rad + 2 * p[7] * uu * vv + p[6] * (q2 + 2 * vv * vv) + p[11] * q2
+        return p[0] * (uu + du) + p[2], p[1] * (vv + dv) + p[3]
     raise NotImplementedError(f"synthetic generator does not draw {model!r}")
 
 

@@ -20,11 +20,16 @@ _lib = None
 
 
 def build(force: bool = False) -> str:
-    """g++ -O3 -fopenmp (x86-64-v3: the GPU boxes' host CPUs are newer than that)."""
-    if force or not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in _DEPS):
-        subprocess.check_call(["g++", "-O3", "-march=x86-64-v3", "-fopenmp", "-std=c++17", "-fPIC", "-shared", "-x", "c++",
-                               SRC, "-o", LIB])
-    return LIB
+    """g++ -O3 -fopenmp.  Built -march=x86-64-v3 (AVX2 + FMA) HERE, because the library travels to the GPU box
+    prebuilt and that box's host CPU is a different model (-march=native of the build container could emit
+    instructions it lacks); set MPBA_CPU_PORT_NATIVE=1 to build -march=native on the machine that will run it
+    (bench.py's reference arm does, and falls back to the prebuilt library when no compiler is there)."""
+    native = os.environ.get("MPBA_CPU_PORT_NATIVE") == "1"
+    lib = LIB.replace(".so", "_native.so") if native else LIB
+    if force or not os.path.exists(lib) or any(os.path.getmtime(d) > os.path.getmtime(lib) for d in _DEPS):
+        subprocess.check_call(["g++", "-O3", "-march=native" if native else "-march=x86-64-v3", "-fopenmp", "-std=c++17",
+                               "-fPIC", "-shared", "-x", "c++", SRC, "-o", lib])
+    return lib
 
 
 def _load():
@@ -32,7 +37,13 @@ def _load():
     if _lib is None:
         from mpsfm_b200 import engine
 
-        _lib = C.CDLL(build())
+        try:
+            path = build()
+        except (OSError, subprocess.CalledProcessError):
+            if not os.path.exists(LIB):
+                raise
+            path = LIB  # no compiler on this box: the prebuilt x86-64-v3 library
+        _lib = C.CDLL(path)
         _lib.ba_cpu_solve.argtypes = [C.POINTER(engine.MpbaProblem), C.POINTER(engine.MpbaOptions),
                                       C.POINTER(engine.MpbaSummary), C.c_int]
         _lib.ba_cpu_max_threads.restype = C.c_int
@@ -40,15 +51,26 @@ def _load():
 
 
 def max_threads() -> int:
-    return int(_load().ba_cpu_max_threads())
+    """Host threads the port runs on by default: every CPU this process may use.  (NOT omp_get_max_threads():
+    torchrun exports OMP_NUM_THREADS=1 to its workers, which would time the reference arm on one core.)"""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
 
 
-def solve(layout, max_num_iterations: int = 50, pcg_tolerance: float = 1e-10, num_threads: int = 0):
+def solve(layout, max_num_iterations: int = 50, pcg_tolerance: float = 1e-10, num_threads: int = 0,
+          linear_solver: str = "cholesky"):
     """Run the LM loop on a ``mpsfm_b200.engine.HostLayout``.  Returns (summary dict, q [C,4], t [C,3], X [P,3]);
-    the layout's arrays are not modified."""
+    the layout's arrays are not modified.  ``linear_solver``: "cholesky" (exact envelope Cholesky of the reduced
+    camera system, what Ceres' SPARSE_SCHUR does) or "pcg" (block-Jacobi PCG to ``pcg_tolerance``).
+    ``num_threads`` 0 = every hardware thread (torchrun exports OMP_NUM_THREADS=1: that is overridden here)."""
     from mpsfm_b200 import engine
 
     lib = _load()
+    lib.ba_cpu_set_linear_solver(1 if linear_solver == "pcg" else 0)
+    if num_threads <= 0:
+        num_threads = max_threads()
     keep = {}
     prob = engine.MpbaProblem()
     for name in engine._DEVICE_FIELDS:

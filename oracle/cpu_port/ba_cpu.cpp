@@ -12,15 +12,18 @@
 // host.  The independent restatement used for PARITY stays the numpy oracle (oracle/lm.py); tests/test_cpu_port.py
 // pins this port to it (same iteration count, costs to 1e-9).
 //
-// Differences to Ceres that matter for the timing: the reduced camera system is solved with block-Jacobi PCG to
-// 1e-10 (Ceres' SPARSE_SCHUR factorises it with CHOLMOD); everything else (evaluation, Schur elimination,
-// back-substitution, step evaluation) has the same operation count per observation.
+// The reduced camera system is solved EXACTLY, as Ceres' SPARSE_SCHUR does with CHOLMOD: an envelope (skyline)
+// Cholesky of S under a reverse Cuthill-McKee ordering of the images (SkylineCholesky below; the ordering and the
+// envelope are computed once per solve, like Ceres' symbolic factorisation).  ba_cpu_set_linear_solver(1) switches
+// to the block-Jacobi PCG (to 1e-10) the first round timed.  Everything else (evaluation, Schur elimination,
+// back-substitution, step evaluation) has the same operation count per observation as the reference's path.
 #include <float.h>
 #include <math.h>
 #include <omp.h>
 #include <string.h>
 
 #include <algorithm>
+#include <queue>
 #include <vector>
 
 #include "../../include/mpba.h"
@@ -330,6 +333,122 @@ int pcg(const mpba_problem* p, const double* S, const double* rhs, double* x, do
   return it;
 }
 
+
+// ---- exact solve of the reduced camera system ------------------------------------------------------------------
+// Reverse Cuthill-McKee on the block graph of S, then a scalar envelope Cholesky: row i keeps L[i][first[i] .. i].
+// Fixed tangent coordinates are identity rows of S (schur_blocks), so S is positive definite whenever Ceres' is.
+struct SkylineCholesky {
+  int C = 0, n = 0;
+  std::vector<int> order, pos;      // order[new block] = old block, pos[old] = new
+  std::vector<int> first;           // per scalar row (new numbering): first column of its envelope
+  std::vector<size_t> rowp;         // start of row i in L
+  std::vector<double> L, b;
+
+  void analyze(const mpba_problem* p) {
+    C = p->num_images;
+    n = 6 * C;
+    std::vector<int> deg(C);
+    for (int i = 0; i < C; ++i) deg[i] = p->s_row_ptr[i + 1] - p->s_row_ptr[i];
+    std::vector<char> seen(C, 0);
+    order.clear();
+    order.reserve(C);
+    auto bfs = [&](int root, std::vector<int>& out, std::vector<char>& mark) {
+      out.clear();
+      std::queue<int> q;
+      q.push(root);
+      mark[root] = 1;
+      std::vector<int> nb;
+      while (!q.empty()) {
+        const int v = q.front();
+        q.pop();
+        out.push_back(v);
+        nb.clear();
+        for (int e = p->s_row_ptr[v]; e < p->s_row_ptr[v + 1]; ++e) {
+          const int w = p->s_col[e];
+          if (!mark[w]) { mark[w] = 1; nb.push_back(w); }
+        }
+        std::sort(nb.begin(), nb.end(), [&](int a, int c) { return deg[a] != deg[c] ? deg[a] < deg[c] : a < c; });
+        for (int w : nb) q.push(w);
+      }
+    };
+    std::vector<int> comp;
+    for (int s0 = 0; s0 < C; ++s0) {
+      if (seen[s0]) continue;
+      // pseudo-peripheral start: the last vertex of a BFS from the component's first vertex
+      std::vector<char> tmp(seen);
+      bfs(s0, comp, tmp);
+      const int start = comp.back();
+      bfs(start, comp, seen);
+      order.insert(order.end(), comp.begin(), comp.end());
+    }
+    std::reverse(order.begin(), order.end());
+    pos.assign(C, 0);
+    for (int k = 0; k < C; ++k) pos[order[k]] = k;
+    first.assign(n, 0);
+    for (int k = 0; k < C; ++k) {
+      const int i = order[k];
+      int lo = k;
+      for (int e = p->s_row_ptr[i]; e < p->s_row_ptr[i + 1]; ++e) lo = std::min(lo, pos[p->s_col[e]]);
+      for (int r = 0; r < 6; ++r) first[6 * k + r] = 6 * lo;
+    }
+    rowp.assign(n + 1, 0);
+    for (int i = 0; i < n; ++i) rowp[i + 1] = rowp[i] + (size_t)(i - first[i] + 1);
+    L.assign(rowp[n], 0.0);
+    b.assign(n, 0.0);
+  }
+
+  // returns false when S is not positive definite (Ceres: linear solver failure -> invalid step)
+  bool solve(const mpba_problem* p, const double* S, const double* rhs, double* x) {
+    std::fill(L.begin(), L.end(), 0.0);
+    for (int k = 0; k < C; ++k) {
+      const int i = order[k];
+      for (int e = p->s_row_ptr[i]; e < p->s_row_ptr[i + 1]; ++e) {
+        const int kj = pos[p->s_col[e]];
+        if (kj > k) continue;
+        const double* Sb = S + (size_t)e * 36;
+        for (int r = 0; r < 6; ++r)
+          for (int c = 0; c < 6; ++c) {
+            const int row = 6 * k + r, col = 6 * kj + c;
+            if (col <= row) L[rowp[row] + (size_t)(col - first[row])] = Sb[6 * r + c];
+          }
+      }
+      for (int r = 0; r < 6; ++r) b[6 * k + r] = rhs[6 * i + r];
+    }
+    for (int i = 0; i < n; ++i) {
+      double* Li = &L[rowp[i]] - first[i];
+      for (int j = first[i]; j <= i; ++j) {
+        const double* Lj = &L[rowp[j]] - first[j];
+        const int k0 = std::max(first[i], first[j]);
+        double s = Li[j];
+        for (int k = k0; k < j; ++k) s -= Li[k] * Lj[k];
+        if (j < i) {
+          Li[j] = s / Lj[j];
+        } else {
+          if (!(s > 0.0) || !std::isfinite(s)) return false;
+          Li[i] = sqrt(s);
+        }
+      }
+    }
+    for (int i = 0; i < n; ++i) {  // L z = b
+      const double* Li = &L[rowp[i]] - first[i];
+      double s = b[i];
+      for (int k = first[i]; k < i; ++k) s -= Li[k] * b[k];
+      b[i] = s / Li[i];
+    }
+    for (int i = n - 1; i >= 0; --i) {  // L^T y = z
+      const double* Li = &L[rowp[i]] - first[i];
+      const double v = b[i] / Li[i];
+      b[i] = v;
+      for (int k = first[i]; k < i; ++k) b[k] -= Li[k] * v;
+    }
+    for (int k = 0; k < C; ++k)
+      for (int r = 0; r < 6; ++r) x[6 * order[k] + r] = b[6 * k + r];
+    return true;
+  }
+};
+
+int g_linear_solver = 0;  // 0: envelope Cholesky (exact, like SPARSE_SCHUR), 1: block-Jacobi PCG
+
 // y_p = L^-T (e - sum Z^T G y_c), candidate points, point part of the model cost change, step norms
 void back_substitute(const mpba_problem* p, const double* X, const double* y, const double* Hpp, const double* gp,
                      const double* Linv, const double* c_pt, const double* fac, bool use_factors, Lm lm, double* Xc,
@@ -433,6 +552,7 @@ extern "C" int ba_cpu_solve(const mpba_problem* prob, const mpba_options* opt_in
   std::vector<double> gc[2] = {std::vector<double>(C * 6), std::vector<double>(C * 6)};
   std::vector<double> c_img(C * 6), c_pt(P * 3), Hpp(P * 6), gp(P * 3), Linv(P * 9), fac(structure_only ? 0 : N * 16),
       S(B * 36), rhs(C * 6), y(C * 6, 0.0);
+  SkylineCholesky chol;
   int cur = 0;
   for (size_t i = 0; i < C; ++i) {  // COLMAP normalises the quaternions; slot 7 = exp(log-scale) of the depth prior
     const double* s = p->img_pose + 8 * i;
@@ -499,7 +619,12 @@ extern "C" int ba_cpu_solve(const mpba_problem* prob, const mpba_options* opt_in
     int pcg_it = 0, pcg_flag = 0;
     if (!structure_only) {
       schur_blocks(p, fac.data(), Hc[cur].data(), gc[cur].data(), c_img.data(), lm, S.data(), rhs.data());
-      pcg_it = pcg(p, S.data(), rhs.data(), y.data(), opt.pcg_tolerance, opt.pcg_max_iterations, pcg_flag);
+      if (g_linear_solver == 1) {
+        pcg_it = pcg(p, S.data(), rhs.data(), y.data(), opt.pcg_tolerance, opt.pcg_max_iterations, pcg_flag);
+      } else {
+        if (chol.n == 0) chol.analyze(p);
+        pcg_flag = chol.solve(p, S.data(), rhs.data(), y.data()) ? 0 : 2;
+      }
     }
     double mcc_c, s2c, x2c, mcc_p, s2p, x2p;
     cam_update(p, pose[cur].data(), y.data(), Hc[cur].data(), gc[cur].data(), c_img.data(), lm, pose[cand].data(), mcc_c,
@@ -592,3 +717,4 @@ extern "C" int ba_cpu_solve(const mpba_problem* prob, const mpba_options* opt_in
 }
 
 extern "C" int ba_cpu_max_threads(void) { return omp_get_max_threads(); }
+extern "C" void ba_cpu_set_linear_solver(int which) { g_linear_solver = which == 1 ? 1 : 0; }

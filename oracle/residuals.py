@@ -98,6 +98,15 @@ def evaluate(problem, state: State | None = None, jacobians: bool = True) -> Lin
     else:
         xy = camera_models.img_from_cam_values(model, params, pc)
     r_rep = xy - problem.obs_xy
+    # COLMAP >= 3.11 ReprojErrorCostFunctor (upstream src/colmap/estimators/cost_functions.h; the generation of COLMAP
+    # that has create_default_bundle_adjuster, bundle_adjustment.py:104): ImgFromCam returns false for a point at
+    # z < epsilon in the camera frame and the functor then writes ZERO residuals -- jets included, so the block's
+    # Jacobian is zero too.  (Unverifiable here: the fork is absent.  PARITY UNPINNED like the rest of this file.)
+    behind = pc[:, 2] < np.finfo(np.float64).eps
+    if behind.any():
+        r_rep[behind] = 0.0
+        if jacobians:
+            dxy_dp[behind] = 0.0
 
     # depth prior rows
     nd = problem.depth_obs.shape[0]

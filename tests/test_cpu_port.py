@@ -26,6 +26,21 @@ def test_cpu_port_follows_the_oracle_trajectory(kw):
     assert np.max(np.abs(t - osum.state.t)) < 1e-6 and np.max(np.abs(X - osum.state.X)) < 1e-6
 
 
+def test_cpu_port_exact_solve_and_pcg_agree_on_a_ring():
+    """The envelope Cholesky (default: what SPARSE_SCHUR does) and the block-Jacobi PCG land on the same trajectory;
+    60 images on a closed ring exercise the reverse Cuthill-McKee ordering (the band wraps around)."""
+    prob = make_scene(60, 1500, 5, seed=4)
+    lay = engine.build_layout(prob)
+    a, qa, ta, Xa = cpu_port.solve(lay)
+    b, qb, tb, Xb = cpu_port.solve(lay, linear_solver="pcg", pcg_tolerance=1e-12)
+    assert a["num_iterations"] == b["num_iterations"] and a["total_pcg_iterations"] == 0 < b["total_pcg_iterations"]
+    assert np.max(np.abs(np.array(a["costs"]) - np.array(b["costs"])) / np.array(a["costs"])) <= 1e-9
+    assert np.max(np.abs(ta - tb)) < 1e-7 and np.max(np.abs(Xa - Xb)) < 1e-7
+    osum = lm.solve(prob)
+    assert a["num_iterations"] == len(osum.iterations) - 1
+    assert abs(a["final_cost"] - osum.final_cost) <= 1e-6 * osum.final_cost
+
+
 def test_cpu_port_structure_only_and_threads():
     prob = make_scene(10, 400, 5, seed=2, depth_loss=LossType.TRIVIAL)
     prob.img_free_mask[:] = 0  # refine_3d_points: every pose constant

@@ -8,7 +8,8 @@ import pytest
 from mpsfm_b200 import engine
 from mpsfm_b200.problem import CameraModel, LossType
 from mpsfm_b200.synthetic import make_scene
-from oracle import lm
+from oracle import geometry, lm
+from oracle.residuals import State, evaluate
 
 pytestmark = pytest.mark.gpu
 
@@ -59,12 +60,62 @@ def test_no_observations_at_all():
         assert np.array_equal(a, b)
 
 
-def test_point_behind_the_camera_fails_loudly():
-    prob = make_scene(6, 60, 3, seed=2, depth_prior=True)
-    prob.pt_xyz[0] = prob.pt_xyz[0] * -50.0  # far behind its cameras: log of a negative depth ratio
+def _behind_scene(depth_prior):
+    prob = make_scene(8, 200, 4, seed=2, depth_prior=depth_prior)
+    # mirror three points through the ring: behind every camera that observes them
+    # (constant points: a free point behind a camera drifts towards z = 0, where 1 / z makes any comparison fragile)
+    for p in (0, 17, 90):
+        prob.pt_xyz[p] = prob.pt_xyz[p] * -12.0
+        prob.pt_const[p] = 1
+    return prob
+
+
+def test_point_behind_the_camera_is_a_zero_block_like_colmap():
+    """Default policy (mpba_options.behind_camera = 0): COLMAP >= 3.11's cost functor writes a zero residual when
+    ImgFromCam fails (z < eps); the solve carries on -- the reference never fails here (bundle_adjustment.py:266,
+    :283).  Residuals, normal equations and the whole trajectory against the oracle, which states the same rule."""
+    prob = _behind_scene(depth_prior=False)
+    ba = engine.BundleAdjuster(prob, device=0)
+    rr, rd, cost, fixed = ba.evaluate()
+    ref = evaluate(prob, State.of(prob), jacobians=False)
+    pz = (geometry.quat_rotate(State.of(prob).q[prob.obs_img], prob.pt_xyz[prob.obs_pt]) + prob.img_t[prob.obs_img])[:, 2]
+    behind = np.flatnonzero(pz < np.finfo(float).eps)
+    assert behind.size >= 3 and np.all(rr[behind] == 0.0) and np.all(ref.r_reproj[behind] == 0.0)
+    assert np.max(np.abs(rr - ref.r_reproj) / (np.abs(ref.r_reproj) + 1e-6)) < 1e-9
+    assert abs(cost - ref.cost) <= 1e-12 * ref.cost
+    summ = ba.solve()
+    osum = lm.solve(prob)
+    assert summ.termination == osum.termination and summ.num_iterations == len(osum.iterations) - 1
+    assert abs(summ.final_cost - osum.final_cost) <= 1e-6 * osum.final_cost
+    q, t, X = ba.state()
+    assert np.max(np.abs(t - osum.state.t)) < 1e-6
+    pz1 = (geometry.quat_rotate(osum.state.q[prob.obs_img], osum.state.X[prob.obs_pt]) + osum.state.t[prob.obs_img])[:, 2]
+    assert summ.num_behind_camera == int(np.sum(pz1 < np.finfo(float).eps)) > 0
+
+
+def test_non_finite_initial_cost_is_a_failed_solve_not_an_exception():
+    """A depth prior on a point with z <= 0 gives log(negative) = nan: Ceres' initial evaluation fails, pyceres.solve
+    returns FAILURE without raising and the parameters stay put (bundle_adjustment.py:285-293 ignores the summary).
+    Same here: MPBA_OK, termination FAILURE, state bitwise untouched."""
+    prob = _behind_scene(depth_prior=True)
+    ba = engine.BundleAdjuster(prob, device=0)
+    before = [a.copy() for a in ba.state()]
+    summ = ba.solve()
+    assert summ.termination == "FAILURE" and summ.num_iterations == 0
+    assert not np.isfinite(summ.initial_cost)
+    for a, b in zip(ba.state(), before):
+        assert np.array_equal(a, b)
+    # the handle stays usable
+    prob2 = make_scene(6, 60, 3, seed=2)
+    ba2 = engine.BundleAdjuster(prob2, device=0)
+    assert ba2.solve().termination == "CONVERGENCE"
+
+
+def test_point_behind_the_camera_strict_mode_is_loud():
+    prob = _behind_scene(depth_prior=True)
     ba = engine.BundleAdjuster(prob, device=0)
     with pytest.raises(engine.EngineError):
-        ba.solve()
+        ba.solve(engine.default_options(behind_camera=1))
 
 
 def test_two_images_minimal_gauge():

@@ -21,6 +21,15 @@ SCENES = {
     "radial_trivial_partial_depth": dict(model=CameraModel.RADIAL, reproj_loss=LossType.TRIVIAL,
                                          depth_loss=LossType.SOFT_L1, depth_frac=0.5, const_point_frac=0.1),
     "simple_pinhole_nodepth": dict(model=CameraModel.SIMPLE_PINHOLE, depth_prior=False),
+    # the six models whose Jacobians come from forward duals on the device: nvcc's FMA
+    # contraction and the device atan / tan are only visible on the CUDA path
+    "opencv_fisheye_softl1": dict(model=CameraModel.OPENCV_FISHEYE),
+    "full_opencv_cauchy": dict(model=CameraModel.FULL_OPENCV, reproj_loss=LossType.CAUCHY),
+    "fov_huber": dict(model=CameraModel.FOV, reproj_loss=LossType.HUBER),
+    "simple_radial_fisheye_softl1": dict(model=CameraModel.SIMPLE_RADIAL_FISHEYE, depth_frac=0.6),
+    "radial_fisheye_trivial": dict(model=CameraModel.RADIAL_FISHEYE, reproj_loss=LossType.TRIVIAL),
+    "thin_prism_fisheye_cauchy": dict(model=CameraModel.THIN_PRISM_FISHEYE, reproj_loss=LossType.CAUCHY,
+                                      const_point_frac=0.05),
 }
 
 
@@ -128,6 +137,42 @@ def test_full_solve_matches_oracle(scene):
     assert t[1, 0] == q0.t[1, 0]
     const = prob.pt_const != 0
     assert np.array_equal(X[const], prob.pt_xyz[const])
+
+
+@pytest.mark.parametrize("case", ["fov_small_omega", "fov_small_radius", "fisheye_on_axis"])
+def test_camera_model_branches_on_device(case):
+    """The series branches of FOV (omega^2 < 1e-4; r^2 < 1e-4) and the r <= eps branch of the fisheye family, on the
+    CUDA path: a scene whose points sit (nearly) on the optical axes, residuals and normal-equation blocks."""
+    if case == "fov_small_omega":
+        prob = make_scene(8, 300, 4, model=CameraModel.FOV, seed=4)
+        prob.cam_params[0, 4] = 5e-3
+    elif case == "fov_small_radius":
+        prob = make_scene(8, 300, 4, model=CameraModel.FOV, seed=4)
+    else:
+        prob = make_scene(8, 300, 4, model=CameraModel.RADIAL_FISHEYE, seed=4)
+    if case != "fov_small_omega":
+        # move a third of the points onto the optical axis of their first observing image (u, v ~ 0 or exactly 0)
+        R = geometry.rotmat(prob.img_q)
+        first = {}
+        for o in range(prob.num_obs):
+            first.setdefault(int(prob.obs_pt[o]), int(prob.obs_img[o]))
+        for p_, i in list(first.items())[::3]:
+            centre = -R[i].T @ prob.img_t[i]
+            depth = 35.0 + (p_ % 7)
+            off = np.array([1e-3, 2e-3, 0.0]) * (p_ % 2) if case == "fov_small_radius" else np.zeros(3)
+            prob.pt_xyz[p_] = centre + R[i].T @ (np.array([0.0, 0.0, depth]) + off * depth)
+    ba = engine.BundleAdjuster(prob, device=0)
+    rr, rd, cost, fixed = ba.evaluate()
+    ref = evaluate(prob, State.of(prob), jacobians=False)
+    assert np.max(np.abs(rr - ref.r_reproj) / (np.abs(ref.r_reproj) + 1e-6)) < 1e-9
+    assert abs(cost - ref.cost) <= 1e-12 * max(ref.cost, 1.0)
+    Hcc, gc, Hpp, gp, _, _ = ba.linearize()
+    lin = evaluate(prob, State.of(prob), jacobians=True)
+    freec = free_columns(prob).astype(float)
+    freep = np.repeat((prob.pt_const == 0)[:, None], 3, axis=1).astype(float)
+    ne = lm.NormalEquations(prob, lin, freec, freep)
+    assert relerr(Hcc, ne.Hcc) < 1e-11 and relerr(gc, ne.gc) < 1e-11
+    assert relerr(Hpp, ne.Hpp) < 1e-11 and relerr(gp, ne.gp) < 1e-11
 
 
 def test_structure_only_refine_3d_points():
