@@ -379,6 +379,79 @@ int mpba_segmented_median(mpba_handle* h, int32_t n, const double* values, int32
                           const int32_t* seg_ptr, void* workspace, size_t workspace_bytes, double* out_median,
                           double* out_mad, void* cuda_stream);
 
+
+/* ---- depth-map integration with normal priors ------------------------------------------------
+ * The step right before every bundle adjustment in the reference (mpsfm/sfm/mapper/base.py:637-644 integrate_bundle
+ * -> mpsfm/sfm/scene/image/integration.py:133-137 Image.integrate -> :383-520 Integration._integrate): per image, an
+ * IRLS loop on the log-depth map z over the H x W grid,
+ *     min  sum wu+ (A1 z + nx)^2 + wu- (A2 z + nx)^2 + wv+ (A3 z + ny)^2 + wv- (A4 z + ny)^2
+ *          + lambda1 prec_d (z_prior - z)^2 + lambda2 prec_s (log z_sparse - z)^2                      (:139-165)
+ * with one-sided difference operators A1..A4 scaled by the normals (:631-680), sigmoid discontinuity weights
+ * (:358-376), the normal equations of every step (:167-234, :445-453) solved by Jacobi-preconditioned CG with the
+ * reference's settings (warm start, rtol = cg_tol, scipy/cupy `cg` semantics, :455-466), and the reference's
+ * termination rules and per-image state (integrated, energy_old, cached wu / wv).  Replaces the cupy csr_matrix +
+ * cupyx cg library calls by ONE kernel launch for a whole batch of images: one thread-block cluster per image, the
+ * five-point operator applied matrix-free, cluster-wide dot products through distributed shared memory.
+ * Every pointer in a job is a DEVICE pointer; the job / result arrays themselves are HOST arrays. */
+#define MPBA_INT_MAX_IRLS 32
+typedef struct mpba_integration_conf {
+  int32_t max_iter;                 /* 10    IRLS steps (<= MPBA_INT_MAX_IRLS) */
+  int32_t cg_max_iter;              /* 5000 */
+  double tol;                       /* 5e-2  relative energy change */
+  double step_size;                 /* 1 */
+  double cg_tol;                    /* 1e-3  rtol of cg */
+  double lambda1, lambda2;          /* 1, 1 */
+  double k;                         /* 1     sigmoid slope */
+  double large_number;              /* 1e6   normal variance of invalid pixels */
+  double depth_magnitude_multiplier, normals_magnitude_multiplier; /* 1, 1 */
+  double scale_filter_factor;       /* 1.5; 0 = scale filter off (conf.scale_filter = False) */
+} mpba_integration_conf;            /* Image.default_conf, mpsfm/sfm/scene/image/base.py:36-53 */
+
+typedef struct mpba_integration_job {
+  int32_t H, W;                     /* grid of the prior maps (camera.nshape) */
+  int32_t num_sparse;               /* triangulated points projected into this image (:95-120) */
+  int32_t integrated;               /* in: the image was integrated before (IntVars.integrated): wu / wv / energy_old hold its state */
+  double K[4];                      /* [K11 sy, K00 sx, K12 sy, K02 sx] as _prepare_integration_variables builds it (:123-129) */
+  const double* depth_prior;        /* [H][W] depth.data_prior */
+  const double* uncertainty;        /* [H][W] depth.uncertainty (variance) */
+  const uint8_t* valid;             /* [H][W] depth.valid */
+  const double* normals;            /* [H][W][3] normals.data */
+  const double* normals_uncertainty;/* [H][W][3][3] normals.uncertainty (only the diagonal is read, :276-278) */
+  const int32_t* sparse_xy;         /* [num_sparse][2] integer pixel (x, y) = (kps * (sx, sy) + 0.5).astype(int), inside the grid */
+  const double* sparse_depth;       /* [num_sparse] depth3d */
+  const double* sparse_zvar;        /* [num_sparse] zvars3d */
+  double* depth;                    /* [H][W] in: depth.data (start), out: refined depth when result.updated */
+  double* wu;                       /* [H*W] in (integrated) / out: cached discontinuity weights */
+  double* wv;
+  double energy_old;                /* in: IntVars.energy_old (read when integrated) */
+  double* variance;                 /* mpba_integration_variances only: [H*W] out, y = Hessian^-1 1 (see below) */
+} mpba_integration_job;
+
+typedef struct mpba_integration_result {
+  int32_t updated;                  /* _integrate's return value: depth was replaced */
+  int32_t integrated;               /* IntVars.integrated after the call */
+  int32_t irls_steps;               /* IRLS steps run */
+  int32_t cg_iterations;            /* total */
+  double energy_old;                /* IntVars.energy_old after the call */
+  double energy[MPBA_INT_MAX_IRLS + 1]; /* energy before the loop and after every step */
+  int32_t cg_steps[MPBA_INT_MAX_IRLS];  /* CG iterations of every step */
+} mpba_integration_result;
+
+void mpba_integration_default_conf(mpba_integration_conf* conf);
+int mpba_integration_workspace_bytes(int32_t num_jobs, const mpba_integration_job* jobs, size_t* bytes);
+int mpba_integrate_depth(mpba_handle* h, int32_t num_jobs, const mpba_integration_job* jobs,
+                         const mpba_integration_conf* conf, void* workspace, size_t workspace_bytes,
+                         mpba_integration_result* results);
+/* Variance propagation (integration.py:522-616: calculate_hessian + IntegrationUncertainty.solve).  The reference
+ * factorises the Hessian of the integration energy at the current depth (fresh weights; sparse term unfiltered and only
+ * when !ignore_depths) with cholespy and, for every query pixel, solves H x = e_pixel and takes x.sum() -- the COLUMN
+ * SUM of H^-1.  H is symmetric, so all those numbers are entries of ONE vector y = H^-1 1: job.variance receives y
+ * (PCG to relative residual var_tol), the caller reads y[round(y_px) * W + round(x_px)] and multiplies by
+ * depth_prior_at_kps^2 (:612-615).  result.cg_iterations = PCG iterations. */
+int mpba_integration_variances(mpba_handle* h, int32_t num_jobs, const mpba_integration_job* jobs,
+                               const mpba_integration_conf* conf, int32_t ignore_depths, double var_tol, void* workspace,
+                               size_t workspace_bytes, mpba_integration_result* results);
+
 /* After a call with opt->profile: per-kernel summed device ms and launch counts (HOST arrays of
  * MPBA_NUM_KERNELS); names from mpba_kernel_name(slot). */
 int mpba_kernel_times(const mpba_handle* h, double* ms, int64_t* launches);

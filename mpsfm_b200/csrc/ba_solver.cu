@@ -57,6 +57,17 @@ struct mpba_handle {
   int rank = 0, world = 1;
 };
 
+// accessors for the other translation units of the library (integrate.cu): the handle's layout stays private here
+namespace mpba {
+cudaStream_t handle_stream(mpba_handle* h) { return h->stream; }
+int handle_device(mpba_handle* h) { return h->device; }
+int handle_fail(mpba_handle* h, int code, const std::string& msg) {
+  if (h) h->err = msg;
+  return code;
+}
+void handle_count_launches(mpba_handle* h, int n) { h->launch_count += n; }
+}  // namespace mpba
+
 namespace {
 
 // Coarse groups of the two-level preconditioner: beyond 18 groups (126 modes) the dense inverse of the coarse matrix

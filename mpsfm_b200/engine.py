@@ -122,6 +122,8 @@ EXPORTS = (
     "mpba_pack_tracks", "mpba_sample_maps", "mpba_depth_prior_terms", "mpba_segmented_median_workspace_bytes",
     "mpba_segmented_median", "mpba_gather_observations", "mpba_host_layout_create", "mpba_host_layout_destroy",
     "mpba_host_gather", "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
+    "mpba_integration_default_conf", "mpba_integration_workspace_bytes", "mpba_integrate_depth",
+    "mpba_integration_variances",
 )
 
 _lib = None

@@ -30,6 +30,13 @@ def test_struct_sizes_match_the_c_abi():
     assert C.sizeof(engine.MpbaIteration) == 64
     assert C.sizeof(engine.MpbaOptions) == 16 + 10 * 8 + 24
     assert C.sizeof(engine.MpbaProblem) % 8 == 0
+    from mpsfm_b200 import integration
+
+    assert C.sizeof(integration.MpbaIntegrationConf) == 8 + 10 * 8
+    assert C.sizeof(integration.MpbaIntegrationJob) == 16 + 32 + 11 * 8 + 8 + 8
+    assert C.sizeof(integration.MpbaIntegrationResult) == 16 + 8 + 33 * 8 + 32 * 4
+    conf = integration.default_conf()
+    assert (conf.max_iter, conf.cg_max_iter, conf.tol, conf.cg_tol, conf.scale_filter_factor) == (10, 5000, 5e-2, 1e-3, 1.5)
 
 
 def test_create_without_gpu_fails_loudly():
