@@ -171,7 +171,10 @@ typedef struct mpba_options {
                                               residual and Jacobian; such observations are counted in
                                               mpba_summary.num_behind_camera.  1: strict -- the projection is evaluated as
                                               written (inf / nan) and a non-finite initial cost returns MPBA_E_NUMERIC */
-  int32_t reserved;
+  int32_t coarse_lag;                      /* 1 (default): the dense inverse of the coarse matrix is a preconditioner --
+                                              the PCG of linear solve i uses the one built from S of solve i - 1 and
+                                              solve i's own is built on a side stream, overlapping the kernels that
+                                              follow; 0: rebuilt on the solve stream before every PCG */
 } mpba_options;
 
 /* ceres::IterationSummary subset, one row per LM iteration (row 0 = initial evaluation) */
@@ -202,7 +205,7 @@ typedef struct mpba_summary {
 } mpba_summary;
 
 /* names of the kernels for mpba_kernel_times, in slot order */
-#define MPBA_NUM_KERNELS 13
+#define MPBA_NUM_KERNELS 14
 
 typedef struct mpba_handle mpba_handle;
 

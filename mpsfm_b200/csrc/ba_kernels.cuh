@@ -191,7 +191,9 @@ struct CoarsePlan {
 };
 cudaError_t launch_coarse_setup(const CoarsePlan& cp, int C, const double* pose, const uint8_t* free_mask,
                                 const int32_t* s_row, const int32_t* s_col, const double* S, double* Zc, double* Ac,
-                                double* Ainv, cudaStream_t st);
+                                double* Ainv, cudaStream_t st, cudaEvent_t after_assemble = nullptr);
+// the gauge modes alone (Z of every image at the given poses)
+cudaError_t launch_coarse_modes(int C, const double* pose, const uint8_t* free_mask, double* Zc, cudaStream_t st);
 
 // ---- step ---------------------------------------------------------------------------------------
 // q (+) -y, t - y, step norms, and the image part of the model cost change (g'y + y'Dy) / 2

@@ -26,11 +26,11 @@ using namespace mpba;
 
 enum KernelSlot {
   KS_IMG_CHUNKS = 0, KS_IMG_FINALIZE, KS_POINTS_SCHUR, KS_S_FINALIZE, KS_PCG, KS_CAM_UPDATE, KS_BACK_SUBSTITUTE,
-  KS_REDUCE, KS_EVALUATE, KS_MISC, KS_COARSE, KS_BLOCK_INVERSE, KS_COLLECTIVE
+  KS_REDUCE, KS_EVALUATE, KS_MISC, KS_COARSE, KS_BLOCK_INVERSE, KS_COLLECTIVE, KS_COARSE_SIDE
 };
 static const char* kKernelNames[MPBA_NUM_KERNELS] = {
     "img_chunks", "img_finalize", "points", "schur_blocks", "pcg", "cam_update", "back_substitute",
-    "reduce", "evaluate", "misc", "coarse_setup", "block_inverse", "nccl_collectives"};
+    "reduce", "evaluate", "misc", "coarse_setup", "block_inverse", "nccl_collectives", "coarse_setup_side_stream"};
 
 struct TimedEvent {
   cudaEvent_t a, b;
@@ -52,6 +52,10 @@ struct mpba_handle {
   int pcg_grid_sms = 0;
   int32_t* h_stage = nullptr;  // pinned staging for the PCG cluster plan
   size_t h_stage_ints = 0;
+  // side stream of the lagged coarse-space setup: the dense inverse of iteration i is built while the
+  // stream kernels of iteration i run and is used by the PCG of iteration i + 1
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_s_ready = nullptr, ev_asm_done = nullptr, ev_inv_done[2] = {nullptr, nullptr};
   // sharded solve (mpba_comm_init)
   ncclComm_t comm = nullptr;
   int rank = 0, world = 1;
@@ -98,7 +102,9 @@ struct Timer {
   mpba_handle* h;
   int slot;
   size_t idx = (size_t)-1;
-  Timer(mpba_handle* h_, int slot_, int nkernels = 1) : h(h_), slot(slot_) {
+  cudaStream_t st;
+  Timer(mpba_handle* h_, int slot_, int nkernels = 1, cudaStream_t st_ = nullptr, bool other = false)
+      : h(h_), slot(slot_), st(other ? st_ : h_->stream) {
     h->launch_count += nkernels;
     h->launches[slot] += nkernels;
     if (!h->profile) return;
@@ -111,10 +117,10 @@ struct Timer {
     }
     idx = h->used++;
     h->pool[idx].slot = slot;
-    cudaEventRecord(h->pool[idx].a, h->stream);
+    cudaEventRecord(h->pool[idx].a, st);
   }
   ~Timer() {
-    if (idx != (size_t)-1) cudaEventRecord(h->pool[idx].b, h->stream);
+    if (idx != (size_t)-1) cudaEventRecord(h->pool[idx].b, st);
   }
 };
 
@@ -133,6 +139,7 @@ struct Workspace {
   double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *img_part, *c_img, *c_pt, *Hpp, *gp, *Hinv, *fac, *S,
       *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal, *scal_all, *Linv, *tpart;
   double *Zc = nullptr, *Ac = nullptr, *Ainv = nullptr;  // coarse space (coarse.cu)
+  double *Zc2 = nullptr, *Ainv2 = nullptr;               // lagged setup: the side stream's own Z, the second inverse
   int32_t* pm_pt = nullptr;   // point of every track-order slot (launch_track_setup)
   int4* cta_desc = nullptr;   // per CTA of the track-order passes
   int4* warp_desc = nullptr;  // per warp group
@@ -192,6 +199,8 @@ void carve(const mpba_problem* p, const mpba_shard* sh, char* base, Workspace& w
     w.Zc = take(so ? 0 : C * 42);
     w.Ac = take(so ? 0 : (size_t)COARSE_SPLIT * COARSE_MAX_DIM * COARSE_MAX_DIM);
     w.Ainv = take(so ? 0 : (size_t)COARSE_MAX_DIM * COARSE_MAX_DIM);
+    w.Zc2 = take(so ? 0 : C * 42);
+    w.Ainv2 = take(so ? 0 : (size_t)COARSE_MAX_DIM * COARSE_MAX_DIM);
   }
   w.pm_pt = reinterpret_cast<int32_t*>(take(((size_t)p->num_obs + 1) / 2 + 1));
   w.cta_desc = reinterpret_cast<int4*>(take(2 * nblk + 2));
@@ -259,6 +268,8 @@ struct Ctx {
   PcgGridCoarse gridco;  // grid kernel: groups of CTAs (build_grid_coarse_plan)
   const mpba_shard* sh = nullptr;  // sharded solve
   bool want_hinv = false;          // Hpp^-1 rows requested (mpba_point_covariances)
+  int coarse_lag = 0;              // 1: the PCG of linear solve i uses the coarse inverse built from S of solve i - 1
+  int solves = 0;                  // linear solves enqueued so far in this call
 };
 
 int check_shard(mpba_handle* h, const mpba_problem* p, const mpba_shard* sh) {
@@ -366,7 +377,10 @@ int fetch_scalars(Ctx& c) {
   CU(cudaMemcpyAsync(h->h_scal, c.w.scal, S_COUNT * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaStreamSynchronize(h->stream));
   CU(cudaGetLastError());
-  if (h->profile) flush_timers(h);
+  if (h->profile) {
+    if (h->side) CU(cudaStreamSynchronize(h->side));  // its events are read below
+    flush_timers(h);
+  }
   return MPBA_OK;
 }
 
@@ -627,6 +641,10 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
   }
   if (!want_system) return MPBA_OK;
   if (schur) {
+    // the side stream's coarse assembly of the previous solve reads S and the poses: it must be through (it is, by
+    // hundreds of microseconds) before S is rewritten
+    if (c.coarse_lag != 0 && h->side != nullptr && c.coarse.G > 0 && c.solves > 0)
+      CU(cudaStreamWaitEvent(h->stream, h->ev_asm_done, 0));
     {
       Timer t(h, KS_S_FINALIZE);
       launch_schur_blocks(c.pv, c.w.fac, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.S, c.w.rhs, c.sh ? 1 : 0,
@@ -647,30 +665,64 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
       Timer t(h, KS_BLOCK_INVERSE);
       launch_block_inverse(c.pv, c.w.S, c.w.Minv, h->stream);
     }
-    // (rebuilding the coarse space only every k-th LM iteration was measured at cfg3: k = 2 gains nothing, k = 4
-    // costs 30 % more PCG iterations)
+    // Coarse space.  Synchronous (coarse_lag = 0): modes, Z^T S Z and its dense inverse on the solve stream, right
+    // before the PCG -- 279 us per LM iteration at cfg3, 232 us of it the latency-bound Gauss-Jordan on four CTAs.
+    // Lagged (default): the inverse is a PRECONDITIONER, any SPD matrix serves; the one built from S of the previous
+    // linear solve is used, and this solve's own is built on the side stream, where it overlaps the stream kernels
+    // that follow (back-substitution, image pass, the next k_points: all of them leave SMs idle at their tails).
+    // Z itself (six numbers per image and mode) is always the current one.  The first solve of a call waits for its
+    // own inverse.  (Rebuilding only every k-th iteration ON the solve stream was measured in round 1: k = 2 gains
+    // nothing, k = 4 costs 30 % more PCG iterations.)
+    const double* ainv_use = c.w.Ainv;
     if (c.coarse.G > 0) {
-      Timer t(h, KS_COARSE, 3);
-      cudaError_t e = launch_coarse_setup(c.coarse, c.pv.C, pose, c.pv.img_free_mask, c.pv.s_row, c.pv.s_col, c.w.S,
-                                          c.w.Zc, c.w.Ac, c.w.Ainv, h->stream);
-      if (e != cudaSuccess) return fail(h, MPBA_E_CUDA, std::string("coarse setup: ") + cudaGetErrorString(e));
+      const bool lag = c.coarse_lag != 0 && h->side != nullptr;
+      if (!lag) {
+        Timer t(h, KS_COARSE, 3);
+        cudaError_t e = launch_coarse_setup(c.coarse, c.pv.C, pose, c.pv.img_free_mask, c.pv.s_row, c.pv.s_col, c.w.S,
+                                            c.w.Zc, c.w.Ac, c.w.Ainv, h->stream);
+        if (e != cudaSuccess) return fail(h, MPBA_E_CUDA, std::string("coarse setup: ") + cudaGetErrorString(e));
+      } else {
+        double* abuf[2] = {c.w.Ainv, c.w.Ainv2};
+        const int mine = c.solves & 1;
+        {
+          Timer t(h, KS_COARSE, 1);
+          cudaError_t e = launch_coarse_modes(c.pv.C, pose, c.pv.img_free_mask, c.w.Zc, h->stream);
+          if (e != cudaSuccess) return fail(h, MPBA_E_CUDA, std::string("coarse modes: ") + cudaGetErrorString(e));
+        }
+        CU(cudaEventRecord(h->ev_s_ready, h->stream));
+        CU(cudaStreamWaitEvent(h->side, h->ev_s_ready, 0));
+        {
+          Timer t(h, KS_COARSE_SIDE, 3, h->side, true);
+          cudaError_t e = launch_coarse_setup(c.coarse, c.pv.C, pose, c.pv.img_free_mask, c.pv.s_row, c.pv.s_col, c.w.S,
+                                              c.w.Zc2, c.w.Ac, abuf[mine], h->side, h->ev_asm_done);
+          if (e != cudaSuccess) return fail(h, MPBA_E_CUDA, std::string("coarse setup: ") + cudaGetErrorString(e));
+        }
+        CU(cudaEventRecord(h->ev_inv_done[mine], h->side));
+        const int use = c.solves == 0 ? mine : (mine ^ 1);
+        CU(cudaStreamWaitEvent(h->stream, h->ev_inv_done[use], 0));
+        ainv_use = abuf[use];
+      }
     }
     {
       Timer t(h, KS_PCG);
       cudaError_t e;
       if (c.cl > 0) {
         PcgClusterArgs a = c.cla;
+        a.Ainv = ainv_use;
         a.S = c.w.S; a.Minv = c.w.Minv; a.rhs = c.w.rhs; a.x = c.w.y; a.scal = c.w.scal;
         a.tol = opt->pcg_tolerance; a.max_iter = opt->pcg_max_iterations;
         e = launch_pcg_cluster(a, c.cl, c.cl_smem, h->stream);
       } else {
         const PcgPlan pl = pcg_plan(h->device, c.pv.C, c.max_row_blocks);
+        PcgGridCoarse gco = c.gridco;
+        gco.Ainv = ainv_use;
         e = launch_pcg(c.pv, pl, c.w.S, c.w.Minv, c.w.rhs, c.w.y, c.w.vz, c.w.vp0, c.w.vp1, c.w.partial,
                        reinterpret_cast<unsigned*>(c.w.partial + 2 * 2048), c.w.scal, opt->pcg_tolerance,
-                       opt->pcg_max_iterations, c.gridco, h->stream);
+                       opt->pcg_max_iterations, gco, h->stream);
       }
       if (e != cudaSuccess) return fail(h, MPBA_E_CUDA, std::string("PCG launch: ") + cudaGetErrorString(e));
     }
+    ++c.solves;
   } else {
     // all poses constant (refine_3d_points, bundle_adjustment.py:276-283): no reduced system, y_c = 0
     CU(cudaMemsetAsync(c.w.y, 0, (size_t)c.pv.C * 6 * sizeof(double), h->stream));
@@ -710,6 +762,7 @@ void mpba_default_options(mpba_options* o) {
   o->pcg_kernel = 0;
   o->pcg_coarse = 0;
   o->behind_camera = 0;
+  o->coarse_lag = 1;
 }
 
 int mpba_create(mpba_handle** out, int device, void* cuda_stream) {
@@ -726,6 +779,19 @@ int mpba_create(mpba_handle** out, int device, void* cuda_stream) {
     delete h;
     return MPBA_E_CUDA;
   }
+  // side stream of the lagged coarse setup; without it (creation failed) the setup stays on the solve stream
+  if (cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking) != cudaSuccess) h->side = nullptr;
+  if (h->side) {
+    bool ok = cudaEventCreateWithFlags(&h->ev_s_ready, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&h->ev_asm_done, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&h->ev_inv_done[0], cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&h->ev_inv_done[1], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) {
+      cudaStreamDestroy(h->side);
+      h->side = nullptr;
+    }
+  }
+  cudaGetLastError();
   *out = h;
   return MPBA_OK;
 }
@@ -739,6 +805,12 @@ void mpba_destroy(mpba_handle* h) {
   }
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->side) {
+    cudaStreamSynchronize(h->side);
+    cudaStreamDestroy(h->side);
+  }
+  for (cudaEvent_t e : {h->ev_s_ready, h->ev_asm_done, h->ev_inv_done[0], h->ev_inv_done[1]})
+    if (e) cudaEventDestroy(e);
   if (h->h_scal) cudaFreeHost(h->h_scal);
   if (h->h_stage) cudaFreeHost(h->h_stage);
   if (h->comm) nccl_api().CommDestroy(h->comm);
@@ -978,6 +1050,11 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
   if (opt_in) opt = *opt_in; else mpba_default_options(&opt);
   reset_profile(h, opt.profile);
   c.pv.loss.behind_strict = opt.behind_camera == 1 ? 1 : 0;
+  c.coarse_lag = opt.coarse_lag != 0 ? 1 : 0;
+  struct SideDrain {  // whatever the exit path: nothing of this call is left running on the side stream
+    mpba_handle* h;
+    ~SideDrain() { if (h->side) cudaStreamSynchronize(h->side); }
+  } side_drain{h};
   rc = build_pcg_cluster_plan(c, prob, opt.pcg_kernel, opt.pcg_coarse);
   if (rc) return rc;
   rc = build_grid_coarse_plan(c, prob, opt.pcg_coarse);
@@ -1203,6 +1280,7 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
   CU(cudaMemcpyAsync(h->h_scal, c.w.scal, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaEventRecord(h->ev1, h->stream));
   CU(cudaStreamSynchronize(h->stream));
+  if (h->side) CU(cudaStreamSynchronize(h->side));
   if (h->profile) flush_timers(h);
   float ms = 0.f;
   cudaEventElapsedTime(&ms, h->ev0, h->ev1);

@@ -334,9 +334,14 @@ __global__ void __launch_bounds__(256) k_coarse_symmetrize(int n, const double* 
 
 size_t coarse_invert_smem_bytes(int n) { return (size_t)n * (n | 1) * sizeof(double); }
 
+cudaError_t launch_coarse_modes(int C, const double* pose, const uint8_t* free_mask, double* Zc, cudaStream_t st) {
+  k_coarse_modes<<<(C + 127) / 128, 128, 0, st>>>(C, pose, free_mask, Zc);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_coarse_setup(const CoarsePlan& cp, int C, const double* pose, const uint8_t* free_mask,
                                 const int32_t* s_row, const int32_t* s_col, const double* S, double* Zc, double* Ac,
-                                double* Ainv, cudaStream_t st) {
+                                double* Ainv, cudaStream_t st, cudaEvent_t after_assemble) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_coarse_invert, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -346,6 +351,7 @@ cudaError_t launch_coarse_setup(const CoarsePlan& cp, int C, const double* pose,
   const int n = 7 * cp.G;
   k_coarse_modes<<<(C + 127) / 128, 128, 0, st>>>(C, pose, free_mask, Zc);
   k_coarse_assemble<<<dim3(cp.G * cp.G, COARSE_SPLIT), 64 * CA_SLICES, 0, st>>>(cp.G, cp.cb_ptr, cp.cb_fine, s_row, s_col, S, Zc, Ac);
+  if (after_assemble) cudaEventRecord(after_assemble, st);  // S and the poses are not read past this point
   if (n <= GJ_SINGLE_MAX) {
     k_coarse_invert<<<1, 1024, coarse_invert_smem_bytes(n), st>>>(n, Ac, Ainv);
   } else {

@@ -29,7 +29,7 @@ from .problem import MAX_CAMERA_PARAMS, BundleProblem
 
 _LIB_PATH = os.environ.get("MPBA_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libmpba.so")
 MPBA_CHUNK = 1024
-MPBA_NUM_KERNELS = 13
+MPBA_NUM_KERNELS = 14
 MPBA_UNIQUE_ID_BYTES = 128
 FLAG_STRUCTURE_ONLY = 1
 
@@ -90,7 +90,7 @@ class MpbaOptions(C.Structure):
         ("function_tolerance", C.c_double), ("gradient_tolerance", C.c_double),
         ("parameter_tolerance", C.c_double), ("pcg_tolerance", C.c_double),
         ("profile", C.c_int32), ("verbose", C.c_int32), ("pcg_kernel", C.c_int32), ("pcg_coarse", C.c_int32),
-        ("behind_camera", C.c_int32), ("reserved", C.c_int32),
+        ("behind_camera", C.c_int32), ("coarse_lag", C.c_int32),
     ]
 
 

@@ -248,3 +248,124 @@ def propagate_variances(inputs: Sequence[MapInputs], conf: Optional[MpbaIntegrat
                                                                        b.results))
     ys = [b.out[k][3].cpu().numpy().reshape(b.out[k][4]) for k in range(b.num)]
     return ys, [int(b.results[k].cg_iterations) for k in range(b.num)]
+
+
+class DepthIntegrator:
+    """The mapper-facing half: ``MpsfmMapper.integrate_bundle`` (mpsfm/sfm/mapper/base.py:619-631) over the reference's
+    own objects.  ``mpsfm_rec.images[imid]`` must offer what ``Integration`` reads: ``.depth.{data, data_prior,
+    uncertainty, valid, activated, uncertainty_update, data_prior_at_kps}``, ``.normals.{data, uncertainty}``,
+    ``.camera.{sx, sy, calibration_matrix()}``, ``.conf`` (integration keys) and ``mpsfm_rec.project_image_3d_points``,
+    ``mpsfm_rec.point_covs.points_zvars``, ``mpsfm_rec.find_points3D_with_small_triangulation_angle``,
+    ``mpsfm_rec.keypoints``.  State (IntVars) is kept per image id by this object."""
+
+    def __init__(self, mpsfm_rec, device: int = 0):
+        self.mpsfm_rec = mpsfm_rec
+        self.device = device
+        self.state = {}
+        self.first_refinement = True
+
+    # _prepare_integration_variables (:92-131)
+    def _prepare(self, imid):
+        rec = self.mpsfm_rec
+        image = rec.images[imid]
+        conf = image.conf
+        _, pts3dids, kps, depth3d, success = rec.project_image_3d_points(imid)
+        if not success:
+            return None
+        pts3dids = np.array(pts3dids)
+        kps = np.array(kps, dtype=np.float64).reshape(-1, 2)
+        depth3d = np.array(depth3d, dtype=np.float64)
+        rt = getattr(conf, "robust_triangles", None)
+        if rt is not None and len(pts3dids):
+            safe = ~np.asarray(rec.find_points3D_with_small_triangulation_angle(min_angle=rt, point3D_ids=pts3dids), dtype=bool)
+            pts3dids, kps, depth3d = pts3dids[safe], kps[safe], depth3d[safe]
+        cam = image.camera
+        kps = kps * np.array([cam.sx, cam.sy])
+        kps = (kps + 0.5).astype(int)
+        H, W = image.depth.data.shape
+        if len(pts3dids) == 0:
+            zvars = np.zeros(0)
+            mask = slice(None)
+        else:
+            _, zvars = rec.point_covs.points_zvars(image, pts3dids)
+            zvars = np.asarray(zvars, dtype=np.float64)
+            x, y = kps.T
+            mask = (x >= 0) & (x < W) & (y >= 0) & (y < H)
+        Km = cam.calibration_matrix()
+        K = [Km[1, 1] * cam.sy, Km[0, 0] * cam.sx, Km[1, 2] * cam.sy, Km[0, 2] * cam.sx]
+        return MapInputs(depth_prior=image.depth.data_prior, uncertainty=image.depth.uncertainty, valid=image.depth.valid,
+                         normals=image.normals.data, normals_uncertainty=image.normals.uncertainty, depth=image.depth.data,
+                         K=K, kps=kps[mask], depth3d=depth3d[mask], zvars3d=zvars[mask])
+
+    @staticmethod
+    def _conf_of(image) -> MpbaIntegrationConf:
+        c = image.conf
+        keys = ("max_iter", "cg_max_iter", "tol", "step_size", "cg_tol", "lambda1", "lambda2", "k", "large_number",
+                "depth_magnitude_multiplier", "normals_magnitude_multiplier")
+        kw = {k: getattr(c, k) for k in keys if hasattr(c, k)}
+        if getattr(c, "scale_filter", True):
+            kw["scale_filter_factor"] = float(getattr(c, "scale_filter_factor", 1.5))
+        else:
+            kw["scale_filter"] = False
+        return default_conf(**kw)
+
+    def integrate_bundle(self, imids, int_covs=True, int_covs_every_iter=False, **kwargs):
+        """Integrates bundle for given image ids (base.py:619-631): every image whose energy moved is refined, all in
+        ONE launch; then (first refinement only, :623-627) the propagated variances of the changed images.
+        Returns {imid: changed}."""
+        rec = self.mpsfm_rec
+        ids, inputs, states, confs = [], [], [], []
+        for imid in imids:
+            image = rec.images[imid]
+            assert image.depth.activated, "Image not registered or depth map not activated"  # :135
+            m = self._prepare(imid)
+            if m is None:
+                continue
+            ids.append(imid)
+            inputs.append(m)
+            states.append(self.state.get(imid))
+            confs.append(self._conf_of(image))
+        changed = {imid: False for imid in imids}
+        # images sharing a conf go in one launch (the mapper uses one conf for all of them)
+        groups = {}
+        for k, cf in enumerate(confs):
+            groups.setdefault(bytes(cf), []).append(k)
+        for key, members in groups.items():
+            outs = integrate_maps([inputs[k] for k in members], confs[members[0]], [states[k] for k in members], self.device)
+            for k, out in zip(members, outs):
+                imid = ids[k]
+                self.state[imid] = out.state
+                if out.updated:
+                    rec.images[imid].depth.data = out.depth.astype(np.float64)  # :515
+                    changed[imid] = True
+        if int_covs and self.first_refinement:
+            todo = [k for k in range(len(ids)) if changed[ids[k]]]
+            if todo:
+                self.calculate_int_covs_at_kps([ids[k] for k in todo])
+        if not int_covs_every_iter:
+            self.first_refinement = False
+        return changed
+
+    def calculate_int_covs_at_kps(self, imids, ignore_depths=None):
+        """calculate_hessian + calculate_int_covs_at_kps (:522-616) at the maps' own resolution (``downscaled`` needs the
+        caller's cv2-resized maps: pass them as the image's maps).  Writes depth.uncertainty_update in place."""
+        rec = self.mpsfm_rec
+        inputs, confs = [], []
+        for imid in imids:
+            image = rec.images[imid]
+            m = self._prepare(imid)
+            inputs.append(m)
+            confs.append(self._conf_of(image))
+        ign = ignore_depths if ignore_depths is not None else bool(getattr(rec.images[imids[0]].conf, "ignore_depths", True))
+        ys, _ = propagate_variances(inputs, confs[0], ignore_depths=ign, device=self.device)
+        out = {}
+        for imid, y in zip(imids, ys):
+            image = rec.images[imid]
+            kps = np.asarray(rec.keypoints(imid), dtype=np.float64)
+            cam = image.camera
+            xy = np.round(kps * np.array([cam.sx, cam.sy])).astype(int)
+            log_uncert = y[xy[:, 1], xy[:, 0]]
+            uncert = log_uncert * np.asarray(image.depth.data_prior_at_kps(kps)) ** 2  # :614
+            image.depth.uncertainty_update[np.arange(len(kps))] = uncert
+            out[imid] = uncert
+        return out
