@@ -1819,8 +1819,8 @@ PcgPlan pcg_plan(int device, int C, int max_row_blocks) {
   if (!sms) {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
-    cudaFuncSetAttribute(k_pcg<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 20480);
-    cudaFuncSetAttribute(k_pcg<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 20480);
+    cudaFuncSetAttribute(k_pcg<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 40960);
+    cudaFuncSetAttribute(k_pcg<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_optin - 40960);
   }
   PcgPlan pl;
   int grid = (C + 7) / 8;          // at least eight block rows per CTA
@@ -1832,7 +1832,7 @@ PcgPlan pcg_plan(int device, int C, int max_row_blocks) {
   const size_t base = rows * (36 + 24) * sizeof(double) + ((rows + 2) & ~(size_t)1) * sizeof(int);
   pl.max_local_blocks = (int)(rows * (size_t)(max_row_blocks > 0 ? max_row_blocks : 1 << 16));
   const size_t with_s = base + (size_t)pl.max_local_blocks * (36 * sizeof(double) + sizeof(int)) + 16;
-  pl.use_smem = (max_row_blocks > 0 && with_s <= (size_t)(smem_optin - 20480)) ? 1 : 0;
+  pl.use_smem = (max_row_blocks > 0 && with_s <= (size_t)(smem_optin - 40960)) ? 1 : 0;
   pl.smem_bytes = pl.use_smem ? with_s : base + 16;
   return pl;
 }

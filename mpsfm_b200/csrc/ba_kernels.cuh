@@ -133,7 +133,10 @@ cudaError_t launch_pcg(const ProblemView& pv, const PcgPlan& pl, const double* S
 // cluster-resident PCG (pcg_cluster.cu): one thread-block cluster of `cl` CTAs, upper blocks of S in
 // registers, exchanges through distributed shared memory.  The plan arrays are built on the host from
 // the block-CSR structure (ba_solver.cu: build_pcg_cluster_plan) and live in the workspace.
-constexpr int PCGC_THREADS = 384;
+#ifndef MPBA_PCGC_THREADS
+#define MPBA_PCGC_THREADS 512  // 128 registers: 88 B of spills outside the iteration loop; measured at cfg3 (r2): 696 us per PCG against 773 us with 384 threads, whose surplus blocks of S sat in shared memory
+#endif
+constexpr int PCGC_THREADS = MPBA_PCGC_THREADS;
 // shared-memory carve of k_pcg_cluster as 32-bit offsets from the dynamic base (doubles; the last three in
 // ints): kept in the kernel argument block = constant bank, so they cost no registers next to the 6x6
 // block of S every thread holds
@@ -181,7 +184,7 @@ bool pcg_cluster_fits(int device, int cl, size_t smem_bytes);
 cudaError_t launch_pcg_cluster(const PcgClusterArgs& a, int cl, size_t smem_bytes, cudaStream_t st);
 
 // coarse space of the two-level preconditioner (coarse.cu)
-constexpr int COARSE_MAX_GROUPS = 32;  // 7 * 32 = 224 modes: 7 column slots of 32 lanes in k_coarse_invert_cluster (<= 18 groups: one CTA)
+constexpr int COARSE_MAX_GROUPS = 64;  // 7 * 64 = 448 modes: <= 18 groups one CTA, <= 32 a four-CTA cluster, beyond a sixteen-CTA cluster (coarse.cu)
 constexpr int COARSE_MAX_DIM = 7 * COARSE_MAX_GROUPS;
 constexpr int COARSE_SPLIT = 8;  // partial coarse matrices of k_coarse_assemble, added in order by k_coarse_invert  // the dense inverse is formed by one CTA in shared memory
 struct CoarsePlan {

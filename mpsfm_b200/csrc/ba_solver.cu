@@ -77,7 +77,18 @@ namespace {
 // Coarse groups of the two-level preconditioner: beyond 18 groups (126 modes) the dense inverse of the coarse matrix
 // moves from one CTA to a four-CTA cluster (one cluster barrier per pivot, ~270 us for 224 modes), which only pays
 // when the PCG iterations it saves are many: large systems.
-int coarse_max_groups(int num_images) { return num_images >= 600 ? COARSE_MAX_GROUPS : 18; }
+// With the lagged setup (coarse_lag) the inverse is off the solve stream and systems beyond one cluster (grid PCG) take
+// 48 groups (336 modes, sixteen-CTA cluster inverse).  Measured (r2, profiles/r02_coarse_groups.md): target10m 32 -> 48
+// groups 2872 -> 1944 PCG iterations per solve, 237 -> 262 LM it/s, 64 groups 1897 / 257; cfg3 (cluster PCG) 32 -> 48
+// groups 2024 -> 1531 iterations but every iteration pays the larger A^-1 product and the side stream's bigger inverse
+// takes SMs from the stream kernels: 481 -> 475 LM it/s, so the cluster path stays at 32.
+// MPBA_COARSE_GROUPS overrides the cap for sweeps.
+int coarse_max_groups(int num_images, int lagged, bool cluster) {
+  static const int env = getenv("MPBA_COARSE_GROUPS") ? atoi(getenv("MPBA_COARSE_GROUPS")) : 0;
+  if (env > 0) return std::min(env, (int)COARSE_MAX_GROUPS);
+  if (num_images < 600) return 18;
+  return (lagged && !cluster) ? 48 : 32;
+}
 
 int fail(mpba_handle* h, int code, const std::string& msg) {
   if (h) h->err = msg;
@@ -486,7 +497,7 @@ int build_pcg_cluster_plan(Ctx& c, const mpba_problem* prob, int pcg_kernel, int
     // coarse space: gpc groups of consecutive images per CTA, at least two images per group
     int min_rows = C;
     for (int k = 0; k < cl; ++k) min_rows = std::min(min_rows, crow[k + 1] - crow[k]);
-    int gpc = (pcg_coarse == 1 || C < 8) ? 0 : std::min(coarse_max_groups(C) / cl, std::max(min_rows / 2, 0));
+    int gpc = (pcg_coarse == 1 || C < 8) ? 0 : std::min(coarse_max_groups(C, c.coarse_lag, true) / cl, std::max(min_rows / 2, 0));
     size_t smem = 0;
     for (;; --gpc) {
       a.gpc = gpc > 0 ? gpc : 0;
@@ -495,6 +506,10 @@ int build_pcg_cluster_plan(Ctx& c, const mpba_problem* prob, int pcg_kernel, int
       smem = pcg_cluster_carve(a);
       if (a.gpc == 0 || (int)smem <= max_smem) break;
     }
+    static const bool plan_dbg = getenv("MPBA_PLAN_DEBUG") != nullptr;
+    if (plan_dbg)
+      fprintf(stderr, "[mpba] cluster plan cl %d: rows<=%d full<=%d halo<=%d blk<=%d min_rows %d gpc %d -> %zu B of %d\n", cl,
+              max_rows, max_full, max_halo, max_blk, min_rows, a.gpc, smem, max_smem);
     if ((int)smem > max_smem || !pcg_cluster_fits(h->device, cl, smem)) {
       if (cl == 16) return MPBA_OK;
       continue;
@@ -577,7 +592,7 @@ int build_grid_coarse_plan(Ctx& c, const mpba_problem* prob, int pcg_coarse) {
   if (c.structure_only || c.cl > 0 || pcg_coarse == 1) return MPBA_OK;
   const int C = prob->num_images, B = prob->num_blocks;
   const PcgPlan pl = pcg_plan(h->device, C, c.max_row_blocks);
-  const int G = std::min(coarse_max_groups(C), pl.grid);
+  const int G = std::min(coarse_max_groups(C, c.coarse_lag, false), pl.grid);
   if (G < 2 || pl.grid > 1024) return MPBA_OK;
   std::vector<int32_t> rp(C + 1), col(B);
   CU(cudaMemcpyAsync(rp.data(), prob->s_row_ptr, (C + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
@@ -1050,7 +1065,9 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
   if (opt_in) opt = *opt_in; else mpba_default_options(&opt);
   reset_profile(h, opt.profile);
   c.pv.loss.behind_strict = opt.behind_camera == 1 ? 1 : 0;
-  c.coarse_lag = opt.coarse_lag != 0 ? 1 : 0;
+  // the lag pays where the dense inverse is the multi-CTA one (>= 600 images); small systems keep the synchronous
+  // setup (a ~20 us single-CTA inverse) and with it the trajectory of the exact preconditioner
+  c.coarse_lag = (opt.coarse_lag != 0 && prob->num_images >= 600) ? 1 : 0;
   struct SideDrain {  // whatever the exit path: nothing of this call is left running on the side stream
     mpba_handle* h;
     ~SideDrain() { if (h->side) cudaStreamSynchronize(h->side); }

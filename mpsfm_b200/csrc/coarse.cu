@@ -206,7 +206,7 @@ __global__ void __launch_bounds__(1024) k_coarse_invert(int n, const double* __r
 // distributed shared memory; pivots go in pairs, one cluster barrier per pair.  The raw inverse goes to global memory and
 // k_coarse_symmetrize averages it with its transpose.
 constexpr int GJC_CTAS = 4, GJC_QR = 2, GJC_QC = 7;
-static_assert(GJC_CTAS * GJC_QR * 32 >= COARSE_MAX_DIM && GJC_QC * 32 >= COARSE_MAX_DIM, "cluster inverse too small");
+static_assert(GJC_CTAS * GJC_QR * 32 >= 224 && GJC_QC * 32 >= 224, "cluster inverse too small for 32 groups");
 __global__ void __cluster_dims__(GJC_CTAS, 1, 1) __launch_bounds__(1024)
     k_coarse_invert_cluster(int n, const double* Ac_part, double* raw) {  // raw may alias Ac_part (see the launcher)
   __shared__ double prow[2][2][32 * GJC_QC];  // [buffer][pivot of the pair][column]
@@ -323,6 +323,77 @@ __global__ void __cluster_dims__(GJC_CTAS, 1, 1) __launch_bounds__(1024)
     }
 }
 
+// 224 < n <= 448 (up to 64 groups): the same elimination on a cluster of SIXTEEN CTAs, one row slot per warp (row
+// i = warp + 32 rank, 14 column slots per lane), one cluster barrier per pivot, the scaled pivot row stored into all
+// sixteen CTAs through distributed shared memory.  ~1 us per pivot: this kernel only ever runs on the side stream of
+// the lagged setup (ba_solver.cu), where its latency is hidden behind the stream kernels of the LM iteration.
+constexpr int GJB_CTAS = 16, GJB_QC = 14;
+static_assert(GJB_CTAS * 32 >= COARSE_MAX_DIM && GJB_QC * 32 >= COARSE_MAX_DIM && GJB_QC <= GJB_CTAS, "big cluster inverse too small");
+__global__ void __cluster_dims__(GJB_CTAS, 1, 1) __launch_bounds__(1024)
+    k_coarse_invert_big(int n, const double* Ac_part, double* raw) {  // raw may alias Ac_part
+  __shared__ double prow[2][32 * GJB_QC];
+  __shared__ double s_inv[2];
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = (int)cluster.block_rank();
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int i = warp + 32 * rank;
+  double a[GJB_QC];
+#pragma unroll
+  for (int qj = 0; qj < GJB_QC; ++qj) {
+    const int j = lane + 32 * qj;
+    double v = 0.0;
+    if (i < n && j < n) {
+#pragma unroll
+      for (int sp = 0; sp < COARSE_SPLIT; ++sp) v += Ac_part[(size_t)sp * n * n + (size_t)i * n + j];
+    }
+    a[qj] = v;
+  }
+  double dv = 0.0;  // original diagonal of the own row: threshold of the pivot test
+#pragma unroll
+  for (int qj = 0; qj < GJB_QC; ++qj)
+    if (qj == rank && lane == warp) dv = a[qj];
+  const double d0 = __shfl_sync(0xffffffffu, dv, warp);
+  cluster.sync();  // every CTA has read its inputs (raw may alias them) and is resident
+#pragma unroll
+  for (int PQ = 0; PQ < GJB_QC; ++PQ) {  // pivots 32 PQ .. 32 PQ + 31: rows of CTA PQ, column slot PQ (compile time)
+    for (int pw = 0; pw < 32; ++pw) {
+      const int p = 32 * PQ + pw;
+      if (p >= n) break;
+      const int buf = p & 1;
+      const bool mine = rank == PQ && warp == pw;
+      if (mine) {
+        const double piv = __shfl_sync(0xffffffffu, a[PQ], pw);
+        const double inv = (piv > 1e-13 * d0 && d0 > 0.0) ? fast_rcp(piv) : 0.0;
+#pragma unroll 1
+        for (int r = 0; r < GJB_CTAS; ++r) {
+          double* dst = cluster.map_shared_rank(&prow[buf][0], r);
+#pragma unroll
+          for (int qj = 0; qj < GJB_QC; ++qj) dst[lane + 32 * qj] = a[qj] * inv;
+          if (lane == 0) *cluster.map_shared_rank(&s_inv[buf], r) = inv;
+        }
+      }
+      double f = __shfl_sync(0xffffffffu, a[PQ], pw);  // column p of my row
+      if (mine) f = 0.0;
+      cluster.sync();
+      const double inv = s_inv[buf];
+      const double* rp = &prow[buf][lane];
+#pragma unroll
+      for (int qj = 0; qj < GJB_QC; ++qj) {
+        const double r = rp[32 * qj];
+        a[qj] -= f * r;
+        if (mine) a[qj] = r;
+      }
+      if (lane == pw) a[PQ] = mine ? inv : -f * inv;
+    }
+  }
+  cluster.sync();  // nobody leaves while a peer may still write its shared memory
+#pragma unroll
+  for (int qj = 0; qj < GJB_QC; ++qj) {
+    const int j = lane + 32 * qj;
+    if (i < n && j < n) raw[(size_t)i * n + j] = a[qj];
+  }
+}
+
 __global__ void __launch_bounds__(256) k_coarse_symmetrize(int n, const double* __restrict__ raw, double* __restrict__ Ainv) {
   const int k = blockIdx.x * 256 + threadIdx.x;
   if (k >= n * n) return;
@@ -346,6 +417,7 @@ cudaError_t launch_coarse_setup(const CoarsePlan& cp, int C, const double* pose,
   if (!attr_set) {
     cudaFuncSetAttribute(k_coarse_invert, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int)coarse_invert_smem_bytes(GJ_SINGLE_MAX));
+    cudaFuncSetAttribute(k_coarse_invert_big, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
     attr_set = true;
   }
   const int n = 7 * cp.G;
@@ -356,7 +428,10 @@ cudaError_t launch_coarse_setup(const CoarsePlan& cp, int C, const double* pose,
     k_coarse_invert<<<1, 1024, coarse_invert_smem_bytes(n), st>>>(n, Ac, Ainv);
   } else {
     // the partial matrices are read into registers before the first cluster barrier: slice 0 is reused for the raw inverse
-    k_coarse_invert_cluster<<<GJC_CTAS, 1024, 0, st>>>(n, Ac, Ac);
+    if (n <= GJC_CTAS * GJC_QR * 32 && n <= GJC_QC * 32)
+      k_coarse_invert_cluster<<<GJC_CTAS, 1024, 0, st>>>(n, Ac, Ac);
+    else
+      k_coarse_invert_big<<<GJB_CTAS, 1024, 0, st>>>(n, Ac, Ac);
     k_coarse_symmetrize<<<(n * n + 255) / 256, 256, 0, st>>>(n, Ac, Ainv);
   }
   return cudaGetLastError();
