@@ -175,6 +175,14 @@ typedef struct mpba_options {
                                               the PCG of linear solve i uses the one built from S of solve i - 1 and
                                               solve i's own is built on a side stream, overlapping the kernels that
                                               follow; 0: rebuilt on the solve stream before every PCG */
+  int32_t lm_loop;                         /* where the LM controller (accept / reject, trust region, termination) runs.
+                                              0 (default): on the device for bundles below 600 images -- the whole LM
+                                              loop is ONE CUDA-graph launch (a WHILE node over the iteration's kernels,
+                                              csrc/lm_loop.cu), one synchronisation per solve -- and on the host above;
+                                              1: host loop always; 2: device loop wherever it is legal (single GPU,
+                                              cluster-resident PCG, profile = verbose = 0, max_num_iterations <= 254).
+                                              Both controllers produce the same iterates bit for bit */
+  int32_t reserved0;
 } mpba_options;
 
 /* ceres::IterationSummary subset, one row per LM iteration (row 0 = initial evaluation) */

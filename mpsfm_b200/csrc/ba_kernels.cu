@@ -381,6 +381,14 @@ __device__ __forceinline__ void point_terms(const ObsLin& o, const double* R, do
   v[8] = R[2] * o.h[0] + R[5] * o.h[1] + R[8] * o.h[2];
 }
 
+// device-controlled LM loop: the trust-region radius lives in device memory (see LmDiag)
+__device__ __forceinline__ void lm_resolve(LmDiag& lm) {
+  if (lm.dev != nullptr) {
+    lm.radius = __ldcg(lm.dev + LD_RADIUS);
+    lm.inv_radius = __ldcg(lm.dev + LD_INV_RADIUS);
+  }
+}
+
 // Per point, from the complete sums: Jacobi scale, LM damping, Cholesky of Hpp + D, Hpp^-1; writes the point's
 // rows of c_pt / Hpp / gp / Hinv / Linv and returns L^-1 (Li), e = L^-1 gp.
 __device__ __forceinline__ void finalize_point(int p, bool active, const double Hp[6], const double g[3], LmDiag lm,
@@ -602,6 +610,8 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
   __shared__ double s_v[PW_THREADS][9];
   __shared__ double s_le[PW_THREADS][9];
   __shared__ __align__(16) int4 s_next;  // descriptor of the CTA prefetch_ahead blocks later
+  if (compute_scaling < 0) compute_scaling = __ldcg(lm.dev + LD_FIRST) != 0.0 ? 1 : 0;
+  lm_resolve(lm);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g0 = blockIdx.x * PW_WARPS, g1 = min(g0 + PW_WARPS, pv.num_track_warps);
   const int4 desc = __ldg(pv.cta_desc + blockIdx.x);  // one load instead of the tw_first -> pt_ptr chain
@@ -770,6 +780,7 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
                                                              const double* __restrict__ c_img, LmDiag lm,
                                                              double* __restrict__ S, double* __restrict__ rhs,
                                                              int partial) {
+  lm_resolve(lm);
   const int u = blockIdx.x;
   const int blk = pv.u_block[u];
   const int i = pv.s_row[blk], j = pv.s_col[blk];
@@ -972,6 +983,7 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
 __global__ void __launch_bounds__(64) k_schur_finish(ProblemView pv, const double* __restrict__ Hc,
                                                      const double* __restrict__ gc, const double* __restrict__ c_img,
                                                      LmDiag lm, double* __restrict__ S, double* __restrict__ rhs) {
+  lm_resolve(lm);
   const int i = blockIdx.x;
   const unsigned mi = pv.img_free_mask[i];
   const int blk = pv.s_diag[i];
@@ -1399,6 +1411,7 @@ __global__ void __launch_bounds__(1024) k_cam_update(ProblemView pv, const doubl
                                                     LmDiag lm, double* __restrict__ pose_cand,
                                                     double* __restrict__ scal) {
   __shared__ double sm[33];
+  lm_resolve(lm);
   double step2 = 0.0, xn2 = 0.0, mcc = 0.0;
   for (int i = threadIdx.x; i < pv.C; i += 1024) {
     const double* ps = pose + (size_t)i * 8;
@@ -1504,6 +1517,7 @@ __global__ void __launch_bounds__(PW_THREADS) k_back_substitute(ProblemView pv, 
                                                                 LmDiag lm, double* __restrict__ X_cand,
                                                                 double* __restrict__ pt_part, int prefetch_ahead) {
   __shared__ __align__(16) double2 rows_all[PW_WARPS][256];
+  lm_resolve(lm);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * PW_WARPS + warp;
   double mcc = 0.0, step2 = 0.0, xn2 = 0.0;

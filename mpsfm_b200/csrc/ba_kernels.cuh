@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "../../include/mpba.h"
 #include "ba_math.cuh"
 
 namespace mpba {
@@ -78,10 +79,38 @@ struct ProblemView {
   LossSpec loss;
 };
 
+// dev != nullptr (device-controlled LM loop, lm_loop.cu): {radius, 1 / radius} are read from dev[LD_RADIUS],
+// dev[LD_INV_RADIUS] when the kernel starts, and "compute_scaling < 0" means dev[LD_FIRST] != 0
 struct LmDiag {
   double radius, lo, hi, inv_radius;
+  const double* dev;
 };
-inline LmDiag make_lm(double radius, double lo, double hi) { return LmDiag{radius, lo, hi, 1.0 / radius}; }
+inline LmDiag make_lm(double radius, double lo, double hi) { return LmDiag{radius, lo, hi, 1.0 / radius, nullptr}; }
+
+// ---- device-controlled LM loop (lm_loop.cu) ---------------------------------------------------
+enum LmDevSlot {  // doubles in device memory: the LM state between two iterations of the graph's WHILE body
+  LD_RADIUS = 0, LD_INV_RADIUS, LD_FIRST, LD_DECREASE, LD_X_COST, LD_MIN_COST, LD_FIXED_COST, LD_GMAX_C, LD_NEED_GMAX,
+  LD_ITERATION, LD_N_OK, LD_N_BAD, LD_INVALID_RUN, LD_TOTAL_PCG, LD_TERMINATION, LD_MSG, LD_ACCEPT, LD_NROWS,
+  LD_COUNT = 24
+};
+enum LmMsg { LM_MSG_NONE = 0, LM_MSG_GRADIENT, LM_MSG_PARAMETER, LM_MSG_FUNCTION, LM_MSG_INVALID, LM_MSG_MAX_ITERATIONS, LM_MSG_MIN_RADIUS };
+constexpr int LM_DEVICE_MAX_ITERATIONS = 254;  // rows reserved in the workspace: initial evaluation + one per iteration
+struct LmControl {
+  double function_tolerance, gradient_tolerance, parameter_tolerance, min_relative_decrease;
+  double max_trust_region_radius, min_trust_region_radius;
+  int max_num_iterations, max_consecutive_invalid;
+};
+struct LmAcceptCopy {
+  const double* src[4];
+  double* dst[4];
+  size_t n[4];
+};
+void launch_lm_init(double* ld, mpba_iteration* rows, double radius, double x_cost, double fixed_cost, double gmax_c,
+                    double* scal, cudaStream_t st);
+void launch_lm_control(double* ld, mpba_iteration* rows, double* scal, const LmControl& o,
+                       cudaGraphConditionalHandle handle, int use_handle, cudaStream_t st);
+void launch_lm_accept(const double* ld, const LmAcceptCopy& cp, cudaStream_t st);
+const char* lm_message(int code);
 
 // ---- image order: Hcc, gc, cost ------------------------------------------------------------
 void launch_img_chunks(const ProblemView& pv, const double* pose, const double* X, double* chunk_part,

@@ -56,6 +56,14 @@ struct mpba_handle {
   // stream kernels of iteration i run and is used by the PCG of iteration i + 1
   cudaStream_t side = nullptr;
   cudaEvent_t ev_s_ready = nullptr, ev_asm_done = nullptr, ev_inv_done[2] = {nullptr, nullptr};
+  // device-controlled LM loop (lm_loop.cu): pinned read-back of the LM state + iteration rows, and the instantiated
+  // WHILE graph of the last solve, reused when the next solve has the same signature (same buffers, sizes, options)
+  double* h_lm = nullptr;
+  cudaGraph_t lm_graph = nullptr;
+  cudaGraphExec_t lm_exec = nullptr;
+  std::vector<unsigned char> lm_signature;
+  int64_t lm_body_launches = 0;
+  int64_t lm_body_slot[MPBA_NUM_KERNELS] = {0};
   // sharded solve (mpba_comm_init)
   ncclComm_t comm = nullptr;
   int rank = 0, world = 1;
@@ -156,8 +164,11 @@ struct Workspace {
   int4* warp_desc = nullptr;  // per warp group
   int32_t* plan = nullptr;  // PCG cluster plan (pcg_cluster.cu)
   size_t plan_ints = 0;
+  double* ld = nullptr;            // device-controlled LM loop: LD_COUNT state doubles, then the iteration rows
+  mpba_iteration* rows = nullptr;
   size_t bytes = 0;
 };
+constexpr size_t LM_DEV_DOUBLES = LD_COUNT + (size_t)(LM_DEVICE_MAX_ITERATIONS + 2) * sizeof(mpba_iteration) / sizeof(double);
 
 size_t plan_capacity_ints(const mpba_problem* p) {
   if (p->flags & MPBA_FLAG_STRUCTURE_ONLY) return 0;
@@ -218,6 +229,8 @@ void carve(const mpba_problem* p, const mpba_shard* sh, char* base, Workspace& w
   w.warp_desc = reinterpret_cast<int4*>(take(2 * (size_t)p->num_track_warps + 2));
   w.plan_ints = plan_capacity_ints(p);
   w.plan = reinterpret_cast<int32_t*>(take((w.plan_ints + 1) / 2));
+  w.ld = take(LM_DEV_DOUBLES);
+  w.rows = w.ld ? reinterpret_cast<mpba_iteration*>(w.ld + LD_COUNT) : nullptr;
   w.bytes = off;
 }
 
@@ -279,6 +292,7 @@ struct Ctx {
   PcgGridCoarse gridco;  // grid kernel: groups of CTAs (build_grid_coarse_plan)
   const mpba_shard* sh = nullptr;  // sharded solve
   bool want_hinv = false;          // Hpp^-1 rows requested (mpba_point_covariances)
+  bool device_lm = false;          // LM controller on the device: no memset nodes in the loop body (lm_loop.cu)
   int coarse_lag = 0;              // 1: the PCG of linear solve i uses the coarse inverse built from S of solve i - 1
   int solves = 0;                  // linear solves enqueued so far in this call
 };
@@ -643,7 +657,7 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
                               const mpba_options* opt, bool want_system) {
   mpba_handle* h = c.h;
   const bool schur = want_system && !c.structure_only;
-  CU(cudaMemsetAsync(c.w.scal + S_BAD_POINTS, 0, sizeof(double), h->stream));
+  if (!c.device_lm) CU(cudaMemsetAsync(c.w.scal + S_BAD_POINTS, 0, sizeof(double), h->stream));
   {
     Timer t(h, KS_POINTS_SCHUR);
     launch_points(c.pv, pose, X, lm, c.w.c_pt, compute_scaling, opt->jacobi_scaling, c.w.Hpp, c.w.gp,
@@ -746,6 +760,157 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
   return MPBA_OK;
 }
 
+// One LM iteration from the state in buffer set `cur`: linear solve, candidate into set `cand`, cost and image blocks at
+// the candidate.  Everything the controller (host loop or k_lm_control) reads afterwards is in c.w.scal.
+int enqueue_lm_iteration(Ctx& c, int cur, int cand, LmDiag lm, int compute_scaling, const mpba_options& opt) {
+  mpba_handle* h = c.h;
+  int rc = enqueue_points_and_system(c, c.w.pose[cur], c.w.X[cur], cur, lm, compute_scaling, &opt, true);
+  if (rc) return rc;
+  {
+    Timer t(h, KS_CAM_UPDATE);
+    launch_cam_update(c.pv, c.w.pose[cur], c.w.y, c.w.Hc[cur], c.w.gc[cur], c.w.c_img, lm, c.w.pose[cand], c.w.scal,
+                      h->stream);
+  }
+  {
+    Timer t(h, KS_BACK_SUBSTITUTE);
+    launch_back_substitute(c.pv, c.w.X[cur], c.w.y, c.w.Hpp, c.w.gp, c.w.Linv, c.w.c_pt, c.w.fac,
+                           c.structure_only ? 0 : 1, lm, c.w.X[cand], c.w.pt_part, h->stream);
+  }
+  {
+    Timer t(h, KS_REDUCE);
+    launch_pt_scalars_step(c.w.pt_part, c.nblk, c.w.scal, h->stream);
+  }
+  if (c.sh) {
+    // every rank wrote the candidates of its own points: all-gather in place (equal counts, pt_stride per rank)
+    Timer t(h, KS_COLLECTIVE);
+    const size_t cnt = (size_t)c.sh->pt_stride * 4;
+    NC(nccl_api().AllGather(c.w.X[cand] + (size_t)c.sh->rank * cnt, c.w.X[cand], cnt, ncclDouble, h->comm, h->stream));
+  }
+  // cost (and, in case the step is accepted, Hcc / gc) at the candidate
+  rc = enqueue_image_pass(c, c.w.pose[cand], c.w.X[cand], cand, 0, opt.jacobi_scaling);
+  if (rc) return rc;
+  return combine_scalars(c);
+}
+
+// ---- device-controlled LM loop (lm_loop.cu) -----------------------------------------------------------------------
+// When: small and medium bundles (< 600 images, the cluster-resident PCG, single GPU, no per-kernel profiling) -- the
+// mapper's local and early global bundle adjustments, where the host controller's launches and synchronisations cost
+// more than the kernels.  lm_loop = 1 forces the host loop, 2 asks for the device loop wherever it is legal.
+bool device_lm_legal(const Ctx& c, const mpba_options& opt) {
+  return !c.sh && !c.h->profile && opt.verbose == 0 && !c.structure_only && c.cl > 0 && c.coarse_lag == 0 &&
+         opt.max_num_iterations <= LM_DEVICE_MAX_ITERATIONS && c.w.ld != nullptr && c.h->h_lm != nullptr &&
+         c.h->side != nullptr;
+}
+
+struct DeviceLmResult {
+  int termination = -1, msg = 0, iteration = 0, n_ok = 0, n_bad = 0, nrows = 0;
+  int64_t total_pcg = 0;
+  double minimum_cost = 0.0;
+};
+
+int run_device_lm(Ctx& c, const mpba_problem* prob, const mpba_options& opt, double radius, double x_cost,
+                  double fixed_cost, double gmax_c, DeviceLmResult& out) {
+  mpba_handle* h = c.h;
+  c.device_lm = true;
+  LmDiag lm = make_lm(radius, opt.min_lm_diagonal, opt.max_lm_diagonal);
+  lm.dev = c.w.ld;
+  LmControl ctl;
+  ctl.function_tolerance = opt.function_tolerance;
+  ctl.gradient_tolerance = opt.gradient_tolerance;
+  ctl.parameter_tolerance = opt.parameter_tolerance;
+  ctl.min_relative_decrease = opt.min_relative_decrease;
+  ctl.max_trust_region_radius = opt.max_trust_region_radius;
+  ctl.min_trust_region_radius = opt.min_trust_region_radius;
+  ctl.max_num_iterations = opt.max_num_iterations;
+  ctl.max_consecutive_invalid = opt.max_num_consecutive_invalid_steps;
+  LmAcceptCopy cp;
+  const size_t C = (size_t)c.pv.C, P = (size_t)c.pv.P;
+  cp.src[0] = c.w.pose[1]; cp.dst[0] = c.w.pose[0]; cp.n[0] = C * 8;
+  cp.src[1] = c.w.X[1];    cp.dst[1] = c.w.X[0];    cp.n[1] = P * 4;
+  cp.src[2] = c.w.Hc[1];   cp.dst[2] = c.w.Hc[0];   cp.n[2] = C * 21;
+  cp.src[3] = c.w.gc[1];   cp.dst[3] = c.w.gc[0];   cp.n[3] = C * 6;
+
+  // everything a kernel node of the body bakes in: the problem (pointers and sizes), the workspace, the options, the
+  // PCG cluster plan and its coarse space
+  std::vector<unsigned char> sig;
+  auto add = [&](const void* p, size_t n) { sig.insert(sig.end(), (const unsigned char*)p, (const unsigned char*)p + n); };
+  add(prob, sizeof(*prob));
+  add(&c.w, sizeof(c.w));
+  add(&opt, sizeof(opt));
+  add(&c.cla, sizeof(c.cla));
+  add(&c.coarse, sizeof(c.coarse));
+  add(&c.cl, sizeof(c.cl));
+  add(&c.cl_smem, sizeof(c.cl_smem));
+  add(&c.pv.loss, sizeof(c.pv.loss));
+
+  launch_lm_init(c.w.ld, c.w.rows, radius, x_cost, fixed_cost, gmax_c, c.w.scal, h->stream);
+  h->launch_count += 1;
+  if (h->lm_exec == nullptr || sig != h->lm_signature) {
+    if (h->lm_exec) cudaGraphExecDestroy(h->lm_exec);
+    if (h->lm_graph) cudaGraphDestroy(h->lm_graph);
+    h->lm_exec = nullptr;
+    h->lm_graph = nullptr;
+    h->lm_signature.clear();
+    CU(cudaGraphCreate(&h->lm_graph, 0));
+    cudaGraphConditionalHandle handle;
+    CU(cudaGraphConditionalHandleCreate(&handle, h->lm_graph, 1, cudaGraphCondAssignDefault));
+    cudaGraphNodeParams np = {};
+    np.type = cudaGraphNodeTypeConditional;
+    np.conditional.handle = handle;
+    np.conditional.type = cudaGraphCondTypeWhile;
+    np.conditional.size = 1;
+    cudaGraphNode_t node;
+    CU(cudaGraphAddNode(&node, h->lm_graph, nullptr, 0, &np));
+    cudaGraph_t body = np.conditional.phGraph_out[0];
+    const int64_t lc0 = h->launch_count;
+    int64_t slot0[MPBA_NUM_KERNELS];
+    memcpy(slot0, h->launches, sizeof(slot0));
+    // captured on the handle's own stream (the caller's may be the legacy default stream, which cannot capture);
+    // nothing runs during capture, the graph itself is launched on the caller's stream
+    if (h->side == nullptr) return fail(h, MPBA_E_CUDA, "device LM loop: no capture stream");
+    CU(cudaStreamSynchronize(h->side));
+    CU(cudaStreamBeginCaptureToGraph(h->side, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+    cudaStream_t callers = h->stream;
+    h->stream = h->side;
+    int rc = enqueue_lm_iteration(c, 0, 1, lm, -1, opt);
+    if (rc == MPBA_OK) {
+      launch_lm_control(c.w.ld, c.w.rows, c.w.scal, ctl, handle, 1, h->stream);
+      launch_lm_accept(c.w.ld, cp, h->stream);
+      h->launch_count += 2;
+    }
+    h->stream = callers;
+    const cudaError_t ce = cudaStreamEndCapture(h->side, nullptr);  // always: the stream must leave capture mode
+    h->lm_body_launches = h->launch_count - lc0;
+    for (int k = 0; k < MPBA_NUM_KERNELS; ++k) h->lm_body_slot[k] = h->launches[k] - slot0[k];
+    h->launch_count = lc0;
+    memcpy(h->launches, slot0, sizeof(slot0));
+    if (rc) return rc;
+    if (ce != cudaSuccess) return fail(h, MPBA_E_CUDA, std::string("LM graph capture: ") + cudaGetErrorString(ce));
+    CU(cudaGraphInstantiate(&h->lm_exec, h->lm_graph, 0));
+    h->lm_signature = sig;
+  }
+  CU(cudaGraphLaunch(h->lm_exec, h->stream));
+  CU(cudaMemcpyAsync(h->h_lm, c.w.ld, LM_DEV_DOUBLES * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  CU(cudaGetLastError());
+  const double* ld = h->h_lm;
+  out.termination = (int)ld[LD_TERMINATION];
+  out.msg = (int)ld[LD_MSG];
+  out.iteration = (int)ld[LD_ITERATION];
+  out.n_ok = (int)ld[LD_N_OK];
+  out.n_bad = (int)ld[LD_N_BAD];
+  out.nrows = (int)ld[LD_NROWS];
+  out.total_pcg = (int64_t)ld[LD_TOTAL_PCG];
+  out.minimum_cost = ld[LD_MIN_COST];
+  // the body ran once per LM iteration (a gradient-tolerance exit ends inside an iteration that is not counted)
+  const int64_t bodies = out.iteration + ((out.msg == LM_MSG_GRADIENT) ? 1 : 0);
+  h->launch_count += h->lm_body_launches * bodies;
+  for (int k = 0; k < MPBA_NUM_KERNELS; ++k) h->launches[k] += h->lm_body_slot[k] * bodies;
+  if (out.termination < 0 || out.nrows < 1 || out.nrows > LM_DEVICE_MAX_ITERATIONS + 2)
+    return fail(h, MPBA_E_CUDA, "device LM loop ended without a termination state");
+  return MPBA_OK;
+}
+
 }  // namespace
 
 // =================================================================================================
@@ -778,6 +943,8 @@ void mpba_default_options(mpba_options* o) {
   o->pcg_coarse = 0;
   o->behind_camera = 0;
   o->coarse_lag = 1;
+  o->lm_loop = 0;
+  o->reserved0 = 0;
 }
 
 int mpba_create(mpba_handle** out, int device, void* cuda_stream) {
@@ -790,6 +957,7 @@ int mpba_create(mpba_handle** out, int device, void* cuda_stream) {
   h->device = device;
   h->stream = static_cast<cudaStream_t>(cuda_stream);
   if (cudaSetDevice(device) != cudaSuccess || cudaMallocHost(&h->h_scal, S_COUNT * sizeof(double)) != cudaSuccess ||
+      cudaMallocHost(&h->h_lm, LM_DEV_DOUBLES * sizeof(double)) != cudaSuccess ||
       cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess) {
     delete h;
     return MPBA_E_CUDA;
@@ -826,7 +994,10 @@ void mpba_destroy(mpba_handle* h) {
   }
   for (cudaEvent_t e : {h->ev_s_ready, h->ev_asm_done, h->ev_inv_done[0], h->ev_inv_done[1]})
     if (e) cudaEventDestroy(e);
+  if (h->lm_exec) cudaGraphExecDestroy(h->lm_exec);
+  if (h->lm_graph) cudaGraphDestroy(h->lm_graph);
   if (h->h_scal) cudaFreeHost(h->h_scal);
+  if (h->h_lm) cudaFreeHost(h->h_lm);
   if (h->h_stage) cudaFreeHost(h->h_stage);
   if (h->comm) nccl_api().CommDestroy(h->comm);
   delete h;
@@ -1155,38 +1326,31 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
     msg = "Maximum number of iterations reached.";
   }
 
+  const bool device_lm = termination < 0 && opt.lm_loop != 1 && device_lm_legal(c, opt) &&
+                         (opt.lm_loop == 2 || prob->num_images < 600);
+  if (device_lm) {
+    // the state sits in buffer set 0 (cur == 0 here); the candidate of every iteration in set 1
+    DeviceLmResult dl;
+    rc = run_device_lm(c, prob, opt, radius, x_cost, fixed_cost, gmax_c, dl);
+    if (rc) return rc;
+    const mpba_iteration* rows = reinterpret_cast<const mpba_iteration*>(h->h_lm + LD_COUNT);
+    nrows = 0;
+    for (int k = 0; k < dl.nrows; ++k) push(rows[k]);
+    termination = dl.termination;
+    msg = lm_message(dl.msg);
+    iteration = dl.iteration;
+    n_ok = dl.n_ok;
+    n_bad = dl.n_bad;
+    total_pcg = dl.total_pcg;
+    minimum_cost = dl.minimum_cost;
+  }
+
   while (termination < 0) {
     const int cand = cur ^ 1;
     const LmDiag lm = make_lm(radius, opt.min_lm_diagonal, opt.max_lm_diagonal);
-    rc = enqueue_points_and_system(c, c.w.pose[cur], c.w.X[cur], cur, lm, first ? 1 : 0, &opt, true);
+    rc = enqueue_lm_iteration(c, cur, cand, lm, first ? 1 : 0, opt);
     if (rc) return rc;
     first = false;
-    {
-      Timer t(h, KS_CAM_UPDATE);
-      launch_cam_update(c.pv, c.w.pose[cur], c.w.y, c.w.Hc[cur], c.w.gc[cur], c.w.c_img, lm, c.w.pose[cand], c.w.scal,
-                        h->stream);
-    }
-    {
-      Timer t(h, KS_BACK_SUBSTITUTE);
-      launch_back_substitute(c.pv, c.w.X[cur], c.w.y, c.w.Hpp, c.w.gp, c.w.Linv, c.w.c_pt, c.w.fac,
-                             c.structure_only ? 0 : 1, lm, c.w.X[cand],
-                             c.w.pt_part, h->stream);
-    }
-    {
-      Timer t(h, KS_REDUCE);
-      launch_pt_scalars_step(c.w.pt_part, c.nblk, c.w.scal, h->stream);
-    }
-    if (c.sh) {
-      // every rank wrote the candidates of its own points: all-gather in place (equal counts, pt_stride per rank)
-      Timer t(h, KS_COLLECTIVE);
-      const size_t cnt = (size_t)c.sh->pt_stride * 4;
-      NC(nccl_api().AllGather(c.w.X[cand] + (size_t)c.sh->rank * cnt, c.w.X[cand], cnt, ncclDouble, h->comm, h->stream));
-    }
-    // cost (and, in case the step is accepted, Hcc / gc) at the candidate
-    rc = enqueue_image_pass(c, c.w.pose[cand], c.w.X[cand], cand, 0, opt.jacobi_scaling);
-    if (rc) return rc;
-    rc = combine_scalars(c);
-    if (rc) return rc;
     rc = fetch_scalars(c);
     if (rc) return rc;
     const double* s = h->h_scal;

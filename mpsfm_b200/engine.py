@@ -90,7 +90,7 @@ class MpbaOptions(C.Structure):
         ("function_tolerance", C.c_double), ("gradient_tolerance", C.c_double),
         ("parameter_tolerance", C.c_double), ("pcg_tolerance", C.c_double),
         ("profile", C.c_int32), ("verbose", C.c_int32), ("pcg_kernel", C.c_int32), ("pcg_coarse", C.c_int32),
-        ("behind_camera", C.c_int32), ("coarse_lag", C.c_int32),
+        ("behind_camera", C.c_int32), ("coarse_lag", C.c_int32), ("lm_loop", C.c_int32), ("reserved0", C.c_int32),
     ]
 
 

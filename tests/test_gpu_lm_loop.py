@@ -1,0 +1,109 @@
+"""The LM controller on the device (csrc/lm_loop.cu: one CUDA-graph WHILE node per solve) against the host loop of
+ba_solver.cu: the same kernels run in the same order on the same numbers, so every iteration row, the termination and
+the final state must agree BIT FOR BIT -- and through the host loop with the oracle (tests/test_gpu_parity.py).
+
+These are the mapper's bundle sizes (mpsfm/sfm/mapper/base.py:442-474: local bundle adjustment on 6-50 images)."""
+
+import numpy as np
+import pytest
+
+from mpsfm_b200 import engine
+from mpsfm_b200.problem import CameraModel, LossType
+from mpsfm_b200.synthetic import make_scene
+
+pytestmark = pytest.mark.gpu
+
+CASES = {
+    "local_6": dict(num_images=6, num_points=3000, obs_per_point=4),
+    "local_20_opencv": dict(num_images=20, num_points=4000, obs_per_point=5, model=CameraModel.OPENCV,
+                            reproj_loss=LossType.HUBER),
+    "local_50_fisheye": dict(num_images=50, num_points=6000, obs_per_point=5, model=CameraModel.OPENCV_FISHEYE),
+    # far from the optimum: rejected steps, the trust region shrinks and grows
+    "rough_start_12": dict(num_images=12, num_points=1500, obs_per_point=4, pose_rot_noise=0.08, pose_pos_noise=0.8,
+                           point_noise=1.0, outlier_frac=0.2),
+    "global_150": dict(num_images=150, num_points=12000, obs_per_point=5, model=CameraModel.SIMPLE_RADIAL),
+}
+
+
+def _solve(prob, loop, **kw):
+    ba = engine.BundleAdjuster(prob, device=0)
+    s = ba.solve(engine.default_options(lm_loop=loop, **kw))
+    q, t, X = ba.state()
+    return ba, s, np.hstack([q, t]), X
+
+
+def _same_rows(a, b):
+    assert len(a) == len(b)
+    for ra, rb in zip(a, b):
+        for k in ra:
+            va, vb = ra[k], rb[k]
+            assert va == vb or (isinstance(va, float) and np.isnan(va) and np.isnan(vb)), (k, va, vb)
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_device_loop_equals_host_loop(name):
+    kw = dict(CASES[name])
+    prob = make_scene(kw.pop("num_images"), kw.pop("num_points"), kw.pop("obs_per_point"), seed=3, **kw)
+    _, sh, pose_h, X_h = _solve(prob, 1)
+    ba, sd, pose_d, X_d = _solve(prob, 2)
+    assert sh.num_iterations >= 3
+    assert (sd.termination, sd.message, sd.num_iterations) == (sh.termination, sh.message, sh.num_iterations)
+    assert (sd.num_successful_steps, sd.num_unsuccessful_steps) == (sh.num_successful_steps, sh.num_unsuccessful_steps)
+    assert sd.total_pcg_iterations == sh.total_pcg_iterations
+    assert sd.initial_cost == sh.initial_cost and sd.final_cost == sh.final_cost and sd.fixed_cost == sh.fixed_cost
+    _same_rows(sd.iterations, sh.iterations)
+    assert np.array_equal(pose_d, pose_h) and np.array_equal(X_d, X_h)
+    # the device loop launches k_lm_init once and k_lm_control + k_lm_accept per iteration on top of the host
+    # loop's kernels (which has one memset per iteration instead): it did run
+    assert sd.kernel_launches > sh.kernel_launches
+
+    # default options pick the device loop below 600 images
+    _, s0, pose_0, X_0 = _solve(prob, 0)
+    assert s0.kernel_launches == sd.kernel_launches and np.array_equal(pose_0, pose_d)
+
+    # a second solve on the same adjuster reuses the instantiated graph: same answer from the same start
+    ba.reset_state()
+    s2 = ba.solve(engine.default_options(lm_loop=2))
+    q_2, t_2, X_2 = ba.state()
+    pose_2 = np.hstack([q_2, t_2])
+    _same_rows(s2.iterations, sd.iterations)
+    assert np.array_equal(pose_2, pose_d) and np.array_equal(X_2, X_d)
+    # ... and with other options the graph is rebuilt (the iteration cap is baked into the controller's arguments)
+    ba.reset_state()
+    s3 = ba.solve(engine.default_options(lm_loop=2, max_num_iterations=2))
+    assert s3.num_iterations == 2 and s3.termination == "NO_CONVERGENCE"
+    _, sh3, _, _ = _solve(prob, 1, max_num_iterations=2)
+    _same_rows(s3.iterations, sh3.iterations)
+
+
+def test_rejected_steps_are_covered():
+    """A rough start with a huge first trust region (plain Gauss-Newton steps): some are rejected, the radius shrinks."""
+    kw = dict(CASES["rough_start_12"])
+    prob = make_scene(kw.pop("num_images"), kw.pop("num_points"), kw.pop("obs_per_point"), seed=3, **kw)
+    found = False
+    for radius in (1e16, 1e10, 1e7):
+        _, sh, pose_h, X_h = _solve(prob, 1, initial_trust_region_radius=radius)
+        _, sd, pose_d, X_d = _solve(prob, 2, initial_trust_region_radius=radius)
+        _same_rows(sd.iterations, sh.iterations)
+        assert np.array_equal(pose_d, pose_h) and np.array_equal(X_d, X_h)
+        assert (sd.num_successful_steps, sd.num_unsuccessful_steps) == (sh.num_successful_steps, sh.num_unsuccessful_steps)
+        found = found or sd.num_unsuccessful_steps > 0
+    assert found, "pick a rougher start: this case is meant to exercise the reject branch"
+
+
+def test_termination_rules_on_the_device():
+    prob = make_scene(8, 1200, 4, seed=5)
+    for kw in (dict(gradient_tolerance=1e30), dict(function_tolerance=0.5), dict(parameter_tolerance=1e3),
+               dict(max_num_iterations=1), dict(min_trust_region_radius=1e5)):
+        _, sh, pose_h, X_h = _solve(prob, 1, **kw)
+        _, sd, pose_d, X_d = _solve(prob, 2, **kw)
+        assert (sd.termination, sd.message, sd.num_iterations) == (sh.termination, sh.message, sh.num_iterations), kw
+        _same_rows(sd.iterations, sh.iterations)
+        assert np.array_equal(pose_d, pose_h) and np.array_equal(X_d, X_h), kw
+
+
+def test_host_loop_is_kept_where_the_device_loop_is_not_legal():
+    prob = make_scene(10, 1500, 4, seed=9)
+    ba = engine.BundleAdjuster(prob, device=0)
+    s = ba.solve(engine.default_options(lm_loop=2, profile=1))  # per-kernel events need the stream launches
+    assert s.termination == "CONVERGENCE" and ba.kernel_times()["pcg"][1] >= s.num_iterations

@@ -28,7 +28,7 @@ def test_library_exports_every_symbol_of_the_header():
 def test_struct_sizes_match_the_c_abi():
     # natural alignment, same as the C compiler's
     assert C.sizeof(engine.MpbaIteration) == 64
-    assert C.sizeof(engine.MpbaOptions) == 16 + 10 * 8 + 24
+    assert C.sizeof(engine.MpbaOptions) == 16 + 10 * 8 + 32
     assert C.sizeof(engine.MpbaProblem) % 8 == 0
     from mpsfm_b200 import integration
 
