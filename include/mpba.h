@@ -140,6 +140,10 @@ typedef struct mpba_problem {
 #define MPBA_FLAG_STRUCTURE_ONLY 1
 
 #define MPBA_CHUNK 1024
+/* Image-order chunk length the host layout uses for a bundle of num_obs observations: MPBA_CHUNK where the bundle
+ * fills the device, halved down to 128 while fewer than ~4 chunks per SM would result -- k_img_chunks is one CTA per
+ * chunk, and the mapper's local bundles (10^4 observations) otherwise run on a dozen CTAs. */
+int32_t mpba_chunk_size(int64_t num_obs);
 
 /* Ceres Solver::Options subset; defaults (mpba_default_options) are Ceres 2.1's, which is what the
  * reference runs with (bundle_adjustment.py:285-293 sets only solver type / threads / verbosity). */
@@ -162,8 +166,10 @@ typedef struct mpba_options {
                                               O(eps^2): 1e-10 leaves the LM trajectory on the exact-solve one to ~1e-13 */
   int32_t profile;                         /* 1: CUDA-event time every kernel launch (see mpba_kernel_times) */
   int32_t verbose;
-  int32_t pcg_kernel;                      /* 0: automatic (cluster-resident when S fits one 16-CTA cluster,
-                                              grid-wide otherwise), 1: force grid-wide, 2: prefer cluster */
+  int32_t pcg_kernel;                      /* 0: automatic (up to 21 images: dense direct solve by one CTA, no CG at all
+                                              -- iterations report pcg_iterations = 0; cluster-resident PCG when S fits
+                                              one 16-CTA cluster, grid-wide otherwise), 1: force grid-wide PCG,
+                                              2: cluster PCG when it fits (never the dense solve), 3: as 0 */
   int32_t pcg_coarse;                      /* 0: two-level preconditioner (block-Jacobi + gauge-mode coarse space over
                                               groups of images) with the cluster kernel, 1: block-Jacobi only */
   int32_t behind_camera;                   /* point at z < epsilon in the camera frame.  0 (default): COLMAP >= 3.11's

@@ -16,6 +16,8 @@
 #include <stdlib.h>
 
 #include "ba_kernels.cuh"
+#include "step_common.cuh"
+#include "lm_control.cuh"
 
 namespace cg = cooperative_groups;
 
@@ -23,9 +25,7 @@ namespace mpba {
 
 namespace {
 
-constexpr unsigned FULL = 0xffffffffu;
 
-__device__ __forceinline__ int upper_idx(int i, int j) { return i * (13 - i) / 2 + (j - i); }
 
 struct ImgConst {
   double pose[8];
@@ -52,38 +52,6 @@ __device__ __forceinline__ void load_point(const double* __restrict__ X, int p, 
   const double2* xp = reinterpret_cast<const double2*>(X + 4 * (size_t)p);
   const double2 a = __ldg(xp), b = __ldg(xp + 1);
   out[0] = a.x; out[1] = a.y; out[2] = b.x;
-}
-
-// deterministic block sum (fixed shuffle tree, then warps in order); result valid in every thread
-template <int NWARP>
-__device__ __forceinline__ double block_sum(double v, double* sm /* [NWARP+1] */) {
-  for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(FULL, v, off);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  __syncthreads();
-  if (lane == 0) sm[warp] = v;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double s = 0.0;
-    for (int w = 0; w < NWARP; ++w) s += sm[w];
-    sm[NWARP] = s;
-  }
-  __syncthreads();
-  return sm[NWARP];
-}
-template <int NWARP>
-__device__ __forceinline__ double block_max(double v, double* sm) {
-  for (int off = 16; off > 0; off >>= 1) v = fmax(v, __shfl_down_sync(FULL, v, off));
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  __syncthreads();
-  if (lane == 0) sm[warp] = v;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double s = 0.0;
-    for (int w = 0; w < NWARP; ++w) s = fmax(s, sm[w]);
-    sm[NWARP] = s;
-  }
-  __syncthreads();
-  return sm[NWARP];
 }
 
 // ================================================================================================
@@ -200,12 +168,9 @@ __global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(Probl
 }
 
 // one thread per (image, value): sums the image's chunk partials in chunk order
-__global__ void __launch_bounds__(256) k_img_finalize(ProblemView pv, const double* __restrict__ chunk_part,
-                                                      double* __restrict__ Hc, double* __restrict__ gc,
-                                                      double* __restrict__ img_part) {
-  const int gid = blockIdx.x * 256 + threadIdx.x;
-  const int i = gid >> 5, v = gid & 31;
-  if (i >= pv.C || v >= 29) return;
+// value v (0..20 Hcc upper, 21..26 gc, 27..28 costs) of image i: chunk partials summed in chunk order
+__device__ __forceinline__ void img_finalize_one(const ProblemView& pv, const double* __restrict__ chunk_part, double* Hc,
+                                                 double* gc, double* img_part, int i, int v) {
   double s = 0.0;
   for (int ch = pv.img_chunk_ptr[i]; ch < pv.img_chunk_ptr[i + 1]; ++ch) s += chunk_part[(size_t)ch * IMG_PART + v];
   const unsigned mask = pv.img_free_mask[i];
@@ -225,12 +190,18 @@ __global__ void __launch_bounds__(256) k_img_finalize(ProblemView pv, const doub
   }
 }
 
-__global__ void __launch_bounds__(1024) k_img_scalars(int C, const uint8_t* __restrict__ free_mask,
-                                                      const double* __restrict__ img_part,
-                                                      const double* __restrict__ Hc, const double* __restrict__ gc,
-                                                      double* __restrict__ c_img, int compute_scaling,
-                                                      int jacobi_scaling, double* __restrict__ scal) {
-  __shared__ double sm[33];
+__global__ void __launch_bounds__(256) k_img_finalize(ProblemView pv, const double* __restrict__ chunk_part,
+                                                      double* __restrict__ Hc, double* __restrict__ gc,
+                                                      double* __restrict__ img_part) {
+  const int gid = blockIdx.x * 256 + threadIdx.x;
+  const int i = gid >> 5, v = gid & 31;
+  if (i >= pv.C || v >= 29) return;
+  img_finalize_one(pv, chunk_part, Hc, gc, img_part, i, v);
+}
+
+__device__ __forceinline__ void img_scalars_body(int C, const uint8_t* __restrict__ free_mask, const double* img_part,
+                                                 const double* Hc, const double* gc, double* c_img,
+                                                 int compute_scaling, int jacobi_scaling, double* scal, double* sm) {
   double cf = 0.0, cx = 0.0, gm = 0.0;
   for (int i = threadIdx.x; i < C; i += 1024) {
     cf += img_part[2 * (size_t)i];
@@ -254,6 +225,34 @@ __global__ void __launch_bounds__(1024) k_img_scalars(int C, const uint8_t* __re
     scal[S_COST_FREE] = cf;
     scal[S_COST_FIXED] = cx;
     scal[S_GMAX_C] = gm;
+  }
+}
+
+__global__ void __launch_bounds__(1024) k_img_scalars(int C, const uint8_t* __restrict__ free_mask,
+                                                      const double* __restrict__ img_part,
+                                                      const double* __restrict__ Hc, const double* __restrict__ gc,
+                                                      double* __restrict__ c_img, int compute_scaling,
+                                                      int jacobi_scaling, double* __restrict__ scal) {
+  __shared__ double sm[33];
+  img_scalars_body(C, free_mask, img_part, Hc, gc, c_img, compute_scaling, jacobi_scaling, scal, sm);
+}
+
+// Small bundles: the two kernels above as one CTA (same sums, same order), then -- device-controlled LM loop -- the
+// LM decision by thread 0 (lm_control.cuh) and the condition of the graph's WHILE node.
+__global__ void __launch_bounds__(1024) k_img_tail(ProblemView pv, const double* __restrict__ chunk_part, double* Hc,
+                                                   double* gc, double* img_part, double* c_img, int compute_scaling,
+                                                   int jacobi_scaling, double* scal, LmTail tail, int with_tail) {
+  __shared__ double sm[33];
+  for (int gid = threadIdx.x; gid < pv.C * 32; gid += 1024) {
+    const int i = gid >> 5, v = gid & 31;
+    if (v < 29) img_finalize_one(pv, chunk_part, Hc, gc, img_part, i, v);
+  }
+  __syncthreads();  // Hc / gc / img_part of this CTA are complete and visible to it
+  img_scalars_body(pv.C, pv.img_free_mask, img_part, Hc, gc, c_img, compute_scaling, jacobi_scaling, scal, sm);
+  if (with_tail && threadIdx.x == 0) {
+    // scal[S_COST_FREE..S_GMAX_C] were written by this very thread; the rest by earlier kernels
+    const bool more = lm_control_step(tail.ld, tail.rows, scal, tail.ctl);
+    cudaGraphSetConditional(tail.handle, more ? 1u : 0u);
   }
 }
 
@@ -379,14 +378,6 @@ __device__ __forceinline__ void point_terms(const ObsLin& o, const double* R, do
   v[6] = R[0] * o.h[0] + R[3] * o.h[1] + R[6] * o.h[2];
   v[7] = R[1] * o.h[0] + R[4] * o.h[1] + R[7] * o.h[2];
   v[8] = R[2] * o.h[0] + R[5] * o.h[1] + R[8] * o.h[2];
-}
-
-// device-controlled LM loop: the trust-region radius lives in device memory (see LmDiag)
-__device__ __forceinline__ void lm_resolve(LmDiag& lm) {
-  if (lm.dev != nullptr) {
-    lm.radius = __ldcg(lm.dev + LD_RADIUS);
-    lm.inv_radius = __ldcg(lm.dev + LD_INV_RADIUS);
-  }
 }
 
 // Per point, from the complete sums: Jacobi scale, LM damping, Cholesky of Hpp + D, Hpp^-1; writes the point's
@@ -1412,48 +1403,7 @@ __global__ void __launch_bounds__(1024) k_cam_update(ProblemView pv, const doubl
                                                     double* __restrict__ scal) {
   __shared__ double sm[33];
   lm_resolve(lm);
-  double step2 = 0.0, xn2 = 0.0, mcc = 0.0;
-  for (int i = threadIdx.x; i < pv.C; i += 1024) {
-    const double* ps = pose + (size_t)i * 8;
-    const double* yi = y + (size_t)i * 6;
-    const unsigned mask = pv.img_free_mask[i];
-    // step norms of a sharded solve are summed over the ranks: every image counts at its owner only
-    const bool used = i >= pv.i0 && i < pv.i1 && pv.img_ptr[i + 1] > pv.img_ptr[i];
-    const double q[4] = {ps[0], ps[1], ps[2], ps[3]};
-    const double d[3] = {-yi[0], -yi[1], -yi[2]};
-    double qn[4];
-    quat_plus(q, d, qn);
-    double* out = pose_cand + (size_t)i * 8;
-    out[0] = qn[0]; out[1] = qn[1]; out[2] = qn[2]; out[3] = qn[3];
-    const double t0 = ps[4] - yi[3], t1 = ps[5] - yi[4], t2 = ps[6] - yi[5];
-    out[4] = t0; out[5] = t1; out[6] = t2; out[7] = ps[7];
-    if (used && (mask & 7u)) {
-      step2 += (qn[0] - q[0]) * (qn[0] - q[0]) + (qn[1] - q[1]) * (qn[1] - q[1]) + (qn[2] - q[2]) * (qn[2] - q[2]) +
-               (qn[3] - q[3]) * (qn[3] - q[3]);
-      xn2 += q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
-    }
-    if (used && (mask & 0x38u)) {
-      step2 += (t0 - ps[4]) * (t0 - ps[4]) + (t1 - ps[5]) * (t1 - ps[5]) + (t2 - ps[6]) * (t2 - ps[6]);
-      xn2 += ps[4] * ps[4] + ps[5] * ps[5] + ps[6] * ps[6];
-    }
-    // image part of the model cost change (g'y + y'Dy) / 2 over the free tangent coordinates (all images,
-    // replicated in a sharded solve: gc / Hc are complete on every rank)
-#pragma unroll
-    for (int r = 0; r < 6; ++r) {
-      if ((mask >> r) & 1u) {
-        const double dj = lm_damping(Hc[(size_t)i * 21 + upper_idx(r, r)], c_img[(size_t)i * 6 + r], lm.radius, lm.lo, lm.hi);
-        mcc += 0.5 * (gc[(size_t)i * 6 + r] * yi[r] + dj * yi[r] * yi[r]);
-      }
-    }
-  }
-  step2 = block_sum<32>(step2, sm);
-  xn2 = block_sum<32>(xn2, sm);
-  mcc = block_sum<32>(mcc, sm);
-  if (threadIdx.x == 0) {
-    scal[S_STEP2_C] = step2;
-    scal[S_XNORM2_C] = xn2;
-    scal[S_MCC_C] = mcc;
-  }
+  cam_update_body(pv, pose, y, Hc, gc, c_img, lm, pose_cand, scal, sm);
 }
 
 // Back-substitution from the stored Schur factors, one thread per observation (same warp packing as k_points).
@@ -1616,19 +1566,21 @@ __global__ void __launch_bounds__(PW_THREADS) k_back_substitute(ProblemView pv, 
 }
 
 __global__ void __launch_bounds__(1024) k_pt_scalars_step(const double* __restrict__ pt_part, int nblk,
-                                                          double* __restrict__ scal) {
+                                                          double* __restrict__ scal, int with_gmax) {
   __shared__ double sm[33];
-  double a = 0.0, b = 0.0, c = 0.0;
+  double a = 0.0, b = 0.0, c = 0.0, gm = 0.0;
   // two rows in flight per thread (same per-thread summation order as a plain loop: row i, then row i + 1024)
   int i = threadIdx.x;
   for (; i + 1024 < nblk; i += 2 * 1024) {
     const double* p0 = pt_part + (size_t)i * PT_PART;
     const double* p1 = pt_part + (size_t)(i + 1024) * PT_PART;
     const double a0 = p0[1], b0 = p0[2], c0 = p0[3], a1 = p1[1], b1 = p1[2], c1 = p1[3];
+    if (with_gmax) gm = fmax(gm, fmax(p0[0], p1[0]));
     a += a0; b += b0; c += c0;
     a += a1; b += b1; c += c1;
   }
   for (; i < nblk; i += 1024) {
+    if (with_gmax) gm = fmax(gm, pt_part[(size_t)i * PT_PART]);
     a += pt_part[(size_t)i * PT_PART + 1];
     b += pt_part[(size_t)i * PT_PART + 2];
     c += pt_part[(size_t)i * PT_PART + 3];
@@ -1636,10 +1588,12 @@ __global__ void __launch_bounds__(1024) k_pt_scalars_step(const double* __restri
   a = block_sum<32>(a, sm);
   b = block_sum<32>(b, sm);
   c = block_sum<32>(c, sm);
+  if (with_gmax) gm = block_max<32>(gm, sm);
   if (threadIdx.x == 0) {
     scal[S_MCC] = a;
     scal[S_STEP2_P] = b;
     scal[S_XNORM2_P] = c;
+    if (with_gmax) scal[S_GMAX_P] = gm;
   }
 }
 
@@ -1784,6 +1738,14 @@ void launch_img_finalize(const ProblemView& pv, const double* chunk_part, double
   const int n = pv.C * 32;
   k_img_finalize<<<(n + 255) / 256, 256, 0, st>>>(pv, chunk_part, Hc, gc, img_part);
 }
+void launch_img_tail(const ProblemView& pv, const double* chunk_part, double* Hc, double* gc, double* img_part,
+                     double* c_img, int compute_scaling, int jacobi_scaling, double* scal, const LmTail* tail,
+                     cudaStream_t st) {
+  LmTail t = {};
+  if (tail) t = *tail;
+  k_img_tail<<<1, 1024, 0, st>>>(pv, chunk_part, Hc, gc, img_part, c_img, compute_scaling, jacobi_scaling, scal, t,
+                                 tail ? 1 : 0);
+}
 void launch_img_scalars(const ProblemView& pv, const double* img_part, const double* Hc, const double* gc,
                         double* c_img, int compute_scaling, int jacobi_scaling, double* scal, cudaStream_t st) {
   k_img_scalars<<<1, 1024, 0, st>>>(pv.C, pv.img_free_mask, img_part, Hc, gc, c_img, compute_scaling, jacobi_scaling,
@@ -1879,8 +1841,8 @@ void launch_back_substitute(const ProblemView& pv, const double* X, const double
                                                                                   use_factors, lm, X_cand, pt_part,
                                                                                   prefetch_ahead);
 }
-void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, cudaStream_t st) {
-  k_pt_scalars_step<<<1, 1024, 0, st>>>(pt_part, nblk, scal);
+void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, int with_gmax, cudaStream_t st) {
+  k_pt_scalars_step<<<1, 1024, 0, st>>>(pt_part, nblk, scal, with_gmax);
 }
 void launch_evaluate(const ProblemView& pv, const double* pose, const double* X, double* r_reproj, double* r_depth,
                      cudaStream_t st) {

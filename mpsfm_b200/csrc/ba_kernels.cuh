@@ -105,6 +105,12 @@ struct LmAcceptCopy {
   double* dst[4];
   size_t n[4];
 };
+struct LmTail {  // the controller as the last step of the fused image tail kernel (launch_img_tail)
+  double* ld;
+  mpba_iteration* rows;
+  LmControl ctl;
+  cudaGraphConditionalHandle handle;
+};
 void launch_lm_init(double* ld, mpba_iteration* rows, double radius, double x_cost, double fixed_cost, double gmax_c,
                     double* scal, cudaStream_t st);
 void launch_lm_control(double* ld, mpba_iteration* rows, double* scal, const LmControl& o,
@@ -121,6 +127,13 @@ void launch_img_finalize(const ProblemView& pv, const double* chunk_part, double
 // image blocks are complete (in a sharded solve: after their all-reduce)
 void launch_img_scalars(const ProblemView& pv, const double* img_part, const double* Hc, const double* gc,
                         double* c_img, int compute_scaling, int jacobi_scaling, double* scal, cudaStream_t st);
+
+// Small bundles (<= IMG_TAIL_MAX_IMAGES images, single GPU): launch_img_finalize + launch_img_scalars as ONE CTA, same
+// sums in the same order; tail != nullptr appends the LM decision (lm_control.cuh) and sets the WHILE condition.
+constexpr int IMG_TAIL_MAX_IMAGES = 128;
+void launch_img_tail(const ProblemView& pv, const double* chunk_part, double* Hc, double* gc, double* img_part,
+                     double* c_img, int compute_scaling, int jacobi_scaling, double* scal, const LmTail* tail,
+                     cudaStream_t st);
 
 // ---- track order: Hpp, gp, point-block Cholesky, Schur factors ------------------------------------
 void launch_points(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,
@@ -227,6 +240,14 @@ cudaError_t launch_coarse_setup(const CoarsePlan& cp, int C, const double* pose,
 // the gauge modes alone (Z of every image at the given poses)
 cudaError_t launch_coarse_modes(int C, const double* pose, const uint8_t* free_mask, double* Zc, cudaStream_t st);
 
+// ---- dense direct solve of a small reduced camera system (dense_solve.cu) ----------------------------
+constexpr int DENSE_SOLVE_MAX_IMAGES = 21;  // 6 * 21 unknowns + the right-hand side = 127 columns of the register tile
+bool dense_solve_fits(int num_images);
+// pose_cand != nullptr: the camera step (launch_cam_update's work) runs as the epilogue of the same kernel
+cudaError_t launch_dense_solve(int C, const int32_t* row_ptr, const int32_t* col, const double* S, const double* rhs,
+                               double* y, double* scal, const ProblemView* pv, const double* pose, const double* Hc,
+                               const double* gc, const double* c_img, LmDiag lm, double* pose_cand, cudaStream_t st);
+
 // ---- step ---------------------------------------------------------------------------------------
 // q (+) -y, t - y, step norms, and the image part of the model cost change (g'y + y'Dy) / 2
 void launch_cam_update(const ProblemView& pv, const double* pose, const double* y, const double* Hc, const double* gc,
@@ -234,7 +255,8 @@ void launch_cam_update(const ProblemView& pv, const double* pose, const double* 
 void launch_back_substitute(const ProblemView& pv, const double* X, const double* y, const double* Hpp,
                             const double* gp, const double* Linv, const double* c_pt, const double* fac,
                             int use_factors, LmDiag lm, double* X_cand, double* pt_part, cudaStream_t st);
-void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, cudaStream_t st);
+// with_gmax: also S_GMAX_P (slot 0 of the partials, written by k_points) -- the LM loop defers that reduction to here
+void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, int with_gmax, cudaStream_t st);
 
 // ---- misc ---------------------------------------------------------------------------------------
 void launch_evaluate(const ProblemView& pv, const double* pose, const double* X, double* r_reproj, double* r_depth,

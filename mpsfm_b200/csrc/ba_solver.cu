@@ -292,6 +292,10 @@ struct Ctx {
   PcgGridCoarse gridco;  // grid kernel: groups of CTAs (build_grid_coarse_plan)
   const mpba_shard* sh = nullptr;  // sharded solve
   bool want_hinv = false;          // Hpp^-1 rows requested (mpba_point_covariances)
+  bool defer_gmax = false;         // LM loop: max |gp| is reduced together with the step scalars (one launch less)
+  const LmTail* tail = nullptr;    // device LM loop: the controller rides on the next fused image tail kernel
+  bool tail_done = false;
+  bool dense = false;              // reduced system solved directly by one CTA (dense_solve.cu): <= 21 images
   bool device_lm = false;          // LM controller on the device: no memset nodes in the loop body (lm_loop.cu)
   int coarse_lag = 0;              // 1: the PCG of linear solve i uses the coarse inverse built from S of solve i - 1
   int solves = 0;                  // linear solves enqueued so far in this call
@@ -375,6 +379,13 @@ int enqueue_image_pass(Ctx& c, const double* pose, const double* X, int k, int c
     NC(nc.AllReduce(c.w.gc[k], c.w.gc[k], C * 6, ncclDouble, ncclSum, h->comm, h->stream));
     NC(nc.AllReduce(c.w.img_part, c.w.img_part, C * 2, ncclDouble, ncclSum, h->comm, h->stream));
     NC(nc.GroupEnd());
+  } else if (c.pv.C <= IMG_TAIL_MAX_IMAGES) {
+    // small bundle: finalize + scalars (+ the LM decision of the device loop) in one single-CTA kernel
+    Timer t(h, KS_IMG_FINALIZE, 1);
+    launch_img_tail(c.pv, c.w.chunk_part, c.w.Hc[k], c.w.gc[k], c.w.img_part, c.w.c_img, compute_scaling, jacobi,
+                    c.w.scal, c.tail, h->stream);
+    if (c.tail) c.tail_done = true;
+    return MPBA_OK;
   } else {
     Timer t(h, KS_IMG_FINALIZE, 1);
     launch_img_finalize(c.pv, c.w.chunk_part, c.w.Hc[k], c.w.gc[k], c.w.img_part, h->stream);
@@ -417,7 +428,9 @@ int build_pcg_cluster_plan(Ctx& c, const mpba_problem* prob, int pcg_kernel, int
   mpba_handle* h = c.h;
   c.cl = 0;
   c.coarse.G = 0;
-  if (c.structure_only || pcg_kernel == 1) return MPBA_OK;
+  // small systems (the mapper's local bundles): one CTA solves S y = rhs directly, no plan to build
+  c.dense = !c.structure_only && (pcg_kernel == 0 || pcg_kernel == 3) && dense_solve_fits(prob->num_images);
+  if (c.structure_only || pcg_kernel == 1 || c.dense) return MPBA_OK;
   const int C = prob->num_images, B = prob->num_blocks;
   std::vector<int32_t> rp(C + 1), col(B);
   CU(cudaMemcpyAsync(rp.data(), prob->s_row_ptr, (C + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
@@ -603,7 +616,7 @@ int build_pcg_cluster_plan(Ctx& c, const mpba_problem* prob, int pcg_kernel, int
 int build_grid_coarse_plan(Ctx& c, const mpba_problem* prob, int pcg_coarse) {
   mpba_handle* h = c.h;
   c.gridco = PcgGridCoarse();
-  if (c.structure_only || c.cl > 0 || pcg_coarse == 1) return MPBA_OK;
+  if (c.structure_only || c.cl > 0 || c.dense || pcg_coarse == 1) return MPBA_OK;
   const int C = prob->num_images, B = prob->num_blocks;
   const PcgPlan pl = pcg_plan(h->device, C, c.max_row_blocks);
   const int G = std::min(coarse_max_groups(C, c.coarse_lag, false), pl.grid);
@@ -654,7 +667,7 @@ int build_grid_coarse_plan(Ctx& c, const mpba_problem* prob, int pcg_coarse) {
 }
 
 int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int kset, LmDiag lm, int compute_scaling,
-                              const mpba_options* opt, bool want_system) {
+                              const mpba_options* opt, bool want_system, double* pose_cand = nullptr) {
   mpba_handle* h = c.h;
   const bool schur = want_system && !c.structure_only;
   if (!c.device_lm) CU(cudaMemsetAsync(c.w.scal + S_BAD_POINTS, 0, sizeof(double), h->stream));
@@ -664,7 +677,7 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
                   c.want_hinv ? c.w.Hinv : nullptr, c.w.Linv, c.w.fac,
                   c.w.pt_part, c.w.scal, schur ? 1 : 0, h->stream);
   }
-  {
+  if (!(c.defer_gmax && want_system)) {
     Timer t(h, KS_REDUCE);
     launch_pt_scalars_gmax(c.w.pt_part, c.nblk, c.w.scal, h->stream);
   }
@@ -689,6 +702,15 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
       NC(nc.AllReduce(c.w.rhs, c.w.rhs, (size_t)c.pv.C * 6, ncclDouble, ncclSum, h->comm, h->stream));
       NC(nc.GroupEnd());
       launch_schur_finish(c.pv, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.S, c.w.rhs, h->stream);
+    }
+    if (c.dense) {
+      Timer t(h, KS_PCG);
+      // pose_cand given (LM iteration): the camera step runs as the epilogue of the same one-CTA kernel
+      cudaError_t e = launch_dense_solve(c.pv.C, c.pv.s_row_ptr, c.pv.s_col, c.w.S, c.w.rhs, c.w.y, c.w.scal, &c.pv, pose,
+                                         c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, pose_cand, h->stream);
+      if (e != cudaSuccess) return fail(h, MPBA_E_CUDA, std::string("dense solve launch: ") + cudaGetErrorString(e));
+      ++c.solves;
+      return MPBA_OK;
     }
     {
       Timer t(h, KS_BLOCK_INVERSE);
@@ -764,9 +786,10 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
 // the candidate.  Everything the controller (host loop or k_lm_control) reads afterwards is in c.w.scal.
 int enqueue_lm_iteration(Ctx& c, int cur, int cand, LmDiag lm, int compute_scaling, const mpba_options& opt) {
   mpba_handle* h = c.h;
-  int rc = enqueue_points_and_system(c, c.w.pose[cur], c.w.X[cur], cur, lm, compute_scaling, &opt, true);
+  int rc = enqueue_points_and_system(c, c.w.pose[cur], c.w.X[cur], cur, lm, compute_scaling, &opt, true,
+                                     c.dense ? c.w.pose[cand] : nullptr);
   if (rc) return rc;
-  {
+  if (!c.dense) {
     Timer t(h, KS_CAM_UPDATE);
     launch_cam_update(c.pv, c.w.pose[cur], c.w.y, c.w.Hc[cur], c.w.gc[cur], c.w.c_img, lm, c.w.pose[cand], c.w.scal,
                       h->stream);
@@ -778,7 +801,7 @@ int enqueue_lm_iteration(Ctx& c, int cur, int cand, LmDiag lm, int compute_scali
   }
   {
     Timer t(h, KS_REDUCE);
-    launch_pt_scalars_step(c.w.pt_part, c.nblk, c.w.scal, h->stream);
+    launch_pt_scalars_step(c.w.pt_part, c.nblk, c.w.scal, c.defer_gmax ? 1 : 0, h->stream);
   }
   if (c.sh) {
     // every rank wrote the candidates of its own points: all-gather in place (equal counts, pt_stride per rank)
@@ -797,7 +820,7 @@ int enqueue_lm_iteration(Ctx& c, int cur, int cand, LmDiag lm, int compute_scali
 // mapper's local and early global bundle adjustments, where the host controller's launches and synchronisations cost
 // more than the kernels.  lm_loop = 1 forces the host loop, 2 asks for the device loop wherever it is legal.
 bool device_lm_legal(const Ctx& c, const mpba_options& opt) {
-  return !c.sh && !c.h->profile && opt.verbose == 0 && !c.structure_only && c.cl > 0 && c.coarse_lag == 0 &&
+  return !c.sh && !c.h->profile && opt.verbose == 0 && !c.structure_only && (c.cl > 0 || c.dense) && c.coarse_lag == 0 &&
          opt.max_num_iterations <= LM_DEVICE_MAX_ITERATIONS && c.w.ld != nullptr && c.h->h_lm != nullptr &&
          c.h->side != nullptr;
 }
@@ -872,11 +895,22 @@ int run_device_lm(Ctx& c, const mpba_problem* prob, const mpba_options& opt, dou
     CU(cudaStreamBeginCaptureToGraph(h->side, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
     cudaStream_t callers = h->stream;
     h->stream = h->side;
+    LmTail tail;
+    tail.ld = c.w.ld;
+    tail.rows = c.w.rows;
+    tail.ctl = ctl;
+    tail.handle = handle;
+    c.tail = &tail;
+    c.tail_done = false;
     int rc = enqueue_lm_iteration(c, 0, 1, lm, -1, opt);
+    c.tail = nullptr;
     if (rc == MPBA_OK) {
-      launch_lm_control(c.w.ld, c.w.rows, c.w.scal, ctl, handle, 1, h->stream);
+      if (!c.tail_done) {  // beyond the fused image tail's size: the controller is a kernel of its own
+        launch_lm_control(c.w.ld, c.w.rows, c.w.scal, ctl, handle, 1, h->stream);
+        h->launch_count += 1;
+      }
       launch_lm_accept(c.w.ld, cp, h->stream);
-      h->launch_count += 2;
+      h->launch_count += 1;
     }
     h->stream = callers;
     const cudaError_t ce = cudaStreamEndCapture(h->side, nullptr);  // always: the stream must leave capture mode
@@ -1239,6 +1273,7 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
   // the lag pays where the dense inverse is the multi-CTA one (>= 600 images); small systems keep the synchronous
   // setup (a ~20 us single-CTA inverse) and with it the trajectory of the exact preconditioner
   c.coarse_lag = (opt.coarse_lag != 0 && prob->num_images >= 600) ? 1 : 0;
+  c.defer_gmax = true;
   struct SideDrain {  // whatever the exit path: nothing of this call is left running on the side stream
     mpba_handle* h;
     ~SideDrain() { if (h->side) cudaStreamSynchronize(h->side); }

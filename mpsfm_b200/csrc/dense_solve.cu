@@ -1,0 +1,194 @@
+// dense_solve.cu -- direct solve of a SMALL reduced camera system (6 C + 1 <= 128: up to 21 images) by one CTA.
+//
+// The mapper's local bundle adjustments (mpsfm/sfm/mapper/base.py:442-474) couple 6-20 images: S is a dense
+// 36..126-square SPD matrix.  Conjugate gradients on it cost 20-30 dependent iterations of several microseconds
+// each (84 us of a 157 us LM iteration at 6 images, round-2 profile); Ceres itself factors systems of this size
+// densely.  Here: the augmented matrix [S | rhs] lives IN REGISTERS of one 1024-thread CTA (thread (warp w, lane l)
+// owns the entries (w + 32 qi, l + 32 qj), 16 doubles) and is reduced by Gauss-Jordan elimination without pivoting
+// (S is SPD: no growth), one CTA barrier per pivot -- the scheme of coarse.cu's k_coarse_invert, ~0.16 us per pivot.
+// The elimination is done in place, so the registers end up holding S^-1 next to the solution column, and one step
+// of iterative refinement (r = rhs - S y from the block-CSR original, y += S^-1 r) removes the elimination's rounding.
+// The register tile is NQ x NQ slots per thread, NQ = ceil((6 C + 1) / 32): 2 for the reference's 6-image local
+// bundles.  The camera step that follows every linear solve (k_cam_update: one CTA as well) runs as the epilogue.
+#include "ba_kernels.cuh"
+#include "step_common.cuh"
+
+namespace mpba {
+
+namespace {
+
+constexpr int DS_DIM = 128;  // up to 4 x 4 register slots: 128 x 128 over 32 warps x 32 lanes
+constexpr unsigned FULLMASK = 0xffffffffu;
+static_assert(6 * DENSE_SOLVE_MAX_IMAGES + 1 <= DS_DIM, "register tile too small");
+
+struct CamStep {  // arguments of the fused camera step (cam_update_body); pose_cand == nullptr: solve only
+  ProblemView pv;
+  const double *pose, *Hc, *gc, *c_img;
+  LmDiag lm;
+  double* pose_cand;
+};
+
+__device__ __forceinline__ double ds_rcp(double a) {  // float seed + Newton steps: full double precision
+  double x = (double)(1.0f / (float)a);
+  x = x * (2.0 - a * x);
+  x = x * (2.0 - a * x);
+  return x * (2.0 - a * x);
+}
+
+template <int DS_Q>
+__global__ void __launch_bounds__(1024) k_dense_solve(int C, const int32_t* __restrict__ row_ptr,
+                                                      const int32_t* __restrict__ col, const double* __restrict__ S,
+                                                      const double* __restrict__ rhs, double* y,
+                                                      double* scal, CamStep cs) {
+  __shared__ int tbl[DENSE_SOLVE_MAX_IMAGES * DENSE_SOLVE_MAX_IMAGES];
+  __shared__ double prow[2][DS_DIM];
+  __shared__ double s_inv[2];
+  __shared__ double xs[DS_DIM], rs[DS_DIM];
+  __shared__ int s_bad;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n = 6 * C;  // column n carries the right-hand side
+  for (int k = tid; k < C * C; k += 1024) tbl[k] = -1;
+  if (tid == 0) s_bad = 0;
+  __syncthreads();
+  for (int i = tid; i < C; i += 1024)
+    for (int b = row_ptr[i]; b < row_ptr[i + 1]; ++b) tbl[i * C + col[b]] = b;
+  __syncthreads();
+  double a[DS_Q][DS_Q];
+#pragma unroll
+  for (int qi = 0; qi < DS_Q; ++qi)
+#pragma unroll
+    for (int qj = 0; qj < DS_Q; ++qj) {
+      const int i = warp + 32 * qi, j = lane + 32 * qj;
+      double v = 0.0;
+      if (i < n && j < n) {
+        const int b = tbl[(i / 6) * C + j / 6];
+        if (b >= 0) v = S[(size_t)b * 36 + (i % 6) * 6 + j % 6];
+      } else if (i < n && j == n) {
+        v = rhs[i];
+      }
+      a[qi][qj] = v;
+    }
+#pragma unroll
+  for (int PQ = 0; PQ < DS_Q; ++PQ) {  // pivots in chunks of 32: the register slot of the pivot row / column is static
+    for (int pw = 0; pw < 32; ++pw) {
+      const int p = 32 * PQ + pw;
+      if (p >= n) break;
+      double* pr = prow[p & 1];
+      if (warp == pw) {  // owner of row p: scale and publish it
+        const double piv = __shfl_sync(FULLMASK, a[PQ][PQ], pw);
+        const bool ok = piv > 0.0 && isfinite(piv);
+        const double inv = ok ? ds_rcp(piv) : 0.0;
+#pragma unroll
+        for (int qj = 0; qj < DS_Q; ++qj) pr[lane + 32 * qj] = a[PQ][qj] * inv;
+        if (lane == 0) {
+          s_inv[p & 1] = inv;
+          if (!ok) s_bad = 1;  // not positive definite: the LM loop treats the step as invalid
+        }
+      }
+      double f[DS_Q];
+#pragma unroll
+      for (int qi = 0; qi < DS_Q; ++qi) f[qi] = __shfl_sync(FULLMASK, a[qi][PQ], pw);  // column p of my rows
+      if (warp == pw) f[PQ] = 0.0;  // row p itself is replaced below
+      __syncthreads();
+      const double inv = s_inv[p & 1];
+      double rp[DS_Q];
+#pragma unroll
+      for (int qj = 0; qj < DS_Q; ++qj) rp[qj] = pr[lane + 32 * qj];
+#pragma unroll
+      for (int qi = 0; qi < DS_Q; ++qi)
+#pragma unroll
+        for (int qj = 0; qj < DS_Q; ++qj) a[qi][qj] -= f[qi] * rp[qj];
+      if (lane == pw) {  // column p of the inverse: -f / pivot
+#pragma unroll
+        for (int qi = 0; qi < DS_Q; ++qi) a[qi][PQ] = -f[qi] * inv;
+      }
+      if (warp == pw) {  // row p: the scaled pivot row, 1 / pivot on the diagonal
+#pragma unroll
+        for (int qj = 0; qj < DS_Q; ++qj) a[PQ][qj] = rp[qj];
+        if (lane == pw) a[PQ][PQ] = inv;
+      }
+    }
+  }
+  // solution column -> shared memory
+#pragma unroll
+  for (int qi = 0; qi < DS_Q; ++qi)
+#pragma unroll
+    for (int qj = 0; qj < DS_Q; ++qj) {
+      const int i = warp + 32 * qi, j = lane + 32 * qj;
+      if (i < n && j == n) xs[i] = a[qi][qj];
+    }
+  __syncthreads();
+  // one refinement step: r = rhs - S x (block-CSR original), x += S^-1 r (the registers)
+  if (tid < n) {
+    const int bi = tid / 6, r = tid % 6;
+    double acc = rhs[tid];
+    for (int b = row_ptr[bi]; b < row_ptr[bi + 1]; ++b) {
+      const double* Sb = S + (size_t)b * 36 + r * 6;
+      const double* xj = xs + 6 * col[b];
+#pragma unroll
+      for (int c = 0; c < 6; ++c) acc -= Sb[c] * xj[c];
+    }
+    rs[tid] = acc;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int qi = 0; qi < DS_Q; ++qi) {
+    const int i = warp + 32 * qi;
+    double acc = 0.0;
+#pragma unroll
+    for (int qj = 0; qj < DS_Q; ++qj) {
+      const int j = lane + 32 * qj;
+      if (j < n) acc += a[qi][qj] * rs[j];
+    }
+    for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(FULLMASK, acc, off);
+    if (i < n && lane == 0) y[i] = s_bad ? 0.0 : xs[i] + acc;
+  }
+  if (warp == 0) {  // |r| / |rhs| before the refinement, for the summary
+    double r2 = 0.0, b2 = 0.0;
+    for (int i = lane; i < n; i += 32) {
+      r2 += rs[i] * rs[i];
+      b2 += rhs[i] * rhs[i];
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+      r2 += __shfl_xor_sync(FULLMASK, r2, off);
+      b2 += __shfl_xor_sync(FULLMASK, b2, off);
+    }
+    if (lane == 0) {
+      scal[S_PCG_ITERS] = 0.0;  // a direct solve: no conjugate-gradient iterations
+      scal[S_PCG_FLAG] = s_bad ? 2.0 : 0.0;
+      scal[S_PCG_RES] = b2 > 0.0 ? sqrt(r2 / b2) : 0.0;
+    }
+  }
+  if (cs.pose_cand != nullptr) {
+    __shared__ double sm[33];
+    __syncthreads();  // y of this CTA is complete and visible to it
+    lm_resolve(cs.lm);
+    cam_update_body(cs.pv, cs.pose, y, cs.Hc, cs.gc, cs.c_img, cs.lm, cs.pose_cand, scal, sm);
+  }
+}
+
+}  // namespace
+
+bool dense_solve_fits(int num_images) { return num_images >= 1 && num_images <= DENSE_SOLVE_MAX_IMAGES; }
+
+cudaError_t launch_dense_solve(int C, const int32_t* row_ptr, const int32_t* col, const double* S, const double* rhs,
+                               double* y, double* scal, const ProblemView* pv, const double* pose, const double* Hc,
+                               const double* gc, const double* c_img, LmDiag lm, double* pose_cand, cudaStream_t st) {
+  CamStep cs = {};
+  if (pv != nullptr && pose_cand != nullptr) {
+    cs.pv = *pv;
+    cs.pose = pose; cs.Hc = Hc; cs.gc = gc; cs.c_img = c_img;
+    cs.lm = lm;
+    cs.pose_cand = pose_cand;
+  }
+  const int nq = (6 * C + 1 + 31) / 32;
+  switch (nq) {
+    case 1: k_dense_solve<1><<<1, 1024, 0, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
+    case 2: k_dense_solve<2><<<1, 1024, 0, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
+    case 3: k_dense_solve<3><<<1, 1024, 0, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
+    default: k_dense_solve<4><<<1, 1024, 0, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
+  }
+  return cudaGetLastError();
+}
+
+}  // namespace mpba

@@ -106,6 +106,12 @@ struct KeyMap {
 
 }  // namespace
 
+extern "C" int32_t mpba_chunk_size(int64_t num_obs) {
+  int32_t chunk = MPBA_CHUNK;
+  while (chunk > 128 && num_obs / chunk < 592) chunk /= 2;
+  return chunk;
+}
+
 extern "C" void mpba_host_layout_destroy(mpba_host_layout* L) { delete L; }
 
 extern "C" int mpba_host_layout_create(int32_t C, int32_t P, int32_t N, const int32_t* obs_img, const int32_t* obs_pt,
@@ -202,19 +208,20 @@ extern "C" int mpba_host_layout_create(int32_t C, int32_t P, int32_t N, const in
 
   lap("observation orders");
   // ---- image-order work chunks
+  const int64_t CHUNK = mpba_chunk_size(ptr_img[C]);
   L->img_chunk_ptr.assign((size_t)C + 1, 0);
   for (int32_t i = 0; i < C; ++i) {
     const int64_t cnt = ptr_img[i + 1] - ptr_img[i];
-    L->img_chunk_ptr[i + 1] = L->img_chunk_ptr[i] + (int32_t)((cnt + MPBA_CHUNK - 1) / MPBA_CHUNK);
+    L->img_chunk_ptr[i + 1] = L->img_chunk_ptr[i] + (int32_t)((cnt + CHUNK - 1) / CHUNK);
   }
   const int32_t nch = L->img_chunk_ptr[C];
   L->chunk_img.resize(nch); L->chunk_begin.resize(nch); L->chunk_end.resize(nch);
   for (int32_t i = 0; i < C; ++i)
     for (int32_t c = L->img_chunk_ptr[i]; c < L->img_chunk_ptr[i + 1]; ++c) {
-      const int64_t b = ptr_img[i] + (int64_t)(c - L->img_chunk_ptr[i]) * MPBA_CHUNK;
+      const int64_t b = ptr_img[i] + (int64_t)(c - L->img_chunk_ptr[i]) * CHUNK;
       L->chunk_img[c] = i;
       L->chunk_begin[c] = (int32_t)b;
-      L->chunk_end[c] = (int32_t)std::min<int64_t>(b + MPBA_CHUNK, ptr_img[i + 1]);
+      L->chunk_end[c] = (int32_t)std::min<int64_t>(b + CHUNK, ptr_img[i + 1]);
     }
 
   // ---- reduced camera system: block-CSR over co-visible image pairs, Schur work lists

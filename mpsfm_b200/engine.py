@@ -29,6 +29,14 @@ from .problem import MAX_CAMERA_PARAMS, BundleProblem
 
 _LIB_PATH = os.environ.get("MPBA_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libmpba.so")
 MPBA_CHUNK = 1024
+
+
+def chunk_size(num_obs: int) -> int:
+    """mpba_chunk_size of include/mpba.h: image-order chunk length for a bundle of ``num_obs`` observations."""
+    chunk = MPBA_CHUNK
+    while chunk > 128 and num_obs // chunk < 592:
+        chunk //= 2
+    return chunk
 MPBA_NUM_KERNELS = 14
 MPBA_UNIQUE_ID_BYTES = 128
 FLAG_STRUCTURE_ONLY = 1
@@ -116,7 +124,7 @@ class MpbaSummary(C.Structure):
 
 
 EXPORTS = (
-    "mpba_version", "mpba_create", "mpba_destroy", "mpba_last_error", "mpba_default_options",
+    "mpba_version", "mpba_chunk_size", "mpba_create", "mpba_destroy", "mpba_last_error", "mpba_default_options",
     "mpba_workspace_bytes", "mpba_evaluate", "mpba_linearize", "mpba_reduced_system", "mpba_solve",
     "mpba_kernel_times", "mpba_kernel_name", "mpba_point_covariances", "mpba_filter_tracks",
     "mpba_pack_tracks", "mpba_sample_maps", "mpba_depth_prior_terms", "mpba_segmented_median_workspace_bytes",
@@ -383,12 +391,13 @@ def build_layout_numpy(problem: BundleProblem) -> HostLayout:
     cm_xy = np.ascontiguousarray(pr.obs_xy[cm_src])
     cm_depth = np.ascontiguousarray(np.stack([d[cm_src], w[cm_src], a[cm_src]], axis=0))
 
-    nch = (img_cnt + MPBA_CHUNK - 1) // MPBA_CHUNK
+    CHUNK = chunk_size(int(img_ptr[-1]))
+    nch = (img_cnt + CHUNK - 1) // CHUNK
     img_chunk_ptr = _ptr_from_counts(nch)
     chunk_img = np.repeat(np.arange(Cn, dtype=np.int32), nch)
     local = np.arange(chunk_img.shape[0], dtype=np.int64) - img_chunk_ptr[chunk_img]
-    chunk_begin = (img_ptr[chunk_img] + local * MPBA_CHUNK).astype(np.int32)
-    chunk_end = np.minimum(chunk_begin.astype(np.int64) + MPBA_CHUNK, img_ptr[chunk_img + 1]).astype(np.int32)
+    chunk_begin = (img_ptr[chunk_img] + local * CHUNK).astype(np.int32)
+    chunk_end = np.minimum(chunk_begin.astype(np.int64) + CHUNK, img_ptr[chunk_img + 1]).astype(np.int32)
 
     # ---- reduced camera system structure and the Schur work lists (one unit per upper block)
     structure_only = bool(np.all(pr.img_free_mask == 0))

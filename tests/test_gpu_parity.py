@@ -227,6 +227,26 @@ def test_no_cpu_fallback_errors_are_loud():
     ba.workspace = ws
 
 
+@pytest.mark.parametrize("shape", [(2, 60, 2), (6, 80, 4), (14, 900, 5), (21, 1500, 6)])
+@pytest.mark.parametrize("radius", [1e4, 1e12])
+def test_dense_direct_solve_of_small_systems(shape, radius):
+    """Up to 21 images the reduced camera system is solved directly by one CTA (dense_solve.cu; the default,
+    pcg_kernel = 0): against numpy's dense solve of the same S, and against the cluster PCG."""
+    prob = make_scene(*shape, seed=7)
+    ba = engine.BundleAdjuster(prob, device=0)
+    S0, rhs0, y0, it0 = ba.reduced_system(radius, engine.default_options())
+    S2, rhs2, y2, it2 = ba.reduced_system(radius, engine.default_options(pcg_kernel=2, pcg_tolerance=1e-13))
+    assert it0 == 0 and it2 > 0 and np.array_equal(S0, S2) and np.array_equal(rhs0, rhs2)
+    S = engine.dense_reduced_system(ba.layout, S0)
+    y_ref = np.linalg.solve(S, rhs0.reshape(-1))
+    scale = np.max(np.abs(y_ref))
+    assert np.max(np.abs(y0.reshape(-1) - y_ref)) <= 1e-9 * scale
+    # no worse than the iterative solve it replaces
+    assert np.max(np.abs(y0.reshape(-1) - y_ref)) <= max(np.max(np.abs(y2.reshape(-1) - y_ref)), 1e-12 * scale)
+    _, _, y0b, _ = ba.reduced_system(radius, engine.default_options())
+    assert np.array_equal(y0, y0b)
+
+
 @pytest.mark.parametrize("shape", [(6, 80, 4), (40, 3000, 5), (260, 12000, 5)])
 def test_cluster_and_grid_pcg_agree(shape):
     """The cluster-resident PCG (pcg_cluster.cu) and the grid-wide PCG solve the same system to the same
@@ -236,8 +256,8 @@ def test_cluster_and_grid_pcg_agree(shape):
     ba = engine.BundleAdjuster(prob, device=0)
     S1, rhs1, y1, it1 = ba.reduced_system(1e4, engine.default_options(pcg_kernel=1, pcg_coarse=1, pcg_tolerance=1e-12))
     S3, rhs3, y3, it3 = ba.reduced_system(1e4, engine.default_options(pcg_kernel=1, pcg_tolerance=1e-12))  # grid, two-level
-    S0, rhs0, y0, it0 = ba.reduced_system(1e4, engine.default_options(pcg_kernel=0, pcg_coarse=1, pcg_tolerance=1e-12))
-    S2, rhs2, y2, it2 = ba.reduced_system(1e4, engine.default_options(pcg_tolerance=1e-12))
+    S0, rhs0, y0, it0 = ba.reduced_system(1e4, engine.default_options(pcg_kernel=2, pcg_coarse=1, pcg_tolerance=1e-12))
+    S2, rhs2, y2, it2 = ba.reduced_system(1e4, engine.default_options(pcg_kernel=2, pcg_tolerance=1e-12))
     assert np.array_equal(S0, S1) and np.array_equal(rhs0, rhs1) and np.array_equal(S0, S2)
     assert abs(it0 - it1) <= 2, (it0, it1)
     assert np.max(np.abs(y0 - y1)) <= 1e-9 * np.max(np.abs(y1))
@@ -253,5 +273,5 @@ def test_cluster_and_grid_pcg_agree(shape):
         assert it2 < 0.6 * it0, (it2, it0)
         assert it3 < 0.7 * it1, (it3, it1)
     # deterministic: bitwise identical on a second run
-    _, _, y2b, it2b = ba.reduced_system(1e4, engine.default_options(pcg_tolerance=1e-12))
+    _, _, y2b, it2b = ba.reduced_system(1e4, engine.default_options(pcg_kernel=2, pcg_tolerance=1e-12))
     assert it2b == it2 and np.array_equal(y2, y2b)

@@ -73,7 +73,11 @@ def test_layout_orders_and_structure(seed):
         assert np.all(prob.obs_img[lay.cm_src[sl]] == i)
     # chunks tile the image order
     assert lay.chunk_begin[0] == 0 and lay.chunk_end[-1] == N
-    assert np.all(lay.chunk_end - lay.chunk_begin <= engine.MPBA_CHUNK)
+    assert np.all(lay.chunk_end - lay.chunk_begin <= engine.chunk_size(N))
+    lib = engine.load_library()
+    lib.mpba_chunk_size.restype, lib.mpba_chunk_size.argtypes = C.c_int32, [C.c_int64]
+    assert all(lib.mpba_chunk_size(n) == engine.chunk_size(n) for n in (0, 1, 75_775, 75_776, 12_000, 303_103, 303_104, 10**7))
+    assert engine.chunk_size(12_000) == 128 and engine.chunk_size(300_000) == 256 and engine.chunk_size(5_000_000) == 1024
     assert np.all(lay.chunk_end[:-1] == lay.chunk_begin[1:])
     # depth rows: w > 0 exactly on the prior observations
     has = np.zeros(N, bool)
