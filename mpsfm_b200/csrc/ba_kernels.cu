@@ -1012,47 +1012,62 @@ __global__ void k_combine_scalars(const double* __restrict__ scal_all, int world
   scal[k] = v;
 }
 
-// block-Jacobi preconditioner: inverse of each 6x6 diagonal block through its Cholesky factor
+// block-Jacobi preconditioner: inverse of each 6x6 diagonal block through its Cholesky factor.  Every loop is unrolled:
+// the two 36-entry work arrays live in registers (with run-time loop bounds they sat in local memory and the kernel
+// took 17 us for ANY number of images -- one thread's dependent chain through L1; round-2 small-bundle profile).
 __global__ void __launch_bounds__(128) k_block_inverse(ProblemView pv, const double* __restrict__ S,
                                                        double* __restrict__ Minv) {
   const int i = blockIdx.x * 128 + threadIdx.x;
   if (i >= pv.C) return;
   double A[36], Li[36];
   const double* src = S + (size_t)pv.s_diag[i] * 36;
+#pragma unroll
   for (int k = 0; k < 36; ++k) A[k] = src[k];
   bool ok = true;
   // in-place Cholesky, lower
+#pragma unroll
   for (int j = 0; j < 6; ++j) {
     double d = A[7 * j];
+#pragma unroll
     for (int k = 0; k < j; ++k) d -= A[6 * j + k] * A[6 * j + k];
-    if (!(d > 0.0)) { ok = false; break; }
-    d = sqrt(d);
+    ok = ok && (d > 0.0);
+    d = sqrt(ok ? d : 1.0);
     A[7 * j] = d;
+#pragma unroll
     for (int r = j + 1; r < 6; ++r) {
       double s = A[6 * r + j];
+#pragma unroll
       for (int k = 0; k < j; ++k) s -= A[6 * r + k] * A[6 * j + k];
       A[6 * r + j] = s / d;
     }
   }
   double* dst = Minv + (size_t)i * 36;
   if (!ok) {
+#pragma unroll
     for (int k = 0; k < 36; ++k) dst[k] = (k % 7 == 0) ? 1.0 : 0.0;
     return;
   }
   // Li = L^-1 (lower)
+#pragma unroll
   for (int k = 0; k < 36; ++k) Li[k] = 0.0;
+#pragma unroll
   for (int c = 0; c < 6; ++c) {
     Li[7 * c] = 1.0 / A[7 * c];
+#pragma unroll
     for (int r = c + 1; r < 6; ++r) {
       double s = 0.0;
+#pragma unroll
       for (int k = c; k < r; ++k) s -= A[6 * r + k] * Li[6 * k + c];
       Li[6 * r + c] = s / A[7 * r];
     }
   }
   // A^-1 = Li^T Li
+#pragma unroll
   for (int r = 0; r < 6; ++r)
+#pragma unroll
     for (int c = 0; c < 6; ++c) {
       double s = 0.0;
+#pragma unroll
       for (int k = (r > c ? r : c); k < 6; ++k) s += Li[6 * k + r] * Li[6 * k + c];
       dst[6 * r + c] = s;
     }

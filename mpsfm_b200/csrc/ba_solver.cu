@@ -94,6 +94,9 @@ namespace {
 int coarse_max_groups(int num_images, int lagged, bool cluster) {
   static const int env = getenv("MPBA_COARSE_GROUPS") ? atoi(getenv("MPBA_COARSE_GROUPS")) : 0;
   if (env > 0) return std::min(env, (int)COARSE_MAX_GROUPS);
+  // mid-size bundles (profiles/r02_small_bundles.md): 50 images 8 groups 4.69 ms per solve, 18 groups 5.28 ms -- the
+  // single-CTA inverse of the coarse matrix costs n^3 and is not hidden (no lag below 600 images)
+  if (num_images < 64) return 8;
   if (num_images < 600) return 18;
   return (lagged && !cluster) ? 48 : 32;
 }
@@ -449,7 +452,13 @@ int build_pcg_cluster_plan(Ctx& c, const mpba_problem* prob, int pcg_kernel, int
   if (plan_capacity_ints(prob) > c.w.plan_ints || (size_t)(8 * (size_t)U + 3 * 17 + 64) > c.w.plan_ints) return MPBA_OK;
 
   const int max_smem = pcg_cluster_max_smem(h->device);
-  for (int cl = 1; cl <= 16; cl *= 2) {
+  static const int env_min_cl = getenv("MPBA_PCG_MIN_CLUSTER") ? atoi(getenv("MPBA_PCG_MIN_CLUSTER")) : 0;
+  // at least four CTAs: one CTA applying the whole preconditioner (17 groups' rows of A^-1) made the 50-image solve
+  // 7.3 ms, four CTAs 4.7 ms (r2 sweep); the dense direct solve already took the systems below 22 images
+  int first_cl = C >= 16 ? 4 : 1;
+  if (env_min_cl > 0) first_cl = 1;
+  while (first_cl < 16 && first_cl < env_min_cl) first_cl *= 2;
+  for (int cl = first_cl; cl <= 16; cl *= 2) {
     // contiguous rows, balanced by upper-block count
     std::vector<int> crow(cl + 1, C);
     crow[0] = 0;

@@ -118,11 +118,37 @@ __device__ __forceinline__ double fast_rcp(double a) {
   x = x * (2.0 - a * x);
   return x * (2.0 - a * x);
 }
+// No CTA-wide barrier in the elimination (round 2; the first version had one __syncthreads per pivot, ~0.7 us each):
+// every pivot row has its own slot in shared memory and its own mbarrier; the owner warp publishes and arrives, the
+// others wait on it (mbarrier.try_wait suspends, no spinning on issue slots) and run ahead as far as the data allows.
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {  // release at CTA scope
+  asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.shared::cta.b64 st, [%0];\n}" ::"r"(
+                   (unsigned)__cvta_generic_to_shared(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {  // acquire at CTA scope
+  const unsigned addr = (unsigned)__cvta_generic_to_shared(bar);
+  unsigned done;
+  do {
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(done)
+                 : "r"(addr), "r"(parity)
+                 : "memory");
+  } while (!done);
+}
 __global__ void __launch_bounds__(1024) k_coarse_invert(int n, const double* __restrict__ Ac_part, double* __restrict__ Ainv) {
-  __shared__ double prow[2][32 * GJ_Q];
-  __shared__ double s_inv[2];
-  extern __shared__ double T[];  // [n][n | 1]: only for the symmetrised write-out
+  // [n][32 GJ_Q] scaled pivot rows during the elimination, then (after a barrier) [n][n | 1] for the symmetrised write-out
+  extern __shared__ double T[];
+  __shared__ double s_inv[GJ_SINGLE_MAX];
+  __shared__ uint64_t s_bar[GJ_SINGLE_MAX];
+  constexpr int W = 32 * GJ_Q;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid < n) mbar_init(&s_bar[tid], 32);
+  __syncthreads();
   double a[GJ_Q][GJ_Q], d0[GJ_Q];
 #pragma unroll
   for (int qi = 0; qi < GJ_Q; ++qi) {
@@ -154,21 +180,22 @@ __global__ void __launch_bounds__(1024) k_coarse_invert(int n, const double* __r
     for (int pw = 0; pw < 32; ++pw) {
       const int p = 32 * PQ + pw;
       if (p >= n) break;
-      double* pr = prow[p & 1];
+      double* pr = T + (size_t)p * W;
       if (warp == pw) {  // owner of row p: scale and publish it
         const double piv = __shfl_sync(0xffffffffu, a[PQ][PQ], pw);
         const double dp = d0[PQ];
         const double inv = (piv > 1e-13 * dp && dp > 0.0) ? fast_rcp(piv) : 0.0;
 #pragma unroll
         for (int qj = 0; qj < GJ_Q; ++qj) pr[lane + 32 * qj] = a[PQ][qj] * inv;
-        if (lane == 0) s_inv[p & 1] = inv;
+        if (lane == 0) s_inv[p] = inv;
+        mbar_arrive(&s_bar[p]);
       }
       double f[GJ_Q];
 #pragma unroll
       for (int qi = 0; qi < GJ_Q; ++qi) f[qi] = __shfl_sync(0xffffffffu, a[qi][PQ], pw);  // column p of my rows
       if (warp == pw) f[PQ] = 0.0;  // row p itself is replaced below
-      __syncthreads();
-      const double inv = s_inv[p & 1];
+      mbar_wait(&s_bar[p], 0);
+      const double inv = s_inv[p];
       double rp[GJ_Q];
 #pragma unroll
       for (int qj = 0; qj < GJ_Q; ++qj) rp[qj] = pr[lane + 32 * qj];
@@ -188,6 +215,7 @@ __global__ void __launch_bounds__(1024) k_coarse_invert(int n, const double* __r
     }
   }
   const int ld = n | 1;
+  __syncthreads();  // every warp is through with the pivot rows: the buffer is reused
 #pragma unroll
   for (int qi = 0; qi < GJ_Q; ++qi)
 #pragma unroll
@@ -403,7 +431,7 @@ __global__ void __launch_bounds__(256) k_coarse_symmetrize(int n, const double* 
 
 }  // namespace
 
-size_t coarse_invert_smem_bytes(int n) { return (size_t)n * (n | 1) * sizeof(double); }
+size_t coarse_invert_smem_bytes(int n) { return (size_t)n * 128 * sizeof(double); }  // [n][32 GJ_Q] >= [n][n | 1]
 
 cudaError_t launch_coarse_modes(int C, const double* pose, const uint8_t* free_mask, double* Zc, cudaStream_t st) {
   k_coarse_modes<<<(C + 127) / 128, 128, 0, st>>>(C, pose, free_mask, Zc);

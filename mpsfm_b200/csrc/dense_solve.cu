@@ -5,7 +5,11 @@
 // each (84 us of a 157 us LM iteration at 6 images, round-2 profile); Ceres itself factors systems of this size
 // densely.  Here: the augmented matrix [S | rhs] lives IN REGISTERS of one 1024-thread CTA (thread (warp w, lane l)
 // owns the entries (w + 32 qi, l + 32 qj), 16 doubles) and is reduced by Gauss-Jordan elimination without pivoting
-// (S is SPD: no growth), one CTA barrier per pivot -- the scheme of coarse.cu's k_coarse_invert, ~0.16 us per pivot.
+// (S is SPD: no growth).  There is NO CTA-wide barrier in the elimination: the warp that owns pivot row p publishes
+// the scaled row in shared memory (every pivot has its own row: no buffer is ever reused) and arrives on that
+// pivot's mbarrier; the other warps wait on it (mbarrier.try_wait suspends them, they do not spin on issue slots)
+// and run ahead as far as the data allows -- the chain owner(p) -> owner(p + 1) is the only serialisation left.
+// Measured against the one-__syncthreads-per-pivot version of this kernel: 97 -> see profiles/r02_small_bundles.md.
 // The elimination is done in place, so the registers end up holding S^-1 next to the solution column, and one step
 // of iterative refinement (r = rhs - S y from the block-CSR original, y += S^-1 r) removes the elimination's rounding.
 // The register tile is NQ x NQ slots per thread, NQ = ceil((6 C + 1) / 32): 2 for the reference's 6-image local
@@ -28,11 +32,30 @@ struct CamStep {  // arguments of the fused camera step (cam_update_body); pose_
   double* pose_cand;
 };
 
-__device__ __forceinline__ double ds_rcp(double a) {  // float seed + Newton steps: full double precision
+__device__ __forceinline__ double ds_rcp(double a) {  // float seed + two Newton steps: 2^-23 -> 2^-46 -> full double
   double x = (double)(1.0f / (float)a);
   x = x * (2.0 - a * x);
-  x = x * (2.0 - a * x);
   return x * (2.0 - a * x);
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {  // release at CTA scope
+  asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.shared::cta.b64 st, [%0];\n}" ::"r"(
+                   (unsigned)__cvta_generic_to_shared(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {  // acquire at CTA scope
+  const unsigned addr = (unsigned)__cvta_generic_to_shared(bar);
+  unsigned done;
+  do {
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(done)
+                 : "r"(addr), "r"(parity)
+                 : "memory");
+  } while (!done);
 }
 
 template <int DS_Q>
@@ -41,13 +64,16 @@ __global__ void __launch_bounds__(1024) k_dense_solve(int C, const int32_t* __re
                                                       const double* __restrict__ rhs, double* y,
                                                       double* scal, CamStep cs) {
   __shared__ int tbl[DENSE_SOLVE_MAX_IMAGES * DENSE_SOLVE_MAX_IMAGES];
-  __shared__ double prow[2][DS_DIM];
-  __shared__ double s_inv[2];
+  extern __shared__ double prow[];  // [n][W]: the scaled pivot rows, one per pivot
+  __shared__ double s_inv[DS_DIM];
+  __shared__ uint64_t s_bar[DS_DIM];  // one mbarrier per pivot: 32 arrivals = the owner warp has published the row
   __shared__ double xs[DS_DIM], rs[DS_DIM];
+  constexpr int W = 32 * DS_Q;
   __shared__ int s_bad;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n = 6 * C;  // column n carries the right-hand side
   for (int k = tid; k < C * C; k += 1024) tbl[k] = -1;
+  if (tid < n) mbar_init(&s_bar[tid], 32);
   if (tid == 0) s_bad = 0;
   __syncthreads();
   for (int i = tid; i < C; i += 1024)
@@ -73,7 +99,7 @@ __global__ void __launch_bounds__(1024) k_dense_solve(int C, const int32_t* __re
     for (int pw = 0; pw < 32; ++pw) {
       const int p = 32 * PQ + pw;
       if (p >= n) break;
-      double* pr = prow[p & 1];
+      double* pr = prow + (size_t)p * W;
       if (warp == pw) {  // owner of row p: scale and publish it
         const double piv = __shfl_sync(FULLMASK, a[PQ][PQ], pw);
         const bool ok = piv > 0.0 && isfinite(piv);
@@ -81,16 +107,17 @@ __global__ void __launch_bounds__(1024) k_dense_solve(int C, const int32_t* __re
 #pragma unroll
         for (int qj = 0; qj < DS_Q; ++qj) pr[lane + 32 * qj] = a[PQ][qj] * inv;
         if (lane == 0) {
-          s_inv[p & 1] = inv;
+          s_inv[p] = inv;
           if (!ok) s_bad = 1;  // not positive definite: the LM loop treats the step as invalid
         }
+        mbar_arrive(&s_bar[p]);  // every lane releases its own part of the row
       }
       double f[DS_Q];
 #pragma unroll
       for (int qi = 0; qi < DS_Q; ++qi) f[qi] = __shfl_sync(FULLMASK, a[qi][PQ], pw);  // column p of my rows
       if (warp == pw) f[PQ] = 0.0;  // row p itself is replaced below
-      __syncthreads();
-      const double inv = s_inv[p & 1];
+      mbar_wait(&s_bar[p], 0);
+      const double inv = s_inv[p];
       double rp[DS_Q];
 #pragma unroll
       for (int qj = 0; qj < DS_Q; ++qj) rp[qj] = pr[lane + 32 * qj];
@@ -182,11 +209,18 @@ cudaError_t launch_dense_solve(int C, const int32_t* row_ptr, const int32_t* col
     cs.pose_cand = pose_cand;
   }
   const int nq = (6 * C + 1 + 31) / 32;
+  const size_t smem = (size_t)6 * C * 32 * nq * sizeof(double);  // <= 126 rows of 128 doubles: 126 KB
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(k_dense_solve<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 96 * 8);
+    cudaFuncSetAttribute(k_dense_solve<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 128 * 8);
+    attr_set = true;
+  }
   switch (nq) {
-    case 1: k_dense_solve<1><<<1, 1024, 0, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
-    case 2: k_dense_solve<2><<<1, 1024, 0, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
-    case 3: k_dense_solve<3><<<1, 1024, 0, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
-    default: k_dense_solve<4><<<1, 1024, 0, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
+    case 1: k_dense_solve<1><<<1, 1024, smem, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
+    case 2: k_dense_solve<2><<<1, 1024, smem, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
+    case 3: k_dense_solve<3><<<1, 1024, smem, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
+    default: k_dense_solve<4><<<1, 1024, smem, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
   }
   return cudaGetLastError();
 }

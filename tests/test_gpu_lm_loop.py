@@ -78,12 +78,12 @@ def test_device_loop_equals_host_loop(name):
 
 def test_rejected_steps_are_covered():
     """These scenes accept every LM step (robust losses: relative decrease > 1 far out, -> 1 near the optimum).  Asking
-    for a relative decrease above 1.2 rejects the late steps: the radius halves, quarters, ... until a rule ends the
-    solve -- the reject branch and the shrinking trust region on both controllers."""
+    for a relative decrease above 1.45 / 1.6 rejects some of them (oracle/lm.py on this scene: 0 0 1 1 1 ... and
+    0 0 0 1 1 0 0 ...): the radius halves, quarters, ... until a step passes or a rule ends the solve -- the reject branch and the shrinking trust region on both controllers."""
     kw = dict(CASES["rough_start_12"])
     prob = make_scene(kw.pop("num_images"), kw.pop("num_points"), kw.pop("obs_per_point"), seed=3, **kw)
     found = False
-    for mrd in (1.2, 2.5):
+    for mrd in (1.45, 1.6):
         _, sh, pose_h, X_h = _solve(prob, 1, min_relative_decrease=mrd)
         _, sd, pose_d, X_d = _solve(prob, 2, min_relative_decrease=mrd)
         _same_rows(sd.iterations, sh.iterations)

@@ -107,7 +107,12 @@ def test_reduced_camera_system_and_pcg(scene):
     yc_o, _ = ne.solve(Dc2, Dp2)
     y_o = (yc_o * c_img).reshape(-1)
     assert np.max(np.abs(y.reshape(-1) - y_o)) <= 1e-7 * np.max(np.abs(y_o))
-    assert 0 < iters < 2000
+    assert iters == 0  # 14 images: the dense direct solve (dense_solve.cu), no conjugate gradients
+    # the iterative path on the same system (what larger bundles run)
+    S2, rhs2, y2, iters2 = ba.reduced_system(radius, engine.default_options(pcg_kernel=2, pcg_tolerance=1e-12))
+    assert np.array_equal(S2, S_blocks) and np.array_equal(rhs2, rhs)
+    assert np.max(np.abs(y2.reshape(-1) - y_o)) <= 1e-7 * np.max(np.abs(y_o))
+    assert 0 < iters2 < 2000
 
 
 def _angle(qa, qb):
