@@ -210,7 +210,7 @@ class Optimizer(BaseClass):
         # --- reprojection residual blocks of the images in the config (COLMAP AddImageToProblem)
         image_ids = list(optim_ids)
         image_index = {imid: k for k, imid in enumerate(image_ids)}
-        o_img, o_p2d, o_p3d, o_xy = [], [], [], []
+        o_img, o_p2d, o_p3d, o_xy, o_row = [], [], [], [], []
         img_obs_offset, img_p2ds = {}, {}
         n = 0
         for imid in optim_ids:
@@ -222,12 +222,14 @@ class Optimizer(BaseClass):
             if p2ds.size == 0:
                 continue
             o_img.append(np.full(p2ds.size, imid, dtype=np.int64))
+            o_row.append(np.full(p2ds.size, image_index[imid], dtype=np.int32))
             o_p2d.append(p2ds)
             o_p3d.append(np.asarray(image.point3D_ids(p2ds), dtype=np.uint64).astype(np.int64))
             o_xy.append(np.asarray(image.keypoint_coordinates(p2ds), dtype=np.float64).reshape(-1, 2))
             n += p2ds.size
         cat = lambda parts, dt, shape: (np.concatenate(parts) if parts else np.zeros(shape, dtype=dt))  # noqa: E731
         obs_img_id = cat(o_img, np.int64, (0,))
+        obs_row = cat(o_row, np.int32, (0,))  # row of the observation's image in the problem, built per image
         obs_p2d = cat(o_p2d, np.int64, (0,))
         obs_p3d = cat(o_p3d, np.int64, (0,))
         obs_xy = cat(o_xy, np.float64, (0, 2))
@@ -255,12 +257,16 @@ class Optimizer(BaseClass):
                 x_xy.append(np.asarray(rec.images[el.image_id].keypoint_coordinates([el.point2D_idx])).reshape(2))
         if x_img:
             obs_img_id = np.concatenate([obs_img_id, np.asarray(x_img, dtype=np.int64)])
+            obs_row = np.concatenate([obs_row, np.asarray([image_index[i] for i in x_img], dtype=np.int32)])
             obs_p2d = np.concatenate([obs_p2d, np.asarray(x_p2d, dtype=np.int64)])
             obs_p3d = np.concatenate([obs_p3d, np.asarray(x_p3d, dtype=np.int64)])
             obs_xy = np.concatenate([obs_xy, np.asarray(x_xy, dtype=np.float64).reshape(-1, 2)])
             point_ids, inverse = np.unique(obs_p3d, return_inverse=True)
-        pt_const = np.array([1 if rec.points3D[int(pid)].track.length() > n_in_problem[int(pid)] else 0
-                             for pid in point_ids], dtype=np.uint8)
+        pid_list = point_ids.tolist()
+        points3D = rec.points3D
+        track_len = np.fromiter((points3D[pid].track.length() for pid in pid_list), dtype=np.int64, count=len(pid_list))
+        in_problem = np.fromiter((n_in_problem[pid] for pid in pid_list), dtype=np.int64, count=len(pid_list))
+        pt_const = (track_len > in_problem).astype(np.uint8)
 
         # --- images: poses, gauge (:111-122), cameras (intrinsics constant, :92-94)
         C = len(image_ids)
@@ -343,9 +349,9 @@ class Optimizer(BaseClass):
             img_q=img_q, img_t=img_t,
             img_camera=np.array([cam_row[c] for c in cam_ids], dtype=np.int32),
             img_free_mask=free, cam_model=cam_model, cam_params=cam_params,
-            pt_xyz=rec.point3D_coordinates([int(p) for p in point_ids]) if point_ids.size else np.zeros((0, 3)),
+            pt_xyz=rec.point3D_coordinates(pid_list) if point_ids.size else np.zeros((0, 3)),
             pt_const=pt_const,
-            obs_img=np.array([image_index[int(i)] for i in obs_img_id], dtype=np.int32),
+            obs_img=obs_row,
             obs_pt=inverse.astype(np.int32), obs_xy=obs_xy,
             depth_obs=cat(d_obs, np.int64, (0,)).astype(np.int32), depth_d=cat(d_d, np.float64, (0,)),
             depth_w=cat(d_w, np.float64, (0,)), depth_a=cat(d_a, np.float64, (0,)),
@@ -410,8 +416,11 @@ class Optimizer(BaseClass):
                 pose.rotation.quat[:] = q[k]
             if mask & 0b111000:
                 pose.translation[:] = t[k]
-        for j in np.flatnonzero(pr.pt_const == 0):
-            rec.points3D[int(assembly.point_ids[j])].xyz[:] = X[j]
+        # one pass over the variable points; the ids and rows as plain Python ints (numpy scalars cost ~3x in this loop)
+        rows = np.flatnonzero(pr.pt_const == 0)
+        points3D = rec.points3D
+        for pid, xyz in zip(assembly.point_ids[rows].tolist(), X[rows]):
+            points3D[pid].xyz[:] = xyz
 
     def __build_problem(self, bundle, fix_pose, fix_scale, **kwargs):
         assembly = self.assemble(bundle, fix_pose, fix_scale, **kwargs)
