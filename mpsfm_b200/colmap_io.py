@@ -239,3 +239,62 @@ def apply_filter(m: ColmapModel, obs_keep, pt_keep, pt_error) -> ColmapModel:
         m, kp_point3D_id=kp_pid, pt_id=m.pt_id[pt_keep], pt_xyz=m.pt_xyz[pt_keep], pt_rgb=m.pt_rgb[pt_keep], pt_error=err,
         track_ptr=np.concatenate([[0], np.cumsum(counts)]).astype(np.int64), track_image_id=m.track_image_id[keep_el],
         track_point2D_idx=m.track_point2D_idx[keep_el])
+
+
+# ----------------------------------------------------------------------------------------------
+# depth cache next to the model: the reference's ``depths.h5`` (mpsfm/sfm/scene/reconstruction/base.py:122-133,
+# written by ``write`` :135-141 beside ``rec/``)
+# ----------------------------------------------------------------------------------------------
+_DEPTH_GROUPS = (("depths", "data"), ("continuity", "continuity_mask"), ("scales", "scale"), ("pdepth", "data_prior"))
+
+
+def cache_depths(registered_images, path) -> str:
+    """``MpsfmReconstruction.cache_depths``: per registered image ``depths/<imid>`` (depth.data), ``continuity/<imid>``
+    (continuity_mask), ``scales/<imid>`` (scale) and ``pdepth/<imid>`` (data_prior), each only where it is not None.
+
+    With h5py importable the file is the reference's HDF5 (same dataset names, gzip on the maps).  h5py is not in this
+    image ("unavailable on this box"): the twin is a compressed ``.npz`` holding the SAME keys -- ``path`` keeps its
+    stem and gets the ``.npz`` suffix -- which ``read_cached_depths`` reads back either way.  Returns the path written."""
+    path = str(path)
+    entries = {}
+    for imid, image in registered_images.items():
+        depth = image.depth
+        for group, attr in _DEPTH_GROUPS:
+            value = getattr(depth, attr, None)
+            if value is not None:
+                entries[f"{group}/{imid}"] = np.asarray(value)
+    try:
+        import h5py
+    except ImportError:
+        h5py = None
+    if h5py is not None:
+        with h5py.File(path, "w") as f:
+            for key, value in entries.items():
+                if key.startswith("scales/"):
+                    f.create_dataset(key, data=value)
+                else:
+                    f.create_dataset(key, data=value, compression="gzip")
+        return path
+    out = (path[: -len(".h5")] if path.endswith(".h5") else path) + ".npz"
+    np.savez_compressed(out, **entries)
+    return out
+
+
+def read_cached_depths(path) -> dict:
+    """{group: {image id: array}} of a file written by ``cache_depths`` (HDF5 or the ``.npz`` twin)."""
+    path = str(path)
+    out = {group: {} for group, _ in _DEPTH_GROUPS}
+    if path.endswith(".npz"):
+        with np.load(path) as z:
+            for key in z.files:
+                group, imid = key.split("/")
+                out[group][int(imid)] = z[key]
+        return out
+    import h5py
+
+    with h5py.File(path, "r") as f:
+        for group in out:
+            if group in f:
+                for imid, ds in f[group].items():
+                    out[group][int(imid)] = ds[()]
+    return out

@@ -158,7 +158,7 @@ void flush_timers(mpba_handle* h) {
 size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Workspace {
-  double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *img_part, *c_img, *c_pt, *Hpp, *gp, *Hinv, *fac, *S,
+  double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *ip[2], *c_img, *c_pt, *Hpp, *gp, *Hinv, *fac, *S,
       *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal, *scal_all, *Linv, *tpart;
   double *Zc = nullptr, *Ac = nullptr, *Ainv = nullptr;  // coarse space (coarse.cu)
   double *Zc2 = nullptr, *Ainv2 = nullptr;               // lagged setup: the side stream's own Z, the second inverse
@@ -167,6 +167,7 @@ struct Workspace {
   int4* warp_desc = nullptr;  // per warp group
   int32_t* plan = nullptr;  // PCG cluster plan (pcg_cluster.cu)
   size_t plan_ints = 0;
+  size_t img_span = 0;  // doubles of [Hc | gc | per-image costs] of one buffer set
   double* ld = nullptr;            // device-controlled LM loop: LD_COUNT state doubles, then the iteration rows
   mpba_iteration* rows = nullptr;
   size_t bytes = 0;
@@ -193,11 +194,15 @@ void carve(const mpba_problem* p, const mpba_shard* sh, char* base, Workspace& w
   for (int k = 0; k < 2; ++k) {
     w.pose[k] = take(C * 8);
     w.X[k] = take(Ppad * 4);
-    w.Hc[k] = take(C * 21);
-    w.gc[k] = take(C * 6);
+    // image blocks, gradients and per-image costs of one buffer set are ONE span: a sharded solve all-reduces it in
+    // one call (img_span doubles from Hc[k])
+    const size_t hc = (C * 21 + 1) & ~(size_t)1;
+    w.Hc[k] = take(hc + C * 6 + C * 2);
+    w.gc[k] = w.Hc[k] ? w.Hc[k] + hc : nullptr;
+    w.ip[k] = w.Hc[k] ? w.gc[k] + C * 6 : nullptr;
+    w.img_span = hc + C * 6 + C * 2;
   }
   w.chunk_part = take((size_t)p->num_chunks * IMG_PART);
-  w.img_part = take(C * 2);
   w.c_img = take(C * 6);
   w.c_pt = take(P * 3);
   w.Hpp = take(P * 6);
@@ -205,8 +210,8 @@ void carve(const mpba_problem* p, const mpba_shard* sh, char* base, Workspace& w
   w.Hinv = take(P * 6);
   w.Linv = take(P * 9);
   w.fac = take((p->flags & MPBA_FLAG_STRUCTURE_ONLY) ? 0 : (size_t)p->num_obs * FAC_STRIDE);
-  w.S = take(B * 36);
-  w.rhs = take(C * 6);
+  w.S = take(B * 36 + C * 6);  // S | rhs: one span, one all-reduce of a sharded solve
+  w.rhs = w.S ? w.S + B * 36 : nullptr;
   w.Minv = take(C * 36);
   w.y = take(C * 6);
   w.vr = take(C * 6);
@@ -372,30 +377,25 @@ int enqueue_image_pass(Ctx& c, const double* pose, const double* X, int k, int c
   if (c.sh) {
     {
       Timer t(h, KS_IMG_FINALIZE, 1);
-      launch_img_finalize(c.pv, c.w.chunk_part, c.w.Hc[k], c.w.gc[k], c.w.img_part, h->stream);
+      launch_img_finalize(c.pv, c.w.chunk_part, c.w.Hc[k], c.w.gc[k], c.w.ip[k], h->stream);
     }
     Timer t(h, KS_COLLECTIVE);
     NcclApi& nc = nccl_api();
-    const size_t C = (size_t)c.pv.C;
-    NC(nc.GroupStart());
-    NC(nc.AllReduce(c.w.Hc[k], c.w.Hc[k], C * 21, ncclDouble, ncclSum, h->comm, h->stream));
-    NC(nc.AllReduce(c.w.gc[k], c.w.gc[k], C * 6, ncclDouble, ncclSum, h->comm, h->stream));
-    NC(nc.AllReduce(c.w.img_part, c.w.img_part, C * 2, ncclDouble, ncclSum, h->comm, h->stream));
-    NC(nc.GroupEnd());
+    NC(nc.AllReduce(c.w.Hc[k], c.w.Hc[k], c.w.img_span, ncclDouble, ncclSum, h->comm, h->stream));
   } else if (c.pv.C <= IMG_TAIL_MAX_IMAGES) {
     // small bundle: finalize + scalars (+ the LM decision of the device loop) in one single-CTA kernel
     Timer t(h, KS_IMG_FINALIZE, 1);
-    launch_img_tail(c.pv, c.w.chunk_part, c.w.Hc[k], c.w.gc[k], c.w.img_part, c.w.c_img, compute_scaling, jacobi,
+    launch_img_tail(c.pv, c.w.chunk_part, c.w.Hc[k], c.w.gc[k], c.w.ip[k], c.w.c_img, compute_scaling, jacobi,
                     c.w.scal, c.tail, h->stream);
     if (c.tail) c.tail_done = true;
     return MPBA_OK;
   } else {
     Timer t(h, KS_IMG_FINALIZE, 1);
-    launch_img_finalize(c.pv, c.w.chunk_part, c.w.Hc[k], c.w.gc[k], c.w.img_part, h->stream);
+    launch_img_finalize(c.pv, c.w.chunk_part, c.w.Hc[k], c.w.gc[k], c.w.ip[k], h->stream);
   }
   {
     Timer t(h, KS_IMG_FINALIZE, 1);
-    launch_img_scalars(c.pv, c.w.img_part, c.w.Hc[k], c.w.gc[k], c.w.c_img, compute_scaling, jacobi, c.w.scal,
+    launch_img_scalars(c.pv, c.w.ip[k], c.w.Hc[k], c.w.gc[k], c.w.c_img, compute_scaling, jacobi, c.w.scal,
                        h->stream);
   }
   return MPBA_OK;
@@ -706,10 +706,7 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
       // "the partial reduced-camera-system blocks ... are combined with NCCL allreduce")
       Timer t(h, KS_COLLECTIVE, 2);
       NcclApi& nc = nccl_api();
-      NC(nc.GroupStart());
-      NC(nc.AllReduce(c.w.S, c.w.S, (size_t)c.pv.B * 36, ncclDouble, ncclSum, h->comm, h->stream));
-      NC(nc.AllReduce(c.w.rhs, c.w.rhs, (size_t)c.pv.C * 6, ncclDouble, ncclSum, h->comm, h->stream));
-      NC(nc.GroupEnd());
+      NC(nc.AllReduce(c.w.S, c.w.S, (size_t)c.pv.B * 36 + (size_t)c.pv.C * 6, ncclDouble, ncclSum, h->comm, h->stream));
       launch_schur_finish(c.pv, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.S, c.w.rhs, h->stream);
     }
     if (c.dense) {

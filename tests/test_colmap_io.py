@@ -136,3 +136,21 @@ def test_filter_edits_on_a_model(tmp_path):
     q2[:, :3] *= -1.0
     colmap_io.update_state(back, q2, view2.img_t + 1.0, view2.pt_xyz * 2.0)
     assert np.array_equal(back.pt_xyz, view2.pt_xyz * 2.0) and np.array_equal(back.img_t, view2.img_t + 1.0)
+
+
+def test_depth_cache_twin_round_trip(tmp_path):
+    """The reference's depths.h5 (reconstruction/base.py:122-133) or, without h5py, its .npz twin with the same keys."""
+    from types import SimpleNamespace as NS
+
+    rng = np.random.default_rng(0)
+    images = {
+        4: NS(depth=NS(data=rng.random((6, 8)), continuity_mask=rng.random((6, 8)) > 0.5, scale=1.25,
+                       data_prior=rng.random((6, 8)))),
+        9: NS(depth=NS(data=rng.random((5, 7)), continuity_mask=None, scale=None, data_prior=None)),
+    }
+    written = colmap_io.cache_depths(images, tmp_path / "depths.h5")
+    back = colmap_io.read_cached_depths(written)
+    assert set(back["depths"]) == {4, 9} and set(back["continuity"]) == {4} and set(back["pdepth"]) == {4}
+    assert np.array_equal(back["depths"][9], images[9].depth.data)
+    assert np.array_equal(back["continuity"][4], images[4].depth.continuity_mask)
+    assert float(back["scales"][4]) == 1.25 and 9 not in back["scales"]
