@@ -293,6 +293,9 @@ constexpr int PW_WARPS = PW_THREADS / 32;
 #ifndef MPBA_POINTS_MINB
 #define MPBA_POINTS_MINB 4
 #endif
+#ifndef MPBA_POINTS_BULK_DEFAULT
+#define MPBA_POINTS_BULK_DEFAULT 0
+#endif
 #ifndef MPBA_POINTS_PREFETCH_DEFAULT
 #define MPBA_POINTS_PREFETCH_DEFAULT 592  // one wave: 148 SMs x 4 CTAs (sweep: profiles/r01_prefetch_sweep_cfg3.json)
 #endif
@@ -386,7 +389,8 @@ __device__ __forceinline__ void finalize_point(int p, bool active, const double 
                                                double* __restrict__ c_pt, int compute_scaling, int jacobi_scaling,
                                                double* __restrict__ Hpp, double* __restrict__ gp,
                                                double* __restrict__ Hinv, double* __restrict__ Linv,
-                                               double* __restrict__ scal, double Li[6], double e[3]) {
+                                               double* __restrict__ scal, double Li[6], double e[3],
+                                               const double* cpre = nullptr /* c_pt row loaded ahead by the caller */) {
   double Hi[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
 #pragma unroll
   for (int j = 0; j < 6; ++j) Li[j] = 0.0;
@@ -398,6 +402,8 @@ __device__ __forceinline__ void finalize_point(int p, bool active, const double 
       c[2] = jacobi_scaling ? 1.0 / (1.0 + sqrt(Hp[5])) : 1.0;
     }
     c_pt[(size_t)p * 3] = c[0]; c_pt[(size_t)p * 3 + 1] = c[1]; c_pt[(size_t)p * 3 + 2] = c[2];
+  } else if (cpre != nullptr) {
+    c[0] = cpre[0]; c[1] = cpre[1]; c[2] = cpre[2];
   } else {
     c[0] = c_pt[(size_t)p * 3]; c[1] = c_pt[(size_t)p * 3 + 1]; c[2] = c_pt[(size_t)p * 3 + 2];
   }
@@ -601,6 +607,8 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
   __shared__ double s_v[PW_THREADS][9];
   __shared__ double s_le[PW_THREADS][9];
   __shared__ __align__(16) int4 s_next;  // descriptor of the CTA prefetch_ahead blocks later
+  __shared__ double s_gw[PW_WARPS];
+  bool gmax_done = false;
   if (compute_scaling < 0) compute_scaling = __ldcg(lm.dev + LD_FIRST) != 0.0 ? 1 : 0;
   lm_resolve(lm);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -619,11 +627,16 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
     // track threads: their slot range and constant flag (independent loads, needed after the first barrier)
     int start = 0, len = 0;
     bool cst = true;
+    double cpre[3] = {0.0, 0.0, 0.0};  // Jacobi scales of the track's point: in flight while the observations linearise
     if (tid < nt) {
       const int a = __ldg(pv.pt_ptr + T0 + tid), b = __ldg(pv.pt_ptr + T0 + tid + 1);
       start = a - base;
       len = b - a;
       cst = pv.pt_const[T0 + tid] != 0;
+      if (!compute_scaling) {
+        const double* cp = c_pt + 3 * (size_t)(T0 + tid);
+        cpre[0] = cp[0]; cpre[1] = cp[1]; cpre[2] = cp[2];
+      }
     }
     // ---- 1. observations: point of the slot (pm_pt), gather, linearise, leave R^T N R / R^T h in shared memory
     int tr = -1;
@@ -661,15 +674,25 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
       }
       double Li[6], e[3];
       finalize_point(T0 + tid, active, v, v + 6, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, scal,
-                     Li, e);
+                     Li, e, cpre);
 #pragma unroll
       for (int j = 0; j < 6; ++j) s_le[tid][j] = Li[j];
 #pragma unroll
       for (int j = 0; j < 3; ++j) s_le[tid][6 + j] = e[j];
       gmax = fmax(fabs(v[6]), fmax(fabs(v[7]), fabs(v[8])));
     }
+    // max |gp| of the CTA rides on the barrier that follows (no block reduction of its own: three barriers less)
+    for (int off = 16; off > 0; off >>= 1) gmax = fmax(gmax, __shfl_xor_sync(FULL, gmax, off));
+    if (lane == 0) s_gw[warp] = gmax;
+    gmax_done = true;
     if (write_factors) {
       __syncthreads();
+      if (tid == 0) {
+        double m = s_gw[0];
+#pragma unroll
+        for (int w = 1; w < PW_WARPS; ++w) m = fmax(m, s_gw[w]);
+        pt_part[(size_t)blockIdx.x * PT_PART] = m;
+      }
       // ---- 3. Schur factors
       double2* rows = rows_all[warp];
       if (act) {
@@ -700,10 +723,224 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
       gmax = points_warp_path(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, fac, scal,
                               write_factors, rows_all[warp], w, lane);
   }
-  {
+  if (!(gmax_done && write_factors)) {  // warp path, or no factor pass: the plain block reduction
     __shared__ double smx[PW_WARPS + 1];
     const double m = block_max<PW_WARPS>(gmax, smx);
     if (threadIdx.x == 0) pt_part[(size_t)blockIdx.x * PT_PART] = m;
+  }
+}
+
+// ---- k_points with a bulk-copy pipeline (experiment of round 2) -----------------------------
+// Same arithmetic as k_points' CTA path, group by group, but PERSISTENT (a few CTAs per SM walk the groups with a
+// grid stride) and fed by cp.async.bulk: everything a group reads contiguously -- keypoints, the three depth-prior
+// arrays, pm_pt, pm_img, the coordinates / pt_ptr / constant flags of its tracks -- lands in a two-stage shared
+// memory ring, completion signalled on an mbarrier (complete_tx), one group ahead of the arithmetic.  What stays a
+// gather is the image record behind pm_img (pose, camera: L1 / L2 resident).  The L2 prefetch hints of k_points
+// (one wave ahead, issued by two warps of every CTA) disappear.  Source ranges are widened to 16-byte boundaries
+// (cp.async.bulk's alignment rule); the in-stage offset of the first element follows from the group descriptor.
+struct PtStage {
+  static constexpr int XY = 0, D0 = 2064, D1 = D0 + 1040, D2 = D1 + 1040, PT = D2 + 1040, IMG = PT + 528, X = IMG + 528,
+                       PTR = X + 4096, CST = PTR + 544, CPT = CST + 144, BYTES = CPT + 3088;
+};
+static_assert(PtStage::BYTES % 16 == 0, "stage size");
+constexpr int PB_SMEM = 2 * PtStage::BYTES + PW_THREADS * 9 * 8 + PW_WARPS * 256 * 16;  // stages | s_le | s_v / rows
+
+__device__ __forceinline__ void pb_mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void pb_mbar_expect(uint64_t* bar, unsigned bytes) {
+  asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n}" ::"r"(
+                   (unsigned)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void pb_mbar_wait(uint64_t* bar, unsigned parity) {
+  const unsigned addr = (unsigned)__cvta_generic_to_shared(bar);
+  unsigned done;
+  do {
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+  } while (!done);
+}
+// bulk copy of the 16-byte aligned cover of [src, src + bytes) to dst; returns the bytes moved
+__device__ __forceinline__ unsigned pb_bulk(void* dst, const void* src, size_t bytes, uint64_t* bar) {
+  const uintptr_t s0 = reinterpret_cast<uintptr_t>(src) & ~(uintptr_t)15;
+  const uintptr_t s1 = (reinterpret_cast<uintptr_t>(src) + bytes + 15) & ~(uintptr_t)15;
+  const unsigned n = (unsigned)(s1 - s0);
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   (unsigned)__cvta_generic_to_shared(dst)), "l"(s0), "r"(n), "r"((unsigned)__cvta_generic_to_shared(bar))
+               : "memory");
+  return n;
+}
+__device__ __forceinline__ int pb_skew(const void* src) { return (int)(reinterpret_cast<uintptr_t>(src) & 15); }
+
+__global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points_bulk(
+    ProblemView pv, const double* __restrict__ pose, const double* __restrict__ X, LmDiag lm, double* __restrict__ c_pt,
+    int compute_scaling, int jacobi_scaling, double* __restrict__ Hpp, double* __restrict__ gp, double* __restrict__ Hinv,
+    double* __restrict__ Linv, double* __restrict__ fac, double* __restrict__ pt_part, double* __restrict__ scal,
+    int write_factors, int num_groups) {
+  extern __shared__ __align__(128) unsigned char pb_smem[];
+  __shared__ uint64_t s_bar[2];
+  __shared__ __align__(16) int4 s_desc[2];
+  __shared__ double smx2[2][PW_WARPS];  // warp maxima of |gp|, by ring parity: thread 0 reads them one barrier later
+  unsigned char* stage0 = pb_smem;
+  double (*s_le)[9] = reinterpret_cast<double (*)[9]>(pb_smem + 2 * PtStage::BYTES);
+  unsigned char* uni = pb_smem + 2 * PtStage::BYTES + PW_THREADS * 9 * 8;
+  double (*s_v)[9] = reinterpret_cast<double (*)[9]>(uni);       // phases 1-2
+  double2* rows_all = reinterpret_cast<double2*>(uni);            // phase 3 (after a CTA barrier)
+  if (compute_scaling < 0) compute_scaling = __ldcg(lm.dev + LD_FIRST) != 0.0 ? 1 : 0;
+  lm_resolve(lm);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const size_t N = (size_t)pv.N;
+  if (tid == 0) {
+    pb_mbar_init(&s_bar[0], 1);
+    pb_mbar_init(&s_bar[1], 1);
+  }
+  __syncthreads();
+  // thread 0: descriptor of group g into s_desc[st] and the group's bulk copies into stage st
+  auto issue = [&](int g, int st) {
+    const int4 d = __ldg(pv.cta_desc + g);
+    s_desc[st] = d;
+    if (d.w > PW_THREADS) {  // oversized group: the warp path reads global memory itself
+      pb_mbar_expect(&s_bar[st], 0);
+      return;
+    }
+    const size_t T0 = (size_t)d.x, nt = (size_t)d.y, base = (size_t)d.z, n = (size_t)d.w;
+    unsigned char* sb = stage0 + (size_t)st * PtStage::BYTES;
+    const void* src[10] = {pv.pm_xy + 2 * base, pv.pm_depth + base, pv.pm_depth + N + base, pv.pm_depth + 2 * N + base,
+                           pv.pm_pt + base,     pv.pm_img + base,   X + 4 * T0,             pv.pt_ptr + T0,
+                           pv.pt_const + T0,    c_pt + 3 * T0};
+    const size_t len[10] = {n * 16, n * 8, n * 8, n * 8, n * 4, n * 4, nt * 32, (nt + 1) * 4, nt,
+                            compute_scaling ? 0 : nt * 24};  // the Jacobi scales exist after the first iteration
+    const int off[10] = {PtStage::XY, PtStage::D0, PtStage::D1, PtStage::D2, PtStage::PT, PtStage::IMG, PtStage::X,
+                         PtStage::PTR, PtStage::CST, PtStage::CPT};
+    unsigned total = 0;
+#pragma unroll
+    for (int k = 0; k < 10; ++k) {
+      const uintptr_t a = reinterpret_cast<uintptr_t>(src[k]);
+      if (len[k]) total += (unsigned)(((a + len[k] + 15) & ~(uintptr_t)15) - (a & ~(uintptr_t)15));
+    }
+    pb_mbar_expect(&s_bar[st], total);
+#pragma unroll
+    for (int k = 0; k < 10; ++k)
+      if (len[k]) pb_bulk(sb + off[k], src[k], len[k], &s_bar[st]);
+  };
+  int g = blockIdx.x;
+  if (tid == 0 && g < num_groups) issue(g, 0);
+  for (int it = 0; g < num_groups; ++it, g += gridDim.x) {
+    const int st = it & 1;
+    double* smx = smx2[st];
+    // the stage of the NEXT group was last read two groups ago: every thread is past that (barrier at the loop's end)
+    if (tid == 0 && g + (int)gridDim.x < num_groups) issue(g + gridDim.x, st ^ 1);
+    pb_mbar_wait(&s_bar[st], (unsigned)(it >> 1) & 1u);  // stage st completes its (it / 2)-th phase
+    const int4 desc = s_desc[st];
+    const int T0 = desc.x, nt = desc.y, base = desc.z, n = desc.w;
+    const unsigned char* sb = stage0 + (size_t)st * PtStage::BYTES;
+    double gmax = 0.0;
+    if (n <= PW_THREADS) {
+      const double2* s_xy = reinterpret_cast<const double2*>(sb + PtStage::XY + pb_skew(pv.pm_xy + 2 * (size_t)base));
+      const double* s_d0 = reinterpret_cast<const double*>(sb + PtStage::D0 + pb_skew(pv.pm_depth + base));
+      const double* s_d1 = reinterpret_cast<const double*>(sb + PtStage::D1 + pb_skew(pv.pm_depth + N + base));
+      const double* s_d2 = reinterpret_cast<const double*>(sb + PtStage::D2 + pb_skew(pv.pm_depth + 2 * N + base));
+      const int* s_pt = reinterpret_cast<const int*>(sb + PtStage::PT + pb_skew(pv.pm_pt + base));
+      const int* s_img = reinterpret_cast<const int*>(sb + PtStage::IMG + pb_skew(pv.pm_img + base));
+      const double2* s_X = reinterpret_cast<const double2*>(sb + PtStage::X);  // 32-byte records: no skew
+      const int* s_ptr = reinterpret_cast<const int*>(sb + PtStage::PTR + pb_skew(pv.pt_ptr + T0));
+      const uint8_t* s_cst = sb + PtStage::CST + pb_skew(pv.pt_const + T0);
+      const double* s_cpt = reinterpret_cast<const double*>(sb + PtStage::CPT + pb_skew(c_pt + 3 * (size_t)T0));
+      int start = 0, len = 0;
+      bool cst = true;
+      if (tid < nt) {
+        const int a = s_ptr[tid], b = s_ptr[tid + 1];
+        start = a - base;
+        len = b - a;
+        cst = s_cst[tid] != 0;
+      }
+      // ---- 1. observations
+      int tr = -1;
+      double Q[9], prot[3] = {0.0, 0.0, 0.0};
+      if (tid < n) {
+        const int pt = s_pt[tid];
+        const double2 xa = s_X[2 * (pt - T0)], xb = s_X[2 * (pt - T0) + 1];
+        if (xb.y == 0.0) {  // slot 3: constant flag
+          tr = pt - T0;
+          const double Xp[3] = {xa.x, xa.y, xb.x};
+          ObsLin o;
+          ImgConst ic;
+          load_img(pv, pose, s_img[tid], ic);
+          const double2 o2 = s_xy[tid];
+          linearize_obs<true, false>(ic.pose, ic.R, Xp, ic.model, ic.prm, o2.x, o2.y, s_d0[tid], s_d1[tid], s_d2[tid], ic.b,
+                                     ic.es, pv.loss, o);
+          double v[9];
+          point_terms(o, ic.R, Q, v);
+#pragma unroll
+          for (int j = 0; j < 9; ++j) s_v[tid][j] = v[j];
+          prot[0] = o.prot[0]; prot[1] = o.prot[1]; prot[2] = o.prot[2];
+        }
+      }
+      const bool act = tr >= 0;
+      __syncthreads();
+      // ---- 2. points
+      if (tid < nt) {
+        const bool active = !cst && len > 0;
+        double v[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        if (active) {
+          for (int k = 0; k < len; ++k) {
+#pragma unroll
+            for (int j = 0; j < 9; ++j) v[j] += s_v[start + k][j];
+          }
+        }
+        double Li[6], e[3];
+        finalize_point(T0 + tid, active, v, v + 6, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, scal,
+                       Li, e, compute_scaling ? nullptr : s_cpt + 3 * tid);
+#pragma unroll
+        for (int j = 0; j < 6; ++j) s_le[tid][j] = Li[j];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) s_le[tid][6 + j] = e[j];
+        gmax = fmax(fabs(v[6]), fmax(fabs(v[7]), fabs(v[8])));
+      }
+      for (int off = 16; off > 0; off >>= 1) gmax = fmax(gmax, __shfl_xor_sync(FULL, gmax, off));
+      if (lane == 0) smx[warp] = gmax;
+      if (write_factors) {
+        __syncthreads();  // s_le complete; s_v no longer read: its bytes become the record rows
+        // ---- 3. Schur factors
+        double2* rows = rows_all + warp * 256;
+        if (act) {
+          double Lo[6], eo[3];
+#pragma unroll
+          for (int j = 0; j < 6; ++j) Lo[j] = s_le[tr][j];
+#pragma unroll
+          for (int j = 0; j < 3; ++j) eo[j] = s_le[tr][6 + j];
+          double2 rec[8];
+          pack_factor(Q, Lo, prot, eo, rec);
+          const int sw = lane & 7;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) rows[lane * 8 + (c ^ sw)] = rec[c];
+        }
+        const unsigned actmask = __ballot_sync(FULL, act);
+        double2* fac2 = reinterpret_cast<double2*>(fac);
+        const int g4 = lane >> 3, c = lane & 7;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int item = 4 * j + g4;
+          if ((actmask >> item) & 1u) fac2[(size_t)(base + 32 * warp + item) * 8 + c] = rows[item * 8 + (c ^ (item & 7))];
+        }
+      }
+    } else {
+      const int w = g * PW_WARPS + warp;
+      if (w < min((g + 1) * PW_WARPS, pv.num_track_warps))
+        gmax = points_warp_path(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, fac, scal,
+                                write_factors, rows_all + warp * 256, w, lane);
+    }
+    if (n > PW_THREADS) {
+      for (int off = 16; off > 0; off >>= 1) gmax = fmax(gmax, __shfl_xor_sync(FULL, gmax, off));
+      if (lane == 0) smx[warp] = gmax;
+    }
+    __syncthreads();  // the warp maxima are in place; also the loop-end barrier of the ring (stage, s_v / rows, s_le)
+    if (tid == 0) {
+      double m = smx[0];
+#pragma unroll
+      for (int w = 1; w < PW_WARPS; ++w) m = fmax(m, smx[w]);
+      pt_part[(size_t)g * PT_PART] = m;
+    }
   }
 }
 
@@ -1083,7 +1320,11 @@ __global__ void __launch_bounds__(128) k_block_inverse(ProblemView pv, const dou
 //   * two grid barriers per iteration instead of three: p <- z + beta p is never published, every CTA
 //     rebuilds the entries of p it gathers from z and the previous p (double buffered),
 //   * a barrier is one atomic arrive + spin on a monotonic counter; the dot-product partials ride on
-//     it through per-CTA slots that every CTA then sums in the same fixed order (deterministic).
+//     it through per-CTA slots that every CTA then sums in the same fixed order (deterministic),
+//   * (round 2) the product gathers its operand ONCE per iteration: the distinct block columns of the CTA's rows
+//     (a bitmap over the images, ranked at kernel start) are pulled from L2 into shared memory by all threads in
+//     one step, and the block products read shared memory.  Before, every block product issued its own two L2
+//     loads behind the column index: 13.7 k of the 35.6 k cycles of an iteration at 5 000 images (r2 cycle counters).
 struct PcgArgs {
   int C, rows_per_cta, max_local_blocks;
   const int32_t* row_ptr;
@@ -1106,6 +1347,8 @@ struct PcgArgs {
   const double* Zc;            // [C][6][7]
   const double* Ainv;          // [nc][nc] (Z^T S Z)^-1, symmetric
   double* tpart;               // [gridDim.x][8] per-CTA Z^T r of its rows (one group per CTA)
+  // halo staging of the product (see k_pcg): capacity in distinct block columns per CTA, 0 = off
+  int halo_cap, halo_words;
 };
 
 constexpr int PCG_THREADS = 512;  // 16 warps: one block row per warp and round, ~2 rounds at 5 000 images
@@ -1151,8 +1394,15 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
   double* s_q = s_r + (size_t)A.rows_per_cta * 6;
   double* s_p = s_q + (size_t)A.rows_per_cta * 6;
   int* s_rowptr = reinterpret_cast<int*>(s_p + (size_t)A.rows_per_cta * 6);
-  double* s_S = reinterpret_cast<double*>(s_rowptr + ((A.rows_per_cta + 2) & ~1));
+  double* s_S = reinterpret_cast<double*>(s_rowptr + ((A.rows_per_cta + 4) & ~3));  // 16-byte steps: s_ph is read as double2
   int* s_col = reinterpret_cast<int*>(s_S + (SMEM ? (size_t)A.max_local_blocks * 36 : 0));
+  // halo staging (A.halo_cap > 0): p of the distinct columns | column of a slot | slot of a local block | bitmap | ranks
+  double* s_ph = reinterpret_cast<double*>(s_col + (SMEM ? ((A.max_local_blocks + 3) & ~3) : 0));
+  int* s_ucol = reinterpret_cast<int*>(s_ph + (size_t)A.halo_cap * 6);
+  int* s_bslot = s_ucol + A.halo_cap;
+  unsigned* s_bits = reinterpret_cast<unsigned*>(s_bslot + (A.halo_cap > 0 ? A.max_local_blocks : 0));
+  int* s_pref = reinterpret_cast<int*>(s_bits + A.halo_words);
+  __shared__ int s_nuniq;
 
   for (int k = threadIdx.x; k < nrows * 36; k += PCG_THREADS) s_minv[k] = A.Minv[(size_t)row0 * 36 + k];
   for (int k = threadIdx.x; k <= nrows; k += PCG_THREADS) s_rowptr[k] = A.row_ptr[row0 + k] - blk_base;
@@ -1164,6 +1414,51 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
   __syncthreads();
   const double* Sbase = SMEM ? s_S : (A.S + (size_t)blk_base * 36);
   const int* colbase = SMEM ? s_col : (A.col + blk_base);
+  bool halo = A.halo_cap > 0;
+  int nuniq = 0;
+  if (halo) {
+    for (int w = threadIdx.x; w < A.halo_words; w += PCG_THREADS) s_bits[w] = 0u;
+    __syncthreads();
+    for (int k = threadIdx.x; k < nblk; k += PCG_THREADS) {
+      const int c = colbase[k];
+      atomicOr(&s_bits[c >> 5], 1u << (c & 31));
+    }
+    __syncthreads();
+    if (warp == 0) {  // exclusive prefix of the word popcounts: rank of a column = s_pref[word] + popc(lower bits)
+      int run = 0;
+      for (int w0 = 0; w0 < A.halo_words; w0 += 32) {
+        const int w = w0 + lane;
+        const int cnt = w < A.halo_words ? __popc(s_bits[w]) : 0;
+        int scan = cnt;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+          const int t = __shfl_up_sync(FULL, scan, off);
+          if (lane >= off) scan += t;
+        }
+        if (w < A.halo_words) s_pref[w] = run + scan - cnt;
+        run += __shfl_sync(FULL, scan, 31);
+      }
+      if (lane == 0) s_nuniq = run;
+    }
+    __syncthreads();
+    nuniq = s_nuniq;
+    halo = nuniq <= A.halo_cap;  // uniform in the CTA; a CTA over capacity keeps the per-block loads (same numbers)
+    if (halo) {
+      for (int w = threadIdx.x; w < A.halo_words; w += PCG_THREADS) {
+        unsigned bits = s_bits[w];
+        int slot = s_pref[w];
+        while (bits) {
+          s_ucol[slot++] = 32 * w + (__ffs(bits) - 1);
+          bits &= bits - 1;
+        }
+      }
+      for (int k = threadIdx.x; k < nblk; k += PCG_THREADS) {
+        const int c = colbase[k];
+        s_bslot[k] = s_pref[c >> 5] + __popc(s_bits[c >> 5] & ((1u << (c & 31)) - 1u));
+      }
+    }
+    __syncthreads();
+  }
 
   double* part0 = A.partial;
   double* part1 = A.partial + gridDim.x;
@@ -1297,20 +1592,40 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
       const long long c0 = clock64();
       // p = z + beta p_old (rebuilt where gathered); q = S p; p'q
       part = 0.0;
+      if (halo) {
+        double2* ph2 = reinterpret_cast<double2*>(s_ph);
+        for (int u = threadIdx.x; u < nuniq * 3; u += PCG_THREADS) {
+          const int j = s_ucol[u / 3], h = u - 3 * (u / 3);
+          const double2 zz = __ldcg(reinterpret_cast<const double2*>(A.z + (size_t)j * 6) + h);
+          const double2 pp = __ldcg(reinterpret_cast<const double2*>(pold + (size_t)j * 6) + h);
+          ph2[u] = make_double2(zz.x + beta * pp.x, zz.y + beta * pp.y);
+        }
+        __syncthreads();
+      }
       for (int lr = warp; lr < nrows; lr += WPB) {
         const int row = row0 + lr;
         const int b0 = s_rowptr[lr], b1 = s_rowptr[lr + 1];
         double acc = 0.0;
         if (lane < 30) {
+          if (halo) {
 #pragma unroll 4
-          for (int blk = b0 + kb0; blk < b1; blk += 5) {
-            const int col = colbase[blk];
-            double zc[6], pc[6];
-            ldcg6(A.z + (size_t)col * 6, zc);
-            ldcg6(pold + (size_t)col * 6, pc);
-            const double* Sb = Sbase + (size_t)blk * 36 + r6 * 6;
+            for (int blk = b0 + kb0; blk < b1; blk += 5) {
+              const double* pc = s_ph + s_bslot[blk] * 6;
+              const double* Sb = Sbase + (size_t)blk * 36 + r6 * 6;
 #pragma unroll
-            for (int c = 0; c < 6; ++c) acc += Sb[c] * (zc[c] + beta * pc[c]);
+              for (int c = 0; c < 6; ++c) acc += Sb[c] * pc[c];
+            }
+          } else {
+#pragma unroll 4
+            for (int blk = b0 + kb0; blk < b1; blk += 5) {
+              const int col = colbase[blk];
+              double zc[6], pc[6];
+              ldcg6(A.z + (size_t)col * 6, zc);
+              ldcg6(pold + (size_t)col * 6, pc);
+              const double* Sb = Sbase + (size_t)blk * 36 + r6 * 6;
+#pragma unroll
+              for (int c = 0; c < 6; ++c) acc += Sb[c] * (zc[c] + beta * pc[c]);
+            }
           }
         }
         const double a1 = __shfl_sync(FULL, acc, r6 + 6), a2 = __shfl_sync(FULL, acc, r6 + 12),
@@ -1318,7 +1633,11 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
         if (lane < 6) {
           const size_t o = (size_t)row * 6 + lane;
           const double qv = acc + a1 + a2 + a3 + a4;
-          const double pi = __ldcg(A.z + o) + beta * __ldcg(pold + o);
+          double pi;
+          if (halo)
+            pi = s_ph[(s_pref[row >> 5] + __popc(s_bits[row >> 5] & ((1u << (row & 31)) - 1u))) * 6 + lane];
+          else
+            pi = __ldcg(A.z + o) + beta * __ldcg(pold + o);
           __stcg(pnew + o, pi);
           s_p[lr * 6 + lane] = pi;
           s_q[lr * 6 + lane] = qv;
@@ -1777,11 +2096,24 @@ void launch_points(const ProblemView& pv, const double* pose, const double* X, L
                    double* fac, double* pt_part, double* scal, int write_factors, cudaStream_t st) {
   static const int force_warp = getenv("MPBA_POINTS_WARP") ? atoi(getenv("MPBA_POINTS_WARP")) : 0;
   static const int prefetch_ahead = getenv("MPBA_POINTS_PREFETCH") ? atoi(getenv("MPBA_POINTS_PREFETCH")) : MPBA_POINTS_PREFETCH_DEFAULT;
-  if (pv.num_track_warps > 0)
-    k_points<<<track_warp_grid(pv.num_track_warps), PW_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling,
-                                                                         jacobi_scaling, Hpp, gp, Hinv, Linv, fac,
-                                                                         pt_part, scal, write_factors, force_warp,
-                                                                         prefetch_ahead);
+  // MPBA_POINTS_BULK=1: the cp.async.bulk / mbarrier pipelined variant (k_points_bulk), persistent CTAs
+  static const int bulk = getenv("MPBA_POINTS_BULK") ? atoi(getenv("MPBA_POINTS_BULK")) : MPBA_POINTS_BULK_DEFAULT;
+  static int bulk_grid = 0;
+  if (bulk && !bulk_grid) {
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaFuncSetAttribute(k_points_bulk, cudaFuncAttributeMaxDynamicSharedMemorySize, PB_SMEM);
+    bulk_grid = sms * MPBA_POINTS_MINB;
+  }
+  const int groups = track_warp_grid(pv.num_track_warps);
+  if (pv.num_track_warps > 0 && bulk && !force_warp)
+    k_points_bulk<<<groups < bulk_grid ? groups : bulk_grid, PW_THREADS, PB_SMEM, st>>>(
+        pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, fac, pt_part, scal, write_factors,
+        groups);
+  else if (pv.num_track_warps > 0)
+    k_points<<<groups, PW_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv,
+                                            fac, pt_part, scal, write_factors, force_warp, prefetch_ahead);
 }
 void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaStream_t st) {
   k_pt_scalars_gmax<<<1, 1024, 0, st>>>(pt_part, nblk, scal);
@@ -1820,11 +2152,30 @@ PcgPlan pcg_plan(int device, int C, int max_row_blocks) {
   pl.rows_per_cta = (C + grid - 1) / grid;
   pl.grid = (C + pl.rows_per_cta - 1) / pl.rows_per_cta;
   const size_t rows = (size_t)pl.rows_per_cta;
-  const size_t base = rows * (36 + 24) * sizeof(double) + ((rows + 2) & ~(size_t)1) * sizeof(int);
+  const size_t base = rows * (36 + 24) * sizeof(double) + ((rows + 4) & ~(size_t)3) * sizeof(int);
   pl.max_local_blocks = (int)(rows * (size_t)(max_row_blocks > 0 ? max_row_blocks : 1 << 16));
-  const size_t with_s = base + (size_t)pl.max_local_blocks * (36 * sizeof(double) + sizeof(int)) + 16;
-  pl.use_smem = (max_row_blocks > 0 && with_s <= (size_t)(smem_optin - 40960)) ? 1 : 0;
-  pl.smem_bytes = pl.use_smem ? with_s : base + 16;
+  // halo staging of the product: distinct columns of a CTA's rows (capacity), the slot of every local block, a bitmap
+  // over the images and its ranks; taken when it fits next to the row-local vectors, S in shared memory after that
+  const size_t budget = (size_t)(smem_optin - 40960);
+  pl.halo_cap = 0;
+  pl.halo_words = 0;
+  size_t halo_bytes = 0;
+  if (max_row_blocks > 0 && C <= (1 << 17)) {
+    const int cap = std::min(std::min(C, pl.max_local_blocks), 2048);
+    const int words = (C + 31) / 32;
+    halo_bytes = (size_t)cap * (6 * sizeof(double) + sizeof(int)) + (size_t)pl.max_local_blocks * sizeof(int) +
+                 2 * (size_t)words * sizeof(int) + 16;
+    if (base + halo_bytes + 16 <= budget) {
+      pl.halo_cap = cap;
+      pl.halo_words = words;
+    } else {
+      halo_bytes = 0;
+    }
+  }
+  const size_t with_s = base + (size_t)pl.max_local_blocks * 36 * sizeof(double) +
+                        (size_t)((pl.max_local_blocks + 3) & ~3) * sizeof(int) + 16;
+  pl.use_smem = (max_row_blocks > 0 && with_s + halo_bytes <= budget) ? 1 : 0;
+  pl.smem_bytes = (pl.use_smem ? with_s : base + 16) + halo_bytes;
   return pl;
 }
 cudaError_t launch_pcg(const ProblemView& pv, const PcgPlan& pl, const double* S, const double* Minv, const double* rhs,
@@ -1836,6 +2187,7 @@ cudaError_t launch_pcg(const ProblemView& pv, const PcgPlan& pl, const double* S
   a.row_ptr = pv.s_row_ptr; a.col = pv.s_col; a.S = S; a.Minv = Minv; a.rhs = rhs; a.x = y;
   a.z = vec_z; a.p0 = vec_p0; a.p1 = vec_p1; a.partial = partial; a.bar = bar; a.scal = scal;
   a.tol = tol; a.max_iter = max_iter;
+  a.halo_cap = pl.halo_cap; a.halo_words = pl.halo_words;
   cudaError_t e = cudaMemsetAsync(bar, 0, sizeof(unsigned), st);
   if (e != cudaSuccess) return e;
   void* args[] = {&a};

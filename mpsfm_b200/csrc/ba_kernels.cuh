@@ -156,6 +156,7 @@ void launch_combine_scalars(const double* scal_all, int world, double* scal, cud
 void launch_block_inverse(const ProblemView& pv, const double* S, double* Minv, cudaStream_t st);
 struct PcgPlan {
   int grid, rows_per_cta, use_smem, max_local_blocks;
+  int halo_cap, halo_words;  // halo staging of the grid PCG's product (0: off)
   size_t smem_bytes;
 };
 PcgPlan pcg_plan(int device, int C, int max_row_blocks);
