@@ -382,11 +382,14 @@ def run_gpu(args):
         traffic = None  # DRAM bytes per launch of that kernel from the committed ncu --set full capture (1 GPU only)
         try:
             if world == 1:
-                traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json"))).get(args.workload, {}).get(top)
+                traffic = json.load(open(os.path.join(ROOT, "profiles", "r02_traffic.json"))).get(args.workload, {}).get(top)
         except Exception:
             traffic = None
         roof = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": ab[top],
+                "traffic": traffic,
+                "traffic_source": ("profiles/r02_traffic.json: DRAM bytes of one launch from the committed ncu --set full "
+                                   "capture of this workload (not re-measured by this run)") if traffic else None,
+                "peak_source": peak_src, "algorithmic_bytes_per_launch": ab[top],
                 "avg_launch_ms": ms / n, "frac_of_nominal_8TBps": achieved / 8000.0}
 
     cpu = (cpu_baseline_sample(args.workload, layout=full, problem=prob, pcg_tol=args.pcg_tol, budget_s=args.ref_budget)
