@@ -963,6 +963,62 @@ __global__ void __launch_bounds__(1024) k_pt_scalars_gmax(const double* __restri
 // ================================================================================================
 // reduced camera system
 // ================================================================================================
+// Inverse of one 6x6 SPD block through its Cholesky factor (identity if it is not positive definite).  Every loop is
+// unrolled: the two 36-entry work arrays live in registers (with run-time loop bounds they sat in local memory and
+// k_block_inverse took 17 us for ANY number of images -- one thread's dependent chain through L1).
+__device__ __forceinline__ void block_inverse6(const double* src, double* __restrict__ dst) {
+  double A[36], Li[36];
+#pragma unroll
+  for (int k = 0; k < 36; ++k) A[k] = src[k];
+  bool ok = true;
+  // in-place Cholesky, lower
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    double d = A[7 * j];
+#pragma unroll
+    for (int k = 0; k < j; ++k) d -= A[6 * j + k] * A[6 * j + k];
+    ok = ok && (d > 0.0);
+    d = sqrt(ok ? d : 1.0);
+    A[7 * j] = d;
+#pragma unroll
+    for (int r = j + 1; r < 6; ++r) {
+      double s = A[6 * r + j];
+#pragma unroll
+      for (int k = 0; k < j; ++k) s -= A[6 * r + k] * A[6 * j + k];
+      A[6 * r + j] = s / d;
+    }
+  }
+  if (!ok) {
+#pragma unroll
+    for (int k = 0; k < 36; ++k) dst[k] = (k % 7 == 0) ? 1.0 : 0.0;
+    return;
+  }
+  // Li = L^-1 (lower)
+#pragma unroll
+  for (int k = 0; k < 36; ++k) Li[k] = 0.0;
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    Li[7 * c] = 1.0 / A[7 * c];
+#pragma unroll
+    for (int r = c + 1; r < 6; ++r) {
+      double s = 0.0;
+#pragma unroll
+      for (int k = c; k < r; ++k) s -= A[6 * r + k] * Li[6 * k + c];
+      Li[6 * r + c] = s / A[7 * r];
+    }
+  }
+  // A^-1 = Li^T Li
+#pragma unroll
+  for (int r = 0; r < 6; ++r)
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+      double s = 0.0;
+#pragma unroll
+      for (int k = (r > c ? r : c); k < 6; ++k) s += Li[6 * k + r] * Li[6 * k + c];
+      dst[6 * r + c] = s;
+    }
+}
+
 constexpr int SB_THREADS = 128;
 // per warp and buffer: 32 items x (record a: 8 chunks, record b: 8 chunks) of 16 bytes = 8 KB; two buffers, 4 warps
 constexpr int SB_WARP_CHUNKS = 512;
@@ -1007,7 +1063,7 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
                                                              const double* __restrict__ gc,
                                                              const double* __restrict__ c_img, LmDiag lm,
                                                              double* __restrict__ S, double* __restrict__ rhs,
-                                                             int partial) {
+                                                             int partial, double* __restrict__ Minv) {
   lm_resolve(lm);
   const int u = blockIdx.x;
   const int blk = pv.u_block[u];
@@ -1204,6 +1260,60 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
     const int r = threadIdx.x - 64;
     rhs[(size_t)i * 6 + r] = ((mi >> r) & 1u) ? (partial ? 0.0 : gc[(size_t)i * 6 + r]) - sm[0][36 + r] : 0.0;
   }
+  if (diag && !partial && Minv != nullptr) {  // CTA-uniform: the block-Jacobi inverse of the block just written
+    // Gauss-Jordan on [M | N] (N starts as the identity) by ONE warp in shared memory, lane = entries lane and lane + 32:
+    // six steps of ~100 cycles.  (One thread running the Cholesky-based block_inverse6 here put its work arrays in
+    // local memory at this kernel's 162 registers and cost the diagonal CTAs 16 us.)  A pivot that is not positive
+    // (the block is not positive definite) makes the block's preconditioner the identity, as k_block_inverse does.
+    double* Mm = sm[1];
+    double* Nn = sm[2];
+    if (threadIdx.x < 36) {
+      Mm[threadIdx.x] = S[(size_t)blk * 36 + threadIdx.x];  // own store: reads back its value
+      Nn[threadIdx.x] = (threadIdx.x % 7 == 0) ? 1.0 : 0.0;
+    }
+    __syncthreads();
+    if (warp == 0) {
+      bool ok = true;
+#pragma unroll
+      for (int p = 0; p < 6; ++p) {
+        const double piv = Mm[7 * p];
+        ok = ok && (piv > 0.0);
+        const double inv = 1.0 / (ok ? piv : 1.0);
+        double m2[2], n2[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int e = lane + 32 * h;
+          m2[h] = 0.0; n2[h] = 0.0;
+          if (e < 36) {
+            const int r = e / 6, c = e % 6;
+            const double f = Mm[6 * r + p];
+            const double mp = Mm[6 * p + c] * inv, np_ = Nn[6 * p + c] * inv;
+            m2[h] = (r == p) ? mp : Mm[e] - f * mp;
+            n2[h] = (r == p) ? np_ : Nn[e] - f * np_;
+          }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int e = lane + 32 * h;
+          if (e < 36) {
+            Mm[e] = m2[h];
+            Nn[e] = n2[h];
+          }
+        }
+        __syncwarp();
+      }
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int e = lane + 32 * h;
+        if (e < 36) {
+          const int r = e / 6, c = e % 6;
+          // symmetrised; identity when a pivot failed
+          Minv[(size_t)i * 36 + e] = ok ? 0.5 * (Nn[6 * r + c] + Nn[6 * c + r]) : ((r == c) ? 1.0 : 0.0);
+        }
+      }
+    }
+  }
 }
 
 // Sharded solve, after the all-reduce of the partial blocks: S(i,i) += Hcc_i + D_i, rhs_i += gc_i, identity rows
@@ -1249,65 +1359,13 @@ __global__ void k_combine_scalars(const double* __restrict__ scal_all, int world
   scal[k] = v;
 }
 
-// block-Jacobi preconditioner: inverse of each 6x6 diagonal block through its Cholesky factor.  Every loop is unrolled:
-// the two 36-entry work arrays live in registers (with run-time loop bounds they sat in local memory and the kernel
-// took 17 us for ANY number of images -- one thread's dependent chain through L1; round-2 small-bundle profile).
+// block-Jacobi preconditioner of a sharded solve (the diagonal blocks are complete only after the all-reduce); the
+// single-GPU solve inverts every diagonal block in the CTA of k_schur_blocks that wrote it.
 __global__ void __launch_bounds__(128) k_block_inverse(ProblemView pv, const double* __restrict__ S,
                                                        double* __restrict__ Minv) {
   const int i = blockIdx.x * 128 + threadIdx.x;
   if (i >= pv.C) return;
-  double A[36], Li[36];
-  const double* src = S + (size_t)pv.s_diag[i] * 36;
-#pragma unroll
-  for (int k = 0; k < 36; ++k) A[k] = src[k];
-  bool ok = true;
-  // in-place Cholesky, lower
-#pragma unroll
-  for (int j = 0; j < 6; ++j) {
-    double d = A[7 * j];
-#pragma unroll
-    for (int k = 0; k < j; ++k) d -= A[6 * j + k] * A[6 * j + k];
-    ok = ok && (d > 0.0);
-    d = sqrt(ok ? d : 1.0);
-    A[7 * j] = d;
-#pragma unroll
-    for (int r = j + 1; r < 6; ++r) {
-      double s = A[6 * r + j];
-#pragma unroll
-      for (int k = 0; k < j; ++k) s -= A[6 * r + k] * A[6 * j + k];
-      A[6 * r + j] = s / d;
-    }
-  }
-  double* dst = Minv + (size_t)i * 36;
-  if (!ok) {
-#pragma unroll
-    for (int k = 0; k < 36; ++k) dst[k] = (k % 7 == 0) ? 1.0 : 0.0;
-    return;
-  }
-  // Li = L^-1 (lower)
-#pragma unroll
-  for (int k = 0; k < 36; ++k) Li[k] = 0.0;
-#pragma unroll
-  for (int c = 0; c < 6; ++c) {
-    Li[7 * c] = 1.0 / A[7 * c];
-#pragma unroll
-    for (int r = c + 1; r < 6; ++r) {
-      double s = 0.0;
-#pragma unroll
-      for (int k = c; k < r; ++k) s -= A[6 * r + k] * Li[6 * k + c];
-      Li[6 * r + c] = s / A[7 * r];
-    }
-  }
-  // A^-1 = Li^T Li
-#pragma unroll
-  for (int r = 0; r < 6; ++r)
-#pragma unroll
-    for (int c = 0; c < 6; ++c) {
-      double s = 0.0;
-#pragma unroll
-      for (int k = (r > c ? r : c); k < 6; ++k) s += Li[6 * k + r] * Li[6 * k + c];
-      dst[6 * r + c] = s;
-    }
+  block_inverse6(S + (size_t)pv.s_diag[i] * 36, Minv + (size_t)i * 36);
 }
 
 // ---- persistent cooperative PCG on the block-CSR reduced camera system --------------------------
@@ -1740,6 +1798,18 @@ __global__ void __launch_bounds__(1024) k_cam_update(ProblemView pv, const doubl
   cam_update_body(pv, pose, y, Hc, gc, c_img, lm, pose_cand, scal, sm);
 }
 
+// The same step on CTAs of 128 images each (1 000 images by ONE CTA took 21 us): slice sums into stage[slice][3], added
+// in slice order by k_pt_scalars_step.  (Fusing these CTAs into k_back_substitute's launch was measured: its registers
+// went 56 -> 72 and the launch lost 27 us.)
+__global__ void __launch_bounds__(PW_THREADS) k_cam_update_slices(ProblemView pv, LmDiag lm, const double* __restrict__ y,
+                                                                  CamStepArgs cam) {
+  __shared__ double sm[PW_THREADS / 32 + 1];
+  lm_resolve(lm);
+  const int k = blockIdx.x;
+  cam_update_range<PW_THREADS>(pv, cam.pose, y, cam.Hc, cam.gc, cam.c_img, lm, cam.pose_cand, k * PW_THREADS,
+                               min(pv.C, (k + 1) * PW_THREADS), cam.stage + 3 * k, sm);
+}
+
 // Back-substitution from the stored Schur factors, one thread per observation (same warp packing as k_points).
 // With Hpp + D = L L^T, Z_a = N_a R_a L^-T, e = L^-1 gp and g_a = G_a y_c(a) (p_rot is in the record):
 //     y_p = (Hpp + D)^-1 (gp - sum_a W_a^T y_c(a)) = L^-T (e - sum_a Z_a^T g_a),      X_cand = X - y_p.
@@ -1803,7 +1873,8 @@ __global__ void __launch_bounds__(PW_THREADS) k_back_substitute(ProblemView pv, 
   __shared__ __align__(16) double2 rows_all[PW_WARPS][256];
   lm_resolve(lm);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int w = blockIdx.x * PW_WARPS + warp;
+  const int bid = (int)blockIdx.x;
+  const int w = bid * PW_WARPS + warp;
   double mcc = 0.0, step2 = 0.0, xn2 = 0.0;
   if (w < pv.num_track_warps) {
     const int4 desc = __ldg(pv.warp_desc + w);  // {first track, tracks, first slot, observations}
@@ -1893,41 +1964,62 @@ __global__ void __launch_bounds__(PW_THREADS) k_back_substitute(ProblemView pv, 
   step2 = block_sum<PW_WARPS>(step2, sm);
   xn2 = block_sum<PW_WARPS>(xn2, sm);
   if (threadIdx.x == 0) {
-    pt_part[(size_t)blockIdx.x * PT_PART + 1] = mcc;
-    pt_part[(size_t)blockIdx.x * PT_PART + 2] = step2;
-    pt_part[(size_t)blockIdx.x * PT_PART + 3] = xn2;
+    pt_part[(size_t)bid * PT_PART + 1] = mcc;
+    pt_part[(size_t)bid * PT_PART + 2] = step2;
+    pt_part[(size_t)bid * PT_PART + 3] = xn2;
   }
 }
 
-__global__ void __launch_bounds__(1024) k_pt_scalars_step(const double* __restrict__ pt_part, int nblk,
-                                                          double* __restrict__ scal, int with_gmax) {
-  __shared__ double sm[33];
+// Sums (and max |gp|) of the per-CTA partials of the track-order passes.  One CTA walking all rows took 31 us at cfg3
+// (39 k rows): now up to 64 CTAs reduce contiguous slices (fixed order inside a slice) into a stage row each, and the
+// CTA that arrives last (ticket) adds the stage rows in slice order -- deterministic, one launch.
+constexpr int PTS_THREADS = 256, PTS_MAX_CTAS = 64;
+__global__ void __launch_bounds__(PTS_THREADS) k_pt_scalars_step(const double* __restrict__ pt_part, int nblk,
+                                                                 double* __restrict__ scal, int with_gmax,
+                                                                 double* stage /* [gridDim.x][4] */, unsigned* ticket,
+                                                                 const double* cam_stage, int cam_rows) {
+  __shared__ double sm[PTS_THREADS / 32 + 1];
+  __shared__ unsigned s_last;
+  const int G = gridDim.x;
+  const int per = (nblk + G - 1) / G;
+  const int r0 = blockIdx.x * per, r1 = min(nblk, r0 + per);
   double a = 0.0, b = 0.0, c = 0.0, gm = 0.0;
-  // two rows in flight per thread (same per-thread summation order as a plain loop: row i, then row i + 1024)
-  int i = threadIdx.x;
-  for (; i + 1024 < nblk; i += 2 * 1024) {
-    const double* p0 = pt_part + (size_t)i * PT_PART;
-    const double* p1 = pt_part + (size_t)(i + 1024) * PT_PART;
-    const double a0 = p0[1], b0 = p0[2], c0 = p0[3], a1 = p1[1], b1 = p1[2], c1 = p1[3];
-    if (with_gmax) gm = fmax(gm, fmax(p0[0], p1[0]));
-    a += a0; b += b0; c += c0;
-    a += a1; b += b1; c += c1;
+  for (int i = r0 + threadIdx.x; i < r1; i += PTS_THREADS) {
+    const double4 v = *reinterpret_cast<const double4*>(pt_part + (size_t)i * PT_PART);
+    if (with_gmax) gm = fmax(gm, v.x);
+    a += v.y; b += v.z; c += v.w;
   }
-  for (; i < nblk; i += 1024) {
-    if (with_gmax) gm = fmax(gm, pt_part[(size_t)i * PT_PART]);
-    a += pt_part[(size_t)i * PT_PART + 1];
-    b += pt_part[(size_t)i * PT_PART + 2];
-    c += pt_part[(size_t)i * PT_PART + 3];
-  }
-  a = block_sum<32>(a, sm);
-  b = block_sum<32>(b, sm);
-  c = block_sum<32>(c, sm);
-  if (with_gmax) gm = block_max<32>(gm, sm);
+  a = block_sum<PTS_THREADS / 32>(a, sm);
+  b = block_sum<PTS_THREADS / 32>(b, sm);
+  c = block_sum<PTS_THREADS / 32>(c, sm);
+  gm = block_max<PTS_THREADS / 32>(gm, sm);
   if (threadIdx.x == 0) {
-    scal[S_MCC] = a;
-    scal[S_STEP2_P] = b;
-    scal[S_XNORM2_P] = c;
-    if (with_gmax) scal[S_GMAX_P] = gm;
+    double* row = stage + 4 * blockIdx.x;
+    __stcg(row, gm); __stcg(row + 1, a); __stcg(row + 2, b); __stcg(row + 3, c);
+    __threadfence();
+    s_last = atomicAdd(ticket, 1u) == (unsigned)(G - 1) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (threadIdx.x < 4) {
+    double acc = 0.0;
+    for (int g = 0; g < G; ++g) {
+      const double v = __ldcg(stage + 4 * g + threadIdx.x);
+      acc = threadIdx.x == 0 ? fmax(acc, v) : acc + v;
+    }
+    if (threadIdx.x == 0) {
+      if (with_gmax) scal[S_GMAX_P] = acc;
+      *ticket = 0u;  // ready for the next launch
+    } else {
+      scal[threadIdx.x == 1 ? S_MCC : (threadIdx.x == 2 ? S_STEP2_P : S_XNORM2_P)] = acc;
+    }
+  } else if (threadIdx.x >= 32 && threadIdx.x < 35 && cam_rows > 0) {
+    // camera step slices written by the extra CTAs of k_back_substitute (complete: that kernel ran before this one)
+    const int q = threadIdx.x - 32;
+    double acc = 0.0;
+    for (int g = 0; g < cam_rows; ++g) acc += cam_stage[3 * g + q];
+    scal[q == 0 ? S_STEP2_C : (q == 1 ? S_XNORM2_C : S_MCC_C)] = acc;
   }
 }
 
@@ -2119,13 +2211,14 @@ void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaS
   k_pt_scalars_gmax<<<1, 1024, 0, st>>>(pt_part, nblk, scal);
 }
 void launch_schur_blocks(const ProblemView& pv, const double* fac, const double* Hc, const double* gc,
-                         const double* c_img, LmDiag lm, double* S, double* rhs, int partial, cudaStream_t st) {
+                         const double* c_img, LmDiag lm, double* S, double* rhs, int partial, double* Minv,
+                         cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_schur_blocks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_STAGE_BYTES);
     attr_set = true;
   }
-  k_schur_blocks<<<pv.U, SB_THREADS, SB_STAGE_BYTES, st>>>(pv, fac, Hc, gc, c_img, lm, S, rhs, partial);
+  k_schur_blocks<<<pv.U, SB_THREADS, SB_STAGE_BYTES, st>>>(pv, fac, Hc, gc, c_img, lm, S, rhs, partial, Minv);
 }
 void launch_schur_finish(const ProblemView& pv, const double* Hc, const double* gc, const double* c_img, LmDiag lm,
                          double* S, double* rhs, cudaStream_t st) {
@@ -2201,15 +2294,24 @@ void launch_cam_update(const ProblemView& pv, const double* pose, const double* 
 }
 void launch_back_substitute(const ProblemView& pv, const double* X, const double* y, const double* Hpp,
                             const double* gp, const double* Linv, const double* c_pt, const double* fac,
-                            int use_factors, LmDiag lm, double* X_cand, double* pt_part, cudaStream_t st) {
+                            int use_factors, LmDiag lm, double* X_cand, double* pt_part, const CamStepArgs* cam,
+                            cudaStream_t st) {
   static const int prefetch_ahead = getenv("MPBA_BACKSUB_PREFETCH") ? atoi(getenv("MPBA_BACKSUB_PREFETCH")) : MPBA_BACKSUB_PREFETCH_DEFAULT;
-  if (pv.num_track_warps > 0)
-    k_back_substitute<<<track_warp_grid(pv.num_track_warps), PW_THREADS, 0, st>>>(pv, X, y, Hpp, gp, Linv, c_pt, fac,
-                                                                                  use_factors, lm, X_cand, pt_part,
-                                                                                  prefetch_ahead);
+  if (cam) k_cam_update_slices<<<cam_step_rows(pv.C), PW_THREADS, 0, st>>>(pv, lm, y, *cam);
+  const int groups = track_warp_grid(pv.num_track_warps);
+  if (groups > 0)
+    k_back_substitute<<<groups, PW_THREADS, 0, st>>>(pv, X, y, Hpp, gp, Linv, c_pt, fac, use_factors, lm, X_cand, pt_part,
+                                                     prefetch_ahead);
 }
-void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, int with_gmax, cudaStream_t st) {
-  k_pt_scalars_step<<<1, 1024, 0, st>>>(pt_part, nblk, scal, with_gmax);
+int cam_step_rows(int num_images) { return (num_images + PW_THREADS - 1) / PW_THREADS; }
+void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, int with_gmax, double* stage,
+                            const double* cam_stage, int cam_rows, cudaStream_t st) {
+  int grid = (nblk + 4 * PTS_THREADS - 1) / (4 * PTS_THREADS);  // at least four rows per thread
+  grid = grid < 1 ? 1 : (grid > PTS_MAX_CTAS ? PTS_MAX_CTAS : grid);
+  // stage: [PTS_MAX_CTAS][4] doubles, then the ticket (zero at rest)
+  k_pt_scalars_step<<<grid, PTS_THREADS, 0, st>>>(pt_part, nblk, scal, with_gmax, stage,
+                                                   reinterpret_cast<unsigned*>(stage + 4 * PTS_MAX_CTAS), cam_stage,
+                                                   cam_rows);
 }
 void launch_evaluate(const ProblemView& pv, const double* pose, const double* X, double* r_reproj, double* r_depth,
                      cudaStream_t st) {

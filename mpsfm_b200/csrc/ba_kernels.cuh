@@ -148,7 +148,8 @@ void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaS
 // partial != 0 (sharded solve): S / rhs receive only this rank's -sum over its own tracks; after the all-reduce
 // launch_schur_finish adds Hcc + D, gc and the identity rows of fixed tangent coordinates.
 void launch_schur_blocks(const ProblemView& pv, const double* fac, const double* Hc, const double* gc,
-                         const double* c_img, LmDiag lm, double* S, double* rhs, int partial, cudaStream_t st);
+                         const double* c_img, LmDiag lm, double* S, double* rhs, int partial, double* Minv,
+                         cudaStream_t st);  // Minv != nullptr (and !partial): block-Jacobi inverses written by the diagonal CTAs
 void launch_schur_finish(const ProblemView& pv, const double* Hc, const double* gc, const double* c_img, LmDiag lm,
                          double* S, double* rhs, cudaStream_t st);
 // scal_all [world][S_COUNT] (all-gathered per-rank scalar blocks) -> scal: sums / max in rank order
@@ -253,11 +254,23 @@ cudaError_t launch_dense_solve(int C, const int32_t* row_ptr, const int32_t* col
 // q (+) -y, t - y, step norms, and the image part of the model cost change (g'y + y'Dy) / 2
 void launch_cam_update(const ProblemView& pv, const double* pose, const double* y, const double* Hc, const double* gc,
                        const double* c_img, LmDiag lm, double* pose_cand, double* scal, cudaStream_t st);
+// cam != nullptr: the camera step (launch_cam_update's work) is launched first as CTAs of 128 images each
+// (k_cam_update_slices); their slice sums land in cam->stage ([cam_step_rows(C)][3]) and are added by
+// launch_pt_scalars_step
+struct CamStepArgs {
+  const double *pose, *Hc, *gc, *c_img;
+  double* pose_cand;
+  double* stage;
+};
+int cam_step_rows(int num_images);
 void launch_back_substitute(const ProblemView& pv, const double* X, const double* y, const double* Hpp,
                             const double* gp, const double* Linv, const double* c_pt, const double* fac,
-                            int use_factors, LmDiag lm, double* X_cand, double* pt_part, cudaStream_t st);
-// with_gmax: also S_GMAX_P (slot 0 of the partials, written by k_points) -- the LM loop defers that reduction to here
-void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, int with_gmax, cudaStream_t st);
+                            int use_factors, LmDiag lm, double* X_cand, double* pt_part, const CamStepArgs* cam,
+                            cudaStream_t st);
+// stage: PT_SCALARS_STAGE doubles of workspace, zero before the first launch (slice partials + the arrival ticket)
+constexpr int PT_SCALARS_STAGE = 4 * 64 + 2;
+void launch_pt_scalars_step(const double* pt_part, int nblk, double* scal, int with_gmax, double* stage,
+                            const double* cam_stage, int cam_rows, cudaStream_t st);
 
 // ---- misc ---------------------------------------------------------------------------------------
 void launch_evaluate(const ProblemView& pv, const double* pose, const double* X, double* r_reproj, double* r_depth,

@@ -159,7 +159,7 @@ size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Workspace {
   double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *ip[2], *c_img, *c_pt, *Hpp, *gp, *Hinv, *fac, *S,
-      *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal, *scal_all, *Linv, *tpart;
+      *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal, *scal_all, *Linv, *tpart, *pts_stage, *cam_stage;
   double *Zc = nullptr, *Ac = nullptr, *Ainv = nullptr;  // coarse space (coarse.cu)
   double *Zc2 = nullptr, *Ainv2 = nullptr;               // lagged setup: the side stream's own Z, the second inverse
   int32_t* pm_pt = nullptr;   // point of every track-order slot (launch_track_setup)
@@ -223,6 +223,8 @@ void carve(const mpba_problem* p, const mpba_shard* sh, char* base, Workspace& w
   w.tpart = take(8 * 1024);
   w.pt_part = take(nblk * PT_PART + 8);
   w.scal = take(S_COUNT);
+  w.pts_stage = take(PT_SCALARS_STAGE);
+  w.cam_stage = take(3 * (size_t)cam_step_rows((int)C) + 2);
   w.scal_all = take(sh ? (size_t)sh->world * S_COUNT : 0);
   {
     const bool so = (p->flags & MPBA_FLAG_STRUCTURE_ONLY) != 0;
@@ -699,7 +701,7 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
     {
       Timer t(h, KS_S_FINALIZE);
       launch_schur_blocks(c.pv, c.w.fac, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.S, c.w.rhs, c.sh ? 1 : 0,
-                          h->stream);
+                          (c.sh || c.dense) ? nullptr : c.w.Minv, h->stream);
     }
     if (c.sh) {
       // partial reduced camera system of this rank's tracks -> all-reduce -> + Hcc + D, + gc (north star:
@@ -718,7 +720,7 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
       ++c.solves;
       return MPBA_OK;
     }
-    {
+    if (c.sh) {  // single GPU: written by the diagonal CTAs of k_schur_blocks
       Timer t(h, KS_BLOCK_INVERSE);
       launch_block_inverse(c.pv, c.w.S, c.w.Minv, h->stream);
     }
@@ -795,19 +797,21 @@ int enqueue_lm_iteration(Ctx& c, int cur, int cand, LmDiag lm, int compute_scali
   int rc = enqueue_points_and_system(c, c.w.pose[cur], c.w.X[cur], cur, lm, compute_scaling, &opt, true,
                                      c.dense ? c.w.pose[cand] : nullptr);
   if (rc) return rc;
-  if (!c.dense) {
-    Timer t(h, KS_CAM_UPDATE);
-    launch_cam_update(c.pv, c.w.pose[cur], c.w.y, c.w.Hc[cur], c.w.gc[cur], c.w.c_img, lm, c.w.pose[cand], c.w.scal,
-                      h->stream);
-  }
+  // the camera step: epilogue of the dense solve (<= 21 images) or extra CTAs of the back-substitution launch
+  CamStepArgs cam;
+  cam.pose = c.w.pose[cur]; cam.Hc = c.w.Hc[cur]; cam.gc = c.w.gc[cur]; cam.c_img = c.w.c_img;
+  cam.pose_cand = c.w.pose[cand];
+  cam.stage = c.w.cam_stage;
+  const int cam_rows = c.dense ? 0 : cam_step_rows(c.pv.C);
   {
     Timer t(h, KS_BACK_SUBSTITUTE);
     launch_back_substitute(c.pv, c.w.X[cur], c.w.y, c.w.Hpp, c.w.gp, c.w.Linv, c.w.c_pt, c.w.fac,
-                           c.structure_only ? 0 : 1, lm, c.w.X[cand], c.w.pt_part, h->stream);
+                           c.structure_only ? 0 : 1, lm, c.w.X[cand], c.w.pt_part, c.dense ? nullptr : &cam, h->stream);
   }
   {
     Timer t(h, KS_REDUCE);
-    launch_pt_scalars_step(c.w.pt_part, c.nblk, c.w.scal, c.defer_gmax ? 1 : 0, h->stream);
+    launch_pt_scalars_step(c.w.pt_part, c.nblk, c.w.scal, c.defer_gmax ? 1 : 0, c.w.pts_stage, c.w.cam_stage, cam_rows,
+                           h->stream);
   }
   if (c.sh) {
     // every rank wrote the candidates of its own points: all-gather in place (equal counts, pt_stride per rank)
@@ -1280,6 +1284,7 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
   // setup (a ~20 us single-CTA inverse) and with it the trajectory of the exact preconditioner
   c.coarse_lag = (opt.coarse_lag != 0 && prob->num_images >= 600) ? 1 : 0;
   c.defer_gmax = true;
+  CU(cudaMemsetAsync(c.w.pts_stage + 4 * 64, 0, 2 * sizeof(double), h->stream));  // arrival ticket of k_pt_scalars_step
   struct SideDrain {  // whatever the exit path: nothing of this call is left running on the side stream
     mpba_handle* h;
     ~SideDrain() { if (h->side) cudaStreamSynchronize(h->side); }

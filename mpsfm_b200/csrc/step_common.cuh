@@ -50,16 +50,19 @@ __device__ __forceinline__ void lm_resolve(LmDiag& lm) {
   }
 }
 
-// Camera step of one LM iteration by ONE CTA of 1024 threads: q (+) -y, t - y, step norms, image part of the model cost
-// change (g'y + y'Dy) / 2.  Body of k_cam_update; also the epilogue of the dense direct solve (dense_solve.cu).
-__device__ __forceinline__ void cam_update_body(const ProblemView& pv, const double* __restrict__ pose,
-                                                const double* y /* may have been written by this kernel */,
-                                                const double* __restrict__ Hc,
-                                                const double* __restrict__ gc, const double* __restrict__ c_img,
-                                                const LmDiag& lm, double* __restrict__ pose_cand,
-                                                double* __restrict__ scal, double* sm /* [33] */) {
+// Camera step of one LM iteration for the images [ibeg, iend) by one CTA of NT threads: q (+) -y, t - y, step norms,
+// image part of the model cost change (g'y + y'Dy) / 2.  out[0..2] = {step^2, |x|^2, model cost change} (thread 0).
+// Used by k_cam_update (one CTA, all images), the epilogue of the dense direct solve (dense_solve.cu) and the extra
+// CTAs of k_back_substitute (128 images each; the slices are added by k_pt_scalars_step).
+template <int NT>
+__device__ __forceinline__ void cam_update_range(const ProblemView& pv, const double* __restrict__ pose,
+                                                 const double* y /* may have been written by this kernel */,
+                                                 const double* __restrict__ Hc, const double* __restrict__ gc,
+                                                 const double* __restrict__ c_img, const LmDiag& lm,
+                                                 double* __restrict__ pose_cand, int ibeg, int iend, double* out,
+                                                 double* sm /* [NT / 32 + 1] */) {
   double step2 = 0.0, xn2 = 0.0, mcc = 0.0;
-  for (int i = threadIdx.x; i < pv.C; i += 1024) {
+  for (int i = ibeg + threadIdx.x; i < iend; i += NT) {
     const double* ps = pose + (size_t)i * 8;
     const double* yi = y + (size_t)i * 6;
     const unsigned mask = pv.img_free_mask[i];
@@ -92,14 +95,29 @@ __device__ __forceinline__ void cam_update_body(const ProblemView& pv, const dou
       }
     }
   }
-  step2 = block_sum<32>(step2, sm);
-  xn2 = block_sum<32>(xn2, sm);
-  mcc = block_sum<32>(mcc, sm);
+  step2 = block_sum<NT / 32>(step2, sm);
+  xn2 = block_sum<NT / 32>(xn2, sm);
+  mcc = block_sum<NT / 32>(mcc, sm);
   if (threadIdx.x == 0) {
-    scal[S_STEP2_C] = step2;
-    scal[S_XNORM2_C] = xn2;
-    scal[S_MCC_C] = mcc;
+    out[0] = step2;
+    out[1] = xn2;
+    out[2] = mcc;
   }
 }
+
+// all images by one CTA of 1024 threads, sums straight into the scalar block
+__device__ __forceinline__ void cam_update_body(const ProblemView& pv, const double* __restrict__ pose, const double* y,
+                                                const double* __restrict__ Hc, const double* __restrict__ gc,
+                                                const double* __restrict__ c_img, const LmDiag& lm,
+                                                double* __restrict__ pose_cand, double* scal, double* sm /* [33] */) {
+  __shared__ double s_out[3];
+  cam_update_range<1024>(pv, pose, y, Hc, gc, c_img, lm, pose_cand, 0, pv.C, s_out, sm);
+  if (threadIdx.x == 0) {
+    scal[S_STEP2_C] = s_out[0];
+    scal[S_XNORM2_C] = s_out[1];
+    scal[S_MCC_C] = s_out[2];
+  }
+}
+
 
 }  // namespace mpba
