@@ -662,7 +662,7 @@ class BundleAdjuster:
                 self.buf["cm_pm"] = self.host["cm_pm"].to(self.device, non_blocking=True)
             if pinned:
                 self._pose_host = torch.empty((lay.C, 8), dtype=torch.float64).pin_memory()
-                self._xyz_host = torch.empty((lay.P, 3), dtype=torch.float64).pin_memory()
+                self._xyz_host = torch.empty((lay.P, 4), dtype=torch.float64).pin_memory()
             for name in ("item_a", "item_b", "chunk_img", "chunk_begin", "chunk_end"):
                 if self.buf[name].numel() == 0:
                     self.buf[name] = torch.zeros(1, dtype=torch.int32, device=self.device)
@@ -770,16 +770,21 @@ class BundleAdjuster:
         self.buf["img_pose"].copy_(torch.from_numpy(pose))
         self.buf["pt_xyz"].copy_(torch.from_numpy(xyz))
 
-    def state(self):
-        """(img_q [C,4], img_t [C,3], pt_xyz [P,3]) as numpy (device -> host)."""
+    def state(self, copy: bool = True):
+        """(img_q [C,4], img_t [C,3], pt_xyz [P,3]) as numpy (device -> host).
+
+        ``copy=False`` (adjusters created with ``pinned=True``): the arrays are VIEWS of the adjuster's pinned staging
+        buffers -- one DMA per buffer, no host-side repacking; they stay valid until the next ``state()`` / ``close()``."""
         if self.host:
-            # pinned result buffers: the padded records are packed on the device, one DMA each, and the host
-            # only does contiguous copies out of the staging buffers
+            # pinned result buffers: the device records ([C,8] poses, [P,4] points) cross PCIe as they are, one
+            # contiguous DMA each; the host only slices
             self._pose_host.copy_(self.buf["img_pose"], non_blocking=True)
-            self._xyz_host.copy_(self.buf["pt_xyz"][:, :3], non_blocking=True)
+            self._xyz_host.copy_(self.buf["pt_xyz"], non_blocking=True)
             self.torch.cuda.current_stream().synchronize()
-            pose = self._pose_host.numpy()
-            return pose[:, :4].copy(), pose[:, 4:7].copy(), self._xyz_host.numpy().copy()
+            pose, xyz = self._pose_host.numpy(), self._xyz_host.numpy()
+            if copy:
+                return pose[:, :4].copy(), pose[:, 4:7].copy(), xyz[:, :3].copy()
+            return pose[:, :4], pose[:, 4:7], xyz[:, :3]
         else:
             pose = self.buf["img_pose"].cpu().numpy()
             xyz = self.buf["pt_xyz"].cpu().numpy()
