@@ -666,9 +666,14 @@ class BundleAdjuster:
             for name in ("item_a", "item_b", "chunk_img", "chunk_begin", "chunk_end"):
                 if self.buf[name].numel() == 0:
                     self.buf[name] = torch.zeros(1, dtype=torch.int32, device=self.device)
-            free = _FREE_HANDLES.setdefault(int(device), [])
-            if free and self.shard is None:
+            # handles are pooled per device; sharded ones per (device, world, rank) with their NCCL communicator, so the
+            # hundreds of bundles of a mapper run pay mpba_create / ncclCommInitRank once
+            self._pool_key = int(device) if self.shard is None else (int(device), int(self.shard.world), int(self.shard.rank))
+            free = _FREE_HANDLES.setdefault(self._pool_key, [])
+            self._comm_ready = False
+            if free:
                 self.handle = free.pop()
+                self._comm_ready = self.shard is not None
             else:
                 self.handle = C.c_void_p()
                 rc = self.lib.mpba_create(C.byref(self.handle), device, None)
@@ -689,7 +694,8 @@ class BundleAdjuster:
             self.prob.s_max_row_blocks = int(np.max(np.diff(lay.s_row_ptr))) if lay.C else 0
             nbytes = C.c_size_t()
             if self.shard is not None:
-                self._init_comm()
+                if not self._comm_ready:
+                    self._init_comm()
                 self._check(self.lib.mpba_workspace_bytes_sharded(C.byref(self.prob), C.byref(self.shard), C.byref(nbytes)))
             else:
                 self._check(self.lib.mpba_workspace_bytes(C.byref(self.prob), C.byref(nbytes)))
@@ -726,9 +732,9 @@ class BundleAdjuster:
 
     def close(self):
         if getattr(self, "handle", None) is not None and self.handle.value:
-            free = _FREE_HANDLES.setdefault(int(self.device.index), [])
-            if self.shard is None and len(free) < 4:
-                free.append(self.handle)  # reused by the next BundleAdjuster on this device
+            free = _FREE_HANDLES.setdefault(getattr(self, "_pool_key", int(self.device.index)), [])
+            if len(free) < 4:
+                free.append(self.handle)  # reused by the next BundleAdjuster on this device (and rank of this world)
             else:
                 self.lib.mpba_destroy(self.handle)
             self.handle = C.c_void_p()
