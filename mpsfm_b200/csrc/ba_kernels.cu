@@ -241,7 +241,8 @@ __global__ void __launch_bounds__(1024) k_img_scalars(int C, const uint8_t* __re
 // LM decision by thread 0 (lm_control.cuh) and the condition of the graph's WHILE node.
 __global__ void __launch_bounds__(1024) k_img_tail(ProblemView pv, const double* __restrict__ chunk_part, double* Hc,
                                                    double* gc, double* img_part, double* c_img, int compute_scaling,
-                                                   int jacobi_scaling, double* scal, LmTail tail, int with_tail) {
+                                                   int jacobi_scaling, double* scal, LmTail tail, int with_tail,
+                                                   PtScalarsArgs ps) {
   __shared__ double sm[33];
   for (int gid = threadIdx.x; gid < pv.C * 32; gid += 1024) {
     const int i = gid >> 5, v = gid & 31;
@@ -249,6 +250,32 @@ __global__ void __launch_bounds__(1024) k_img_tail(ProblemView pv, const double*
   }
   __syncthreads();  // Hc / gc / img_part of this CTA are complete and visible to it
   img_scalars_body(pv.C, pv.img_free_mask, img_part, Hc, gc, c_img, compute_scaling, jacobi_scaling, scal, sm);
+  if (ps.nblk >= 0) {
+    // the point scalars of the step (k_pt_scalars_step's work: a few hundred rows at these sizes) and the slice sums of
+    // the camera step ride along: one launch less per LM iteration
+    double a = 0.0, b = 0.0, c = 0.0, gm = 0.0;
+    for (int i = threadIdx.x; i < ps.nblk; i += 1024) {
+      const double4 v = *reinterpret_cast<const double4*>(ps.pt_part + (size_t)i * PT_PART);
+      gm = fmax(gm, v.x);
+      a += v.y; b += v.z; c += v.w;
+    }
+    a = block_sum<32>(a, sm);
+    b = block_sum<32>(b, sm);
+    c = block_sum<32>(c, sm);
+    gm = block_max<32>(gm, sm);
+    if (threadIdx.x == 0) {
+      scal[S_MCC] = a;
+      scal[S_STEP2_P] = b;
+      scal[S_XNORM2_P] = c;
+      if (ps.with_gmax) scal[S_GMAX_P] = gm;
+    }
+    if (threadIdx.x < 3 && ps.cam_rows > 0) {
+      double acc = 0.0;
+      for (int g = 0; g < ps.cam_rows; ++g) acc += ps.cam_stage[3 * g + threadIdx.x];
+      scal[threadIdx.x == 0 ? S_STEP2_C : (threadIdx.x == 1 ? S_XNORM2_C : S_MCC_C)] = acc;
+    }
+    __syncthreads();  // the controller below reads what threads 1 and 2 wrote
+  }
   if (with_tail && threadIdx.x == 0) {
     // scal[S_COST_FREE..S_GMAX_C] were written by this very thread; the rest by earlier kernels
     const bool more = lm_control_step(tail.ld, tail.rows, scal, tail.ctl);
@@ -2166,11 +2193,13 @@ void launch_img_finalize(const ProblemView& pv, const double* chunk_part, double
 }
 void launch_img_tail(const ProblemView& pv, const double* chunk_part, double* Hc, double* gc, double* img_part,
                      double* c_img, int compute_scaling, int jacobi_scaling, double* scal, const LmTail* tail,
-                     cudaStream_t st) {
+                     const PtScalarsArgs* pts, cudaStream_t st) {
   LmTail t = {};
   if (tail) t = *tail;
+  PtScalarsArgs ps = {nullptr, -1, 0, nullptr, 0};
+  if (pts) ps = *pts;
   k_img_tail<<<1, 1024, 0, st>>>(pv, chunk_part, Hc, gc, img_part, c_img, compute_scaling, jacobi_scaling, scal, t,
-                                 tail ? 1 : 0);
+                                 tail ? 1 : 0, ps);
 }
 void launch_img_scalars(const ProblemView& pv, const double* img_part, const double* Hc, const double* gc,
                         double* c_img, int compute_scaling, int jacobi_scaling, double* scal, cudaStream_t st) {

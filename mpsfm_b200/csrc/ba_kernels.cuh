@@ -131,9 +131,19 @@ void launch_img_scalars(const ProblemView& pv, const double* img_part, const dou
 // Small bundles (<= IMG_TAIL_MAX_IMAGES images, single GPU): launch_img_finalize + launch_img_scalars as ONE CTA, same
 // sums in the same order; tail != nullptr appends the LM decision (lm_control.cuh) and sets the WHILE condition.
 constexpr int IMG_TAIL_MAX_IMAGES = 128;
+// pts != nullptr: the reduction of the step's point scalars (launch_pt_scalars_step's work) and of the camera-step
+// slices is done by the same CTA (bundles whose track-order passes have at most IMG_TAIL_MAX_PT_ROWS CTAs)
+struct PtScalarsArgs {
+  const double* pt_part;
+  int nblk;  // < 0: nothing to reduce
+  int with_gmax;
+  const double* cam_stage;
+  int cam_rows;
+};
+constexpr int IMG_TAIL_MAX_PT_ROWS = 8192;
 void launch_img_tail(const ProblemView& pv, const double* chunk_part, double* Hc, double* gc, double* img_part,
                      double* c_img, int compute_scaling, int jacobi_scaling, double* scal, const LmTail* tail,
-                     cudaStream_t st);
+                     const PtScalarsArgs* pts, cudaStream_t st);
 
 // ---- track order: Hpp, gp, point-block Cholesky, Schur factors ------------------------------------
 void launch_points(const ProblemView& pv, const double* pose, const double* X, LmDiag lm, double* c_pt,

@@ -304,6 +304,7 @@ struct Ctx {
   bool want_hinv = false;          // Hpp^-1 rows requested (mpba_point_covariances)
   bool defer_gmax = false;         // LM loop: max |gp| is reduced together with the step scalars (one launch less)
   const LmTail* tail = nullptr;    // device LM loop: the controller rides on the next fused image tail kernel
+  const PtScalarsArgs* tail_pts = nullptr;  // small bundles: the step's point scalars are reduced by that kernel too
   bool tail_done = false;
   bool dense = false;              // reduced system solved directly by one CTA (dense_solve.cu): <= 21 images
   bool device_lm = false;          // LM controller on the device: no memset nodes in the loop body (lm_loop.cu)
@@ -388,7 +389,7 @@ int enqueue_image_pass(Ctx& c, const double* pose, const double* X, int k, int c
     // small bundle: finalize + scalars (+ the LM decision of the device loop) in one single-CTA kernel
     Timer t(h, KS_IMG_FINALIZE, 1);
     launch_img_tail(c.pv, c.w.chunk_part, c.w.Hc[k], c.w.gc[k], c.w.ip[k], c.w.c_img, compute_scaling, jacobi,
-                    c.w.scal, c.tail, h->stream);
+                    c.w.scal, c.tail, c.tail_pts, h->stream);
     if (c.tail) c.tail_done = true;
     return MPBA_OK;
   } else {
@@ -808,7 +809,10 @@ int enqueue_lm_iteration(Ctx& c, int cur, int cand, LmDiag lm, int compute_scali
     launch_back_substitute(c.pv, c.w.X[cur], c.w.y, c.w.Hpp, c.w.gp, c.w.Linv, c.w.c_pt, c.w.fac,
                            c.structure_only ? 0 : 1, lm, c.w.X[cand], c.w.pt_part, c.dense ? nullptr : &cam, h->stream);
   }
-  {
+  // small bundles: the fused image tail of the candidate pass reduces the point scalars as well
+  const bool pts_in_tail = !c.sh && c.pv.C <= IMG_TAIL_MAX_IMAGES && c.nblk <= IMG_TAIL_MAX_PT_ROWS;
+  PtScalarsArgs pts = {c.w.pt_part, (int)c.nblk, c.defer_gmax ? 1 : 0, c.w.cam_stage, cam_rows};
+  if (!pts_in_tail) {
     Timer t(h, KS_REDUCE);
     launch_pt_scalars_step(c.w.pt_part, c.nblk, c.w.scal, c.defer_gmax ? 1 : 0, c.w.pts_stage, c.w.cam_stage, cam_rows,
                            h->stream);
@@ -820,7 +824,9 @@ int enqueue_lm_iteration(Ctx& c, int cur, int cand, LmDiag lm, int compute_scali
     NC(nccl_api().AllGather(c.w.X[cand] + (size_t)c.sh->rank * cnt, c.w.X[cand], cnt, ncclDouble, h->comm, h->stream));
   }
   // cost (and, in case the step is accepted, Hcc / gc) at the candidate
+  c.tail_pts = pts_in_tail ? &pts : nullptr;
   rc = enqueue_image_pass(c, c.w.pose[cand], c.w.X[cand], cand, 0, opt.jacobi_scaling);
+  c.tail_pts = nullptr;
   if (rc) return rc;
   return combine_scalars(c);
 }

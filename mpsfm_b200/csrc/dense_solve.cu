@@ -58,8 +58,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {  // 
   } while (!done);
 }
 
-template <int DS_Q>
-__global__ void __launch_bounds__(1024) k_dense_solve(int C, const int32_t* __restrict__ row_ptr,
+// NW warps; thread (warp w, lane l) owns the entries (w + NW qi, l + 32 qj), qi < RQ, qj < CQ.  Systems up to 63 unknowns
+// (10 images: the reference's local bundles) run on 8 warps -- 8 x 2 slots per thread, a quarter of the shuffles and
+// shared-memory traffic per pivot of the 32-warp tile; larger ones on 32 warps with a 3 x 3 or 4 x 4 tile.
+template <int NW, int RQ, int CQ>
+__global__ void __launch_bounds__(32 * NW) k_dense_solve(int C, const int32_t* __restrict__ row_ptr,
                                                       const int32_t* __restrict__ col, const double* __restrict__ S,
                                                       const double* __restrict__ rhs, double* y,
                                                       double* scal, CamStep cs) {
@@ -68,23 +71,23 @@ __global__ void __launch_bounds__(1024) k_dense_solve(int C, const int32_t* __re
   __shared__ double s_inv[DS_DIM];
   __shared__ uint64_t s_bar[DS_DIM];  // one mbarrier per pivot: 32 arrivals = the owner warp has published the row
   __shared__ double xs[DS_DIM], rs[DS_DIM];
-  constexpr int W = 32 * DS_Q;
+  constexpr int W = 32 * CQ, NT = 32 * NW;
   __shared__ int s_bad;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n = 6 * C;  // column n carries the right-hand side
-  for (int k = tid; k < C * C; k += 1024) tbl[k] = -1;
+  for (int k = tid; k < C * C; k += NT) tbl[k] = -1;
   if (tid < n) mbar_init(&s_bar[tid], 32);
   if (tid == 0) s_bad = 0;
   __syncthreads();
-  for (int i = tid; i < C; i += 1024)
+  for (int i = tid; i < C; i += NT)
     for (int b = row_ptr[i]; b < row_ptr[i + 1]; ++b) tbl[i * C + col[b]] = b;
   __syncthreads();
-  double a[DS_Q][DS_Q];
+  double a[RQ][CQ];
 #pragma unroll
-  for (int qi = 0; qi < DS_Q; ++qi)
+  for (int qi = 0; qi < RQ; ++qi)
 #pragma unroll
-    for (int qj = 0; qj < DS_Q; ++qj) {
-      const int i = warp + 32 * qi, j = lane + 32 * qj;
+    for (int qj = 0; qj < CQ; ++qj) {
+      const int i = warp + NW * qi, j = lane + 32 * qj;
       double v = 0.0;
       if (i < n && j < n) {
         const int b = tbl[(i / 6) * C + j / 6];
@@ -95,53 +98,67 @@ __global__ void __launch_bounds__(1024) k_dense_solve(int C, const int32_t* __re
       a[qi][qj] = v;
     }
 #pragma unroll
-  for (int PQ = 0; PQ < DS_Q; ++PQ) {  // pivots in chunks of 32: the register slot of the pivot row / column is static
-    for (int pw = 0; pw < 32; ++pw) {
-      const int p = 32 * PQ + pw;
+  for (int PQ = 0; PQ < RQ; ++PQ) {  // pivots in chunks of NW: the register slots of the pivot row / column are static
+    constexpr int dummy = 0;
+    (void)dummy;
+    const int CS = (NW * PQ) >> 5;  // column slot of the chunk's pivots (NW divides 32: one slot per chunk)
+    for (int pw = 0; pw < NW; ++pw) {
+      const int p = NW * PQ + pw;
       if (p >= n) break;
+      const int lp = p & 31;  // lane holding column p
       double* pr = prow + (size_t)p * W;
       if (warp == pw) {  // owner of row p: scale and publish it
-        const double piv = __shfl_sync(FULLMASK, a[PQ][PQ], pw);
+        double piv = 0.0;
+#pragma unroll
+        for (int qj = 0; qj < CQ; ++qj)
+          if (qj == CS) piv = __shfl_sync(FULLMASK, a[PQ][qj], lp);
         const bool ok = piv > 0.0 && isfinite(piv);
         const double inv = ok ? ds_rcp(piv) : 0.0;
 #pragma unroll
-        for (int qj = 0; qj < DS_Q; ++qj) pr[lane + 32 * qj] = a[PQ][qj] * inv;
+        for (int qj = 0; qj < CQ; ++qj) pr[lane + 32 * qj] = a[PQ][qj] * inv;
         if (lane == 0) {
           s_inv[p] = inv;
           if (!ok) s_bad = 1;  // not positive definite: the LM loop treats the step as invalid
         }
         mbar_arrive(&s_bar[p]);  // every lane releases its own part of the row
       }
-      double f[DS_Q];
+      double f[RQ];
 #pragma unroll
-      for (int qi = 0; qi < DS_Q; ++qi) f[qi] = __shfl_sync(FULLMASK, a[qi][PQ], pw);  // column p of my rows
+      for (int qi = 0; qi < RQ; ++qi) {
+        f[qi] = 0.0;
+#pragma unroll
+        for (int qj = 0; qj < CQ; ++qj)
+          if (qj == CS) f[qi] = __shfl_sync(FULLMASK, a[qi][qj], lp);  // column p of my rows
+      }
       if (warp == pw) f[PQ] = 0.0;  // row p itself is replaced below
       mbar_wait(&s_bar[p], 0);
       const double inv = s_inv[p];
-      double rp[DS_Q];
+      double rp[CQ];
 #pragma unroll
-      for (int qj = 0; qj < DS_Q; ++qj) rp[qj] = pr[lane + 32 * qj];
+      for (int qj = 0; qj < CQ; ++qj) rp[qj] = pr[lane + 32 * qj];
 #pragma unroll
-      for (int qi = 0; qi < DS_Q; ++qi)
+      for (int qi = 0; qi < RQ; ++qi)
 #pragma unroll
-        for (int qj = 0; qj < DS_Q; ++qj) a[qi][qj] -= f[qi] * rp[qj];
-      if (lane == pw) {  // column p of the inverse: -f / pivot
+        for (int qj = 0; qj < CQ; ++qj) a[qi][qj] -= f[qi] * rp[qj];
+      if (lane == lp) {  // column p of the inverse: -f / pivot
 #pragma unroll
-        for (int qi = 0; qi < DS_Q; ++qi) a[qi][PQ] = -f[qi] * inv;
+        for (int qi = 0; qi < RQ; ++qi)
+#pragma unroll
+          for (int qj = 0; qj < CQ; ++qj)
+            if (qj == CS) a[qi][qj] = -f[qi] * inv;
       }
       if (warp == pw) {  // row p: the scaled pivot row, 1 / pivot on the diagonal
 #pragma unroll
-        for (int qj = 0; qj < DS_Q; ++qj) a[PQ][qj] = rp[qj];
-        if (lane == pw) a[PQ][PQ] = inv;
+        for (int qj = 0; qj < CQ; ++qj) a[PQ][qj] = (qj == CS && lane == lp) ? inv : rp[qj];
       }
     }
   }
   // solution column -> shared memory
 #pragma unroll
-  for (int qi = 0; qi < DS_Q; ++qi)
+  for (int qi = 0; qi < RQ; ++qi)
 #pragma unroll
-    for (int qj = 0; qj < DS_Q; ++qj) {
-      const int i = warp + 32 * qi, j = lane + 32 * qj;
+    for (int qj = 0; qj < CQ; ++qj) {
+      const int i = warp + NW * qi, j = lane + 32 * qj;
       if (i < n && j == n) xs[i] = a[qi][qj];
     }
   __syncthreads();
@@ -159,11 +176,11 @@ __global__ void __launch_bounds__(1024) k_dense_solve(int C, const int32_t* __re
   }
   __syncthreads();
 #pragma unroll
-  for (int qi = 0; qi < DS_Q; ++qi) {
-    const int i = warp + 32 * qi;
+  for (int qi = 0; qi < RQ; ++qi) {
+    const int i = warp + NW * qi;
     double acc = 0.0;
 #pragma unroll
-    for (int qj = 0; qj < DS_Q; ++qj) {
+    for (int qj = 0; qj < CQ; ++qj) {
       const int j = lane + 32 * qj;
       if (j < n) acc += a[qi][qj] * rs[j];
     }
@@ -187,10 +204,16 @@ __global__ void __launch_bounds__(1024) k_dense_solve(int C, const int32_t* __re
     }
   }
   if (cs.pose_cand != nullptr) {
-    __shared__ double sm[33];
+    __shared__ double sm[NW + 1];
+    __shared__ double s_out[3];
     __syncthreads();  // y of this CTA is complete and visible to it
     lm_resolve(cs.lm);
-    cam_update_body(cs.pv, cs.pose, y, cs.Hc, cs.gc, cs.c_img, cs.lm, cs.pose_cand, scal, sm);
+    cam_update_range<NT>(cs.pv, cs.pose, y, cs.Hc, cs.gc, cs.c_img, cs.lm, cs.pose_cand, 0, cs.pv.C, s_out, sm);
+    if (tid == 0) {
+      scal[S_STEP2_C] = s_out[0];
+      scal[S_XNORM2_C] = s_out[1];
+      scal[S_MCC_C] = s_out[2];
+    }
   }
 }
 
@@ -208,20 +231,23 @@ cudaError_t launch_dense_solve(int C, const int32_t* row_ptr, const int32_t* col
     cs.lm = lm;
     cs.pose_cand = pose_cand;
   }
-  const int nq = (6 * C + 1 + 31) / 32;
-  const size_t smem = (size_t)6 * C * 32 * nq * sizeof(double);  // <= 126 rows of 128 doubles: 126 KB
+  const int cols = 6 * C + 1;  // unknowns + the right-hand side
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(k_dense_solve<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 96 * 8);
-    cudaFuncSetAttribute(k_dense_solve<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 128 * 8);
+    cudaFuncSetAttribute(k_dense_solve<32, 3, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 96 * 8);
+    cudaFuncSetAttribute(k_dense_solve<32, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 128 * 8);
     attr_set = true;
   }
-  switch (nq) {
-    case 1: k_dense_solve<1><<<1, 1024, smem, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
-    case 2: k_dense_solve<2><<<1, 1024, smem, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
-    case 3: k_dense_solve<3><<<1, 1024, smem, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
-    default: k_dense_solve<4><<<1, 1024, smem, st>>>(C, row_ptr, col, S, rhs, y, scal, cs); break;
-  }
+  const int cq = (cols + 31) / 32;
+  const size_t smem = (size_t)6 * C * 32 * cq * sizeof(double);  // one published row per pivot: <= 126 x 128 doubles
+  if (cols <= 32)
+    k_dense_solve<8, 4, 1><<<1, 256, smem, st>>>(C, row_ptr, col, S, rhs, y, scal, cs);
+  else if (cols <= 64)
+    k_dense_solve<8, 8, 2><<<1, 256, smem, st>>>(C, row_ptr, col, S, rhs, y, scal, cs);
+  else if (cols <= 96)
+    k_dense_solve<32, 3, 3><<<1, 1024, smem, st>>>(C, row_ptr, col, S, rhs, y, scal, cs);
+  else
+    k_dense_solve<32, 4, 4><<<1, 1024, smem, st>>>(C, row_ptr, col, S, rhs, y, scal, cs);
   return cudaGetLastError();
 }
 
