@@ -396,6 +396,21 @@ int mpba_segmented_median(mpba_handle* h, int32_t n, const double* values, int32
                           const int32_t* seg_ptr, void* workspace, size_t workspace_bytes, double* out_median,
                           double* out_mad, void* cuda_stream);
 
+/* The same select WITHOUT a caller workspace and without any allocation (no cudaMalloc / cudaFree, no allocating
+ * library routine): its scratch is a file-scope `static __device__` array of the library.  No counterpart in the
+ * reference: added for callers that cannot allocate (CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  Limits: n <= MPBA_MEDIAN_STATIC_MAX_VALUES and num_segments <=
+ * MPBA_MEDIAN_STATIC_MAX_SEGMENTS, beyond them MPBA_E_WORKSPACE with a message (mpba_last_error when h != NULL; h may
+ * be NULL).  The array (about 2.6 MB) exists on every GPU that loads the library until the process exits; its device
+ * address is looked up once per device (the device CURRENT at the call) with cudaGetSymbolAddress.  Every call shares
+ * the array, which keeps the previous call's contents (what must start at zero is cleared by the call): calls that
+ * overlap on the GPU -- two streams, two host threads -- race on it and must be serialised by the caller.  Same
+ * results, bit for bit, and same completion contract as mpba_segmented_median. */
+#define MPBA_MEDIAN_STATIC_MAX_VALUES 262144
+#define MPBA_MEDIAN_STATIC_MAX_SEGMENTS 256
+int mpba_segmented_median_static(mpba_handle* h, int32_t n, const double* values, int32_t num_segments,
+                                 const int32_t* seg_ptr, double* out_median, double* out_mad, void* cuda_stream);
+
 
 /* ---- depth-map integration with normal priors ------------------------------------------------
  * The step right before every bundle adjustment in the reference (mpsfm/sfm/mapper/base.py:637-644 integrate_bundle

@@ -11,6 +11,9 @@
 #include <math.h>
 #include <stdint.h>
 
+#include <mutex>
+#include <string>
+
 #include "../../include/mpba.h"
 
 namespace {
@@ -366,5 +369,100 @@ extern "C" int mpba_segmented_median(mpba_handle* h, int32_t n, const double* va
   }
   if (cudaGetLastError() != cudaSuccess) return MPBA_E_CUDA;
   if (cudaStreamSynchronize(st) != cudaSuccess) return MPBA_E_CUDA;
+  return MPBA_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// mpba_segmented_median_static: the same select with its scratch in a file-scope device array -- for callers
+// that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in
+// the reference.
+//   * g_sel_static is a module-lifetime allocation of MPBA_MEDIAN_STATIC_BYTES (~2.6 MB) on EVERY GPU that loads the
+//     library, held until the process exits;
+//   * in host code the NAME g_sel_static is a host-side stand-in, not a device address: the device address is taken
+//     once per device, with that device current, by cudaGetSymbolAddress and cached (sel_static_base);
+//   * all calls share the array and it keeps the previous call's contents: k_sel_init clears everything that must
+//     start at zero (segment states, histograms), |x - median| is fully rewritten before it is read.  Calls that
+//     overlap on the GPU (two streams, two host threads) RACE on it: serialise them.
+// ------------------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr size_t sel_align256(size_t x) { return (x + 255) & ~(size_t)255; }
+constexpr size_t SEL_STATIC_BYTES =
+    sel_align256(sizeof(int32_t) * ((size_t)MPBA_MEDIAN_STATIC_MAX_SEGMENTS + 1)) +
+    sel_align256(sizeof(uint32_t) * 512 * (size_t)MPBA_MEDIAN_STATIC_MAX_SEGMENTS) +
+    sel_align256(sizeof(SelState) * (size_t)MPBA_MEDIAN_STATIC_MAX_SEGMENTS) +
+    sel_align256(sizeof(double) * (size_t)MPBA_MEDIAN_STATIC_MAX_VALUES);
+
+static __device__ __align__(256) unsigned char g_sel_static[SEL_STATIC_BYTES];
+
+constexpr int SEL_STATIC_MAX_DEVICES = 64;
+std::mutex g_sel_static_mutex;
+void* g_sel_static_addr[SEL_STATIC_MAX_DEVICES] = {nullptr};
+
+// device address of g_sel_static on the CURRENT device (looked up once per device); nullptr + *err on failure
+void* sel_static_base(cudaError_t* err) {
+  int dev = -1;
+  *err = cudaGetDevice(&dev);
+  if (*err != cudaSuccess) return nullptr;
+  if (dev < 0 || dev >= SEL_STATIC_MAX_DEVICES) {
+    *err = cudaErrorInvalidDevice;
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(g_sel_static_mutex);
+  if (g_sel_static_addr[dev] == nullptr) {
+    void* ptr = nullptr;
+    *err = cudaGetSymbolAddress(&ptr, g_sel_static);
+    if (*err != cudaSuccess || ptr == nullptr) {
+      if (*err == cudaSuccess) *err = cudaErrorInvalidSymbol;
+      return nullptr;
+    }
+    g_sel_static_addr[dev] = ptr;
+  }
+  return g_sel_static_addr[dev];
+}
+
+}  // namespace
+
+namespace mpba {
+int handle_fail(mpba_handle* h, int code, const std::string& msg);  // ba_solver.cu: records the message (h may be NULL)
+}
+
+extern "C" int mpba_segmented_median_static(mpba_handle* h, int32_t n, const double* values, int32_t num_segments,
+                                            const int32_t* seg_ptr, double* out_median, double* out_mad,
+                                            void* cuda_stream) {
+  if (n < 0 || num_segments < 0) return mpba::handle_fail(h, MPBA_E_INVALID, "segmented_median_static: negative size");
+  if (n > MPBA_MEDIAN_STATIC_MAX_VALUES || num_segments > MPBA_MEDIAN_STATIC_MAX_SEGMENTS)
+    return mpba::handle_fail(h, MPBA_E_WORKSPACE,
+                             "segmented_median_static: " + std::to_string(n) + " values / " +
+                                 std::to_string(num_segments) + " segments exceed the static scratch (at most " +
+                                 std::to_string(MPBA_MEDIAN_STATIC_MAX_VALUES) + " values, " +
+                                 std::to_string(MPBA_MEDIAN_STATIC_MAX_SEGMENTS) +
+                                 " segments): use mpba_segmented_median with a caller-owned workspace");
+  if (num_segments == 0) return MPBA_OK;
+  if (!seg_ptr || !out_median || (n > 0 && !values))
+    return mpba::handle_fail(h, MPBA_E_INVALID, "segmented_median_static: NULL array");
+  cudaError_t ce = cudaSuccess;
+  void* base = sel_static_base(&ce);
+  if (base == nullptr)
+    return mpba::handle_fail(h, MPBA_E_CUDA, std::string("segmented_median_static: cudaGetSymbolAddress: ") +
+                                                 cudaGetErrorString(ce));
+  const int S = num_segments;
+  size_t need = 0;
+  // carved for the MAXIMUM sizes, so that the layout (and the address of every part) never depends on the call
+  SelWork W = carve_sel(base, MPBA_MEDIAN_STATIC_MAX_VALUES, MPBA_MEDIAN_STATIC_MAX_SEGMENTS, &need);
+  if (need > SEL_STATIC_BYTES) return mpba::handle_fail(h, MPBA_E_WORKSPACE, "segmented_median_static: scratch layout");
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  k_sel_init<<<1, 1024, 0, st>>>(S, seg_ptr, W);  // clears the states and histograms of the S segments in use
+  if (run_select(n, S, seg_ptr, values, W, st) != MPBA_OK) return mpba::handle_fail(h, MPBA_E_CUDA, "segmented_median_static: launch");
+  k_sel_finish<<<(S + 255) / 256, 256, 0, st>>>(S, seg_ptr, W, out_median);
+  if (out_mad) {
+    k_abs_dev<<<n / SEL_CHUNK + S + 1, SEL_THREADS, 0, st>>>(S, seg_ptr, values, out_median, W);
+    if (run_select(n, S, seg_ptr, W.dev, W, st) != MPBA_OK) return mpba::handle_fail(h, MPBA_E_CUDA, "segmented_median_static: launch");
+    k_sel_finish<<<(S + 255) / 256, 256, 0, st>>>(S, seg_ptr, W, out_mad);
+  }
+  ce = cudaGetLastError();
+  if (ce != cudaSuccess) return mpba::handle_fail(h, MPBA_E_CUDA, std::string("segmented_median_static: ") + cudaGetErrorString(ce));
+  ce = cudaStreamSynchronize(st);  // same contract as mpba_segmented_median: returns after the stream completed
+  if (ce != cudaSuccess) return mpba::handle_fail(h, MPBA_E_CUDA, std::string("segmented_median_static: ") + cudaGetErrorString(ce));
   return MPBA_OK;
 }

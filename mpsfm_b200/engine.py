@@ -128,7 +128,7 @@ EXPORTS = (
     "mpba_workspace_bytes", "mpba_evaluate", "mpba_linearize", "mpba_reduced_system", "mpba_solve",
     "mpba_kernel_times", "mpba_kernel_name", "mpba_point_covariances", "mpba_filter_tracks",
     "mpba_pack_tracks", "mpba_sample_maps", "mpba_depth_prior_terms", "mpba_segmented_median_workspace_bytes",
-    "mpba_segmented_median", "mpba_gather_observations", "mpba_host_layout_create", "mpba_host_layout_destroy",
+    "mpba_segmented_median", "mpba_segmented_median_static", "mpba_gather_observations", "mpba_host_layout_create", "mpba_host_layout_destroy",
     "mpba_host_gather", "mpba_comm_unique_id", "mpba_comm_init", "mpba_workspace_bytes_sharded", "mpba_solve_sharded",
     "mpba_integration_default_conf", "mpba_integration_workspace_bytes", "mpba_integrate_depth",
     "mpba_integration_variances",
@@ -171,6 +171,8 @@ def load_library(path: Optional[str] = None):
                                            C.c_void_p, C.c_double, C.c_int32, C.c_double, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.mpba_segmented_median_workspace_bytes.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_size_t)]
+    lib.mpba_segmented_median_static.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                                 C.c_void_p, C.c_void_p]
     lib.mpba_segmented_median.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t,
                                           C.c_void_p, C.c_void_p, C.c_void_p]
     lib.mpba_host_layout_create.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
