@@ -2256,6 +2256,24 @@ void launch_schur_finish(const ProblemView& pv, const double* Hc, const double* 
 void launch_combine_scalars(const double* scal_all, int world, double* scal, cudaStream_t st) {
   k_combine_scalars<<<1, 32, 0, st>>>(scal_all, world, scal);
 }
+namespace {
+__global__ void __launch_bounds__(1024) k_plan_hash(const int32_t* __restrict__ region, size_t n, unsigned long long* out) {
+  __shared__ unsigned long long sm[32];
+  unsigned long long acc = 0;
+  for (size_t i = threadIdx.x; i < n; i += 1024) acc += plan_hash_term(__ldcg(region + i), i);
+  for (int off = 16; off > 0; off >>= 1) acc += __shfl_down_sync(FULL, acc, off);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    acc = sm[threadIdx.x];
+    for (int off = 16; off > 0; off >>= 1) acc += __shfl_down_sync(FULL, acc, off);
+    if (threadIdx.x == 0) *out = acc;
+  }
+}
+}  // namespace
+void launch_plan_hash(const int32_t* region, size_t n, unsigned long long* out, cudaStream_t st) {
+  k_plan_hash<<<1, 1024, 0, st>>>(region, n, out);
+}
 void launch_block_inverse(const ProblemView& pv, const double* S, double* Minv, cudaStream_t st) {
   k_block_inverse<<<(pv.C + 127) / 128, 128, 0, st>>>(pv, S, Minv);
 }

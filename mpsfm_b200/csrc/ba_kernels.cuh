@@ -252,6 +252,15 @@ cudaError_t launch_coarse_setup(const CoarsePlan& cp, int C, const double* pose,
 // the gauge modes alone (Z of every image at the given poses)
 cudaError_t launch_coarse_modes(int C, const double* pose, const uint8_t* free_mask, double* Zc, cudaStream_t st);
 
+// ---- hash of the plan region (ba_solver.cu: upload_plan): order-independent sum of mixed (value, index) words
+MPBA_HD unsigned long long plan_hash_term(int32_t x, unsigned long long i) {
+  unsigned long long z = (((unsigned long long)(uint32_t)x << 32) | (i & 0xffffffffull)) + 0x9E3779B97F4A7C15ull * (i + 1);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+void launch_plan_hash(const int32_t* region, size_t n, unsigned long long* out, cudaStream_t st);
+
 // ---- dense direct solve of a small reduced camera system (dense_solve.cu) ----------------------------
 constexpr int DENSE_SOLVE_MAX_IMAGES = 21;  // 6 * 21 unknowns + the right-hand side = 127 columns of the register tile
 bool dense_solve_fits(int num_images);
