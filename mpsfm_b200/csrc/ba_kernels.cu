@@ -990,60 +990,48 @@ __global__ void __launch_bounds__(1024) k_pt_scalars_gmax(const double* __restri
 // ================================================================================================
 // reduced camera system
 // ================================================================================================
-// Inverse of one 6x6 SPD block through its Cholesky factor (identity if it is not positive definite).  Every loop is
-// unrolled: the two 36-entry work arrays live in registers (with run-time loop bounds they sat in local memory and
-// k_block_inverse took 17 us for ANY number of images -- one thread's dependent chain through L1).
-__device__ __forceinline__ void block_inverse6(const double* src, double* __restrict__ dst) {
-  double A[36], Li[36];
-#pragma unroll
-  for (int k = 0; k < 36; ++k) A[k] = src[k];
+// Inverse of the SPD 6x6 block in Mm (shared memory, 36 doubles; destroyed) by ONE warp: Gauss-Jordan on [M | N], N (36
+// doubles of shared memory) starting as the identity; lane = entries lane and lane + 32, six steps of ~100 cycles.
+// The symmetrised result goes to dst; a pivot that is not positive (block not positive definite) makes it the identity.
+__device__ __forceinline__ void warp_inverse6(double* Mm, double* Nn, int lane, double* __restrict__ dst) {
   bool ok = true;
-  // in-place Cholesky, lower
 #pragma unroll
-  for (int j = 0; j < 6; ++j) {
-    double d = A[7 * j];
+  for (int p = 0; p < 6; ++p) {
+    const double piv = Mm[7 * p];
+    ok = ok && (piv > 0.0);
+    const double inv = 1.0 / (ok ? piv : 1.0);
+    double m2[2], n2[2];
 #pragma unroll
-    for (int k = 0; k < j; ++k) d -= A[6 * j + k] * A[6 * j + k];
-    ok = ok && (d > 0.0);
-    d = sqrt(ok ? d : 1.0);
-    A[7 * j] = d;
+    for (int h = 0; h < 2; ++h) {
+      const int e = lane + 32 * h;
+      m2[h] = 0.0; n2[h] = 0.0;
+      if (e < 36) {
+        const int r = e / 6, c = e % 6;
+        const double f = Mm[6 * r + p];
+        const double mp = Mm[6 * p + c] * inv, np_ = Nn[6 * p + c] * inv;
+        m2[h] = (r == p) ? mp : Mm[e] - f * mp;
+        n2[h] = (r == p) ? np_ : Nn[e] - f * np_;
+      }
+    }
+    __syncwarp();
 #pragma unroll
-    for (int r = j + 1; r < 6; ++r) {
-      double s = A[6 * r + j];
+    for (int h = 0; h < 2; ++h) {
+      const int e = lane + 32 * h;
+      if (e < 36) {
+        Mm[e] = m2[h];
+        Nn[e] = n2[h];
+      }
+    }
+    __syncwarp();
+  }
 #pragma unroll
-      for (int k = 0; k < j; ++k) s -= A[6 * r + k] * A[6 * j + k];
-      A[6 * r + j] = s / d;
+  for (int h = 0; h < 2; ++h) {
+    const int e = lane + 32 * h;
+    if (e < 36) {
+      const int r = e / 6, c = e % 6;
+      dst[e] = ok ? 0.5 * (Nn[6 * r + c] + Nn[6 * c + r]) : ((r == c) ? 1.0 : 0.0);
     }
   }
-  if (!ok) {
-#pragma unroll
-    for (int k = 0; k < 36; ++k) dst[k] = (k % 7 == 0) ? 1.0 : 0.0;
-    return;
-  }
-  // Li = L^-1 (lower)
-#pragma unroll
-  for (int k = 0; k < 36; ++k) Li[k] = 0.0;
-#pragma unroll
-  for (int c = 0; c < 6; ++c) {
-    Li[7 * c] = 1.0 / A[7 * c];
-#pragma unroll
-    for (int r = c + 1; r < 6; ++r) {
-      double s = 0.0;
-#pragma unroll
-      for (int k = c; k < r; ++k) s -= A[6 * r + k] * Li[6 * k + c];
-      Li[6 * r + c] = s / A[7 * r];
-    }
-  }
-  // A^-1 = Li^T Li
-#pragma unroll
-  for (int r = 0; r < 6; ++r)
-#pragma unroll
-    for (int c = 0; c < 6; ++c) {
-      double s = 0.0;
-#pragma unroll
-      for (int k = (r > c ? r : c); k < 6; ++k) s += Li[6 * k + r] * Li[6 * k + c];
-      dst[6 * r + c] = s;
-    }
 }
 
 constexpr int SB_THREADS = 128;
@@ -1299,47 +1287,7 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
       Nn[threadIdx.x] = (threadIdx.x % 7 == 0) ? 1.0 : 0.0;
     }
     __syncthreads();
-    if (warp == 0) {
-      bool ok = true;
-#pragma unroll
-      for (int p = 0; p < 6; ++p) {
-        const double piv = Mm[7 * p];
-        ok = ok && (piv > 0.0);
-        const double inv = 1.0 / (ok ? piv : 1.0);
-        double m2[2], n2[2];
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const int e = lane + 32 * h;
-          m2[h] = 0.0; n2[h] = 0.0;
-          if (e < 36) {
-            const int r = e / 6, c = e % 6;
-            const double f = Mm[6 * r + p];
-            const double mp = Mm[6 * p + c] * inv, np_ = Nn[6 * p + c] * inv;
-            m2[h] = (r == p) ? mp : Mm[e] - f * mp;
-            n2[h] = (r == p) ? np_ : Nn[e] - f * np_;
-          }
-        }
-        __syncwarp();
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const int e = lane + 32 * h;
-          if (e < 36) {
-            Mm[e] = m2[h];
-            Nn[e] = n2[h];
-          }
-        }
-        __syncwarp();
-      }
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int e = lane + 32 * h;
-        if (e < 36) {
-          const int r = e / 6, c = e % 6;
-          // symmetrised; identity when a pivot failed
-          Minv[(size_t)i * 36 + e] = ok ? 0.5 * (Nn[6 * r + c] + Nn[6 * c + r]) : ((r == c) ? 1.0 : 0.0);
-        }
-      }
-    }
+    if (warp == 0) warp_inverse6(Mm, Nn, lane, Minv + (size_t)i * 36);
   }
 }
 
@@ -1347,7 +1295,9 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
 // on fixed tangent coordinates.  One thread per entry of a diagonal block (+ 6 for rhs).
 __global__ void __launch_bounds__(64) k_schur_finish(ProblemView pv, const double* __restrict__ Hc,
                                                      const double* __restrict__ gc, const double* __restrict__ c_img,
-                                                     LmDiag lm, double* __restrict__ S, double* __restrict__ rhs) {
+                                                     LmDiag lm, double* __restrict__ S, double* __restrict__ rhs,
+                                                     double* __restrict__ Minv) {
+  __shared__ double Mm[36], Nn[36];
   lm_resolve(lm);
   const int i = blockIdx.x;
   const unsigned mi = pv.img_free_mask[i];
@@ -1364,10 +1314,15 @@ __global__ void __launch_bounds__(64) k_schur_finish(ProblemView pv, const doubl
       val = (r == c) ? 1.0 : 0.0;
     }
     S[(size_t)blk * 36 + e] = val;
+    Mm[e] = val;
+    Nn[e] = (r == c) ? 1.0 : 0.0;
   } else if (threadIdx.x < 42) {
     const int r = threadIdx.x - 36;
     rhs[(size_t)i * 6 + r] = ((mi >> r) & 1u) ? gc[(size_t)i * 6 + r] + rhs[(size_t)i * 6 + r] : 0.0;
   }
+  __syncthreads();
+  // block-Jacobi inverse of the completed diagonal block (the single-GPU solve does this in k_schur_blocks)
+  if (threadIdx.x < 32 && Minv != nullptr) warp_inverse6(Mm, Nn, threadIdx.x, Minv + (size_t)i * 36);
 }
 
 // Per-rank scalar blocks, all-gathered -> one block, identical on every rank (fixed rank order).
@@ -1384,15 +1339,6 @@ __global__ void k_combine_scalars(const double* __restrict__ scal_all, int world
     v = is_sum ? v + x : fmax(v, x);
   }
   scal[k] = v;
-}
-
-// block-Jacobi preconditioner of a sharded solve (the diagonal blocks are complete only after the all-reduce); the
-// single-GPU solve inverts every diagonal block in the CTA of k_schur_blocks that wrote it.
-__global__ void __launch_bounds__(128) k_block_inverse(ProblemView pv, const double* __restrict__ S,
-                                                       double* __restrict__ Minv) {
-  const int i = blockIdx.x * 128 + threadIdx.x;
-  if (i >= pv.C) return;
-  block_inverse6(S + (size_t)pv.s_diag[i] * 36, Minv + (size_t)i * 36);
 }
 
 // ---- persistent cooperative PCG on the block-CSR reduced camera system --------------------------
@@ -2250,8 +2196,8 @@ void launch_schur_blocks(const ProblemView& pv, const double* fac, const double*
   k_schur_blocks<<<pv.U, SB_THREADS, SB_STAGE_BYTES, st>>>(pv, fac, Hc, gc, c_img, lm, S, rhs, partial, Minv);
 }
 void launch_schur_finish(const ProblemView& pv, const double* Hc, const double* gc, const double* c_img, LmDiag lm,
-                         double* S, double* rhs, cudaStream_t st) {
-  k_schur_finish<<<pv.C, 64, 0, st>>>(pv, Hc, gc, c_img, lm, S, rhs);
+                         double* S, double* rhs, double* Minv, cudaStream_t st) {
+  k_schur_finish<<<pv.C, 64, 0, st>>>(pv, Hc, gc, c_img, lm, S, rhs, Minv);
 }
 void launch_combine_scalars(const double* scal_all, int world, double* scal, cudaStream_t st) {
   k_combine_scalars<<<1, 32, 0, st>>>(scal_all, world, scal);
@@ -2273,9 +2219,6 @@ __global__ void __launch_bounds__(1024) k_plan_hash(const int32_t* __restrict__ 
 }  // namespace
 void launch_plan_hash(const int32_t* region, size_t n, unsigned long long* out, cudaStream_t st) {
   k_plan_hash<<<1, 1024, 0, st>>>(region, n, out);
-}
-void launch_block_inverse(const ProblemView& pv, const double* S, double* Minv, cudaStream_t st) {
-  k_block_inverse<<<(pv.C + 127) / 128, 128, 0, st>>>(pv, S, Minv);
 }
 PcgPlan pcg_plan(int device, int C, int max_row_blocks) {
   static int sms = 0, smem_optin = 0;

@@ -161,10 +161,9 @@ void launch_schur_blocks(const ProblemView& pv, const double* fac, const double*
                          const double* c_img, LmDiag lm, double* S, double* rhs, int partial, double* Minv,
                          cudaStream_t st);  // Minv != nullptr (and !partial): block-Jacobi inverses written by the diagonal CTAs
 void launch_schur_finish(const ProblemView& pv, const double* Hc, const double* gc, const double* c_img, LmDiag lm,
-                         double* S, double* rhs, cudaStream_t st);
+                         double* S, double* rhs, double* Minv, cudaStream_t st);
 // scal_all [world][S_COUNT] (all-gathered per-rank scalar blocks) -> scal: sums / max in rank order
 void launch_combine_scalars(const double* scal_all, int world, double* scal, cudaStream_t st);
-void launch_block_inverse(const ProblemView& pv, const double* S, double* Minv, cudaStream_t st);
 struct PcgPlan {
   int grid, rows_per_cta, use_smem, max_local_blocks;
   int halo_cap, halo_words;  // halo staging of the grid PCG's product (0: off)

@@ -769,7 +769,9 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
       Timer t(h, KS_COLLECTIVE, 2);
       NcclApi& nc = nccl_api();
       NC(nc.AllReduce(c.w.S, c.w.S, (size_t)c.pv.B * 36 + (size_t)c.pv.C * 6, ncclDouble, ncclSum, h->comm, h->stream));
-      launch_schur_finish(c.pv, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.S, c.w.rhs, h->stream);
+      // ... and the block-Jacobi inverses of the completed diagonal blocks (unless the dense solve follows)
+      launch_schur_finish(c.pv, c.w.Hc[kset], c.w.gc[kset], c.w.c_img, lm, c.w.S, c.w.rhs, c.dense ? nullptr : c.w.Minv,
+                          h->stream);
     }
     if (c.dense) {
       Timer t(h, KS_PCG);
@@ -780,10 +782,7 @@ int enqueue_points_and_system(Ctx& c, const double* pose, const double* X, int k
       ++c.solves;
       return MPBA_OK;
     }
-    if (c.sh) {  // single GPU: written by the diagonal CTAs of k_schur_blocks
-      Timer t(h, KS_BLOCK_INVERSE);
-      launch_block_inverse(c.pv, c.w.S, c.w.Minv, h->stream);
-    }
+    // (the block-Jacobi inverses were written by the diagonal CTAs of k_schur_blocks / k_schur_finish)
     // Coarse space.  Synchronous (coarse_lag = 0): modes, Z^T S Z and its dense inverse on the solve stream, right
     // before the PCG -- 279 us per LM iteration at cfg3, 232 us of it the latency-bound Gauss-Jordan on four CTAs.
     // Lagged (default): the inverse is a PRECONDITIONER, any SPD matrix serves; the one built from S of the previous
