@@ -1179,12 +1179,14 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
           // rows 0..2: P_a^T [KP | K], rows 3..5: [KP | K]
-          M[c] += qa[1] * KP[6 + c] - qa[2] * KP[3 + c];
-          M[6 + c] += qa[2] * KP[c] - qa[0] * KP[6 + c];
-          M[12 + c] += qa[0] * KP[3 + c] - qa[1] * KP[c];
-          M[3 + c] += qa[1] * K[6 + c] - qa[2] * K[3 + c];
-          M[9 + c] += qa[2] * K[c] - qa[0] * K[6 + c];
-          M[15 + c] += qa[0] * K[3 + c] - qa[1] * K[c];
+          // two fused multiply-adds into the accumulator instead of (product, fused difference, add): a third fewer
+          // instructions on the 18 cross-product entries of an item in a kernel bound by instruction issue
+          M[c] = fma(qa[1], KP[6 + c], fma(-qa[2], KP[3 + c], M[c]));
+          M[6 + c] = fma(qa[2], KP[c], fma(-qa[0], KP[6 + c], M[6 + c]));
+          M[12 + c] = fma(qa[0], KP[3 + c], fma(-qa[1], KP[c], M[12 + c]));
+          M[3 + c] = fma(qa[1], K[6 + c], fma(-qa[2], K[3 + c], M[3 + c]));
+          M[9 + c] = fma(qa[2], K[c], fma(-qa[0], K[6 + c], M[9 + c]));
+          M[15 + c] = fma(qa[0], K[3 + c], fma(-qa[1], K[c], M[15 + c]));
           M[18 + c] += KP[c];
           M[24 + c] += KP[3 + c];
           M[30 + c] += KP[6 + c];
