@@ -2201,6 +2201,20 @@ void launch_schur_finish(const ProblemView& pv, const double* Hc, const double* 
                          double* S, double* rhs, double* Minv, cudaStream_t st) {
   k_schur_finish<<<pv.C, 64, 0, st>>>(pv, Hc, gc, c_img, lm, S, rhs, Minv);
 }
+namespace {
+__global__ void k_stage_scalars(const double* __restrict__ scal, double* __restrict__ rows, int rank, int world) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= world * S_COUNT) return;
+  const int r = k / S_COUNT, j = k - r * S_COUNT;
+  double v = 0.0;
+  if (r == rank) v = scal[j];
+  rows[k] = v;
+}
+}  // namespace
+void launch_stage_scalars(const double* scal, double* rows, int rank, int world, cudaStream_t st) {
+  const int n = world * S_COUNT;
+  k_stage_scalars<<<(n + 255) / 256, 256, 0, st>>>(scal, rows, rank, world);
+}
 void launch_combine_scalars(const double* scal_all, int world, double* scal, cudaStream_t st) {
   k_combine_scalars<<<1, 32, 0, st>>>(scal_all, world, scal);
 }

@@ -164,6 +164,8 @@ void launch_schur_finish(const ProblemView& pv, const double* Hc, const double* 
                          double* S, double* rhs, double* Minv, cudaStream_t st);
 // scal_all [world][S_COUNT] (all-gathered per-rank scalar blocks) -> scal: sums / max in rank order
 void launch_combine_scalars(const double* scal_all, int world, double* scal, cudaStream_t st);
+// rows [world][S_COUNT]: this rank's scalar block into row `rank`, zeros elsewhere (gathered by a SUM all-reduce)
+void launch_stage_scalars(const double* scal, double* rows, int rank, int world, cudaStream_t st);
 struct PcgPlan {
   int grid, rows_per_cta, use_smem, max_local_blocks;
   int halo_cap, halo_words;  // halo staging of the grid PCG's product (0: off)

@@ -204,7 +204,7 @@ size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Workspace {
   double *pose[2], *X[2], *chunk_part, *Hc[2], *gc[2], *ip[2], *c_img, *c_pt, *Hpp, *gp, *Hinv, *fac, *S,
-      *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal, *scal_all, *Linv, *tpart, *pts_stage, *cam_stage;
+      *rhs, *Minv, *y, *vr, *vz, *vp0, *vp1, *vq, *partial, *pt_part, *scal, *sr[2], *Linv, *tpart, *pts_stage, *cam_stage;
   double *Zc = nullptr, *Ac = nullptr, *Ainv = nullptr;  // coarse space (coarse.cu)
   double *Zc2 = nullptr, *Ainv2 = nullptr;               // lagged setup: the side stream's own Z, the second inverse
   int32_t* pm_pt = nullptr;   // point of every track-order slot (launch_track_setup)
@@ -241,11 +241,15 @@ void carve(const mpba_problem* p, const mpba_shard* sh, char* base, Workspace& w
     w.X[k] = take(Ppad * 4);
     // image blocks, gradients and per-image costs of one buffer set are ONE span: a sharded solve all-reduces it in
     // one call (img_span doubles from Hc[k])
+    // (sharded: + one row of S_COUNT scalars per rank -- every rank fills its own row, zeros elsewhere, so the SUM
+    // all-reduce of the span also gathers the per-rank scalar blocks: one collective instead of two)
     const size_t hc = (C * 21 + 1) & ~(size_t)1;
-    w.Hc[k] = take(hc + C * 6 + C * 2);
+    const size_t rows = sh ? (size_t)sh->world * S_COUNT : 0;
+    w.Hc[k] = take(hc + C * 6 + C * 2 + rows);
     w.gc[k] = w.Hc[k] ? w.Hc[k] + hc : nullptr;
     w.ip[k] = w.Hc[k] ? w.gc[k] + C * 6 : nullptr;
-    w.img_span = hc + C * 6 + C * 2;
+    w.sr[k] = w.Hc[k] ? w.ip[k] + C * 2 : nullptr;
+    w.img_span = hc + C * 6 + C * 2 + rows;
   }
   w.chunk_part = take((size_t)p->num_chunks * IMG_PART);
   w.c_img = take(C * 6);
@@ -270,7 +274,6 @@ void carve(const mpba_problem* p, const mpba_shard* sh, char* base, Workspace& w
   w.scal = take(S_COUNT);
   w.pts_stage = take(PT_SCALARS_STAGE);
   w.cam_stage = take(3 * (size_t)cam_step_rows((int)C) + 2);
-  w.scal_all = take(sh ? (size_t)sh->world * S_COUNT : 0);
   {
     const bool so = (p->flags & MPBA_FLAG_STRUCTURE_ONLY) != 0;
     w.Zc = take(so ? 0 : C * 42);
@@ -351,6 +354,7 @@ struct Ctx {
   const LmTail* tail = nullptr;    // device LM loop: the controller rides on the next fused image tail kernel
   const PtScalarsArgs* tail_pts = nullptr;  // small bundles: the step's point scalars are reduced by that kernel too
   bool tail_done = false;
+  const double* scal_rows = nullptr;  // sharded: the gathered per-rank scalar rows of the last image pass
   bool dense = false;              // reduced system solved directly by one CTA (dense_solve.cu): <= 21 images
   bool device_lm = false;          // LM controller on the device: no memset nodes in the loop body (lm_loop.cu)
   int coarse_lag = 0;              // 1: the PCG of linear solve i uses the coarse inverse built from S of solve i - 1
@@ -429,6 +433,8 @@ int enqueue_image_pass(Ctx& c, const double* pose, const double* X, int k, int c
     }
     Timer t(h, KS_COLLECTIVE);
     NcclApi& nc = nccl_api();
+    launch_stage_scalars(c.w.scal, c.w.sr[k], c.sh->rank, c.sh->world, h->stream);
+    c.scal_rows = c.w.sr[k];
     NC(nc.AllReduce(c.w.Hc[k], c.w.Hc[k], c.w.img_span, ncclDouble, ncclSum, h->comm, h->stream));
   } else if (c.pv.C <= IMG_TAIL_MAX_IMAGES) {
     // small bundle: finalize + scalars (+ the LM decision of the device loop) in one single-CTA kernel
@@ -453,9 +459,10 @@ int enqueue_image_pass(Ctx& c, const double* pose, const double* X, int k, int c
 int combine_scalars(Ctx& c) {
   mpba_handle* h = c.h;
   if (!c.sh) return MPBA_OK;
-  Timer t(h, KS_COLLECTIVE, 2);
-  NC(nccl_api().AllGather(c.w.scal, c.w.scal_all, S_COUNT, ncclDouble, h->comm, h->stream));
-  launch_combine_scalars(c.w.scal_all, c.sh->world, c.w.scal, h->stream);
+  // the rows came with the all-reduce of the image pass that just ran (enqueue_image_pass)
+  if (c.scal_rows == nullptr) return fail(h, MPBA_E_INVALID, "combine_scalars without an image pass");
+  Timer t(h, KS_COLLECTIVE, 1);
+  launch_combine_scalars(c.scal_rows, c.sh->world, c.w.scal, h->stream);
   return MPBA_OK;
 }
 
