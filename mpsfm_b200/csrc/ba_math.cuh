@@ -391,6 +391,8 @@ struct LossSpec {
   // frame and the functor then returns a ZERO residual (and, through the jets, a zero Jacobian) instead of inf;
   // 1: strict -- the projection is evaluated as written (inf / nan residual, the solve reports it)
   int behind_strict;
+  // loss scale of the point-to-plane normal-prior rows (EXTENSION, see linearize_obs); the loss type is depth_loss
+  double plane_scale;
 };
 
 struct ObsLin {
@@ -399,15 +401,24 @@ struct ObsLin {
   double prot[3];  // R(q) X
   double rho;      // rho_reproj + rho_depth of the two blocks (not halved)
   double r[3];     // raw residuals (x, y, log-depth); r[2] = 0 without a prior
+  double rn;       // raw point-to-plane residual of the normal-prior row (extension); 0 without one
 };
 
 // One observation.  pose = {qx,qy,qz,qw,tx,ty,tz}, R = rotmat(q), X the point, (d, w, a) the depth
 // prior (w == 0: none), (b, es) the image's shift and exp(log-scale) (the kernels keep exp(s) in slot 7 of the
 // pose record: one exp per image and state instead of one per observation).
+//
+// plane != nullptr: EXTENSION without a counterpart in the reference (the reference has no Ceres
+// residual for normals; they act through the depth-integration solver).  One more 1-D row per observation, the
+// point-to-plane distance to the monocular surface patch at the keypoint,
+//     r_n = m . p_cam - c,      m = sqrt(w_n) n,   c = sqrt(w_n) n . q,
+// n the prior unit normal in the camera frame, q the prior surface point (prior depth times the keypoint's ray), both
+// folded by the host into plane = {m_x, m_y, m_z, c} (m = 0: no row).  Loss: ScaledLoss(depth_loss(plane_scale), 1).
+// Linear in p_cam: dr_n / dp_cam = m.  Defined in oracle/residuals.py; parity "n/a" (nothing to compare with upstream).
 template <bool WANT_JAC, bool WANT_RHO>
 MPBA_HD void linearize_obs(const double* pose, const double R[9], const double X[3], int model, const double* prm,
                            double ox, double oy, double d, double w, double a, double b, double es,
-                           const LossSpec& ls, ObsLin& o) {
+                           const LossSpec& ls, ObsLin& o, const double* plane = nullptr) {
   o.prot[0] = R[0] * X[0] + R[1] * X[1] + R[2] * X[2];
   o.prot[1] = R[3] * X[0] + R[4] * X[1] + R[5] * X[2];
   o.prot[2] = R[6] * X[0] + R[7] * X[1] + R[8] * X[2];
@@ -461,6 +472,22 @@ MPBA_HD void linearize_obs(const double* pose, const double R[9], const double X
       // a2 = (0, 0, -1/z)
       o.N[5] += rhod1 * iz * iz;
       o.h[2] -= rhod1 * iz * r2;
+    }
+  }
+  o.rn = 0.0;
+  if (plane != nullptr) {
+    const double m0 = plane[0], m1 = plane[1], m2 = plane[2];
+    if (m0 != 0.0 || m1 != 0.0 || m2 != 0.0) {
+      const double rn = m0 * px + m1 * py + m2 * pz - plane[3];
+      o.rn = rn;
+      double rhon, rhon1;
+      loss_eval<WANT_RHO>(ls.depth_loss, ls.plane_scale, 1.0, rn * rn, rhon, rhon1);
+      o.rho += rhon;
+      if (WANT_JAC) {
+        o.N[0] += rhon1 * m0 * m0; o.N[1] += rhon1 * m0 * m1; o.N[2] += rhon1 * m0 * m2;
+        o.N[3] += rhon1 * m1 * m1; o.N[4] += rhon1 * m1 * m2; o.N[5] += rhon1 * m2 * m2;
+        o.h[0] += rhon1 * m0 * rn; o.h[1] += rhon1 * m1 * rn; o.h[2] += rhon1 * m2 * rn;
+      }
     }
   }
 }

@@ -111,6 +111,14 @@ class BundleProblem:
     reproj_loss_scale: float = 1.5  # reproj_loss_scale * kp_std (:101)
     reproj_loss_weight: float = 1.0  # loss_function_magnitude = 1/kp_std^2 (:99)
     depth_loss: LossType = LossType.CAUCHY
+    # EXTENSION (no counterpart in the reference): point-to-plane normal-prior rows.  Row j refers to
+    # observation plane_obs[j]:  r = m_j . p_cam - c_j  with  m = sqrt(w_n) n  (n: prior unit normal in the camera
+    # frame) and  c = m . q  (q: prior surface point = prior depth x the keypoint's ray).  Loss: depth_loss with the
+    # global scale plane_loss_scale, weight 1.  None / empty: no such rows.
+    plane_obs: np.ndarray | None = None  # [N_n] int32 index into observations
+    plane_m: np.ndarray | None = None  # [N_n,3]
+    plane_c: np.ndarray | None = None  # [N_n]
+    plane_loss_scale: float = 1.0
 
     # ------------------------------------------------------------------
     @property
@@ -128,6 +136,10 @@ class BundleProblem:
     @property
     def num_depth(self) -> int:
         return int(self.depth_obs.shape[0])
+
+    @property
+    def num_plane(self) -> int:
+        return 0 if self.plane_obs is None else int(np.asarray(self.plane_obs).shape[0])
 
     def normalized(self) -> "BundleProblem":
         """Return a copy with canonical dtypes/contiguity and unit quaternions.
@@ -159,6 +171,9 @@ class BundleProblem:
             depth_w=f(self.depth_w, (-1,)),
             depth_a=f(self.depth_a, (-1,)),
             shift_scale=f(self.shift_scale, (-1, 2)),
+            plane_obs=None if self.plane_obs is None else i(self.plane_obs),
+            plane_m=None if self.plane_m is None else f(self.plane_m, (-1, 3)),
+            plane_c=None if self.plane_c is None else f(self.plane_c, (-1,)),
             reproj_loss=LossType.parse(self.reproj_loss),
             depth_loss=LossType.parse(self.depth_loss),
         )
@@ -189,6 +204,16 @@ class BundleProblem:
                 raise ValueError("at most one depth prior per observation")
             if not np.all(self.depth_d > 0):
                 raise ValueError("depth priors must be > 0 (bundle_adjustment.py:139)")
+        nn = self.num_plane
+        if nn:
+            if self.plane_m is None or self.plane_c is None or self.plane_m.shape != (nn, 3) or self.plane_c.shape != (nn,):
+                raise ValueError("normal-prior arrays disagree on N_n")
+            if self.plane_obs.min() < 0 or self.plane_obs.max() >= N:
+                raise ValueError("plane_obs out of range")
+            if int(np.bincount(self.plane_obs, minlength=N).max()) > 1:
+                raise ValueError("at most one normal prior per observation")
+            if not self.plane_loss_scale > 0:
+                raise ValueError("plane_loss_scale must be > 0")
         for m in np.unique(self.cam_model):
             if int(m) not in CameraModel._value2member_map_:
                 raise ValueError(f"unknown camera model id {m}")

@@ -9,6 +9,9 @@ Restates (file:line under /root/reference/mpsfm/sfm/mapper/):
   ``logloss=True``: ``r = log(exp(s) d + b) - log((q * X + t)_z)``, one ``ScaledLoss(loss(a_j), w_j)`` per
   observation (:160-161).  The functor's source is not available; this form is SURVEY.md section 8
   row a-4's inference from the call site and ``optimize_prior_shiftscale`` (:236-241) -- PARITY UNPINNED;
+* EXTENSION, nothing upstream to compare with ("parity n/a"): point-to-plane normal-prior
+  rows ``r = m . (q * X + t) - c`` (``problem.plane_*``; m = sqrt(w_n) n, c = m . prior surface point), loss
+  ``ScaledLoss(depth_loss(plane_loss_scale), 1)``.  This file DEFINES them; the kernels restate it;
 * local parameterisations (:114-122): tangent of an image = (half-angle rotation vector, translation),
   Jacobians formed the Ceres way, ambient autodiff Jacobian times ``PlusJacobian``;
 * ``ceres::internal::Corrector`` applied per residual block; cost = 1/2 sum rho.
@@ -48,10 +51,12 @@ class Linearization:
     r_depth: np.ndarray  # [N_d] raw residuals
     cost: float  # 1/2 sum rho over blocks with at least one non-constant parameter block
     fixed_cost: float  # blocks whose parameter blocks are all constant (Ceres removes them)
-    # robustified rows per observation (row 2 = depth prior; zero where the observation has none)
-    r: np.ndarray | None = None  # [N,3]
-    Jc: np.ndarray | None = None  # [N,3,6] w.r.t. image tangent (masked columns zeroed)
-    Jp: np.ndarray | None = None  # [N,3,3] w.r.t. point (zero for constant points)
+    # robustified rows per observation (row 2 = depth prior; zero where the observation has none; with normal-prior
+    # rows in the problem there is a row 3 = point-to-plane)
+    r: np.ndarray | None = None  # [N,3 or 4]
+    Jc: np.ndarray | None = None  # [N,3 or 4,6] w.r.t. image tangent (masked columns zeroed)
+    Jp: np.ndarray | None = None  # [N,3 or 4,3] w.r.t. point (zero for constant points)
+    r_plane: np.ndarray | None = None  # [N_n] raw point-to-plane residuals (extension)
 
 
 def free_columns(problem) -> np.ndarray:
@@ -126,7 +131,18 @@ def evaluate(problem, state: State | None = None, jacobians: bool = True) -> Lin
     fixed = img_const & pt_const
     cost = 0.5 * float(np.sum(rho_rep[0][~fixed])) + 0.5 * float(np.sum(rho_dep[0][~fixed[di]]))
     fixed_cost = 0.5 * float(np.sum(rho_rep[0][fixed])) + 0.5 * float(np.sum(rho_dep[0][fixed[di]]))
-    lin = Linearization(r_rep, r_dep, cost, fixed_cost)
+    # normal-prior rows (extension)
+    nn = getattr(problem, "num_plane", 0)
+    r_pl = np.zeros(0)
+    if nn:
+        ni = np.asarray(problem.plane_obs)
+        pm = np.asarray(problem.plane_m, dtype=np.float64)
+        r_pl = np.einsum("ni,ni->n", pm, pc[ni]) - np.asarray(problem.plane_c, dtype=np.float64)
+        s_pl = r_pl * r_pl
+        rho_pl = losses.scaled_rho(int(problem.depth_loss), np.full(nn, float(problem.plane_loss_scale)), np.ones(nn), s_pl)
+        cost += 0.5 * float(np.sum(rho_pl[0][~fixed[ni]]))
+        fixed_cost += 0.5 * float(np.sum(rho_pl[0][fixed[ni]]))
+    lin = Linearization(r_rep, r_dep, cost, fixed_cost, r_plane=r_pl)
     if not jacobians:
         return lin
 
@@ -134,8 +150,9 @@ def evaluate(problem, state: State | None = None, jacobians: bool = True) -> Lin
     plusJ = geometry.quat_plus_jacobian(q)  # [N,4,3]
     dp_drot = np.einsum("nij,njk->nik", dp_dq, plusJ)  # [N,3,3]
     R = geometry.rotmat(q)  # d(q*X+t)/dX; equals the jet derivative for unit q
-    Jc = np.zeros((N, 3, 6))
-    Jp = np.zeros((N, 3, 3))
+    rows = 4 if nn else 3
+    Jc = np.zeros((N, rows, 6))
+    Jp = np.zeros((N, rows, 3))
     Jc[:, :2, :3] = np.einsum("nij,njk->nik", dxy_dp, dp_drot)
     Jc[:, :2, 3:] = dxy_dp
     Jp[:, :2, :] = np.einsum("nij,njk->nik", dxy_dp, R)
@@ -146,7 +163,7 @@ def evaluate(problem, state: State | None = None, jacobians: bool = True) -> Lin
     Jp[di, 2, :] = dz[:, None] * R[di, 2, :]
 
     # ---- corrector (per block)
-    r = np.zeros((N, 3))
+    r = np.zeros((N, rows))
     sc, alpha_sq, sqrt_r1 = losses.corrector(s_rep, rho_rep[1], rho_rep[2])
     # J <- sqrt(rho') (J - alpha_sq r r^T J)
     rJc = np.einsum("ni,nij->nj", r_rep, Jc[:, :2, :])
@@ -158,6 +175,15 @@ def evaluate(problem, state: State | None = None, jacobians: bool = True) -> Lin
     Jc[di, 2, :] = sqrt_r1_d[:, None] * (Jc[di, 2, :] * (1.0 - alpha_sq_d * s_dep)[:, None])
     Jp[di, 2, :] = sqrt_r1_d[:, None] * (Jp[di, 2, :] * (1.0 - alpha_sq_d * s_dep)[:, None])
     r[di, 2] = scd * r_dep
+    if nn:
+        # dr/dp = m; through the same chain as the other rows
+        Jc[ni, 3, :3] = np.einsum("ni,nij->nj", pm, dp_drot[ni])
+        Jc[ni, 3, 3:] = pm
+        Jp[ni, 3, :] = np.einsum("ni,nij->nj", pm, R[ni])
+        scn, alpha_sq_n, sqrt_r1_n = losses.corrector(s_pl, rho_pl[1], rho_pl[2])
+        Jc[ni, 3, :] = sqrt_r1_n[:, None] * (Jc[ni, 3, :] * (1.0 - alpha_sq_n * s_pl)[:, None])
+        Jp[ni, 3, :] = sqrt_r1_n[:, None] * (Jp[ni, 3, :] * (1.0 - alpha_sq_n * s_pl)[:, None])
+        r[ni, 3] = scn * r_pl
 
     # ---- constant parameter blocks / fixed tangent coordinates carry no columns
     Jc *= free_columns(problem)[oi][:, None, :]

@@ -9,10 +9,12 @@ extern "C" {
 
 // per observation: pose [n][8], X [n][3], model [n], prm [n][12], xy [n][2], dwa [n][3], bs [n][2]
 // out [n][40]: N(6) h(3) prot(3) rho(1) r(3) Hcc_upper(21) gc(6)  = 43 -> use 48 stride
-void hc_obs(int n, const double* pose, const double* X, const int* model, const double* prm, const double* xy,
-            const double* dwa, const double* bs, int reproj_loss, int depth_loss, double reproj_scale,
-            double reproj_weight, int want_jac, double* out) {
+// plane [n][4] = {m, c} of the normal-prior extension or NULL; out[43] = its raw residual
+void hc_obs_plane(int n, const double* pose, const double* X, const int* model, const double* prm, const double* xy,
+                  const double* dwa, const double* bs, int reproj_loss, int depth_loss, double reproj_scale,
+                  double reproj_weight, int want_jac, const double* plane, double plane_scale, double* out) {
   LossSpec ls{reproj_loss, depth_loss, reproj_scale, reproj_weight};
+  ls.plane_scale = plane_scale;
   for (int i = 0; i < n; ++i) {
     double R[9];
     quat_to_rotmat(pose + 8 * i, R);
@@ -21,10 +23,10 @@ void hc_obs(int n, const double* pose, const double* X, const int* model, const 
     for (int k = 0; k < 3; ++k) o.h[k] = 0;
     if (want_jac)
       linearize_obs<true, true>(pose + 8 * i, R, X + 3 * i, model[i], prm + 12 * i, xy[2 * i], xy[2 * i + 1], dwa[3 * i],
-                                dwa[3 * i + 1], dwa[3 * i + 2], bs[2 * i], exp(bs[2 * i + 1]), ls, o);
+                                dwa[3 * i + 1], dwa[3 * i + 2], bs[2 * i], exp(bs[2 * i + 1]), ls, o, plane ? plane + 4 * i : nullptr);
     else
       linearize_obs<false, true>(pose + 8 * i, R, X + 3 * i, model[i], prm + 12 * i, xy[2 * i], xy[2 * i + 1], dwa[3 * i],
-                                 dwa[3 * i + 1], dwa[3 * i + 2], bs[2 * i], exp(bs[2 * i + 1]), ls, o);
+                                 dwa[3 * i + 1], dwa[3 * i + 2], bs[2 * i], exp(bs[2 * i + 1]), ls, o, plane ? plane + 4 * i : nullptr);
     double* d = out + 48 * i;
     for (int k = 0; k < 6; ++k) d[k] = o.N[k];
     for (int k = 0; k < 3; ++k) d[6 + k] = o.h[k];
@@ -35,7 +37,15 @@ void hc_obs(int n, const double* pose, const double* X, const int* model, const 
       gt_n_g_upper(o.prot, o.N, d + 16);
       gt_vec(o.prot, o.h, d + 37);
     }
+    d[43] = o.rn;
   }
+}
+
+void hc_obs(int n, const double* pose, const double* X, const int* model, const double* prm, const double* xy,
+            const double* dwa, const double* bs, int reproj_loss, int depth_loss, double reproj_scale,
+            double reproj_weight, int want_jac, double* out) {
+  hc_obs_plane(n, pose, X, model, prm, xy, dwa, bs, reproj_loss, depth_loss, reproj_scale, reproj_weight, want_jac,
+               nullptr, 1.0, out);
 }
 
 void hc_gt_k_g(const double* pa, const double* K, const double* pb, double* M) { gt_k_g(pa, K, pb, M); }

@@ -31,10 +31,15 @@ def obs_quantities(hc, problem, state_q, state_t, state_X, want_jac=True):
     dwa[problem.depth_obs, 2] = problem.depth_a
     bs = np.ascontiguousarray(problem.shift_scale[oi])
     out = np.zeros((n, 48))
-    hc.hc_obs(C.c_int(n), _p(pose), _p(X), _p(model), _p(prm), _p(xy), _p(dwa), _p(bs),
-              C.c_int(int(problem.reproj_loss)), C.c_int(int(problem.depth_loss)),
-              C.c_double(problem.reproj_loss_scale), C.c_double(problem.reproj_loss_weight),
-              C.c_int(1 if want_jac else 0), _p(out))
+    plane = None
+    if getattr(problem, "num_plane", 0):
+        plane = np.zeros((n, 4))
+        plane[problem.plane_obs, :3], plane[problem.plane_obs, 3] = problem.plane_m, problem.plane_c
+    hc.hc_obs_plane(C.c_int(n), _p(pose), _p(X), _p(model), _p(prm), _p(xy), _p(dwa), _p(bs),
+                    C.c_int(int(problem.reproj_loss)), C.c_int(int(problem.depth_loss)),
+                    C.c_double(problem.reproj_loss_scale), C.c_double(problem.reproj_loss_weight),
+                    C.c_int(1 if want_jac else 0), _p(plane) if plane is not None else None,
+                    C.c_double(float(getattr(problem, "plane_loss_scale", 1.0))), _p(out))
     iu = np.triu_indices(6)
     Hcc = np.zeros((n, 6, 6))
     Hcc[:, iu[0], iu[1]] = out[:, 16:37]
@@ -45,7 +50,7 @@ def obs_quantities(hc, problem, state_q, state_t, state_X, want_jac=True):
     Nm[:, 1, 0], Nm[:, 1, 1], Nm[:, 1, 2] = N6[:, 1], N6[:, 3], N6[:, 4]
     Nm[:, 2, 0], Nm[:, 2, 1], Nm[:, 2, 2] = N6[:, 2], N6[:, 4], N6[:, 5]
     return {"N": Nm, "h": out[:, 6:9], "prot": out[:, 9:12], "rho": out[:, 12], "r": out[:, 13:16],
-            "Hcc": Hcc, "gc": out[:, 37:43]}
+            "Hcc": Hcc, "gc": out[:, 37:43], "rn": out[:, 43]}
 
 
 def g_matrix(p):

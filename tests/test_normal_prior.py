@@ -1,0 +1,120 @@
+"""The normal-prior rows (EXTENSION -- nothing upstream to hold them against, "parity n/a").
+
+oracle/residuals.py DEFINES the rows; here (a) the definition is checked against finite differences of its own cost,
+(b) the product's arithmetic (ba_math.cuh built with g++, tests/hostcheck) is held against that definition at the
+1e-9 gate of the other rows, (c) the host side (undistortion, plane construction) against the forward camera models."""
+
+import numpy as np
+import pytest
+
+from mpsfm_b200 import normal_prior
+from mpsfm_b200.problem import CameraModel, LossType
+from mpsfm_b200.synthetic import DEFAULT_PARAMS, _distort, make_scene
+from oracle import geometry, lm
+from oracle.residuals import State, evaluate
+
+import kernel_emulation as ke
+
+
+def rel(a, b):
+    return np.max(np.abs(a - b) / (np.abs(b) + 1e-300 + 1e-12 * np.max(np.abs(b))))
+
+
+def _scene(model=CameraModel.SIMPLE_RADIAL, depth_loss=LossType.CAUCHY, **kw):
+    prob = make_scene(8, 150, 4, model=model, seed=4, depth_loss=depth_loss, depth_frac=0.8, **kw)
+    return normal_prior.synthetic_normal_priors(prob, frac=0.6, seed=1)
+
+
+@pytest.mark.parametrize("model", sorted(DEFAULT_PARAMS))
+def test_cam_from_img_inverts_the_forward_model(model):
+    rng = np.random.default_rng(int(model))
+    uv = rng.uniform(-0.5, 0.5, size=(500, 2))
+    uv[0] = 0.0
+    p = np.asarray(DEFAULT_PARAMS[model])
+    with np.errstate(invalid="ignore", divide="ignore"):
+        x, y = _distort(model, p, np.where(uv[:, 0] == 0, 1e-13, uv[:, 0]), uv[:, 1])
+    back = normal_prior.cam_from_img(model, p, np.stack([x, y], axis=1))
+    assert np.max(np.abs(back - uv)) < 1e-11
+
+
+def test_plane_rows_vanish_on_the_prior_surface():
+    prob = _scene()
+    assert prob.num_plane > 100 and np.all(np.isin(prob.plane_obs, prob.depth_obs))
+    # a point at q = depth * (u, v, 1) of its own observation has residual 0 and lies at the prior depth
+    o = prob.plane_obs
+    k = np.searchsorted(prob.depth_obs, o)
+    cam = prob.img_camera[prob.obs_img[o]]
+    uv = normal_prior.cam_from_img(CameraModel(int(prob.cam_model[0])), prob.cam_params[0], prob.obs_xy[o])
+    q = prob.depth_d[k][:, None] * np.concatenate([uv, np.ones((o.size, 1))], axis=1)
+    assert np.all(cam == 0)
+    assert np.max(np.abs(np.einsum("ni,ni->n", prob.plane_m, q) - prob.plane_c)) < 1e-9
+    assert np.allclose(np.linalg.norm(prob.plane_m, axis=1), 1.0 / 0.05)
+    with pytest.raises(ValueError):
+        no_depth = np.setdiff1d(np.arange(prob.num_obs), prob.depth_obs)[:3]
+        normal_prior.plane_rows(prob, no_depth, np.tile([0, 0, -1.0], (3, 1)), 1.0)
+
+
+@pytest.mark.parametrize("depth_loss", [LossType.CAUCHY, LossType.TRIVIAL, LossType.HUBER])
+def test_oracle_gradient_is_the_derivative_of_its_cost(depth_loss):
+    prob = _scene(depth_loss=depth_loss)
+    st = State.of(prob)
+    lin = evaluate(prob, st, jacobians=True)
+    base = evaluate(dataclass_without_planes(prob), st, jacobians=True)
+    assert lin.r.shape[1] == 4 and base.r.shape[1] == 3
+    assert lin.cost > base.cost and lin.r_plane.shape == (prob.num_plane,)
+    assert np.array_equal(lin.r[:, :3], base.r[:, :3]) and np.array_equal(lin.Jc[:, :3], base.Jc[:, :3])
+    # gradient of 0.5 sum rho w.r.t. one point / one image tangent by central differences
+    oi, op = prob.obs_img, prob.obs_pt
+    gp = lm.segment_sum(op, np.einsum("nki,nk->ni", lin.Jp, lin.r), prob.num_points)
+    gc = lm.segment_sum(oi, np.einsum("nki,nk->ni", lin.Jc, lin.r), prob.num_images)
+    h, tol = 1e-4, 2e-4  # the cost is ~1e6 with the trivial loss: 1e-16 * 1e6 / h of rounding
+    for p in prob.obs_pt[prob.plane_obs[:4]]:
+        for a in range(3):
+            c = []
+            for sgn in (1, -1):
+                X = st.X.copy()
+                X[p, a] += sgn * h
+                c.append(evaluate(prob, State(st.q, st.t, X), jacobians=False).cost)
+            assert abs((c[0] - c[1]) / (2 * h) - gp[p, a]) < tol * max(1.0, abs(gp[p, a]))
+    img = int(prob.obs_img[prob.plane_obs[-1]])
+    assert prob.img_free_mask[img] == 0b111111
+    for a in range(6):
+        c = []
+        for sgn in (1, -1):
+            d = np.zeros(6)
+            d[a] = sgn * h
+            q, t = st.q.copy(), st.t.copy()
+            q[img] = geometry.quat_plus(st.q[img][None], d[None, :3])[0]
+            t[img] = st.t[img] + d[3:]
+            c.append(evaluate(prob, State(q, t, st.X), jacobians=False).cost)
+        assert abs((c[0] - c[1]) / (2 * h) - gc[img, a]) < tol * max(1.0, abs(gc[img, a]))
+
+
+def dataclass_without_planes(prob):
+    import dataclasses
+
+    return dataclasses.replace(prob, plane_obs=None, plane_m=None, plane_c=None)
+
+
+@pytest.mark.parametrize("model", [CameraModel.PINHOLE, CameraModel.SIMPLE_RADIAL, CameraModel.OPENCV])
+@pytest.mark.parametrize("depth_loss", [LossType.CAUCHY, LossType.SOFT_L1, LossType.TRIVIAL])
+def test_product_arithmetic_matches_the_definition(hostcheck, model, depth_loss):
+    prob = _scene(model=model, depth_loss=depth_loss)
+    prob.img_free_mask[:] = 0b111111
+    st = State.of(prob)
+    lin = evaluate(prob, st, jacobians=True)
+    q = ke.obs_quantities(hostcheck, prob, st.q, st.t, st.X)
+    assert rel(q["rn"][prob.plane_obs], lin.r_plane) < 1e-9
+    others = np.setdiff1d(np.arange(prob.num_obs), prob.plane_obs)
+    assert np.all(q["rn"][others] == 0.0)
+    assert abs(0.5 * q["rho"].sum() - (lin.cost + lin.fixed_cost)) <= 1e-12 * lin.cost
+    assert rel(q["Hcc"], np.einsum("nki,nkj->nij", lin.Jc, lin.Jc)) < 1e-9
+    assert rel(q["gc"], np.einsum("nki,nk->ni", lin.Jc, lin.r)) < 1e-9
+    R = geometry.rotmat(st.q[prob.obs_img])
+    assert rel(np.einsum("nki,nkl,nlj->nij", R, q["N"], R), np.einsum("nki,nkj->nij", lin.Jp, lin.Jp)) < 1e-9
+    assert rel(np.einsum("nki,nk->ni", R, q["h"]), np.einsum("nki,nk->ni", lin.Jp, lin.r)) < 1e-9
+    G = ke.g_matrix(q["prot"])
+    assert rel(np.einsum("nki,nkl,nlj->nij", G, q["N"], R), np.einsum("nki,nkj->nij", lin.Jc, lin.Jp)) < 1e-9
+    # without Jacobians: same cost
+    q0 = ke.obs_quantities(hostcheck, prob, st.q, st.t, st.X, want_jac=False)
+    assert np.array_equal(q0["rho"], q["rho"])
