@@ -135,6 +135,16 @@ typedef struct mpba_problem {
   int32_t num_track_warps;
   int32_t reserved;
   const int32_t* track_warp_first; /* [num_track_warps + 1] */
+
+  /* EXTENSION without a counterpart in the reference (its bundle adjustment has no residual for monocular normals,
+   * mpsfm/sfm/mapper/bundle_adjustment.py:60-100; defined by oracle/residuals.py):
+   * point-to-plane rows  r = m . p_cam - c  with  m = sqrt(w_n) n,  c = m . (prior surface point),  loss
+   * ScaledLoss(depth_loss(plane_loss_scale), 1).  One record {m_x, m_y, m_z, c} per observation in both orders
+   * (m = 0: no row); both NULL: the problem has no such rows and nothing changes.  Sharded solves: the rank's slots,
+ * like pm_xy / cm_xy. */
+  const double* pm_plane;       /* [N][4] track order, or NULL */
+  const double* cm_plane;       /* [N][4] image order, or NULL */
+  double plane_loss_scale;      /* > 0 when the arrays are given */
 } mpba_problem;
 
 #define MPBA_FLAG_STRUCTURE_ONLY 1

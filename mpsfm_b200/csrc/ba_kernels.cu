@@ -77,6 +77,9 @@ constexpr int IMG_WARPS = IMG_THREADS / 32;
 #ifndef MPBA_IMG_PREFETCH_DEFAULT
 #define MPBA_IMG_PREFETCH_DEFAULT 444  // one wave: 148 SMs x 3 CTAs
 #endif
+// PLANE: the problem carries normal-prior rows (extension, ba_math.cuh: linearize_obs); the default instantiation
+// is the kernel without them, instruction for instruction
+template <bool PLANE>
 __global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(ProblemView pv, const double* __restrict__ pose,
                                                     const double* __restrict__ X, double* __restrict__ chunk_part,
                                                     int prefetch_ahead) {
@@ -104,7 +107,9 @@ __global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(Probl
   struct Operands {
     double2 xa, xb, o2;
     double d, w, a;
+    double pl[PLANE ? 4 : 1];
   };
+  const double2* pln = reinterpret_cast<const double2*>(pv.cm_plane);
   auto fetch = [&](int k, Operands& op) {
     const int pt = __ldg(pv.cm_pt + k);
     const double2* xp = reinterpret_cast<const double2*>(X + 4 * (size_t)pt);
@@ -114,6 +119,10 @@ __global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(Probl
     op.d = __ldg(dd + k);
     op.w = __ldg(dd + N + k);
     op.a = __ldg(dd + 2 * N + k);
+    if (PLANE) {
+      const double2 p0 = __ldg(pln + 2 * (size_t)k), p1 = __ldg(pln + 2 * (size_t)k + 1);
+      op.pl[0] = p0.x; op.pl[1] = p0.y; op.pl[PLANE ? 2 : 0] = p1.x; op.pl[PLANE ? 3 : 0] = p1.y;
+    }
   };
   int k = beg + (int)threadIdx.x;
   Operands cur, nxt;
@@ -124,7 +133,7 @@ __global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(Probl
     const double Xp[3] = {cur.xa.x, cur.xa.y, cur.xb.x};
     ObsLin o;
     linearize_obs<true, true>(ic.pose, ic.R, Xp, ic.model, ic.prm, cur.o2.x, cur.o2.y, cur.d, cur.w, cur.a, ic.b, ic.es,
-                              pv.loss, o);
+                              pv.loss, o, PLANE ? cur.pl : nullptr);
     double H[21], g[6];
     gt_n_g_upper(o.prot, o.N, H);
     gt_vec(o.prot, o.h, g);
@@ -301,6 +310,7 @@ __device__ __forceinline__ double warp_transpose_reduce32(double (&v)[36], int l
   return v[0];
 }
 
+template <bool PLANE>
 __device__ __forceinline__ void track_obs(const ProblemView& pv, const double* __restrict__ pose, const double Xp[3],
                                           int k, ObsLin& o, ImgConst& ic) {
   const int img = __ldg(pv.pm_img + k);
@@ -308,7 +318,14 @@ __device__ __forceinline__ void track_obs(const ProblemView& pv, const double* _
   const double2 o2 = __ldg(reinterpret_cast<const double2*>(pv.pm_xy) + k);
   const size_t N = (size_t)pv.N;
   const double d = __ldg(pv.pm_depth + k), w = __ldg(pv.pm_depth + N + k), a = __ldg(pv.pm_depth + 2 * N + k);
-  linearize_obs<true, false>(ic.pose, ic.R, Xp, ic.model, ic.prm, o2.x, o2.y, d, w, a, ic.b, ic.es, pv.loss, o);
+  if (PLANE) {
+    const double2* pp = reinterpret_cast<const double2*>(pv.pm_plane) + 2 * (size_t)k;
+    const double2 p0 = __ldg(pp), p1 = __ldg(pp + 1);
+    const double pl[4] = {p0.x, p0.y, p1.x, p1.y};
+    linearize_obs<true, false>(ic.pose, ic.R, Xp, ic.model, ic.prm, o2.x, o2.y, d, w, a, ic.b, ic.es, pv.loss, o, pl);
+  } else {
+    linearize_obs<true, false>(ic.pose, ic.R, Xp, ic.model, ic.prm, o2.x, o2.y, d, w, a, ic.b, ic.es, pv.loss, o);
+  }
 }
 
 constexpr int PT_THREADS = 128;  // k_evaluate: one thread per track
@@ -478,6 +495,7 @@ __device__ __forceinline__ void pack_factor(const double Q[9], const double Li[6
 
 // ---- warp path of the track-order pass: the tracks of ONE warp group (used when a CTA's groups hold a track
 // longer than 32 observations).  Sums by segmented shuffle tree (<= 32 observations) or whole-warp rounds.
+template <bool PLANE>
 __device__ __noinline__ double points_warp_path(const ProblemView pv, const double* __restrict__ pose,
                                                 const double* __restrict__ X, LmDiag lm, double* __restrict__ c_pt,
                                                 int compute_scaling, int jacobi_scaling, double* __restrict__ Hpp,
@@ -499,7 +517,7 @@ __device__ __noinline__ double points_warp_path(const ProblemView pv, const doub
         load_point(X, wt.t0 + wt.tl, Xp);
         ObsLin o;
         ImgConst ic;
-        track_obs(pv, pose, Xp, wt.base + lane, o, ic);
+        track_obs<PLANE>(pv, pose, Xp, wt.base + lane, o, ic);
         point_terms(o, ic.R, Q, v);
         prot[0] = o.prot[0]; prot[1] = o.prot[1]; prot[2] = o.prot[2];
       }
@@ -556,7 +574,7 @@ __device__ __noinline__ double points_warp_path(const ProblemView pv, const doub
         for (int k = lane; k < wt.n; k += 32) {
           ObsLin o;
           ImgConst ic;
-          track_obs(pv, pose, Xp, wt.base + k, o, ic);
+          track_obs<PLANE>(pv, pose, Xp, wt.base + k, o, ic);
           double Q[9], t[9];
           point_terms(o, ic.R, Q, t);
 #pragma unroll
@@ -577,7 +595,7 @@ __device__ __noinline__ double points_warp_path(const ProblemView pv, const doub
         for (int k = lane; k < wt.n; k += 32) {
           ObsLin o;
           ImgConst ic;
-          track_obs(pv, pose, Xp, wt.base + k, o, ic);
+          track_obs<PLANE>(pv, pose, Xp, wt.base + k, o, ic);
           double Q[9], t[9];
           point_terms(o, ic.R, Q, t);
           double2 rec[8];
@@ -622,6 +640,7 @@ __device__ __forceinline__ void prefetch_track_cta(const ProblemView& pv, const 
 //      through swizzled shared-memory rows so that the stores leave as whole 128-byte lines.
 // The reductions are keyed by point without atomics (north star item 2); the per-point algebra runs on densely
 // packed track threads instead of a few lanes of every warp.
+template <bool PLANE>
 __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(ProblemView pv, const double* __restrict__ pose,
                                                        const double* __restrict__ X, LmDiag lm,
                                                        double* __restrict__ c_pt, int compute_scaling,
@@ -677,7 +696,7 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
         const double Xp[3] = {xa.x, xa.y, xb.x};
         ObsLin o;
         ImgConst ic;
-        track_obs(pv, pose, Xp, base + tid, o, ic);
+        track_obs<PLANE>(pv, pose, Xp, base + tid, o, ic);
         double v[9];
         point_terms(o, ic.R, Q, v);
 #pragma unroll
@@ -747,7 +766,7 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points(Problem
   } else {
     const int w = g0 + warp;
     if (w < g1)
-      gmax = points_warp_path(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, fac, scal,
+      gmax = points_warp_path<PLANE>(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, fac, scal,
                               write_factors, rows_all[warp], w, lane);
   }
   if (!(gmax_done && write_factors)) {  // warp path, or no factor pass: the plain block reduction
@@ -954,7 +973,7 @@ __global__ void __launch_bounds__(PW_THREADS, MPBA_POINTS_MINB) k_points_bulk(
     } else {
       const int w = g * PW_WARPS + warp;
       if (w < min((g + 1) * PW_WARPS, pv.num_track_warps))
-        gmax = points_warp_path(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, fac, scal,
+        gmax = points_warp_path<false>(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, fac, scal,
                                 write_factors, rows_all + warp * 256, w, lane);
     }
     if (n > PW_THREADS) {
@@ -2132,7 +2151,10 @@ void launch_img_chunks(const ProblemView& pv, const double* pose, const double* 
   // CTAs of lookahead of the L2 prefetch (0: off); the environment is read once per process
   static const int prefetch_ahead = getenv("MPBA_IMG_PREFETCH") ? atoi(getenv("MPBA_IMG_PREFETCH")) : MPBA_IMG_PREFETCH_DEFAULT;
   if (pv.num_chunks > 0)
-    k_img_chunks<<<pv.num_chunks, IMG_THREADS, 0, st>>>(pv, pose, X, chunk_part, prefetch_ahead);
+    if (pv.cm_plane)
+      k_img_chunks<true><<<pv.num_chunks, IMG_THREADS, 0, st>>>(pv, pose, X, chunk_part, prefetch_ahead);
+    else
+      k_img_chunks<false><<<pv.num_chunks, IMG_THREADS, 0, st>>>(pv, pose, X, chunk_part, prefetch_ahead);
 }
 void launch_img_finalize(const ProblemView& pv, const double* chunk_part, double* Hc, double* gc, double* img_part,
                          cudaStream_t st) {
@@ -2176,13 +2198,16 @@ void launch_points(const ProblemView& pv, const double* pose, const double* X, L
     bulk_grid = sms * MPBA_POINTS_MINB;
   }
   const int groups = track_warp_grid(pv.num_track_warps);
-  if (pv.num_track_warps > 0 && bulk && !force_warp)
+  if (pv.num_track_warps > 0 && bulk && !force_warp && !pv.pm_plane)
     k_points_bulk<<<groups < bulk_grid ? groups : bulk_grid, PW_THREADS, PB_SMEM, st>>>(
         pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv, fac, pt_part, scal, write_factors,
         groups);
+  else if (pv.num_track_warps > 0 && pv.pm_plane)
+    k_points<true><<<groups, PW_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv,
+                                                  Linv, fac, pt_part, scal, write_factors, force_warp, prefetch_ahead);
   else if (pv.num_track_warps > 0)
-    k_points<<<groups, PW_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv, Linv,
-                                            fac, pt_part, scal, write_factors, force_warp, prefetch_ahead);
+    k_points<false><<<groups, PW_THREADS, 0, st>>>(pv, pose, X, lm, c_pt, compute_scaling, jacobi_scaling, Hpp, gp, Hinv,
+                                                   Linv, fac, pt_part, scal, write_factors, force_warp, prefetch_ahead);
 }
 void launch_pt_scalars_gmax(const double* pt_part, int nblk, double* scal, cudaStream_t st) {
   k_pt_scalars_gmax<<<1, 1024, 0, st>>>(pt_part, nblk, scal);

@@ -63,6 +63,8 @@ struct ProblemView {
   const int32_t* cm_pt;
   const double* cm_xy;
   const double* cm_depth;
+  const double* pm_plane;  // [N][4] normal-prior rows (extension, mpba.h) or nullptr; selects the <PLANE> kernels
+  const double* cm_plane;
   const int32_t* chunk_img;
   const int32_t* chunk_begin;
   const int32_t* chunk_end;

@@ -313,6 +313,10 @@ int check_problem(mpba_handle* h, const mpba_problem* p) {
     return fail(h, MPBA_E_INVALID, "track_warp_first missing (mpba_pack_tracks)");
   if (p->reproj_loss < 0 || p->reproj_loss > 3 || p->depth_loss < 0 || p->depth_loss > 3)
     return fail(h, MPBA_E_INVALID, "unknown loss type");
+  if ((p->pm_plane == nullptr) != (p->cm_plane == nullptr))
+    return fail(h, MPBA_E_INVALID, "normal-prior rows: pm_plane and cm_plane must both be given or both be NULL");
+  if (p->pm_plane && !(p->plane_loss_scale > 0.0))
+    return fail(h, MPBA_E_INVALID, "normal-prior rows: plane_loss_scale must be > 0");
   return MPBA_OK;
 }
 
@@ -330,6 +334,8 @@ ProblemView view_of(const mpba_problem* p) {
   v.loss.reproj_loss = p->reproj_loss; v.loss.depth_loss = p->depth_loss;
   v.loss.reproj_scale = p->reproj_loss_scale; v.loss.reproj_weight = p->reproj_loss_weight;
   v.loss.behind_strict = 0;
+  v.pm_plane = p->pm_plane; v.cm_plane = p->cm_plane;
+  v.loss.plane_scale = p->pm_plane ? p->plane_loss_scale : 1.0;
   v.p0 = 0; v.p1 = v.P; v.i0 = 0; v.i1 = v.C;
   v.num_track_warps = p->num_track_warps; v.tw_first = p->track_warp_first;
   return v;

@@ -77,6 +77,8 @@ class MpbaProblem(C.Structure):
         ("reproj_loss_scale", C.c_double), ("reproj_loss_weight", C.c_double),
         ("flags", C.c_int32), ("s_max_row_blocks", C.c_int32),
         ("num_track_warps", C.c_int32), ("reserved", C.c_int32), ("track_warp_first", C.c_void_p),
+        # normal-prior rows (extension, include/mpba.h); NULL / 0: none
+        ("pm_plane", C.c_void_p), ("cm_plane", C.c_void_p), ("plane_loss_scale", C.c_double),
     ]
 
 
@@ -253,6 +255,10 @@ class HostLayout:
     reproj_loss_weight: float
     flags: int
     cm_pm: Optional[np.ndarray] = None  # [N] track-order slot of every image-order slot (unsharded layouts)
+    # normal-prior rows (extension, mpsfm_b200/normal_prior.py): {m, c} per slot in both orders, or None
+    pm_plane: Optional[np.ndarray] = None  # [N,4]
+    cm_plane: Optional[np.ndarray] = None  # [N,4]
+    plane_loss_scale: float = 1.0
 
     @property
     def num_blocks(self) -> int:
@@ -292,6 +298,16 @@ class MpbaHostLayoutView(C.Structure):
                     "pt_ptr", "pm_img", "pm_src", "img_ptr", "cm_pt", "cm_src", "cm_pm", "chunk_img", "chunk_begin",
                     "chunk_end", "img_chunk_ptr", "s_row_ptr", "s_col", "s_diag", "s_transpose", "s_row", "u_block",
                     "u_item_ptr", "item_a", "item_b", "track_warp_first")])
+
+
+def _plane_slots(pr: BundleProblem, pm_src, cm_src) -> dict:
+    """HostLayout fields of the normal-prior rows (extension): the {m, c} record of every slot in both orders."""
+    if not pr.num_plane:
+        return {}
+    full = np.zeros((pr.num_obs, 4))
+    full[pr.plane_obs, :3], full[pr.plane_obs, 3] = pr.plane_m, pr.plane_c
+    return {"pm_plane": np.ascontiguousarray(full[pm_src]), "cm_plane": np.ascontiguousarray(full[cm_src]),
+            "plane_loss_scale": float(pr.plane_loss_scale)}
 
 
 def build_layout(problem: BundleProblem) -> HostLayout:
@@ -356,7 +372,7 @@ def build_layout(problem: BundleProblem) -> HostLayout:
         pm_xy=vals["pm"][0], pm_depth=vals["pm"][1], cm_xy=vals["cm"][0], cm_depth=vals["cm"][1],
         reproj_loss=int(pr.reproj_loss), depth_loss=int(pr.depth_loss),
         reproj_loss_scale=float(pr.reproj_loss_scale), reproj_loss_weight=float(pr.reproj_loss_weight),
-        flags=FLAG_STRUCTURE_ONLY if structure_only else 0, **idx)
+        flags=FLAG_STRUCTURE_ONLY if structure_only else 0, **_plane_slots(pr, idx["pm_src"], idx["cm_src"]), **idx)
 
 
 def build_layout_numpy(problem: BundleProblem) -> HostLayout:
@@ -459,7 +475,7 @@ def build_layout_numpy(problem: BundleProblem) -> HostLayout:
     pm_pos[pm_src] = np.arange(N, dtype=np.int32)
 
     return HostLayout(
-        cm_pm=pm_pos[cm_src],
+        cm_pm=pm_pos[cm_src], **_plane_slots(pr, pm_src, cm_src),
         C=Cn, K=K, P=P, N=N,
         img_pose=pose, img_camera=pr.img_camera, img_free_mask=pr.img_free_mask,
         img_shift_scale=np.ascontiguousarray(pr.shift_scale), cam_model=pr.cam_model, cam_params=params,
@@ -551,6 +567,8 @@ def shard_layout(lay: HostLayout, rank: int, world: int):
         chunk_end=(lay.chunk_end[ch0:ch1].astype(np.int64) - c0).astype(np.int32),
         img_chunk_ptr=np.clip(lay.img_chunk_ptr.astype(np.int64) - ch0, 0, ch1 - ch0).astype(np.int32),
         u_item_ptr=u_item_ptr, item_a=item_a, item_b=item_b, cm_pm=None,
+        pm_plane=None if lay.pm_plane is None else pad1(lay.pm_plane[s0:s1]),
+        cm_plane=None if lay.cm_plane is None else pad1(lay.cm_plane[c0:c1]),
     )
     out.track_warp_first = pack_tracks(out.pt_ptr, spec.pt_begin, spec.pt_end)
     return out, spec
@@ -653,6 +671,14 @@ class BundleAdjuster:
                     self.host[name] = t
                 self.buf[name] = t.to(self.device, non_blocking=pinned)
                 self.h2d_bytes += arr.nbytes
+            if lay.pm_plane is not None:
+                for name in ("pm_plane", "cm_plane"):
+                    t = torch.from_numpy(np.ascontiguousarray(getattr(lay, name)))
+                    if pinned:
+                        t = t.pin_memory()
+                        self.host[name] = t
+                    self.buf[name] = t.to(self.device, non_blocking=pinned)
+                    self.h2d_bytes += t.numel() * 8
             if self._derive_cm:
                 if lay.cm_pm is not None:
                     cm_pm = lay.cm_pm
@@ -693,6 +719,9 @@ class BundleAdjuster:
             self.prob.reproj_loss, self.prob.depth_loss = lay.reproj_loss, lay.depth_loss
             self.prob.reproj_loss_scale, self.prob.reproj_loss_weight = lay.reproj_loss_scale, lay.reproj_loss_weight
             self.prob.flags = lay.flags
+            if lay.pm_plane is not None:
+                self.prob.pm_plane, self.prob.cm_plane = self.buf["pm_plane"].data_ptr(), self.buf["cm_plane"].data_ptr()
+                self.prob.plane_loss_scale = lay.plane_loss_scale
             self.prob.s_max_row_blocks = int(np.max(np.diff(lay.s_row_ptr))) if lay.C else 0
             nbytes = C.c_size_t()
             if self.shard is not None:

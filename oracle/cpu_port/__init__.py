@@ -88,6 +88,10 @@ def solve(layout, max_num_iterations: int = 50, pcg_tolerance: float = 1e-10, nu
     prob.reproj_loss, prob.depth_loss = layout.reproj_loss, layout.depth_loss
     prob.reproj_loss_scale, prob.reproj_loss_weight = layout.reproj_loss_scale, layout.reproj_loss_weight
     prob.flags = layout.flags
+    if getattr(layout, "pm_plane", None) is not None:  # normal-prior rows (extension)
+        keep["pm_plane"], keep["cm_plane"] = np.ascontiguousarray(layout.pm_plane), np.ascontiguousarray(layout.cm_plane)
+        prob.pm_plane, prob.cm_plane = keep["pm_plane"].ctypes.data, keep["cm_plane"].ctypes.data
+        prob.plane_loss_scale = layout.plane_loss_scale
     opt = engine.MpbaOptions(
         max_num_iterations=max_num_iterations, max_num_consecutive_invalid_steps=5, jacobi_scaling=1,
         pcg_max_iterations=50000, initial_trust_region_radius=1e4, max_trust_region_radius=1e16,

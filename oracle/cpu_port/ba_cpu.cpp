@@ -72,7 +72,7 @@ void image_pass(const mpba_problem* p, const LossSpec& ls, const double* pose, c
       ObsLin o;
       linearize_obs<true, true>(ic.pose, ic.R, X + 4 * (size_t)pt, ic.model, ic.prm, p->cm_xy[2 * (size_t)k],
                                 p->cm_xy[2 * (size_t)k + 1], p->cm_depth[k], p->cm_depth[N + k], p->cm_depth[2 * N + k],
-                                ic.b, ic.es, ls, o);
+                                ic.b, ic.es, ls, o, p->cm_plane ? p->cm_plane + 4 * (size_t)k : nullptr);
       double H[21], g[6];
       gt_n_g_upper(o.prot, o.N, H);
       gt_vec(o.prot, o.h, g);
@@ -110,7 +110,8 @@ void points_pass(const mpba_problem* p, const LossSpec& ls, const double* pose, 
         ObsLin o;
         linearize_obs<true, false>(ic.pose, ic.R, X + 4 * (size_t)pt, ic.model, ic.prm, p->pm_xy[2 * (size_t)k],
                                    p->pm_xy[2 * (size_t)k + 1], p->pm_depth[k], p->pm_depth[N + k],
-                                   p->pm_depth[2 * N + k], ic.b, ic.es, ls, o);
+                                   p->pm_depth[2 * N + k], ic.b, ic.es, ls, o,
+                                   p->pm_plane ? p->pm_plane + 4 * (size_t)k : nullptr);
         double* Q = &Qs[(size_t)(k - beg) * 12];
         sym3_mul_mat(o.N, ic.R, Q);
         const double* R = ic.R;
@@ -546,6 +547,7 @@ extern "C" int ba_cpu_solve(const mpba_problem* prob, const mpba_options* opt_in
   const size_t C = p->num_images, P = p->num_points, N = p->num_obs, B = p->num_blocks;
   const bool structure_only = (p->flags & MPBA_FLAG_STRUCTURE_ONLY) != 0;
   LossSpec ls{p->reproj_loss, p->depth_loss, p->reproj_loss_scale, p->reproj_loss_weight};
+  ls.plane_scale = p->pm_plane ? p->plane_loss_scale : 1.0;
   std::vector<double> pose[2] = {std::vector<double>(C * 8), std::vector<double>(C * 8)};
   std::vector<double> X[2] = {std::vector<double>(P * 4), std::vector<double>(P * 4)};
   std::vector<double> Hc[2] = {std::vector<double>(C * 21), std::vector<double>(C * 21)};

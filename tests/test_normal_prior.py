@@ -118,3 +118,41 @@ def test_product_arithmetic_matches_the_definition(hostcheck, model, depth_loss)
     # without Jacobians: same cost
     q0 = ke.obs_quantities(hostcheck, prob, st.q, st.t, st.X, want_jac=False)
     assert np.array_equal(q0["rho"], q["rho"])
+
+
+def test_layout_carries_the_plane_records_in_both_orders():
+    from mpsfm_b200 import engine
+
+    prob = _scene()
+    for lay in (engine.build_layout(prob), engine.build_layout_numpy(prob)):
+        full = np.zeros((prob.num_obs, 4))
+        full[prob.plane_obs, :3], full[prob.plane_obs, 3] = prob.plane_m, prob.plane_c
+        assert np.array_equal(lay.pm_plane, full[lay.pm_src]) and np.array_equal(lay.cm_plane, full[lay.cm_src])
+        assert lay.plane_loss_scale == prob.plane_loss_scale
+    plain = engine.build_layout(dataclass_without_planes(prob))
+    assert plain.pm_plane is None and plain.cm_plane is None
+    # shards carry their own slots
+    sh, spec = engine.shard_layout(engine.build_layout(prob), 1, 2)
+    lay = engine.build_layout(prob)
+    s0, s1 = int(lay.pt_ptr[spec.pt_begin]), int(lay.pt_ptr[spec.pt_end])
+    c0, c1 = int(lay.img_ptr[spec.img_begin]), int(lay.img_ptr[spec.img_end])
+    assert np.array_equal(sh.pm_plane[: s1 - s0], lay.pm_plane[s0:s1])
+    assert np.array_equal(sh.cm_plane[: c1 - c0], lay.cm_plane[c0:c1])
+
+
+def test_cpu_port_with_plane_rows_follows_the_oracle_trajectory():
+    """The CPU port runs the product's linearize_obs: the whole LM trajectory with the extra rows against the oracle's."""
+    from mpsfm_b200 import engine
+    from oracle import cpu_port
+
+    prob = normal_prior.synthetic_normal_priors(make_scene(14, 700, 5, seed=9, model=CameraModel.SIMPLE_RADIAL,
+                                                           depth_frac=0.7), frac=0.6, seed=2)
+    osum = lm.solve(prob)
+    base = lm.solve(dataclass_without_planes(prob))
+    summ, q, t, X = cpu_port.solve(engine.build_layout(prob))
+    assert summ["num_iterations"] == len(osum.iterations) - 1
+    oc = np.array([it.cost for it in osum.iterations])
+    assert np.max(np.abs(np.array(summ["costs"]) - oc) / oc) <= 1e-6
+    assert np.max(np.abs(t - osum.state.t)) < 1e-6 and np.max(np.abs(X - osum.state.X)) < 1e-6
+    # the rows do something: another optimum than without them
+    assert np.max(np.abs(osum.state.X - base.state.X)) > 1e-4
