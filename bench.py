@@ -423,6 +423,7 @@ def run_gpu(args):
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": ab[top],
                 "avg_launch_ms": ms / n, "frac_of_nominal_8TBps": achieved / 8000.0}
 
+    extension = normal_prior_extension(args, prob, local, opt, opt_prof) if (world == 1 and not args.no_extension) else None
     cpu = (cpu_baseline_sample(args.workload, layout=full, problem=prob, pcg_tol=args.pcg_tol, budget_s=args.ref_budget)
            if (world == 1 and not args.no_cpu_baseline) else None)
     C_, P_, L_ = CONFIGS[args.workload]
@@ -454,8 +455,46 @@ def run_gpu(args):
         "roofline": roof,
         "kernels": per_kernel,
         "cpu_baseline": cpu,
+        "extension": extension,
     }
     print(json.dumps(line))
+
+
+def normal_prior_extension(args, prob, device, opt, opt_prof):
+    """The workload with the normal-prior rows switched on (EXTENSION, parity n/a: the reference has no such residual --
+    SURVEY.md section 8 row a-9, oracle/residuals.py defines it), timed apart from the headline: same scene, a
+    point-to-plane row on half of the depth-prior observations, resident inputs, the same K steps."""
+    import torch
+
+    from mpsfm_b200 import engine, normal_prior
+
+    t0 = time.perf_counter()
+    pn = normal_prior.synthetic_normal_priors(prob, frac=0.5, seed=0)
+    t_rows = time.perf_counter() - t0
+    ba = engine.BundleAdjuster(pn, device=device)
+    for _ in range(args.warmup):
+        ba.reset_state()
+        ba.solve(opt)
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    iters = 0
+    ev0.record()
+    for _ in range(args.steps):
+        ba.reset_state()
+        s = ba.solve(opt)
+        iters += s.num_iterations
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    ba.reset_state()
+    ba.solve(opt_prof)
+    kt = {k: round(1e3 * v[0] / max(v[1], 1), 2) for k, v in ba.kernel_times().items() if k in ("img_chunks", "points")}
+    ba.close()
+    return {"normal_prior": {
+        "note": "extension, parity n/a (no such residual upstream); not part of `value`",
+        "value": iters / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / args.steps, "rows": int(pn.num_plane),
+        "lm_iterations_per_solve": s.num_iterations, "final_cost": s.final_cost, "termination": s.message,
+        "extra_bytes_per_observation": 64, "avg_us": kt, "host_rows_s": round(t_rows, 2)}}
 
 
 def main():
@@ -472,6 +511,8 @@ def main():
     ap.add_argument("--ref-total", dest="ref_total", type=float, default=150.0,
                     help="reference arm: seconds all its steps together may take (bounds --ref-budget per step)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extension", dest="no_extension", action="store_true",
+                    help="skip the separate normal-prior (extension) measurement")
     ap.add_argument("--e2e-serial", dest="e2e_serial", action="store_true",
                     help="end-to-end steps strictly one after the other (no overlap of the next upload with the solve)")
     ap.add_argument("--sharding", default="shard", choices=["shard", "replicas"])

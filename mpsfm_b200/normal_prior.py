@@ -101,15 +101,17 @@ def with_normal_priors(problem: BundleProblem, obs, normals_cam, weight, loss_sc
                                plane_loss_scale=float(loss_scale)).normalized()
 
 
-def synthetic_normal_priors(problem: BundleProblem, frac: float = 0.5, seed: int = 0, sigma: float = 0.05,
+def synthetic_normal_priors(problem: BundleProblem, frac: float = 0.5, seed: int = 0, rel_sigma: float = 0.05,
                             loss_scale: float = 2.0, tilt: float = 0.6) -> BundleProblem:
     """Seeded normal priors on a fraction of the depth-prior observations of a synthetic scene: normals facing the
-    camera, tilted by up to ``tilt`` rad off the viewing ray; weight 1 / sigma^2 with ``sigma`` a plane distance in
-    scene units; ``loss_scale`` in units of sigma."""
+    camera, tilted by up to ``tilt`` rad off the optical axis; plane-distance std ``rel_sigma`` x the prior depth (the
+    order of the scenes' depth noise, so the rows sit at ~1 sigma at the optimum); ``loss_scale`` in units of sigma."""
     rng = np.random.Generator(np.random.PCG64(seed + 9176))
-    pick = problem.depth_obs[rng.random(problem.num_depth) < frac]
+    keep = rng.random(problem.num_depth) < frac
+    pick = problem.depth_obs[keep]
     n = pick.shape[0]
     axis = rng.normal(size=(n, 3))
     axis /= np.linalg.norm(axis, axis=1, keepdims=True)
     normals = np.array([0.0, 0.0, -1.0]) + np.tan(rng.uniform(0, tilt, size=(n, 1))) * axis * np.array([1.0, 1.0, 0.0])
+    sigma = rel_sigma * problem.depth_d[keep]
     return with_normal_priors(problem, pick, normals, 1.0 / sigma**2, loss_scale)

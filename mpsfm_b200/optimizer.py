@@ -95,7 +95,12 @@ class Optimizer(BaseClass):
                 # (mpba_segmented_median) instead of per-image numpy
                 "stats_on_device": False,
                 # under torchrun: shard every solve over the ranks' GPUs (mpba_solve_sharded)
-                "sharded": False},
+                "sharded": False,
+                # EXTENSION, off by default (nothing upstream does this): one
+                # point-to-plane row per depth-prior observation of an image that has monocular normals
+                # (mpsfm_b200/normal_prior.py).  rel_sigma: plane-distance std as a fraction of the prior depth;
+                # loss_scale: scale of the depth loss on the whitened row
+                "normal_prior": {"enabled": False, "rel_sigma": 0.02, "loss_scale": 2.0}},
     }
 
     def _sample_bundle_on_device(self, optim_ids, img_p2ds, depth_type):
@@ -295,6 +300,9 @@ class Optimizer(BaseClass):
         # --- depth-prior residual blocks (:124-176)
         depth_rows = {}
         d_obs, d_d, d_w, d_a = [], [], [], []
+        np_conf = conf.gpu.get("normal_prior", None) or {}
+        want_normals = bool(np_conf.get("enabled", False)) and with_depth
+        n_obs, n_vec, n_depth = [], [], []
         pm = param_multiplier * self.truncation_multiplier  # :109
         sampled = self._sample_bundle_on_device(optim_ids, img_p2ds, depth_type) if with_depth else None
         if with_depth:
@@ -344,6 +352,20 @@ class Optimizer(BaseClass):
                 d_d.append(depths)
                 d_w.append(magnitudes)
                 d_a.append(params)
+                normals = getattr(rec.images[imid], "normals", None) if want_normals else None
+                if normals is not None and getattr(normals, "data", None) is not None:
+                    # nearest pixel of the normal map at the keypoint (the reference's bilinear sampler,
+                    # priorutils.py:49-62, is single-channel); rows with a degenerate normal are left out
+                    nmap = np.asarray(normals.data, dtype=np.float64)
+                    cam = rec.images[imid].depth.camera
+                    kps = np.asarray(rec.images[imid].keypoint_coordinates(p2Ds), dtype=np.float64).reshape(-1, 2)
+                    col = np.clip(np.rint(kps[:, 0] * cam.sx).astype(np.int64), 0, nmap.shape[1] - 1)
+                    row = np.clip(np.rint(kps[:, 1] * cam.sy).astype(np.int64), 0, nmap.shape[0] - 1)
+                    vec = nmap[row, col]
+                    ok = np.isfinite(vec).all(axis=1) & (np.linalg.norm(vec, axis=1) > 1e-6)
+                    n_obs.append((img_obs_offset[imid] + pos)[ok])
+                    n_vec.append(vec[ok])
+                    n_depth.append(depths[ok])
 
         problem = BundleProblem(
             img_q=img_q, img_t=img_t,
@@ -363,6 +385,12 @@ class Optimizer(BaseClass):
         )
         if not fix_scale:
             raise NotImplementedError("fix_scale=False is never used by the reference's call sites (:263-283)")
+        if n_obs and sum(a.size for a in n_obs):
+            from . import normal_prior
+
+            sigma = float(np_conf.get("rel_sigma", 0.02)) * np.concatenate(n_depth)
+            problem = normal_prior.with_normal_priors(problem, np.concatenate(n_obs), np.concatenate(n_vec),
+                                                      1.0 / sigma**2, float(np_conf.get("loss_scale", 2.0)))
         return Assembly(problem=problem, image_ids=image_ids, num_optim_images=len(optim_ids), point_ids=point_ids,
                         obs_image_id=obs_img_id, obs_point2D_idx=obs_p2d, obs_point3D_id=obs_p3d,
                         depth_rows=depth_rows, kp_std=kp_std, variable_points=variable_points)

@@ -153,6 +153,14 @@ class Depth:
         return self._data_at_kps(kps, self.valid) == 1
 
 
+class Normals:
+    """The attribute of /root/reference/mpsfm/sfm/scene/image/normals.py the normal-prior extension reads: ``data``,
+    the [H,W,3] unit normals of the monocular network in the camera frame, on the depth map's grid."""
+
+    def __init__(self, data):
+        self.data = np.array(data, dtype=np.float64)
+
+
 class Image:
     def __init__(self, image_id, camera_id, cam_from_world, keypoints, kp_std=1.0, name=None):
         self.image_id, self.camera_id = image_id, camera_id
@@ -161,6 +169,7 @@ class Image:
         self.kp_std = kp_std
         self.name = name or f"im{image_id}.jpg"
         self.depth = None
+        self.normals = None
 
     # --- fork API used by the reference (bundle_adjustment.py:52-54, :126-136)
     def get_observation_point2D_idxs(self):

@@ -124,3 +124,19 @@ def build_scene(seed=0, num_images=8, num_points=300, track_len=4, extra_kps=25,
                             np.array([p.xy for p in im.points2D]).reshape(-1, 2))
         im.depth.data = im.depth.data_prior * (1.0 + 0.01 * np.cos(gx / 400.0))  # "integrated" depth differs from the prior
     return rec
+
+
+def attach_normals(rec):
+    """Monocular normals for every image, derived from its own prior depth map the way a geometry network's output
+    relates to it: n ~ d(p)/dx x d(p)/dy of the back-projected grid p = depth * ray, oriented towards the camera."""
+    cam = rec.rec.cameras[1]
+    for im in rec.images.values():
+        depth = im.depth.data_prior
+        H, W = depth.shape
+        gx, gy = np.meshgrid(np.arange(W) / cam.sx, np.arange(H) / cam.sy)
+        p = depth[..., None] * np.stack([(gx - WIDTH / 2) / F, (gy - HEIGHT / 2) / F, np.ones_like(gx)], axis=-1)
+        n = np.cross(np.gradient(p, axis=1), np.gradient(p, axis=0))
+        n /= np.maximum(np.linalg.norm(n, axis=-1, keepdims=True), 1e-300)
+        n[n[..., 2] > 0] *= -1.0
+        im.normals = fs.Normals(n)
+    return rec

@@ -121,3 +121,30 @@ def test_bad_plane_arguments_are_rejected():
         ba.solve()
     ba.prob.cm_plane = keep
     assert ba.solve().termination == "CONVERGENCE"
+
+
+def test_optimizer_ba_with_the_option_follows_the_oracle():
+    import copy
+    import sys
+
+    sys.path.insert(0, __file__.rsplit("/", 1)[0])
+    from mpsfm_b200.optimizer import Optimizer
+    from scene_factory import attach_normals, build_scene
+
+    rec = attach_normals(build_scene(seed=11, num_images=8, num_points=260))
+    conf = {"gpu": {"normal_prior": {"enabled": True, "rel_sigma": 0.05}}}
+    bundle = {"optim_ids": [2, 1, 3, 4, 5, 6, 7, 8], "pts3D": set(rec.points3D)}
+    opt = Optimizer(conf, rec, None)
+    opt.update_truncation_multiplier(rec.reg_image_ids())
+    opt_o = Optimizer(conf, copy.deepcopy(rec), None)
+    opt_o.truncation_multiplier = opt.truncation_multiplier
+    asm_o = opt_o.assemble(bundle, fix_pose=False, mode="global", allow_scale_filter=True)
+    assert asm_o.problem.num_plane > 0
+    osum = lm.solve(asm_o.problem)
+    out, ok = opt.ba(bundle, mode="global", allow_scale_filter=True)
+    assert ok is True
+    summ = opt.last_summary
+    assert summ.num_iterations == len(osum.iterations) - 1
+    assert abs(summ.final_cost - osum.final_cost) <= 1e-6 * osum.final_cost
+    for k, pid in enumerate(opt.last_assembly.point_ids):
+        assert np.max(np.abs(rec.points3D[int(pid)].xyz - osum.state.X[k])) < 1e-6

@@ -48,7 +48,7 @@ def test_plane_rows_vanish_on_the_prior_surface():
     q = prob.depth_d[k][:, None] * np.concatenate([uv, np.ones((o.size, 1))], axis=1)
     assert np.all(cam == 0)
     assert np.max(np.abs(np.einsum("ni,ni->n", prob.plane_m, q) - prob.plane_c)) < 1e-9
-    assert np.allclose(np.linalg.norm(prob.plane_m, axis=1), 1.0 / 0.05)
+    assert np.allclose(np.linalg.norm(prob.plane_m, axis=1), 1.0 / (0.05 * prob.depth_d[k]))
     with pytest.raises(ValueError):
         no_depth = np.setdiff1d(np.arange(prob.num_obs), prob.depth_obs)[:3]
         normal_prior.plane_rows(prob, no_depth, np.tile([0, 0, -1.0], (3, 1)), 1.0)
@@ -156,3 +156,38 @@ def test_cpu_port_with_plane_rows_follows_the_oracle_trajectory():
     assert np.max(np.abs(t - osum.state.t)) < 1e-6 and np.max(np.abs(X - osum.state.X)) < 1e-6
     # the rows do something: another optimum than without them
     assert np.max(np.abs(osum.state.X - base.state.X)) > 1e-4
+
+
+def test_optimizer_option_adds_rows_for_images_with_normals():
+    """``gpu.normal_prior.enabled`` (off by default): the assembled problem gains one row per depth-prior observation of
+    the images that carry a normal map; everything else of the assembly is unchanged."""
+    from mpsfm_b200.optimizer import Optimizer
+    from scene_factory import attach_normals, build_scene
+
+    rec = attach_normals(build_scene(seed=11, num_images=8, num_points=260))
+    rec.images[3].normals = None  # one image without a normal map
+    bundle = {"optim_ids": [2, 1, 3, 4, 5, 6, 7, 8], "pts3D": set(rec.points3D)}
+    off = Optimizer({}, rec, None)
+    off.update_truncation_multiplier(rec.reg_image_ids())
+    on = Optimizer({"gpu": {"normal_prior": {"enabled": True, "rel_sigma": 0.05}}}, rec, None)
+    on.truncation_multiplier = off.truncation_multiplier
+    a0 = off.assemble(bundle, fix_pose=False, mode="global", allow_scale_filter=True).problem
+    a1 = on.assemble(bundle, fix_pose=False, mode="global", allow_scale_filter=True).problem
+    assert a0.num_plane == 0 and a1.num_plane > 0
+    for f in ("obs_img", "obs_pt", "obs_xy", "depth_obs", "depth_d", "depth_w", "depth_a", "img_q", "img_t", "pt_xyz"):
+        assert np.array_equal(getattr(a0, f), getattr(a1, f)), f
+    row3 = [2, 1, 3, 4, 5, 6, 7, 8].index(3)
+    with_map = a1.depth_obs[a1.obs_img[a1.depth_obs] != row3]
+    assert np.array_equal(np.sort(a1.plane_obs), np.sort(with_map))
+    k = np.searchsorted(a1.depth_obs, a1.plane_obs)
+    assert np.allclose(np.linalg.norm(a1.plane_m, axis=1), 1.0 / (0.05 * a1.depth_d[k]))
+    assert np.all(a1.plane_m[:, 2] < 0)  # facing the camera
+    # the oracle solves it, and the planes pull: another optimum, points closer to the prior surface
+    s0, s1 = lm.solve(a0), lm.solve(a1)
+    assert s1.termination == "CONVERGENCE"
+
+    def plane_rms(sol):
+        pc = geometry.quat_rotate(sol.state.q[a1.obs_img], sol.state.X[a1.obs_pt]) + sol.state.t[a1.obs_img]
+        return float(np.sqrt(np.mean((np.einsum("ni,ni->n", a1.plane_m, pc[a1.plane_obs]) - a1.plane_c) ** 2)))
+
+    assert plane_rms(s1) < plane_rms(s0)
