@@ -75,12 +75,17 @@ constexpr int IMG_WARPS = IMG_THREADS / 32;
 #define MPBA_IMG_MINB 3
 #endif
 #ifndef MPBA_IMG_PREFETCH_DEFAULT
-#define MPBA_IMG_PREFETCH_DEFAULT 444  // one wave: 148 SMs x 3 CTAs
+#define MPBA_IMG_PREFETCH_DEFAULT 740  // one wave: 148 SMs x 5 CTAs
 #endif
 // PLANE: the problem carries normal-prior rows (extension, ba_math.cuh: linearize_obs); the default instantiation
 // is the kernel without them, instruction for instruction
-template <bool PLANE>
-__global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(ProblemView pv, const double* __restrict__ pose,
+// SACC (the default; MPBA_IMG_SMEM_ACC=0 selects the register variant for comparison): the 29 per-thread accumulators
+// live in shared memory ([29][threads], conflict free) instead of 58 registers and the next observation's operands are
+// not double-buffered in registers: 96 registers, five CTAs per SM instead of three at 168 -- the kernel is bound by
+// the latency of its FP64 chains (ncu: fp64 pipe 33 % busy, 12 warps per SM), so the extra warps pay: 247 -> 202 us at
+// cfg3 (profiles/r02_img_chunks_variants.md; 4 CTAs with the double buffer 214, 6 CTAs 224, 7 CTAs 270)
+template <bool PLANE, bool SACC>
+__global__ void __launch_bounds__(IMG_THREADS, SACC ? 5 : MPBA_IMG_MINB) k_img_chunks(ProblemView pv, const double* __restrict__ pose,
                                                     const double* __restrict__ X, double* __restrict__ chunk_part,
                                                     int prefetch_ahead) {
   const int c = blockIdx.x;
@@ -98,8 +103,12 @@ __global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(Probl
   const size_t N = (size_t)pv.N;
 
   double acc[29];
+  __shared__ double s_acc[SACC ? 29 : 1][SACC ? IMG_THREADS : 1];
 #pragma unroll
-  for (int j = 0; j < 29; ++j) acc[j] = 0.0;
+  for (int j = 0; j < 29; ++j) {
+    acc[j] = 0.0;
+    if (SACC) s_acc[SACC ? j : 0][SACC ? threadIdx.x : 0] = 0.0;
+  }
 
   // Software pipeline: the operands of the thread's NEXT observation (index -> point gather, xy, depth row) are
   // in flight while the current one is linearised -- with 12 warps per SM (168 registers, three 128-thread CTAs)
@@ -124,11 +133,13 @@ __global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(Probl
       op.pl[0] = p0.x; op.pl[1] = p0.y; op.pl[PLANE ? 2 : 0] = p1.x; op.pl[PLANE ? 3 : 0] = p1.y;
     }
   };
+  constexpr bool PIPE = !SACC;  // SACC: no register double buffer, five CTAs per SM hide the gathers
   int k = beg + (int)threadIdx.x;
   Operands cur, nxt;
-  if (k < end) fetch(k, cur);
+  if (PIPE && k < end) fetch(k, cur);
   for (; k < end; k += IMG_THREADS) {
-    const bool more = k + IMG_THREADS < end;
+    const bool more = PIPE && k + IMG_THREADS < end;
+    if (!PIPE) fetch(k, cur);
     if (more) fetch(k + IMG_THREADS, nxt);
     const double Xp[3] = {cur.xa.x, cur.xa.y, cur.xb.x};
     ObsLin o;
@@ -137,13 +148,26 @@ __global__ void __launch_bounds__(IMG_THREADS, MPBA_IMG_MINB) k_img_chunks(Probl
     double H[21], g[6];
     gt_n_g_upper(o.prot, o.N, H);
     gt_vec(o.prot, o.h, g);
-#pragma unroll
-    for (int j = 0; j < 21; ++j) acc[j] += H[j];
-#pragma unroll
-    for (int j = 0; j < 6; ++j) acc[21 + j] += g[j];
     const bool fixed = img_const && (cur.xb.y != 0.0);
-    if (fixed) acc[28] += o.rho; else acc[27] += o.rho;
+    if (SACC) {
+      const int t = SACC ? threadIdx.x : 0;
+#pragma unroll
+      for (int j = 0; j < 21; ++j) s_acc[SACC ? j : 0][t] += H[j];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) s_acc[SACC ? 21 + j : 0][t] += g[j];
+      s_acc[SACC ? (fixed ? 28 : 27) : 0][t] += o.rho;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 21; ++j) acc[j] += H[j];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) acc[21 + j] += g[j];
+      if (fixed) acc[28] += o.rho; else acc[27] += o.rho;
+    }
     if (more) cur = nxt;
+  }
+  if (SACC) {
+#pragma unroll
+    for (int j = 0; j < 29; ++j) acc[j] = s_acc[SACC ? j : 0][SACC ? threadIdx.x : 0];
   }
 
   __shared__ double sm[IMG_WARPS][IMG_PART];
@@ -2150,11 +2174,16 @@ __global__ void k_expand_hcc(int C, const double* __restrict__ Hc, double* __res
 void launch_img_chunks(const ProblemView& pv, const double* pose, const double* X, double* chunk_part, cudaStream_t st) {
   // CTAs of lookahead of the L2 prefetch (0: off); the environment is read once per process
   static const int prefetch_ahead = getenv("MPBA_IMG_PREFETCH") ? atoi(getenv("MPBA_IMG_PREFETCH")) : MPBA_IMG_PREFETCH_DEFAULT;
-  if (pv.num_chunks > 0)
-    if (pv.cm_plane)
-      k_img_chunks<true><<<pv.num_chunks, IMG_THREADS, 0, st>>>(pv, pose, X, chunk_part, prefetch_ahead);
-    else
-      k_img_chunks<false><<<pv.num_chunks, IMG_THREADS, 0, st>>>(pv, pose, X, chunk_part, prefetch_ahead);
+  static const bool sacc = !(getenv("MPBA_IMG_SMEM_ACC") && atoi(getenv("MPBA_IMG_SMEM_ACC")) == 0);
+  if (pv.num_chunks <= 0) return;
+  if (pv.cm_plane && sacc)
+    k_img_chunks<true, true><<<pv.num_chunks, IMG_THREADS, 0, st>>>(pv, pose, X, chunk_part, prefetch_ahead);
+  else if (pv.cm_plane)
+    k_img_chunks<true, false><<<pv.num_chunks, IMG_THREADS, 0, st>>>(pv, pose, X, chunk_part, prefetch_ahead);
+  else if (sacc)
+    k_img_chunks<false, true><<<pv.num_chunks, IMG_THREADS, 0, st>>>(pv, pose, X, chunk_part, prefetch_ahead);
+  else
+    k_img_chunks<false, false><<<pv.num_chunks, IMG_THREADS, 0, st>>>(pv, pose, X, chunk_part, prefetch_ahead);
 }
 void launch_img_finalize(const ProblemView& pv, const double* chunk_part, double* Hc, double* gc, double* img_part,
                          cudaStream_t st) {

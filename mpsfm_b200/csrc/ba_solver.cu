@@ -18,6 +18,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>  // header-only NVTX 3: no link dependency, a pointer test per call when no tool is attached
+
 #include "../../include/mpba.h"
 #include "ba_kernels.cuh"
 #include "nccl_dyn.h"
@@ -165,13 +167,23 @@ int upload_plan(mpba_handle* h, int32_t* dev, const int32_t* staged, size_t n) {
   return MPBA_OK;
 }
 
+// NVTX range for the lifetime of a scope (domain-less, named): "mpba_solve", "lm_iteration", and one per stage
+// through Timer below -- what `ncu --nvtx --nvtx-include` and timeline tools filter on
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
+
 struct Timer {
   mpba_handle* h;
   int slot;
   size_t idx = (size_t)-1;
   cudaStream_t st;
+  NvtxRange range;
   Timer(mpba_handle* h_, int slot_, int nkernels = 1, cudaStream_t st_ = nullptr, bool other = false)
-      : h(h_), slot(slot_), st(other ? st_ : h_->stream) {
+      : h(h_), slot(slot_), st(other ? st_ : h_->stream), range(kKernelNames[slot_]) {
     h->launch_count += nkernels;
     h->launches[slot] += nkernels;
     if (!h->profile) return;
@@ -1351,6 +1363,7 @@ int mpba_reduced_system(mpba_handle* h, const mpba_problem* prob, void* workspac
 
 static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard* shard, void* workspace,
                       size_t workspace_bytes, const mpba_options* opt_in, mpba_summary* sum) {
+  NvtxRange nvtx_solve(shard ? "mpba_solve_sharded" : "mpba_solve");
   Ctx c;
   int rc = begin(h, prob, workspace, workspace_bytes, c, shard);
   if (rc) return rc;
@@ -1471,6 +1484,7 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
   }
 
   while (termination < 0) {
+    NvtxRange nvtx_iteration("lm_iteration");
     const int cand = cur ^ 1;
     const LmDiag lm = make_lm(radius, opt.min_lm_diagonal, opt.max_lm_diagonal);
     rc = enqueue_lm_iteration(c, cur, cand, lm, first ? 1 : 0, opt);
