@@ -121,7 +121,8 @@ extern "C" int mpba_host_layout_create(int32_t C, int32_t P, int32_t N, const in
     return MPBA_E_INVALID;
   for (int64_t k = 0; k < N; ++k)
     if (obs_img[k] < 0 || obs_img[k] >= C || obs_pt[k] < 0 || obs_pt[k] >= P) return MPBA_E_INVALID;
-  const int threads = hw_threads();
+  // below ~64k observations every phase is shorter than the start of a thread pool
+  const int threads = N < 65536 ? 1 : hw_threads();
   mpba_host_layout* L = new mpba_host_layout();
   const bool dbg = getenv("MPBA_DEBUG") != nullptr;
   auto t_prev = std::chrono::steady_clock::now();
@@ -238,7 +239,37 @@ extern "C" int mpba_host_layout_create(int32_t C, int32_t P, int32_t N, const in
   }
   const int32_t* pm_img = L->pm_img.data();
   std::vector<int64_t> all_keys;
-  {
+  // Up to 2048 images the (image, image) -> block map is a dense C x C table (<= 16 MB, a few hundred KB for the
+  // mapper's bundles): marking and look-up are one indexed access, and a row-major scan yields the blocks sorted.
+  const bool dense_table = (int64_t)C * C <= ((int64_t)1 << 22);
+  std::vector<int32_t> table;
+  if (dense_table) {
+    table.assign((size_t)C * C, -1);
+    std::vector<std::atomic<uint8_t>> mark((size_t)C * C);
+    for (auto& m : mark) m.store(0, std::memory_order_relaxed);
+    if (n_items > 0)
+      parallel_ranges(P, threads, [&](int, int64_t pb, int64_t pe) {
+        for (int64_t p = pb; p < pe; ++p) {
+          if (pair_ptr[p + 1] == pair_ptr[p]) continue;
+          const int64_t s0 = ptr_pt[p], s1 = ptr_pt[p + 1];
+          for (int64_t a = s0; a < s1; ++a)
+            for (int64_t b = a; b < s1; ++b) {
+              const size_t i = (size_t)pm_img[a], j = (size_t)pm_img[b];
+              // test first: once a pair is marked its line stays shared between the threads' caches
+              if (!mark[i * C + j].load(std::memory_order_relaxed)) {
+                mark[i * C + j].store(1, std::memory_order_relaxed);
+                mark[j * C + i].store(1, std::memory_order_relaxed);
+              }
+            }
+        }
+      });
+    for (int64_t i = 0; i < C; ++i) mark[(size_t)(i * C + i)].store(1, std::memory_order_relaxed);
+    for (size_t k = 0; k < mark.size(); ++k)
+      if (mark[k].load(std::memory_order_relaxed)) {
+        table[k] = (int32_t)all_keys.size();
+        all_keys.push_back((int64_t)k);
+      }
+  } else {
     std::vector<std::vector<int64_t>> found((size_t)threads);
     if (n_items > 0)
       parallel_ranges(P, threads, [&](int t, int64_t pb, int64_t pe) {
@@ -271,9 +302,12 @@ extern "C" int mpba_host_layout_create(int32_t C, int32_t P, int32_t N, const in
     delete L;
     return MPBA_E_INVALID;
   }
-  KeyMap block_of;
-  block_of.init((size_t)B);
-  for (int64_t b = 0; b < B; ++b) block_of.insert(all_keys[b], (int32_t)b);
+  KeyMap block_map;
+  if (!dense_table) {
+    block_map.init((size_t)B);
+    for (int64_t b = 0; b < B; ++b) block_map.insert(all_keys[b], (int32_t)b);
+  }
+  auto block_of_find = [&](int64_t key) -> int32_t { return dense_table ? table[(size_t)key] : block_map.find(key); };
   L->s_row_ptr.assign((size_t)C + 1, 0);
   L->s_col.resize((size_t)B); L->s_row.resize((size_t)B); L->s_transpose.resize((size_t)B); L->s_diag.resize((size_t)C);
   for (int64_t b = 0; b < B; ++b) {
@@ -281,7 +315,7 @@ extern "C" int mpba_host_layout_create(int32_t C, int32_t P, int32_t N, const in
     L->s_row[b] = (int32_t)i;
     L->s_col[b] = (int32_t)j;
     ++L->s_row_ptr[i + 1];
-    L->s_transpose[b] = block_of.find(j * C + i);
+    L->s_transpose[b] = block_of_find(j * C + i);
     if (i == j) L->s_diag[i] = (int32_t)b;
     if (i <= j) L->u_block.push_back((int32_t)b);
   }
@@ -315,7 +349,7 @@ extern "C" int mpba_host_layout_create(int32_t C, int32_t P, int32_t N, const in
         for (int64_t a = s0; a < s1; ++a)
           for (int64_t b = a; b < s1; ++b, ++k) {
             const int64_t key = (int64_t)pm_img[a] * C + pm_img[b];
-            if (key != last_key) { last_key = key; last_blk = block_of.find(key); }
+            if (key != last_key) { last_key = key; last_blk = block_of_find(key); }
             item_block[k] = last_blk;
             ++c[last_blk];
           }

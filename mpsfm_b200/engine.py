@@ -300,6 +300,28 @@ class MpbaHostLayoutView(C.Structure):
                     "u_item_ptr", "item_a", "item_b", "track_warp_first")])
 
 
+class _NativeLayoutOwner:
+    """Keeps a mpba_host_layout alive while numpy views of its buffers exist."""
+
+    def __init__(self, lib, handle):
+        self._lib, self._handle = lib, handle
+
+    def __del__(self):
+        if self._handle is not None and self._handle.value:
+            self._lib.mpba_host_layout_destroy(self._handle)
+            self._handle = None
+
+
+_SCRATCH = {}
+
+
+def _scratch(name: str, n: int) -> np.ndarray:
+    buf = _SCRATCH.get(name)
+    if buf is None or buf.shape[0] < n:
+        buf = _SCRATCH[name] = np.empty(max(n, 1024) * 5 // 4, dtype=np.float64)
+    return buf[:n]
+
+
 def _plane_slots(pr: BundleProblem, pm_src, cm_src) -> dict:
     """HostLayout fields of the normal-prior rows (extension): the {m, c} record of every slot in both orders."""
     if not pr.num_plane:
@@ -334,20 +356,28 @@ def build_layout(problem: BundleProblem) -> HostLayout:
     if rc != 0:
         raise ValueError(f"mpba_host_layout_create failed with code {rc} (index out of range, or more than 2^31-1 "
                          "Schur items: shard the problem across GPUs)")
-    try:
-        def take(name, n):
-            return np.ctypeslib.as_array(getattr(view, name), shape=(n,)).copy() if n else np.zeros(0, dtype=np.int32)
+    # the index arrays are VIEWS of the native builder's buffers (no copy: at the mapper's bundle sizes the copies cost
+    # as much as building them); the owner object frees the native layout when the last array is gone
+    owner = _NativeLayoutOwner(lib, handle)
 
-        B, U = view.num_blocks, view.num_upper
-        idx = {name: take(name, n) for name, n in (
-            ("pt_ptr", P + 1), ("pm_img", N), ("pm_src", N), ("img_ptr", Cn + 1), ("cm_pt", N), ("cm_src", N), ("cm_pm", N),
-            ("chunk_img", view.num_chunks), ("chunk_begin", view.num_chunks), ("chunk_end", view.num_chunks),
-            ("img_chunk_ptr", Cn + 1), ("s_row_ptr", Cn + 1), ("s_col", B), ("s_diag", Cn), ("s_transpose", B),
-            ("s_row", B), ("u_block", U), ("u_item_ptr", U + 1), ("item_a", view.num_items),
-            ("item_b", view.num_items), ("track_warp_first", view.num_track_warps + 1))}
-    finally:
-        lib.mpba_host_layout_destroy(handle)
-    d, w, a = np.ones(N), np.zeros(N), np.ones(N)
+    def take(name, n):
+        if not n:
+            return np.zeros(0, dtype=np.int32)
+        # the ctypes array is the base object of every numpy view derived from it, and it holds the owner
+        mem = (C.c_int32 * n).from_address(C.cast(getattr(view, name), C.c_void_p).value)
+        mem._owner = owner
+        return np.frombuffer(mem, dtype=np.int32)
+
+    B, U = view.num_blocks, view.num_upper
+    idx = {name: take(name, n) for name, n in (
+        ("pt_ptr", P + 1), ("pm_img", N), ("pm_src", N), ("img_ptr", Cn + 1), ("cm_pt", N), ("cm_src", N), ("cm_pm", N),
+        ("chunk_img", view.num_chunks), ("chunk_begin", view.num_chunks), ("chunk_end", view.num_chunks),
+        ("img_chunk_ptr", Cn + 1), ("s_row_ptr", Cn + 1), ("s_col", B), ("s_diag", Cn), ("s_transpose", B),
+        ("s_row", B), ("u_block", U), ("u_item_ptr", U + 1), ("item_a", view.num_items),
+        ("item_b", view.num_items), ("track_warp_first", view.num_track_warps + 1))}
+    # d / w / a in natural order are temporaries of this call: grow-only scratch instead of 24 N bytes of fresh pages
+    d, w, a = _scratch("d", N), _scratch("w", N), _scratch("a", N)
+    d.fill(1.0), w.fill(0.0), a.fill(1.0)
     d[pr.depth_obs], w[pr.depth_obs], a[pr.depth_obs] = pr.depth_d, pr.depth_w, pr.depth_a
     obs_xy = np.ascontiguousarray(pr.obs_xy, dtype=np.float64)
     vals = {}
