@@ -1116,6 +1116,13 @@ __device__ __forceinline__ void warp_gather_records(const double2* __restrict__ 
 // reduced across the CTA (shuffle transpose + shared memory), and written once as
 //   S(i,i) = Hcc_i + D_i - T(i,i),  S(i,j) = -T(i,j),  S(j,i) = S(i,j)^T,  rhs_i = gc_i - sum G_a^T Z_a e
 // with identity rows / zero rhs on fixed tangent coordinates (gauge, bundle_adjustment.py:114-121).
+// BULK (MPBA_SCHUR_BULK=1, a measured experiment, NOT the default): every lane fetches the two records of ITS item with
+// one cp.async.bulk each (128 B and 96 B, completion on a per-warp mbarrier) instead of the warp issuing sixteen 16-byte
+// cp.async per lane with a shuffle each -- the gather is a third of the instructions of an issue-bound kernel.  Rows are
+// padded to 9 resp. 7 chunks so that lane i reading chunk c of its own row is conflict free without the XOR swizzle.
+// Same results, but 714 us against 309 us at cfg3: 30 M bulk copies of ~112 B are bound by the rate of the copy unit
+// (one per ~6.7 cycles per SM), not by the issue slots they free (profiles/r02_schur_blocks_bulk.md).
+template <bool BULK>
 __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, const double* __restrict__ fac,
                                                              const double* __restrict__ Hc,
                                                              const double* __restrict__ gc,
@@ -1142,8 +1149,35 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
   const double2* fac2 = reinterpret_cast<const double2*>(fac);
   double2* wst = stage + (size_t)warp * 2 * SB_WARP_CHUNKS;
   const int tid = threadIdx.x;
+  __shared__ uint64_t s_bar[SB_THREADS / 32][2];
+  if (BULK) {
+    if (lane == 0) {
+      pb_mbar_init(&s_bar[warp][0], 1);
+      pb_mbar_init(&s_bar[warp][1], 1);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncwarp();
+  }
   auto issue = [&](int buf, int ka, int kb) {
     double2* rows = wst + buf * SB_WARP_CHUNKS;
+    if (BULK) {
+      // rows a: [32][9] chunks (288 of the 512), rows b: [32][7] chunks from chunk 288
+      const bool hb = kb >= 0 && kb != ka;
+      const unsigned na = __popc(__ballot_sync(FULL, ka >= 0)), nb = __popc(__ballot_sync(FULL, hb));
+      if (na == 0) return;  // past the end of the item list: no phase is opened (and none is waited for)
+      if (lane == 0) pb_mbar_expect(&s_bar[warp][buf], na * 128u + nb * 96u);
+      __syncwarp();
+      const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar[warp][buf]);
+      if (ka >= 0)
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 128, [%2];" ::"r"(
+                         (unsigned)__cvta_generic_to_shared(rows + lane * 9)), "l"(fac2 + (size_t)ka * 8), "r"(bar)
+                     : "memory");
+      if (hb)
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 96, [%2];" ::"r"(
+                         (unsigned)__cvta_generic_to_shared(rows + 288 + lane * 7)), "l"(fac2 + (size_t)kb * 8), "r"(bar)
+                     : "memory");
+      return;
+    }
     warp_gather_records(fac2, ka, 8, rows, lane);
     warp_gather_records(fac2, kb == ka ? -1 : kb, 6, rows + 256, lane);  // Z and p_rot of b; e is not needed
   };
@@ -1154,7 +1188,7 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
     kb = __ldg(pv.item_b + it);
   }
   issue(0, ka, kb);
-  cp_async_commit();
+  if (!BULK) cp_async_commit();
   if (it + SB_THREADS < it1) {
     ka1 = __ldg(pv.item_a + it + SB_THREADS);
     kb1 = __ldg(pv.item_b + it + SB_THREADS);
@@ -1165,17 +1199,23 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
     const bool cur = it < it1;
     __syncwarp();  // the rows about to be overwritten were read two tiles ago by every lane
     issue((tile + 1) & 1, ka1, kb1);
-    cp_async_commit();
+    if (!BULK) cp_async_commit();
     int ka2 = -1, kb2 = -1;
     if (it + 2 * SB_THREADS < it1) {
       ka2 = __ldg(pv.item_a + it + 2 * SB_THREADS);
       kb2 = __ldg(pv.item_b + it + 2 * SB_THREADS);
     }
-    cp_async_wait<1>();
-    __syncwarp();  // every lane's copies of this tile have landed
+    if (BULK) {
+      // the warp has items in this tile iff its first lane has one (items of a tile are contiguous over the threads)
+      if (base + warp * 32 < it1) pb_mbar_wait(&s_bar[warp][tile & 1], (unsigned)(tile >> 1) & 1u);
+    } else {
+      cp_async_wait<1>();
+      __syncwarp();  // every lane's copies of this tile have landed
+    }
     if (cur) {
-      const double2* src = wst + (tile & 1) * SB_WARP_CHUNKS + lane * 8;
-      const int sw = lane & 7;
+      const double2* src = wst + (tile & 1) * SB_WARP_CHUNKS + (BULK ? lane * 9 : lane * 8);
+      const double2* srcb = wst + (tile & 1) * SB_WARP_CHUNKS + (BULK ? 288 + lane * 7 : 256 + lane * 8);
+      const int sw = BULK ? 0 : (lane & 7);
       double za[9], zb[9], qa[3], qb[3];
       {
         const double2 c0 = src[0 ^ sw], c1 = src[1 ^ sw], c2 = src[2 ^ sw], c3 = src[3 ^ sw], c4 = src[4 ^ sw],
@@ -1198,8 +1238,8 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
         for (int k = 0; k < 9; ++k) zb[k] = za[k];
         qb[0] = qa[0]; qb[1] = qa[1]; qb[2] = qa[2];
       } else {
-        const double2 c0 = src[256 + (0 ^ sw)], c1 = src[256 + (1 ^ sw)], c2 = src[256 + (2 ^ sw)],
-                      c3 = src[256 + (3 ^ sw)], c4 = src[256 + (4 ^ sw)], c5 = src[256 + (5 ^ sw)];
+        const double2 c0 = srcb[0 ^ sw], c1 = srcb[1 ^ sw], c2 = srcb[2 ^ sw], c3 = srcb[3 ^ sw], c4 = srcb[4 ^ sw],
+                      c5 = srcb[5 ^ sw];
         zb[0] = c0.x; zb[1] = c0.y; zb[2] = c1.x; zb[3] = c1.y; zb[4] = c2.x; zb[5] = c2.y; zb[6] = c3.x; zb[7] = c3.y;
         zb[8] = c4.x; qb[0] = 2.0 * c4.y; qb[1] = 2.0 * c5.x; qb[2] = 2.0 * c5.y;
       }
@@ -1265,7 +1305,7 @@ __global__ void __launch_bounds__(SB_THREADS) k_schur_blocks(ProblemView pv, con
     ka = ka1; kb = kb1;
     ka1 = ka2; kb1 = kb2;
   }
-  cp_async_wait<0>();
+  if (!BULK) cp_async_wait<0>();
 
   // ---- CTA reduction: lane e of every warp ends with entry e (e < 32), entries 32..35 by butterfly
   __shared__ double sm[SB_THREADS / 32][44];
@@ -2245,11 +2285,16 @@ void launch_schur_blocks(const ProblemView& pv, const double* fac, const double*
                          const double* c_img, LmDiag lm, double* S, double* rhs, int partial, double* Minv,
                          cudaStream_t st) {
   static bool attr_set = false;
+  static const bool bulk = getenv("MPBA_SCHUR_BULK") && atoi(getenv("MPBA_SCHUR_BULK")) != 0;
   if (!attr_set) {
-    cudaFuncSetAttribute(k_schur_blocks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_STAGE_BYTES);
+    cudaFuncSetAttribute(k_schur_blocks<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_STAGE_BYTES);
+    cudaFuncSetAttribute(k_schur_blocks<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_STAGE_BYTES);
     attr_set = true;
   }
-  k_schur_blocks<<<pv.U, SB_THREADS, SB_STAGE_BYTES, st>>>(pv, fac, Hc, gc, c_img, lm, S, rhs, partial, Minv);
+  if (bulk)
+    k_schur_blocks<true><<<pv.U, SB_THREADS, SB_STAGE_BYTES, st>>>(pv, fac, Hc, gc, c_img, lm, S, rhs, partial, Minv);
+  else
+    k_schur_blocks<false><<<pv.U, SB_THREADS, SB_STAGE_BYTES, st>>>(pv, fac, Hc, gc, c_img, lm, S, rhs, partial, Minv);
 }
 void launch_schur_finish(const ProblemView& pv, const double* Hc, const double* gc, const double* c_img, LmDiag lm,
                          double* S, double* rhs, double* Minv, cudaStream_t st) {
