@@ -1099,14 +1099,19 @@ __device__ __forceinline__ void cp_async_wait() {
 // of records).  Record i of the warp lands in shared memory at row i with its chunks XOR-swizzled by (i & 7):
 // the copies of one instruction fill four rows, and lane i reading chunk c of ITS row hits 8 distinct 16-byte
 // columns per quarter warp -> no bank conflicts either way.
+// The destination of copy j of a lane is rows + item * 8 + (c ^ (item & 7)) with item = 4 j + g; since g < 4 that is
+// (8 g + (c ^ g)) + 32 j for even j and (8 g + ((c ^ g) ^ 4)) + 32 j for odd j: two lane constants and an immediate
+// (the kernel is bound by instruction issue; the XOR form cost three integer instructions per copy).
 __device__ __forceinline__ void warp_gather_records(const double2* __restrict__ fac2, int slot, int nchunks,
                                                     double2* rows /* [32][8] */, int lane) {
   const int g = lane >> 3, c = lane & 7;
+  double2* const even = rows + 8 * g + (c ^ g);
+  double2* const odd = rows + 8 * g + ((c ^ g) ^ 4);
+  const bool want = c < nchunks;
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    const int item = 4 * j + g;
-    const int s = __shfl_sync(FULL, slot, item);
-    if (s >= 0 && c < nchunks) cp_async16(rows + item * 8 + (c ^ (item & 7)), fac2 + (size_t)s * 8 + c);
+    const int s = __shfl_sync(FULL, slot, 4 * j + g);
+    if (s >= 0 && want) cp_async16(((j & 1) ? odd : even) + 32 * j, fac2 + (size_t)s * 8 + c);
   }
 }
 
