@@ -200,6 +200,7 @@ constexpr int PCGC_THREADS = MPBA_PCGC_THREADS;
 struct PcgClusterCarve {
   int dep, x, r, u, p, s, w, minv, sdiag, halo, extra, parts, red;
   int zloc, ainv, rcall, ec, glrp;  // (glrp: int view, local row pointers of the owned groups)
+  int zs, zr;  // Z^T s and Z^T r of ALL groups, kept by recurrence on every CTA (pcg_cluster.cu)
   // two-level preconditioner: Z rows of the owned images, owned rows of A_c^-1, Z^T r, e_c
   int rp;     // row pointers of the owned rows, relative to the first owned full block
   int hdesc;  // halo source: owner CTA << 20 | local row at the owner

@@ -18,7 +18,12 @@
 //         B: deposits complete  -> w = S u (row sums), partial gamma / delta to every CTA
 //         C: partials complete  -> alpha, beta; p, s, x, r, u = M^-1 r updates (row local)
 //   * every CTA computes the same alpha / beta from the same partials in the same order, so the
-//     termination decision is uniform without a broadcast.
+//     termination decision is uniform without a broadcast,
+//   * the coarse term of the preconditioner needs Z^T r of ALL groups on every CTA.  Computing it from the updated r
+//     costs a fourth cluster barrier per iteration; instead every CTA keeps Z^T r and Z^T s by the recurrences of r
+//     and s (s = w + beta s, r -= alpha s  =>  Z^T s = Z^T w + beta Z^T s, Z^T r -= alpha Z^T s): the partial Z^T w
+//     of the owned rows travels with the dot-product partials before barrier C.  (Timed build, cfg3: barrier D cost
+//     ~1.9 k of ~18 k cycles per iteration.)
 //
 // Iterates coincide with textbook PCG in exact arithmetic; the iteration count semantics (number of
 // x updates, relative residual sqrt(r'M^-1 r / b'M^-1 b)) are those of k_pcg.
@@ -69,49 +74,93 @@ __device__ __forceinline__ void load6(const double* src, double (&v)[6]) {
 }
 
 // u = M^-1 r on the owned rows, r and u in shared memory.  M^-1 = blockdiag(S)^-1 + Z (Z^T S Z)^-1 Z^T (coarse.cu);
-// without a coarse space (A.G == 0) only the block-Jacobi term.  Contains one cluster barrier when A.G != 0: every
-// CTA must call it at the same point.  Z^T r of a group is formed by one warp (fixed order) and stored to every
-// CTA; each CTA then multiplies its own rows of A_c^-1.
+// without a coarse space (A.G == 0) only the block-Jacobi term.  Z^T r of all groups comes from a direct restriction
+// (first application: one cluster barrier, every CTA must call it at the same point) or from the recurrence kept
+// beside r; each CTA then multiplies its own rows of A_c^-1.
+#ifdef MPBA_PCG_TIMING
+// per-thread cycle sums of the preconditioner's phases: barrier | Z^T r | sync D | A^-1 rows | barrier | combine
+#define PRE_ARG , long long (&g_pre_cyc)[6]
+#define PRE_PASS , pre_cyc
+#define PRE_TICK(k)                                        \
+  do {                                                     \
+    const long long now_ = clock64();                      \
+    g_pre_cyc[k] += now_ - t_;                             \
+    t_ = now_;                                             \
+  } while (0)
+#else
+#define PRE_TICK(k)
+#define PRE_ARG
+#define PRE_PASS
+#endif
+
+// Z^T v of the owned groups (v = r or w in shared memory at offset voff), one warp per (group, mode) in fixed order,
+// stored into rcall of EVERY CTA of the cluster; complete after the next cluster barrier.
+__device__ __forceinline__ void restrict_to_all(double* smem, const int* smi, const PcgClusterArgs& A,
+                                                cg::cluster_group& cluster, int rank, int CL, int voff) {
+  const PcgClusterCarve& m = A.m;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int ntask = A.gpc * 7;
+  for (int task = warp; task < ntask; task += T / 32) {
+    const int gl = task / 7, a = task - 7 * gl;
+    const int i0 = smi[m.glrp + gl] * 6, i1 = smi[m.glrp + gl + 1] * 6;
+    double acc = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;  // independent chains: the loop is shared-memory latency bound
+    int idx = i0 + lane;
+    for (; idx + 96 < i1; idx += 128) {
+      acc += smem[m.zloc + idx * 7 + a] * smem[voff + idx];
+      acc1 += smem[m.zloc + (idx + 32) * 7 + a] * smem[voff + idx + 32];
+      acc2 += smem[m.zloc + (idx + 64) * 7 + a] * smem[voff + idx + 64];
+      acc3 += smem[m.zloc + (idx + 96) * 7 + a] * smem[voff + idx + 96];
+    }
+    for (; idx < i1; idx += 32) acc += smem[m.zloc + idx * 7 + a] * smem[voff + idx];
+    acc = (acc + acc1) + (acc2 + acc3);
+    for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(FULL, acc, off);
+    if (lane < CL) {
+      double* dst = ((lane == rank) ? smem : cluster.map_shared_rank(smem, lane)) + m.rcall;
+      dst[(rank * A.gpc + gl) * 7 + a] = acc;
+    }
+  }
+}
+
+// DIRECT: Z^T r is formed from r (one cluster barrier; the first application of a solve, which also seeds the
+// recurrence); otherwise it is read from the recurrence (m.zr) and the call holds no cluster barrier.
+template <bool DIRECT>
 __device__ __forceinline__ void apply_precond(double* smem, const int* smi, const PcgClusterArgs& A,
-                                              cg::cluster_group& cluster, int rank, int CL, int nrows) {
+                                              cg::cluster_group& cluster, int rank, int CL, int nrows PRE_ARG) {
   const PcgClusterCarve& m = A.m;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#ifdef MPBA_PCG_TIMING
+  long long t_ = clock64();
+#endif
   __syncthreads();  // r is complete
+  PRE_TICK(0);
   if (A.G) {
     const int ntask = A.gpc * 7;
-    for (int task = warp; task < ntask; task += T / 32) {
-      const int gl = task / 7, a = task - 7 * gl;
-      const int i0 = smi[m.glrp + gl] * 6, i1 = smi[m.glrp + gl + 1] * 6;
-      double acc = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;  // independent chains: the loop is shared-memory latency bound
-      int idx = i0 + lane;
-      for (; idx + 96 < i1; idx += 128) {
-        acc += smem[m.zloc + idx * 7 + a] * smem[m.r + idx];
-        acc1 += smem[m.zloc + (idx + 32) * 7 + a] * smem[m.r + idx + 32];
-        acc2 += smem[m.zloc + (idx + 64) * 7 + a] * smem[m.r + idx + 64];
-        acc3 += smem[m.zloc + (idx + 96) * 7 + a] * smem[m.r + idx + 96];
-      }
-      for (; idx < i1; idx += 32) acc += smem[m.zloc + idx * 7 + a] * smem[m.r + idx];
-      acc = (acc + acc1) + (acc2 + acc3);
-      for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(FULL, acc, off);
-      if (lane < CL) {
-        double* dst = ((lane == rank) ? smem : cluster.map_shared_rank(smem, lane)) + m.rcall;
-        dst[(rank * A.gpc + gl) * 7 + a] = acc;
+    if (DIRECT) {
+      restrict_to_all(smem, smi, A, cluster, rank, CL, m.r);
+      PRE_TICK(1);
+      cluster.sync();  // D: Z^T r of every group is everywhere
+      PRE_TICK(2);
+      for (int k = tid; k < A.nc; k += T) {
+        smem[m.zr + k] = smem[m.rcall + k];
+        smem[m.zs + k] = 0.0;
       }
     }
-    cluster.sync();  // D: Z^T r of every group is everywhere
+    const int zsrc = DIRECT ? m.rcall : m.zr;
     for (int task = warp; task < ntask; task += T / 32) {
       double acc = 0.0, acc1 = 0.0;
       int k = lane;
       for (; k + 32 < A.nc; k += 64) {
-        acc += smem[m.ainv + task * A.nc + k] * smem[m.rcall + k];
-        acc1 += smem[m.ainv + task * A.nc + k + 32] * smem[m.rcall + k + 32];
+        acc += smem[m.ainv + task * A.nc + k] * smem[zsrc + k];
+        acc1 += smem[m.ainv + task * A.nc + k + 32] * smem[zsrc + k + 32];
       }
-      if (k < A.nc) acc += smem[m.ainv + task * A.nc + k] * smem[m.rcall + k];
+      if (k < A.nc) acc += smem[m.ainv + task * A.nc + k] * smem[zsrc + k];
       acc += acc1;
       for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(FULL, acc, off);
       if (lane == 0) smem[m.ec + task] = acc;
     }
+    PRE_TICK(3);
     __syncthreads();
+    PRE_TICK(4);
   }
   for (int q = tid; q < nrows * 6; q += T) {
     const int lr = q / 6, c = q - 6 * lr;
@@ -133,6 +182,7 @@ __device__ __forceinline__ void apply_precond(double* smem, const int* smi, cons
     }
     smem[m.u + q] = (z + z1) + (zc0 + zc1);
   }
+  PRE_TICK(5);
 }
 
 // row items: warp w, lane l < 30 -> row slot 5 w + l / 6 (+ 5 * warps per pass), component l % 6, so the six
@@ -202,7 +252,10 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
   }
   const int sub = lane / 6, comp = lane % 6;
   const bool row_lane = lane < 30;
-  apply_precond(smem, smi, A, cluster, rank, CL, nrows);
+#ifdef MPBA_PCG_TIMING
+  long long pre_cyc[6] = {0, 0, 0, 0, 0, 0};
+#endif
+  apply_precond<true>(smem, smi, A, cluster, rank, CL, nrows PRE_PASS);
 
   double gamma0 = 0.0, tol2g0 = 0.0, inv_gamma_prev = 0.0, inv_alpha_prev = 0.0, last_gamma = 0.0;
   int iters = 0, flag = 1;
@@ -292,7 +345,8 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
       pd += __shfl_down_sync(FULL, pd, off);
     }
     if (lane == 0) reinterpret_cast<double2*>(smem + m.red)[warp] = make_double2(pg, pd);
-    __syncthreads();
+    __syncthreads();  // w and the warp partials are complete
+    if (A.G) restrict_to_all(smem, smi, A, cluster, rank, CL, m.w);  // Z^T w of the owned groups to every CTA
     if (warp == 0) {  // warp 0 folds the warp partials (fixed tree) and lane k delivers the result to CTA k
       double2 v = lane < T / 32 ? reinterpret_cast<const double2*>(smem + m.red)[lane] : make_double2(0.0, 0.0);
       for (int off = 8; off > 0; off >>= 1) {
@@ -367,7 +421,13 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
         smem[m.r + o] -= alpha * sn;
       }
     }
-    apply_precond(smem, smi, A, cluster, rank, CL, nrows);
+    // the same recurrences for the coarse restrictions (identical on every CTA): Z^T s, Z^T r
+    for (int t = tid; t < A.nc; t += T) {
+      const double zsn = smem[m.rcall + t] + beta * smem[m.zs + t];
+      smem[m.zs + t] = zsn;
+      smem[m.zr + t] -= alpha * zsn;
+    }
+    apply_precond<false>(smem, smi, A, cluster, rank, CL, nrows PRE_PASS);
     inv_gamma_prev = 1.0 / gamma;
     inv_alpha_prev = denom * inv_gamma_prev;
 #ifdef MPBA_PCG_TIMING
@@ -380,6 +440,10 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
     A.scal[S_PCG_FLAG] = (double)flag;
     A.scal[S_PCG_RES] = gamma0 > 0.0 ? sqrt(fabs(last_gamma) / gamma0) : 0.0;
 #ifdef MPBA_PCG_TIMING
+    printf("[pcg precond cycles / iteration] barrier %lld  ZTr %lld  syncD %lld  Ainv %lld  barrier %lld  combine %lld  | update total %lld (x/r/p/s part %lld)\n",
+           pre_cyc[0] / (iters + 1), pre_cyc[1] / (iters + 1), pre_cyc[2] / (iters + 1), pre_cyc[3] / (iters + 1),
+           pre_cyc[4] / (iters + 1), pre_cyc[5] / (iters + 1), tU / (iters + 1),
+           (tU - pre_cyc[0] - pre_cyc[1] - pre_cyc[2] - pre_cyc[3] - pre_cyc[4] - pre_cyc[5]) / (iters + 1));
     A.scal[S_PCG_CYC_SPMV] = (double)(tH + tP);
     A.scal[S_PCG_CYC_REDUCE] = (double)(tA + tB + tC);
     A.scal[S_PCG_CYC_UPDATE] = (double)(tR + tU);
@@ -419,6 +483,8 @@ size_t pcg_cluster_carve(PcgClusterArgs& A) {
   c.ainv = o;  o += A.gpc * 7 * A.nc;
   c.rcall = o; o += A.nc;
   c.ec = o;    o += A.gpc * 7;
+  c.zs = o;    o += A.nc;
+  c.zr = o;    o += A.nc;
   o += o & 1;
   c.glrp = 2 * o;
   o += (A.gpc + 4) / 2;
