@@ -1591,7 +1591,9 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
   // group, so its Z^T r is 7 numbers; they travel with the r'M^-1 r partial through the same grid barrier, then
   // every CTA forms t = Z^T r (all groups, fixed order), e = A^-1 t (redundantly: nc^2 multiply-adds), and
   //     r'z = r'M^-1 r + t'e,        z_i = (M^-1 r)_i + Z_i e_g      for its own rows,
-  // publishes z and meets the others at one more barrier before the next product.
+  // publishes z and meets the others at one more barrier before the next product.  That is the FIRST application;
+  // inside the loop t follows the recurrence of r (r -= alpha q  =>  t -= alpha Z^T q): the seven numbers a CTA
+  // contributes to Z^T q travel with the p'q partial, so an iteration has two grid barriers, not three.
   __shared__ double s_t[PCG_MAX_NC], s_e[PCG_MAX_NC], s_tw[PCG_THREADS / 32][8];
   __shared__ double s_ainv[7 * PCG_MAX_NC];  // the own group's seven rows of (Z^T S Z)^-1
   const bool coarse = A.G > 0;
@@ -1641,6 +1643,42 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
     }
     __syncthreads();
     // this group's share of t'e, counted once (by the group's first CTA); the sum rides on the next exchange
+    double te = 0.0;
+    if (threadIdx.x == 0 && row0 == A.grp_row_ptr[my_group]) {
+#pragma unroll
+      for (int m = 0; m < 7; ++m) te += s_t[my_group * 7 + m] * s_e[my_group * 7 + m];
+    }
+    return te;
+  };
+  // inside the loop: t -= alpha Z^T q from the partials published before the p'q exchange (all groups, on every CTA)
+  auto coarse_recur_t = [&](double alpha) {
+    const int nc = A.nc;
+    for (int k = threadIdx.x; k < nc; k += PCG_THREADS) {
+      const int g = k / 7, m = k % 7;
+      const int c0 = (A.grp_row_ptr[g] + A.rows_per_cta - 1) / A.rows_per_cta;
+      const int c1 = min((int)gridDim.x, (A.grp_row_ptr[g + 1] + A.rows_per_cta - 1) / A.rows_per_cta);
+      double t = 0.0, t1 = 0.0;
+      int cta = c0;
+      for (; cta + 1 < c1; cta += 2) {
+        t += __ldcg(A.tpart + (size_t)cta * 8 + m);
+        t1 += __ldcg(A.tpart + (size_t)(cta + 1) * 8 + m);
+      }
+      if (cta < c1) t += __ldcg(A.tpart + (size_t)cta * 8 + m);
+      s_t[k] -= alpha * (t + t1);
+    }
+  };
+  // e of the own group from the current t; returns this CTA's share of t'e (thread 0 of the group's first CTA)
+  auto coarse_e = [&]() -> double {
+    const int nc = A.nc;
+    __syncthreads();  // t is complete
+    if (warp < 7) {
+      double acc = 0.0;
+      for (int k = lane; k < nc; k += 32) acc += s_ainv[warp * nc + k] * s_t[k];
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(FULL, acc, off);
+      if (lane == 0) s_e[my_group * 7 + warp] = acc;
+    }
+    __syncthreads();
     double te = 0.0;
     if (threadIdx.x == 0 && row0 == A.grp_row_ptr[my_group]) {
 #pragma unroll
@@ -1713,6 +1751,7 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
       const long long c0 = clock64();
       // p = z + beta p_old (rebuilt where gathered); q = S p; p'q
       part = 0.0;
+      double tqacc = 0.0;  // lanes 0..6: Z^T q over the warp's rows
       if (halo) {
         double2* ph2 = reinterpret_cast<double2*>(s_ph);
         for (int u = threadIdx.x; u < nuniq * 3; u += PCG_THREADS) {
@@ -1751,9 +1790,18 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
         }
         const double a1 = __shfl_sync(FULL, acc, r6 + 6), a2 = __shfl_sync(FULL, acc, r6 + 12),
                      a3 = __shfl_sync(FULL, acc, r6 + 18), a4 = __shfl_sync(FULL, acc, r6 + 24);
+        const double qv = acc + a1 + a2 + a3 + a4;  // meaningful in lanes 0..5
+        if (coarse) {
+          double a = 0.0;
+#pragma unroll
+          for (int r = 0; r < 6; ++r) {
+            const double qc = __shfl_sync(FULL, qv, r);
+            if (lane < 7) a += __ldg(A.Zc + (size_t)row * 42 + r * 7 + lane) * qc;
+          }
+          tqacc += a;
+        }
         if (lane < 6) {
           const size_t o = (size_t)row * 6 + lane;
-          const double qv = acc + a1 + a2 + a3 + a4;
           double pi;
           if (halo)
             pi = s_ph[(s_pref[row >> 5] + __popc(s_bits[row >> 5] & ((1u << (row & 31)) - 1u))) * 6 + lane];
@@ -1765,6 +1813,10 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
           part += pi * qv;
         }
       }
+      if (coarse) {
+        const double tt[1] = {tqacc};
+        coarse_publish_t(tt);
+      }
       const long long c1 = clock64();
       const double pq = grid_reduce(part, part0, A.bar, gen, sm);
       const long long c2 = clock64();
@@ -1773,9 +1825,9 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
         break;
       }
       const double alpha = rz / pq;
+      if (coarse) coarse_recur_t(alpha);  // L2 loads in flight while the rows are updated
       // x += alpha p, r -= alpha q, z = M^-1 r
       part = 0.0;
-      double tacc = 0.0;
       for (int lr = warp; lr < nrows; lr += WPB) {
         const int row = row0 + lr;
         double rr = 0.0;
@@ -1794,27 +1846,13 @@ __global__ void __launch_bounds__(PCG_THREADS) k_pcg(PcgArgs A) {
           if (coarse) s_zj[lr * 6 + lane] = zz; else __stcg(A.z + (size_t)row * 6 + lane, zz);
           part += rr * zz;
         }
-        if (coarse) {
-          double a = 0.0;
-#pragma unroll
-          for (int r = 0; r < 6; ++r) {
-            const double rc = __shfl_sync(FULL, rr, r);
-            if (lane < 7) a += __ldg(A.Zc + (size_t)row * 42 + r * 7 + lane) * rc;
-          }
-          tacc += a;
-        }
       }
-      if (coarse) {
-        const double tt[1] = {tacc};
-        coarse_publish_t(tt);
+      if (coarse) {  // r'z = r'M^-1 r + t'e; z = M^-1 r + Z e is published before the one exchange of this half
+        part += coarse_e();
+        coarse_apply_z();
       }
       const long long c3 = clock64();
-      double rz_new = grid_reduce(part, part1, A.bar, gen, sm);
-      if (coarse) {  // r'z = r'M^-1 r + t'e: the second term arrives with the exchange that publishes z
-        const double te_part = coarse_solve();
-        coarse_apply_z();
-        rz_new += grid_reduce(te_part, part0, A.bar, gen, sm);
-      }
+      const double rz_new = grid_reduce(part, part1, A.bar, gen, sm);
       const long long c4 = clock64();
       t_spmv += c1 - c0;
       t_upd += c3 - c2;
