@@ -80,3 +80,25 @@ def test_out_of_range_index_is_rejected():
     rc = lib.mpba_host_layout_create(4, 50, img.size, img.ctypes.data, pt.ctypes.data,
                                      np.zeros(50, np.uint8).ctypes.data, 0, C.byref(handle), C.byref(view))
     assert rc == -1
+
+
+def test_index_arrays_outlive_the_layout_object():
+    """build_layout returns views of the native builder's buffers: the memory must stay alive as long as any array
+    (or a slice of one, or a torch tensor made from one) does, and pickles must be plain copies."""
+    import gc
+    import pickle
+
+    from mpsfm_b200.synthetic import make_scene
+
+    prob = make_scene(12, 900, 4, seed=5)
+    want = engine.build_layout_numpy(prob)
+    lay = engine.build_layout(prob)
+    item_a, tail = lay.item_a, lay.pm_src[100:200]
+    blob = pickle.dumps(lay.s_col)
+    del lay
+    gc.collect()
+    for _ in range(3):  # churn the native allocator
+        engine.build_layout(make_scene(12, 900, 4, seed=6))
+    gc.collect()
+    assert np.array_equal(item_a, want.item_a) and np.array_equal(tail, want.pm_src[100:200])
+    assert np.array_equal(pickle.loads(blob), want.s_col)
