@@ -42,23 +42,29 @@ namespace {
 constexpr int T = PCGC_THREADS;
 constexpr unsigned FULL = 0xffffffffu;
 
-// a = S v (row product), t = S^T v2 (column product) of one 6x6 row-major block
-__device__ __forceinline__ void block_products(const double (&S)[36], const double (&uj)[6], const double (&ui)[6],
-                                               double (&a)[6], double (&t)[6]) {
+// a = S v (row product), t = S^T v2 (column product) of one 6x6 row-major block whose entries 34 and 35 are read from
+// shared memory at their use: 34 + 24 + 12 doubles in flight instead of 36 + 24 + 12 (the last four registers were
+// spilled to local memory, an L2 round trip per iteration after the L1 invalidation every cluster barrier ends with)
+__device__ __forceinline__ void block_products_tail(const double (&S)[34], const double2* tail, const double (&uj)[6],
+                                                    const double (&ui)[6], double (&a)[6], double (&t)[6]) {
 #pragma unroll
-  for (int r = 0; r < 6; ++r) {
+  for (int r = 0; r < 5; ++r) {
     double acc = 0.0;
 #pragma unroll
     for (int c = 0; c < 6; ++c) acc += S[6 * r + c] * uj[c];
     a[r] = acc;
   }
 #pragma unroll
-  for (int c = 0; c < 6; ++c) {
+  for (int c = 0; c < 4; ++c) {
     double acc = 0.0;
 #pragma unroll
     for (int r = 0; r < 6; ++r) acc += S[6 * r + c] * ui[r];
     t[c] = acc;
   }
+  const double2 s45 = *tail;  // S[34], S[35]
+  a[5] = S[30] * uj[0] + S[31] * uj[1] + S[32] * uj[2] + S[33] * uj[3] + s45.x * uj[4] + s45.y * uj[5];
+  t[4] = S[4] * ui[0] + S[10] * ui[1] + S[16] * ui[2] + S[22] * ui[3] + S[28] * ui[4] + s45.x * ui[5];
+  t[5] = S[5] * ui[0] + S[11] * ui[1] + S[17] * ui[2] + S[23] * ui[3] + S[29] * ui[4] + s45.y * ui[5];
 }
 
 __device__ __forceinline__ void store6(double* dst, const double (&v)[6]) {
@@ -205,19 +211,22 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
   const int full0 = A.row_ptr[row0];
 
   // ---- one-time loads: my register block, spilled blocks, diagonal blocks, M^-1 rows, r = b
-  double Sreg[36];
+  double Sreg[34];
+  double2* const stail = reinterpret_cast<double2*>(smem + m.stail) + tid;
   const bool have = tid < nub;
   if (have) {
     const double2* src = reinterpret_cast<const double2*>(A.S + (size_t)A.ub_sblk[ub0 + tid] * 36);
 #pragma unroll
-    for (int e = 0; e < 18; ++e) {
+    for (int e = 0; e < 17; ++e) {
       const double2 v = src[e];
       Sreg[2 * e] = v.x;
       Sreg[2 * e + 1] = v.y;
     }
+    *stail = src[17];
   } else {
 #pragma unroll
-    for (int e = 0; e < 36; ++e) Sreg[e] = 0.0;
+    for (int e = 0; e < 34; ++e) Sreg[e] = 0.0;
+    *stail = make_double2(0.0, 0.0);
   }
   const int nextra = nub > T ? nub - T : 0;
   for (int k = tid; k < nextra * 36; k += T) {
@@ -254,10 +263,17 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
   const bool row_lane = lane < 30;
 #ifdef MPBA_PCG_TIMING
   long long pre_cyc[6] = {0, 0, 0, 0, 0, 0};
+  long long upd_cyc[3] = {0, 0, 0};  // fold + alpha | x r p s | zs zr
 #endif
   apply_precond<true>(smem, smi, A, cluster, rank, CL, nrows PRE_PASS);
 
-  double gamma0 = 0.0, tol2g0 = 0.0, inv_gamma_prev = 0.0, inv_alpha_prev = 0.0, last_gamma = 0.0;
+  // The scalars carried from one iteration to the next live in shared memory (written by thread 0, CTA barriers lie
+  // between every write and the reads): as registers they were spilled to local memory, and every cluster barrier
+  // ends with an L1 invalidation (CCTL.IVALL is how barrier.cluster.wait.acquire compiles) -- the reload of
+  // 1 / gamma_prev sat on the critical path of every iteration as an L2 round trip.
+  enum { SC_GAMMA0 = 0, SC_TOL2G0, SC_INV_GAMMA, SC_INV_ALPHA, SC_LAST_GAMMA };
+  if (tid == 0)
+    for (int e = 0; e < 8; ++e) smem[m.sc + e] = 0.0;
   int iters = 0, flag = 1;
 #ifdef MPBA_PCG_TIMING
   long long tA = 0, tH = 0, tP = 0, tB = 0, tR = 0, tC = 0, tU = 0;
@@ -286,7 +302,7 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
       const int* md = smi + m.xmeta + 5 * tid;
       load6(smem + m.halo + md[1] * 6, uj);
       load6(smem + m.u + md[0] * 6, ui);
-      block_products(Sreg, uj, ui, a, t);
+      block_products_tail(Sreg, stail, uj, ui, a, t);
       store6(smem + m.dep + md[2] * 6, a);
       const int tc = md[3];
       double* dst = ((tc == rank) ? smem : cluster.map_shared_rank(smem, tc)) + m.dep;
@@ -377,21 +393,22 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
       delta = __shfl_sync(FULL, v.y, 0);
     }
     if (k == 0) {
-      gamma0 = gamma;
-      tol2g0 = A.tol * A.tol * gamma0;
-      if (!(gamma0 > 0.0) || !isfinite(gamma0)) {
-        flag = (gamma0 == 0.0) ? 0 : 2;
-        last_gamma = 0.0;
-        break;
+      if (tid == 0) {
+        smem[m.sc + SC_GAMMA0] = gamma;
+        smem[m.sc + SC_TOL2G0] = A.tol * A.tol * gamma;
+      }
+      if (!(gamma > 0.0) || !isfinite(gamma)) {
+        flag = (gamma == 0.0) ? 0 : 2;
+        break;  // SC_LAST_GAMMA stays 0
       }
     }
-    last_gamma = gamma;
+    if (tid == 0) smem[m.sc + SC_LAST_GAMMA] = gamma;
     if (!isfinite(gamma)) {
       flag = 2;
       break;
     }
     iters = k;
-    if (k > 0 && fabs(gamma) <= tol2g0) {
+    if (k > 0 && fabs(gamma) <= smem[m.sc + SC_TOL2G0]) {
       flag = 0;
       break;
     }
@@ -401,13 +418,17 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
     }
     // beta = gamma / gamma_prev, alpha = gamma / (delta - beta gamma / alpha_prev): one division on the
     // critical path, the reciprocals for the next iteration are taken off it
-    const double beta = gamma * inv_gamma_prev;
-    const double denom = delta - beta * gamma * inv_alpha_prev;
+    const double beta = gamma * smem[m.sc + SC_INV_GAMMA];
+    const double denom = delta - beta * gamma * smem[m.sc + SC_INV_ALPHA];
     if (!(denom > 0.0) || !isfinite(denom)) {
       flag = 2;
       break;
     }
     const double alpha = gamma / denom;
+#ifdef MPBA_PCG_TIMING
+    const long long u1 = clock64();
+    upd_cyc[0] += u1 - c6;
+#endif
     for (int lr0 = 0; lr0 < nrows; lr0 += ROWS_PER_PASS) {
       const int lr = lr0 + 5 * warp + sub;
       const bool act = row_lane && lr < nrows;
@@ -421,15 +442,25 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
         smem[m.r + o] -= alpha * sn;
       }
     }
+#ifdef MPBA_PCG_TIMING
+    const long long u2 = clock64();
+    upd_cyc[1] += u2 - u1;
+#endif
     // the same recurrences for the coarse restrictions (identical on every CTA): Z^T s, Z^T r
     for (int t = tid; t < A.nc; t += T) {
       const double zsn = smem[m.rcall + t] + beta * smem[m.zs + t];
       smem[m.zs + t] = zsn;
       smem[m.zr + t] -= alpha * zsn;
     }
+#ifdef MPBA_PCG_TIMING
+    upd_cyc[2] += clock64() - u2;
+#endif
     apply_precond<false>(smem, smi, A, cluster, rank, CL, nrows PRE_PASS);
-    inv_gamma_prev = 1.0 / gamma;
-    inv_alpha_prev = denom * inv_gamma_prev;
+    if (tid == 0) {  // every thread is past its reads of the two (CTA barriers inside apply_precond)
+      const double ig = 1.0 / gamma;
+      smem[m.sc + SC_INV_GAMMA] = ig;
+      smem[m.sc + SC_INV_ALPHA] = denom * ig;
+    }
 #ifdef MPBA_PCG_TIMING
     tU += clock64() - c6;
 #endif
@@ -438,12 +469,15 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
   if (rank == 0 && tid == 0) {
     A.scal[S_PCG_ITERS] = (double)iters;
     A.scal[S_PCG_FLAG] = (double)flag;
+    const double gamma0 = smem[m.sc + SC_GAMMA0], last_gamma = smem[m.sc + SC_LAST_GAMMA];
     A.scal[S_PCG_RES] = gamma0 > 0.0 ? sqrt(fabs(last_gamma) / gamma0) : 0.0;
 #ifdef MPBA_PCG_TIMING
     printf("[pcg precond cycles / iteration] barrier %lld  ZTr %lld  syncD %lld  Ainv %lld  barrier %lld  combine %lld  | update total %lld (x/r/p/s part %lld)\n",
            pre_cyc[0] / (iters + 1), pre_cyc[1] / (iters + 1), pre_cyc[2] / (iters + 1), pre_cyc[3] / (iters + 1),
            pre_cyc[4] / (iters + 1), pre_cyc[5] / (iters + 1), tU / (iters + 1),
            (tU - pre_cyc[0] - pre_cyc[1] - pre_cyc[2] - pre_cyc[3] - pre_cyc[4] - pre_cyc[5]) / (iters + 1));
+    printf("[pcg update cycles / iteration] fold+alpha %lld  xrps %lld  zszr %lld\n", upd_cyc[0] / (iters + 1),
+           upd_cyc[1] / (iters + 1), upd_cyc[2] / (iters + 1));
     A.scal[S_PCG_CYC_SPMV] = (double)(tH + tP);
     A.scal[S_PCG_CYC_REDUCE] = (double)(tA + tB + tC);
     A.scal[S_PCG_CYC_UPDATE] = (double)(tR + tU);
@@ -485,6 +519,9 @@ size_t pcg_cluster_carve(PcgClusterArgs& A) {
   c.ec = o;    o += A.gpc * 7;
   c.zs = o;    o += A.nc;
   c.zr = o;    o += A.nc;
+  c.sc = o;    o += 8;
+  o += o & 1;  // double2 access
+  c.stail = o; o += 2 * T;
   o += o & 1;
   c.glrp = 2 * o;
   o += (A.gpc + 4) / 2;
