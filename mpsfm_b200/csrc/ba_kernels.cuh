@@ -202,7 +202,7 @@ struct PcgClusterCarve {
   int zloc, ainv, rcall, ec, glrp;  // (glrp: int view, local row pointers of the owned groups)
   int zs, zr;  // Z^T s and Z^T r of ALL groups, kept by recurrence on every CTA (pcg_cluster.cu)
   int sc;      // loop-carried scalars (gamma_0, tol^2 gamma_0, 1 / gamma_prev, 1 / alpha_prev, last gamma)
-  int stail;   // [threads] double2: entries 34, 35 of every thread's register block of S
+  int stail;   // [2][threads] double2: entries 32..35 of every thread's register block of S
   // two-level preconditioner: Z rows of the owned images, owned rows of A_c^-1, Z^T r, e_c
   int rp;     // row pointers of the owned rows, relative to the first owned full block
   int hdesc;  // halo source: owner CTA << 20 | local row at the owner

@@ -42,10 +42,25 @@ namespace {
 constexpr int T = PCGC_THREADS;
 constexpr unsigned FULL = 0xffffffffu;
 
-// a = S v (row product), t = S^T v2 (column product) of one 6x6 row-major block whose entries 34 and 35 are read from
-// shared memory at their use: 34 + 24 + 12 doubles in flight instead of 36 + 24 + 12 (the last four registers were
-// spilled to local memory, an L2 round trip per iteration after the L1 invalidation every cluster barrier ends with)
-__device__ __forceinline__ void block_products_tail(const double (&S)[34], const double2* tail, const double (&uj)[6],
+// Cluster barrier with release / acquire semantics, every thread of the CTA in converged control flow (.aligned).
+// cg::cluster_group::sync() is the same pair without .aligned, for which the compiler adds a divergence check per
+// warp and a CTA barrier behind the wait; the loop below runs three of them per iteration.
+__device__ __forceinline__ void cluster_sync_aligned() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// the two halves, for work that touches only this CTA's own data while the barrier completes
+__device__ __forceinline__ void cluster_arrive_aligned() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cluster_wait_aligned() {
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// a = S v (row product), t = S^T v2 (column product) of one 6x6 row-major block whose entries 32..35 are read from
+// shared memory at their use: 32 + 24 + 12 doubles in flight instead of 36 + 24 + 12 (the compiler spilled the last
+// registers of the block to local memory: an L2 round trip per iteration, because every cluster barrier ends with an
+// L1 invalidation)
+__device__ __forceinline__ void block_products_tail(const double (&S)[32], const double2* tail, const double (&uj)[6],
                                                     const double (&ui)[6], double (&a)[6], double (&t)[6]) {
 #pragma unroll
   for (int r = 0; r < 5; ++r) {
@@ -55,16 +70,20 @@ __device__ __forceinline__ void block_products_tail(const double (&S)[34], const
     a[r] = acc;
   }
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
+  for (int c = 0; c < 6; ++c) {
     double acc = 0.0;
 #pragma unroll
-    for (int r = 0; r < 6; ++r) acc += S[6 * r + c] * ui[r];
+    for (int r = 0; r < 5; ++r) acc += S[6 * r + c] * ui[r];
     t[c] = acc;
   }
-  const double2 s45 = *tail;  // S[34], S[35]
-  a[5] = S[30] * uj[0] + S[31] * uj[1] + S[32] * uj[2] + S[33] * uj[3] + s45.x * uj[4] + s45.y * uj[5];
-  t[4] = S[4] * ui[0] + S[10] * ui[1] + S[16] * ui[2] + S[22] * ui[3] + S[28] * ui[4] + s45.x * ui[5];
-  t[5] = S[5] * ui[0] + S[11] * ui[1] + S[17] * ui[2] + S[23] * ui[3] + S[29] * ui[4] + s45.y * ui[5];
+  const double2 s23 = tail[0], s45 = tail[T];  // S[32], S[33] | S[34], S[35]  ([2][threads]: conflict free)
+  a[5] = S[30] * uj[0] + S[31] * uj[1] + s23.x * uj[2] + s23.y * uj[3] + s45.x * uj[4] + s45.y * uj[5];
+  t[0] += S[30] * ui[5];
+  t[1] += S[31] * ui[5];
+  t[2] += s23.x * ui[5];
+  t[3] += s23.y * ui[5];
+  t[4] += s45.x * ui[5];
+  t[5] += s45.y * ui[5];
 }
 
 __device__ __forceinline__ void store6(double* dst, const double (&v)[6]) {
@@ -144,7 +163,7 @@ __device__ __forceinline__ void apply_precond(double* smem, const int* smi, cons
     if (DIRECT) {
       restrict_to_all(smem, smi, A, cluster, rank, CL, m.r);
       PRE_TICK(1);
-      cluster.sync();  // D: Z^T r of every group is everywhere
+      cluster_sync_aligned();  // D: Z^T r of every group is everywhere
       PRE_TICK(2);
       for (int k = tid; k < A.nc; k += T) {
         smem[m.zr + k] = smem[m.rcall + k];
@@ -211,22 +230,23 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
   const int full0 = A.row_ptr[row0];
 
   // ---- one-time loads: my register block, spilled blocks, diagonal blocks, M^-1 rows, r = b
-  double Sreg[34];
+  double Sreg[32];
   double2* const stail = reinterpret_cast<double2*>(smem + m.stail) + tid;
   const bool have = tid < nub;
   if (have) {
     const double2* src = reinterpret_cast<const double2*>(A.S + (size_t)A.ub_sblk[ub0 + tid] * 36);
 #pragma unroll
-    for (int e = 0; e < 17; ++e) {
+    for (int e = 0; e < 16; ++e) {
       const double2 v = src[e];
       Sreg[2 * e] = v.x;
       Sreg[2 * e + 1] = v.y;
     }
-    *stail = src[17];
+    stail[0] = src[16];
+    stail[T] = src[17];
   } else {
 #pragma unroll
-    for (int e = 0; e < 34; ++e) Sreg[e] = 0.0;
-    *stail = make_double2(0.0, 0.0);
+    for (int e = 0; e < 32; ++e) Sreg[e] = 0.0;
+    stail[0] = stail[T] = make_double2(0.0, 0.0);
   }
   const int nextra = nub > T ? nub - T : 0;
   for (int k = tid; k < nextra * 36; k += T) {
@@ -283,7 +303,7 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
 #endif
   for (int k = 0;; ++k) {
     TICK(c0);
-    cluster.sync();  // A: every CTA's u is in place
+    cluster_sync_aligned();  // A: every CTA's u is in place
     TICK(c1);
     // halo: the u rows this CTA's blocks multiply with, pulled once per iteration
     for (int q = tid; q < nhalo * 3; q += T) {
@@ -329,14 +349,31 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
       store6(dst + md[4] * 6, t);
     }
     TICK(c3);
-    cluster.sync();  // B: all deposits landed
+    cluster_arrive_aligned();  // B: my deposits are on their way ...
+    // ... and while the others' land: the part of the first pass of row sums that needs only this CTA's own data
+    // (diagonal block times u, r.u, the row's slot range)
+    double dg_pre = 0.0, uu_pre = 0.0, ru_pre = 0.0;
+    int s0_pre = 0, s1_pre = 0;
+    {
+      const int lr = 5 * warp + sub;
+      if (row_lane && lr < nrows) {
+        s0_pre = smi[m.rp + lr];
+        s1_pre = smi[m.rp + lr + 1];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) dg_pre += smem[m.sdiag + lr * 36 + comp * 6 + j] * smem[m.u + lr * 6 + j];
+        uu_pre = smem[m.u + lr * 6 + comp];
+        ru_pre = smem[m.r + lr * 6 + comp] * uu_pre;
+      }
+    }
+    cluster_wait_aligned();  // B: all deposits landed
     TICK(c4);
     // w = S u on the owned rows (diagonal block from shared memory + deposits in column order); dot partials
     double pg = 0.0, pd = 0.0;
     for (int lr0 = 0; lr0 < nrows; lr0 += ROWS_PER_PASS) {
       const int lr = lr0 + 5 * warp + sub;
       if (row_lane && lr < nrows) {
-        const int s0 = smi[m.rp + lr], s1 = smi[m.rp + lr + 1];
+        const bool first = lr0 == 0;
+        const int s0 = first ? s0_pre : smi[m.rp + lr], s1 = first ? s1_pre : smi[m.rp + lr + 1];
         double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
         int sl = s0;
         for (; sl + 3 < s1; sl += 4) {
@@ -346,13 +383,17 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
           a3 += smem[m.dep + (size_t)(sl + 3) * 6 + comp];
         }
         for (; sl < s1; ++sl) a0 += smem[m.dep + (size_t)sl * 6 + comp];
-        double dg = 0.0;
+        double dg = dg_pre, uu = uu_pre, ru = ru_pre;
+        if (!first) {
+          dg = 0.0;
 #pragma unroll
-        for (int j = 0; j < 6; ++j) dg += smem[m.sdiag + lr * 36 + comp * 6 + j] * smem[m.u + lr * 6 + j];
+          for (int j = 0; j < 6; ++j) dg += smem[m.sdiag + lr * 36 + comp * 6 + j] * smem[m.u + lr * 6 + j];
+          uu = smem[m.u + lr * 6 + comp];
+          ru = smem[m.r + lr * 6 + comp] * uu;
+        }
         const double acc = ((a0 + a1) + (a2 + a3)) + dg;
         smem[m.w + lr * 6 + comp] = acc;
-        const double uu = smem[m.u + lr * 6 + comp];
-        pg += smem[m.r + lr * 6 + comp] * uu;
+        pg += ru;
         pd += acc * uu;
       }
     }
@@ -377,7 +418,7 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
       }
     }
     TICK(c5);
-    cluster.sync();  // C: partials of every CTA are here
+    cluster_sync_aligned();  // C: partials of every CTA are here
     TICK(c6);
 #ifdef MPBA_PCG_TIMING
     tA += c1 - c0; tH += c2 - c1; tP += c3 - c2; tB += c4 - c3; tR += c5 - c4; tC += c6 - c5;
@@ -521,7 +562,7 @@ size_t pcg_cluster_carve(PcgClusterArgs& A) {
   c.zr = o;    o += A.nc;
   c.sc = o;    o += 8;
   o += o & 1;  // double2 access
-  c.stail = o; o += 2 * T;
+  c.stail = o; o += 4 * T;
   o += o & 1;
   c.glrp = 2 * o;
   o += (A.gpc + 4) / 2;
