@@ -284,6 +284,7 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
 #ifdef MPBA_PCG_TIMING
   long long pre_cyc[6] = {0, 0, 0, 0, 0, 0};
   long long upd_cyc[3] = {0, 0, 0};  // fold + alpha | x r p s | zs zr
+  long long row_cyc[3] = {0, 0, 0};  // row sums + warp reduce | barrier | restriction of w
 #endif
   apply_precond<true>(smem, smi, A, cluster, rank, CL, nrows PRE_PASS);
 
@@ -402,9 +403,22 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
       pd += __shfl_down_sync(FULL, pd, off);
     }
     if (lane == 0) reinterpret_cast<double2*>(smem + m.red)[warp] = make_double2(pg, pd);
+#ifdef MPBA_PCG_TIMING
+    const long long r1 = clock64();
+    row_cyc[0] += r1 - c4;
+#endif
     __syncthreads();  // w and the warp partials are complete
+#ifdef MPBA_PCG_TIMING
+    const long long r2 = clock64();
+    row_cyc[1] += r2 - r1;
+#endif
     if (A.G) restrict_to_all(smem, smi, A, cluster, rank, CL, m.w);  // Z^T w of the owned groups to every CTA
-    if (warp == 0) {  // warp 0 folds the warp partials (fixed tree) and lane k delivers the result to CTA k
+#ifdef MPBA_PCG_TIMING
+    row_cyc[2] += clock64() - r2;
+#endif
+    // the LAST warp folds the warp partials (fixed tree) and lane k delivers the result to CTA k: it owns no rows and
+    // no restriction task at the cluster sizes in use, so the fold runs beside the restrictions instead of behind one
+    if (warp == T / 32 - 1) {
       double2 v = lane < T / 32 ? reinterpret_cast<const double2*>(smem + m.red)[lane] : make_double2(0.0, 0.0);
       for (int off = 8; off > 0; off >>= 1) {
         v.x += __shfl_down_sync(FULL, v.x, off);
@@ -517,8 +531,9 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
            pre_cyc[0] / (iters + 1), pre_cyc[1] / (iters + 1), pre_cyc[2] / (iters + 1), pre_cyc[3] / (iters + 1),
            pre_cyc[4] / (iters + 1), pre_cyc[5] / (iters + 1), tU / (iters + 1),
            (tU - pre_cyc[0] - pre_cyc[1] - pre_cyc[2] - pre_cyc[3] - pre_cyc[4] - pre_cyc[5]) / (iters + 1));
-    printf("[pcg update cycles / iteration] fold+alpha %lld  xrps %lld  zszr %lld\n", upd_cyc[0] / (iters + 1),
-           upd_cyc[1] / (iters + 1), upd_cyc[2] / (iters + 1));
+    printf("[pcg update cycles / iteration] fold+alpha %lld  xrps %lld  zszr %lld | rowsum %lld  barrier %lld  restrict %lld\n",
+           upd_cyc[0] / (iters + 1), upd_cyc[1] / (iters + 1), upd_cyc[2] / (iters + 1), row_cyc[0] / (iters + 1),
+           row_cyc[1] / (iters + 1), row_cyc[2] / (iters + 1));
     A.scal[S_PCG_CYC_SPMV] = (double)(tH + tP);
     A.scal[S_PCG_CYC_REDUCE] = (double)(tA + tB + tC);
     A.scal[S_PCG_CYC_UPDATE] = (double)(tR + tU);
