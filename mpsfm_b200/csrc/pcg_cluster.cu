@@ -136,7 +136,9 @@ __device__ __forceinline__ void restrict_to_all(double* smem, const int* smi, co
       acc2 += smem[m.zloc + (idx + 64) * 7 + a] * smem[voff + idx + 64];
       acc3 += smem[m.zloc + (idx + 96) * 7 + a] * smem[voff + idx + 96];
     }
-    for (; idx < i1; idx += 32) acc += smem[m.zloc + idx * 7 + a] * smem[voff + idx];
+    if (idx < i1) acc += smem[m.zloc + idx * 7 + a] * smem[voff + idx];  // the tail on alternating chains
+    if (idx + 32 < i1) acc1 += smem[m.zloc + (idx + 32) * 7 + a] * smem[voff + idx + 32];
+    if (idx + 64 < i1) acc2 += smem[m.zloc + (idx + 64) * 7 + a] * smem[voff + idx + 64];
     acc = (acc + acc1) + (acc2 + acc3);
     for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(FULL, acc, off);
     if (lane < CL) {
@@ -150,7 +152,8 @@ __device__ __forceinline__ void restrict_to_all(double* smem, const int* smi, co
 // recurrence); otherwise it is read from the recurrence (m.zr) and the call holds no cluster barrier.
 template <bool DIRECT>
 __device__ __forceinline__ void apply_precond(double* smem, const int* smi, const PcgClusterArgs& A,
-                                              cg::cluster_group& cluster, int rank, int CL, int nrows PRE_ARG) {
+                                              cg::cluster_group& cluster, int rank, int CL, int nrows,
+                                              int gl_first /* group of row tid / 6 */ PRE_ARG) {
   const PcgClusterCarve& m = A.m;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 #ifdef MPBA_PCG_TIMING
@@ -172,14 +175,19 @@ __device__ __forceinline__ void apply_precond(double* smem, const int* smi, cons
     }
     const int zsrc = DIRECT ? m.rcall : m.zr;
     for (int task = warp; task < ntask; task += T / 32) {
-      double acc = 0.0, acc1 = 0.0;
+      double acc = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;  // four chains: the dot is shared-memory latency bound
+      const double* arow = smem + m.ainv + task * A.nc;
       int k = lane;
-      for (; k + 32 < A.nc; k += 64) {
-        acc += smem[m.ainv + task * A.nc + k] * smem[zsrc + k];
-        acc1 += smem[m.ainv + task * A.nc + k + 32] * smem[zsrc + k + 32];
+      for (; k + 96 < A.nc; k += 128) {
+        acc += arow[k] * smem[zsrc + k];
+        acc1 += arow[k + 32] * smem[zsrc + k + 32];
+        acc2 += arow[k + 64] * smem[zsrc + k + 64];
+        acc3 += arow[k + 96] * smem[zsrc + k + 96];
       }
-      if (k < A.nc) acc += smem[m.ainv + task * A.nc + k] * smem[zsrc + k];
-      acc += acc1;
+      if (k < A.nc) acc += arow[k] * smem[zsrc + k];
+      if (k + 32 < A.nc) acc1 += arow[k + 32] * smem[zsrc + k + 32];
+      if (k + 64 < A.nc) acc2 += arow[k + 64] * smem[zsrc + k + 64];
+      acc = (acc + acc1) + (acc2 + acc3);
       for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(FULL, acc, off);
       if (lane == 0) smem[m.ec + task] = acc;
     }
@@ -196,8 +204,11 @@ __device__ __forceinline__ void apply_precond(double* smem, const int* smi, cons
       z1 += smem[m.minv + lr * 36 + c * 6 + j + 1] * smem[m.r + lr * 6 + j + 1];
     }
     if (A.G) {
-      int gl = 0;
-      while (lr >= smi[m.glrp + gl + 1]) ++gl;
+      int gl = gl_first;  // looked up once per solve for the first pass (a chain of dependent loads otherwise)
+      if (q != tid) {
+        gl = 0;
+        while (lr >= smi[m.glrp + gl + 1]) ++gl;
+      }
 #pragma unroll
       for (int a = 0; a < 6; a += 2) {
         zc0 += smem[m.zloc + q * 7 + a] * smem[m.ec + gl * 7 + a];
@@ -286,7 +297,11 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
   long long upd_cyc[3] = {0, 0, 0};  // fold + alpha | x r p s | zs zr
   long long row_cyc[3] = {0, 0, 0};  // row sums + warp reduce | barrier | restriction of w
 #endif
-  apply_precond<true>(smem, smi, A, cluster, rank, CL, nrows PRE_PASS);
+  int gl_first = 0;
+  __syncthreads();  // the one-time loads above (glrp among them) are in place
+  if (A.G && tid < nrows * 6)
+    while (tid / 6 >= smi[m.glrp + gl_first + 1]) ++gl_first;
+  apply_precond<true>(smem, smi, A, cluster, rank, CL, nrows, gl_first PRE_PASS);
 
   // The scalars carried from one iteration to the next live in shared memory (written by thread 0, CTA barriers lie
   // between every write and the reads): as registers they were spilled to local memory, and every cluster barrier
@@ -510,7 +525,7 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
 #ifdef MPBA_PCG_TIMING
     upd_cyc[2] += clock64() - u2;
 #endif
-    apply_precond<false>(smem, smi, A, cluster, rank, CL, nrows PRE_PASS);
+    apply_precond<false>(smem, smi, A, cluster, rank, CL, nrows, gl_first PRE_PASS);
     if (tid == 0) {  // every thread is past its reads of the two (CTA barriers inside apply_precond)
       const double ig = 1.0 / gamma;
       smem[m.sc + SC_INV_GAMMA] = ig;
