@@ -392,13 +392,31 @@ __global__ void __launch_bounds__(T, 1) k_pcg_cluster(PcgClusterArgs A) {
         const int s0 = first ? s0_pre : smi[m.rp + lr], s1 = first ? s1_pre : smi[m.rp + lr + 1];
         double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
         int sl = s0;
+        {
+          // eight slots per round on eight chains (a row has ~27 deposits: the sum is a chain of dependent adds)
+          double b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
+          const double* dp = smem + m.dep + comp;
+          for (; sl + 7 < s1; sl += 8) {
+            a0 += dp[(size_t)sl * 6];
+            a1 += dp[(size_t)(sl + 1) * 6];
+            a2 += dp[(size_t)(sl + 2) * 6];
+            a3 += dp[(size_t)(sl + 3) * 6];
+            b0 += dp[(size_t)(sl + 4) * 6];
+            b1 += dp[(size_t)(sl + 5) * 6];
+            b2 += dp[(size_t)(sl + 6) * 6];
+            b3 += dp[(size_t)(sl + 7) * 6];
+          }
+          a0 += b0; a1 += b1; a2 += b2; a3 += b3;
+        }
         for (; sl + 3 < s1; sl += 4) {
           a0 += smem[m.dep + (size_t)sl * 6 + comp];
           a1 += smem[m.dep + (size_t)(sl + 1) * 6 + comp];
           a2 += smem[m.dep + (size_t)(sl + 2) * 6 + comp];
           a3 += smem[m.dep + (size_t)(sl + 3) * 6 + comp];
         }
-        for (; sl < s1; ++sl) a0 += smem[m.dep + (size_t)sl * 6 + comp];
+        if (sl < s1) a0 += smem[m.dep + (size_t)sl * 6 + comp];
+        if (sl + 1 < s1) a1 += smem[m.dep + (size_t)(sl + 1) * 6 + comp];
+        if (sl + 2 < s1) a2 += smem[m.dep + (size_t)(sl + 2) * 6 + comp];
         double dg = dg_pre, uu = uu_pre, ru = ru_pre;
         if (!first) {
           dg = 0.0;
