@@ -79,6 +79,7 @@ struct mpba_handle {
   // sharded solve (mpba_comm_init)
   ncclComm_t comm = nullptr;
   int rank = 0, world = 1;
+  int* d_agree = nullptr;  // one int of device memory: the ranks' agreement on a call's local validation result
 };
 
 // accessors for the other translation units of the library (integrate.cu): the handle's layout stays private here
@@ -1135,6 +1136,7 @@ void mpba_destroy(mpba_handle* h) {
   if (h->plan_hash_seen_pinned) cudaFreeHost(h->plan_hash_seen_pinned);
   if (h->h_stage) cudaFreeHost(h->h_stage);
   if (h->comm) nccl_api().CommDestroy(h->comm);
+  if (h->d_agree) cudaFree(h->d_agree);
   delete h;
 }
 
@@ -1201,7 +1203,24 @@ int mpba_comm_init(mpba_handle* h, int world, int rank, const void* id, const ch
   NC(nc.CommInitRank(&h->comm, world, uid, rank));
   h->world = world;
   h->rank = rank;
+  if (!h->d_agree) CU(cudaMalloc(&h->d_agree, sizeof(int)));
   return MPBA_OK;
+}
+
+// Sharded calls: a rank whose local checks failed (bad arguments, workspace too small) must not leave the others
+// blocked in their first collective.  Every rank contributes its local code; the minimum (codes are <= 0) is what all
+// of them return.  One 4-byte all-reduce and one synchronisation per sharded call.
+static int agree_on_rc(mpba_handle* h, int world, int rc_local) {
+  if (!h || !h->comm || world <= 1 || !h->d_agree) return rc_local;
+  int v = rc_local;
+  if (cudaSetDevice(h->device) != cudaSuccess) return rc_local;
+  if (cudaMemcpyAsync(h->d_agree, &v, sizeof(int), cudaMemcpyHostToDevice, h->stream) != cudaSuccess) return rc_local;
+  if (nccl_api().AllReduce(h->d_agree, h->d_agree, 1, ncclInt, ncclMin, h->comm, h->stream) != ncclSuccess) return rc_local;
+  if (cudaMemcpyAsync(&v, h->d_agree, sizeof(int), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess) return rc_local;
+  if (cudaStreamSynchronize(h->stream) != cudaSuccess) return rc_local;
+  if (v != MPBA_OK && rc_local == MPBA_OK)
+    return fail(h, v, "sharded call abandoned: another rank failed its local checks with code " + std::to_string(v));
+  return rc_local != MPBA_OK ? rc_local : v;
 }
 
 int mpba_kernel_times(const mpba_handle* h, double* ms, int64_t* launches) {
@@ -1366,6 +1385,7 @@ static int solve_impl(mpba_handle* h, const mpba_problem* prob, const mpba_shard
   NvtxRange nvtx_solve(shard ? "mpba_solve_sharded" : "mpba_solve");
   Ctx c;
   int rc = begin(h, prob, workspace, workspace_bytes, c, shard);
+  if (shard) rc = agree_on_rc(h, shard->world, rc);
   if (rc) return rc;
   if (!sum) return fail(h, MPBA_E_INVALID, "summary is NULL");
   mpba_options opt;

@@ -67,6 +67,22 @@ def main():
     ok = (res["iterations"][0] == res["iterations"][1] and res["accept"][0] == res["accept"][1]
           and res["cost_rel"] is not None and res["cost_rel"] <= 1e-10 and res["final_rel"] <= 1e-10
           and res["dq"] <= 1e-8 and res["dt"] <= 1e-8 and res["dX"] <= 1e-7 and res["replicas_identical"])
+    # one rank fails its LOCAL checks (workspace too small): every rank must come back with an error instead of the
+    # others waiting in their first collective, and the communicator must still be usable afterwards
+    keep = sh.workspace
+    if rank == world - 1:
+        sh.workspace = torch.empty(256, dtype=torch.uint8, device="cuda")
+    sh.reset_state()
+    try:
+        sh.solve(opt)
+        res["local_failure_reported"] = False
+    except engine.EngineError as e:
+        res["local_failure_reported"] = ("workspace too small" in str(e)) if rank == world - 1 else ("another rank" in str(e))
+    sh.workspace = keep
+    sh.reset_state()
+    again = sh.solve(opt)
+    res["solve_after_failure"] = again.num_iterations == sN.num_iterations and again.final_cost == sN.final_cost
+    ok = ok and res["local_failure_reported"] and res["solve_after_failure"]
     flags = torch.tensor([1.0 if ok else 0.0], device="cuda")
     dist.all_reduce(flags, op=dist.ReduceOp.MIN)
     if rank == 0:
