@@ -141,18 +141,44 @@ extern "C" int mpba_host_layout_create(int32_t C, int32_t P, int32_t N, const in
     std::vector<int32_t> nat((size_t)N), by_img;
     for (int32_t k = 0; k < N; ++k) nat[k] = k;
     counting_sort(nat, obs_img, C, by_img, ptr_img);
+    lap("  by image");
     L->cm_src.resize((size_t)N);
     L->cm_pt.resize((size_t)N);
     std::atomic<int32_t> next_img(0);
+    // An image's segment of by_img is in natural order (the counting sort is stable), so a STABLE sort by point gives
+    // (point, natural index) order: LSD radix sort on the point index, 11 bits per pass (two passes up to 4 M points)
+    // instead of a comparison sort of 64-bit keys.
+    int pt_bits = 1;
+    while (pt_bits < 31 && ((int64_t)1 << pt_bits) < (int64_t)P) ++pt_bits;
+    const int passes = (pt_bits + 10) / 11;
     auto sort_images = [&] {
-      std::vector<uint64_t> keys;
+      std::vector<uint64_t> keys, tmp;
+      std::vector<int32_t> hist((size_t)2048);
       for (;;) {
         const int32_t i = next_img.fetch_add(1);
         if (i >= C) break;
         const int64_t b = ptr_img[i], e = ptr_img[i + 1];
-        keys.resize((size_t)(e - b));
+        const size_t n = (size_t)(e - b);
+        keys.resize(n);
+        tmp.resize(n);
         for (int64_t k = b; k < e; ++k) keys[k - b] = ((uint64_t)(uint32_t)obs_pt[by_img[k]] << 32) | (uint32_t)by_img[k];
-        std::sort(keys.begin(), keys.end());
+        if (n < 64) {
+          std::sort(keys.begin(), keys.end());  // (point, natural index): the same order
+        } else {
+          for (int pass = 0; pass < passes; ++pass) {
+            const int shift = 32 + 11 * pass;
+            std::fill(hist.begin(), hist.end(), 0);
+            for (size_t k = 0; k < n; ++k) ++hist[(keys[k] >> shift) & 2047u];
+            int32_t run = 0;
+            for (int d = 0; d < 2048; ++d) {
+              const int32_t c = hist[d];
+              hist[d] = run;
+              run += c;
+            }
+            for (size_t k = 0; k < n; ++k) tmp[(size_t)hist[(keys[k] >> shift) & 2047u]++] = keys[k];
+            keys.swap(tmp);
+          }
+        }
         for (int64_t k = b; k < e; ++k) {
           L->cm_src[k] = (int32_t)(keys[k - b] & 0xffffffffu);
           L->cm_pt[k] = (int32_t)(keys[k - b] >> 32);
@@ -167,6 +193,7 @@ extern "C" int mpba_host_layout_create(int32_t C, int32_t P, int32_t N, const in
       sort_images();
     }
   }
+  lap("  inside images");
   ptr_pt.assign((size_t)P + 1, 0);
   for (int64_t k = 0; k < N; ++k) ++ptr_pt[(size_t)L->cm_pt[k] + 1];
   for (int32_t p = 0; p < P; ++p) ptr_pt[p + 1] += ptr_pt[p];
@@ -190,6 +217,7 @@ extern "C" int mpba_host_layout_create(int32_t C, int32_t P, int32_t N, const in
       place(0);
     }
   }
+  lap("  track order");
   L->pt_ptr.assign(ptr_pt.begin(), ptr_pt.end());
   L->img_ptr.assign(ptr_img.begin(), ptr_img.end());
   L->pm_img.resize((size_t)N);
